@@ -1,0 +1,302 @@
+#!/usr/bin/env python
+"""bench.py — GRCN frames/sec on B200 (BASELINE.json metric), one process per GPU.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--mode inference|train] [--impl ours|reference]
+
+Default workload = BASELINE.json configs[1]: gaze_grcn inference, 256 clips x T=35 per GPU, 7x7 grid,
+hidden 256, bf16 operands / fp32 accumulate, synthetic C3D conv5b features [B,T,1024,7,7] and
+random-init weights (reference init).  A "step" is one forward pass of the whole hot path
+(pack -> projection -> input convs -> T recurrent steps -> composed head -> softmax+loss) over one batch.
+`value`: inputs resident in HBM.  `e2e`: through the model-class API with pinned HOST buffers, H2D of the
+features + gt and D2H of the gaze maps + loss inside the timed region.
+`--impl reference`: the oracle's torch-CPU fp32 restatement of the reference graph (TensorFlow 1 cannot be
+installed here) on the host cores, a bounded sample of the same workload per step.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np
+import torch
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--mode", default="inference", choices=["inference", "train"])
+    ap.add_argument("--model", default="gaze_grcn")
+    ap.add_argument("--batch", type=int, default=256, help="clips per GPU")
+    ap.add_argument("--T", type=int, default=35)
+    ap.add_argument("--hidden", type=int, default=256)
+    ap.add_argument("--grid", type=int, default=7)
+    ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--cpu-clips", type=int, default=2)
+    return ap.parse_args()
+
+
+class ClockSampler(object):
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+                for nm, v in zip(names, r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d["hbm_gbs"], d["bf16_tflops"], d.get("bf16_tflops_sustained", d["bf16_tflops"]), "measured"
+    return 6650.0, 1590.0, 1400.0, "fallback"
+
+
+def flops_per_frame(Ch, G=7, Cin=512, Cfeat=1024, lstm=False):
+    """ALGORITHMIC flops (in-bounds taps only), SURVEY.md 8(d)."""
+    P = G * G
+    inb = (3 * G - 2) ** 2
+    ng_x = 4 if lstm else 3
+    return {"proj": 2.0 * P * Cfeat * Cin, "i2h": 2.0 * ng_x * inb * Cin * Ch, "h2h": 2.0 * 3 * inb * Ch * Ch}
+
+
+# ----------------------------------------------------------------------------------------------
+def cpu_reference_step(model, p, c3d, gt, train=False):
+    """The oracle's torch-CPU fp32 restatement with the reference's op structure (T-unrolled, per-gate convs)."""
+    from oracle import model_oracle as O
+    pt = O.to_torch(p, torch.float32, requires_grad=train)
+    x = torch.from_numpy(c3d)
+    g = torch.from_numpy(gt)
+    with torch.set_grad_enabled(train):
+        logits = O.recurrent_network(model, pt, c3d=x)
+        probs = O.softmax_2d(logits)
+        loss = O.loss_fn(logits, g, "xentropy")
+        if train:
+            loss.backward()
+    return float(loss), probs
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    from oracle import model_oracle as O
+    from recurrent_gaze_prediction_b200 import synthetic as SY
+    B = args.cpu_clips
+    p = O.init_params(args.model, hidden=args.hidden, T=args.T, grid=args.grid, seed=0, regime="R")
+    rng = np.random.RandomState(0)
+    c3d = SY.make_c3d(rng, B, args.T, 1024, args.grid)
+    GH = args.grid if args.model == "gaze_grcn77" else 49
+    gt, _ = SY.make_gazemaps(rng, B, args.T, GH, GH, normalize=True)
+    train = args.mode == "train"
+    for _ in range(args.warmup):
+        cpu_reference_step(args.model, p, c3d, gt, train)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cpu_reference_step(args.model, p, c3d, gt, train)
+    dt = (time.perf_counter() - t0) / args.steps
+    fps = B * args.T / dt
+    cores = torch.get_num_threads()
+    sample = "%d clips x T=%d per step (bounded sample of the %d-clip workload), torch-CPU fp32 restatement of the " \
+             "reference graph (oracle/model_oracle.py), %d threads of %d cores" % (B, args.T, args.batch, cores,
+                                                                                 os.cpu_count())
+    out = {"impl": "reference", "metric": metric_name(args), "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
+           "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
+           "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "config": workload_config(args),
+           "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample},
+           "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(out))
+
+
+def metric_name(args):
+    return "GRCN frames/sec (%s)" % ("fwd" if args.mode == "inference" else "train: fwd+BPTT+Adam")
+
+
+def workload_config(args):
+    return {"workload": "%s %s, %d clips/GPU x T=%d, %dx%d grid, C3D conv5b 1024x%dx%d -> proj 512, hidden %d, "
+                        "49x49 gaze maps" % (args.model, args.mode, args.batch, args.T, args.grid, args.grid,
+                                             args.grid, args.grid, args.hidden),
+            "clips_per_gpu": args.batch, "T": args.T, "grid": args.grid, "hidden": args.hidden,
+            "l2_policy": "inputs larger than L2 (features 1.8 GB/step at the default size)",
+            "parallelism": "dp%d (clips sharded, no data-path collective in inference)" % args.gpus}
+
+
+# ----------------------------------------------------------------------------------------------
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    import torch.distributed as dist
+    from oracle import model_oracle as O          # parameter init + cpu_baseline leg only
+    from recurrent_gaze_prediction_b200 import synthetic as SY
+    from recurrent_gaze_prediction_b200.engine import GazeEngine
+    from recurrent_gaze_prediction_b200 import lib as L
+
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    B, T, G, Ch = args.batch, args.T, args.grid, args.hidden
+    dtype = 1 if args.dtype == "bf16" else 0
+    train = args.mode == "train"
+    p = O.init_params(args.model, hidden=Ch, T=T, grid=G, seed=0, regime="R")
+    eng = GazeEngine(args.model, B=B, T=T, G=G, Ch=Ch, dtype=dtype, device=dev, train=train)
+    eng.load_tf_params(p)
+    GH = eng.GH
+    # synthetic inputs: a small pool tiled to the batch (host RNG cost), distinct per rank
+    rng = np.random.RandomState(1234 + rank)
+    pool = min(B, 8)
+    c3d_pool = SY.make_c3d(rng, pool, T, 1024, G)
+    gt_pool, _ = SY.make_gazemaps(rng, pool, T, GH, GH, normalize=True)
+    reps = (B + pool - 1) // pool
+    c3d_h = torch.from_numpy(np.tile(c3d_pool, (reps, 1, 1, 1, 1))[:B]).pin_memory()
+    gt_h = torch.from_numpy(np.tile(gt_pool, (reps, 1, 1, 1))[:B]).pin_memory()
+    c3d_d, gt_d = c3d_h.to(dev), gt_h.to(dev)
+    probs_h = torch.empty(B, T, GH, GH, dtype=torch.float32).pin_memory()
+    loss_h = torch.empty(1, dtype=torch.float32).pin_memory()
+
+    def step_resident():
+        eng.forward(c3d=c3d_d, gt=gt_d)
+        if train:
+            eng.backward()
+            eng.optimizer_step()
+
+    def step_e2e():
+        c3d_d.copy_(c3d_h, non_blocking=True)
+        gt_d.copy_(gt_h, non_blocking=True)
+        step_resident()
+        if not train:
+            probs_h.copy_(eng.probs, non_blocking=True)
+        loss_h.copy_(eng.loss, non_blocking=True)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup, sample_clocks=False):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        cs = ClockSampler(local) if sample_clocks else None
+        if cs:
+            cs.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = eng.lib.launches
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        clocks = cs.stop() if cs else None
+        t = torch.tensor([ms], device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t[0]) / steps, clocks, (eng.lib.launches - l0)
+
+    ms_step, clocks, launches = timed(step_resident, args.steps, args.warmup, sample_clocks=(rank == 0))
+    frames = B * T * world
+    value = frames / (ms_step * 1e-3)
+    e2e = None
+    if not args.no_e2e:
+        ms_e2e, _, _ = timed(step_e2e, max(2, args.steps // 2), 2)
+        h2d = c3d_h.numel() * 4 + gt_h.numel() * 4
+        d2h = (0 if train else probs_h.numel() * 4) + 4
+        e2e = {"value": frames / (ms_e2e * 1e-3), "unit": "frames/s", "ms_per_step": ms_e2e,
+               "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h}
+
+    # roofline of the dominant kernel: the input-half conv GEMM (all T frames at once), timed live with CUDA events
+    hbm, tf_burst, tf_sus, which = peaks()
+    fl = flops_per_frame(Ch, G, lstm=eng.lstm)
+    roof = None
+    if rank == 0:
+        evs = eng.time_stages(c3d_d, gt_d, iters=3)
+        i2h_ms = evs["i2h"]
+        ach = fl["i2h"] * B * T / (i2h_ms * 1e-3) / 1e12
+        roof = {"kernel": "tapgemm i2h (3x3 SAME conv, all T frames, M=%d N=%d K=9x512)" % (T * B * eng.S, eng.ngx * Ch),
+                "bound": "tensor", "achieved": ach, "peak": tf_sus, "unit": "TFLOP/s", "frac": ach / tf_sus,
+                "peak_source": which + " (sustained bf16; burst %.1f)" % tf_burst, "traffic": None,
+                "ms_per_launch": i2h_ms, "stage_ms": evs}
+
+    cpu = None
+    if rank == 0 and not args.no_cpu_baseline:
+        nb = args.cpu_clips
+        pc = O.init_params(args.model, hidden=Ch, T=T, grid=G, seed=0, regime="R")
+        c3 = c3d_pool[:nb]
+        g = gt_pool[:nb]
+        cpu_reference_step(args.model, pc, c3, g, train)
+        t0 = time.perf_counter()
+        n = 0
+        while time.perf_counter() - t0 < 10.0 or n < 2:
+            cpu_reference_step(args.model, pc, c3, g, train)
+            n += 1
+        dt = (time.perf_counter() - t0) / n
+        cpu = {"value": nb * T / dt, "unit": "frames/s", "cores": torch.get_num_threads(), "kind": "port",
+               "sample": "%d clips x T=%d per pass, %d passes, torch-CPU fp32 restatement of the reference graph "
+                         "(oracle/model_oracle.py; TF1 not installable)" % (nb, T, n)}
+    if rank == 0:
+        out = {"metric": metric_name(args), "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+               "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+               "vs_baseline": None, "dtype": args.dtype, "data": "synthetic", "config": workload_config(args),
+               "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu,
+               "step_tflops": sum(fl.values()) * B * T / (ms_step * 1e-3) / 1e12}
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,141 @@
+/* rgp.h — C-ABI of librgp_sm100.so: the B200 (sm_100a) hot path of Recurrent Gaze Prediction.
+ *
+ * The reference (yj-yu/Recurrent_Gaze_Prediction) has no FFI layer: every numeric site is a
+ * TensorFlow-1 / NumPy library call made from Python.  Each entry point below names the
+ * reference call site(s) it replaces (paths relative to the reference root).  All pointers are
+ * DEVICE pointers owned by the caller unless a comment says "host"; `stream` is a cudaStream_t
+ * passed as void*; every function returns 0 on success or a negative code, never throws, never
+ * allocates device memory (workspace sizes are queried / documented per op) and records a
+ * message retrievable with rgp_last_error().  dtype: 0 = fp32 operands (CUDA-core FMA engine),
+ * 1 = bf16 operands with fp32 accumulation (tcgen05 / TMEM / TMA engine).
+ *
+ * Row layouts ("q-layout" / "p-layout"), see DESIGN.md section 3:
+ *   a G x G frame is stored as Wp = G+1 columns and G+1 rows of C-channel vectors (frame stride
+ *   S = Wp*Wp rows); position (y,x) lives at p-row  f*S + (y+1)*Wp + (x+1)  (operand layout,
+ *   zero everywhere else) and produces its output at q-row f*S + y*Wp + x.  A 3x3 SAME conv tap
+ *   (ky,kx) is then the constant row shift ky*Wp + kx, i.e. a plain 2-D TMA box.
+ */
+#ifndef RGP_H_
+#define RGP_H_
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RGP_MAX_TAPS 16
+
+/* epilogue selectors of rgp_tapgemm */
+enum {
+  RGP_EPI_STORE_F32 = 0,   /* out_f32[m*ldo + n] (+)= acc                                          */
+  RGP_EPI_PROJ = 1,        /* dense row -> p-row, + bias, store operand dtype (gaze_grcn.py:239-242) */
+  RGP_EPI_GRU_ZR = 2,      /* z = sig(acc+Xz) ; r = sig(acc+Xr) ; rh = r*h   (gaze_grcn.py:108-119)  */
+  RGP_EPI_GRU_C = 3,       /* c = tanh(acc+Xc); h' = z*h + (1-z)*c ; BN-scale (gaze_grcn.py:122-127,325) */
+  RGP_EPI_HEAD = 4,        /* composed transposed-conv head scatter + out_b  (gaze_grcn.py:326-366)  */
+  RGP_EPI_STORE_OP_P = 5,  /* store operand dtype at p-row (valid rows only): dX of a SAME conv       */
+  RGP_EPI_STORE_OP = 6     /* store operand dtype at row m                                            */
+};
+
+/* One "tap GEMM":  acc[m,n] = sum_tap sum_k A[m + tap_off[tap], k] * Bw[tap*N + n, k]
+ * A: [rowsA, lda] operand dtype, row-major.  Bw: [ntaps*N, K] operand dtype (K contiguous).
+ * This single contraction serves the 1x1 projection, the 3x3 SAME convolutions of the ConvGRU /
+ * ConvLSTM cells (input half for all T frames at once, recurrent half per step) and the
+ * composed transposed-convolution head. */
+typedef struct rgp_tapgemm_args {
+  const void* A; long long rowsA; int lda;
+  const void* Bw;
+  int M, N, K, ntaps;
+  int tap_off[RGP_MAX_TAPS];
+  int dtype;            /* 0 fp32, 1 bf16 */
+  int engine;           /* 0 = by dtype (fp32 -> FMA engine, bf16 -> tcgen05 engine); 1 = force the FMA engine */
+  int epi;              /* RGP_EPI_* */
+  int accumulate;       /* STORE_F32 only: out += acc */
+  /* geometry of the row layouts */
+  int S, Wp, G;         /* q-layout of the M rows: frame stride, width, valid extent */
+  int P;                /* PROJ: dense rows per frame (G*G) */
+  int So, Wo, pado;     /* secondary output layout (PROJ: p-layout S,Wp,1; GRU_C: head input layout) */
+  int Ch;               /* hidden width */
+  int B, T, t;          /* clips, frames per clip, current step (GRU_C / HEAD time-major -> [B,T]) */
+  /* generic pointer slots; meaning per epilogue is documented in DESIGN.md section 4 */
+  float* out_f32; int ldo;
+  void* out_op;  void* out_op2;
+  const float* xg; int ldx;     /* precomputed input-half pre-activations, q-layout */
+  const float* hprev_f32;       /* p-layout fp32 master state */
+  float* hnext_f32;
+  float* z_f32;                 /* q-layout [M, Ch] */
+  float* save_r; float* save_c; /* optional (training): q-layout [M, Ch] */
+  const float* bias;            /* PROJ: [N]; HEAD: [1]; GRU_C: bn scale [Ch] (may be NULL) */
+  const float* bias2;           /* GRU_C: bn shift [Ch] (may be NULL) */
+  float alpha;                  /* GRU_C: 1/sqrt(1+eps) of the frozen batch-norm (gaze_grcn.py:325) */
+} rgp_tapgemm_args;
+
+int rgp_tapgemm(const rgp_tapgemm_args* a, void* stream);
+
+/* ---- model path ------------------------------------------------------------------------- */
+/* gaze_grcn.py:225-227 (tf.transpose NCHW->NHWC of the C3D blob) fused with the fp32->operand
+ * cast and the [B,T]->time-major reorder: c3d [B,T,C,P] fp32 -> out [(t*B+b)*P + p, C]. */
+int rgp_pack_c3d(const float* c3d, void* out, int B, int T, int C, int P, int dtype, void* stream);
+/* embedded features [B,T,G,G,C] fp32 (BASELINE 'L1' entry, after the projection) -> p-layout */
+int rgp_pack_emb(const float* emb, void* out, int B, int T, int G, int C, int dtype, void* stream);
+/* fp32 -> operand dtype cast of a flat buffer (weights after an optimiser step) */
+int rgp_cast(const float* src, void* dst, long long n, int dtype, void* stream);
+/* gaze_grcn77.py:206-211: logits[b,t,y,x] = h . out_W + out_b from the p-layout fp32 state */
+int rgp_fc_head(const float* h_f32, const float* out_W, const float* out_b, float* logits,
+                int B, int T, int t, int G, int Ch, void* stream);
+/* ConvLSTM gate maths, gaze_lstm.py:112-133 (bugs preserved), after the hidden conv GEMM */
+int rgp_lstm_gates(const float* xg, int ldx, const float* hconv, const float* wci, const float* wcf,
+                   const float* wco, float* c_f32, float* h_f32, void* h_op_next, void* hs_op,
+                   int B, int G, int Ch, int So, int Wo, int pado, int dtype, float* save, void* stream);
+/* head weight composition (weight space, once per weight version): gaze_grcn.py:292-314,326-366.
+ * w1 [5,5,64,Ch], w2 [5,5,32,64], w3 [7,7,12,32], out_w [12] fp32 (TF layouts) ->
+ * w123 [19,19,Ch] fp32 (workspace w23 [11,11,64], w3f [7,7,32]) and the operand-dtype tap matrix
+ * bhead [16*48, Ch]. */
+int rgp_head_compose(const float* w1, const float* w2, const float* w3, const float* out_w,
+                     float* w3f, float* w23, float* w123, void* bhead, int Ch, int dtype, void* stream);
+/* model_util.py:61-72 + gaze_rnn.py:149-159,381-408: per-frame spatial softmax, soft-label
+ * cross-entropy (or l2), and d(loss)/d(logits).  loss_type 0 xentropy, 1 l2, 2 KLD.
+ * frame_loss [n_frames] fp32 per-frame partial losses (already divided by B*T);
+ * probs / dlogits may be NULL. */
+int rgp_softmax_xent_fwd_bwd(const float* logits, const float* gt, float* probs, float* dlogits,
+                             float* frame_loss, int n_frames, int hw, float inv_bt, int loss_type,
+                             void* stream);
+/* deterministic sum of n floats into out[0] (double accumulation) */
+int rgp_reduce_sum(const float* x, long long n, float* out, void* stream);
+
+/* ---- optimiser: base.py:262-297, gaze_rnn.py:435-444 ------------------------------------ */
+/* sumsq[0] += sum g^2 in double (call rgp_zero first); then clip + TF-Adam in one pass. */
+int rgp_sumsq(const float* g, long long n, double* sumsq, void* stream);
+/* lr_t = lr*sqrt(1-beta2^t)/(1-beta1^t) is formed on the host in double (TF does the same in
+ * its python wrapper); clip <= 0 disables clipping; p_op (may be NULL) receives the operand-dtype copy. */
+int rgp_gradnorm_clip_adam(float* p, const float* g, float* m, float* v, long long n,
+                           const double* sumsq, float clip, float lr_t, float beta1, float beta2,
+                           float eps, void* p_op, int dtype, void* stream);
+int rgp_zero(void* p, long long bytes, void* stream);
+
+/* ---- saliency metrics: evaluation_metrics.py -------------------------------------------- */
+/* resize stand-in for skimage.transform.resize(order=3) (see oracle/metrics_oracle.py) */
+int rgp_resize_bicubic(const double* src, double* dst, int n, int h, int w, int oh, int ow,
+                       int mode_nearest, void* stream);
+/* evaluation_metrics.py:15-17,207-236 (+NSS): per frame: out[f*4+{0,1,2}] = sim, cc, nss; maps f64 */
+int rgp_sim_cc_nss(const double* pred, const double* gt, const uint8_t* fix, double* out,
+                   int n, int hw, void* stream);
+/* evaluation_metrics.py:42-98: AUC-Judd per frame.  sal [n,hw] f64 (already jittered+normalised
+ * by rgp_normalize_range), fix [n,hw] u8.  counts [n,maxfix] int64 = #{S >= thr_k} (bit-exact
+ * contract), auc [n] f64.  workspace: thr [n,maxfix] f64. */
+int rgp_auc_judd(const double* sal, const uint8_t* fix, double* thr, long long* counts, double* auc,
+                 int n, int hw, int maxfix, void* stream);
+/* evaluation_metrics.py:101-204: AUC-Borji / shuffled with host-drawn index tensor
+ * idx [n, nfix_max, nrep] int32 (-1 = absent), nfix [n]; auc [n] f64; tp/fp counts exported. */
+int rgp_auc_sampled(const double* sal, const uint8_t* fix, const int* idx, double* auc,
+                    int n, int hw, int nfix_max, int nrep, double step, void* stream);
+/* x <- (x + jitter*1e-7 - min)/(max-min) per frame (evaluation_metrics.py:78-81,15-17) */
+int rgp_normalize_range(double* x, const double* jitter, int n, int hw, void* stream);
+
+const char* rgp_last_error(void);
+int rgp_version(void);
+/* 1 if the tcgen05 engine can run on the current device (sm_100), else 0 */
+int rgp_has_tcgen05(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

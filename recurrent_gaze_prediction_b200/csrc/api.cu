@@ -1,0 +1,49 @@
+// api.cu — C-ABI plumbing: error slot, version, engine dispatch of rgp_tapgemm.
+#include <stdarg.h>
+#include <string.h>
+#include "common.cuh"
+
+namespace rgp {
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int check_launch(const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("%s: %s", what, cudaGetErrorString(e));
+    return -5;
+  }
+  return 0;
+}
+}  // namespace rgp
+
+extern "C" {
+
+const char* rgp_last_error(void) { return rgp::g_err; }
+int rgp_version(void) { return 100; }
+
+int rgp_has_tcgen05(void) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+  cudaDeviceProp p;
+  if (cudaGetDeviceProperties(&p, dev) != cudaSuccess) return 0;
+  return p.major == 10 ? 1 : 0;
+}
+
+int rgp_tapgemm(const rgp_tapgemm_args* a, void* stream) {
+  RGP_CHECK_ARG(a != nullptr, "rgp_tapgemm: null args");
+  RGP_CHECK_ARG(a->ntaps >= 1 && a->ntaps <= RGP_MAX_TAPS, "rgp_tapgemm: ntaps=%d out of range", a->ntaps);
+  RGP_CHECK_ARG(a->M > 0 && a->N > 0 && a->K > 0, "rgp_tapgemm: bad shape M=%d N=%d K=%d", a->M, a->N, a->K);
+  RGP_CHECK_ARG(a->dtype == 0 || a->dtype == 1, "rgp_tapgemm: dtype %d", a->dtype);
+  RGP_CHECK_ARG(a->epi >= 0 && a->epi <= RGP_EPI_STORE_OP, "rgp_tapgemm: unknown epilogue %d", a->epi);
+  if (a->dtype == 1 && a->engine != 1) return rgp::tapgemm_tc(*a, (cudaStream_t)stream);
+  return rgp::tapgemm_simt(*a, (cudaStream_t)stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,159 @@
+// common.cuh — shared device helpers and the fused epilogues of the tap-GEMM engines.
+// Reference arithmetic cited per epilogue (paths relative to the reference root).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include "../../include/rgp.h"
+
+namespace rgp {
+
+void set_error(const char* fmt, ...);
+int check_launch(const char* what);
+
+#define RGP_CHECK_ARG(cond, ...)                 \
+  do {                                           \
+    if (!(cond)) {                               \
+      rgp::set_error(__VA_ARGS__);               \
+      return -22;                                \
+    }                                            \
+  } while (0)
+
+template <typename T> struct OpT;
+template <> struct OpT<float> {
+  static __device__ __forceinline__ float ld(const float* p) { return *p; }
+  static __device__ __forceinline__ void st(float* p, float v) { *p = v; }
+};
+template <> struct OpT<__nv_bfloat16> {
+  static __device__ __forceinline__ float ld(const __nv_bfloat16* p) { return __bfloat162float(*p); }
+  static __device__ __forceinline__ void st(__nv_bfloat16* p, float v) { *p = __float2bfloat16_rn(v); }
+};
+
+// accurate libm forms: the gates sit in the epilogue, their cost is noise next to the GEMM, and
+// the fp32 parity bar (1e-4 relative on the gaze maps) leaves no room for ex2.approx on tiny pre-activations
+__device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + expf(-x)); }
+__device__ __forceinline__ float tanhf_(float x) { return tanhf(x); }
+
+// Per-row geometry computed once per output row of a tile.
+struct RowInfo {
+  int m;
+  bool inrange;   // m < M
+  bool valid;     // row is a real (y<G, x<G) position of its frame
+  long long prow; // p-layout row of this position in the primary geometry (m + Wp + 1)
+  long long orow; // row in the secondary output layout (PROJ: p-row; GRU_C: head-input row)
+  long long obase;// HEAD: element offset of logits[b,t,0,0]; hy, hx = 6a-3, 6b-3
+  int hy, hx;
+};
+
+__device__ __forceinline__ RowInfo make_row(const rgp_tapgemm_args& a, int m) {
+  RowInfo r;
+  r.m = m;
+  r.inrange = m < a.M;
+  r.valid = false;
+  r.prow = 0; r.orow = 0; r.obase = 0; r.hy = 0; r.hx = 0;
+  if (!r.inrange) return r;
+  switch (a.epi) {
+    case RGP_EPI_PROJ: {
+      int f = m / a.P, p = m - f * a.P;
+      int y = p / a.G, x = p - y * a.G;
+      r.valid = true;
+      r.orow = (long long)f * a.So + (y + a.pado) * a.Wo + (x + a.pado);
+      break;
+    }
+    case RGP_EPI_HEAD: {
+      int f = m / a.S, q = m - f * a.S;
+      int ya = q / a.Wp, xb = q - ya * a.Wp;
+      r.valid = (ya < 9) && (xb < 9);
+      int t = f / a.B, b = f - t * a.B;   // frames are time-major
+      r.obase = ((long long)b * a.T + t) * 2401;
+      r.hy = 6 * ya - 3; r.hx = 6 * xb - 3;
+      break;
+    }
+    case RGP_EPI_STORE_F32:
+    case RGP_EPI_STORE_OP:
+      r.valid = true;
+      break;
+    default: {
+      int f = m / a.S, q = m - f * a.S;
+      int y = q / a.Wp, x = q - y * a.Wp;
+      r.valid = (y < a.G) && (x < a.G);
+      r.prow = (long long)m + a.Wp + 1;
+      if (a.epi == RGP_EPI_GRU_C && a.out_op2)
+        r.orow = (long long)f * a.So + (y + a.pado) * a.Wo + (x + a.pado);
+      break;
+    }
+  }
+  return r;
+}
+
+// One output element. TA = operand dtype.
+template <typename TA>
+__device__ __forceinline__ void epi_elem(const rgp_tapgemm_args& a, const RowInfo& r, int n, float acc) {
+  if (!r.inrange || n >= a.N) return;
+  switch (a.epi) {
+    case RGP_EPI_STORE_F32: {
+      float* o = a.out_f32 + (long long)r.m * a.ldo + n;
+      *o = a.accumulate ? (*o + acc) : acc;
+      break;
+    }
+    case RGP_EPI_STORE_OP: {
+      OpT<TA>::st((TA*)a.out_op + (long long)r.m * a.ldo + n, acc);
+      break;
+    }
+    case RGP_EPI_STORE_OP_P: {
+      if (r.valid) OpT<TA>::st((TA*)a.out_op + r.prow * a.ldo + n, acc);
+      break;
+    }
+    case RGP_EPI_PROJ: {  // gaze_grcn.py:239-242 xw_plus_b, written straight into the conv operand layout
+      OpT<TA>::st((TA*)a.out_op + r.orow * a.ldo + n, acc + a.bias[n]);
+      break;
+    }
+    case RGP_EPI_GRU_ZR: {  // gaze_grcn.py:108-119
+      float pre = acc + a.xg[(long long)r.m * a.ldx + n];
+      float s = sigmoidf_(pre);
+      if (n < a.Ch) {
+        a.z_f32[(long long)r.m * a.Ch + n] = s;
+      } else {
+        int j = n - a.Ch;
+        if (a.save_r) a.save_r[(long long)r.m * a.Ch + j] = s;
+        if (r.valid) {
+          float hp = a.hprev_f32[r.prow * a.Ch + j];
+          OpT<TA>::st((TA*)a.out_op + r.prow * a.Ch + j, s * hp);   // r (.) h, the operand of U
+        }
+      }
+      break;
+    }
+    case RGP_EPI_GRU_C: {  // gaze_grcn.py:122-127 ; BN-scale gaze_grcn.py:325
+      float pre = acc + a.xg[(long long)r.m * a.ldx + 2 * a.Ch + n];
+      float c = tanhf_(pre);
+      if (a.save_c) a.save_c[(long long)r.m * a.Ch + n] = c;
+      if (r.valid) {
+        float z = a.z_f32[(long long)r.m * a.Ch + n];
+        float hp = a.hprev_f32[r.prow * a.Ch + n];
+        float hn = z * hp + (1.0f - z) * c;
+        a.hnext_f32[r.prow * a.Ch + n] = hn;
+        OpT<TA>::st((TA*)a.out_op + r.prow * a.Ch + n, hn);
+        if (a.out_op2) {
+          float v = hn;
+          if (a.bias) v = a.bias[n] * (hn * a.alpha) + a.bias2[n];
+          OpT<TA>::st((TA*)a.out_op2 + r.orow * a.Ch + n, v);
+        }
+      }
+      break;
+    }
+    case RGP_EPI_HEAD: {  // composed head: class n = ry*6+rx -> logits[b,t,6a+ry-3,6b+rx-3]
+      if (r.valid && n < 36) {
+        int ry = n / 6, rx = n - ry * 6;
+        int Y = r.hy + ry, X = r.hx + rx;
+        if (Y >= 0 && Y < 49 && X >= 0 && X < 49) a.out_f32[r.obase + Y * 49 + X] = acc + a.bias[0];
+      }
+      break;
+    }
+  }
+}
+
+int tapgemm_simt(const rgp_tapgemm_args& a, cudaStream_t s);
+int tapgemm_tc(const rgp_tapgemm_args& a, cudaStream_t s);
+
+}  // namespace rgp

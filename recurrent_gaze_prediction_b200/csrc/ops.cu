@@ -1,0 +1,426 @@
+// ops.cu — bandwidth-bound kernels of the RGP path: layout packing, gate maths of the ConvLSTM,
+// head weight composition, spatial softmax + loss, gradient norm + clip + TF-Adam.
+#include "common.cuh"
+
+namespace rgp {
+
+// ---------------------------------------------------------------------------------------------
+// pack: gaze_grcn.py:225-227 (NCHW -> NHWC transpose of the C3D blob) + cast + time-major reorder
+// ---------------------------------------------------------------------------------------------
+template <typename TA>
+__global__ void __launch_bounds__(256) pack_c3d_kernel(const float* __restrict__ c3d, TA* __restrict__ out,
+                                                        int B, int T, int C, int P) {
+  extern __shared__ float tile[];  // [64][P+1]
+  const int f_in = blockIdx.x;     // b*T + t
+  const int b = f_in / T, t = f_in - b * T;
+  const int c0 = blockIdx.y * 64;
+  const float* src = c3d + ((long long)f_in * C + c0) * P;
+  const int n = 64 * P;
+  for (int i = threadIdx.x; i < n; i += 256) {
+    int c = i / P, p = i - c * P;
+    tile[c * (P + 1) + p] = src[i];
+  }
+  __syncthreads();
+  TA* dst = out + ((long long)(t * B + b) * P) * C + c0;
+  for (int i = threadIdx.x; i < n; i += 256) {
+    int p = i >> 6, c = i & 63;
+    OpT<TA>::st(dst + (long long)p * C + c, tile[c * (P + 1) + p]);
+  }
+}
+
+// emb [B,T,G,G,C] fp32 -> p-layout [(t*B+b)*S + (y+1)*Wp + x+1, C]
+template <typename TA>
+__global__ void __launch_bounds__(256) pack_emb_kernel(const float* __restrict__ emb, TA* __restrict__ out,
+                                                        int B, int T, int G, int C) {
+  const int Wp = G + 1, S = Wp * Wp, P = G * G;
+  long long idx = (long long)blockIdx.x * 256 + threadIdx.x;  // one thread per 4 channels
+  long long total = (long long)B * T * P * (C / 4);
+  if (idx >= total) return;
+  int c4 = (int)(idx % (C / 4));
+  long long pos = idx / (C / 4);
+  int p = (int)(pos % P);
+  long long f_in = pos / P;
+  int b = (int)(f_in / T), t = (int)(f_in - (long long)b * T);
+  int y = p / G, x = p - y * G;
+  float4 v = *reinterpret_cast<const float4*>(emb + pos * C + c4 * 4);
+  TA* d = out + (((long long)(t * B + b)) * S + (y + 1) * Wp + (x + 1)) * C + c4 * 4;
+  OpT<TA>::st(d, v.x); OpT<TA>::st(d + 1, v.y); OpT<TA>::st(d + 2, v.z); OpT<TA>::st(d + 3, v.w);
+}
+
+template <typename TA>
+__global__ void cast_kernel(const float* __restrict__ s, TA* __restrict__ d, long long n) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  long long stride = (long long)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) OpT<TA>::st(d + i, s[i]);
+}
+
+// ---------------------------------------------------------------------------------------------
+// gaze_grcn77.py:206-211 : per-position FC Ch -> 1 on the fp32 state (p-layout), one warp per position
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) fc_head_kernel(const float* __restrict__ h, const float* __restrict__ w,
+                                                       const float* __restrict__ bias, float* __restrict__ logits,
+                                                       int B, int T, int t, int G, int Ch) {
+  const int Wp = G + 1, S = Wp * Wp, P = G * G;
+  int warp = (blockIdx.x * 256 + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= B * P) return;
+  int b = warp / P, p = warp - b * P;
+  int y = p / G, x = p - y * G;
+  const float* hr = h + ((long long)b * S + (y + 1) * Wp + (x + 1)) * Ch;
+  float s = 0.f;
+  for (int c = lane; c < Ch; c += 32) s = fmaf(hr[c], w[c], s);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if (lane == 0) logits[((long long)b * T + t) * P + p] = s + bias[0];
+}
+
+// ---------------------------------------------------------------------------------------------
+// ConvLSTM gates — gaze_lstm.py:112-133, literally (candidate reuses the W_hi conv; output gate
+// peeps at the OLD cell; peepholes are full [G,G,Ch] tensors).
+// xg [M,4Ch] = conv(x,{W_xi,W_xf,W_xc,W_xo}); hconv [M,3Ch] = conv(h,{W_hi,W_hf,W_ho}); q-layout rows.
+// save (optional, training) [M,5Ch] = i, f, g(tanh candidate), o, c_prev.
+// ---------------------------------------------------------------------------------------------
+template <typename TA>
+__global__ void __launch_bounds__(256) lstm_gates_kernel(const float* __restrict__ xg, int ldx,
+                                                          const float* __restrict__ hconv,
+                                                          const float* __restrict__ wci, const float* __restrict__ wcf,
+                                                          const float* __restrict__ wco, float* __restrict__ c_f32,
+                                                          float* __restrict__ h_f32, TA* __restrict__ h_op_next,
+                                                          TA* __restrict__ hs_op, int B, int G, int Ch, int So, int Wo,
+                                                          int pado, float* __restrict__ save) {
+  const int Wp = G + 1, S = Wp * Wp, P = G * G;
+  long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (idx >= (long long)B * P * Ch) return;
+  int n = (int)(idx % Ch);
+  int pos = (int)(idx / Ch);
+  int b = pos / P, p = pos - b * P;
+  int y = p / G, x = p - y * G;
+  long long m = (long long)b * S + y * Wp + x;
+  long long prow = m + Wp + 1;
+  const float* xr = xg + m * ldx;
+  const float* hr = hconv + m * 3 * Ch;
+  float cp = c_f32[prow * Ch + n];
+  int pe = (y * G + x) * Ch + n;
+  float hi = hr[n];
+  float gi = sigmoidf_(xr[n] + hi + wci[pe] * cp);
+  float gf = sigmoidf_(xr[Ch + n] + hr[Ch + n] + wcf[pe] * cp);
+  float gg = tanhf_(xr[2 * Ch + n] + hi);
+  float cn = gf * cp + gi * gg;
+  float go = sigmoidf_(xr[3 * Ch + n] + hr[2 * Ch + n] + wco[pe] * cp);
+  float hn = tanhf_(cn) * go;
+  c_f32[prow * Ch + n] = cn;
+  h_f32[prow * Ch + n] = hn;
+  OpT<TA>::st(h_op_next + prow * Ch + n, hn);
+  if (hs_op) {
+    long long orow = (long long)b * So + (y + pado) * Wo + (x + pado);
+    OpT<TA>::st(hs_op + orow * Ch + n, hn);
+  }
+  if (save) {
+    float* sv = save + m * 5 * Ch;
+    sv[n] = gi; sv[Ch + n] = gf; sv[2 * Ch + n] = gg; sv[3 * Ch + n] = go; sv[4 * Ch + n] = cp;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Head weight composition (weight space).  The head of gaze_grcn.py:326-366 is linear:
+// deconv 5x5/s3 (Ch->64) o deconv 5x5/s2 (64->32) o deconv 7x7/s1 SAME (32->12) o FC 12->1.
+// Composite = one transposed conv 19x19 / stride 6 (Ch -> 1), VALID 7->55, cropped by 3 to 49:
+//   logit[Y,X] = sum_{i,j,c} hs[i,j,c] * W123[Y+3-6i, X+3-6j, c] + out_b
+// ---------------------------------------------------------------------------------------------
+__global__ void compose_w3f_kernel(const float* __restrict__ w3, const float* __restrict__ ow, float* __restrict__ w3f) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;  // (k3,l3,e): 49*32
+  if (i >= 49 * 32) return;
+  int e = i & 31, kl = i >> 5;
+  float s = 0.f;
+  for (int o = 0; o < 12; ++o) s = fmaf(w3[(kl * 12 + o) * 32 + e], ow[o], s);
+  w3f[i] = s;
+}
+__global__ void compose_w23_kernel(const float* __restrict__ w2, const float* __restrict__ w3f, float* __restrict__ w23) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;  // (s,t,m): 121*64
+  if (i >= 121 * 64) return;
+  int m = i & 63, st = i >> 6;
+  int s = st / 11, t = st - s * 11;
+  float acc = 0.f;
+  for (int k2 = 0; k2 < 5; ++k2) {
+    int k3 = s - k2;
+    if (k3 < 0 || k3 > 6) continue;
+    for (int l2 = 0; l2 < 5; ++l2) {
+      int l3 = t - l2;
+      if (l3 < 0 || l3 > 6) continue;
+      const float* a = w2 + ((k2 * 5 + l2) * 32) * 64 + m;  // w2[k2,l2,e,m]
+      const float* b = w3f + (k3 * 7 + l3) * 32;
+      for (int e = 0; e < 32; ++e) acc = fmaf(a[e * 64], b[e], acc);
+    }
+  }
+  w23[i] = acc;
+}
+__global__ void compose_w123_kernel(const float* __restrict__ w1, const float* __restrict__ w23, float* __restrict__ w123, int Ch) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;  // (u,v,c): 361*Ch
+  if (i >= 361 * Ch) return;
+  int c = i % Ch, uv = i / Ch;
+  int u = uv / 19, v = uv - u * 19;
+  float acc = 0.f;
+  for (int k1 = 0; k1 < 5; ++k1) {
+    int s = u - 2 * k1;
+    if (s < 0 || s > 10) continue;
+    for (int l1 = 0; l1 < 5; ++l1) {
+      int t = v - 2 * l1;
+      if (t < 0 || t > 10) continue;
+      const float* a = w1 + ((long long)(k1 * 5 + l1) * 64) * Ch + c;  // w1[k1,l1,m,c]
+      const float* b = w23 + (s * 11 + t) * 64;
+      for (int m = 0; m < 64; ++m) acc = fmaf(a[(long long)m * Ch], b[m], acc);
+    }
+  }
+  w123[i] = acc;
+}
+template <typename TA>
+__global__ void compose_bhead_kernel(const float* __restrict__ w123, TA* __restrict__ bhead, int Ch) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;  // (tap, n, c): 16*48*Ch
+  if (i >= 16 * 48 * Ch) return;
+  int c = i % Ch, tn = i / Ch;
+  int n = tn % 48, tap = tn / 48;
+  int dy = tap >> 2, dx = tap & 3;
+  float v = 0.f;
+  if (n < 36) {
+    int ry = n / 6, rx = n - ry * 6;
+    int u = 6 * dy + ry, w = 6 * dx + rx;
+    if (u < 19 && w < 19) v = w123[(u * 19 + w) * Ch + c];
+  }
+  OpT<TA>::st(bhead + i, v);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Spatial softmax + loss + dlogits: model_util.py:61-72, gaze_rnn.py:149-159,381-408.
+// One CTA per frame; the frame (<= 4096 positions) lives in shared memory; one pass over HBM:
+// read logits + gt, write probs and/or dlogits.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float block_reduce(float v, float* red, bool is_max) {
+  int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    float t = __shfl_xor_sync(0xffffffffu, v, o);
+    v = is_max ? fmaxf(v, t) : v + t;
+  }
+  __syncthreads();
+  if (lane == 0) red[w] = v;
+  __syncthreads();
+  float r = red[0];
+  for (int i = 1; i < (int)(blockDim.x >> 5); ++i) r = is_max ? fmaxf(r, red[i]) : r + red[i];
+  return r;
+}
+
+__global__ void __launch_bounds__(256) softmax_xent_kernel(const float* __restrict__ logits, const float* __restrict__ gt,
+                                                            float* __restrict__ probs, float* __restrict__ dlogits,
+                                                            float* __restrict__ frame_loss, int hw, float inv_bt,
+                                                            int loss_type) {
+  extern __shared__ float row[];  // hw logits
+  __shared__ float red[8];
+  const long long base = (long long)blockIdx.x * hw;
+  const float* lg = logits + base;
+  const float* g = gt + base;
+  if (loss_type == 1) {  // l2: gaze_rnn.py:387-389 — no softmax, model output is the raw map
+    float s = 0.f;
+    for (int i = threadIdx.x; i < hw; i += 256) {
+      float d = lg[i] - g[i];
+      s = fmaf(0.5f * d, d, s);
+      if (probs) probs[base + i] = lg[i];
+      if (dlogits) dlogits[base + i] = d * inv_bt;
+    }
+    s = block_reduce(s, red, false);
+    if (threadIdx.x == 0) frame_loss[blockIdx.x] = s * inv_bt;
+    return;
+  }
+  float mx = -INFINITY;
+  for (int i = threadIdx.x; i < hw; i += 256) {
+    float v = lg[i];
+    row[i] = v;
+    mx = fmaxf(mx, v);
+  }
+  mx = block_reduce(mx, red, true);
+  float se = 0.f;
+  for (int i = threadIdx.x; i < hw; i += 256) se += expf(row[i] - mx);
+  se = block_reduce(se, red, false);
+  const float lse = logf(se);
+  float loss = 0.f;
+  for (int i = threadIdx.x; i < hw; i += 256) {
+    float gv = g[i];
+    float x = row[i] - mx - lse;  // log_softmax (own elements of row[]: no hazard)
+    loss = fmaf(-gv, x, loss);
+    if (loss_type == 2 && gv > 0.f) loss = fmaf(gv, logf(gv), loss);
+    float p = expf(x);
+    if (probs) probs[base + i] = p;
+    if (dlogits) dlogits[base + i] = (p - gv) * inv_bt;  // TF gradient of softmax_cross_entropy_with_logits
+  }
+  loss = block_reduce(loss, red, false);
+  if (threadIdx.x == 0) frame_loss[blockIdx.x] = loss * inv_bt;
+}
+
+__global__ void __launch_bounds__(1024) reduce_sum_kernel(const float* __restrict__ x, long long n, float* __restrict__ out) {
+  __shared__ double red[32];
+  double s = 0.0;
+  for (long long i = threadIdx.x; i < n; i += 1024) s += (double)x[i];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+    for (int i = 0; i < 32; ++i) t += red[i];
+    out[0] = (float)t;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// base.py:287-297: clip_by_global_norm + tf.train.AdamOptimizer (epsilon outside the bias correction)
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) sumsq_kernel(const float* __restrict__ g, long long n, double* __restrict__ out) {
+  __shared__ double red[8];
+  double s = 0.0;
+  long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  long long stride = (long long)gridDim.x * 256;
+  for (; i < n; i += stride) { double v = g[i]; s += v * v; }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+    for (int k = 0; k < 8; ++k) t += red[k];
+    atomicAdd(out, t);
+  }
+}
+
+template <typename TA>
+__global__ void __launch_bounds__(256) clip_adam_kernel(float* __restrict__ p, const float* __restrict__ g,
+                                                         float* __restrict__ m, float* __restrict__ v, long long n,
+                                                         const double* __restrict__ sumsq, float clip, float lr_t,
+                                                         float b1, float b2, float eps, TA* __restrict__ p_op) {
+  const float norm = (float)sqrt(sumsq[0]);
+  const float scale = clip > 0.f ? clip / fmaxf(norm, clip) : 1.0f;
+  long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  long long stride = (long long)gridDim.x * 256;
+  for (; i < n; i += stride) {
+    float gi = g[i] * scale;
+    float mi = b1 * m[i] + (1.0f - b1) * gi;
+    float vi = b2 * v[i] + (1.0f - b2) * gi * gi;
+    float pi = p[i] - lr_t * mi / (sqrtf(vi) + eps);
+    m[i] = mi; v[i] = vi; p[i] = pi;
+    if (p_op) OpT<TA>::st(p_op + i, pi);
+  }
+}
+
+}  // namespace rgp
+
+using namespace rgp;
+
+extern "C" {
+
+int rgp_pack_c3d(const float* c3d, void* out, int B, int T, int C, int P, int dtype, void* stream) {
+  RGP_CHECK_ARG(C % 64 == 0, "rgp_pack_c3d: C=%d must be a multiple of 64", C);
+  dim3 grid(B * T, C / 64);
+  size_t sm = (size_t)64 * (P + 1) * sizeof(float);
+  if (sm > 48 * 1024) {
+    cudaFuncSetAttribute(pack_c3d_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+    cudaFuncSetAttribute(pack_c3d_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+  }
+  if (dtype == 0) pack_c3d_kernel<float><<<grid, 256, sm, (cudaStream_t)stream>>>(c3d, (float*)out, B, T, C, P);
+  else pack_c3d_kernel<__nv_bfloat16><<<grid, 256, sm, (cudaStream_t)stream>>>(c3d, (__nv_bfloat16*)out, B, T, C, P);
+  return check_launch("rgp_pack_c3d");
+}
+
+int rgp_pack_emb(const float* emb, void* out, int B, int T, int G, int C, int dtype, void* stream) {
+  RGP_CHECK_ARG(C % 4 == 0, "rgp_pack_emb: C=%d must be a multiple of 4", C);
+  long long total = (long long)B * T * G * G * (C / 4);
+  int grid = (int)((total + 255) / 256);
+  if (dtype == 0) pack_emb_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>(emb, (float*)out, B, T, G, C);
+  else pack_emb_kernel<__nv_bfloat16><<<grid, 256, 0, (cudaStream_t)stream>>>(emb, (__nv_bfloat16*)out, B, T, G, C);
+  return check_launch("rgp_pack_emb");
+}
+
+int rgp_cast(const float* src, void* dst, long long n, int dtype, void* stream) {
+  int grid = (int)((n + 1023) / 1024);
+  if (grid > 148 * 8) grid = 148 * 8;
+  if (grid < 1) grid = 1;
+  if (dtype == 0) cast_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>(src, (float*)dst, n);
+  else cast_kernel<__nv_bfloat16><<<grid, 256, 0, (cudaStream_t)stream>>>(src, (__nv_bfloat16*)dst, n);
+  return check_launch("rgp_cast");
+}
+
+int rgp_fc_head(const float* h_f32, const float* out_W, const float* out_b, float* logits, int B, int T, int t,
+                int G, int Ch, void* stream) {
+  int warps = B * G * G;
+  int grid = (warps * 32 + 255) / 256;
+  fc_head_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(h_f32, out_W, out_b, logits, B, T, t, G, Ch);
+  return check_launch("rgp_fc_head");
+}
+
+int rgp_lstm_gates(const float* xg, int ldx, const float* hconv, const float* wci, const float* wcf,
+                   const float* wco, float* c_f32, float* h_f32, void* h_op_next, void* hs_op, int B, int G,
+                   int Ch, int So, int Wo, int pado, int dtype, float* save, void* stream) {
+  long long total = (long long)B * G * G * Ch;
+  int grid = (int)((total + 255) / 256);
+  if (dtype == 0)
+    lstm_gates_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>(xg, ldx, hconv, wci, wcf, wco, c_f32, h_f32,
+                                                                      (float*)h_op_next, (float*)hs_op, B, G, Ch, So,
+                                                                      Wo, pado, save);
+  else
+    lstm_gates_kernel<__nv_bfloat16><<<grid, 256, 0, (cudaStream_t)stream>>>(
+        xg, ldx, hconv, wci, wcf, wco, c_f32, h_f32, (__nv_bfloat16*)h_op_next, (__nv_bfloat16*)hs_op, B, G, Ch, So,
+        Wo, pado, save);
+  return check_launch("rgp_lstm_gates");
+}
+
+int rgp_head_compose(const float* w1, const float* w2, const float* w3, const float* out_w, float* w3f, float* w23,
+                     float* w123, void* bhead, int Ch, int dtype, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  compose_w3f_kernel<<<(49 * 32 + 255) / 256, 256, 0, s>>>(w3, out_w, w3f);
+  compose_w23_kernel<<<(121 * 64 + 255) / 256, 256, 0, s>>>(w2, w3f, w23);
+  compose_w123_kernel<<<(361 * Ch + 255) / 256, 256, 0, s>>>(w1, w23, w123, Ch);
+  int n = 16 * 48 * Ch;
+  if (dtype == 0) compose_bhead_kernel<float><<<(n + 255) / 256, 256, 0, s>>>(w123, (float*)bhead, Ch);
+  else compose_bhead_kernel<__nv_bfloat16><<<(n + 255) / 256, 256, 0, s>>>(w123, (__nv_bfloat16*)bhead, Ch);
+  return check_launch("rgp_head_compose");
+}
+
+int rgp_softmax_xent_fwd_bwd(const float* logits, const float* gt, float* probs, float* dlogits, float* frame_loss,
+                             int n_frames, int hw, float inv_bt, int loss_type, void* stream) {
+  RGP_CHECK_ARG(hw > 0 && hw <= 12000, "rgp_softmax_xent_fwd_bwd: hw=%d unsupported", hw);
+  RGP_CHECK_ARG(loss_type >= 0 && loss_type <= 2, "rgp_softmax_xent_fwd_bwd: unknown loss_type %d", loss_type);
+  softmax_xent_kernel<<<n_frames, 256, hw * sizeof(float), (cudaStream_t)stream>>>(logits, gt, probs, dlogits,
+                                                                                     frame_loss, hw, inv_bt, loss_type);
+  return check_launch("rgp_softmax_xent_fwd_bwd");
+}
+
+int rgp_reduce_sum(const float* x, long long n, float* out, void* stream) {
+  reduce_sum_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(x, n, out);
+  return check_launch("rgp_reduce_sum");
+}
+
+int rgp_sumsq(const float* g, long long n, double* sumsq, void* stream) {
+  int grid = (int)((n + 2047) / 2048);
+  if (grid > 148 * 4) grid = 148 * 4;
+  if (grid < 1) grid = 1;
+  sumsq_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(g, n, sumsq);
+  return check_launch("rgp_sumsq");
+}
+
+int rgp_gradnorm_clip_adam(float* p, const float* g, float* m, float* v, long long n, const double* sumsq, float clip,
+                           float lr_t, float beta1, float beta2, float eps, void* p_op, int dtype, void* stream) {
+  int grid = (int)((n + 1023) / 1024);
+  if (grid > 148 * 8) grid = 148 * 8;
+  if (grid < 1) grid = 1;
+  if (dtype == 0 || p_op == nullptr)
+    clip_adam_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>(p, g, m, v, n, sumsq, clip, lr_t, beta1, beta2, eps,
+                                                                     (float*)p_op);
+  else
+    clip_adam_kernel<__nv_bfloat16><<<grid, 256, 0, (cudaStream_t)stream>>>(p, g, m, v, n, sumsq, clip, lr_t, beta1,
+                                                                             beta2, eps, (__nv_bfloat16*)p_op);
+  return check_launch("rgp_gradnorm_clip_adam");
+}
+
+int rgp_zero(void* p, long long bytes, void* stream) {
+  cudaError_t e = cudaMemsetAsync(p, 0, (size_t)bytes, (cudaStream_t)stream);
+  if (e != cudaSuccess) { set_error("rgp_zero: %s", cudaGetErrorString(e)); return -5; }
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,376 @@
+"""GazeEngine — host orchestration of the RGP hot path over the C-ABI of ``librgp_sm100.so``.
+
+One engine instance = one model replica on one GPU: it owns the flat parameter / gradient /
+Adam buffers, the activation slabs, and issues the kernels of one forward (and backward) pass on
+the current CUDA stream.  PyTorch is used for device allocations and streams only; all arithmetic
+happens in the library (``include/rgp.h``).  Reference call sites are cited per step.
+
+Row layouts: frames are time-major, f = t*B + b.  A G x G frame occupies
+S = (G+1)^2 rows of C-channel vectors; position (y,x) is stored at "p-row" f*S+(y+1)*Wp+(x+1) of
+an otherwise-zero operand buffer and its conv output lands at "q-row" f*S+y*Wp+x, which makes
+every tap of a 3x3 SAME convolution a constant row shift ky*Wp+kx.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+import os
+from collections import OrderedDict
+
+import numpy as np
+import torch
+
+from . import lib as L
+
+BN_EPS = 1e-3
+HEAD_S, HEAD_W, HEAD_PAD = 100, 10, 3   # head-input layout: 10x10 rows per frame, data at (+3,+3)
+LOSS_TYPES = {"xentropy": 0, "l2": 1, "KLD": 2}
+
+
+def _tdtype(dtype):
+    return torch.float32 if dtype == 0 else torch.bfloat16
+
+
+class GazeEngine(object):
+    def __init__(self, model="gaze_grcn", B=2, T=35, G=7, Ch=128, Cin=512, Cfeat=1024, dtype=0,
+                 device="cuda", lib=None, train=False, head=None, engine=None):
+        if model not in ("gaze_grcn", "gaze_grcn77", "gaze_lstm"):
+            raise ValueError("unknown model %r" % (model,))
+        self.model, self.B, self.T, self.G, self.Ch, self.Cin, self.Cfeat = model, B, T, G, Ch, Cin, Cfeat
+        if engine is None:   # RGP_ENGINE=1 forces the FMA engine for bf16 operands (debug / A-B checks)
+            engine = int(os.environ.get("RGP_ENGINE", "0"))
+        self.dtype, self.train, self.engine = dtype, train, engine
+        self.device = torch.device(device)
+        self.lib = lib if lib is not None else L.get_lib()
+        self.lstm = model == "gaze_lstm"
+        self.head = head or ("fc" if model == "gaze_grcn77" else "deconv")
+        if self.head == "deconv" and G != 7:
+            raise ValueError("the transposed-conv head (gaze_grcn.py:326-358) is defined for a 7x7 grid only")
+        self.use_bn = (model == "gaze_grcn" and self.head == "deconv")
+        self.GH = 49 if self.head == "deconv" else G
+        self.Wp = G + 1
+        self.S = self.Wp * self.Wp
+        self.P = G * G
+        self.tail = ((2 * self.Wp + 2 + 31) // 32) * 32
+        self.ngx = 4 if self.lstm else 3        # gates fed by the input conv
+        self.tdt = _tdtype(dtype)
+        self.taps3 = [ky * self.Wp + kx for ky in range(3) for kx in range(3)]
+        self._build_params()
+        self._alloc()
+        self.head_version = -1
+        self.param_version = 0
+
+    # ------------------------------------------------------------------ parameters
+    def _build_params(self):
+        Ch, Cin, T, G = self.Ch, self.Cin, self.T, self.G
+        spec = OrderedDict()
+        spec["proj_W_op"] = (Cin, self.Cfeat)
+        spec["proj_b"] = (Cin,)
+        spec["Wx_op"] = (9 * self.ngx * Ch, Cin)
+        if self.lstm:
+            spec["Wh_op"] = (9 * 3 * Ch, Ch)
+            spec["Whc_dead"] = (3, 3, Ch, Ch)
+            for nm in ("wci", "wcf", "wco"):
+                spec[nm] = (G, G, Ch)
+        else:
+            spec["Uzr_op"] = (9 * 2 * Ch, Ch)
+            spec["Uc_op"] = (9 * Ch, Ch)
+        if self.head == "deconv":
+            spec["w1"] = (5, 5, 64, Ch)
+            spec["w2"] = (5, 5, 32, 64)
+            spec["w3"] = (7, 7, 12, 32)
+            spec["out_W"] = (12,)
+        else:
+            spec["out_W"] = (Ch,)
+        spec["out_b"] = (1,)
+        if self.use_bn:
+            spec["bn_gamma"] = (T, Ch)
+            spec["bn_beta"] = (T, Ch)
+        self.spec = spec
+        self.offsets = OrderedDict()
+        off = 0
+        for k, shp in spec.items():
+            n = int(np.prod(shp))
+            self.offsets[k] = (off, n)
+            off += (n + 63) // 64 * 64      # keep every tensor 256-byte aligned (TMA / vector loads)
+        self.nparams = off
+        dev = self.device
+        self.params = torch.zeros(off, dtype=torch.float32, device=dev)
+        self.params_op = self.params if self.dtype == 0 else torch.zeros(off, dtype=self.tdt, device=dev)
+        if self.train:
+            self.grads = torch.zeros(off, dtype=torch.float32, device=dev)
+            self.adam_m = torch.zeros(off, dtype=torch.float32, device=dev)
+            self.adam_v = torch.zeros(off, dtype=torch.float32, device=dev)
+            self.sumsq = torch.zeros(1, dtype=torch.float64, device=dev)
+
+    def view(self, name, buf=None):
+        off, n = self.offsets[name]
+        buf = self.params if buf is None else buf
+        return buf[off:off + n].view(*self.spec[name])
+
+    def _ptr(self, name, buf=None):
+        off, _ = self.offsets[name]
+        buf = self.params if buf is None else buf
+        return buf.data_ptr() + off * buf.element_size()
+
+    def load_tf_params(self, p):
+        """Load a parameter dict with the reference's variable names and TF layouts
+        (conv kernels [kH,kW,Cin,Cout], conv_transpose kernels [kH,kW,Cout,Cin])."""
+        Ch = self.Ch
+
+        def conv_op(ws):  # list of [3,3,Cin,Cout] -> [9*sum(Cout), Cin]
+            w = np.concatenate([np.asarray(x, dtype=np.float32) for x in ws], axis=3)  # [3,3,Cin,N]
+            return np.ascontiguousarray(w.transpose(0, 1, 3, 2)).reshape(-1, w.shape[2])
+
+        host = {}
+        if "proj_c3d_W" in p:
+            host["proj_W_op"] = np.ascontiguousarray(np.asarray(p["proj_c3d_W"], dtype=np.float32).T)
+            host["proj_b"] = np.asarray(p["proj_c3d_b"], dtype=np.float32)
+        if self.lstm:
+            host["Wx_op"] = conv_op([p["ConvLSTM_Wx" + g] for g in "ifco"])
+            host["Wh_op"] = conv_op([p["ConvLSTM_Wh" + g] for g in "ifo"])
+            host["Whc_dead"] = np.asarray(p["ConvLSTM_Whc"], dtype=np.float32)
+            for g in "ifo":
+                host["wc" + g] = np.asarray(p["ConvLSTM_Wc" + g], dtype=np.float32)
+        else:
+            host["Wx_op"] = conv_op([p["GRU_Conv_Wz"], p["GRU_Conv_Wr"], p["GRU_Conv_W"]])
+            host["Uzr_op"] = conv_op([p["GRU_Conv_Uz"], p["GRU_Conv_Ur"]])
+            host["Uc_op"] = conv_op([p["GRU_Conv_U"]])
+        if self.head == "deconv":
+            host["w1"] = np.asarray(p["Upsampling/weight1"], dtype=np.float32)
+            host["w2"] = np.asarray(p["Upsampling/weight2"], dtype=np.float32)
+            host["w3"] = np.asarray(p["Upsampling/weight3"], dtype=np.float32)
+        host["out_W"] = np.asarray(p["out_W"], dtype=np.float32).reshape(-1)
+        host["out_b"] = np.asarray(p["out_b"], dtype=np.float32).reshape(-1)
+        if self.use_bn:
+            host["bn_gamma"] = np.asarray(p["bn_gamma"], dtype=np.float32)
+            host["bn_beta"] = np.asarray(p["bn_beta"], dtype=np.float32)
+        flat = np.zeros(self.nparams, dtype=np.float32)
+        for k, v in host.items():
+            off, n = self.offsets[k]
+            assert v.size == n, (k, v.shape, self.spec[k])
+            flat[off:off + n] = v.reshape(-1)
+        self.params.copy_(torch.from_numpy(flat))
+        self.refresh_operands()
+
+    def op_to_tf(self, flat):
+        """Inverse of load_tf_params on a flat host array (parameters or gradients)."""
+        Ch, Cin = self.Ch, self.Cin
+        flat = np.asarray(flat)
+
+        def get(k):
+            off, n = self.offsets[k]
+            return flat[off:off + n].reshape(self.spec[k])
+
+        def conv_tf(k, cin, names):
+            w = get(k).reshape(3, 3, -1, cin).transpose(0, 1, 3, 2)   # [3,3,cin,N]
+            return {nm: np.ascontiguousarray(w[..., i * Ch:(i + 1) * Ch]) for i, nm in enumerate(names)}
+
+        out = OrderedDict()
+        out["proj_c3d_W"] = np.ascontiguousarray(get("proj_W_op").T)
+        out["proj_c3d_b"] = get("proj_b").copy()
+        if self.lstm:
+            out.update(conv_tf("Wx_op", Cin, ["ConvLSTM_Wx" + g for g in "ifco"]))
+            out.update(conv_tf("Wh_op", Ch, ["ConvLSTM_Wh" + g for g in "ifo"]))
+            out["ConvLSTM_Whc"] = get("Whc_dead").copy()
+            for g in "ifo":
+                out["ConvLSTM_Wc" + g] = get("wc" + g).copy()
+        else:
+            out.update(conv_tf("Wx_op", Cin, ["GRU_Conv_Wz", "GRU_Conv_Wr", "GRU_Conv_W"]))
+            out.update(conv_tf("Uzr_op", Ch, ["GRU_Conv_Uz", "GRU_Conv_Ur"]))
+            out.update(conv_tf("Uc_op", Ch, ["GRU_Conv_U"]))
+        if self.head == "deconv":
+            out["Upsampling/weight1"] = get("w1").copy()
+            out["Upsampling/weight2"] = get("w2").copy()
+            out["Upsampling/weight3"] = get("w3").copy()
+            out["out_W"] = get("out_W").reshape(12, 1).copy()
+        else:
+            out["out_W"] = get("out_W").reshape(Ch, 1).copy()
+        out["out_b"] = get("out_b").copy()
+        if self.use_bn:
+            out["bn_gamma"] = get("bn_gamma").copy()
+            out["bn_beta"] = get("bn_beta").copy()
+        return out
+
+    def refresh_operands(self):
+        """Re-derive everything that depends on the parameter values (operand-dtype copy, composed head)."""
+        if self.dtype != 0:
+            self.lib.rgp_cast(self.params.data_ptr(), self.params_op.data_ptr(), self.nparams, self.dtype, self._s())
+        self.param_version += 1
+
+    # ------------------------------------------------------------------ buffers
+    def _alloc(self):
+        B, T, S, Ch, Cin = self.B, self.T, self.S, self.Ch, self.Cin
+        dev, tdt = self.device, self.tdt
+        z = lambda *shape, dt=torch.float32: torch.zeros(*shape, dtype=dt, device=dev)
+        self.rows_step = B * S + self.tail
+        self.Apack = z(T * B * self.P, self.Cfeat, dt=tdt)
+        self.Xp = z(T * B * S + self.tail, Cin, dt=tdt)
+        self.Xg = z(T * B * S, self.ngx * Ch)
+        self.Hop = z(T + 1, self.rows_step, Ch, dt=tdt)          # operand copies of h_0..h_T (p-layout)
+        self.Hf = z(T + 1, self.rows_step, Ch)                   # fp32 master state
+        nsl = T if self.train else 1
+        if self.lstm:
+            self.Cf = z(self.rows_step, Ch)
+            self.Hconv = z(B * S, 3 * Ch)
+            self.Lsave = z(T, B * S, 5 * Ch) if self.train else None
+        else:
+            self.RH = z(nsl, self.rows_step, Ch, dt=tdt)
+            self.Z = z(nsl, B * S, Ch)
+            self.Rs = z(T, B * S, Ch) if self.train else None
+            self.Cs = z(T, B * S, Ch) if self.train else None
+        hw = self.GH * self.GH
+        if self.head == "deconv":
+            self.HS = z(T * B * HEAD_S + 128, Ch, dt=tdt)
+            self.w3f = z(49 * 32)
+            self.w23 = z(121 * 64)
+            self.w123 = z(361 * Ch)
+            self.bhead = z(16 * 48, Ch, dt=tdt)
+        self.logits = z(B, T, self.GH, self.GH)
+        self.probs = z(B, T, self.GH, self.GH)
+        self.frame_loss = z(B * T)
+        self.loss = z(1)
+        if self.train:
+            self.dlogits = z(B, T, self.GH, self.GH)
+
+    def _s(self):
+        if self.device.type == "cuda":
+            return torch.cuda.current_stream(self.device).cuda_stream
+        return 0
+
+    def _gemm(self, **kw):
+        a = L.TapGemmArgs()
+        a.dtype, a.engine = self.dtype, self.engine
+        taps = kw.pop("taps")
+        a.ntaps = len(taps)
+        for i, o in enumerate(taps):
+            a.tap_off[i] = o
+        for k, v in kw.items():
+            setattr(a, k, v)
+        self.lib.rgp_tapgemm(C.byref(a), self._s())
+
+    # ------------------------------------------------------------------ forward
+    def forward(self, c3d=None, emb=None, gt=None, loss_type="xentropy"):
+        """c3d [B,T,Cfeat,G,G] fp32 (reference entry, gaze_grcn.py:173) or emb [B,T,G,G,Cin] fp32
+        (already-projected features).  Returns logits [B,T,GH,GW]; with gt also fills probs and loss."""
+        self.stage_embed(c3d, emb)
+        self.stage_i2h()
+        self.stage_recurrence()
+        self.stage_head()
+        if gt is not None:
+            self.loss_fwd(gt, loss_type)
+        return self.logits
+
+    def _pop(self, name):
+        return self._ptr(name, self.params_op)
+
+    def stage_embed(self, c3d=None, emb=None):
+        """(a1) layout + projection: gaze_grcn.py:223-254."""
+        lib, s = self.lib, self._s()
+        B, T, S, Cin, Wp, G = self.B, self.T, self.S, self.Cin, self.Wp, self.G
+        if c3d is not None:
+            assert tuple(c3d.shape) == (B, T, self.Cfeat, G, G) and c3d.dtype == torch.float32
+            lib.rgp_pack_c3d(c3d.data_ptr(), self.Apack.data_ptr(), B, T, self.Cfeat, self.P, self.dtype, s)
+            self._gemm(A=self.Apack.data_ptr(), rowsA=T * B * self.P, lda=self.Cfeat, Bw=self._pop("proj_W_op"),
+                       M=T * B * self.P, N=Cin, K=self.Cfeat, taps=[0], epi=L.EPI_PROJ, P=self.P, G=G,
+                       So=S, Wo=Wp, pado=1, out_op=self.Xp.data_ptr(), ldo=Cin, bias=self._ptr("proj_b"))
+        else:
+            assert tuple(emb.shape) == (B, T, G, G, Cin) and emb.dtype == torch.float32
+            lib.rgp_pack_emb(emb.data_ptr(), self.Xp.data_ptr(), B, T, G, Cin, self.dtype, s)
+
+    def stage_i2h(self):
+        """(a3) input half of every gate for all T frames at once: gaze_grcn.py:108-109,112-113,122-123."""
+        NX = self.ngx * self.Ch
+        self._gemm(A=self.Xp.data_ptr(), rowsA=self.Xp.shape[0], lda=self.Cin, Bw=self._pop("Wx_op"),
+                   M=self.T * self.B * self.S, N=NX, K=self.Cin, taps=self.taps3, epi=L.EPI_STORE_F32,
+                   out_f32=self.Xg.data_ptr(), ldo=NX, S=self.S, Wp=self.Wp, G=self.G)
+
+    def stage_recurrence(self):
+        """(a4/a6/a7) the T-step recurrence: gaze_grcn.py:259-288, gaze_lstm.py:260-286."""
+        lib, s = self.lib, self._s()
+        B, T, S, Ch, Wp, G = self.B, self.T, self.S, self.Ch, self.Wp, self.G
+        es = self.Hop.element_size()
+        pop = self._pop
+        NX = self.ngx * Ch
+        M = B * S
+        for t in range(T):
+            xg = self.Xg.data_ptr() + t * M * NX * 4
+            hs = 0
+            if self.head == "deconv":
+                hs = self.HS.data_ptr() + t * B * HEAD_S * Ch * es
+            if self.lstm:
+                if t == 0:
+                    lib.rgp_zero(self.Cf.data_ptr(), self.Cf.numel() * 4, s)
+                self._gemm(A=self.Hop[t].data_ptr(), rowsA=self.rows_step, lda=Ch, Bw=pop("Wh_op"), M=M, N=3 * Ch,
+                           K=Ch, taps=self.taps3, epi=L.EPI_STORE_F32, out_f32=self.Hconv.data_ptr(), ldo=3 * Ch,
+                           S=S, Wp=Wp, G=G)
+                lib.rgp_lstm_gates(xg, NX, self.Hconv.data_ptr(), self._ptr("wci"), self._ptr("wcf"),
+                                   self._ptr("wco"), self.Cf.data_ptr(), self.Hf[t + 1].data_ptr(),
+                                   self.Hop[t + 1].data_ptr(), hs, B, G, Ch, HEAD_S, HEAD_W, HEAD_PAD, self.dtype,
+                                   self.Lsave[t].data_ptr() if self.train else 0, s)
+            else:
+                sl = t if self.train else 0
+                common = dict(M=M, K=Ch, taps=self.taps3, S=S, Wp=Wp, G=G, Ch=Ch, B=B, T=T, t=t, xg=xg, ldx=NX,
+                              rowsA=self.rows_step, lda=Ch, hprev_f32=self.Hf[t].data_ptr(),
+                              z_f32=self.Z[sl].data_ptr())
+                self._gemm(A=self.Hop[t].data_ptr(), Bw=pop("Uzr_op"), N=2 * Ch, epi=L.EPI_GRU_ZR,
+                           out_op=self.RH[sl].data_ptr(), save_r=self.Rs[t].data_ptr() if self.train else 0,
+                           **common)
+                extra = {}
+                if self.use_bn:
+                    extra = dict(bias=self._ptr("bn_gamma") + t * Ch * 4, bias2=self._ptr("bn_beta") + t * Ch * 4,
+                                 alpha=1.0 / math.sqrt(1.0 + BN_EPS))
+                self._gemm(A=self.RH[sl].data_ptr(), Bw=pop("Uc_op"), N=Ch, epi=L.EPI_GRU_C,
+                           hnext_f32=self.Hf[t + 1].data_ptr(), out_op=self.Hop[t + 1].data_ptr(), out_op2=hs,
+                           So=HEAD_S, Wo=HEAD_W, pado=HEAD_PAD, save_c=self.Cs[t].data_ptr() if self.train else 0,
+                           **common, **extra)
+            if self.head == "fc":   # gaze_grcn77.py:206-211
+                lib.rgp_fc_head(self.Hf[t + 1].data_ptr(), self._ptr("out_W"), self._ptr("out_b"),
+                                self.logits.data_ptr(), B, T, t, G, Ch, s)
+
+    def stage_head(self):
+        """(a8-a10) composed transposed-conv head: gaze_grcn.py:318-366."""
+        if self.head != "deconv":
+            return
+        self._compose_head()
+        taps = [(3 - dy) * HEAD_W + (3 - dx) for dy in range(4) for dx in range(4)]
+        self._gemm(A=self.HS.data_ptr(), rowsA=self.HS.shape[0], lda=self.Ch, Bw=self.bhead.data_ptr(),
+                   M=self.T * self.B * HEAD_S, N=48, K=self.Ch, taps=taps, epi=L.EPI_HEAD, S=HEAD_S, Wp=HEAD_W,
+                   G=9, B=self.B, T=self.T, out_f32=self.logits.data_ptr(), bias=self._ptr("out_b"))
+
+    def time_stages(self, c3d, gt, iters=3):
+        """CUDA-event time (ms, mean of `iters`) of each stage of one forward pass on the current stream."""
+        names = ["embed", "i2h", "recurrence", "head", "loss"]
+        fns = [lambda: self.stage_embed(c3d), self.stage_i2h, self.stage_recurrence, self.stage_head,
+               lambda: self.loss_fwd(gt)]
+        acc = dict((n, 0.0) for n in names)
+        for _ in range(iters):
+            evs = [torch.cuda.Event(enable_timing=True) for _ in range(len(fns) + 1)]
+            evs[0].record()
+            for i, f in enumerate(fns):
+                f()
+                evs[i + 1].record()
+            torch.cuda.synchronize()
+            for i, n in enumerate(names):
+                acc[n] += evs[i].elapsed_time(evs[i + 1]) / iters
+        return acc
+
+    def _compose_head(self):
+        if self.head_version == self.param_version:
+            return
+        self.lib.rgp_head_compose(self._ptr("w1"), self._ptr("w2"), self._ptr("w3"), self._ptr("out_W"),
+                                  self.w3f.data_ptr(), self.w23.data_ptr(), self.w123.data_ptr(),
+                                  self.bhead.data_ptr(), self.Ch, self.dtype, self._s())
+        self.head_version = self.param_version
+
+    def loss_fwd(self, gt, loss_type="xentropy"):
+        if loss_type not in LOSS_TYPES:
+            raise NotImplementedError(str(loss_type))   # gaze_rnn.py:405-406
+        assert tuple(gt.shape) == tuple(self.logits.shape) and gt.dtype == torch.float32
+        n, hw = self.B * self.T, self.GH * self.GH
+        self.lib.rgp_softmax_xent_fwd_bwd(self.logits.data_ptr(), gt.data_ptr(), self.probs.data_ptr(),
+                                          self.dlogits.data_ptr() if self.train else 0,
+                                          self.frame_loss.data_ptr(), n, hw, 1.0 / n, LOSS_TYPES[loss_type],
+                                          self._s())
+        self.lib.rgp_reduce_sum(self.frame_loss.data_ptr(), n, self.loss.data_ptr(), self._s())
+        return self.loss

@@ -1,0 +1,105 @@
+"""ctypes binding of ``librgp_sm100.so`` (the C-ABI declared in ``include/rgp.h``).
+
+The product path has no CPU fallback: if the shared library is missing or a call
+fails, a ``RuntimeError`` is raised.  PyTorch is used by the callers only to own
+device memory and streams; every pointer handed to the library is a raw device
+address (``tensor.data_ptr()``).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+RGP_MAX_TAPS = 16
+EPI_STORE_F32, EPI_PROJ, EPI_GRU_ZR, EPI_GRU_C, EPI_HEAD, EPI_STORE_OP_P, EPI_STORE_OP = range(7)
+
+_vp, _i, _ll, _f, _d = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_double
+
+
+class TapGemmArgs(C.Structure):
+    """Mirror of ``rgp_tapgemm_args`` (include/rgp.h) — field order is the ABI."""
+    _fields_ = [
+        ("A", _vp), ("rowsA", _ll), ("lda", _i),
+        ("Bw", _vp),
+        ("M", _i), ("N", _i), ("K", _i), ("ntaps", _i),
+        ("tap_off", _i * RGP_MAX_TAPS),
+        ("dtype", _i), ("engine", _i), ("epi", _i), ("accumulate", _i),
+        ("S", _i), ("Wp", _i), ("G", _i), ("P", _i),
+        ("So", _i), ("Wo", _i), ("pado", _i), ("Ch", _i),
+        ("B", _i), ("T", _i), ("t", _i),
+        ("out_f32", _vp), ("ldo", _i),
+        ("out_op", _vp), ("out_op2", _vp),
+        ("xg", _vp), ("ldx", _i),
+        ("hprev_f32", _vp), ("hnext_f32", _vp), ("z_f32", _vp),
+        ("save_r", _vp), ("save_c", _vp),
+        ("bias", _vp), ("bias2", _vp), ("alpha", _f),
+    ]
+
+
+_SIGS = {
+    "rgp_tapgemm": [C.POINTER(TapGemmArgs), _vp],
+    "rgp_pack_c3d": [_vp, _vp, _i, _i, _i, _i, _i, _vp],
+    "rgp_pack_emb": [_vp, _vp, _i, _i, _i, _i, _i, _vp],
+    "rgp_cast": [_vp, _vp, _ll, _i, _vp],
+    "rgp_fc_head": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp],
+    "rgp_lstm_gates": [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp, _vp],
+    "rgp_head_compose": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp],
+    "rgp_softmax_xent_fwd_bwd": [_vp, _vp, _vp, _vp, _vp, _i, _i, _f, _i, _vp],
+    "rgp_reduce_sum": [_vp, _ll, _vp, _vp],
+    "rgp_sumsq": [_vp, _ll, _vp, _vp],
+    "rgp_gradnorm_clip_adam": [_vp, _vp, _vp, _vp, _ll, _vp, _f, _f, _f, _f, _f, _vp, _i, _vp],
+    "rgp_zero": [_vp, _ll, _vp],
+}
+
+
+def lib_path():
+    return os.path.join(os.path.dirname(os.path.abspath(__file__)), "librgp_sm100.so")
+
+
+class RgpLib(object):
+    """Loaded library; every C entry point is a method that raises on a non-zero return."""
+
+    def __init__(self, path=None):
+        path = path or lib_path()
+        if not os.path.exists(path):
+            raise RuntimeError("librgp_sm100.so not found at %s — run `python -c 'import __graft_entry__ as g; "
+                               "g.build()'` (there is no CPU fallback)" % path)
+        self._dll = C.CDLL(path)
+        self._dll.rgp_last_error.restype = C.c_char_p
+        self._dll.rgp_version.restype = _i
+        self._dll.rgp_has_tcgen05.restype = _i
+        for name, sig in _SIGS.items():
+            fn = getattr(self._dll, name)
+            fn.argtypes = sig
+            fn.restype = _i
+            setattr(self, name, self._wrap(name, fn))
+        self.path = path
+        self.launches = 0
+
+    def _wrap(self, name, fn):
+        def call(*args):
+            rc = fn(*args)
+            self.launches += 1
+            if rc != 0:
+                raise RuntimeError("%s failed (%d): %s" % (name, rc, self._dll.rgp_last_error().decode()))
+            return rc
+        return call
+
+    def version(self):
+        return self._dll.rgp_version()
+
+    def has_tcgen05(self):
+        return bool(self._dll.rgp_has_tcgen05())
+
+    def symbols(self):
+        return sorted(list(_SIGS) + ["rgp_last_error", "rgp_version", "rgp_has_tcgen05"])
+
+
+_LIB = None
+
+
+def get_lib():
+    global _LIB
+    if _LIB is None:
+        _LIB = RgpLib()
+    return _LIB

@@ -1,0 +1,267 @@
+"""NumPy emulation of the C-ABI of librgp_sm100.so — TEST INFRASTRUCTURE ONLY.
+
+It interprets the same argument structs / raw addresses the CUDA library receives, on host
+memory, so that the host orchestration in ``recurrent_gaze_prediction_b200/engine.py`` (buffer
+offsets, tap tables, row layouts, weight repacking, head composition, BPTT wiring) can be checked
+against the oracle on a machine without a GPU.  The product never imports this module; only
+``-m "not gpu"`` tests inject it as the ``lib`` argument of ``GazeEngine``.  fp32 (dtype 0) only.
+"""
+import ctypes as C
+import math
+
+import numpy as np
+
+from recurrent_gaze_prediction_b200 import lib as L
+
+_CT = {np.float32: C.c_float, np.float64: C.c_double, np.int32: C.c_int, np.int64: C.c_longlong,
+       np.uint8: C.c_ubyte}
+
+
+def arr(ptr, shape, dtype=np.float32):
+    if isinstance(ptr, C.c_void_p):
+        ptr = ptr.value
+    n = int(np.prod(shape))
+    buf = (_CT[dtype] * n).from_address(int(ptr))
+    return np.ctypeslib.as_array(buf).reshape(shape)
+
+
+def _sig(x):
+    return (1.0 / (1.0 + np.exp(-x.astype(np.float64)))).astype(np.float32)
+
+
+class EmuLib(object):
+    def __init__(self):
+        self.launches = 0
+        self.calls = []
+
+    def has_tcgen05(self):
+        return False
+
+    # -------------------------------------------------------------- tap GEMM
+    def rgp_tapgemm(self, aref, stream):
+        a = aref._obj
+        assert a.dtype == 0, "the emulator is fp32-only"
+        self.calls.append(("tapgemm", a.epi, a.M, a.N, a.K, a.ntaps))
+        M, N, K = a.M, a.N, a.K
+        A = arr(a.A, (a.rowsA, a.lda))
+        Bw = arr(a.Bw, (a.ntaps * N, K))
+        acc = np.zeros((M, N), dtype=np.float64)
+        rows = np.arange(M)
+        for tp in range(a.ntaps):
+            r = rows + a.tap_off[tp]
+            ok = (r >= 0) & (r < a.rowsA)
+            At = np.zeros((M, K), dtype=np.float64)
+            At[ok] = A[r[ok], :K]
+            acc += At @ Bw[tp * N:(tp + 1) * N].astype(np.float64).T
+        acc = acc.astype(np.float32)
+        e = a.epi
+        if e == L.EPI_STORE_F32:
+            out = arr(a.out_f32, (M, a.ldo))
+            if a.accumulate:
+                out[:, :N] += acc
+            else:
+                out[:, :N] = acc
+            return 0
+        if e == L.EPI_STORE_OP:
+            arr(a.out_op, (M, a.ldo))[:, :N] = acc
+            return 0
+        if e == L.EPI_PROJ:
+            f, p = np.divmod(rows, a.P)
+            y, x = np.divmod(p, a.G)
+            orow = f * a.So + (y + a.pado) * a.Wo + (x + a.pado)
+            out = arr(a.out_op, (int(orow.max()) + 1, a.ldo))
+            out[orow, :N] = acc + arr(a.bias, (N,))[None, :]
+            return 0
+        if e == L.EPI_HEAD:
+            f, q = np.divmod(rows, a.S)
+            ya, xb = np.divmod(q, a.Wp)
+            t, b = np.divmod(f, a.B)
+            out = arr(a.out_f32, (a.B, a.T, 49, 49))
+            bias = arr(a.bias, (1,))[0]
+            for n in range(36):
+                ry, rx = divmod(n, 6)
+                Y, X = 6 * ya + ry - 3, 6 * xb + rx - 3
+                ok = (ya < 9) & (xb < 9) & (Y >= 0) & (Y < 49) & (X >= 0) & (X < 49)
+                out[b[ok], t[ok], Y[ok], X[ok]] = acc[ok, n] + bias
+            return 0
+        # p/q-layout epilogues
+        f, q = np.divmod(rows, a.S)
+        y, x = np.divmod(q, a.Wp)
+        valid = (y < a.G) & (x < a.G)
+        prow = rows + a.Wp + 1
+        Ch = a.Ch
+        nrow_p = M + a.Wp + 2
+        if e == L.EPI_STORE_OP_P:
+            out = arr(a.out_op, (nrow_p, a.ldo))
+            out[prow[valid], :N] = acc[valid]
+            return 0
+        xg = arr(a.xg, (M, a.ldx))
+        hprev = arr(a.hprev_f32, (nrow_p, Ch))
+        if e == L.EPI_GRU_ZR:
+            s = _sig(acc + xg[:, :2 * Ch])
+            arr(a.z_f32, (M, Ch))[:] = s[:, :Ch]
+            r = s[:, Ch:]
+            if a.save_r:
+                arr(a.save_r, (M, Ch))[:] = r
+            out = arr(a.out_op, (nrow_p, Ch))
+            out[prow[valid]] = r[valid] * hprev[prow[valid]]
+            return 0
+        if e == L.EPI_GRU_C:
+            c = np.tanh((acc + xg[:, 2 * Ch:3 * Ch]).astype(np.float64)).astype(np.float32)
+            if a.save_c:
+                arr(a.save_c, (M, Ch))[:] = c
+            z = arr(a.z_f32, (M, Ch))
+            pv = prow[valid]
+            hn = z[valid] * hprev[pv] + (1.0 - z[valid]) * c[valid]
+            arr(a.hnext_f32, (nrow_p, Ch))[pv] = hn
+            arr(a.out_op, (nrow_p, Ch))[pv] = hn
+            if a.out_op2:
+                orow = f * a.So + (y + a.pado) * a.Wo + (x + a.pado)
+                v = hn
+                if a.bias:
+                    v = arr(a.bias, (Ch,))[None] * (hn * np.float32(a.alpha)) + arr(a.bias2, (Ch,))[None]
+                out2 = arr(a.out_op2, (int(orow.max()) + 1, Ch))
+                out2[orow[valid]] = v
+            return 0
+        raise NotImplementedError(e)
+
+    # -------------------------------------------------------------- elementwise
+    def rgp_pack_c3d(self, c3d, out, B, T, Cc, P, dtype, stream):
+        src = arr(c3d, (B, T, Cc, P))
+        dst = arr(out, (T, B, P, Cc))
+        dst[:] = src.transpose(1, 0, 3, 2)
+        return 0
+
+    def rgp_pack_emb(self, emb, out, B, T, G, Cc, dtype, stream):
+        Wp = G + 1
+        S = Wp * Wp
+        src = arr(emb, (B, T, G, G, Cc))
+        dst = arr(out, (T * B * S + Wp + 2, Cc))
+        for b in range(B):
+            for t in range(T):
+                for y in range(G):
+                    r0 = (t * B + b) * S + (y + 1) * Wp + 1
+                    dst[r0:r0 + G] = src[b, t, y]
+        return 0
+
+    def rgp_cast(self, src, dst, n, dtype, stream):
+        arr(dst, (n,))[:] = arr(src, (n,))
+        return 0
+
+    def rgp_zero(self, p, nbytes, stream):
+        C.memset(int(p), 0, int(nbytes))
+        return 0
+
+    def rgp_fc_head(self, h, w, b, logits, B, T, t, G, Ch, stream):
+        Wp = G + 1
+        S = Wp * Wp
+        hh = arr(h, (B * S + Wp + 2, Ch))
+        ww = arr(w, (Ch,))
+        out = arr(logits, (B, T, G, G))
+        for bb in range(B):
+            for y in range(G):
+                for x in range(G):
+                    out[bb, t, y, x] = hh[bb * S + (y + 1) * Wp + x + 1] @ ww + arr(b, (1,))[0]
+        return 0
+
+    def rgp_lstm_gates(self, xg, ldx, hconv, wci, wcf, wco, c_f32, h_f32, h_op_next, hs_op, B, G, Ch, So, Wo, pado,
+                       dtype, save, stream):
+        Wp = G + 1
+        S = Wp * Wp
+        M = B * S
+        X = arr(xg, (M, ldx))
+        Hc = arr(hconv, (M, 3 * Ch))
+        cf = arr(c_f32, (M + Wp + 2, Ch))
+        hf = arr(h_f32, (M + Wp + 2, Ch))
+        ho = arr(h_op_next, (M + Wp + 2, Ch))
+        pi, pf, po = (arr(w, (G, G, Ch)) for w in (wci, wcf, wco))
+        for b in range(B):
+            for y in range(G):
+                for x in range(G):
+                    m = b * S + y * Wp + x
+                    pr = m + Wp + 1
+                    cp = cf[pr].copy()
+                    hi = Hc[m, :Ch]
+                    gi = _sig(X[m, :Ch] + hi + pi[y, x] * cp)
+                    gf = _sig(X[m, Ch:2 * Ch] + Hc[m, Ch:2 * Ch] + pf[y, x] * cp)
+                    gg = np.tanh(X[m, 2 * Ch:3 * Ch] + hi)
+                    cn = gf * cp + gi * gg
+                    go = _sig(X[m, 3 * Ch:4 * Ch] + Hc[m, 2 * Ch:] + po[y, x] * cp)
+                    hn = np.tanh(cn) * go
+                    cf[pr] = cn
+                    hf[pr] = hn
+                    ho[pr] = hn
+                    if hs_op:
+                        orow = b * So + (y + pado) * Wo + x + pado
+                        arr(hs_op, (orow + 1, Ch))[orow] = hn
+                    if save:
+                        sv = arr(save, (M, 5 * Ch))
+                        sv[m] = np.concatenate([gi, gf, gg, go, cp])
+        return 0
+
+    def rgp_head_compose(self, w1, w2, w3, ow, w3f, w23, w123, bhead, Ch, dtype, stream):
+        W1, W2, W3 = arr(w1, (5, 5, 64, Ch)), arr(w2, (5, 5, 32, 64)), arr(w3, (7, 7, 12, 32))
+        oW = arr(ow, (12,))
+        W3f = np.einsum("kloe,o->kle", W3.astype(np.float64), oW.astype(np.float64))
+        W23 = np.zeros((11, 11, 64))
+        for k2 in range(5):
+            for l2 in range(5):
+                W23[k2:k2 + 7, l2:l2 + 7] += np.einsum("em,kle->klm", W2[k2, l2].astype(np.float64), W3f)
+        W123 = np.zeros((19, 19, Ch))
+        for k1 in range(5):
+            for l1 in range(5):
+                W123[2 * k1:2 * k1 + 11, 2 * l1:2 * l1 + 11] += np.einsum("mc,stm->stc", W1[k1, l1].astype(np.float64), W23)
+        arr(w3f, (7, 7, 32))[:] = W3f
+        arr(w23, (11, 11, 64))[:] = W23
+        arr(w123, (19, 19, Ch))[:] = W123
+        bh = arr(bhead, (16, 48, Ch))
+        bh[:] = 0
+        for dy in range(4):
+            for dx in range(4):
+                for ry in range(6):
+                    for rx in range(6):
+                        u, v = 6 * dy + ry, 6 * dx + rx
+                        if u < 19 and v < 19:
+                            bh[dy * 4 + dx, ry * 6 + rx] = W123[u, v]
+        return 0
+
+    def rgp_softmax_xent_fwd_bwd(self, logits, gt, probs, dlogits, frame_loss, n, hw, inv_bt, loss_type, stream):
+        lg = arr(logits, (n, hw)).astype(np.float64)
+        g = arr(gt, (n, hw)).astype(np.float64)
+        fl = arr(frame_loss, (n,))
+        if loss_type == 1:
+            d = lg - g
+            fl[:] = 0.5 * (d * d).sum(1) * inv_bt
+            p = lg
+        else:
+            x = lg - lg.max(1, keepdims=True)
+            lsm = x - np.log(np.exp(x).sum(1, keepdims=True))
+            loss = -(g * lsm).sum(1)
+            if loss_type == 2:
+                loss = loss + np.where(g > 0, g * np.log(np.maximum(g, 1e-300)), 0.0).sum(1)
+            fl[:] = loss * inv_bt
+            p = np.exp(lsm)
+            d = p - g
+        if probs:
+            arr(probs, (n, hw))[:] = p
+        if dlogits:
+            arr(dlogits, (n, hw))[:] = d * inv_bt
+        return 0
+
+    def rgp_reduce_sum(self, x, n, out, stream):
+        arr(out, (1,))[0] = arr(x, (n,)).astype(np.float64).sum()
+        return 0
+
+    def rgp_sumsq(self, g, n, out, stream):
+        arr(out, (1,), np.float64)[0] += (arr(g, (n,)).astype(np.float64) ** 2).sum()
+        return 0
+
+    def rgp_gradnorm_clip_adam(self, p, g, m, v, n, sumsq, clip, lr_t, b1, b2, eps, p_op, dtype, stream):
+        P, G, Mm, V = (arr(x, (n,)) for x in (p, g, m, v))
+        norm = math.sqrt(arr(sumsq, (1,), np.float64)[0])
+        scale = clip / max(norm, clip) if clip > 0 else 1.0
+        gg = G * np.float32(scale)
+        Mm[:] = b1 * Mm + (1 - b1) * gg
+        V[:] = b2 * V + (1 - b2) * gg * gg
+        P[:] = P - lr_t * Mm / (np.sqrt(V) + eps)
+        return 0

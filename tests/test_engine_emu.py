@@ -1,0 +1,55 @@
+"""Host orchestration (engine.py) over the NumPy emulation of the C-ABI vs the oracle — CPU only.
+Checks the row layouts, tap tables, weight repacking, composed head and (below) the BPTT wiring."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import model_oracle as O
+from recurrent_gaze_prediction_b200 import synthetic as SY
+from recurrent_gaze_prediction_b200.engine import GazeEngine
+from emu_lib import EmuLib
+
+
+def _setup(model, B=2, T=3, Ch=16, G=7, seed=0, regime="S", entry="c3d", Cin=32, Cfeat=64, train=False):
+    p = O.init_params(model, hidden=Ch, T=T, grid=G, dim_proj=Cin, dim_feature=Cfeat, seed=seed, regime=regime)
+    rng = np.random.RandomState(seed + 100)
+    GH = 7 if model == "gaze_grcn77" else 49
+    if model == "gaze_grcn77":
+        GH = G
+    c3d = SY.make_c3d(rng, B, T, Cfeat, G)
+    emb = SY.make_embedded(rng, B, T, G, Cin)
+    gt, _ = SY.make_gazemaps(rng, B, T, GH, GH, normalize=True)
+    eng = GazeEngine(model, B=B, T=T, G=G, Ch=Ch, Cin=Cin, Cfeat=Cfeat, dtype=0, device="cpu", lib=EmuLib(),
+                     train=train)
+    eng.load_tf_params(p)
+    return p, c3d, emb, gt, eng
+
+
+@pytest.mark.parametrize("model", ["gaze_grcn", "gaze_grcn77", "gaze_lstm"])
+@pytest.mark.parametrize("entry", ["c3d", "emb"])
+def test_forward_matches_oracle(model, entry):
+    p, c3d, emb, gt, eng = _setup(model)
+    kw = dict(c3d=torch.from_numpy(c3d)) if entry == "c3d" else dict(emb=torch.from_numpy(emb))
+    okw = dict(c3d=c3d.astype(np.float64)) if entry == "c3d" else dict(emb=emb.astype(np.float64))
+    for lt in ("xentropy", "l2", "KLD"):
+        logits = eng.forward(gt=torch.from_numpy(gt), loss_type=lt, **kw).numpy()
+        ref_logits, ref_probs, ref_loss, _ = O.forward_loss_grads(model, p, gt.astype(np.float64), loss_type=lt, **okw)
+        scale = np.abs(ref_logits).max()
+        assert np.abs(logits - ref_logits).max() <= 2e-5 * scale
+        if lt != "l2":
+            assert np.allclose(eng.probs.numpy(), ref_probs, rtol=1e-4, atol=1e-9)
+        assert abs(float(eng.loss[0]) - ref_loss) <= 1e-5 * abs(ref_loss) + 1e-7
+
+
+def test_grid14_embedded_entry():
+    p, c3d, emb, gt, eng = _setup("gaze_grcn77", B=1, T=2, Ch=8, G=14, entry="emb")
+    logits = eng.forward(emb=torch.from_numpy(emb)).numpy()
+    ref, _, _, _ = O.forward_loss_grads("gaze_grcn77", p, gt.astype(np.float64), emb=emb.astype(np.float64))
+    assert np.abs(logits - ref).max() <= 2e-5 * np.abs(ref).max()
+
+
+def test_param_roundtrip():
+    p, *_, eng = _setup("gaze_lstm")
+    back = eng.op_to_tf(eng.params.numpy())
+    for k, v in p.items():
+        assert np.allclose(back[k].reshape(np.asarray(v).shape), np.asarray(v, dtype=np.float32)), k

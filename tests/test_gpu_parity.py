@@ -1,0 +1,145 @@
+"""GPU parity tests proper: the CUDA path (through the C-ABI) against the oracle on seeded inputs.
+Tolerances are the north star's: fp32 gaze maps <= 1e-4 relative, bf16 tensor-core path <= 2e-2."""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import model_oracle as O
+from recurrent_gaze_prediction_b200 import lib as L
+from recurrent_gaze_prediction_b200 import synthetic as SY
+from recurrent_gaze_prediction_b200.engine import GazeEngine
+from emu_lib import EmuLib
+
+pytestmark = pytest.mark.gpu
+TOL = {0: 1e-4, 1: 2e-2}
+
+
+def _dev_ptr(t):
+    return t.data_ptr()
+
+
+def _run_tapgemm_case(dtype, engine, M, N, K, taps, seed, epi=L.EPI_STORE_F32):
+    """Generic tap GEMM (STORE_F32) on the GPU vs the NumPy emulation on the same (rounded) operands."""
+    rng = np.random.RandomState(seed)
+    rowsA = M + max(taps) + 5
+    tdt = torch.float32 if dtype == 0 else torch.bfloat16
+    A = torch.from_numpy(rng.standard_normal((rowsA, K)).astype(np.float32)).to(tdt)
+    Bw = torch.from_numpy((rng.standard_normal((len(taps) * N, K)) / np.sqrt(K * len(taps))).astype(np.float32)).to(tdt)
+    Af, Bf = A.float().contiguous(), Bw.float().contiguous()
+    out_ref = torch.zeros(M, N)
+
+    def args(Ap, Bp, outp, dt):
+        a = L.TapGemmArgs()
+        a.A, a.rowsA, a.lda, a.Bw = Ap, rowsA, K, Bp
+        a.M, a.N, a.K, a.ntaps = M, N, K, len(taps)
+        for i, o in enumerate(taps):
+            a.tap_off[i] = o
+        a.dtype, a.engine, a.epi = dt, engine, epi
+        a.out_f32, a.ldo = outp, N
+        return a
+
+    EmuLib().rgp_tapgemm(C.byref(args(Af.data_ptr(), Bf.data_ptr(), out_ref.data_ptr(), 0)), 0)
+    Ad, Bd = A.cuda(), Bw.cuda()
+    out = torch.zeros(M, N, device="cuda")
+    L.get_lib().rgp_tapgemm(C.byref(args(Ad.data_ptr(), Bd.data_ptr(), out.data_ptr(), dtype)),
+                            torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    err = (out.cpu() - out_ref).abs().max().item()
+    return err, out_ref.abs().max().item()
+
+
+@pytest.mark.parametrize("dtype,engine", [(0, 0), (1, 1), (1, 0)])
+@pytest.mark.parametrize("M,N,K,taps", [
+    (300, 96, 64, [0]),
+    (1000, 768, 512, [0, 1, 2, 8, 9, 10, 16, 17, 18]),
+    (515, 48, 128, [33 - 10 * dy - dx for dy in range(4) for dx in range(4)]),
+    (128, 256, 1024, [0]),
+    (4096, 512, 256, [0, 1, 2, 8, 9, 10, 16, 17, 18]),
+])
+def test_tapgemm_matches_emulation(dtype, engine, M, N, K, taps):
+    err, scale = _run_tapgemm_case(dtype, engine, M, N, K, taps, seed=M + N)
+    assert err <= 2e-5 * max(scale, 1.0) * (1 if dtype == 0 else 4), (err, scale)
+
+
+def _case(model, B, T, Ch, G=7, seed=0, regime="S", entry="c3d", Cin=512, Cfeat=1024):
+    p = O.init_params(model, hidden=Ch, T=T, grid=G, dim_proj=Cin, dim_feature=Cfeat, seed=seed, regime=regime)
+    rng = np.random.RandomState(seed + 100)
+    GH = G if model == "gaze_grcn77" else 49
+    c3d = SY.make_c3d(rng, B, T, Cfeat, G) if entry == "c3d" else None
+    emb = SY.make_embedded(rng, B, T, G, Cin) if entry == "emb" else None
+    gt, _ = SY.make_gazemaps(rng, B, T, GH, GH, normalize=True)
+    return p, c3d, emb, gt
+
+
+@pytest.mark.parametrize("dtype", [0, 1])
+@pytest.mark.parametrize("model,Ch,regime,entry", [
+    ("gaze_grcn", 128, "S", "c3d"),
+    ("gaze_grcn", 256, "S", "c3d"),
+    ("gaze_grcn", 128, "R", "c3d"),
+    ("gaze_grcn77", 128, "S", "c3d"),
+    ("gaze_lstm", 128, "S", "c3d"),
+    ("gaze_grcn", 128, "S", "emb"),
+])
+def test_forward_parity(dtype, model, Ch, regime, entry):
+    B, T = 3, 6
+    p, c3d, emb, gt = _case(model, B, T, Ch, regime=regime, entry=entry)
+    okw = dict(c3d=c3d.astype(np.float64)) if entry == "c3d" else dict(emb=emb.astype(np.float64))
+    ref_logits, ref_probs, ref_loss, _ = O.forward_loss_grads(model, p, gt.astype(np.float64), **okw)
+    eng = GazeEngine(model, B=B, T=T, Ch=Ch, dtype=dtype, device="cuda")
+    eng.load_tf_params(p)
+    kw = dict(c3d=torch.from_numpy(c3d).cuda()) if entry == "c3d" else dict(emb=torch.from_numpy(emb).cuda())
+    eng.forward(gt=torch.from_numpy(gt).cuda(), **kw)
+    torch.cuda.synchronize()
+    probs = eng.probs.cpu().numpy().astype(np.float64)
+    logits = eng.logits.cpu().numpy().astype(np.float64)
+    tol = TOL[dtype]
+    # gaze maps: relative to the map's peak (the quantity the saliency metrics consume)
+    rel = np.abs(probs - ref_probs).max(axis=(2, 3)) / ref_probs.max(axis=(2, 3))
+    assert rel.max() <= tol, (rel.max(), np.abs(logits - ref_logits).max())
+    assert abs(float(eng.loss.cpu()[0]) - ref_loss) <= tol * abs(ref_loss)
+
+
+@pytest.mark.parametrize("dtype", [0, 1])
+def test_grid14_long_sequence_lstm_and_gru(dtype):
+    """BASELINE config 4 shape family: 14x14 grid, embedded-feature entry, longer T (kept small here)."""
+    for model in ("gaze_grcn77",):
+        B, T, Ch, G = 2, 12, 128, 14
+        p, _, emb, gt = _case(model, B, T, Ch, G=G, entry="emb")
+        ref_logits, ref_probs, ref_loss, _ = O.forward_loss_grads(model, p, gt.astype(np.float64),
+                                                                  emb=emb.astype(np.float64))
+        eng = GazeEngine(model, B=B, T=T, G=G, Ch=Ch, dtype=dtype, device="cuda")
+        eng.load_tf_params(p)
+        eng.forward(emb=torch.from_numpy(emb).cuda(), gt=torch.from_numpy(gt).cuda())
+        torch.cuda.synchronize()
+        probs = eng.probs.cpu().numpy().astype(np.float64)
+        rel = np.abs(probs - ref_probs).max(axis=(2, 3)) / ref_probs.max(axis=(2, 3))
+        assert rel.max() <= TOL[dtype], rel.max()
+
+
+@pytest.mark.parametrize("loss_type", ["xentropy", "l2", "KLD"])
+def test_softmax_loss_kernel(loss_type):
+    rng = np.random.RandomState(3)
+    n, hw = 37, 2401
+    logits = (rng.standard_normal((n, hw)) * 3).astype(np.float32)
+    gt = rng.uniform(size=(n, hw)).astype(np.float32)
+    gt /= gt.sum(1, keepdims=True)
+    emu = EmuLib()
+    pr, dl, fl = np.zeros((n, hw), np.float32), np.zeros((n, hw), np.float32), np.zeros(n, np.float32)
+    lt = {"xentropy": 0, "l2": 1, "KLD": 2}[loss_type]
+    emu.rgp_softmax_xent_fwd_bwd(logits.ctypes.data, gt.ctypes.data, pr.ctypes.data, dl.ctypes.data, fl.ctypes.data,
+                                 n, hw, 1.0 / n, lt, 0)
+    lg, g = torch.from_numpy(logits).cuda(), torch.from_numpy(gt).cuda()
+    P, D, F = torch.zeros_like(lg), torch.zeros_like(lg), torch.zeros(n, device="cuda")
+    L.get_lib().rgp_softmax_xent_fwd_bwd(lg.data_ptr(), g.data_ptr(), P.data_ptr(), D.data_ptr(), F.data_ptr(),
+                                         n, hw, 1.0 / n, lt, torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    assert np.allclose(P.cpu().numpy(), pr, rtol=2e-5, atol=1e-9)
+    assert np.allclose(D.cpu().numpy(), dl, rtol=2e-4, atol=1e-9)
+    assert np.allclose(F.cpu().numpy(), fl, rtol=2e-5)
+
+
+def test_library_is_the_cuda_one():
+    lib = L.get_lib()
+    assert lib.path.endswith("librgp_sm100.so") and lib.has_tcgen05()
