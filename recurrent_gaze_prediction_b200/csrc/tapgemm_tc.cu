@@ -1,4 +1,444 @@
+// tapgemm_tc.cu — the tcgen05 / TMEM / TMA engine of the tap GEMM (bf16 operands, fp32 accumulate).
+//
+// Persistent, warp-specialised kernel, one CTA per SM:
+//   warp 0      : TMA producer.  Per k-step it issues two 2-D tile loads (SWIZZLE_128B): a 128 x 64 box of
+//                 A at row (m0 + tap_off[tap]) — a conv tap is only a row shift in the p-layout — and a
+//                 BN x 64 box of the tap's weight matrix.  4..6-stage mbarrier ring.
+//   warp 1      : TMEM allocator + MMA issuer: one elected thread issues tcgen05.mma (M=128, N=BN, K=16)
+//                 x4 per stage, accumulating all taps x K/64 chunks into one TMEM accumulator; tcgen05.commit
+//                 releases the smem stage and finally signals the epilogue.  Two accumulator stages in TMEM
+//                 so the epilogue of tile i overlaps the main loop of tile i+1.
+//   warps 2..5  : epilogue.  tcgen05.ld 32 lanes x 32 columns -> registers -> fused epilogue (common.cuh).
+#include <cuda.h>
+#include <cudaTypedefs.h>
+#include <map>
+#include <mutex>
+#include <tuple>
 #include "common.cuh"
+
 namespace rgp {
-int tapgemm_tc(const rgp_tapgemm_args& a, cudaStream_t s) { set_error("tcgen05 engine not built yet"); return -38; }
+
+namespace {
+
+constexpr int BM = 128, BK = 64;
+constexpr int NTHREADS = 192;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
 }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred P1;\n"
+      "LAB_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+      "@P1 bra DONE;\n"
+      "bra LAB_WAIT;\n"
+      "DONE:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* tmap, uint64_t* bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_u32(smem_dst)), "l"(tmap), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void tc_mma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                            uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tc_ld32(uint32_t taddr, float v[32]) {
+  uint32_t* r = reinterpret_cast<uint32_t*>(v);
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tc_ld16(uint32_t taddr, float v[16]) {
+  uint32_t* r = reinterpret_cast<uint32_t*>(v);
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];\n"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// K-major, SWIZZLE_128B shared-memory matrix descriptor (sm_100 UMMA): rows of 128 bytes (64 bf16),
+// 8-row swizzle atoms 1024 bytes apart (SBO); LBO unused for swizzled K-major; version = 1; layout = 2.
+__device__ __forceinline__ uint64_t make_sdesc(uint32_t saddr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+
+// ---- vectorised row-chunk epilogue helpers (one thread = one output row, 32 consecutive columns) ----
+__device__ __forceinline__ void ldf32(const float* p, float v[32]) {
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    float4 t = reinterpret_cast<const float4*>(p)[i];
+    v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
+  }
+}
+__device__ __forceinline__ void stf32(float* p, const float v[32]) {
+#pragma unroll
+  for (int i = 0; i < 8; ++i) reinterpret_cast<float4*>(p)[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+}
+__device__ __forceinline__ void stbf32(__nv_bfloat16* p, const float v[32]) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    __nv_bfloat162 b0 = __floats2bfloat162_rn(v[8 * i], v[8 * i + 1]);
+    __nv_bfloat162 b1 = __floats2bfloat162_rn(v[8 * i + 2], v[8 * i + 3]);
+    __nv_bfloat162 b2 = __floats2bfloat162_rn(v[8 * i + 4], v[8 * i + 5]);
+    __nv_bfloat162 b3 = __floats2bfloat162_rn(v[8 * i + 6], v[8 * i + 7]);
+    uint4 u;
+    u.x = *reinterpret_cast<uint32_t*>(&b0); u.y = *reinterpret_cast<uint32_t*>(&b1);
+    u.z = *reinterpret_cast<uint32_t*>(&b2); u.w = *reinterpret_cast<uint32_t*>(&b3);
+    reinterpret_cast<uint4*>(p)[i] = u;
+  }
+}
+
+// 32 consecutive columns [n0, n0+32) of row r.  Fast paths need N % 32 == 0 and 32-element-aligned leading dims.
+__device__ __forceinline__ void epi_row32(const rgp_tapgemm_args& a, const RowInfo& r, int n0, float v[32], bool vec) {
+  using TA = __nv_bfloat16;
+  if (!r.inrange) return;
+  if (vec) {
+    switch (a.epi) {
+      case RGP_EPI_STORE_F32:
+        if (!a.accumulate) { stf32(a.out_f32 + (long long)r.m * a.ldo + n0, v); return; }
+        break;
+      case RGP_EPI_PROJ: {
+        float b[32];
+        ldf32(a.bias + n0, b);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] += b[i];
+        stbf32((TA*)a.out_op + r.orow * a.ldo + n0, v);
+        return;
+      }
+      case RGP_EPI_GRU_ZR: {
+        float x[32];
+        ldf32(a.xg + (long long)r.m * a.ldx + n0, x);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = sigmoidf_(v[i] + x[i]);
+        if (n0 < a.Ch) {
+          stf32(a.z_f32 + (long long)r.m * a.Ch + n0, v);
+        } else {
+          int j = n0 - a.Ch;
+          if (a.save_r) stf32(a.save_r + (long long)r.m * a.Ch + j, v);
+          if (r.valid) {
+            ldf32(a.hprev_f32 + r.prow * a.Ch + j, x);
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] *= x[i];
+            stbf32((TA*)a.out_op + r.prow * a.Ch + j, v);
+          }
+        }
+        return;
+      }
+      case RGP_EPI_GRU_C: {
+        float x[32];
+        ldf32(a.xg + (long long)r.m * a.ldx + 2 * a.Ch + n0, x);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = tanhf_(v[i] + x[i]);
+        if (a.save_c) stf32(a.save_c + (long long)r.m * a.Ch + n0, v);
+        if (r.valid) {
+          float z[32];
+          ldf32(a.z_f32 + (long long)r.m * a.Ch + n0, z);
+          ldf32(a.hprev_f32 + r.prow * a.Ch + n0, x);
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] = z[i] * x[i] + (1.0f - z[i]) * v[i];
+          stf32(a.hnext_f32 + r.prow * a.Ch + n0, v);
+          stbf32((TA*)a.out_op + r.prow * a.Ch + n0, v);
+          if (a.out_op2) {
+            if (a.bias) {
+              ldf32(a.bias + n0, x);
+              ldf32(a.bias2 + n0, z);
+#pragma unroll
+              for (int i = 0; i < 32; ++i) v[i] = x[i] * (v[i] * a.alpha) + z[i];
+            }
+            stbf32((TA*)a.out_op2 + r.orow * a.Ch + n0, v);
+          }
+        }
+        return;
+      }
+      default:
+        break;
+    }
+  }
+#pragma unroll 4
+  for (int i = 0; i < 32; ++i) epi_elem<TA>(a, r, n0 + i, v[i]);
+}
+
+template <int BN>
+struct Cfg {
+  static constexpr int kStageBytes = BM * BK * 2 + BN * BK * 2;
+  static constexpr int kStages = (BN >= 256) ? 4 : ((BN >= 128) ? 6 : 8);
+  static constexpr int kAccStride = (BN <= 32) ? 32 : ((BN <= 64) ? 64 : ((BN <= 128) ? 128 : 256));
+  static constexpr int kTmemCols = 2 * kAccStride;
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+template <int BN>
+__global__ void __launch_bounds__(NTHREADS, 1)
+tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                  const rgp_tapgemm_args a) {
+  using C = Cfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::kStages * C::kStageBytes);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + C::kStages;
+  uint64_t* tfull = bars + 2 * C::kStages;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int mtiles = (a.M + BM - 1) / BM, ntiles = a.N / BN;
+  const int total_tiles = mtiles * ntiles;
+  const int kchunks = a.K / BK;
+  const int ksteps = a.ntaps * kchunks;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
+    for (int i = 0; i < C::kStages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 4); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"((uint32_t)C::kTmemCols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int mt = tile / ntiles, nt = tile - mt * ntiles;
+        const int m0 = mt * BM, n0 = nt * BN;
+        for (int ks = 0; ks < ksteps; ++ks) {
+          const int tap = ks / kchunks, kc = ks - tap * kchunks;
+          mbar_wait(&empty[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * C::kStageBytes;
+          uint8_t* sb = sa + BM * BK * 2;
+          mbar_expect_tx(&full[stage], C::kStageBytes);
+          tma_load_2d(sa, &tmA, &full[stage], kc * BK, m0 + a.tap_off[tap]);
+          tma_load_2d(sb, &tmB, &full[stage], kc * BK, tap * a.N + n0);
+          if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    // instruction descriptor: D=f32, A=B=bf16, both K-major, N=BN, M=128
+    constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+    int stage = 0; uint32_t phase = 0;
+    int acc = 0; uint32_t accphase = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      mbar_wait(&tempty[acc], accphase ^ 1);
+      tc_fence_after();
+      const uint32_t tacc = tmem_base + (uint32_t)(acc * C::kAccStride);
+      for (int ks = 0; ks < ksteps; ++ks) {
+        mbar_wait(&full[stage], phase);
+        tc_fence_after();
+        if (lane == 0) {
+          const uint32_t sa = smem_u32(smem + stage * C::kStageBytes);
+          const uint32_t sb = sa + BM * BK * 2;
+          const uint64_t adesc = make_sdesc(sa), bdesc = make_sdesc(sb);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k)   // +32 bytes (>>4 = 2) per K=16 slice inside the 128-byte swizzle row
+            tc_mma_bf16(tacc, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (ks | k) ? 1u : 0u);
+          tc_commit(&empty[stage]);
+          if (ks == ksteps - 1) tc_commit(&tfull[acc]);
+        }
+        __syncwarp();
+        if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+      }
+      if (++acc == 2) { acc = 0; accphase ^= 1; }
+    }
+  } else {
+    // ===================== epilogue (warps 2..5 -> TMEM lane groups (warp % 4)) =====================
+    const int lg = warp & 3;
+    int acc = 0; uint32_t accphase = 0;
+    const bool vec = (a.N % 32 == 0) && (a.ldo % 4 == 0) && (a.ldx % 4 == 0) && (a.Ch % 32 == 0 || a.Ch == 0);
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const int mt = tile / ntiles, nt = tile - mt * ntiles;
+      const int m0 = mt * BM, n0 = nt * BN;
+      mbar_wait(&tfull[acc], accphase);
+      tc_fence_after();
+      const RowInfo r = make_row(a, m0 + lg * 32 + lane);
+      const uint32_t tbase = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(acc * C::kAccStride);
+      if constexpr (BN % 32 == 0) {
+#pragma unroll 1
+        for (int c = 0; c < BN; c += 32) {
+          float v[32];
+          tc_ld32(tbase + (uint32_t)c, v);
+          epi_row32(a, r, n0 + c, v, vec);
+        }
+      } else {
+#pragma unroll 1
+        for (int c = 0; c < BN; c += 16) {
+          float v[16];
+          tc_ld16(tbase + (uint32_t)c, v);
+#pragma unroll 4
+          for (int i = 0; i < 16; ++i) epi_elem<__nv_bfloat16>(a, r, n0 + c + i, v[i]);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty[acc]);
+      if (++acc == 2) { acc = 0; accphase ^= 1; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)C::kTmemCols)
+                 : "memory");
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side: tensor maps (cuTensorMapEncodeTiled through the runtime's driver entry point) + launch
+// ---------------------------------------------------------------------------------------------
+PFN_cuTensorMapEncodeTiled_v12000 get_encode() {
+  static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(p);
+  });
+  return fn;
+}
+
+struct MapKey {
+  const void* p; long long rows; int ld; int k; int boxrows;
+  bool operator<(const MapKey& o) const {
+    return std::tie(p, rows, ld, k, boxrows) < std::tie(o.p, o.rows, o.ld, o.k, o.boxrows);
+  }
+};
+
+int make_map(const void* base, long long rows, int ld, int K, int boxrows, CUtensorMap* out) {
+  static std::map<MapKey, CUtensorMap> cache;
+  static std::mutex mu;
+  MapKey key{base, rows, ld, K, boxrows};
+  {
+    std::lock_guard<std::mutex> g(mu);
+    auto it = cache.find(key);
+    if (it != cache.end()) { *out = it->second; return 0; }
+  }
+  auto enc = get_encode();
+  if (!enc) { set_error("cuTensorMapEncodeTiled not available from the driver"); return -38; }
+  cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)boxrows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed (%d) base=%p rows=%lld ld=%d K=%d box=%d", (int)r, base, rows, ld, K, boxrows);
+    return -5;
+  }
+  std::lock_guard<std::mutex> g(mu);
+  if (cache.size() > 4096) cache.clear();
+  cache[key] = *out;
+  return 0;
+}
+
+int num_sms() {
+  static int n = 0;
+  if (!n) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+  }
+  return n;
+}
+
+template <int BN>
+int launch(const rgp_tapgemm_args& a, cudaStream_t s) {
+  using C = Cfg<BN>;
+  CUtensorMap tmA, tmB;
+  int rc = make_map(a.A, a.rowsA, a.lda, a.K, BM, &tmA);
+  if (rc) return rc;
+  rc = make_map(a.Bw, (long long)a.ntaps * a.N, a.K, a.K, BN, &tmB);
+  if (rc) return rc;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(tapgemm_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes);
+    if (e != cudaSuccess) { set_error("cudaFuncSetAttribute(smem=%d): %s", C::kSmemBytes, cudaGetErrorString(e)); return -5; }
+    attr_set = true;
+  }
+  const int mtiles = (a.M + BM - 1) / BM, ntiles = a.N / BN;
+  int grid = mtiles * ntiles;
+  if (grid > num_sms()) grid = num_sms();
+  tapgemm_tc_kernel<BN><<<grid, NTHREADS, C::kSmemBytes, s>>>(tmA, tmB, a);
+  return check_launch("tapgemm_tc");
+}
+
+}  // namespace
+
+int tapgemm_tc(const rgp_tapgemm_args& a, cudaStream_t s) {
+  RGP_CHECK_ARG(a.K % BK == 0, "tapgemm_tc: K=%d must be a multiple of %d", a.K, BK);
+  RGP_CHECK_ARG(a.lda % 8 == 0, "tapgemm_tc: lda=%d must be a multiple of 8 (16-byte TMA stride)", a.lda);
+  RGP_CHECK_ARG(((uintptr_t)a.A & 15) == 0 && ((uintptr_t)a.Bw & 15) == 0, "tapgemm_tc: operands must be 16-byte aligned");
+  if (a.N % 256 == 0) return launch<256>(a, s);
+  if (a.N % 128 == 0) return launch<128>(a, s);
+  if (a.N % 64 == 0) return launch<64>(a, s);
+  if (a.N % 48 == 0) return launch<48>(a, s);
+  if (a.N % 32 == 0) return launch<32>(a, s);
+  if (a.N % 16 == 0) return launch<16>(a, s);
+  set_error("tapgemm_tc: N=%d must be a multiple of 16", a.N);
+  return -22;
+}
+
+}  // namespace rgp
