@@ -108,6 +108,11 @@ __device__ __forceinline__ uint64_t make_sdesc(uint32_t saddr) {
   return d;
 }
 
+// single-MUFU gates for the bf16 engine (rel. error ~2^-11, below the bf16 operand rounding of 2^-9;
+// the fp32 engine keeps the libm forms)
+__device__ __forceinline__ float tanh_fast(float x) { float y; asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float sigmoid_fast(float x) { return fmaf(0.5f, tanh_fast(0.5f * x), 0.5f); }
+
 // ---- vectorised row-chunk epilogue helpers (one thread = one output row, 32 consecutive columns) ----
 __device__ __forceinline__ void ldf32(const float* p, float v[32]) {
 #pragma unroll
@@ -155,7 +160,7 @@ __device__ __forceinline__ void epi_row32(const rgp_tapgemm_args& a, const RowIn
         float x[32];
         ldf32(a.xg + (long long)r.m * a.ldx + n0, x);
 #pragma unroll
-        for (int i = 0; i < 32; ++i) v[i] = sigmoidf_(v[i] + x[i]);
+        for (int i = 0; i < 32; ++i) v[i] = sigmoid_fast(v[i] + x[i]);
         if (n0 < a.Ch) {
           stf32(a.z_f32 + (long long)r.m * a.Ch + n0, v);
         } else {
@@ -174,7 +179,7 @@ __device__ __forceinline__ void epi_row32(const rgp_tapgemm_args& a, const RowIn
         float x[32];
         ldf32(a.xg + (long long)r.m * a.ldx + 2 * a.Ch + n0, x);
 #pragma unroll
-        for (int i = 0; i < 32; ++i) v[i] = tanhf_(v[i] + x[i]);
+        for (int i = 0; i < 32; ++i) v[i] = tanh_fast(v[i] + x[i]);
         if (a.save_c) stf32(a.save_c + (long long)r.m * a.Ch + n0, v);
         if (r.valid) {
           float z[32];
@@ -204,13 +209,113 @@ __device__ __forceinline__ void epi_row32(const rgp_tapgemm_args& a, const RowIn
   for (int i = 0; i < 32; ++i) epi_elem<TA>(a, r, n0 + i, v[i]);
 }
 
+
+// ---- coalesced quad epilogue: after a transpose through shared memory a lane owns 4 consecutive columns of
+// a row, so that one warp-wide 16-byte access touches 4 rows x 128 bytes (4 cache lines instead of 32) ----
+struct RowLite { int m; int flags; long long prow; long long orow; };   // flags: 1 = in range, 2 = valid position
+
+
+__device__ __forceinline__ void st_bf16x4(__nv_bfloat16* p, float4 v) {
+  __nv_bfloat162 b0 = __floats2bfloat162_rn(v.x, v.y), b1 = __floats2bfloat162_rn(v.z, v.w);
+  uint2 u;
+  u.x = *reinterpret_cast<uint32_t*>(&b0); u.y = *reinterpret_cast<uint32_t*>(&b1);
+  *reinterpret_cast<uint2*>(p) = u;
+}
+__device__ __forceinline__ float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+__device__ __forceinline__ void st4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
+
+__device__ __forceinline__ bool quad_mode(int epi, int accumulate) {
+  // measured on B200 (profiles/r01_notes.md): the transposed quad path wins for the pure-store epilogues; the
+  // gate epilogues are faster thread-per-row (8 independent 16-byte loads per array in flight per thread)
+  return (epi == RGP_EPI_STORE_F32 && !accumulate) || epi == RGP_EPI_PROJ;
+}
+
+// The quad epilogue is split in two so that the global loads of several rows are all in flight before the
+// first dependent instruction (the stores of one row may alias the loads of the next as far as the compiler
+// knows, which would otherwise serialise one L2 round trip per row).
+struct QuadIn { float4 x, z, h; };
+
+__device__ __forceinline__ void quad_load(const rgp_tapgemm_args& a, const RowLite& q, int n, QuadIn& in) {
+  const bool valid = (q.flags & 2) != 0;
+  switch (a.epi) {
+    case RGP_EPI_GRU_ZR:
+      in.x = ld4(a.xg + (long long)q.m * a.ldx + n);
+      if (n >= a.Ch && valid) in.h = ld4(a.hprev_f32 + q.prow * a.Ch + (n - a.Ch));
+      break;
+    case RGP_EPI_GRU_C:
+      in.x = ld4(a.xg + (long long)q.m * a.ldx + 2 * a.Ch + n);
+      if (valid) {
+        in.z = ld4(a.z_f32 + (long long)q.m * a.Ch + n);
+        in.h = ld4(a.hprev_f32 + q.prow * a.Ch + n);
+      }
+      break;
+    default:
+      break;
+  }
+}
+
+__device__ __forceinline__ void quad_store(const rgp_tapgemm_args& a, const RowLite& q, int n, float4 v,
+                                           const QuadIn& in, const float4& g, const float4& b) {
+  using TA = __nv_bfloat16;
+  const bool valid = (q.flags & 2) != 0;
+  switch (a.epi) {
+    case RGP_EPI_STORE_F32:
+      st4(a.out_f32 + (long long)q.m * a.ldo + n, v);
+      break;
+    case RGP_EPI_PROJ:   // g = bias[n..n+3]
+      v.x += g.x; v.y += g.y; v.z += g.z; v.w += g.w;
+      st_bf16x4((TA*)a.out_op + q.orow * a.ldo + n, v);
+      break;
+    case RGP_EPI_GRU_ZR: {
+      v.x = sigmoid_fast(v.x + in.x.x); v.y = sigmoid_fast(v.y + in.x.y);
+      v.z = sigmoid_fast(v.z + in.x.z); v.w = sigmoid_fast(v.w + in.x.w);
+      if (n < a.Ch) {
+        st4(a.z_f32 + (long long)q.m * a.Ch + n, v);
+      } else {
+        const int j = n - a.Ch;
+        if (a.save_r) st4(a.save_r + (long long)q.m * a.Ch + j, v);
+        if (valid) {
+          v.x *= in.h.x; v.y *= in.h.y; v.z *= in.h.z; v.w *= in.h.w;
+          st_bf16x4((TA*)a.out_op + q.prow * a.Ch + j, v);
+        }
+      }
+      break;
+    }
+    case RGP_EPI_GRU_C: {
+      v.x = tanh_fast(v.x + in.x.x); v.y = tanh_fast(v.y + in.x.y);
+      v.z = tanh_fast(v.z + in.x.z); v.w = tanh_fast(v.w + in.x.w);
+      if (a.save_c) st4(a.save_c + (long long)q.m * a.Ch + n, v);
+      if (valid) {
+        const float4 z = in.z, h = in.h;
+        v.x = z.x * h.x + (1.0f - z.x) * v.x; v.y = z.y * h.y + (1.0f - z.y) * v.y;
+        v.z = z.z * h.z + (1.0f - z.z) * v.z; v.w = z.w * h.w + (1.0f - z.w) * v.w;
+        st4(a.hnext_f32 + q.prow * a.Ch + n, v);
+        st_bf16x4((TA*)a.out_op + q.prow * a.Ch + n, v);
+        if (a.out_op2) {
+          if (a.bias) {
+            v.x = g.x * (v.x * a.alpha) + b.x; v.y = g.y * (v.y * a.alpha) + b.y;
+            v.z = g.z * (v.z * a.alpha) + b.z; v.w = g.w * (v.w * a.alpha) + b.w;
+          }
+          st_bf16x4((TA*)a.out_op2 + q.orow * a.Ch + n, v);
+        }
+      }
+      break;
+    }
+    default:
+      break;
+  }
+}
+
+constexpr int kScrLd = 36;                          // floats per scratch row (32 + 4 pad: conflict-free 16-byte accesses)
+constexpr int kEpiScratchBytes = 4 * 32 * kScrLd * 4 + 4 * 32 * (int)sizeof(RowLite);
+
 template <int BN>
 struct Cfg {
   static constexpr int kStageBytes = BM * BK * 2 + BN * BK * 2;
   static constexpr int kStages = (BN >= 256) ? 4 : ((BN >= 128) ? 6 : 8);
   static constexpr int kAccStride = (BN <= 32) ? 32 : ((BN <= 64) ? 64 : ((BN <= 128) ? 128 : 256));
   static constexpr int kTmemCols = 2 * kAccStride;
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/ + kEpiScratchBytes;
 };
 
 template <int BN>
@@ -226,6 +331,8 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   uint64_t* tfull = bars + 2 * C::kStages;
   uint64_t* tempty = tfull + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+  float* scr_base = reinterpret_cast<float*>(smem + C::kStages * C::kStageBytes + 256);
+  RowLite* rl_base = reinterpret_cast<RowLite*>(scr_base + 4 * 32 * kScrLd);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int mtiles = (a.M + BM - 1) / BM, ntiles = a.N / BN;
@@ -302,20 +409,73 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     // ===================== epilogue (warps 2..5 -> TMEM lane groups (warp % 4)) =====================
     const int lg = warp & 3;
     int acc = 0; uint32_t accphase = 0;
-    const bool vec = (a.N % 32 == 0) && (a.ldo % 4 == 0) && (a.ldx % 4 == 0) && (a.Ch % 32 == 0 || a.Ch == 0);
+    const bool vec = (a.N % 32 == 0) && (a.ldo % 8 == 0) && (a.ldx % 4 == 0) && (a.Ch % 32 == 0);
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const int mt = tile / ntiles, nt = tile - mt * ntiles;
       const int m0 = mt * BM, n0 = nt * BN;
+      const RowInfo r = make_row(a, m0 + lg * 32 + lane);
+      // While the MMAs of this tile are still running: pull the epilogue's inputs (pre-activations from the
+      // input-half GEMM, z, h_{t-1}) from HBM into L2, one 128-byte line per prefetch, this thread's row.
+      if (r.inrange && (a.epi == RGP_EPI_GRU_ZR || a.epi == RGP_EPI_GRU_C)) {
+        const float* px = a.xg + (long long)r.m * a.ldx + (a.epi == RGP_EPI_GRU_C ? 2 * a.Ch : 0) + n0;
+        for (int c = 0; c < BN; c += 32) asm volatile("prefetch.global.L2 [%0];" ::"l"(px + c));
+        if (r.valid) {
+          const int jb = (a.epi == RGP_EPI_GRU_ZR) ? (n0 >= a.Ch ? n0 - a.Ch : -1) : n0;
+          if (jb >= 0) {
+            const float* ph = a.hprev_f32 + r.prow * a.Ch + jb;
+            for (int c = 0; c < BN && jb + c < a.Ch; c += 32) asm volatile("prefetch.global.L2 [%0];" ::"l"(ph + c));
+          }
+          if (a.epi == RGP_EPI_GRU_C) {
+            const float* pz = a.z_f32 + (long long)r.m * a.Ch + n0;
+            for (int c = 0; c < BN; c += 32) asm volatile("prefetch.global.L2 [%0];" ::"l"(pz + c));
+          }
+        }
+      }
       mbar_wait(&tfull[acc], accphase);
       tc_fence_after();
-      const RowInfo r = make_row(a, m0 + lg * 32 + lane);
       const uint32_t tbase = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(acc * C::kAccStride);
       if constexpr (BN % 32 == 0) {
+        const bool quad = vec && quad_mode(a.epi, a.accumulate);
+        float* scr = scr_base + (warp - 2) * 32 * kScrLd;
+        RowLite* rl = rl_base + (warp - 2) * 32;
+        if (quad) {
+          RowLite q;
+          q.m = r.m; q.flags = (r.inrange ? 1 : 0) | (r.valid ? 2 : 0); q.prow = r.prow; q.orow = r.orow;
+          rl[lane] = q;
+        }
 #pragma unroll 1
         for (int c = 0; c < BN; c += 32) {
           float v[32];
           tc_ld32(tbase + (uint32_t)c, v);
-          epi_row32(a, r, n0 + c, v, vec);
+          if (quad) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+              st4(scr + lane * kScrLd + 4 * i, make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]));
+            __syncwarp();
+            const int rr = lane >> 3, cg = (lane & 7) * 4;
+            const int n = n0 + c + cg;
+            float4 g = make_float4(0.f, 0.f, 0.f, 0.f), bb = g;
+            if ((a.epi == RGP_EPI_PROJ || a.epi == RGP_EPI_GRU_C) && a.bias) g = ld4(a.bias + n);
+            if (a.epi == RGP_EPI_GRU_C && a.bias) bb = ld4(a.bias2 + n);
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+              QuadIn in[4];
+              RowLite q[4];
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                q[i] = rl[4 * (4 * half + i) + rr];
+                if (q[i].flags & 1) quad_load(a, q[i], n, in[i]);
+              }
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const float4 t = ld4(scr + (4 * (4 * half + i) + rr) * kScrLd + cg);
+                if (q[i].flags & 1) quad_store(a, q[i], n, t, in[i], g, bb);
+              }
+            }
+            __syncwarp();
+          } else {
+            epi_row32(a, r, n0 + c, v, vec);
+          }
         }
       } else {
 #pragma unroll 1

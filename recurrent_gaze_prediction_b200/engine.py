@@ -338,6 +338,22 @@ class GazeEngine(object):
                    M=self.T * self.B * HEAD_S, N=48, K=self.Ch, taps=taps, epi=L.EPI_HEAD, S=HEAD_S, Wp=HEAD_W,
                    G=9, B=self.B, T=self.T, out_f32=self.logits.data_ptr(), bias=self._ptr("out_b"))
 
+    def make_graph(self, fn):
+        """Capture the launches fn() issues into a CUDA graph (one submission per step instead of ~80
+        launches: the recurrence is launch-bound at small batch).  Returns (graph, kernels_per_replay)."""
+        dev = self.device
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            fn()      # warm-up outside capture: function attributes, tensor-map cache, head composition
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        g = torch.cuda.CUDAGraph()
+        n0 = self.lib.launches
+        with torch.cuda.graph(g):
+            fn()
+        return g, self.lib.launches - n0
+
     def time_stages(self, c3d, gt, iters=3):
         """CUDA-event time (ms, mean of `iters`) of each stage of one forward pass on the current stream."""
         names = ["embed", "i2h", "recurrence", "head", "loss"]
