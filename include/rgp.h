@@ -32,7 +32,12 @@ enum {
   RGP_EPI_GRU_C = 3,       /* c = tanh(acc+Xc); h' = z*h + (1-z)*c ; BN-scale (gaze_grcn.py:122-127,325) */
   RGP_EPI_HEAD = 4,        /* composed transposed-conv head scatter + out_b  (gaze_grcn.py:326-366)  */
   RGP_EPI_STORE_OP_P = 5,  /* store operand dtype at p-row (valid rows only): dX of a SAME conv       */
-  RGP_EPI_STORE_OP = 6     /* store operand dtype at row m                                            */
+  RGP_EPI_STORE_OP = 6,    /* store operand dtype at row m                                            */
+  /* BPTT (base.py:278-281 tf.gradients of gaze_grcn.py:108-127) */
+  RGP_EPI_BWD_RH = 7,      /* acc = d(r.h): dpre_r = acc*h*r(1-r) -> dG[:,Ch:2Ch]; dhpart += acc*r     */
+  RGP_EPI_BWD_H = 8,       /* acc = convT(dpre_z,dpre_r): dh = acc + dhpart + head term; gate backward of step t-1 */
+  RGP_EPI_DHS = 9,         /* head backward: store fp32 acc at the recurrence q-row of the head-layout row */
+  RGP_EPI_DX_DENSE = 10    /* store operand dtype at the dense row f*P + y*G + x (valid rows only)     */
 };
 
 /* One "tap GEMM":  acc[m,n] = sum_tap sum_k A[m + tap_off[tap], k] * Bw[tap*N + n, k]
@@ -66,6 +71,11 @@ typedef struct rgp_tapgemm_args {
   const float* bias;            /* PROJ: [N]; HEAD: [1]; GRU_C: bn scale [Ch] (may be NULL) */
   const float* bias2;           /* GRU_C: bn shift [Ch] (may be NULL) */
   float alpha;                  /* GRU_C: 1/sqrt(1+eps) of the frozen batch-norm (gaze_grcn.py:325) */
+  /* BPTT slots */
+  float* dhpart;                /* [M, Ch] fp32 q-layout: part of dL/dh_{t-1} that does not pass through a conv */
+  const float* dhs;             /* [M, Ch] fp32 q-layout: dL/d(head input) of the step whose gates are differentiated */
+  const float* save_z;          /* [M, Ch] saved z of that step */
+  void* dg; int ldg;            /* dL/d(pre-activations) [M, 3Ch] operand dtype, columns z | r | c */
 } rgp_tapgemm_args;
 
 int rgp_tapgemm(const rgp_tapgemm_args* a, void* stream);
@@ -110,6 +120,43 @@ int rgp_gradnorm_clip_adam(float* p, const float* g, float* m, float* v, long lo
                            const double* sumsq, float clip, float lr_t, float beta1, float beta2,
                            float eps, void* p_op, int dtype, void* stream);
 int rgp_zero(void* p, long long bytes, void* stream);
+
+/* ---- BPTT (base.py:278-281) --------------------------------------------------------------- */
+/* Weight-gradient contraction over rows ("wgrad"):
+ *   D[tap][i, j] += sum_{m<M} Y[m, ycol0+i] * X[m + tap_off[tap], xcol0+j],  i<Ny, j<Nx
+ * Y [>=M, ldy], X [rowsX, ldx] operand dtype row-major; D fp32 [ntaps][Ny][Nx] (the op layout of a
+ * conv weight: [tap][Cout][Cin]); accumulates (split-K partials are added atomically). */
+typedef struct rgp_wgrad_args {
+  const void* Y; int ldy; int ycol0; int Ny;
+  const void* X; long long rowsX; int ldx; int xcol0; int Nx;
+  int M, ntaps; int tap_off[RGP_MAX_TAPS];
+  float* D;
+  int dtype, engine;
+} rgp_wgrad_args;
+int rgp_wgrad(const rgp_wgrad_args* a, void* stream);
+/* gate backward of the LAST step (no incoming recurrent gradient): dh = dhs * (gamma*alpha) */
+int rgp_gru_bwd_last(const float* dhs, const float* gamma, float alpha, const float* z, const float* c,
+                     const float* hprev_f32, void* dg, int ldg, float* dhpart, int B, int G, int Ch,
+                     int dtype, void* stream);
+/* per-tap transpose + cast: src fp32 [ntaps][R][Cc] -> dst operand dtype [ntaps][Cc][R] */
+int rgp_transpose_taps(const float* src, void* dst, int ntaps, int R, int Cc, int dtype, void* stream);
+/* head backward, data side: im2col of dlogits [B,T,49,49] into the head-input row layout:
+ * patches[(t*B+b)*100 + (i+3)*10 + j+3, u*19+v] = dlogits[b,t,6i+u-3,6j+v-3] (0 outside), ld = 384 */
+int rgp_head_patches(const float* dlogits, void* patches, int B, int T, int dtype, void* stream);
+/* head backward, weight side: dW123 [384(361 used), Ch] fp32 -> gradients of w1, w2, w3, out_W (accumulated) */
+int rgp_head_compose_bwd(const float* dw123, const float* w1, const float* w2, const float* w3,
+                         const float* out_w, const float* w3f, const float* w23, float* dw23, float* dw3f,
+                         float* gw1, float* gw2, float* gw3, float* gout_w, int Ch, void* stream);
+/* w123 [361, Ch] fp32 -> operand dtype [Ch, 384] (transposed, zero padded) for the dhs GEMM */
+int rgp_head_w123t(const float* w123, void* out, int Ch, int dtype, void* stream);
+/* frozen-BN backward (gaze_grcn.py:325): dgamma[t,c] += alpha * sum dhs*h ; dbeta[t,c] += sum dhs */
+int rgp_bn_bwd(const float* dhs, const float* h_f32, float* dgamma, float* dbeta, float alpha,
+               int B, int G, int Ch, void* stream);
+/* out[j] += sum_m X[m, j] (X operand dtype [M, ld]) — bias gradients */
+int rgp_colsum(const void* X, int ld, int M, int N, float* out, int dtype, void* stream);
+/* gaze_grcn77.py:206-211 backward: dhs[m,c] = dlogit*out_W[c]; gout_W[c] += sum dlogit*h; gout_b += sum dlogit */
+int rgp_fc_head_bwd(const float* dlogits, const float* h_f32, const float* out_W, float* dhs,
+                    float* gout_W, float* gout_b, int B, int T, int t, int G, int Ch, void* stream);
 
 /* ---- saliency metrics: evaluation_metrics.py -------------------------------------------- */
 /* resize stand-in for skimage.transform.resize(order=3) (see oracle/metrics_oracle.py) */

@@ -1,0 +1,293 @@
+// bwd_ops.cu — bandwidth-bound kernels of the hand-written BPTT (the reference leaves this to
+// tf.gradients, base.py:278-281): last-step gate backward, per-tap weight transposes, im2col of dlogits for
+// the composed head, weight-space chain rule of the head composition, frozen-BN and bias gradients.
+#include "common.cuh"
+
+namespace rgp {
+
+template <typename TA>
+__global__ void __launch_bounds__(256) gru_bwd_last_kernel(const float* __restrict__ dhs, const float* __restrict__ gamma,
+                                                            float alpha, const float* __restrict__ z,
+                                                            const float* __restrict__ c, const float* __restrict__ hprev,
+                                                            TA* __restrict__ dg, int ldg, float* __restrict__ dhpart,
+                                                            int B, int G, int Ch) {
+  const int Wp = G + 1, S = Wp * Wp, P = G * G;
+  long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (idx >= (long long)B * P * Ch) return;
+  int n = (int)(idx % Ch);
+  int pos = (int)(idx / Ch);
+  int b = pos / P, p = pos - b * P;
+  int y = p / G, x = p - y * G;
+  long long m = (long long)b * S + y * Wp + x;
+  float dh = dhs[m * Ch + n];
+  if (gamma) dh *= gamma[n] * alpha;
+  gru_gate_bwd<TA>(z, c, hprev, dg, ldg, dhpart, Ch, m, m + Wp + 1, n, dh);
+}
+
+template <typename TA>
+__global__ void __launch_bounds__(256) transpose_taps_kernel(const float* __restrict__ src, TA* __restrict__ dst, int R, int Cc) {
+  __shared__ float tile[32][33];
+  const int tap = blockIdx.z;
+  const float* s = src + (long long)tap * R * Cc;
+  TA* d = dst + (long long)tap * R * Cc;
+  int r0 = blockIdx.y * 32, c0 = blockIdx.x * 32;
+  int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+  for (int i = ty; i < 32; i += 8) {
+    int r = r0 + i, c = c0 + tx;
+    tile[i][tx] = (r < R && c < Cc) ? s[(long long)r * Cc + c] : 0.f;
+  }
+  __syncthreads();
+  for (int i = ty; i < 32; i += 8) {
+    int c = c0 + i, r = r0 + tx;
+    if (c < Cc && r < R) OpT<TA>::st(d + (long long)c * R + r, tile[tx][i]);
+  }
+}
+
+// patches[(t*B+b)*100 + (i+3)*10 + (j+3), u*19+v] = dlogits[b,t,6i+u-3,6j+v-3]; one CTA per (frame, position)
+template <typename TA>
+__global__ void __launch_bounds__(128) head_patches_kernel(const float* __restrict__ dl, TA* __restrict__ patches, int B, int T) {
+  const int pos = blockIdx.x % 49, f = blockIdx.x / 49;   // f = t*B + b
+  const int i = pos / 7, j = pos - i * 7;
+  const int t = f / B, b = f - t * B;
+  const float* src = dl + ((long long)b * T + t) * 2401;
+  TA* dst = patches + ((long long)f * 100 + (i + 3) * 10 + (j + 3)) * 384;
+  for (int k = threadIdx.x; k < 384; k += 128) {
+    float v = 0.f;
+    if (k < 361) {
+      int u = k / 19, w = k - u * 19;
+      int Y = 6 * i + u - 3, X = 6 * j + w - 3;
+      if (Y >= 0 && Y < 49 && X >= 0 && X < 49) v = src[Y * 49 + X];
+    }
+    OpT<TA>::st(dst + k, v);
+  }
+}
+
+template <typename TA>
+__global__ void head_w123t_kernel(const float* __restrict__ w123, TA* __restrict__ out, int Ch) {
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;   // (c, k): Ch*384
+  if (idx >= Ch * 384) return;
+  int k = idx % 384, c = idx / 384;
+  OpT<TA>::st(out + idx, k < 361 ? w123[(long long)k * Ch + c] : 0.f);
+}
+
+// ---- weight-space chain rule of the head composition (see compose_* in ops.cu) ----
+__global__ void cb_dw1_kernel(const float* __restrict__ dw123, const float* __restrict__ w23, float* __restrict__ gw1, int Ch) {
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;   // (k1,l1,m,c)
+  if (idx >= 25 * 64 * Ch) return;
+  int c = idx % Ch, r = idx / Ch;
+  int m = r & 63, kl = r >> 6;
+  int k1 = kl / 5, l1 = kl - k1 * 5;
+  float acc = 0.f;
+  for (int s = 0; s < 11; ++s)
+    for (int t = 0; t < 11; ++t)
+      acc = fmaf(dw123[((long long)(2 * k1 + s) * 19 + (2 * l1 + t)) * Ch + c], w23[(s * 11 + t) * 64 + m], acc);
+  gw1[idx] += acc;
+}
+__global__ void cb_dw23_kernel(const float* __restrict__ dw123, const float* __restrict__ w1, float* __restrict__ dw23, int Ch) {
+  // one warp per (s,t,m): reduce over k1,l1,c
+  int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= 121 * 64) return;
+  int m = warp & 63, st = warp >> 6;
+  int s = st / 11, t = st - s * 11;
+  float acc = 0.f;
+  for (int kl = 0; kl < 25; ++kl) {
+    int k1 = kl / 5, l1 = kl - k1 * 5;
+    const float* a = dw123 + ((long long)(2 * k1 + s) * 19 + (2 * l1 + t)) * Ch;
+    const float* b = w1 + ((long long)kl * 64 + m) * Ch;
+    for (int c = lane; c < Ch; c += 32) acc = fmaf(a[c], b[c], acc);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if (lane == 0) dw23[warp] = acc;
+}
+__global__ void cb_dw2_kernel(const float* __restrict__ dw23, const float* __restrict__ w3f, float* __restrict__ gw2) {
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;   // (k2,l2,e,m): 25*32*64
+  if (idx >= 25 * 32 * 64) return;
+  int m = idx & 63, r = idx >> 6;
+  int e = r & 31, kl = r >> 5;
+  int k2 = kl / 5, l2 = kl - k2 * 5;
+  float acc = 0.f;
+  for (int k3 = 0; k3 < 7; ++k3)
+    for (int l3 = 0; l3 < 7; ++l3)
+      acc = fmaf(dw23[((k2 + k3) * 11 + (l2 + l3)) * 64 + m], w3f[(k3 * 7 + l3) * 32 + e], acc);
+  gw2[idx] += acc;
+}
+__global__ void cb_dw3f_kernel(const float* __restrict__ dw23, const float* __restrict__ w2, float* __restrict__ dw3f) {
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;   // (k3,l3,e): 49*32
+  if (idx >= 49 * 32) return;
+  int e = idx & 31, kl = idx >> 5;
+  int k3 = kl / 7, l3 = kl - k3 * 7;
+  float acc = 0.f;
+  for (int k2 = 0; k2 < 5; ++k2)
+    for (int l2 = 0; l2 < 5; ++l2) {
+      const float* a = dw23 + ((k2 + k3) * 11 + (l2 + l3)) * 64;
+      const float* b = w2 + ((k2 * 5 + l2) * 32 + e) * 64;
+      for (int m = 0; m < 64; ++m) acc = fmaf(a[m], b[m], acc);
+    }
+  dw3f[idx] = acc;
+}
+__global__ void cb_dw3_kernel(const float* __restrict__ dw3f, const float* __restrict__ w3, const float* __restrict__ ow,
+                              float* __restrict__ gw3, float* __restrict__ gow) {
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;   // (k3,l3,o,e): 49*12*32
+  if (idx < 49 * 12 * 32) {
+    int e = idx & 31, r = idx >> 5;
+    int o = r % 12, kl = r / 12;
+    gw3[idx] += dw3f[kl * 32 + e] * ow[o];
+  }
+  if (idx < 12) {   // d out_W[o] = sum_{kl,e} dw3f[kl,e] * w3[kl,o,e]
+    float acc = 0.f;
+    for (int kl = 0; kl < 49; ++kl)
+      for (int e = 0; e < 32; ++e) acc = fmaf(dw3f[kl * 32 + e], w3[(kl * 12 + idx) * 32 + e], acc);
+    gow[idx] += acc;
+  }
+}
+
+// dgamma[c] += alpha * sum_{b,pos} dhs[m,c]*h[prow,c]; dbeta[c] += sum dhs[m,c]   (one step; block per 32 channels)
+__global__ void __launch_bounds__(256) bn_bwd_kernel(const float* __restrict__ dhs, const float* __restrict__ h,
+                                                      float* __restrict__ dgamma, float* __restrict__ dbeta, float alpha,
+                                                      int B, int G, int Ch) {
+  __shared__ float sg[8][32], sb[8][32];
+  const int Wp = G + 1, S = Wp * Wp, P = G * G;
+  const int c = blockIdx.x * 32 + (threadIdx.x & 31);
+  const int w = threadIdx.x >> 5;
+  float ag = 0.f, ab = 0.f;
+  if (c < Ch) {
+    for (int pos = blockIdx.y * 8 + w; pos < B * P; pos += 8 * gridDim.y) {
+      int b = pos / P, p = pos - b * P;
+      int y = p / G, x = p - y * G;
+      long long m = (long long)b * S + y * Wp + x;
+      float d = dhs[m * Ch + c];
+      ag = fmaf(d, h[(m + Wp + 1) * Ch + c], ag);
+      ab += d;
+    }
+  }
+  sg[w][threadIdx.x & 31] = ag; sb[w][threadIdx.x & 31] = ab;
+  __syncthreads();
+  if (w == 0 && c < Ch) {
+    for (int k = 1; k < 8; ++k) { ag += sg[k][threadIdx.x]; ab += sb[k][threadIdx.x]; }
+    atomicAdd(dgamma + c, ag * alpha);
+    atomicAdd(dbeta + c, ab);
+  }
+}
+
+template <typename TA>
+__global__ void __launch_bounds__(256) colsum_kernel(const TA* __restrict__ X, int ld, int M, int N, float* __restrict__ out) {
+  __shared__ float sm[8][32];
+  const int c = blockIdx.x * 32 + (threadIdx.x & 31);
+  const int w = threadIdx.x >> 5;
+  float acc = 0.f;
+  if (c < N)
+    for (int m = blockIdx.y * 8 + w; m < M; m += 8 * gridDim.y) acc += OpT<TA>::ld(X + (long long)m * ld + c);
+  sm[w][threadIdx.x & 31] = acc;
+  __syncthreads();
+  if (w == 0 && c < N) {
+    for (int k = 1; k < 8; ++k) acc += sm[k][threadIdx.x];
+    atomicAdd(out + c, acc);
+  }
+}
+
+// gaze_grcn77.py:206-211 backward; one warp per position
+__global__ void __launch_bounds__(256) fc_head_bwd_kernel(const float* __restrict__ dl, const float* __restrict__ h,
+                                                           const float* __restrict__ w, float* __restrict__ dhs,
+                                                           float* __restrict__ gw, float* __restrict__ gb, int B, int T,
+                                                           int t, int G, int Ch) {
+  const int Wp = G + 1, S = Wp * Wp, P = G * G;
+  int warp = (blockIdx.x * 256 + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= B * P) return;
+  int b = warp / P, p = warp - b * P;
+  int y = p / G, x = p - y * G;
+  long long m = (long long)b * S + y * Wp + x;
+  float d = dl[((long long)b * T + t) * P + p];
+  const float* hr = h + (m + Wp + 1) * Ch;
+  for (int c = lane; c < Ch; c += 32) {
+    dhs[m * Ch + c] = d * w[c];
+    atomicAdd(gw + c, d * hr[c]);
+  }
+  if (lane == 0) atomicAdd(gb, d);
+}
+
+}  // namespace rgp
+
+using namespace rgp;
+#define DISPATCH_TA(dtype, CALL_F32, CALL_BF16) \
+  do { if ((dtype) == 0) { CALL_F32; } else { CALL_BF16; } } while (0)
+
+extern "C" {
+
+int rgp_gru_bwd_last(const float* dhs, const float* gamma, float alpha, const float* z, const float* c,
+                     const float* hprev_f32, void* dg, int ldg, float* dhpart, int B, int G, int Ch, int dtype,
+                     void* stream) {
+  long long total = (long long)B * G * G * Ch;
+  int grid = (int)((total + 255) / 256);
+  cudaStream_t s = (cudaStream_t)stream;
+  DISPATCH_TA(dtype,
+              (gru_bwd_last_kernel<float><<<grid, 256, 0, s>>>(dhs, gamma, alpha, z, c, hprev_f32, (float*)dg, ldg, dhpart, B, G, Ch)),
+              (gru_bwd_last_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>(dhs, gamma, alpha, z, c, hprev_f32, (__nv_bfloat16*)dg, ldg, dhpart, B, G, Ch)));
+  return check_launch("rgp_gru_bwd_last");
+}
+
+int rgp_transpose_taps(const float* src, void* dst, int ntaps, int R, int Cc, int dtype, void* stream) {
+  dim3 grid((Cc + 31) / 32, (R + 31) / 32, ntaps);
+  cudaStream_t s = (cudaStream_t)stream;
+  DISPATCH_TA(dtype, (transpose_taps_kernel<float><<<grid, 256, 0, s>>>(src, (float*)dst, R, Cc)),
+              (transpose_taps_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>(src, (__nv_bfloat16*)dst, R, Cc)));
+  return check_launch("rgp_transpose_taps");
+}
+
+int rgp_head_patches(const float* dlogits, void* patches, int B, int T, int dtype, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  int grid = B * T * 49;
+  DISPATCH_TA(dtype, (head_patches_kernel<float><<<grid, 128, 0, s>>>(dlogits, (float*)patches, B, T)),
+              (head_patches_kernel<__nv_bfloat16><<<grid, 128, 0, s>>>(dlogits, (__nv_bfloat16*)patches, B, T)));
+  return check_launch("rgp_head_patches");
+}
+
+int rgp_head_w123t(const float* w123, void* out, int Ch, int dtype, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  int grid = (Ch * 384 + 255) / 256;
+  DISPATCH_TA(dtype, (head_w123t_kernel<float><<<grid, 256, 0, s>>>(w123, (float*)out, Ch)),
+              (head_w123t_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>(w123, (__nv_bfloat16*)out, Ch)));
+  return check_launch("rgp_head_w123t");
+}
+
+int rgp_head_compose_bwd(const float* dw123, const float* w1, const float* w2, const float* w3, const float* out_w,
+                         const float* w3f, const float* w23, float* dw23, float* dw3f, float* gw1, float* gw2,
+                         float* gw3, float* gout_w, int Ch, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  cb_dw1_kernel<<<(25 * 64 * Ch + 255) / 256, 256, 0, s>>>(dw123, w23, gw1, Ch);
+  cb_dw23_kernel<<<(121 * 64 * 32 + 255) / 256, 256, 0, s>>>(dw123, w1, dw23, Ch);
+  cb_dw2_kernel<<<(25 * 32 * 64 + 255) / 256, 256, 0, s>>>(dw23, w3f, gw2);
+  cb_dw3f_kernel<<<(49 * 32 + 255) / 256, 256, 0, s>>>(dw23, w2, dw3f);
+  cb_dw3_kernel<<<(49 * 12 * 32 + 255) / 256, 256, 0, s>>>(dw3f, w3, out_w, gw3, gout_w);
+  return check_launch("rgp_head_compose_bwd");
+}
+
+int rgp_bn_bwd(const float* dhs, const float* h_f32, float* dgamma, float* dbeta, float alpha, int B, int G, int Ch,
+               void* stream) {
+  int gy = (B * G * G + 63) / 64;
+  if (gy > 64) gy = 64;
+  dim3 grid((Ch + 31) / 32, gy);
+  bn_bwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(dhs, h_f32, dgamma, dbeta, alpha, B, G, Ch);
+  return check_launch("rgp_bn_bwd");
+}
+
+int rgp_colsum(const void* X, int ld, int M, int N, float* out, int dtype, void* stream) {
+  int gy = (M + 511) / 512;
+  if (gy > 296) gy = 296;
+  if (gy < 1) gy = 1;
+  dim3 grid((N + 31) / 32, gy);
+  cudaStream_t s = (cudaStream_t)stream;
+  DISPATCH_TA(dtype, (colsum_kernel<float><<<grid, 256, 0, s>>>((const float*)X, ld, M, N, out)),
+              (colsum_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>((const __nv_bfloat16*)X, ld, M, N, out)));
+  return check_launch("rgp_colsum");
+}
+
+int rgp_fc_head_bwd(const float* dlogits, const float* h_f32, const float* out_W, float* dhs, float* gout_W,
+                    float* gout_b, int B, int T, int t, int G, int Ch, void* stream) {
+  int warps = B * G * G;
+  int grid = (warps * 32 + 255) / 256;
+  fc_head_bwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(dlogits, h_f32, out_W, dhs, gout_W, gout_b, B, T, t, G, Ch);
+  return check_launch("rgp_fc_head_bwd");
+}
+
+}  // extern "C"

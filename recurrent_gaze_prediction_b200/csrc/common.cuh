@@ -74,6 +74,14 @@ __device__ __forceinline__ RowInfo make_row(const rgp_tapgemm_args& a, int m) {
     case RGP_EPI_STORE_OP:
       r.valid = true;
       break;
+    case RGP_EPI_DHS: {   // M rows in the head-input layout (S=100, Wp=10, data at +3,+3) -> recurrence q-row
+      int f = m / a.S, q = m - f * a.S;
+      int ya = q / a.Wp, xb = q - ya * a.Wp;
+      int i = ya - a.pado, j = xb - a.pado;
+      r.valid = (i >= 0) && (i < a.G) && (j >= 0) && (j < a.G);
+      r.orow = (long long)f * a.So + i * a.Wo + j;
+      break;
+    }
     default: {
       int f = m / a.S, q = m - f * a.S;
       int y = q / a.Wp, x = q - y * a.Wp;
@@ -81,10 +89,26 @@ __device__ __forceinline__ RowInfo make_row(const rgp_tapgemm_args& a, int m) {
       r.prow = (long long)m + a.Wp + 1;
       if (a.epi == RGP_EPI_GRU_C && a.out_op2)
         r.orow = (long long)f * a.So + (y + a.pado) * a.Wo + (x + a.pado);
+      if (a.epi == RGP_EPI_DX_DENSE) r.orow = (long long)f * a.P + y * a.G + x;
       break;
     }
   }
   return r;
+}
+
+// Gate backward of one GRU step at one (position m, channel n), given dh = dL/dh_t (gaze_grcn.py:118-127):
+//   h_t = z h_{t-1} + (1-z) c  =>  dz = dh (h_{t-1} - c), dc = dh (1-z), dh_{t-1} += dh z
+//   dpre_z = dz z (1-z) ; dpre_c = dc (1-c^2)      (dpre_r needs d(r.h), i.e. the transposed conv: BWD_RH)
+template <typename TA>
+__device__ __forceinline__ void gru_gate_bwd(const float* __restrict__ save_z, const float* __restrict__ save_c,
+                                             const float* __restrict__ hprev, TA* __restrict__ dg, int ldg,
+                                             float* __restrict__ dhpart, int Ch, long long m, long long prow, int n,
+                                             float dh) {
+  float z = save_z[m * Ch + n], c = save_c[m * Ch + n], hp = hprev[prow * Ch + n];
+  float dz = dh * (hp - c), dc = dh * (1.0f - z);
+  OpT<TA>::st(dg + m * ldg + n, dz * z * (1.0f - z));
+  OpT<TA>::st(dg + m * ldg + 2 * Ch + n, dc * (1.0f - c * c));
+  dhpart[m * Ch + n] = dh * z;
 }
 
 // One output element. TA = operand dtype.
@@ -142,6 +166,33 @@ __device__ __forceinline__ void epi_elem(const rgp_tapgemm_args& a, const RowInf
       }
       break;
     }
+    case RGP_EPI_BWD_RH: {  // acc = dL/d(r.h) at this position
+      if (r.valid) {
+        long long m = r.m;
+        float rr = a.save_r[m * a.Ch + n], hp = a.hprev_f32[r.prow * a.Ch + n];
+        OpT<TA>::st((TA*)a.dg + m * a.ldg + a.Ch + n, acc * hp * rr * (1.0f - rr));
+        a.dhpart[m * a.Ch + n] += acc * rr;
+      }
+      break;
+    }
+    case RGP_EPI_BWD_H: {  // acc = convT([dpre_z,dpre_r]) of step t -> full dL/dh_{t-1}, then gates of step t-1
+      if (r.valid) {
+        long long m = r.m;
+        float hd = a.dhs[m * a.Ch + n];
+        if (a.bias) hd *= a.bias[n] * a.alpha;
+        float dh = acc + a.dhpart[m * a.Ch + n] + hd;
+        gru_gate_bwd<TA>(a.save_z, a.save_c, a.hprev_f32, (TA*)a.dg, a.ldg, a.dhpart, a.Ch, m, r.prow, n, dh);
+      }
+      break;
+    }
+    case RGP_EPI_DHS: {
+      if (r.valid) a.out_f32[r.orow * a.ldo + n] = acc;
+      break;
+    }
+    case RGP_EPI_DX_DENSE: {
+      if (r.valid) OpT<TA>::st((TA*)a.out_op + r.orow * a.ldo + n, acc);
+      break;
+    }
     case RGP_EPI_HEAD: {  // composed head: class n = ry*6+rx -> logits[b,t,6a+ry-3,6b+rx-3]
       if (r.valid && n < 36) {
         int ry = n / 6, rx = n - ry * 6;
@@ -154,6 +205,8 @@ __device__ __forceinline__ void epi_elem(const rgp_tapgemm_args& a, const RowInf
 }
 
 int tapgemm_simt(const rgp_tapgemm_args& a, cudaStream_t s);
+int wgrad_simt(const rgp_wgrad_args& a, cudaStream_t s);
+int wgrad_tc(const rgp_wgrad_args& a, cudaStream_t s);
 int tapgemm_tc(const rgp_tapgemm_args& a, cudaStream_t s);
 
 }  // namespace rgp

@@ -203,19 +203,20 @@ class GazeEngine(object):
         B, T, S, Ch, Cin = self.B, self.T, self.S, self.Ch, self.Cin
         dev, tdt = self.device, self.tdt
         z = lambda *shape, dt=torch.float32: torch.zeros(*shape, dtype=dt, device=dev)
-        self.rows_step = B * S + self.tail
+        self.rows_step = B * S + self.tail        # rows a step-GEMM may touch: its slab + the zero halo behind it
         self.Apack = z(T * B * self.P, self.Cfeat, dt=tdt)
         self.Xp = z(T * B * S + self.tail, Cin, dt=tdt)
         self.Xg = z(T * B * S, self.ngx * Ch)
-        self.Hop = z(T + 1, self.rows_step, Ch, dt=tdt)          # operand copies of h_0..h_T (p-layout)
-        self.Hf = z(T + 1, self.rows_step, Ch)                   # fp32 master state
+        # h_0..h_T as contiguous B*S-row slabs (slab t = h_{t-1}): operand copy (p-layout) + fp32 master
+        self.Hop = z((T + 1) * B * S + self.tail, Ch, dt=tdt)
+        self.Hf = z((T + 1) * B * S + self.tail, Ch)
         nsl = T if self.train else 1
         if self.lstm:
             self.Cf = z(self.rows_step, Ch)
             self.Hconv = z(B * S, 3 * Ch)
             self.Lsave = z(T, B * S, 5 * Ch) if self.train else None
         else:
-            self.RH = z(nsl, self.rows_step, Ch, dt=tdt)
+            self.RH = z(nsl * B * S + self.tail, Ch, dt=tdt)
             self.Z = z(nsl, B * S, Ch)
             self.Rs = z(T, B * S, Ch) if self.train else None
             self.Cs = z(T, B * S, Ch) if self.train else None
@@ -231,7 +232,28 @@ class GazeEngine(object):
         self.frame_loss = z(B * T)
         self.loss = z(1)
         if self.train:
+            if self.lstm:
+                raise NotImplementedError("BPTT is implemented for the ConvGRU models (gaze_grcn, gaze_grcn77); "
+                                          "gaze_lstm is forward-only in this round")
             self.dlogits = z(B, T, self.GH, self.GH)
+            self.dG = z(T * B * S, 3 * Ch, dt=tdt)          # dL/d(pre-activations), columns z | r | c
+            self.dhs = z(T * B * S, Ch)                     # dL/d(head input) in the recurrence q-layout
+            self.dhpart = z(B * S, Ch)
+            self.UcT = z(9 * Ch, Ch, dt=tdt)
+            self.UzrT = z(9 * Ch, 2 * Ch, dt=tdt)
+            self.WxT = z(9 * Cin, 3 * Ch, dt=tdt)
+            self.dEmb = z(T * B * self.P, Cin, dt=tdt)
+            if self.head == "deconv":
+                self.patches = z(T * B * HEAD_S + 128, 384, dt=tdt)
+                self.w123T = z(Ch, 384, dt=tdt)
+                self.dw123 = z(384, Ch)
+                self.dw23 = z(121 * 64)
+                self.dw3f = z(49 * 32)
+            self.step = 0
+
+    def _slab(self, buf, t):
+        """device address of the B*S-row slab t of a flat [rows, C] buffer"""
+        return buf.data_ptr() + t * self.B * self.S * buf.shape[-1] * buf.element_size()
 
     def _s(self):
         if self.device.type == "cuda":
@@ -250,15 +272,16 @@ class GazeEngine(object):
         self.lib.rgp_tapgemm(C.byref(a), self._s())
 
     # ------------------------------------------------------------------ forward
-    def forward(self, c3d=None, emb=None, gt=None, loss_type="xentropy"):
+    def forward(self, c3d=None, emb=None, gt=None, loss_type="xentropy", global_batch=None):
         """c3d [B,T,Cfeat,G,G] fp32 (reference entry, gaze_grcn.py:173) or emb [B,T,G,G,Cin] fp32
         (already-projected features).  Returns logits [B,T,GH,GW]; with gt also fills probs and loss."""
         self.stage_embed(c3d, emb)
         self.stage_i2h()
         self.stage_recurrence()
         self.stage_head()
+        self.entry = "c3d" if c3d is not None else "emb"
         if gt is not None:
-            self.loss_fwd(gt, loss_type)
+            self.loss_fwd(gt, loss_type, global_batch)
         return self.logits
 
     def _pop(self, name):
@@ -301,31 +324,31 @@ class GazeEngine(object):
             if self.lstm:
                 if t == 0:
                     lib.rgp_zero(self.Cf.data_ptr(), self.Cf.numel() * 4, s)
-                self._gemm(A=self.Hop[t].data_ptr(), rowsA=self.rows_step, lda=Ch, Bw=pop("Wh_op"), M=M, N=3 * Ch,
+                self._gemm(A=self._slab(self.Hop, t), rowsA=self.rows_step, lda=Ch, Bw=pop("Wh_op"), M=M, N=3 * Ch,
                            K=Ch, taps=self.taps3, epi=L.EPI_STORE_F32, out_f32=self.Hconv.data_ptr(), ldo=3 * Ch,
                            S=S, Wp=Wp, G=G)
                 lib.rgp_lstm_gates(xg, NX, self.Hconv.data_ptr(), self._ptr("wci"), self._ptr("wcf"),
-                                   self._ptr("wco"), self.Cf.data_ptr(), self.Hf[t + 1].data_ptr(),
-                                   self.Hop[t + 1].data_ptr(), hs, B, G, Ch, HEAD_S, HEAD_W, HEAD_PAD, self.dtype,
+                                   self._ptr("wco"), self.Cf.data_ptr(), self._slab(self.Hf, t + 1),
+                                   self._slab(self.Hop, t + 1), hs, B, G, Ch, HEAD_S, HEAD_W, HEAD_PAD, self.dtype,
                                    self.Lsave[t].data_ptr() if self.train else 0, s)
             else:
                 sl = t if self.train else 0
                 common = dict(M=M, K=Ch, taps=self.taps3, S=S, Wp=Wp, G=G, Ch=Ch, B=B, T=T, t=t, xg=xg, ldx=NX,
-                              rowsA=self.rows_step, lda=Ch, hprev_f32=self.Hf[t].data_ptr(),
+                              rowsA=self.rows_step, lda=Ch, hprev_f32=self._slab(self.Hf, t),
                               z_f32=self.Z[sl].data_ptr())
-                self._gemm(A=self.Hop[t].data_ptr(), Bw=pop("Uzr_op"), N=2 * Ch, epi=L.EPI_GRU_ZR,
-                           out_op=self.RH[sl].data_ptr(), save_r=self.Rs[t].data_ptr() if self.train else 0,
+                self._gemm(A=self._slab(self.Hop, t), Bw=pop("Uzr_op"), N=2 * Ch, epi=L.EPI_GRU_ZR,
+                           out_op=self._slab(self.RH, sl), save_r=self.Rs[t].data_ptr() if self.train else 0,
                            **common)
                 extra = {}
                 if self.use_bn:
                     extra = dict(bias=self._ptr("bn_gamma") + t * Ch * 4, bias2=self._ptr("bn_beta") + t * Ch * 4,
                                  alpha=1.0 / math.sqrt(1.0 + BN_EPS))
-                self._gemm(A=self.RH[sl].data_ptr(), Bw=pop("Uc_op"), N=Ch, epi=L.EPI_GRU_C,
-                           hnext_f32=self.Hf[t + 1].data_ptr(), out_op=self.Hop[t + 1].data_ptr(), out_op2=hs,
+                self._gemm(A=self._slab(self.RH, sl), Bw=pop("Uc_op"), N=Ch, epi=L.EPI_GRU_C,
+                           hnext_f32=self._slab(self.Hf, t + 1), out_op=self._slab(self.Hop, t + 1), out_op2=hs,
                            So=HEAD_S, Wo=HEAD_W, pado=HEAD_PAD, save_c=self.Cs[t].data_ptr() if self.train else 0,
                            **common, **extra)
             if self.head == "fc":   # gaze_grcn77.py:206-211
-                lib.rgp_fc_head(self.Hf[t + 1].data_ptr(), self._ptr("out_W"), self._ptr("out_b"),
+                lib.rgp_fc_head(self._slab(self.Hf, t + 1), self._ptr("out_W"), self._ptr("out_b"),
                                 self.logits.data_ptr(), B, T, t, G, Ch, s)
 
     def stage_head(self):
@@ -379,14 +402,120 @@ class GazeEngine(object):
                                   self.bhead.data_ptr(), self.Ch, self.dtype, self._s())
         self.head_version = self.param_version
 
-    def loss_fwd(self, gt, loss_type="xentropy"):
+    def loss_fwd(self, gt, loss_type="xentropy", global_batch=None):
+        """global_batch: clips over all data-parallel ranks (the loss and its gradient are means over B_global*T)."""
         if loss_type not in LOSS_TYPES:
             raise NotImplementedError(str(loss_type))   # gaze_rnn.py:405-406
         assert tuple(gt.shape) == tuple(self.logits.shape) and gt.dtype == torch.float32
         n, hw = self.B * self.T, self.GH * self.GH
         self.lib.rgp_softmax_xent_fwd_bwd(self.logits.data_ptr(), gt.data_ptr(), self.probs.data_ptr(),
                                           self.dlogits.data_ptr() if self.train else 0,
-                                          self.frame_loss.data_ptr(), n, hw, 1.0 / n, LOSS_TYPES[loss_type],
+                                          self.frame_loss.data_ptr(), n, hw, 1.0 / ((global_batch or self.B) * self.T),
+                                          LOSS_TYPES[loss_type],
                                           self._s())
         self.lib.rgp_reduce_sum(self.frame_loss.data_ptr(), n, self.loss.data_ptr(), self._s())
         return self.loss
+
+    # ------------------------------------------------------------------ backward (BPTT) — base.py:278-281
+    def _wgrad(self, Y, ldy, ycol0, Ny, X, rowsX, ldx, Nx, M, taps, D):
+        a = L.WgradArgs()
+        a.Y, a.ldy, a.ycol0, a.Ny = Y, ldy, ycol0, Ny
+        a.X, a.rowsX, a.ldx, a.xcol0, a.Nx = X, rowsX, ldx, 0, Nx
+        a.M, a.ntaps = M, len(taps)
+        for i, o in enumerate(taps):
+            a.tap_off[i] = o
+        a.D, a.dtype, a.engine = D, self.dtype, self.engine
+        self.lib.rgp_wgrad(C.byref(a), self._s())
+
+    def backward(self):
+        """Hand-written BPTT of the last forward(gt=...) (train=True): fills self.grads (flat, op layouts).
+        dL/dlogits = (softmax - gt)/(B*T) was written by the fused softmax/loss kernel."""
+        assert self.train, "construct the engine with train=True"
+        lib, s = self.lib, self._s()
+        B, T, S, Ch, Cin, Wp, G, P = self.B, self.T, self.S, self.Ch, self.Cin, self.Wp, self.G, self.P
+        M = B * S
+        es = self.dG.element_size()
+        g = lambda name: self._ptr(name, self.grads)
+        alpha = 1.0 / math.sqrt(1.0 + BN_EPS)
+        lib.rgp_zero(self.grads.data_ptr(), self.grads.numel() * 4, s)
+        # ---- head backward
+        if self.head == "deconv":
+            lib.rgp_head_patches(self.dlogits.data_ptr(), self.patches.data_ptr(), B, T, self.dtype, s)
+            lib.rgp_head_w123t(self.w123.data_ptr(), self.w123T.data_ptr(), Ch, self.dtype, s)
+            self._gemm(A=self.patches.data_ptr(), rowsA=self.patches.shape[0], lda=384, Bw=self.w123T.data_ptr(),
+                       M=T * B * HEAD_S, N=Ch, K=384, taps=[0], epi=L.EPI_DHS, S=HEAD_S, Wp=HEAD_W, pado=HEAD_PAD,
+                       G=G, So=S, Wo=Wp, out_f32=self.dhs.data_ptr(), ldo=Ch)
+            lib.rgp_zero(self.dw123.data_ptr(), self.dw123.numel() * 4, s)
+            self._wgrad(self.patches.data_ptr(), 384, 0, 384, self.HS.data_ptr(), self.HS.shape[0], Ch, Ch,
+                        T * B * HEAD_S, [0], self.dw123.data_ptr())
+            lib.rgp_head_compose_bwd(self.dw123.data_ptr(), self._ptr("w1"), self._ptr("w2"), self._ptr("w3"),
+                                     self._ptr("out_W"), self.w3f.data_ptr(), self.w23.data_ptr(),
+                                     self.dw23.data_ptr(), self.dw3f.data_ptr(), g("w1"), g("w2"), g("w3"),
+                                     g("out_W"), Ch, s)
+            lib.rgp_reduce_sum(self.dlogits.data_ptr(), self.dlogits.numel(), g("out_b"), s)
+            if self.use_bn:
+                for t in range(T):
+                    lib.rgp_bn_bwd(self._slab(self.dhs, t), self._slab(self.Hf, t + 1), g("bn_gamma") + t * Ch * 4,
+                                   g("bn_beta") + t * Ch * 4, alpha, B, G, Ch, s)
+        else:
+            for t in range(T):
+                lib.rgp_fc_head_bwd(self.dlogits.data_ptr(), self._slab(self.Hf, t + 1), self._ptr("out_W"),
+                                    self._slab(self.dhs, t), g("out_W"), g("out_b"), B, T, t, G, Ch, s)
+        # ---- transposed operand copies of the conv weights (dX = conv^T)
+        lib.rgp_transpose_taps(self._ptr("Uc_op"), self.UcT.data_ptr(), 9, Ch, Ch, self.dtype, s)
+        lib.rgp_transpose_taps(self._ptr("Uzr_op"), self.UzrT.data_ptr(), 9, 2 * Ch, Ch, self.dtype, s)
+        # ---- recurrence, backwards in time: two tap GEMMs per step (mirror of the forward)
+        gam = (lambda t: self._ptr("bn_gamma") + t * Ch * 4) if self.use_bn else (lambda t: 0)
+        lib.rgp_gru_bwd_last(self._slab(self.dhs, T - 1), gam(T - 1), alpha, self.Z[T - 1].data_ptr(),
+                             self.Cs[T - 1].data_ptr(), self._slab(self.Hf, T - 1), self._slab(self.dG, T - 1),
+                             3 * Ch, self.dhpart.data_ptr(), B, G, Ch, self.dtype, s)
+        btaps = [Wp + 1 - o for o in self.taps3]
+        for t in range(T - 1, -1, -1):
+            dg_t = self._slab(self.dG, t)
+            common = dict(M=M, rowsA=M, lda=3 * Ch, N=Ch, taps=btaps, S=S, Wp=Wp, G=G, Ch=Ch,
+                          dhpart=self.dhpart.data_ptr())
+            self._gemm(A=dg_t + 2 * Ch * es, K=Ch, Bw=self.UcT.data_ptr(), epi=L.EPI_BWD_RH,
+                       save_r=self.Rs[t].data_ptr(), hprev_f32=self._slab(self.Hf, t), dg=dg_t, ldg=3 * Ch, **common)
+            if t > 0:
+                extra = dict(bias=gam(t - 1), alpha=alpha) if self.use_bn else {}
+                self._gemm(A=dg_t, K=2 * Ch, Bw=self.UzrT.data_ptr(), epi=L.EPI_BWD_H,
+                           dhs=self._slab(self.dhs, t - 1), save_z=self.Z[t - 1].data_ptr(),
+                           save_c=self.Cs[t - 1].data_ptr(), hprev_f32=self._slab(self.Hf, t - 1),
+                           dg=self._slab(self.dG, t - 1), ldg=3 * Ch, **common, **extra)
+        # ---- weight gradients: contractions over all T*B*S rows at once
+        rowsT = T * M
+        self._wgrad(self.dG.data_ptr(), 3 * Ch, 0, 2 * Ch, self.Hop.data_ptr(), self.Hop.shape[0], Ch, Ch, rowsT,
+                    self.taps3, g("Uzr_op"))
+        self._wgrad(self.dG.data_ptr(), 3 * Ch, 2 * Ch, Ch, self.RH.data_ptr(), self.RH.shape[0], Ch, Ch, rowsT,
+                    self.taps3, g("Uc_op"))
+        self._wgrad(self.dG.data_ptr(), 3 * Ch, 0, 3 * Ch, self.Xp.data_ptr(), self.Xp.shape[0], Cin, Cin, rowsT,
+                    self.taps3, g("Wx_op"))
+        # ---- projection (only when the reference entry [B,T,1024,7,7] was used)
+        if self.entry == "c3d":
+            lib.rgp_transpose_taps(self._ptr("Wx_op"), self.WxT.data_ptr(), 9, 3 * Ch, Cin, self.dtype, s)
+            self._gemm(A=self.dG.data_ptr(), rowsA=rowsT, lda=3 * Ch, K=3 * Ch, Bw=self.WxT.data_ptr(), M=rowsT, N=Cin,
+                       taps=btaps, epi=L.EPI_DX_DENSE, S=S, Wp=Wp, G=G, P=P, out_op=self.dEmb.data_ptr(), ldo=Cin)
+            self._wgrad(self.dEmb.data_ptr(), Cin, 0, Cin, self.Apack.data_ptr(), self.Apack.shape[0], self.Cfeat,
+                        self.Cfeat, T * B * P, [0], g("proj_W_op"))
+            lib.rgp_colsum(self.dEmb.data_ptr(), Cin, T * B * P, Cin, g("proj_b"), self.dtype, s)
+
+    # ------------------------------------------------------------------ optimiser — base.py:262-297, gaze_rnn.py:435-444
+    def learning_rate(self, lr0=1e-4, decay=0.8, decay_steps=500):
+        return lr0 * decay ** (self.step // decay_steps)
+
+    def optimizer_step(self, lr0=1e-4, decay=0.8, clip=10.0, beta1=0.9, beta2=0.999, eps=1e-8, allreduce=None):
+        """clip_by_global_norm + TF-Adam on the flat buffers.  `allreduce(grads)` (optional) sums the gradient
+        over data-parallel ranks first: the norm must be taken over the GLOBAL gradient (base.py:287-297)."""
+        lib, s = self.lib, self._s()
+        if allreduce is not None:
+            allreduce(self.grads)
+        lib.rgp_zero(self.sumsq.data_ptr(), 8, s)
+        lib.rgp_sumsq(self.grads.data_ptr(), self.nparams, self.sumsq.data_ptr(), s)
+        t = self.step + 1
+        lr = self.learning_rate(lr0, decay)
+        lr_t = lr * math.sqrt(1.0 - beta2 ** t) / (1.0 - beta1 ** t)
+        lib.rgp_gradnorm_clip_adam(self.params.data_ptr(), self.grads.data_ptr(), self.adam_m.data_ptr(),
+                                   self.adam_v.data_ptr(), self.nparams, self.sumsq.data_ptr(), clip, lr_t, beta1,
+                                   beta2, eps, self.params_op.data_ptr() if self.dtype != 0 else 0, self.dtype, s)
+        self.step += 1
+        self.param_version += 1

@@ -11,7 +11,8 @@ import ctypes as C
 import os
 
 RGP_MAX_TAPS = 16
-EPI_STORE_F32, EPI_PROJ, EPI_GRU_ZR, EPI_GRU_C, EPI_HEAD, EPI_STORE_OP_P, EPI_STORE_OP = range(7)
+(EPI_STORE_F32, EPI_PROJ, EPI_GRU_ZR, EPI_GRU_C, EPI_HEAD, EPI_STORE_OP_P, EPI_STORE_OP,
+ EPI_BWD_RH, EPI_BWD_H, EPI_DHS, EPI_DX_DENSE) = range(11)
 
 _vp, _i, _ll, _f, _d = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_double
 
@@ -33,6 +34,18 @@ class TapGemmArgs(C.Structure):
         ("hprev_f32", _vp), ("hnext_f32", _vp), ("z_f32", _vp),
         ("save_r", _vp), ("save_c", _vp),
         ("bias", _vp), ("bias2", _vp), ("alpha", _f),
+        ("dhpart", _vp), ("dhs", _vp), ("save_z", _vp), ("dg", _vp), ("ldg", _i),
+    ]
+
+
+class WgradArgs(C.Structure):
+    """Mirror of ``rgp_wgrad_args`` (include/rgp.h)."""
+    _fields_ = [
+        ("Y", _vp), ("ldy", _i), ("ycol0", _i), ("Ny", _i),
+        ("X", _vp), ("rowsX", _ll), ("ldx", _i), ("xcol0", _i), ("Nx", _i),
+        ("M", _i), ("ntaps", _i), ("tap_off", _i * RGP_MAX_TAPS),
+        ("D", _vp),
+        ("dtype", _i), ("engine", _i),
     ]
 
 
@@ -49,6 +62,15 @@ _SIGS = {
     "rgp_sumsq": [_vp, _ll, _vp, _vp],
     "rgp_gradnorm_clip_adam": [_vp, _vp, _vp, _vp, _ll, _vp, _f, _f, _f, _f, _f, _vp, _i, _vp],
     "rgp_zero": [_vp, _ll, _vp],
+    "rgp_wgrad": [C.POINTER(WgradArgs), _vp],
+    "rgp_gru_bwd_last": [_vp, _vp, _f, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _i, _vp],
+    "rgp_transpose_taps": [_vp, _vp, _i, _i, _i, _i, _vp],
+    "rgp_head_patches": [_vp, _vp, _i, _i, _i, _vp],
+    "rgp_head_compose_bwd": [_vp] * 13 + [_i, _vp],
+    "rgp_head_w123t": [_vp, _vp, _i, _i, _vp],
+    "rgp_bn_bwd": [_vp, _vp, _vp, _vp, _f, _i, _i, _i, _vp],
+    "rgp_colsum": [_vp, _i, _i, _i, _vp, _i, _vp],
+    "rgp_fc_head_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp],
 }
 
 

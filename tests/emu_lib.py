@@ -84,6 +84,15 @@ class EmuLib(object):
                 ok = (ya < 9) & (xb < 9) & (Y >= 0) & (Y < 49) & (X >= 0) & (X < 49)
                 out[b[ok], t[ok], Y[ok], X[ok]] = acc[ok, n] + bias
             return 0
+        if e == L.EPI_DHS:
+            f, q = np.divmod(rows, a.S)
+            ya, xb = np.divmod(q, a.Wp)
+            i, j = ya - a.pado, xb - a.pado
+            ok = (i >= 0) & (i < a.G) & (j >= 0) & (j < a.G)
+            orow = f * a.So + i * a.Wo + j
+            out = arr(a.out_f32, (int(orow[ok].max()) + 1, a.ldo))
+            out[orow[ok], :N] = acc[ok]
+            return 0
         # p/q-layout epilogues
         f, q = np.divmod(rows, a.S)
         y, x = np.divmod(q, a.Wp)
@@ -95,8 +104,32 @@ class EmuLib(object):
             out = arr(a.out_op, (nrow_p, a.ldo))
             out[prow[valid], :N] = acc[valid]
             return 0
-        xg = arr(a.xg, (M, a.ldx))
+        if e == L.EPI_DX_DENSE:
+            orow = f * a.P + y * a.G + x
+            out = arr(a.out_op, (int(orow[valid].max()) + 1, a.ldo))
+            out[orow[valid], :N] = acc[valid]
+            return 0
         hprev = arr(a.hprev_f32, (nrow_p, Ch))
+        if e in (L.EPI_BWD_RH, L.EPI_BWD_H):
+            dg = arr(a.dg, (M, a.ldg))
+            dhp = arr(a.dhpart, (M, Ch))
+            v, pv = valid, prow[valid]
+            if e == L.EPI_BWD_RH:
+                r = arr(a.save_r, (M, Ch))
+                dg[v, Ch:2 * Ch] = acc[v] * hprev[pv] * r[v] * (1 - r[v])
+                dhp[v] += acc[v] * r[v]
+                return 0
+            hd = arr(a.dhs, (M, Ch))[v]
+            if a.bias:
+                hd = hd * arr(a.bias, (Ch,))[None] * np.float32(a.alpha)
+            dh = acc[v] + dhp[v] + hd
+            z, c = arr(a.save_z, (M, Ch))[v], arr(a.save_c, (M, Ch))[v]
+            hp = hprev[pv]
+            dg[v, :Ch] = dh * (hp - c) * z * (1 - z)
+            dg[v, 2 * Ch:3 * Ch] = dh * (1 - z) * (1 - c * c)
+            dhp[v] = dh * z
+            return 0
+        xg = arr(a.xg, (M, a.ldx))
         if e == L.EPI_GRU_ZR:
             s = _sig(acc + xg[:, :2 * Ch])
             arr(a.z_f32, (M, Ch))[:] = s[:, :Ch]
@@ -264,4 +297,121 @@ class EmuLib(object):
         Mm[:] = b1 * Mm + (1 - b1) * gg
         V[:] = b2 * V + (1 - b2) * gg * gg
         P[:] = P - lr_t * Mm / (np.sqrt(V) + eps)
+        return 0
+
+    # -------------------------------------------------------------- BPTT
+    def rgp_wgrad(self, aref, stream):
+        a = aref._obj
+        assert a.dtype == 0
+        Y = arr(a.Y, (a.M, a.ldy))[:, a.ycol0:a.ycol0 + a.Ny].astype(np.float64)
+        X = arr(a.X, (a.rowsX, a.ldx))
+        D = arr(a.D, (a.ntaps, a.Ny, a.Nx))
+        rows = np.arange(a.M)
+        for tp in range(a.ntaps):
+            r = rows + a.tap_off[tp]
+            ok = (r >= 0) & (r < a.rowsX)
+            Xt = np.zeros((a.M, a.Nx))
+            Xt[ok] = X[r[ok], a.xcol0:a.xcol0 + a.Nx]
+            D[tp] += (Y.T @ Xt).astype(np.float32)
+        return 0
+
+    def rgp_gru_bwd_last(self, dhs, gamma, alpha, z, c, hprev, dg, ldg, dhpart, B, G, Ch, dtype, stream):
+        Wp = G + 1
+        S = Wp * Wp
+        M = B * S
+        rows = np.arange(M)
+        f, q = np.divmod(rows, S)
+        y, x = np.divmod(q, Wp)
+        v = (y < G) & (x < G)
+        pv = rows[v] + Wp + 1
+        dh = arr(dhs, (M, Ch))[v]
+        if gamma:
+            dh = dh * arr(gamma, (Ch,))[None] * np.float32(alpha)
+        zz, cc, hp = arr(z, (M, Ch))[v], arr(c, (M, Ch))[v], arr(hprev, (M + Wp + 2, Ch))[pv]
+        d = arr(dg, (M, ldg))
+        d[v, :Ch] = dh * (hp - cc) * zz * (1 - zz)
+        d[v, 2 * Ch:3 * Ch] = dh * (1 - zz) * (1 - cc * cc)
+        arr(dhpart, (M, Ch))[v] = dh * zz
+        return 0
+
+    def rgp_transpose_taps(self, src, dst, ntaps, R, Cc, dtype, stream):
+        arr(dst, (ntaps, Cc, R))[:] = arr(src, (ntaps, R, Cc)).transpose(0, 2, 1)
+        return 0
+
+    def rgp_head_patches(self, dlogits, patches, B, T, dtype, stream):
+        dl = arr(dlogits, (B, T, 49, 49))
+        pt = arr(patches, (T * B * 100, 384))
+        pad = np.zeros((B, T, 49 + 18, 49 + 18), dtype=np.float32)
+        pad[:, :, 3:52, 3:52] = dl          # index Y+3
+        for t in range(T):
+            for b in range(B):
+                for i in range(7):
+                    for j in range(7):
+                        row = (t * B + b) * 100 + (i + 3) * 10 + j + 3
+                        pt[row, :361] = pad[b, t, 6 * i:6 * i + 19, 6 * j:6 * j + 19].reshape(-1)
+                        pt[row, 361:] = 0
+        return 0
+
+    def rgp_head_w123t(self, w123, out, Ch, dtype, stream):
+        o = arr(out, (Ch, 384))
+        o[:] = 0
+        o[:, :361] = arr(w123, (361, Ch)).T
+        return 0
+
+    def rgp_head_compose_bwd(self, dw123, w1, w2, w3, ow, w3f, w23, dw23, dw3f, gw1, gw2, gw3, gow, Ch, stream):
+        D = arr(dw123, (384, Ch))[:361].reshape(19, 19, Ch).astype(np.float64)
+        W1, W2, W3 = arr(w1, (5, 5, 64, Ch)), arr(w2, (5, 5, 32, 64)), arr(w3, (7, 7, 12, 32))
+        oW, W3f, W23 = arr(ow, (12,)), arr(w3f, (7, 7, 32)), arr(w23, (11, 11, 64))
+        G1, G2, G3, Go = arr(gw1, (5, 5, 64, Ch)), arr(gw2, (5, 5, 32, 64)), arr(gw3, (7, 7, 12, 32)), arr(gow, (12,))
+        d23 = np.zeros((11, 11, 64))
+        for k1 in range(5):
+            for l1 in range(5):
+                blk = D[2 * k1:2 * k1 + 11, 2 * l1:2 * l1 + 11]           # [s,t,c]
+                G1[k1, l1] += np.einsum("stc,stm->mc", blk, W23)
+                d23 += np.einsum("stc,mc->stm", blk, W1[k1, l1])
+        d3f = np.zeros((7, 7, 32))
+        for k2 in range(5):
+            for l2 in range(5):
+                blk = d23[k2:k2 + 7, l2:l2 + 7]                            # [k3,l3,m]
+                G2[k2, l2] += np.einsum("klm,kle->em", blk, W3f)
+                d3f += np.einsum("klm,em->kle", blk, W2[k2, l2])
+        arr(dw23, (11, 11, 64))[:] = d23
+        arr(dw3f, (7, 7, 32))[:] = d3f
+        G3 += np.einsum("kle,o->kloe", d3f, oW)
+        Go += np.einsum("kle,kloe->o", d3f, W3)
+        return 0
+
+    def rgp_bn_bwd(self, dhs, h, dgamma, dbeta, alpha, B, G, Ch, stream):
+        Wp = G + 1
+        S = Wp * Wp
+        M = B * S
+        rows = np.arange(M)
+        f, q = np.divmod(rows, S)
+        y, x = np.divmod(q, Wp)
+        v = (y < G) & (x < G)
+        d = arr(dhs, (M, Ch))[v].astype(np.float64)
+        hh = arr(h, (M + Wp + 2, Ch))[rows[v] + Wp + 1]
+        arr(dgamma, (Ch,))[:] += (alpha * (d * hh).sum(0)).astype(np.float32)
+        arr(dbeta, (Ch,))[:] += d.sum(0).astype(np.float32)
+        return 0
+
+    def rgp_colsum(self, X, ld, M, N, out, dtype, stream):
+        arr(out, (N,))[:] += arr(X, (M, ld))[:, :N].astype(np.float64).sum(0).astype(np.float32)
+        return 0
+
+    def rgp_fc_head_bwd(self, dlogits, h, w, dhs, gw, gb, B, T, t, G, Ch, stream):
+        Wp = G + 1
+        S = Wp * Wp
+        dl = arr(dlogits, (B, T, G, G))
+        hh = arr(h, (B * S + Wp + 2, Ch))
+        ww = arr(w, (Ch,))
+        dh = arr(dhs, (B * S, Ch))
+        for b in range(B):
+            for y in range(G):
+                for x in range(G):
+                    m = b * S + y * Wp + x
+                    d = dl[b, t, y, x]
+                    dh[m] = d * ww
+                    arr(gw, (Ch,))[:] += d * hh[m + Wp + 1]
+                    arr(gb, (1,))[0] += d
         return 0

@@ -53,3 +53,52 @@ def test_param_roundtrip():
     back = eng.op_to_tf(eng.params.numpy())
     for k, v in p.items():
         assert np.allclose(back[k].reshape(np.asarray(v).shape), np.asarray(v, dtype=np.float32)), k
+
+
+def _grad_check(model, entry, loss_type="xentropy", B=2, T=3, Ch=16):
+    p, c3d, emb, gt, eng = _setup(model, B=B, T=T, Ch=Ch, train=True)
+    kw = dict(c3d=torch.from_numpy(c3d)) if entry == "c3d" else dict(emb=torch.from_numpy(emb))
+    okw = dict(c3d=c3d.astype(np.float64)) if entry == "c3d" else dict(emb=emb.astype(np.float64))
+    eng.forward(gt=torch.from_numpy(gt), loss_type=loss_type, **kw)
+    eng.backward()
+    got = eng.op_to_tf(eng.grads.numpy())
+    _, _, _, ref = O.forward_loss_grads(model, p, gt.astype(np.float64), loss_type=loss_type, **okw)
+    for k, r in ref.items():
+        a = got[k].reshape(r.shape).astype(np.float64)
+        scale = np.abs(r).max()
+        # out_b's gradient is sum(softmax - gt) = 0 up to fp32 cancellation -> absolute floor
+        assert np.abs(a - r).max() <= 2e-4 * scale + (1e-6 if k == "out_b" else 1e-12), (k, np.abs(a - r).max(), scale)
+    return eng, p
+
+
+@pytest.mark.parametrize("model", ["gaze_grcn", "gaze_grcn77"])
+@pytest.mark.parametrize("entry", ["c3d", "emb"])
+def test_bptt_matches_oracle_autograd(model, entry):
+    _grad_check(model, entry)
+
+
+def test_bptt_l2_loss():
+    _grad_check("gaze_grcn", "c3d", loss_type="l2")
+
+
+def test_clip_adam_steps_match_oracle():
+    """Two optimiser steps (global-norm clip + TF-Adam + staircase LR) against the oracle restatement."""
+    model = "gaze_grcn"
+    p, c3d, emb, gt, eng = _setup(model, train=True)
+    names = list(p.keys())
+    params = [np.asarray(p[k], dtype=np.float64).copy() for k in names]
+    m = [np.zeros_like(x) for x in params]
+    v = [np.zeros_like(x) for x in params]
+    for step in range(2):
+        eng.forward(c3d=torch.from_numpy(c3d), gt=torch.from_numpy(gt))
+        eng.backward()
+        eng.optimizer_step(lr0=1e-2, clip=1e-3)      # clip small enough to bite
+        pd = dict(zip(names, params))
+        _, _, _, grads = O.forward_loss_grads(model, pd, gt.astype(np.float64), c3d=c3d.astype(np.float64))
+        gl = [grads[k] for k in names]
+        gl, norm = O.clip_by_global_norm(gl, 1e-3)
+        assert norm > 1e-3
+        params, m, v = O.adam_step(params, gl, m, v, step + 1, O.learning_rate(step, 1e-2))
+        got = eng.op_to_tf(eng.params.numpy())
+        for k, r in zip(names, params):
+            assert np.allclose(got[k].reshape(r.shape), r, rtol=2e-4, atol=1e-7), (step, k)

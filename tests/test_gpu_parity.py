@@ -143,3 +143,63 @@ def test_softmax_loss_kernel(loss_type):
 def test_library_is_the_cuda_one():
     lib = L.get_lib()
     assert lib.path.endswith("librgp_sm100.so") and lib.has_tcgen05()
+
+
+@pytest.mark.parametrize("dtype", [0, 1])
+@pytest.mark.parametrize("model,Ch,entry", [("gaze_grcn", 128, "c3d"), ("gaze_grcn77", 128, "emb"),
+                                            ("gaze_grcn", 256, "c3d")])
+def test_bptt_parity(dtype, model, Ch, entry):
+    """Hand-written BPTT vs torch autograd on the oracle (float64).  fp32 path: 1e-3 of each tensor's max;
+    bf16 path: 5e-2 (operands and saved activations are rounded to bf16)."""
+    B, T = 3, 5
+    p, c3d, emb, gt = _case(model, B, T, Ch, regime="S", entry=entry)
+    okw = dict(c3d=c3d.astype(np.float64)) if entry == "c3d" else dict(emb=emb.astype(np.float64))
+    _, _, ref_loss, ref = O.forward_loss_grads(model, p, gt.astype(np.float64), **okw)
+    eng = GazeEngine(model, B=B, T=T, Ch=Ch, dtype=dtype, device="cuda", train=True)
+    eng.load_tf_params(p)
+    kw = dict(c3d=torch.from_numpy(c3d).cuda()) if entry == "c3d" else dict(emb=torch.from_numpy(emb).cuda())
+    eng.forward(gt=torch.from_numpy(gt).cuda(), **kw)
+    eng.backward()
+    torch.cuda.synchronize()
+    got = eng.op_to_tf(eng.grads.cpu().numpy())
+    tol = 1e-3 if dtype == 0 else 5e-2
+    for k, r in ref.items():
+        if entry == "emb" and k.startswith("proj_c3d"):
+            continue
+        a = got[k].reshape(r.shape).astype(np.float64)
+        scale = np.abs(r).max()
+        err = np.abs(a - r).max()
+        assert err <= tol * scale + (1e-6 if k == "out_b" else 1e-12), (k, err, scale)
+
+
+@pytest.mark.parametrize("dtype", [0, 1])
+def test_training_steps_reduce_loss_and_track_oracle(dtype):
+    """3 optimiser steps (clip + TF-Adam) on the GPU vs the oracle restatement (fp32: parameters agree)."""
+    model, B, T, Ch = "gaze_grcn", 2, 4, 128
+    p, c3d, emb, gt = _case(model, B, T, Ch, regime="S")
+    eng = GazeEngine(model, B=B, T=T, Ch=Ch, dtype=dtype, device="cuda", train=True)
+    eng.load_tf_params(p)
+    names = list(p.keys())
+    params = [np.asarray(p[k], dtype=np.float64).copy() for k in names]
+    m = [np.zeros_like(x) for x in params]
+    v = [np.zeros_like(x) for x in params]
+    c3d_d, gt_d = torch.from_numpy(c3d).cuda(), torch.from_numpy(gt).cuda()
+    losses = []
+    for step in range(3):
+        eng.forward(c3d=c3d_d, gt=gt_d)
+        losses.append(float(eng.loss.cpu()[0]))
+        eng.backward()
+        eng.optimizer_step(lr0=1e-3, clip=10.0)
+        _, _, ref_loss, grads = O.forward_loss_grads(model, dict(zip(names, params)), gt.astype(np.float64),
+                                                     c3d=c3d.astype(np.float64))
+        assert abs(losses[-1] - ref_loss) <= (1e-4 if dtype == 0 else 2e-2) * abs(ref_loss)
+        gl, _ = O.clip_by_global_norm([grads[k] for k in names], 10.0)
+        params, m, v = O.adam_step(params, gl, m, v, step + 1, O.learning_rate(step, 1e-3))
+    assert losses[-1] < losses[0]
+    if dtype == 0:
+        got = eng.op_to_tf(eng.params.cpu().numpy())
+        for k, r in zip(names, params):
+            # Adam's first steps move every weight by ~lr regardless of gradient size: compare the displacement
+            d_ref = r - np.asarray(p[k], dtype=np.float64)
+            d_got = got[k].reshape(r.shape) - np.asarray(p[k], dtype=np.float32)
+            assert np.abs(d_got - d_ref).max() <= 0.05 * np.abs(d_ref).max() + 1e-7, k
