@@ -159,23 +159,32 @@ int rgp_fc_head_bwd(const float* dlogits, const float* h_f32, const float* out_W
                     float* gout_W, float* gout_b, int B, int T, int t, int G, int Ch, void* stream);
 
 /* ---- saliency metrics: evaluation_metrics.py -------------------------------------------- */
-/* resize stand-in for skimage.transform.resize(order=3) (see oracle/metrics_oracle.py) */
+/* All metric arithmetic is IEEE float64 with explicit round-to-nearest operations (no FMA contraction):
+ * thresholds and integer counts are a bit-exact contract with NumPy's float64 evaluation.
+ * Maps are [n, hw] row-major, one frame per row; fix is uint8 (non-zero = fixated). */
+/* evaluation_metrics.py:15-17,246: fp32 model output [n,hw] -> float64, optionally (x-min)/(max-min) per frame */
+int rgp_metrics_prep(const float* src, double* dst, int n, int hw, int normalize, void* stream);
+/* stand-in for skimage.transform.resize(order=3) (evaluation_metrics.py:76,137,248,255; see
+ * oracle/metrics_oracle.py resize_bicubic): [n,h,w] -> [n,oh,ow]; mode_nearest 0 = 'constant', 1 = 'nearest' */
 int rgp_resize_bicubic(const double* src, double* dst, int n, int h, int w, int oh, int ow,
                        int mode_nearest, void* stream);
-/* evaluation_metrics.py:15-17,207-236 (+NSS): per frame: out[f*4+{0,1,2}] = sim, cc, nss; maps f64 */
+/* evaluation_metrics.py:207-236 (+NSS): out [n,8] = sim, cc, nss, min(pred), max(pred), n_fix, sum(pred), sum(gt).
+ * fix may be NULL (nss = NaN). */
 int rgp_sim_cc_nss(const double* pred, const double* gt, const uint8_t* fix, double* out,
                    int n, int hw, void* stream);
-/* evaluation_metrics.py:42-98: AUC-Judd per frame.  sal [n,hw] f64 (already jittered+normalised
- * by rgp_normalize_range), fix [n,hw] u8.  counts [n,maxfix] int64 = #{S >= thr_k} (bit-exact
- * contract), auc [n] f64.  workspace: thr [n,maxfix] f64. */
-int rgp_auc_judd(const double* sal, const uint8_t* fix, double* thr, long long* counts, double* auc,
-                 int n, int hw, int maxfix, void* stream);
-/* evaluation_metrics.py:101-204: AUC-Borji / shuffled with host-drawn index tensor
- * idx [n, nfix_max, nrep] int32 (-1 = absent), nfix [n]; auc [n] f64; tp/fp counts exported. */
-int rgp_auc_sampled(const double* sal, const uint8_t* fix, const int* idx, double* auc,
-                    int n, int hw, int nfix_max, int nrep, double step, void* stream);
-/* x <- (x + jitter*1e-7 - min)/(max-min) per frame (evaluation_metrics.py:78-81,15-17) */
-int rgp_normalize_range(double* x, const double* jitter, int n, int hw, void* stream);
+/* evaluation_metrics.py:42-98: AUC-Judd per frame.  sal [n,hw] f64 (resized prediction), jitter [n,hw] f64 = the
+ * host's random.rand(H,W) draw (NULL: jitter=False).  Outputs: thr [n,maxfix] f64 = normalised fixation values
+ * sorted descending (NaN padded), counts [n,maxfix] int64 = #{S >= thr_k} (-1 padded; bit-exact contract),
+ * auc [n] f64 (NaN: no fixation; -1: more than maxfix fixations).  maxfix <= 1024. */
+int rgp_auc_judd(const double* sal, const double* jitter, const uint8_t* fix, double* thr, long long* counts,
+                 double* auc, int n, int hw, int maxfix, void* stream);
+/* evaluation_metrics.py:101-204: AUC-Borji / shuffled AUC with the host-drawn index tensor idx [n,nrows,nrep]
+ * int32 (pixel index of each negative; -1 = absent row).  sal [n,hw] f64 un-normalised, with per-frame
+ * (min,max) at minmax[f*mm_stride + {0,1}] (e.g. columns 3,4 of rgp_sim_cc_nss's output).  auc [n] f64 = mean over
+ * repetitions; tpc/fpc (optional, both or neither) int32 [n,nrep,nthr_max]: counts at threshold i*step. */
+int rgp_auc_sampled(const double* sal, const uint8_t* fix, const int* idx, const double* minmax, int mm_stride,
+                    double* auc, int* tpc, int* fpc, int n, int hw, int nrows, int nrep, double step,
+                    int nthr_max, int maxfix, void* stream);
 
 const char* rgp_last_error(void);
 int rgp_version(void);

@@ -1,0 +1,596 @@
+// metrics.cu — saliency evaluation metrics (reference: evaluation_metrics.py) as bandwidth kernels.
+//
+// All arithmetic is IEEE double with explicit round-to-nearest intrinsics (__dadd_rn / __dmul_rn ...): the
+// compiler may not contract a*b+c into an FMA here, because the AUC contracts are bit-exact — the thresholds
+// and the integer counts #{S >= thr} must come out identical to NumPy's float64 evaluation of the same
+// expressions (evaluation_metrics.py:78-97,152-163).
+//
+// Kernel shapes:
+//   * per-frame map kernels (sim/cc/nss, AUC-Judd) give one frame to a CLUSTER of 8 CTAs.  Each CTA streams
+//     1/8 of the frame from HBM (16-byte loads), the partial sums / extrema / fixation values are exchanged
+//     through distributed shared memory in rank order (deterministic), and the second pass re-reads the same
+//     slice while it is still in L2 — one DRAM pass per frame.
+//   * the sampled AUCs (Borji / shuffled) are gathers: one CTA per frame, one thread per repetition.
+#include <cooperative_groups.h>
+#include <math_constants.h>
+#include "common.cuh"
+
+namespace cg = cooperative_groups;
+
+namespace rgp {
+namespace {
+
+constexpr int kCluster = 8;
+constexpr int kThreads = 256;
+constexpr int kMaxFix = 1024;      // fixations per frame held in shared memory by the AUC kernels
+
+__device__ __forceinline__ double dA(double a, double b) { return __dadd_rn(a, b); }
+__device__ __forceinline__ double dS(double a, double b) { return __dsub_rn(a, b); }
+__device__ __forceinline__ double dM(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ double dD(double a, double b) { return __ddiv_rn(a, b); }
+// np.min / np.max propagate NaN
+__device__ __forceinline__ double nmin(double a, double b) { return (a != a || b != b) ? CUDART_NAN : (a < b ? a : b); }
+__device__ __forceinline__ double nmax(double a, double b) { return (a != a || b != b) ? CUDART_NAN : (a > b ? a : b); }
+
+struct SumOp { __device__ static double id() { return 0.0; } __device__ static double op(double a, double b) { return a + b; } };
+struct MinOp { __device__ static double id() { return CUDART_INF; } __device__ static double op(double a, double b) { return nmin(a, b); } };
+struct MaxOp { __device__ static double id() { return -CUDART_INF; } __device__ static double op(double a, double b) { return nmax(a, b); } };
+
+template <class Op>
+__device__ __forceinline__ double warp_red(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = Op::op(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+// fixed-order block reduction; result valid in every thread; `scr` holds >= 32 doubles
+template <class Op>
+__device__ __forceinline__ double block_red(double v, double* scr) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+  v = warp_red<Op>(v);
+  __syncthreads();
+  if (lane == 0) scr[w] = v;
+  __syncthreads();
+  double r = Op::id();
+  for (int i = 0; i < nw; ++i) r = Op::op(r, scr[i]);
+  return r;
+}
+
+// ---------------------------------------------------------------------------------------------
+// fp32 model output -> float64 map, optionally min-max normalised (evaluation_metrics.py:15-17,246)
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads) metrics_prep_kernel(const float* __restrict__ src, double* __restrict__ dst,
+                                                                int hw, int normalize) {
+  __shared__ double scr[32];
+  const float* s = src + (long long)blockIdx.x * hw;
+  double* d = dst + (long long)blockIdx.x * hw;
+  double mn = CUDART_INF, mx = -CUDART_INF;
+  if (normalize) {
+    for (int i = threadIdx.x; i < hw; i += blockDim.x) { double v = (double)s[i]; mn = nmin(mn, v); mx = nmax(mx, v); }
+    mn = block_red<MinOp>(mn, scr);
+    mx = block_red<MaxOp>(mx, scr);
+  }
+  const double range = dS(mx, mn);
+  for (int i = threadIdx.x; i < hw; i += blockDim.x) {
+    double v = (double)s[i];
+    d[i] = normalize ? dD(dS(v, mn), range) : v;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// bicubic resize (stand-in for skimage.transform.resize(order=3), see oracle/metrics_oracle.py:61-92).
+// Operation order is the oracle's: out = sum_i wr_i * (sum_j wc_j * src[r0+i, c0+j]), taps left to right,
+// coordinate (o + 0.5) * (in / out) - 0.5, result clipped to the source range.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void cubic_w(double t, double w[4]) {
+  const double t2 = dM(t, t), t3 = dM(t2, t);
+  w[0] = dM(0.5, dS(dA(-t3, dM(2.0, t2)), t));
+  w[1] = dM(0.5, dA(dS(dM(3.0, t3), dM(5.0, t2)), 2.0));
+  w[2] = dM(0.5, dA(dA(dM(-3.0, t3), dM(4.0, t2)), t));
+  w[3] = dM(0.5, dS(t3, t2));
+}
+
+__global__ void __launch_bounds__(kThreads) resize_bicubic_kernel(const double* __restrict__ src, double* __restrict__ dst,
+                                                                  int h, int w, int oh, int ow, int nearest, int in_smem) {
+  extern __shared__ double simg[];
+  __shared__ double scr[32];
+  const int f = blockIdx.y;
+  const double* s = src + (long long)f * h * w;
+  double mn = CUDART_INF, mx = -CUDART_INF;
+  for (int i = threadIdx.x; i < h * w; i += blockDim.x) {
+    double v = s[i];
+    if (in_smem) simg[i] = v;
+    mn = nmin(mn, v); mx = nmax(mx, v);
+  }
+  mn = block_red<MinOp>(mn, scr);
+  mx = block_red<MaxOp>(mx, scr);
+  __syncthreads();
+  const double* img = in_smem ? simg : s;
+  const double sr = dD((double)h, (double)oh), sc = dD((double)w, (double)ow);
+  const long long npx = (long long)oh * ow;
+  double* d = dst + (long long)f * npx;
+  for (long long o = (long long)blockIdx.x * blockDim.x + threadIdx.x; o < npx; o += (long long)gridDim.x * blockDim.x) {
+    const int r = (int)(o / ow), c = (int)(o - (long long)r * ow);
+    const double rs = dS(dM(dA((double)r, 0.5), sr), 0.5), cs = dS(dM(dA((double)c, 0.5), sc), 0.5);
+    const double rf = floor(rs), cf = floor(cs);
+    double wr[4], wc[4];
+    cubic_w(dS(rs, rf), wr);
+    cubic_w(dS(cs, cf), wc);
+    const int r0 = (int)rf - 1, c0 = (int)cf - 1;
+    double out = 0.0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      int ri = r0 + i;
+      const bool rok = ri >= 0 && ri < h;
+      ri = min(max(ri, 0), h - 1);
+      double row = 0.0;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        int ci = c0 + j;
+        const bool ok = rok && ci >= 0 && ci < w;
+        ci = min(max(ci, 0), w - 1);
+        double v = img[ri * w + ci];
+        if (!nearest && !ok) v = 0.0;
+        row = dA(row, dM(wc[j], v));
+      }
+      out = dA(out, dM(wr[i], row));
+    }
+    out = (out < mn) ? mn : out;   // np.minimum(np.maximum(out, lo), hi); NaN stays NaN
+    out = (out > mx) ? mx : out;
+    d[o] = out;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// cluster helpers: slice of the frame owned by this CTA, and the rank-ordered exchange of partials
+// ---------------------------------------------------------------------------------------------
+struct Slice { int begin, end; };
+__device__ __forceinline__ Slice my_slice(int hw, int rank) {
+  int per = (hw + kCluster - 1) / kCluster;
+  per = (per + 15) & ~15;                      // keeps 16-byte alignment of every slice start inside a frame
+  Slice s;
+  s.begin = min(hw, rank * per);
+  s.end = min(hw, s.begin + per);
+  return s;
+}
+
+// out[k] = op over ranks 0..7 (in rank order) of part[k] as stored in each CTA's shared memory.
+// Call between two cluster.sync(): the first publishes `part`, the caller's next one protects its reuse.
+template <class Op>
+__device__ __forceinline__ double cluster_gather(cg::cluster_group& cl, double* part, int k) {
+  double r = Op::id();
+  for (int q = 0; q < kCluster; ++q) r = Op::op(r, cl.map_shared_rank(part, q)[k]);
+  return r;
+}
+
+// ---------------------------------------------------------------------------------------------
+// sim / cc / nss (+ min, max, n_fix of the prediction) — evaluation_metrics.py:207-236, NSS per
+// oracle/metrics_oracle.py:237-246.  pred, gt float64 [n, hw]; fix uint8 [n, hw]; out [n, 8].
+// ---------------------------------------------------------------------------------------------
+__global__ void __cluster_dims__(kCluster, 1, 1) __launch_bounds__(kThreads)
+sim_cc_nss_kernel(const double* __restrict__ pred, const double* __restrict__ gt, const uint8_t* __restrict__ fix,
+                  double* __restrict__ out, int n, int hw) {
+  cg::cluster_group cl = cg::this_cluster();
+  __shared__ double scr[32];
+  __shared__ double part1[8], part2[8], tot[16];
+  const int rank = (int)cl.block_rank();
+  const int ncl = gridDim.x / kCluster;
+  const Slice sl = my_slice(hw, rank);
+  const bool vec = (hw & 1) == 0;
+  for (int f = blockIdx.x / kCluster; f < n; f += ncl) {
+    const double* p = pred + (long long)f * hw;
+    const double* g = gt + (long long)f * hw;
+    const uint8_t* fx = fix ? fix + (long long)f * hw : nullptr;
+    // ---- pass 1 (HBM): sums, extrema, fixation statistics
+    double sp = 0.0, sg = 0.0, mn = CUDART_INF, mx = -CUDART_INF, spf = 0.0, nf = 0.0;
+    if (vec) {
+      const double2* p2 = reinterpret_cast<const double2*>(p);
+      const double2* g2 = reinterpret_cast<const double2*>(g);
+      const uchar2* f2 = reinterpret_cast<const uchar2*>(fx);
+#pragma unroll 4
+      for (int i = sl.begin / 2 + threadIdx.x; i < sl.end / 2; i += kThreads) {
+        const double2 a = p2[i], b = g2[i];
+        sp += a.x + a.y; sg += b.x + b.y;
+        mn = nmin(mn, nmin(a.x, a.y)); mx = nmax(mx, nmax(a.x, a.y));
+        if (fx) {
+          const uchar2 m = f2[i];
+          if (m.x) { spf += a.x; nf += 1.0; }
+          if (m.y) { spf += a.y; nf += 1.0; }
+        }
+      }
+    } else {
+      for (int i = sl.begin + threadIdx.x; i < sl.end; i += kThreads) {
+        const double a = p[i];
+        sp += a; sg += g[i]; mn = nmin(mn, a); mx = nmax(mx, a);
+        if (fx && fx[i]) { spf += a; nf += 1.0; }
+      }
+    }
+    sp = block_red<SumOp>(sp, scr); sg = block_red<SumOp>(sg, scr);
+    mn = block_red<MinOp>(mn, scr); mx = block_red<MaxOp>(mx, scr);
+    spf = block_red<SumOp>(spf, scr); nf = block_red<SumOp>(nf, scr);
+    if (threadIdx.x == 0) { part1[0] = sp; part1[1] = sg; part1[2] = mn; part1[3] = mx; part1[4] = spf; part1[5] = nf; }
+    cl.sync();
+    if (threadIdx.x == 0) {
+      tot[0] = cluster_gather<SumOp>(cl, part1, 0); tot[1] = cluster_gather<SumOp>(cl, part1, 1);
+      tot[2] = cluster_gather<MinOp>(cl, part1, 2); tot[3] = cluster_gather<MaxOp>(cl, part1, 3);
+      tot[4] = cluster_gather<SumOp>(cl, part1, 4); tot[5] = cluster_gather<SumOp>(cl, part1, 5);
+    }
+    __syncthreads();
+    const double tsp = tot[0], tsg = tot[1];
+    const double mp = tsp / (double)hw, mg = tsg / (double)hw;
+    // ---- pass 2 (L2): centred second moments and the histogram intersection
+    double vpp = 0.0, vgg = 0.0, vpg = 0.0, ssim = 0.0;
+    if (vec) {
+      const double2* p2 = reinterpret_cast<const double2*>(p);
+      const double2* g2 = reinterpret_cast<const double2*>(g);
+#pragma unroll 4
+      for (int i = sl.begin / 2 + threadIdx.x; i < sl.end / 2; i += kThreads) {
+        const double2 a = p2[i], b = g2[i];
+        const double ax = a.x - mp, ay = a.y - mp, bx = b.x - mg, by = b.y - mg;
+        vpp += ax * ax + ay * ay; vgg += bx * bx + by * by; vpg += ax * bx + ay * by;
+        ssim += fmin(dD(b.x, tsg), dD(a.x, tsp)) + fmin(dD(b.y, tsg), dD(a.y, tsp));
+      }
+    } else {
+      for (int i = sl.begin + threadIdx.x; i < sl.end; i += kThreads) {
+        const double a = p[i], b = g[i];
+        const double ax = a - mp, bx = b - mg;
+        vpp += ax * ax; vgg += bx * bx; vpg += ax * bx;
+        ssim += fmin(dD(b, tsg), dD(a, tsp));
+      }
+    }
+    vpp = block_red<SumOp>(vpp, scr); vgg = block_red<SumOp>(vgg, scr);
+    vpg = block_red<SumOp>(vpg, scr); ssim = block_red<SumOp>(ssim, scr);
+    if (threadIdx.x == 0) { part2[0] = vpp; part2[1] = vgg; part2[2] = vpg; part2[3] = ssim; }
+    cl.sync();
+    if (rank == 0 && threadIdx.x == 0) {
+      const double tpp = cluster_gather<SumOp>(cl, part2, 0), tgg = cluster_gather<SumOp>(cl, part2, 1);
+      const double tpg = cluster_gather<SumOp>(cl, part2, 2), tsim = cluster_gather<SumOp>(cl, part2, 3);
+      double* o = out + (long long)f * 8;
+      o[0] = tsim;
+      o[1] = tpg / (sqrt(tpp) * sqrt(tgg));                      // Pearson r; 0/0 -> NaN like np.corrcoef
+      const double sd = sqrt(tpp / (double)hw);
+      o[2] = (tot[5] > 0.0) ? ((tot[4] / tot[5]) - mp) / sd : CUDART_NAN;
+      o[3] = tot[2]; o[4] = tot[3]; o[5] = tot[5]; o[6] = tsp; o[7] = tsg;
+    }
+    cl.sync();   // part1/part2/tot are reused by the next frame; nobody may still be reading them
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// AUC-Judd — evaluation_metrics.py:42-98.  sal float64 [n, hw] (the resized prediction), jitter float64
+// [n, hw] (the host's random.rand(H, W) draw, may be NULL = jitter=False), fix uint8 [n, hw].
+// Per frame: x = sal + jitter*1e-7 ; S = (x - min x)/(max x - min x) ; thresholds = S at the fixations,
+// sorted descending ; counts[k] = #{S >= thr_k} ; AUC = trapz over (fp, tp).
+// Outputs: thr [n, maxfix] float64 (sorted, NaN padded), counts [n, maxfix] int64 (-1 padded), auc [n].
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ double judd_x(double s, double j, bool has_j) { return has_j ? dA(s, dM(j, 1e-7)) : s; }
+
+__global__ void __cluster_dims__(kCluster, 1, 1) __launch_bounds__(kThreads)
+auc_judd_kernel(const double* __restrict__ sal, const double* __restrict__ jitter, const uint8_t* __restrict__ fix,
+                double* __restrict__ thr_out, long long* __restrict__ counts, double* __restrict__ auc,
+                int n, int hw, int maxfix) {
+  cg::cluster_group cl = cg::this_cluster();
+  __shared__ double scr[32];
+  __shared__ double part[4];
+  __shared__ double myfix[kMaxFix];     // raw x at this CTA's fixated pixels (unordered)
+  __shared__ double thr[kMaxFix];       // all fixation values of the frame, normalised, sorted descending
+  __shared__ int hist[kMaxFix];
+  __shared__ int mycount, total_s;
+  __shared__ double mnmx[2];
+  const int rank = (int)cl.block_rank();
+  const int ncl = gridDim.x / kCluster;
+  const Slice sl = my_slice(hw, rank);
+  const bool vec = (hw & 1) == 0;
+  const bool hj = jitter != nullptr;
+  for (int f = blockIdx.x / kCluster; f < n; f += ncl) {
+    const double* s = sal + (long long)f * hw;
+    const double* jt = hj ? jitter + (long long)f * hw : nullptr;
+    const uint8_t* fx = fix + (long long)f * hw;
+    if (threadIdx.x == 0) mycount = 0;
+    for (int i = threadIdx.x; i < kMaxFix; i += kThreads) hist[i] = 0;
+    __syncthreads();
+    // ---- pass 1 (HBM): extrema of the jittered map, values at the fixations
+    double mn = CUDART_INF, mx = -CUDART_INF;
+    if (vec) {
+      const double2* s2 = reinterpret_cast<const double2*>(s);
+      const double2* j2 = reinterpret_cast<const double2*>(jt);
+      const uchar2* f2 = reinterpret_cast<const uchar2*>(fx);
+#pragma unroll 4
+      for (int i = sl.begin / 2 + threadIdx.x; i < sl.end / 2; i += kThreads) {
+        const double2 a = s2[i];
+        double2 j = make_double2(0.0, 0.0);
+        if (hj) j = j2[i];
+        const uchar2 m = f2[i];
+        const double x0 = judd_x(a.x, j.x, hj), x1 = judd_x(a.y, j.y, hj);
+        mn = nmin(mn, nmin(x0, x1)); mx = nmax(mx, nmax(x0, x1));
+        if (m.x) { int k = atomicAdd(&mycount, 1); if (k < kMaxFix) myfix[k] = x0; }
+        if (m.y) { int k = atomicAdd(&mycount, 1); if (k < kMaxFix) myfix[k] = x1; }
+      }
+    } else {
+      for (int i = sl.begin + threadIdx.x; i < sl.end; i += kThreads) {
+        const double x0 = judd_x(s[i], hj ? jt[i] : 0.0, hj);
+        mn = nmin(mn, x0); mx = nmax(mx, x0);
+        if (fx[i]) { int k = atomicAdd(&mycount, 1); if (k < kMaxFix) myfix[k] = x0; }
+      }
+    }
+    mn = block_red<MinOp>(mn, scr); mx = block_red<MaxOp>(mx, scr);
+    if (threadIdx.x == 0) { part[0] = mn; part[1] = mx; part[2] = (double)mycount; }
+    cl.sync();
+    // ---- every CTA assembles the frame's threshold list (rank order), normalises and sorts it
+    if (threadIdx.x == 0) {
+      mnmx[0] = cluster_gather<MinOp>(cl, part, 0);
+      mnmx[1] = cluster_gather<MaxOp>(cl, part, 1);
+      total_s = (int)cluster_gather<SumOp>(cl, part, 2);
+    }
+    __syncthreads();
+    const double gmn = mnmx[0], range = dS(mnmx[1], mnmx[0]);
+    const int total = total_s;
+    const bool ok = total > 0 && total <= maxfix && total <= kMaxFix;
+    int np2 = 1;
+    while (np2 < total) np2 <<= 1;
+    if (ok) {
+      int base = 0;
+      for (int q = 0; q < kCluster; ++q) {
+        const int cq = (int)cl.map_shared_rank(part, q)[2];
+        const double* lq = cl.map_shared_rank(myfix, q);
+        for (int i = threadIdx.x; i < cq; i += kThreads) thr[base + i] = dD(dS(lq[i], gmn), range);
+        base += cq;
+      }
+      for (int i = total + threadIdx.x; i < np2; i += kThreads) thr[i] = -CUDART_INF;
+      __syncthreads();
+      for (int k = 2; k <= np2; k <<= 1)            // bitonic sort, descending (NaN never reaches here unless range = 0)
+        for (int j = k >> 1; j > 0; j >>= 1) {
+          for (int i = threadIdx.x; i < np2; i += kThreads) {
+            const int l = i ^ j;
+            if (l > i) {
+              const double a = thr[i], b = thr[l];
+              const bool desc = (i & k) == 0;
+              if (desc ? (a < b) : (a > b)) { thr[i] = b; thr[l] = a; }
+            }
+          }
+          __syncthreads();
+        }
+      // ---- pass 2 (L2): rank every pixel against the thresholds
+      const double lowest = thr[total - 1];
+      auto rank_px = [&](double x) {
+        const double v = dD(dS(x, gmn), range);
+        if (v >= lowest) {
+          int lo = 0, hi = total - 1;                // first k with thr[k] <= v
+          while (lo < hi) { const int mid = (lo + hi) >> 1; if (thr[mid] <= v) hi = mid; else lo = mid + 1; }
+          atomicAdd(&hist[lo], 1);
+        }
+      };
+      if (vec) {
+        const double2* s2 = reinterpret_cast<const double2*>(s);
+        const double2* j2 = reinterpret_cast<const double2*>(jt);
+#pragma unroll 4
+        for (int i = sl.begin / 2 + threadIdx.x; i < sl.end / 2; i += kThreads) {
+          const double2 a = s2[i];
+          double2 j = make_double2(0.0, 0.0);
+          if (hj) j = j2[i];
+          rank_px(judd_x(a.x, j.x, hj));
+          rank_px(judd_x(a.y, j.y, hj));
+        }
+      } else {
+        for (int i = sl.begin + threadIdx.x; i < sl.end; i += kThreads) rank_px(judd_x(s[i], hj ? jt[i] : 0.0, hj));
+      }
+    }
+    cl.sync();
+    if (rank == 0) {
+      if (ok) {
+        for (int k = threadIdx.x; k < total; k += kThreads) {
+          int c = 0;
+          for (int q = 0; q < kCluster; ++q) c += cl.map_shared_rank(hist, q)[k];
+          hist[k] = c;                                // rank 0's own bins were read before being overwritten (same k, same thread)
+        }
+      }
+      __syncthreads();
+      for (int k = threadIdx.x; k < maxfix; k += kThreads) {
+        thr_out[(long long)f * maxfix + k] = (ok && k < total) ? thr[k] : CUDART_NAN;
+        if (!ok || k >= total) counts[(long long)f * maxfix + k] = -1;
+      }
+      if (threadIdx.x == 0) {
+        double a = CUDART_NAN;                        // no fixation -> NaN (evaluation_metrics.py:71-73)
+        if (ok) {
+          long long above = 0;
+          double tp0 = 0.0, fp0 = 0.0, acc = 0.0;
+          const double nfix = (double)total, nneg = (double)(hw - total);
+          for (int k = 0; k < total; ++k) {
+            above += hist[k];
+            counts[(long long)f * maxfix + k] = above;
+            const double tp1 = (double)(k + 1) / nfix, fp1 = (double)(above - k - 1) / nneg;
+            acc += (fp1 - fp0) * (tp1 + tp0) / 2.0;
+            tp0 = tp1; fp0 = fp1;
+          }
+          acc += (1.0 - fp0) * (1.0 + tp0) / 2.0;
+          a = acc;
+        } else if (total > 0) {
+          a = -1.0;                                   // more fixations than maxfix: flagged, the host wrapper raises
+        }
+        auc[f] = a;
+      }
+    }
+    cl.sync();
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// AUC-Borji / shuffled AUC — evaluation_metrics.py:101-204.  One CTA per frame, one thread per repetition.
+// sal float64 [n, hw] (un-normalised resized prediction) with per-frame (min, max) in minmax[f*mm_stride + {0,1}];
+// S = (sal - min)/(max - min) is formed only at the gathered pixels.  idx int32 [n, nrows, nrep]: pixel indices of
+// the negatives (host-drawn: randint for Borji, permuted union picks for shuffled), -1 = absent row.
+// Per repetition: thresholds i*step, i < ceil(max(S_fix U S_rand)/step) (np.arange(0, mx, step)); tp/fp counts;
+// AUC = trapz; output = mean over repetitions.  tpc/fpc (optional) int32 [n, nrep, nthr_max]: the integer counts at
+// threshold i*step (-1 beyond the repetition's list) — the bit-exact contract.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads)
+auc_sampled_kernel(const double* __restrict__ sal, const uint8_t* __restrict__ fix, const int* __restrict__ idx,
+                   const double* __restrict__ minmax, int mm_stride, double* __restrict__ auc,
+                   int* __restrict__ tpc, int* __restrict__ fpc, int n, int hw, int nrows, int nrep, double step,
+                   int nthr_max, int maxfix) {
+  __shared__ double sfix[kMaxFix];
+  __shared__ int pos[kMaxFix];
+  __shared__ int cnt;
+  extern __shared__ double rep_auc[];   // [nrep]
+  for (int f = blockIdx.x; f < n; f += gridDim.x) {
+    const double* s = sal + (long long)f * hw;
+    const uint8_t* fx = fix + (long long)f * hw;
+    const double mn = minmax[(long long)f * mm_stride], range = dS(minmax[(long long)f * mm_stride + 1], mn);
+    __syncthreads();
+    if (threadIdx.x == 0) cnt = 0;
+    __syncthreads();
+    // fixation positions (16 pixels per load when the frame is 16-byte aligned)
+    if ((hw & 15) == 0) {
+      const uint4* f4 = reinterpret_cast<const uint4*>(fx);
+      for (int i = threadIdx.x; i < hw / 16; i += kThreads) {
+        const uint4 v = f4[i];
+        if (v.x | v.y | v.z | v.w) {
+          const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+          for (int q = 0; q < 4; ++q)
+#pragma unroll
+            for (int b = 0; b < 4; ++b)
+              if ((w[q] >> (8 * b)) & 0xffu) { int k = atomicAdd(&cnt, 1); if (k < kMaxFix) pos[k] = i * 16 + q * 4 + b; }
+        }
+      }
+    } else {
+      for (int i = threadIdx.x; i < hw; i += kThreads)
+        if (fx[i]) { int k = atomicAdd(&cnt, 1); if (k < kMaxFix) pos[k] = i; }
+    }
+    __syncthreads();
+    const int nfix = cnt;
+    const bool ok = nfix > 0 && nfix <= maxfix && nfix <= kMaxFix;
+    if (ok)
+      for (int i = threadIdx.x; i < nfix; i += kThreads) sfix[i] = dD(dS(s[pos[i]], mn), range);
+    __syncthreads();
+    for (int rep = threadIdx.x; rep < nrep; rep += kThreads) {
+      double a = CUDART_NAN;
+      if (ok) {
+        const int* ix = idx + (long long)f * nrows * nrep + rep;
+        double mx = -CUDART_INF;
+        for (int i = 0; i < nfix; ++i) mx = nmax(mx, sfix[i]);
+        for (int i = 0; i < nrows; ++i) {
+          const int p = ix[(long long)i * nrep];
+          if (p >= 0) mx = nmax(mx, dD(dS(s[p], mn), range));
+        }
+        int L = (mx > 0.0) ? (int)ceil(dD(mx, step)) : 0;       // len(np.arange(0, mx, step))
+        if (L > nthr_max) L = nthr_max;
+        double tp0 = 0.0, fp0 = 0.0, acc = 0.0;
+        const double dn = (double)nfix;
+        for (int t = L - 1; t >= 0; --t) {                      // thresholds descending = the reference's [::-1]
+          const double th = dM((double)t, step);
+          int ct = 0, cf = 0;
+          for (int i = 0; i < nfix; ++i) ct += (sfix[i] >= th) ? 1 : 0;
+          for (int i = 0; i < nrows; ++i) {
+            const int p = ix[(long long)i * nrep];
+            if (p >= 0) cf += (dD(dS(s[p], mn), range) >= th) ? 1 : 0;
+          }
+          if (tpc) { tpc[((long long)f * nrep + rep) * nthr_max + t] = ct; fpc[((long long)f * nrep + rep) * nthr_max + t] = cf; }
+          const double tp1 = (double)ct / dn, fp1 = (double)cf / dn;
+          acc += (fp1 - fp0) * (tp1 + tp0) / 2.0;
+          tp0 = tp1; fp0 = fp1;
+        }
+        acc += (1.0 - fp0) * (1.0 + tp0) / 2.0;
+        a = acc;
+        if (tpc)
+          for (int t = L; t < nthr_max; ++t) { tpc[((long long)f * nrep + rep) * nthr_max + t] = -1; fpc[((long long)f * nrep + rep) * nthr_max + t] = -1; }
+      } else if (tpc) {
+        for (int t = 0; t < nthr_max; ++t) { tpc[((long long)f * nrep + rep) * nthr_max + t] = -1; fpc[((long long)f * nrep + rep) * nthr_max + t] = -1; }
+      }
+      rep_auc[rep] = a;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double sum = 0.0;
+      for (int r = 0; r < nrep; ++r) sum += rep_auc[r];
+      auc[f] = (nfix > 0 && !ok) ? -1.0 : sum / (double)nrep;   // -1: more fixations than maxfix (host raises)
+    }
+  }
+}
+
+}  // namespace
+}  // namespace rgp
+
+// ---------------------------------------------------------------------------------------------
+// C-ABI
+// ---------------------------------------------------------------------------------------------
+namespace {
+int sm_count() {
+  static int nsm = 0;
+  if (!nsm) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev);
+    if (nsm <= 0) nsm = 148;
+  }
+  return nsm;
+}
+}  // namespace
+
+extern "C" {
+
+int rgp_metrics_prep(const float* src, double* dst, int n, int hw, int normalize, void* stream) {
+  RGP_CHECK_ARG(n >= 0 && hw > 0, "rgp_metrics_prep: n=%d hw=%d", n, hw);
+  if (n == 0) return 0;
+  rgp::metrics_prep_kernel<<<n, rgp::kThreads, 0, (cudaStream_t)stream>>>(src, dst, hw, normalize);
+  return rgp::check_launch("rgp_metrics_prep");
+}
+
+int rgp_resize_bicubic(const double* src, double* dst, int n, int h, int w, int oh, int ow, int mode_nearest,
+                       void* stream) {
+  RGP_CHECK_ARG(n >= 0 && h > 0 && w > 0 && oh > 0 && ow > 0, "rgp_resize_bicubic: bad shape");
+  if (n == 0) return 0;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (h == oh && w == ow) {   // evaluation path when the maps already are at fixation resolution: a copy
+    cudaError_t e = cudaMemcpyAsync(dst, src, (size_t)n * h * w * sizeof(double), cudaMemcpyDeviceToDevice, s);
+    if (e != cudaSuccess) { rgp::set_error("rgp_resize_bicubic: %s", cudaGetErrorString(e)); return -5; }
+    return 0;
+  }
+  const size_t bytes = (size_t)h * w * sizeof(double);
+  const int in_smem = bytes <= 160 * 1024;
+  static bool attr = false;
+  if (!attr) {
+    cudaFuncSetAttribute(rgp::resize_bicubic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+    attr = true;
+  }
+  const long long npx = (long long)oh * ow;
+  int bx = (int)((npx + rgp::kThreads * 8 - 1) / (rgp::kThreads * 8));   // ~8 output pixels per thread amortise the source load
+  if (bx < 1) bx = 1;
+  dim3 grid(bx, n);
+  rgp::resize_bicubic_kernel<<<grid, rgp::kThreads, in_smem ? bytes : 0, s>>>(src, dst, h, w, oh, ow, mode_nearest, in_smem);
+  return rgp::check_launch("rgp_resize_bicubic");
+}
+
+int rgp_sim_cc_nss(const double* pred, const double* gt, const uint8_t* fix, double* out, int n, int hw, void* stream) {
+  RGP_CHECK_ARG(n >= 0 && hw > 0, "rgp_sim_cc_nss: n=%d hw=%d", n, hw);
+  if (n == 0) return 0;
+  const int ncl = n < sm_count() ? n : sm_count();
+  rgp::sim_cc_nss_kernel<<<ncl * rgp::kCluster, rgp::kThreads, 0, (cudaStream_t)stream>>>(pred, gt, fix, out, n, hw);
+  return rgp::check_launch("rgp_sim_cc_nss");
+}
+
+int rgp_auc_judd(const double* sal, const double* jitter, const uint8_t* fix, double* thr, long long* counts,
+                 double* auc, int n, int hw, int maxfix, void* stream) {
+  RGP_CHECK_ARG(n >= 0 && hw > 0, "rgp_auc_judd: n=%d hw=%d", n, hw);
+  RGP_CHECK_ARG(maxfix >= 1 && maxfix <= rgp::kMaxFix, "rgp_auc_judd: maxfix=%d must be in 1..%d", maxfix, rgp::kMaxFix);
+  if (n == 0) return 0;
+  const int ncl = n < sm_count() ? n : sm_count();
+  rgp::auc_judd_kernel<<<ncl * rgp::kCluster, rgp::kThreads, 0, (cudaStream_t)stream>>>(sal, jitter, fix, thr, counts,
+                                                                                      auc, n, hw, maxfix);
+  return rgp::check_launch("rgp_auc_judd");
+}
+
+int rgp_auc_sampled(const double* sal, const uint8_t* fix, const int* idx, const double* minmax, int mm_stride,
+                    double* auc, int* tpc, int* fpc, int n, int hw, int nrows, int nrep, double step, int nthr_max,
+                    int maxfix, void* stream) {
+  RGP_CHECK_ARG(n >= 0 && hw > 0 && nrows >= 0 && nrep >= 1, "rgp_auc_sampled: n=%d hw=%d nrows=%d nrep=%d", n, hw, nrows, nrep);
+  RGP_CHECK_ARG(step > 0.0 && nthr_max >= 1, "rgp_auc_sampled: step=%g nthr_max=%d", step, nthr_max);
+  RGP_CHECK_ARG(maxfix >= 1 && maxfix <= rgp::kMaxFix, "rgp_auc_sampled: maxfix=%d must be in 1..%d", maxfix, rgp::kMaxFix);
+  RGP_CHECK_ARG((tpc == nullptr) == (fpc == nullptr), "rgp_auc_sampled: tpc and fpc must both be given or both NULL");
+  if (n == 0) return 0;
+  const int grid = n < 8 * sm_count() ? n : 8 * sm_count();
+  rgp::auc_sampled_kernel<<<grid, rgp::kThreads, (size_t)nrep * sizeof(double), (cudaStream_t)stream>>>(
+      sal, fix, idx, minmax, mm_stride, auc, tpc, fpc, n, hw, nrows, nrep, step, nthr_max, maxfix);
+  return rgp::check_launch("rgp_auc_sampled");
+}
+
+}  // extern "C"

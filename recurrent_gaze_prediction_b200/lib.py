@@ -71,6 +71,12 @@ _SIGS = {
     "rgp_bn_bwd": [_vp, _vp, _vp, _vp, _f, _i, _i, _i, _vp],
     "rgp_colsum": [_vp, _i, _i, _i, _vp, _i, _vp],
     "rgp_fc_head_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp],
+    # saliency metrics (evaluation_metrics.py)
+    "rgp_metrics_prep": [_vp, _vp, _i, _i, _i, _vp],
+    "rgp_resize_bicubic": [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp],
+    "rgp_sim_cc_nss": [_vp, _vp, _vp, _vp, _i, _i, _vp],
+    "rgp_auc_judd": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp],
+    "rgp_auc_sampled": [_vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _i, _i, _i, _d, _i, _i, _vp],
 }
 
 

@@ -415,3 +415,136 @@ class EmuLib(object):
                     arr(gw, (Ch,))[:] += d * hh[m + Wp + 1]
                     arr(gb, (1,))[0] += d
         return 0
+
+    # -------------------------------------------------------------- saliency metrics (csrc/metrics.cu)
+    # NumPy float64 restatements of the KERNELS' algorithms (rank-by-search for Judd, per-repetition
+    # count loops for the sampled AUCs), so the host wrapper in evaluation_metrics.py is checked on CPU.
+    def rgp_metrics_prep(self, src, dst, n, hw, normalize, stream):
+        s = arr(src, (n, hw)).astype(np.float64)
+        d = arr(dst, (n, hw), np.float64)
+        if normalize:
+            with np.errstate(invalid="ignore", divide="ignore"):
+                mn, mx = s.min(1, keepdims=True), s.max(1, keepdims=True)
+                d[:] = (s - mn) / (mx - mn)
+        else:
+            d[:] = s
+        return 0
+
+    def rgp_resize_bicubic(self, src, dst, n, h, w, oh, ow, mode_nearest, stream):
+        s = arr(src, (n, h, w), np.float64)
+        d = arr(dst, (n, oh, ow), np.float64)
+        if (h, w) == (oh, ow):
+            d[:] = s
+            return 0
+
+        def weights(t):
+            t2 = t * t
+            t3 = t2 * t
+            return (0.5 * (-t3 + 2.0 * t2 - t), 0.5 * (3.0 * t3 - 5.0 * t2 + 2.0),
+                    0.5 * (-3.0 * t3 + 4.0 * t2 + t), 0.5 * (t3 - t2))
+        rs = (np.arange(oh, dtype=np.float64) + 0.5) * (float(h) / oh) - 0.5
+        cs = (np.arange(ow, dtype=np.float64) + 0.5) * (float(w) / ow) - 0.5
+        rf, cf = np.floor(rs), np.floor(cs)
+        wr, wc = weights(rs - rf), weights(cs - cf)
+        r0, c0 = rf.astype(np.int64) - 1, cf.astype(np.int64) - 1
+        for f in range(n):
+            img = s[f]
+            out = np.zeros((oh, ow))
+            for i in range(4):
+                ri = r0 + i
+                row = np.zeros((oh, ow))
+                for j in range(4):
+                    ci = c0 + j
+                    v = img[np.clip(ri, 0, h - 1)[:, None], np.clip(ci, 0, w - 1)[None, :]]
+                    if not mode_nearest:
+                        ok = ((ri >= 0) & (ri < h))[:, None] & ((ci >= 0) & (ci < w))[None, :]
+                        v = np.where(ok, v, 0.0)
+                    row = row + wc[j][None, :] * v
+                out = out + wr[i][:, None] * row
+            d[f] = np.minimum(np.maximum(out, img.min()), img.max())
+        return 0
+
+    def rgp_sim_cc_nss(self, pred, gt, fix, out, n, hw, stream):
+        p = arr(pred, (n, hw), np.float64)
+        g = arr(gt, (n, hw), np.float64)
+        o = arr(out, (n, 8), np.float64)
+        fx = arr(fix, (n, hw), np.uint8) if fix else None
+        with np.errstate(invalid="ignore", divide="ignore"):
+            for f in range(n):
+                sp, sg = p[f].sum(), g[f].sum()
+                a, b = p[f] - sp / hw, g[f] - sg / hw
+                o[f, 0] = np.minimum(g[f] / sg, p[f] / sp).sum()
+                o[f, 1] = (a * b).sum() / (np.sqrt((a * a).sum()) * np.sqrt((b * b).sum()))
+                nf = int((fx[f] > 0).sum()) if fx is not None else 0
+                o[f, 2] = ((p[f][fx[f] > 0].sum() / nf) - sp / hw) / np.sqrt((a * a).sum() / hw) if nf else np.nan
+                o[f, 3], o[f, 4], o[f, 5], o[f, 6], o[f, 7] = p[f].min(), p[f].max(), nf, sp, sg
+        return 0
+
+    def rgp_auc_judd(self, sal, jitter, fix, thr, counts, auc, n, hw, maxfix, stream):
+        s = arr(sal, (n, hw), np.float64)
+        jt = arr(jitter, (n, hw), np.float64) if jitter else None
+        fx = arr(fix, (n, hw), np.uint8)
+        th = arr(thr, (n, maxfix), np.float64)
+        cn = arr(counts, (n, maxfix), np.int64)
+        au = arr(auc, (n,), np.float64)
+        th[:] = np.nan
+        cn[:] = -1
+        for f in range(n):
+            F = fx[f] > 0
+            total = int(F.sum())
+            if total == 0:
+                au[f] = np.nan
+                continue
+            if total > maxfix:
+                au[f] = -1.0
+                continue
+            x = s[f] + jt[f] * 1e-7 if jt is not None else s[f]
+            S = (x - x.min()) / (x.max() - x.min())
+            t = np.sort(S[F])[::-1]
+            asc = np.sort(S)
+            above = hw - np.searchsorted(asc, t, side="left")      # #{S >= thr_k}
+            th[f, :total], cn[f, :total] = t, above
+            tp = np.r_[0.0, np.arange(1, total + 1) / float(total), 1.0]
+            fp = np.r_[0.0, (above - np.arange(1, total + 1)) / float(hw - total), 1.0]
+            au[f] = float((np.diff(fp) * (tp[1:] + tp[:-1]) / 2.0).sum())
+        return 0
+
+    def rgp_auc_sampled(self, sal, fix, idx, minmax, mm_stride, auc, tpc, fpc, n, hw, nrows, nrep, step, nthr_max,
+                        maxfix, stream):
+        s = arr(sal, (n, hw), np.float64)
+        fx = arr(fix, (n, hw), np.uint8)
+        ix = arr(idx, (n, nrows, nrep), np.int32)
+        au = arr(auc, (n,), np.float64)
+        tp_o = arr(tpc, (n, nrep, nthr_max), np.int32) if tpc else None
+        fp_o = arr(fpc, (n, nrep, nthr_max), np.int32) if fpc else None
+        if tp_o is not None:
+            tp_o[:] = -1
+            fp_o[:] = -1
+        for f in range(n):
+            mm = arr(int(minmax) + 8 * f * mm_stride, (2,), np.float64)
+            F = fx[f] > 0
+            nfix = int(F.sum())
+            if nfix == 0:
+                au[f] = np.nan
+                continue
+            if nfix > maxfix:
+                au[f] = -1.0
+                continue
+            S = (s[f] - mm[0]) / (mm[1] - mm[0])
+            sfix = S[F]
+            acc = 0.0
+            for rep in range(nrep):
+                p = ix[f, :, rep]
+                srand = S[p[p >= 0]]
+                mx = max(sfix.max(), srand.max()) if srand.size else sfix.max()
+                thr = np.arange(0, mx, step)[::-1]
+                ct = np.array([(sfix >= t).sum() for t in thr], dtype=np.int64)
+                cf = np.array([(srand >= t).sum() for t in thr], dtype=np.int64)
+                if tp_o is not None:
+                    tp_o[f, rep, :len(thr)] = ct[::-1]
+                    fp_o[f, rep, :len(thr)] = cf[::-1]
+                tp = np.r_[0.0, ct / float(nfix), 1.0]
+                fp = np.r_[0.0, cf / float(nfix), 1.0]
+                acc += float((np.diff(fp) * (tp[1:] + tp[:-1]) / 2.0).sum())
+            au[f] = acc / nrep
+        return 0

@@ -1,0 +1,144 @@
+"""GPU parity of the saliency-metric kernels (csrc/metrics.cu, through the C-ABI) against the reference goldens and
+the float64 oracle.  Integer contracts (AUC-Judd rank counts, Borji / shuffled tp/fp counts) and the thresholds are
+BIT-EXACT; sim / cc / NSS are reductions whose summation order differs from NumPy's pairwise sum: 1e-10 absolute
+(the north star asks for +-0.005)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import metrics_oracle as MO
+from recurrent_gaze_prediction_b200 import evaluation_metrics as EM
+from recurrent_gaze_prediction_b200 import synthetic as SY
+from test_metrics_emu import G, check_against_golden, golden_case
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def eng():
+    return EM.MetricsEngine(device="cuda")
+
+
+@pytest.mark.parametrize("tag", ["s49", "vas"])
+def test_kernels_match_reference_goldens(eng, tag):
+    check_against_golden(eng, tag, tol=1e-12)
+
+
+@pytest.mark.parametrize("tag", ["s49", "vas"])
+def test_integer_contracts_bit_exact(eng, tag):
+    pred, gt, fix, union, jit, ridx, sidx = golden_case(tag)
+    r = eng.evaluate_batch(pred, gt, fix, union=union, jitter_values=jit, rand_index=ridx, shuf_index=sidx,
+                           return_counts=True)
+    N = len(pred)
+    for i in range(N):
+        F = (fix[i] > 0.5).ravel()
+        n_fix = int(F.sum())
+        if n_fix == 0:
+            assert (r["AUC_Judd_counts"][i] == -1).all()
+            continue
+        p = MO.normalize_range(pred[i].astype(np.float64))
+        S = MO.normalize_range(p + jit[i] * 1e-7).ravel()
+        thr, above = MO.auc_judd_counts(S, F)
+        assert np.array_equal(r["AUC_Judd_thresholds"][i][:n_fix], thr)          # float64 bit pattern
+        assert np.array_equal(r["AUC_Judd_counts"][i][:n_fix], above)
+        assert (r["AUC_Judd_counts"][i][n_fix:] == -1).all()
+        S = MO.normalize_range(p).ravel()
+        for name, index in (("AUC_Borji", ridx[i]), ("AUC_shuffled", sidx[i])):
+            for rep, (thresholds, tpc, fpc) in enumerate(MO.borji_counts(S[F], S[index], 0.1)):
+                L = len(thresholds)
+                assert np.array_equal(r[name + "_tp"][i, rep, :L], tpc[::-1]), (name, i, rep)
+                assert np.array_equal(r[name + "_fp"][i, rep, :L], fpc[::-1]), (name, i, rep)
+                assert (r[name + "_tp"][i, rep, L:] == -1).all()
+
+
+def test_resize_bicubic_bit_exact_vs_oracle(eng):
+    rng = np.random.RandomState(0)
+    x = rng.uniform(size=(5, 49, 49))
+    for shape, mode in (((360, 480), "constant"), ((360, 480), "nearest"), ((60, 80), "constant"), ((20, 31), "nearest")):
+        y = eng.resize(torch.from_numpy(x).cuda(), shape, mode).cpu().numpy()
+        for i in range(len(x)):
+            assert np.array_equal(y[i], MO.resize_bicubic(x[i], shape, mode)), (shape, mode, i)
+    big = rng.uniform(size=(2, 200, 300))          # source too large for the shared-memory path
+    y = eng.resize(torch.from_numpy(big).cuda(), (360, 480), "constant").cpu().numpy()
+    assert np.array_equal(y[1], MO.resize_bicubic(big[1], (360, 480), "constant"))
+
+
+def test_vas_scale_full_suite_vs_oracle(eng):
+    """BASELINE config 5: 49x49 model maps scored against 360x480 fixation maps, all six metrics."""
+    rng = np.random.RandomState(7)
+    B, T, H, W = 2, 8, 360, 480
+    gt, _ = SY.make_gazemaps(rng, B, T, 49, 49)
+    pred = (gt + 0.3 * rng.uniform(size=gt.shape)).astype(np.float32)
+    fix = SY.make_fixationmaps(rng, gt, H, W)
+    N = B * T
+    pred, gt, fix = pred.reshape(N, 49, 49), gt.reshape(N, 49, 49), fix.reshape(N, H, W)
+    fix[3] = 0                                                                 # a frame without fixations
+    union = (fix[rng.choice(N, 10, replace=False)] > 0).sum(0).astype(np.float64)
+    nfix = fix.reshape(N, -1).sum(1)
+    jit = rng.rand(N, H, W)
+    ridx = [rng.randint(0, H * W, [int(n), 100]) for n in nfix]
+    np.random.seed(11)
+    sidx = [EM.shuffled_sample_index(union.ravel() > 0.5, 100, int(n)) if n else np.zeros((0, 100), np.int64) for n in nfix]
+    r = eng.evaluate_batch(pred, gt, fix, union=union, jitter_values=jit, rand_index=ridx, shuf_index=sidx)
+    for i in range(N):
+        kws = {"AUC_Judd": dict(jitter_values=jit[i]), "AUC_Borji": dict(rand_index=ridx[i]),
+               "AUC_shuffled": dict(rand_index=sidx[i])}
+        for m in EM.ALL_METRICS:
+            want = MO.saliency_score_single(m, pred[i].astype(np.float64), gt[i], fix[i], union, **kws.get(m, {}))
+            got = r[m][i]
+            if np.isnan(want):
+                assert np.isnan(got), (m, i)
+            else:
+                assert abs(got - want) <= (1e-12 if m.startswith("AUC") else 1e-10), (m, i, got, want)
+    assert np.isnan(r["AUC_Judd"][3]) and np.isnan(r["NSS"][3]) and not np.isnan(r["sim"][3])
+
+
+def test_edge_cases(eng):
+    rng = np.random.RandomState(2)
+    H, W = 30, 41                                     # odd pixel count: scalar (non-vectorised) load path
+    pred = rng.uniform(size=(3, H, W)).astype(np.float32)
+    gt = rng.uniform(size=(3, H, W)).astype(np.float32)
+    fix = np.zeros((3, H, W), np.uint8)
+    fix[0, 2, 3] = fix[0, 9, 9] = 1
+    fix[2].reshape(-1)[::7] = 1                       # many fixations
+    pred[1] = 0.5                                     # constant map: normalize_range -> NaN everywhere
+    jit = rng.rand(3, H, W)
+    r = eng.evaluate_batch(pred, gt, fix, metrics=("sim", "cc", "NSS", "AUC_Judd"), jitter_values=jit)
+    for i in (0, 2):
+        for m, kw in (("sim", {}), ("cc", {}), ("NSS", {}), ("AUC_Judd", dict(jitter_values=jit[i]))):
+            want = MO.saliency_score_single(m, pred[i].astype(np.float64), gt[i], fix[i], **kw)
+            assert abs(r[m][i] - want) <= 1e-10, (m, i)
+    assert np.isnan(r["sim"][1]) and np.isnan(r["cc"][1]) and np.isnan(r["AUC_Judd"][1])
+    # empty batch is a no-op; more fixations than the kernels hold is an error, not a wrong number
+    assert eng.to_f64(torch.zeros(0, 4, 4, device="cuda"), True).shape[0] == 0
+    with pytest.raises(ValueError):
+        eng.evaluate_batch(np.zeros((1, 49, 49), np.float32), np.zeros((1, 49, 49), np.float32),
+                           np.ones((1, 49, 49), np.uint8), metrics=("AUC_Judd",))
+
+
+def test_size_independent_properties_at_scale(eng):
+    """N = 512 frames at 360x480 (too slow for the oracle): invariances the metrics must satisfy."""
+    rng = np.random.RandomState(5)
+    N, H, W = 512, 360, 480
+    base, _ = SY.make_gazemaps(rng, 8, 8, 49, 49)
+    base = base.reshape(64, 49, 49)
+    pred = np.tile(base, (N // 64, 1, 1)) + (0.05 * rng.uniform(size=(N, 49, 49))).astype(np.float32)
+    gt = np.tile(base, (N // 64, 1, 1))
+    fix = np.tile(SY.make_fixationmaps(rng, base[:, None], H, W).reshape(64, H, W), (N // 64, 1, 1))
+    r1 = eng.evaluate_batch(pred, gt, fix, metrics=("sim", "cc", "NSS", "AUC_Judd"), jitter=False)
+    # affine invariance: the prediction is min-max normalised first, so a*pred+b (a>0) scores the same
+    # (a power-of-two scale is exact in fp32 -> identical bits; a general affine map only moves fp32 roundings)
+    r2 = eng.evaluate_batch(4.0 * pred, gt, fix, metrics=("sim", "cc", "NSS", "AUC_Judd"), jitter=False)
+    r2b = eng.evaluate_batch(3.0 * pred + 1.0, gt, fix, metrics=("sim", "cc", "NSS", "AUC_Judd"), jitter=False)
+    for m in r1:
+        assert np.array_equal(r1[m], r2[m]), m
+        assert np.allclose(r1[m], r2b[m], rtol=0, atol=1e-3), m
+    assert ((r1["AUC_Judd"] >= 0) & (r1["AUC_Judd"] <= 1)).all() and (r1["AUC_Judd"].mean() > 0.8)
+    assert ((r1["sim"] > 0) & (r1["sim"] <= 1)).all() and (np.abs(r1["cc"]) <= 1 + 1e-12).all()
+    # scoring the ground truth against itself: sim = cc = 1
+    r3 = eng.evaluate_batch(gt[:64], gt[:64], fix[:64], metrics=("sim", "cc"))
+    assert np.allclose(r3["sim"], 1.0, atol=1e-12) and np.allclose(r3["cc"], 1.0, atol=1e-12)
+    # determinism: same inputs, same bits
+    r4 = eng.evaluate_batch(pred, gt, fix, metrics=("sim", "cc", "NSS", "AUC_Judd"), jitter=False)
+    for m in r1:
+        assert np.array_equal(r1[m], r4[m]), m
