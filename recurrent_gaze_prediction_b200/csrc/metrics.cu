@@ -227,14 +227,14 @@ sim_cc_nss_kernel(const double* __restrict__ pred, const double* __restrict__ gt
         const double2 a = p2[i], b = g2[i];
         const double ax = a.x - mp, ay = a.y - mp, bx = b.x - mg, by = b.y - mg;
         vpp += ax * ax + ay * ay; vgg += bx * bx + by * by; vpg += ax * bx + ay * by;
-        ssim += fmin(dD(b.x, tsg), dD(a.x, tsp)) + fmin(dD(b.y, tsg), dD(a.y, tsp));
+        ssim += nmin(dD(b.x, tsg), dD(a.x, tsp)) + nmin(dD(b.y, tsg), dD(a.y, tsp));   // np.minimum propagates NaN
       }
     } else {
       for (int i = sl.begin + threadIdx.x; i < sl.end; i += kThreads) {
         const double a = p[i], b = g[i];
         const double ax = a - mp, bx = b - mg;
         vpp += ax * ax; vgg += bx * bx; vpg += ax * bx;
-        ssim += fmin(dD(b, tsg), dD(a, tsp));
+        ssim += nmin(dD(b, tsg), dD(a, tsp));
       }
     }
     vpp = block_red<SumOp>(vpp, scr); vgg = block_red<SumOp>(vgg, scr);

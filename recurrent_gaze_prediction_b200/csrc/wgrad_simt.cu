@@ -84,6 +84,5 @@ int wgrad_simt(const rgp_wgrad_args& a, cudaStream_t s) {
   return check_launch("wgrad_simt");
 }
 
-int wgrad_tc(const rgp_wgrad_args& a, cudaStream_t s) { return wgrad_simt(a, s); }
 
 }  // namespace rgp

@@ -205,3 +205,38 @@ def test_training_steps_reduce_loss_and_track_oracle(dtype):
             d_ref = r - np.asarray(p[k], dtype=np.float64)
             d_got = got[k].reshape(r.shape) - np.asarray(p[k], dtype=np.float32)
             assert np.abs(d_got - d_ref).max() <= 0.05 * np.abs(d_ref).max() + 1e-7, k
+
+
+@pytest.mark.parametrize("engine", [0, 1])
+@pytest.mark.parametrize("M,Ny,Nx,ldy,ycol0,taps", [
+    (960, 256, 128, 384, 0, [0, 1, 2, 8, 9, 10, 16, 17, 18]),      # U_zr wgrad shape at Ch=128
+    (1000, 128, 128, 384, 256, [0, 1, 2, 8, 9, 10, 16, 17, 18]),   # U_c: column window of dG, M % 64 != 0
+    (20000, 768, 512, 768, 0, [0, 9, 18]),                          # W_x shape: several row slabs per tile (stream-K)
+    (4100, 384, 256, 384, 0, [0]),                                  # composed-head wgrad
+    (3000, 512, 1024, 512, 0, [0]),                                 # projection wgrad
+    (700, 200, 64, 200, 0, [0, 3]),                                 # ragged Ny (not a multiple of 128), BN = 64
+])
+def test_wgrad_matches_numpy(engine, M, Ny, Nx, ldy, ycol0, taps):
+    """Weight-gradient contraction over rows (tcgen05 MN-major engine, engine=0; CUDA-core engine, engine=1)."""
+    rng = np.random.RandomState(M + Ny)
+    rowsX = M + max(taps) + 7
+    Y = torch.from_numpy(rng.standard_normal((M, ldy)).astype(np.float32)).to(torch.bfloat16)
+    X = torch.from_numpy(rng.standard_normal((rowsX, Nx)).astype(np.float32)).to(torch.bfloat16)
+    Yf, Xf = Y.float().numpy().astype(np.float64), X.float().numpy().astype(np.float64)
+    ref = np.stack([Yf[:, ycol0:ycol0 + Ny].T @ Xf[o:o + M] for o in taps])
+    Yd, Xd = Y.cuda(), X.cuda()
+    D = torch.zeros(len(taps), Ny, Nx, device="cuda")
+    a = L.WgradArgs()
+    a.Y, a.ldy, a.ycol0, a.Ny = Yd.data_ptr(), ldy, ycol0, Ny
+    a.X, a.rowsX, a.ldx, a.xcol0, a.Nx = Xd.data_ptr(), rowsX, Nx, 0, Nx
+    a.M, a.ntaps = M, len(taps)
+    for i, o in enumerate(taps):
+        a.tap_off[i] = o
+    a.D, a.dtype, a.engine = D.data_ptr(), 1, engine
+    lib = L.get_lib()
+    lib.rgp_wgrad(C.byref(a), torch.cuda.current_stream().cuda_stream)
+    lib.rgp_wgrad(C.byref(a), torch.cuda.current_stream().cuda_stream)      # accumulates: D = 2 * contraction
+    torch.cuda.synchronize()
+    got = D.cpu().numpy().astype(np.float64) / 2
+    err = np.abs(got - ref).max()
+    assert err <= 2e-5 * np.sqrt(M) * 4, (err, np.abs(ref).max())
