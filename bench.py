@@ -167,7 +167,9 @@ def workload_config(args):
                                              args.grid, args.grid, args.hidden),
             "clips_per_gpu": args.batch, "T": args.T, "grid": args.grid, "hidden": args.hidden,
             "l2_policy": "inputs larger than L2 (features 1.8 GB/step at the default size)",
-            "parallelism": "dp%d (clips sharded, no data-path collective in inference)" % args.gpus}
+            "parallelism": ("dp%d (clips sharded across ranks; one NCCL all-reduce of the flat fp32 gradient per step)"
+                            if args.mode == "train" else
+                            "dp%d (clips sharded across ranks, no data-path collective in inference)") % args.gpus}
 
 
 # ----------------------------------------------------------------------------------------------
@@ -180,8 +182,8 @@ def main():
         run_reference(args, rank, world)
         return
     import torch.distributed as dist
-    from oracle import model_oracle as O          # parameter init + cpu_baseline leg only
     from recurrent_gaze_prediction_b200 import synthetic as SY
+    from recurrent_gaze_prediction_b200.models.model_util import init_parameters
     from recurrent_gaze_prediction_b200.engine import GazeEngine
     from recurrent_gaze_prediction_b200 import lib as L
 
@@ -192,7 +194,7 @@ def main():
     B, T, G, Ch = args.batch, args.T, args.grid, args.hidden
     dtype = 1 if args.dtype == "bf16" else 0
     train = args.mode == "train"
-    p = O.init_params(args.model, hidden=Ch, T=T, grid=G, seed=0, regime="R")
+    p = init_parameters(args.model, hidden=Ch, T=T, grid=G, seed=0)      # the reference's initialisers
     eng = GazeEngine(args.model, B=B, T=T, G=G, Ch=Ch, dtype=dtype, device=dev, train=train)
     eng.load_tf_params(p)
     GH = eng.GH
@@ -208,17 +210,41 @@ def main():
     probs_h = torch.empty(B, T, GH, GH, dtype=torch.float32).pin_memory()
     loss_h = torch.empty(1, dtype=torch.float32).pin_memory()
 
-    def step_eager():
-        eng.forward(c3d=c3d_d, gt=gt_d)
+    allreduce = (lambda t: dist.all_reduce(t, op=dist.ReduceOp.SUM)) if world > 1 else None
+
+    def fwd_bwd():
+        eng.forward(c3d=c3d_d, gt=gt_d, global_batch=B * world)
         if train:
             eng.backward()
-            eng.optimizer_step()
 
-    graph, per_replay = (None, 0) if args.no_graph else eng.make_graph(step_eager)
+    def opt():
+        # data parallel: ONE NCCL all-reduce (sum) of the flat fp32 gradient, then the global-norm clip + TF-Adam
+        # identically on every rank (base.py:287-297: the norm is over the GLOBAL gradient)
+        eng.optimizer_step(allreduce=allreduce)
+
+    def step_eager():
+        fwd_bwd()
+        if train:
+            opt()
+
+    graph, per_replay, graph2 = None, 0, None
+    if not args.no_graph:
+        if train and world > 1:      # the collective stays outside the captured region: fwd+BPTT graph, all-reduce, Adam graph
+            graph, per_replay = eng.make_graph(fwd_bwd)
+            allreduce, keep = None, allreduce
+            graph2, n2 = eng.make_graph(opt)
+            allreduce = keep
+            per_replay += n2
+        else:
+            graph, per_replay = eng.make_graph(step_eager)
 
     def step_resident():
         if graph is None:
             step_eager()
+        elif graph2 is not None:
+            graph.replay()
+            dist.all_reduce(eng.grads, op=dist.ReduceOp.SUM)
+            graph2.replay()
         else:
             graph.replay()
 
@@ -285,7 +311,7 @@ def main():
     cpu = None
     if rank == 0 and not args.no_cpu_baseline:
         nb = args.cpu_clips
-        pc = O.init_params(args.model, hidden=Ch, T=T, grid=G, seed=0, regime="R")
+        pc = p
         c3 = c3d_pool[:nb]
         g = gt_pool[:nb]
         cpu_reference_step(args.model, pc, c3, g, train)

@@ -59,6 +59,7 @@ class GazeEngine(object):
         self._alloc()
         self.head_version = -1
         self.param_version = 0
+        self._state_dirty = False     # slab 0 (h_0, and c_0 for the LSTM) holds a caller-provided state
 
     # ------------------------------------------------------------------ parameters
     def _build_params(self):
@@ -272,12 +273,16 @@ class GazeEngine(object):
         self.lib.rgp_tapgemm(C.byref(a), self._s())
 
     # ------------------------------------------------------------------ forward
-    def forward(self, c3d=None, emb=None, gt=None, loss_type="xentropy", global_batch=None):
+    def forward(self, c3d=None, emb=None, gt=None, loss_type="xentropy", global_batch=None, carry_state=False):
         """c3d [B,T,Cfeat,G,G] fp32 (reference entry, gaze_grcn.py:173) or emb [B,T,G,G,Cin] fp32
-        (already-projected features).  Returns logits [B,T,GH,GW]; with gt also fills probs and loss."""
+        (already-projected features).  Returns logits [B,T,GH,GW]; with gt also fills probs and loss.
+        carry_state=True starts from the state left in slab 0 by set_initial_state() / carry_last_state()
+        (cell-level API, chunked long clips) instead of h_0 = 0 (gaze_grcn.py:262)."""
+        if not carry_state and self._state_dirty:
+            self.reset_state()
         self.stage_embed(c3d, emb)
         self.stage_i2h()
-        self.stage_recurrence()
+        self.stage_recurrence(zero_cell=not carry_state)
         self.stage_head()
         self.entry = "c3d" if c3d is not None else "emb"
         if gt is not None:
@@ -308,7 +313,48 @@ class GazeEngine(object):
                    M=self.T * self.B * self.S, N=NX, K=self.Cin, taps=self.taps3, epi=L.EPI_STORE_F32,
                    out_f32=self.Xg.data_ptr(), ldo=NX, S=self.S, Wp=self.Wp, G=self.G)
 
-    def stage_recurrence(self):
+    # ---- recurrent state access (zero_state / cell-level API: gaze_grcn.py:132-146, gaze_lstm.py:136-148)
+    def _pview(self, buf, t):
+        """slab t of a p-layout buffer as [B, Wp, Wp, C]; position (y, x) lives at [:, y+1, x+1]"""
+        n = self.B * self.S
+        return buf[t * n:(t + 1) * n].view(self.B, self.Wp, self.Wp, buf.shape[-1])
+
+    def reset_state(self):
+        n = self.B * self.S
+        self.lib.rgp_zero(self.Hf.data_ptr(), n * self.Ch * 4, self._s())
+        self.lib.rgp_zero(self.Hop.data_ptr(), n * self.Ch * self.Hop.element_size(), self._s())
+        self._state_dirty = False
+
+    def set_initial_state(self, h, c=None):
+        """h (and c for the LSTM) [B,G,G,Ch] fp32 device tensors -> slab 0 (fp32 master + operand copy)."""
+        B, G, Ch, s = self.B, self.G, self.Ch, self._s()
+        assert tuple(h.shape) == (B, G, G, Ch) and h.dtype == torch.float32, "state must be [B,%d,%d,%d] fp32" % (G, G, Ch)
+        h = h.contiguous()
+        self.lib.rgp_pack_emb(h.data_ptr(), self.Hf.data_ptr(), B, 1, G, Ch, 0, s)
+        self.lib.rgp_pack_emb(h.data_ptr(), self.Hop.data_ptr(), B, 1, G, Ch, self.dtype, s)
+        if self.lstm:
+            assert c is not None and tuple(c.shape) == (B, G, G, Ch)
+            self.lib.rgp_zero(self.Cf.data_ptr(), self.Cf.numel() * 4, s)
+            self.lib.rgp_pack_emb(c.contiguous().data_ptr(), self.Cf.data_ptr(), B, 1, G, Ch, 0, s)
+        self._state_dirty = True
+
+    def read_state(self, t=None):
+        """h_t (after t steps; default: after the last step) as [B,G,G,Ch] fp32; LSTM: (c, h) with c the current cell."""
+        t = self.T if t is None else t
+        h = self._pview(self.Hf, t)[:, 1:, 1:, :].contiguous()
+        if self.lstm:
+            return self._pview(self.Cf, 0)[:, 1:, 1:, :].contiguous(), h
+        return h
+
+    def carry_last_state(self):
+        """h_T -> slab 0, so that the next forward(carry_state=True) continues the same clips (chunked long clips,
+        extract_map.py:148-238)."""
+        n = self.B * self.S
+        self.Hf[:n].copy_(self.Hf[self.T * n:(self.T + 1) * n])
+        self.Hop[:n].copy_(self.Hop[self.T * n:(self.T + 1) * n])
+        self._state_dirty = True
+
+    def stage_recurrence(self, zero_cell=True):
         """(a4/a6/a7) the T-step recurrence: gaze_grcn.py:259-288, gaze_lstm.py:260-286."""
         lib, s = self.lib, self._s()
         B, T, S, Ch, Wp, G = self.B, self.T, self.S, self.Ch, self.Wp, self.G
@@ -322,7 +368,7 @@ class GazeEngine(object):
             if self.head == "deconv":
                 hs = self.HS.data_ptr() + t * B * HEAD_S * Ch * es
             if self.lstm:
-                if t == 0:
+                if t == 0 and zero_cell:
                     lib.rgp_zero(self.Cf.data_ptr(), self.Cf.numel() * 4, s)
                 self._gemm(A=self._slab(self.Hop, t), rowsA=self.rows_step, lda=Ch, Bw=pop("Wh_op"), M=M, N=3 * Ch,
                            K=Ch, taps=self.taps3, epi=L.EPI_STORE_F32, out_f32=self.Hconv.data_ptr(), ldo=3 * Ch,

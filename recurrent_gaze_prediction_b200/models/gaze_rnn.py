@@ -1,0 +1,297 @@
+"""Recurrent gaze-prediction model base — mirror of the reference's ``models/gaze_rnn.py``.
+
+``GazePredictionGRU`` keeps the reference's constructor / attribute / method contract (``gaze_rnn.py:66-105`` ctor,
+``:108-209`` build_model, ``:363-408`` create_loss_and_summary, ``:435-478`` learning rate + train op, ``:483-565``
+single_step, ``:568-650`` generate, ``:653-679`` evaluate / generate_and_evaluate).  The TF session is replaced by
+a :class:`GazeEngine`: "placeholders" (``c3d_input``, ``frame_images``, ``gt_gazemap``) are device buffers that
+``single_step`` / ``generate`` fill from pinned host memory, and ``session.run`` is one forward (+ backward +
+clip/Adam) pass of hand-written kernels on the model's CUDA stream.
+
+The class named GazePredictionGRU in the reference is itself the *dense* GRU variant (parity
+unpinned, lowest priority); here it only carries the shared machinery and refuses to build a network — use the
+GRCN / GRCN77 / LSTM subclasses.
+"""
+from __future__ import annotations
+
+import logging
+import time
+
+import numpy as np
+import torch
+
+from ..engine import GazeEngine, LOSS_TYPES
+from .. import lib as L
+from .. import evaluation_metrics as EM
+from .base import BaseModelConfig, ModelBase
+from .model_util import init_parameters, normalize_probability_map
+
+log = logging.getLogger("rgp")
+
+
+class _E(dict):
+    """attribute dict (the reference uses easydict)"""
+    __getattr__ = dict.__getitem__
+    __setattr__ = dict.__setitem__
+
+
+CONSTANTS = _E(image_width=98, image_height=98, gazemap_width=49, gazemap_height=49,
+               saliencymap_width=49, saliencymap_height=49)        # gaze_rnn.py:34-40
+
+
+class GRUModelConfig(BaseModelConfig):
+    """gaze_rnn.py:44-61, plus the knobs the reference hard-codes inside its graph builders (hidden width 128
+    ``gaze_grcn.py:211``, projection 512 ``:204``, grid 7) and the B200 execution options."""
+
+    def __init__(self):
+        super(GRUModelConfig, self).__init__()
+        self.n_lstm_steps = 42
+        self.batch_size = 7
+        self.dim_feature = 1024
+        self.dim_sal = 1024 * 49
+        self.dim_sal_proj = 1024
+        self.optimization_method = 'adam'
+        self.loss_type = 'xentropy'
+        self.use_flip_batch = True
+        # --- extensions (defaults reproduce the reference) ---
+        self.rnn_state_size = 128
+        self.dim_cnn_proj = 512
+        self.grid = 7
+        self.dtype = 'bf16'           # 'bf16': tcgen05 engine, fp32 accumulate; 'fp32': CUDA-core engine
+        self.device = 'cuda'
+        self.seed = 0
+        self.learning_rate_decay_steps = 500
+
+
+def _shard(x, rank, world):
+    n = len(x) // world
+    return x[rank * n:(rank + 1) * n]
+
+
+class GazePredictionGRU(ModelBase):
+    model_name = None            # engine model key, set by subclasses
+    train_mode_default = True
+
+    def __init__(self, session, data_sets, config=None, gazemap_height=None, gazemap_width=None):
+        config = config if config is not None else GRUModelConfig()
+        self.session = session            # opaque: None, or a dict {'rank':, 'world_size':, 'allreduce':, 'lib':}
+        self.data_sets = data_sets
+        self.config = config
+        super(GazePredictionGRU, self).__init__(config)
+        self.batch_size = config.batch_size
+        self.n_lstm_steps = config.n_lstm_steps
+        self.dim_feature = config.dim_feature
+        self.dim_sal = config.dim_sal
+        self.dim_sal_proj = config.dim_sal_proj
+        self.dim_cnn_proj = getattr(config, "dim_cnn_proj", 512)
+        self.gazemap_height = gazemap_height or self._default_gazemap_hw()[0]
+        self.gazemap_width = gazemap_width or self._default_gazemap_hw()[1]
+        self.image_height = CONSTANTS.image_height
+        self.image_width = CONSTANTS.image_width
+        sess = session if isinstance(session, dict) else {}
+        self.rank = int(sess.get("rank", 0))
+        self.world_size = int(sess.get("world_size", 1))
+        self._allreduce = sess.get("allreduce")
+        self._lib = sess.get("lib")
+        if self.batch_size % self.world_size:
+            raise ValueError("batch_size %d is not divisible by the %d data-parallel ranks" % (self.batch_size, self.world_size))
+        self.local_batch = self.batch_size // self.world_size
+        self.build_model()
+        self.build_train_op()
+
+    def _default_gazemap_hw(self):
+        return CONSTANTS.gazemap_height, CONSTANTS.gazemap_width
+
+    # ---------------------------------------------------------------- graph = engine + device "placeholders"
+    def build_model(self):
+        """gaze_rnn.py:108-209: inputs, network, loss."""
+        if self.model_name is None:
+            raise NotImplementedError("the dense GRU variant (gaze_rnn.py:241-351) is not part of the B200 hot path; "
+                                      "use GazePredictionGRCN / GazePredictionLSTM")
+        c = self.config
+        B, T, G = self.local_batch, self.n_lstm_steps, getattr(c, "grid", 7)
+        dev = torch.device(getattr(c, "device", "cuda"))
+        dtype = 1 if getattr(c, "dtype", "bf16") == "bf16" else 0
+        train = bool(getattr(c, "trainable", True)) and self.model_name != "gaze_lstm"
+        self.engine = GazeEngine(self.model_name, B=B, T=T, G=G, Ch=getattr(c, "rnn_state_size", 128),
+                                 Cin=self.dim_cnn_proj, Cfeat=c.dim_feature, dtype=dtype, device=dev, lib=self._lib,
+                                 train=train)
+        GH = self.engine.GH
+        if (self.gazemap_height, self.gazemap_width) != (GH, GH):
+            raise ValueError("%s predicts %dx%d gaze maps, not %dx%d" % (self.model_name, GH, GH, self.gazemap_height,
+                                                                         self.gazemap_width))
+        self.engine.load_tf_params(init_parameters(self.model_name, hidden=self.engine.Ch, T=T, grid=G,
+                                                   dim_proj=self.dim_cnn_proj, dim_feature=c.dim_feature,
+                                                   seed=getattr(c, "seed", 0)))
+        z = lambda *s: torch.zeros(*s, dtype=torch.float32, device=dev)
+        self.frame_images = None                                     # unused by the RGP path (gaze_grcn.py:173-376 never reads it)
+        self.c3d_input = z(B, T, c.dim_feature, G, G)                # gaze_rnn.py:118-121
+        self.gt_gazemap = z(B, T, GH, GH)                            # gaze_rnn.py:122-126
+        self.dropout_keep_prob = 1.0                                 # never fires in GRCN / LSTM
+        self.predicted_gazemaps_logit = self.engine.logits           # gaze_rnn.py:156
+        self.predicted_gazemaps = self.engine.probs if c.loss_type in ('xentropy', 'KLD') else self.engine.logits
+        self.loss = self.engine.loss
+        if c.loss_type not in LOSS_TYPES:
+            raise NotImplementedError(str(c.loss_type))             # gaze_rnn.py:405-406
+        pin = dev.type == "cuda"
+        self._c3d_host = torch.zeros(B, T, c.dim_feature, G, G, dtype=torch.float32, pin_memory=pin)
+        self._gt_host = torch.zeros(B, T, GH, GH, dtype=torch.float32, pin_memory=pin)
+
+    @staticmethod
+    def create_loss_and_summary(predicted_gazemaps, gt_gazemap, loss_type='xentropy', lib=None):
+        """gaze_rnn.py:363-408: scalar loss of logits [B,T,GH,GW] against gt (device tensors).  'KLD' (broken in
+        the reference, :395-403) is xent - H(gt), which has the same gradient."""
+        if loss_type not in LOSS_TYPES:
+            raise NotImplementedError(str(loss_type))
+        lib = lib or L.get_lib()
+        B, T, GH, GW = predicted_gazemaps.shape
+        assert tuple(gt_gazemap.shape) == (B, T, GH, GW)
+        dev = predicted_gazemaps.device
+        fl = torch.zeros(B * T, dtype=torch.float32, device=dev)
+        out = torch.zeros(1, dtype=torch.float32, device=dev)
+        s = torch.cuda.current_stream(dev).cuda_stream if dev.type == "cuda" else 0
+        lib.rgp_softmax_xent_fwd_bwd(predicted_gazemaps.contiguous().data_ptr(), gt_gazemap.contiguous().data_ptr(), 0, 0,
+                                     fl.data_ptr(), B * T, GH * GW, 1.0 / (B * T), LOSS_TYPES[loss_type], s)
+        lib.rgp_reduce_sum(fl.data_ptr(), B * T, out.data_ptr(), s)
+        return out
+
+    # ---------------------------------------------------------------- optimiser (gaze_rnn.py:435-478, base.py:262-297)
+    def _learning_rate_at(self, step):
+        """tf.train.exponential_decay(lr0, global_step, 500, decay, staircase=True) (gaze_rnn.py:439-443)."""
+        c = self.config
+        return self.initial_learning_rate * self._lr_scale * \
+            self.learning_rate_decay ** (step // getattr(c, "learning_rate_decay_steps", 500))
+
+    def build_train_op(self):
+        self.global_step = 0
+        self.learning_rate = self.current_learning_rate
+        self.train_op = self._train_step if self.engine.train else None
+        self.no_op = lambda: None        # the ShallowNet train-op of the reference is a no_op (gaze_rnn.py:459-466)
+
+    def _train_step(self):
+        self.engine.backward()
+        self.engine.optimizer_step(lr0=self.initial_learning_rate * self._lr_scale, decay=self.learning_rate_decay,
+                                   clip=self.max_grad_norm, allreduce=self._allreduce)
+        self.global_step = self.engine.step
+
+    # ---------------------------------------------------------------- feeding ("session.run")
+    def _feed(self, batch_c3d, batch_maps):
+        """host batch (global batch_size clips) -> this rank's shard -> pinned staging -> device placeholders"""
+        c3d = np.reshape(batch_c3d, [self.batch_size, -1, self.dim_feature, self.engine.G, self.engine.G])
+        c3d = _shard(c3d, self.rank, self.world_size)
+        maps = _shard(np.asarray(batch_maps, dtype=np.float32), self.rank, self.world_size)
+        if c3d.shape[1] != self.n_lstm_steps:
+            raise ValueError("clip length %d != n_lstm_steps %d" % (c3d.shape[1], self.n_lstm_steps))
+        self._c3d_host.copy_(torch.from_numpy(np.ascontiguousarray(c3d, dtype=np.float32)))
+        self._gt_host.copy_(torch.from_numpy(np.ascontiguousarray(maps)))
+        self.c3d_input.copy_(self._c3d_host, non_blocking=True)
+        self.gt_gazemap.copy_(self._gt_host, non_blocking=True)
+
+    def run(self, train=False):
+        """One pass over the fed placeholders: forward + loss (+ BPTT + clip/Adam when train).  Returns the loss."""
+        self.engine.forward(c3d=self.c3d_input, gt=self.gt_gazemap, loss_type=self.config.loss_type,
+                            global_batch=self.batch_size)
+        if train:
+            if self.train_op is None:
+                raise RuntimeError("this model was built without a train op")
+            self.train_op()
+        loss = float(self.engine.loss.cpu()[0])
+        if self.world_size > 1 and self._allreduce is not None:
+            t = self.engine.loss.clone()
+            self._allreduce(t)          # local losses are already scaled by 1/(B_global*T): the sum is the global loss
+            loss = float(t.cpu()[0])
+        return loss
+
+    def single_step(self, train_mode=True, dataset=None):
+        """gaze_rnn.py:483-565."""
+        _start_time = time.time()
+        if dataset is None:
+            dataset = self.data_sets.train if train_mode else self.data_sets.valid
+        batch_images, batch_maps, batch_fixmaps, batch_c3d, batch_pupil, batch_clipnames = dataset.next_batch(self.batch_size)
+        assert batch_images.dtype == np.float32
+        batch_c3d = np.reshape(batch_c3d, [self.batch_size, -1, self.dim_feature, self.engine.G, self.engine.G])
+        if self.config.loss_type in ('xentropy', 'KLD'):
+            batch_maps = normalize_probability_map(batch_maps)
+        if train_mode and self.config.use_flip_batch:        # gaze_rnn.py:504-510 (global numpy RNG, same draw)
+            batch_size = len(batch_images)
+            indices = np.random.choice(batch_size, batch_size // 2, replace=False)
+            if batch_images.shape[2] > 1:
+                batch_images[indices, :] = batch_images[indices, :, :, ::-1, :]
+            batch_maps[indices, :] = batch_maps[indices, :, :, ::-1]
+            batch_c3d[indices, :] = batch_c3d[indices, :, :, :, ::-1]
+            batch_fixmaps[indices, :] = batch_fixmaps[indices, :, :, ::-1]
+        self._feed(batch_c3d, batch_maps)
+        loss = self.run(train=train_mode)
+        self.last_loss = loss
+        step = self.current_step
+        _end_time = time.time()
+        if (not train_mode) or np.mod(step, self.config.steps_per_logprint) == 0:
+            epoch = float(step * self.batch_size) / max(1, len(self.data_sets.train))
+            (log.info if train_mode else log.warning)(
+                " [%5s epoch %.1f / step %4d] %sbatch total-loss: %.5f, target-loss: %.5f "
+                "(%.3f sec/batch, %.3f instances/sec) (lr=%.3g)",
+                'train' if train_mode else 'val', epoch, step,
+                (self.config.train_tag + ' | ') if self.config.train_tag else '', loss, loss,
+                _end_time - _start_time, self.batch_size / (_end_time - _start_time), self.current_learning_rate)
+        return step
+
+    def generate(self, dataset, max_instances=50):
+        """gaze_rnn.py:568-650: batched inference; per-frame lists under the reference's dict keys."""
+        GH, GW = self.gazemap_height, self.gazemap_width
+        pred, gts, fixs, images, names, c3ds = [], [], [], [], [], []
+        n_instances = len(dataset)
+        if max_instances is not None:
+            n_instances = min(n_instances, max_instances)
+        step_num = int(np.ceil(n_instances / float(self.batch_size)))
+        assert step_num > 0
+        for _ in range(step_num):
+            batch_images, batch_maps, batch_fixmaps, batch_c3d, batch_pupil, batch_filename = dataset.next_batch(self.batch_size)
+            batch_images = np.asarray(list(batch_images))
+            assert batch_images.dtype == np.float32
+            batch_c3d = np.reshape(batch_c3d, [self.batch_size, -1, self.dim_feature, self.engine.G, self.engine.G])
+            if self.config.loss_type == 'xentropy':
+                batch_maps = normalize_probability_map(batch_maps)
+            self._feed(batch_c3d, batch_maps)
+            self.run(train=False)
+            gazes = self.predicted_gazemaps.cpu().numpy()
+            if self.world_size > 1:        # final gather of the shards: every rank returns all frames
+                import torch.distributed as dist
+                parts = [None] * self.world_size
+                dist.all_gather_object(parts, gazes)
+                gazes = np.concatenate(parts, axis=0)
+            c3ds.extend(batch_c3d)
+            pred.extend(gazes)
+            gts.extend(batch_maps)
+            fixs.extend(batch_fixmaps)
+            images.extend(np.concatenate(batch_images))
+            names.extend(batch_filename)
+        pred = np.vstack(pred).reshape([-1, GH, GW])
+        gts = np.vstack(gts).reshape([-1, GH, GW])
+        c3ds = np.vstack(c3ds).reshape([-1, self.dim_feature, self.engine.G, self.engine.G])
+        try:
+            fixs = np.vstack(fixs)
+        except ValueError:                  # per-clip fixation maps at differing resolutions (gaze_rnn.py:632-640)
+            fixs = [fm[t] for fm in fixs for t in range(len(fm))]
+            assert len(fixs) == len(pred)
+        return {'pred_gazemap_list': pred, 'gt_gazemap_list': gts, 'images_list': images,
+                'fixationmap_list': fixs, 'clipname_list': names, 'c3d_list': c3ds}
+
+    def evaluate(self, pred_gazemap_list, gt_gazemap_list, fixationmap_list, images_list, **_ignored):
+        """gaze_rnn.py:653-674.  (`**_ignored` absorbs the extra keys generate() returns — the reference raises a
+        TypeError there)"""
+        assert len(pred_gazemap_list) == len(gt_gazemap_list) == len(fixationmap_list) == len(images_list), \
+            "Length mismatch: %d %d %d %d" % (len(pred_gazemap_list), len(gt_gazemap_list), len(fixationmap_list),
+                                              len(images_list))
+        batch_scores = {}
+        log.info('Evaluation on %d images', len(gt_gazemap_list))
+        eng = EM.MetricsEngine(device=self.engine.device, lib=self._lib)
+        for metric in EM.AVAILABLE_METRICS:
+            batch_scores[metric] = EM.saliency_score(metric, pred_gazemap_list, gt_gazemap_list, fixationmap_list,
+                                                     engine=eng)
+            log.info('Saliency %s : %f', metric, batch_scores[metric])
+        self.report_evaluate_summary(batch_scores)
+        return batch_scores
+
+    def generate_and_evaluate(self, dataset, max_instances=50):
+        ret = self.generate(dataset, max_instances)
+        scores = self.evaluate(**ret)
+        return ret, scores

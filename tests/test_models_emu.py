@@ -1,0 +1,195 @@
+"""The reference-facing model classes (recurrent_gaze_prediction_b200/models/*) over the NumPy emulation of the
+C-ABI: constructor / attribute / method contract of gaze_rnn.py, cells vs the oracle's cell maths, train steps vs the
+oracle's clip + TF-Adam, checkpoint round trip, generate/evaluate dict contract.  CPU only."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import model_oracle as O
+from recurrent_gaze_prediction_b200 import synthetic as SY
+from recurrent_gaze_prediction_b200.models import gaze_grcn, gaze_grcn77, gaze_lstm, gaze_rnn
+from recurrent_gaze_prediction_b200.models.model_util import init_parameters
+from emu_lib import EmuLib
+
+
+def small_config(T=3, B=4, Ch=16):
+    c = gaze_rnn.GRUModelConfig()
+    c.n_lstm_steps, c.batch_size, c.rnn_state_size = T, B, Ch
+    c.dim_feature, c.dim_cnn_proj = 64, 32
+    c.dtype, c.device = 'fp32', 'cpu'
+    c.initial_learning_rate = 1e-2
+    c.steps_per_logprint = 1000
+    return c
+
+
+def data(T=3, n=12, **kw):
+    return SY.read_synthetic_data_sets(n, 12, 12, T=T, dim_feature=64, **kw)
+
+
+def test_constructor_contract_and_single_step_matches_oracle():
+    c = small_config()
+    ds = data()
+    m = gaze_grcn.GazePredictionGRCN({'lib': EmuLib()}, ds, c)
+    for attr in ("batch_size", "n_lstm_steps", "predicted_gazemaps", "predicted_gazemaps_logit", "loss", "c3d_input",
+                 "frame_images", "gt_gazemap", "dropout_keep_prob", "train_op", "global_step", "learning_rate", "session"):
+        assert hasattr(m, attr), attr
+    assert tuple(m.c3d_input.shape) == (4, 3, 64, 7, 7) and tuple(m.gt_gazemap.shape) == (4, 3, 49, 49)
+    assert m.current_step == 0 and abs(m.current_learning_rate - 1e-2) < 1e-12
+    # oracle replay of the same step: same parameters (same seed, same creation order), same batch, same flip draw
+    p = init_parameters("gaze_grcn", hidden=16, T=3, dim_proj=32, dim_feature=64, seed=0)
+    ref_ds = data()
+    imgs, maps, fix, c3d, _, _ = ref_ds.train.next_batch(4)
+    c3d = c3d.reshape(4, 3, 64, 7, 7)
+    maps = O.normalize_probability_map(maps)
+    np.random.seed(5)
+    idx = np.random.choice(4, 2, replace=False)
+    maps[idx] = maps[idx][:, :, :, ::-1]
+    c3d[idx] = c3d[idx][:, :, :, :, ::-1]
+    _, _, ref_loss, grads = O.forward_loss_grads("gaze_grcn", p, maps.astype(np.float64), c3d=c3d.astype(np.float64))
+    np.random.seed(5)
+    step = m.single_step(train_mode=True)
+    assert step == 1 and m.current_step == 1
+    assert abs(m.last_loss - ref_loss) <= 1e-5 * abs(ref_loss)
+    names = list(p)
+    gl, _ = O.clip_by_global_norm([grads[k] for k in names], 10.0)
+    newp, _, _ = O.adam_step([np.asarray(p[k], np.float64) for k in names], gl, [np.zeros_like(p[k]) for k in names],
+                             [np.zeros_like(p[k]) for k in names], 1, 1e-2)
+    got = m.engine.op_to_tf(m.engine.params.numpy())
+    for k, r in zip(names, newp):
+        if k == "out_b":
+            continue    # its true gradient is sum(softmax - gt) = 0: Adam normalises rounding noise to +-lr
+        assert np.allclose(got[k].reshape(r.shape), r, rtol=2e-4, atol=1e-6), k
+    # validation step does not train
+    before = m.engine.params.clone()
+    assert m.single_step(train_mode=False) == 1
+    assert torch.equal(before, m.engine.params)
+
+
+def test_staircase_learning_rate_and_decay():
+    c = small_config()
+    m = gaze_grcn.GazePredictionGRCN({'lib': EmuLib()}, data(), c)
+    assert abs(m._learning_rate_at(499) - 1e-2) < 1e-15
+    assert abs(m._learning_rate_at(500) - 1e-2 * 0.8) < 1e-15
+    assert abs(m._learning_rate_at(1234) - 1e-2 * 0.8 ** 2) < 1e-15
+    assert abs(m.decay_learning_rate(0.5) - 5e-3) < 1e-15
+
+
+def test_checkpoint_roundtrip(tmp_path):
+    c = small_config()
+    c.train_dir = str(tmp_path)
+    lib = EmuLib()
+    m = gaze_grcn.GazePredictionGRCN({'lib': lib}, data(), c)
+    np.random.seed(0)
+    m.single_step()
+    m.single_step()
+    path = m.save_model_checkpoint(c.train_dir)
+    assert os.path.isfile(path) and os.path.isfile(os.path.join(c.train_dir, "model", "checkpoint"))
+    with np.load(path) as z:
+        assert "GRU_Conv_Wz" in z.files and z["GRU_Conv_Wz"].shape == (3, 3, 32, 16)      # reference names + TF layouts
+        assert "Upsampling/weight1" in z.files and int(z["__global_step__"]) == 2
+    c2 = small_config()
+    c2.train_dir, c2.seed = str(tmp_path), 123
+    m2 = gaze_grcn.GazePredictionGRCN({'lib': lib}, data(), c2)
+    assert not torch.equal(m.engine.params, m2.engine.params)
+    assert m2.reload_checkpoint()
+    assert torch.allclose(m.engine.params, m2.engine.params) and m2.current_step == 2
+    assert torch.equal(m.engine.adam_v, m2.engine.adam_v)
+    c3 = small_config()
+    c3.train_dir = str(tmp_path / "nothing_here")
+    assert not gaze_grcn.GazePredictionGRCN({'lib': lib}, data(), c3).reload_checkpoint()
+
+
+def test_generate_and_evaluate_contract():
+    c = small_config(T=3, B=4)
+    ds = data(n=12)
+    m = gaze_grcn.GazePredictionGRCN({'lib': EmuLib()}, ds, c)
+    ret = m.generate(ds.valid, max_instances=8)
+    assert sorted(ret) == ['c3d_list', 'clipname_list', 'fixationmap_list', 'gt_gazemap_list', 'images_list',
+                           'pred_gazemap_list']
+    assert ret['pred_gazemap_list'].shape == (8 * 3, 49, 49) and ret['gt_gazemap_list'].shape == (24, 49, 49)
+    assert np.allclose(ret['pred_gazemap_list'].sum(axis=(1, 2)), 1.0, atol=1e-4)          # probabilities (gaze_rnn.py:156)
+    assert len(ret['fixationmap_list']) == 24 and len(ret['images_list']) == 24 and len(ret['clipname_list']) == 8
+    np.random.seed(1)
+    scores = m.evaluate(**ret)
+    assert sorted(scores) == sorted(['sim', 'cc', 'AUC_shuffled', 'AUC_Borji'])
+    assert 0 < scores['sim'] <= 1 and -1 <= scores['cc'] <= 1 and 0 <= scores['AUC_Borji'] <= 1
+    assert m.evaluation_history[-1][1] == scores
+    with pytest.raises(AssertionError):
+        m.evaluate(ret['pred_gazemap_list'][:3], ret['gt_gazemap_list'], ret['fixationmap_list'], ret['images_list'])
+
+
+def test_loss_builder_and_errors():
+    lib = EmuLib()
+    rng = np.random.RandomState(0)
+    logits = torch.from_numpy(rng.standard_normal((2, 3, 7, 7)).astype(np.float32))
+    gt = torch.from_numpy(O.normalize_probability_map(rng.uniform(size=(2, 3, 7, 7))).astype(np.float32))
+    for lt in ("xentropy", "l2", "KLD"):
+        got = float(gaze_rnn.GazePredictionGRU.create_loss_and_summary(logits, gt, lt, lib=lib)[0])
+        want = float(O.loss_fn(logits.double(), gt.double(), lt))
+        assert abs(got - want) <= 1e-5 * abs(want) + 1e-7, lt
+    with pytest.raises(NotImplementedError):
+        gaze_rnn.GazePredictionGRU.create_loss_and_summary(logits, gt, "hinge", lib=lib)
+    c = small_config()
+    c.loss_type = "hinge"
+    with pytest.raises(NotImplementedError):
+        gaze_grcn.GazePredictionGRCN({'lib': lib}, data(), c)
+    with pytest.raises(NotImplementedError):                     # the dense GRU variant is out of scope
+        gaze_rnn.GazePredictionGRU({'lib': lib}, data(), small_config())
+    c = small_config(B=4)
+    with pytest.raises(ValueError):
+        gaze_grcn.GazePredictionGRCN({'lib': lib, 'world_size': 3}, data(), c)
+
+
+def test_cells_match_oracle_cell_maths():
+    lib = EmuLib()
+    rng = np.random.RandomState(3)
+    B, G, Cin, Ch = 2, 7, 32, 16
+    x = torch.from_numpy(rng.standard_normal((B, G, G, Cin)).astype(np.float32))
+    # GRU cell
+    cell = gaze_grcn.GRU_RCN_Cell(Ch, Cin, device='cpu', lib=lib)
+    assert (cell.input_size, cell.output_size, cell.state_size) == (Cin, Ch, Ch)
+    big = {k: v * 2000 for k, v in cell.variables.items()}          # leave the sigma=1e-4 regime so gates move
+    cell.load_variables(big)
+    h0 = torch.from_numpy(rng.standard_normal((B, G, G, Ch)).astype(np.float32))
+    out, h1 = cell(x, h0)
+    pt = {k: torch.tensor(v, dtype=torch.float64) for k, v in big.items()}
+    _, ref = O.gru_rcn_cell(x.double(), h0.double(), pt)
+    assert torch.allclose(h1.double(), ref, atol=2e-5) and torch.equal(out, h1)
+    out2, h2 = cell(x, cell.zero_state(B))
+    _, ref2 = O.gru_rcn_cell(x.double(), torch.zeros(B, G, G, Ch, dtype=torch.float64), pt)
+    assert torch.allclose(h2.double(), ref2, atol=2e-5)
+    with pytest.raises(AssertionError):
+        cell(torch.zeros(B, 6, 7, Cin), h0)
+    # LSTM cell (reference arithmetic as written)
+    lc = gaze_lstm.LSTM_RCN_Cell(Ch, Cin, device='cpu', lib=lib)
+    assert lc.state_size == 2 * Ch
+    bigl = {k: v * 2000 for k, v in lc.variables.items()}
+    lc.load_variables(bigl)
+    s0 = torch.from_numpy(rng.standard_normal((B, G, G, 2 * Ch)).astype(np.float32))
+    h, s1 = lc(x, s0)
+    ptl = {k: torch.tensor(v, dtype=torch.float64) for k, v in bigl.items()}
+    refh, refs = O.lstm_rcn_cell(x.double(), s0.double(), ptl)
+    assert torch.allclose(s1.double(), refs, atol=2e-5) and torch.allclose(h.double(), refh, atol=2e-5)
+
+
+@pytest.mark.parametrize("mod,cls,model,GH", [(gaze_grcn, "GazePredictionGRCN", "gaze_grcn", 49),
+                                              (gaze_grcn77, "GazePredictionGRCN", "gaze_grcn77", 7),
+                                              (gaze_lstm, "GazePredictionLSTM", "gaze_lstm", 49)])
+def test_network_builders_match_oracle(mod, cls, model, GH):
+    rng = np.random.RandomState(1)
+    B, T = 2, 3
+    c3d = SY.make_c3d(rng, B, T, 64, 7)
+    p = O.init_params(model, hidden=16, T=T, dim_proj=32, dim_feature=64, seed=4, regime="S")
+    net = {}
+    logits = getattr(mod, cls).create_gazeprediction_network(None, torch.from_numpy(c3d), net=net, params=p,
+                                                             rnn_state_size=16, lib=EmuLib())
+    ref, _, _, _ = O.forward_loss_grads(model, p, np.full((B, T, GH, GH), 1.0 / GH ** 2), c3d=c3d.astype(np.float64))
+    assert tuple(logits.shape) == (B, T, GH, GH)
+    assert np.abs(logits.numpy() - ref).max() <= 2e-5 * np.abs(ref).max()
+    assert tuple(net['c3d_embedded'].shape) == (B, T, 7, 7, 32) and len(net['rcn_outputs']) == T
+    onet = {}
+    O.recurrent_network(model, O.to_torch(p), c3d=torch.from_numpy(c3d).double(), net=onet)
+    assert torch.allclose(net['c3d_embedded'].double(), onet['c3d_embedded'], atol=1e-4)
+    assert torch.allclose(net['rcn_outputs'][-1].double(), onet['rcn_outputs'][-1], atol=1e-4)
