@@ -1,0 +1,80 @@
+"""Reference-facing model classes and entry points on the real library (B200)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import model_oracle as O
+from recurrent_gaze_prediction_b200 import synthetic as SY
+from recurrent_gaze_prediction_b200.models import evaluate_gaze, gaze_grcn, gaze_lstm, gaze_rnn, train_gaze
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("dtype,tol", [("fp32", 1e-4), ("bf16", 2e-2)])
+def test_network_builder_matches_oracle(dtype, tol):
+    rng = np.random.RandomState(0)
+    B, T = 2, 4
+    c3d = SY.make_c3d(rng, B, T)
+    p = O.init_params("gaze_grcn", hidden=128, T=T, seed=1, regime="S")
+    net = {}
+    logits = gaze_grcn.GazePredictionGRCN.create_gazeprediction_network(None, torch.from_numpy(c3d).cuda(), net=net,
+                                                                        params=p, dtype=dtype)
+    gt = np.full((B, T, 49, 49), 1.0 / 2401)
+    ref, ref_probs, _, _ = O.forward_loss_grads("gaze_grcn", p, gt, c3d=c3d.astype(np.float64))
+    probs = torch.softmax(logits.reshape(B, T, -1).double(), -1).reshape(B, T, 49, 49).cpu().numpy()
+    rel = np.abs(probs - ref_probs).max(axis=(2, 3)) / ref_probs.max(axis=(2, 3))
+    assert rel.max() <= tol
+    assert tuple(net['c3d_embedded'].shape) == (B, T, 7, 7, 512)
+
+
+@pytest.mark.parametrize("dtype,tol", [("fp32", 2e-5), ("bf16", 2e-2)])
+def test_cells_on_gpu(dtype, tol):
+    rng = np.random.RandomState(3)
+    B, G, Cin, Ch = 3, 7, 512, 128
+    x = torch.from_numpy(rng.standard_normal((B, G, G, Cin)).astype(np.float32)).cuda()
+    cell = gaze_grcn.GRU_RCN_Cell(Ch, Cin, dtype=dtype)
+    big = {k: v * 300 for k, v in cell.variables.items()}
+    cell.load_variables(big)
+    h0 = torch.from_numpy(rng.standard_normal((B, G, G, Ch)).astype(np.float32)).cuda()
+    _, h1 = cell(x, h0)
+    _, ref = O.gru_rcn_cell(x.cpu().double(), h0.cpu().double(), {k: torch.tensor(v) for k, v in big.items()})
+    assert (h1.cpu().double() - ref).abs().max() <= tol * max(1.0, ref.abs().max())
+    lc = gaze_lstm.LSTM_RCN_Cell(Ch, Cin, dtype=dtype)
+    bigl = {k: v * 300 for k, v in lc.variables.items()}
+    lc.load_variables(bigl)
+    s0 = torch.from_numpy(rng.standard_normal((B, G, G, 2 * Ch)).astype(np.float32)).cuda()
+    h, s1 = lc(x, s0)
+    refh, refs = O.lstm_rcn_cell(x.cpu().double(), s0.cpu().double(), {k: torch.tensor(v) for k, v in bigl.items()})
+    assert (s1.cpu().double() - refs).abs().max() <= tol * max(1.0, refs.abs().max())
+
+
+def test_train_and_evaluate_entry_points(tmp_path):
+    args = train_gaze.make_parser().parse_args(
+        ["--model", "gaze_grcn", "--dataset", "synthetic", "--max_steps", "6", "--batch_size", "4", "--n_lstm_steps", "5",
+         "--train_dir", str(tmp_path), "--learning_rate", "0.001", "--dtype", "bf16"])
+    np.random.seed(0)
+    model, scores = train_gaze.train(args)
+    assert model.current_step == 7 and np.isfinite(model.last_loss)
+    assert sorted(scores) == ['AUC_Borji', 'AUC_shuffled', 'cc', 'sim']
+    path = model.save_model_checkpoint(str(tmp_path))
+    out = evaluate_gaze.main(["--model", "gaze_grcn", "--dataset", "synthetic", "--checkpoint_path", path,
+                              "--num_frames", "30", "--batch_size", "4", "--n_lstm_steps", "5",
+                              "--fixation_original_scale"])
+    assert len(out['AUC_Judd']) == 40 and np.isfinite(np.nanmean(out['AUC_Judd']))
+    gen = os.path.join(str(tmp_path), "generated-synthetic-7", "overall.txt")
+    assert os.path.isfile(gen)
+
+
+def test_training_through_the_model_class_learns():
+    """30 Adam steps on one repeated synthetic batch: the loss must fall (end-to-end sanity of fwd+BPTT+Adam)."""
+    c = gaze_rnn.GRUModelConfig()
+    c.n_lstm_steps, c.batch_size, c.initial_learning_rate, c.use_flip_batch = 6, 4, 1e-3, False
+    ds = SY.read_synthetic_data_sets(4, 4, 4, T=6)
+    m = gaze_grcn.GazePredictionGRCN(None, ds, c)
+    losses = []
+    for _ in range(30):
+        m.single_step()
+        losses.append(m.last_loss)
+    assert losses[-1] < losses[0] - 0.05, (losses[0], losses[-1])
