@@ -307,6 +307,9 @@ def main():
                 "bound": "tensor", "achieved": ach, "peak": tf_sus, "unit": "TFLOP/s", "frac": ach / tf_sus,
                 "peak_source": which + " (sustained bf16; burst %.1f)" % tf_burst, "traffic": None,
                 "ms_per_launch": i2h_ms, "stage_ms": evs}
+        if train:
+            eng.forward(c3d=c3d_d, gt=gt_d, global_batch=B * world)
+            roof["stage_ms_bwd"] = eng.time_backward(iters=3)
 
     cpu = None
     if rank == 0 and not args.no_cpu_baseline:

@@ -152,6 +152,10 @@ int rgp_head_w123t(const float* w123, void* out, int Ch, int dtype, void* stream
 /* frozen-BN backward (gaze_grcn.py:325): dgamma[t,c] += alpha * sum dhs*h ; dbeta[t,c] += sum dhs */
 int rgp_bn_bwd(const float* dhs, const float* h_f32, float* dgamma, float* dbeta, float alpha,
                int B, int G, int Ch, void* stream);
+/* the same for all T steps in one launch: dhs [T*B*S, Ch] (slab t = step t), h_f32 = slab of h_1 (slab t = h_{t+1}),
+ * dgamma / dbeta [T, Ch] */
+int rgp_bn_bwd_all(const float* dhs, const float* h_f32, float* dgamma, float* dbeta, float alpha,
+                   int B, int T, int G, int Ch, void* stream);
 /* out[j] += sum_m X[m, j] (X operand dtype [M, ld]) — bias gradients */
 int rgp_colsum(const void* X, int ld, int M, int N, float* out, int dtype, void* stream);
 /* gaze_grcn77.py:206-211 backward: dhs[m,c] = dlogit*out_W[c]; gout_W[c] += sum dlogit*h; gout_b += sum dlogit */

@@ -148,6 +148,11 @@ __global__ void __launch_bounds__(256) bn_bwd_kernel(const float* __restrict__ d
                                                       int B, int G, int Ch) {
   __shared__ float sg[8][32], sb[8][32];
   const int Wp = G + 1, S = Wp * Wp, P = G * G;
+  // blockIdx.z = time step (rgp_bn_bwd_all): consecutive B*S-row slabs of dhs / h, consecutive [Ch] rows of dgamma / dbeta
+  dhs += (long long)blockIdx.z * B * S * Ch;
+  h += (long long)blockIdx.z * B * S * Ch;
+  dgamma += (long long)blockIdx.z * Ch;
+  dbeta += (long long)blockIdx.z * Ch;
   const int c = blockIdx.x * 32 + (threadIdx.x & 31);
   const int w = threadIdx.x >> 5;
   float ag = 0.f, ab = 0.f;
@@ -269,6 +274,16 @@ int rgp_bn_bwd(const float* dhs, const float* h_f32, float* dgamma, float* dbeta
   dim3 grid((Ch + 31) / 32, gy);
   bn_bwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(dhs, h_f32, dgamma, dbeta, alpha, B, G, Ch);
   return check_launch("rgp_bn_bwd");
+}
+
+int rgp_bn_bwd_all(const float* dhs, const float* h_f32, float* dgamma, float* dbeta, float alpha, int B, int T, int G,
+                   int Ch, void* stream) {
+  int gy = (B * G * G + 63) / 64;
+  if (gy > 16) gy = 16;
+  if (gy < 1) gy = 1;
+  dim3 grid((Ch + 31) / 32, gy, T);
+  bn_bwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(dhs, h_f32, dgamma, dbeta, alpha, B, G, Ch);
+  return check_launch("rgp_bn_bwd_all");
 }
 
 int rgp_colsum(const void* X, int ld, int M, int N, float* out, int dtype, void* stream) {

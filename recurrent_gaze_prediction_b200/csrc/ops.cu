@@ -269,6 +269,49 @@ __global__ void __launch_bounds__(1024) reduce_sum_kernel(const float* __restric
   }
 }
 
+// Large n: kRedBlocks CTAs write fixed-order partials; the last CTA to arrive adds them in index order, so the
+// result does not depend on scheduling.  The scratch is library-static: calls must not overlap on different
+// streams of one process (include/rgp.h: one stream per model instance).
+constexpr int kRedBlocks = 296;
+__device__ double g_red_part[kRedBlocks];
+__device__ unsigned int g_red_count = 0;
+
+__global__ void __launch_bounds__(512) reduce_sum_big_kernel(const float* __restrict__ x, long long n, float* __restrict__ out) {
+  __shared__ double red[16];
+  __shared__ bool last;
+  const long long per = ((n / 4 + gridDim.x - 1) / gridDim.x) * 4;         // float4-aligned contiguous share per CTA
+  const long long b = (long long)blockIdx.x * per;
+  const long long e = (b + per < n) ? b + per : n;
+  double s = 0.0;
+  if (((uintptr_t)x & 15) == 0) {
+    const float4* x4 = reinterpret_cast<const float4*>(x + b);
+    const long long n4 = (e > b) ? (e - b) / 4 : 0;
+    for (long long i = threadIdx.x; i < n4; i += 512) { const float4 v = x4[i]; s += (double)v.x + (double)v.y + (double)v.z + (double)v.w; }
+    for (long long i = b + n4 * 4 + threadIdx.x; i < e; i += 512) s += (double)x[i];
+  } else {
+    for (long long i = b + threadIdx.x; i < e; i += 512) s += (double)x[i];
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+    for (int i = 0; i < 16; ++i) t += red[i];
+    g_red_part[blockIdx.x] = t;
+    __threadfence();
+    last = (atomicAdd(&g_red_count, 1u) == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (last && threadIdx.x == 0) {
+    __threadfence();
+    double t = 0.0;
+    for (unsigned i = 0; i < gridDim.x; ++i) t += *(volatile double*)&g_red_part[i];
+    out[0] = (float)t;
+    g_red_count = 0;
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // base.py:287-297: clip_by_global_norm + tf.train.AdamOptimizer (epsilon outside the bias correction)
 // ---------------------------------------------------------------------------------------------
@@ -391,7 +434,8 @@ int rgp_softmax_xent_fwd_bwd(const float* logits, const float* gt, float* probs,
 }
 
 int rgp_reduce_sum(const float* x, long long n, float* out, void* stream) {
-  reduce_sum_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(x, n, out);
+  if (n > (1 << 16)) reduce_sum_big_kernel<<<kRedBlocks, 512, 0, (cudaStream_t)stream>>>(x, n, out);
+  else reduce_sum_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(x, n, out);
   return check_launch("rgp_reduce_sum");
 }
 

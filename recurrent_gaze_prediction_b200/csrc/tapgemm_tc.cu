@@ -116,6 +116,63 @@ __device__ __forceinline__ void epi_row32(const rgp_tapgemm_args& a, const RowIn
         }
         return;
       }
+      case RGP_EPI_BWD_RH: {   // acc = dL/d(r.h): dpre_r and the direct part of dL/dh_{t-1}  (common.cuh epi_elem)
+        if (!r.valid) return;
+        float rr[32], x[32];
+        ldf32(a.save_r + (long long)r.m * a.Ch + n0, rr);
+        ldf32(a.hprev_f32 + r.prow * a.Ch + n0, x);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) x[i] = v[i] * x[i] * rr[i] * (1.0f - rr[i]);
+        stbf32((TA*)a.dg + (long long)r.m * a.ldg + a.Ch + n0, x);
+        float* dp = a.dhpart + (long long)r.m * a.Ch + n0;
+        ldf32(dp, x);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) x[i] = fmaf(v[i], rr[i], x[i]);
+        stf32(dp, x);
+        return;
+      }
+      case RGP_EPI_BWD_H: {    // acc = convT(dpre_z, dpre_r) of step t: full dL/dh_{t-1}, then the gates of step t-1
+        if (!r.valid) return;
+        float x[32], y[32];
+        ldf32(a.dhs + (long long)r.m * a.Ch + n0, x);
+        if (a.bias) {
+          ldf32(a.bias + n0, y);
+#pragma unroll
+          for (int i = 0; i < 32; ++i) x[i] *= y[i] * a.alpha;
+        }
+        float* dp = a.dhpart + (long long)r.m * a.Ch + n0;
+        ldf32(dp, y);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] += x[i] + y[i];                  // dh
+        ldf32(a.save_z + (long long)r.m * a.Ch + n0, x);                   // z
+#pragma unroll
+        for (int i = 0; i < 32; ++i) y[i] = v[i] * x[i];                   // dh * z -> dhpart
+        stf32(dp, y);
+        float c[32];
+        ldf32(a.save_c + (long long)r.m * a.Ch + n0, c);
+        ldf32(a.hprev_f32 + r.prow * a.Ch + n0, y);                        // h_{t-2}
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          const float dz = v[i] * (y[i] - c[i]), dc = v[i] * (1.0f - x[i]);
+          y[i] = dz * x[i] * (1.0f - x[i]);
+          c[i] = dc * (1.0f - c[i] * c[i]);
+        }
+        stbf32((TA*)a.dg + (long long)r.m * a.ldg + n0, y);
+        stbf32((TA*)a.dg + (long long)r.m * a.ldg + 2 * a.Ch + n0, c);
+        return;
+      }
+      case RGP_EPI_DHS:
+        if (r.valid) stf32(a.out_f32 + r.orow * a.ldo + n0, v);
+        return;
+      case RGP_EPI_DX_DENSE:
+        if (r.valid) stbf32((TA*)a.out_op + r.orow * a.ldo + n0, v);
+        return;
+      case RGP_EPI_STORE_OP:
+        stbf32((TA*)a.out_op + (long long)r.m * a.ldo + n0, v);
+        return;
+      case RGP_EPI_STORE_OP_P:
+        if (r.valid) stbf32((TA*)a.out_op + r.prow * a.ldo + n0, v);
+        return;
       default:
         break;
     }
@@ -324,7 +381,7 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     // ===================== epilogue (warps 2..5 -> TMEM lane groups (warp % 4)) =====================
     const int lg = warp & 3;
     int acc = 0; uint32_t accphase = 0;
-    const bool vec = (a.N % 32 == 0) && (a.ldo % 8 == 0) && (a.ldx % 4 == 0) && (a.Ch % 32 == 0);
+    const bool vec = (a.N % 32 == 0) && (a.ldo % 8 == 0) && (a.ldx % 4 == 0) && (a.Ch % 32 == 0) && (a.ldg % 8 == 0);
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const int mt = tile / ntiles, nt = tile - mt * ntiles;
       const int m0 = mt * BM, n0 = nt * BN;
@@ -516,7 +573,9 @@ int tapgemm_tc(const rgp_tapgemm_args& a, cudaStream_t s) {
   RGP_CHECK_ARG(a.K % BK == 0, "tapgemm_tc: K=%d must be a multiple of %d", a.K, BK);
   RGP_CHECK_ARG(a.lda % 8 == 0, "tapgemm_tc: lda=%d must be a multiple of 8 (16-byte TMA stride)", a.lda);
   RGP_CHECK_ARG(((uintptr_t)a.A & 15) == 0 && ((uintptr_t)a.Bw & 15) == 0, "tapgemm_tc: operands must be 16-byte aligned");
-  if (a.N % 256 == 0) return launch<256>(a, s);
+  const int mtiles = (a.M + BM - 1) / BM;
+  // less than half a wave of 128x256 tiles (small-batch recurrence steps): 128x128 tiles fill twice the SMs
+  if (a.N % 256 == 0 && (long long)mtiles * (a.N / 256) * 2 > num_sms()) return launch<256>(a, s);
   if (a.N % 128 == 0) return launch<128>(a, s);
   if (a.N % 64 == 0) return launch<64>(a, s);
   if (a.N % 48 == 0) return launch<48>(a, s);

@@ -59,6 +59,7 @@ class GazeEngine(object):
         self._alloc()
         self.head_version = -1
         self.param_version = 0
+        self._prof = None             # list of (section, cuda event) while time_backward() runs
         self._state_dirty = False     # slab 0 (h_0, and c_0 for the LSTM) holds a caller-provided state
 
     # ------------------------------------------------------------------ parameters
@@ -473,6 +474,27 @@ class GazeEngine(object):
         a.D, a.dtype, a.engine = D, self.dtype, self.engine
         self.lib.rgp_wgrad(C.byref(a), self._s())
 
+    def _mark(self, name):
+        if self._prof is not None:
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record()
+            self._prof.append((name, ev))
+
+    def time_backward(self, iters=3, **opt):
+        """CUDA-event time (ms, mean of `iters`) of each section of backward() + optimizer_step()."""
+        acc = OrderedDict()
+        for _ in range(iters):
+            self._prof = []
+            self._mark("start")
+            self.backward()
+            self.optimizer_step(**opt)
+            self._mark("clip_adam")
+            torch.cuda.synchronize()
+            for (n0, e0), (n1, e1) in zip(self._prof[:-1], self._prof[1:]):
+                acc[n1] = acc.get(n1, 0.0) + e0.elapsed_time(e1) / iters
+            self._prof = None
+        return acc
+
     def backward(self):
         """Hand-written BPTT of the last forward(gt=...) (train=True): fills self.grads (flat, op layouts).
         dL/dlogits = (softmax - gt)/(B*T) was written by the fused softmax/loss kernel."""
@@ -500,16 +522,17 @@ class GazeEngine(object):
                                      g("out_W"), Ch, s)
             lib.rgp_reduce_sum(self.dlogits.data_ptr(), self.dlogits.numel(), g("out_b"), s)
             if self.use_bn:
-                for t in range(T):
-                    lib.rgp_bn_bwd(self._slab(self.dhs, t), self._slab(self.Hf, t + 1), g("bn_gamma") + t * Ch * 4,
-                                   g("bn_beta") + t * Ch * 4, alpha, B, G, Ch, s)
+                lib.rgp_bn_bwd_all(self.dhs.data_ptr(), self._slab(self.Hf, 1), g("bn_gamma"), g("bn_beta"), alpha,
+                                   B, T, G, Ch, s)
         else:
             for t in range(T):
                 lib.rgp_fc_head_bwd(self.dlogits.data_ptr(), self._slab(self.Hf, t + 1), self._ptr("out_W"),
                                     self._slab(self.dhs, t), g("out_W"), g("out_b"), B, T, t, G, Ch, s)
+        self._mark("head_bwd")
         # ---- transposed operand copies of the conv weights (dX = conv^T)
         lib.rgp_transpose_taps(self._ptr("Uc_op"), self.UcT.data_ptr(), 9, Ch, Ch, self.dtype, s)
         lib.rgp_transpose_taps(self._ptr("Uzr_op"), self.UzrT.data_ptr(), 9, 2 * Ch, Ch, self.dtype, s)
+        self._mark("weight_transposes")
         # ---- recurrence, backwards in time: two tap GEMMs per step (mirror of the forward)
         gam = (lambda t: self._ptr("bn_gamma") + t * Ch * 4) if self.use_bn else (lambda t: 0)
         lib.rgp_gru_bwd_last(self._slab(self.dhs, T - 1), gam(T - 1), alpha, self.Z[T - 1].data_ptr(),
@@ -528,6 +551,7 @@ class GazeEngine(object):
                            dhs=self._slab(self.dhs, t - 1), save_z=self.Z[t - 1].data_ptr(),
                            save_c=self.Cs[t - 1].data_ptr(), hprev_f32=self._slab(self.Hf, t - 1),
                            dg=self._slab(self.dG, t - 1), ldg=3 * Ch, **common, **extra)
+        self._mark("recurrence_bwd")
         # ---- weight gradients: contractions over all T*B*S rows at once
         rowsT = T * M
         self._wgrad(self.dG.data_ptr(), 3 * Ch, 0, 2 * Ch, self.Hop.data_ptr(), self.Hop.shape[0], Ch, Ch, rowsT,
@@ -536,6 +560,7 @@ class GazeEngine(object):
                     self.taps3, g("Uc_op"))
         self._wgrad(self.dG.data_ptr(), 3 * Ch, 0, 3 * Ch, self.Xp.data_ptr(), self.Xp.shape[0], Cin, Cin, rowsT,
                     self.taps3, g("Wx_op"))
+        self._mark("wgrad_cell")
         # ---- projection (only when the reference entry [B,T,1024,7,7] was used)
         if self.entry == "c3d":
             lib.rgp_transpose_taps(self._ptr("Wx_op"), self.WxT.data_ptr(), 9, 3 * Ch, Cin, self.dtype, s)
@@ -544,6 +569,7 @@ class GazeEngine(object):
             self._wgrad(self.dEmb.data_ptr(), Cin, 0, Cin, self.Apack.data_ptr(), self.Apack.shape[0], self.Cfeat,
                         self.Cfeat, T * B * P, [0], g("proj_W_op"))
             lib.rgp_colsum(self.dEmb.data_ptr(), Cin, T * B * P, Cin, g("proj_b"), self.dtype, s)
+        self._mark("proj_bwd")
 
     # ------------------------------------------------------------------ optimiser — base.py:262-297, gaze_rnn.py:435-444
     def learning_rate(self, lr0=1e-4, decay=0.8, decay_steps=500):

@@ -69,6 +69,7 @@ _SIGS = {
     "rgp_head_compose_bwd": [_vp] * 13 + [_i, _vp],
     "rgp_head_w123t": [_vp, _vp, _i, _i, _vp],
     "rgp_bn_bwd": [_vp, _vp, _vp, _vp, _f, _i, _i, _i, _vp],
+    "rgp_bn_bwd_all": [_vp, _vp, _vp, _vp, _f, _i, _i, _i, _i, _vp],
     "rgp_colsum": [_vp, _i, _i, _i, _vp, _i, _vp],
     "rgp_fc_head_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp],
     # saliency metrics (evaluation_metrics.py)

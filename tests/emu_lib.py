@@ -548,3 +548,11 @@ class EmuLib(object):
                 acc += float((np.diff(fp) * (tp[1:] + tp[:-1]) / 2.0).sum())
             au[f] = acc / nrep
         return 0
+
+    def rgp_bn_bwd_all(self, dhs, h, dgamma, dbeta, alpha, B, T, G, Ch, stream):
+        S = (G + 1) * (G + 1)
+        for t in range(T):
+            off = t * B * S * Ch * 4
+            self.rgp_bn_bwd(int(dhs) + off, int(h) + off, int(dgamma) + t * Ch * 4, int(dbeta) + t * Ch * 4, alpha, B, G,
+                            Ch, stream)
+        return 0

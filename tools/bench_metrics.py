@@ -1,0 +1,87 @@
+#!/usr/bin/env python
+"""Saliency-metric kernels at VAS scale (BASELINE config 5): N frames, 49x49 model maps scored against 360x480
+fixation maps.  Prints one JSON line: frames/s of the full suite, per-kernel CUDA-event time and achieved HBM GB/s
+(algorithmic bytes: float64 pred + gt, uint8 fix per pixel), and the NumPy oracle on a bounded sample beside it."""
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import numpy as np
+import torch
+
+from recurrent_gaze_prediction_b200 import evaluation_metrics as EM
+from recurrent_gaze_prediction_b200 import synthetic as SY
+
+
+def ev_time(fn, iters=5):
+    fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters
+
+
+def main():
+    N, H, W = int(os.environ.get("N", 1024)), 360, 480
+    rng = np.random.RandomState(0)
+    base, _ = SY.make_gazemaps(rng, 8, 8, 49, 49)
+    base = base.reshape(64, 49, 49)
+    gt = np.tile(base, (N // 64, 1, 1))
+    pred = (gt + 0.2 * rng.uniform(size=gt.shape)).astype(np.float32)
+    fix = np.tile(SY.make_fixationmaps(rng, base[:, None], H, W).reshape(64, H, W), (N // 64, 1, 1))
+    eng = EM.MetricsEngine(chunk=N)
+    dev = eng.device
+    p32, g32 = torch.from_numpy(pred).to(dev), torch.from_numpy(gt).to(dev)
+    fx = torch.from_numpy(fix).to(dev)
+    jit = torch.rand(N, H, W, dtype=torch.float64, device=dev)
+    nfix = fix.reshape(N, -1).sum(1)
+    maxfix = int(nfix.max())
+    idx = torch.from_numpy(np.stack([rng.randint(0, H * W, [maxfix, 100]) for _ in range(N)]).astype(np.int32)).to(dev)
+    hw = H * W
+    p64 = eng.to_f64(p32, True)
+    g64 = eng.to_f64(g32, False)
+    pr, gr = eng.resize(p64, (H, W)), eng.resize(g64, (H, W))
+    stats = eng.sim_cc_nss(pr, gr, fx)
+    res = {}
+    peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] if os.path.exists(
+        os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
+    cases = [
+        ("prep", lambda: eng.to_f64(p32, True), N * 49 * 49 * 12),
+        ("resize_bicubic(49->360x480)", lambda: eng.resize(p64, (H, W)), N * (49 * 49 * 8 + hw * 8)),
+        ("sim_cc_nss", lambda: eng.sim_cc_nss(pr, gr, fx), N * hw * 17),
+        ("auc_judd", lambda: eng.auc_judd(pr, fx, jit, maxfix), N * hw * 17),
+        ("auc_sampled(borji)", lambda: eng.auc_sampled(pr, fx, idx, stats[:, 3:], 8, 0.1, maxfix), N * (hw + maxfix * 100 * 12)),
+    ]
+    total = 0.0
+    for name, fn, nbytes in cases:
+        ms = ev_time(fn)
+        total += ms
+        res[name] = {"ms": ms, "GBps": nbytes / ms / 1e6, "frac_hbm": nbytes / ms / 1e6 / peak}
+    total += res["resize_bicubic(49->360x480)"]["ms"]        # gt is resized too
+    # NumPy oracle (the reference's algorithm, float64) on a bounded sample
+    from oracle import metrics_oracle as MO
+    ns = 4
+    t0 = time.perf_counter()
+    for i in range(ns):
+        jv = np.random.RandomState(i).rand(H, W)
+        ri = rng.randint(0, hw, [int(nfix[i]), 100])
+        for m, kw in (("sim", {}), ("cc", {}), ("NSS", {}), ("AUC_Judd", dict(jitter_values=jv)), ("AUC_Borji", dict(rand_index=ri))):
+            MO.saliency_score_single(m, pred[i].astype(np.float64), gt[i], fix[i], **kw)
+    cpu = ns / (time.perf_counter() - t0)
+    out = {"metric": "saliency metric suite frames/sec (sim, cc, NSS, AUC-Judd, AUC-Borji; 49x49 -> 360x480)",
+           "value": N / (total * 1e-3), "unit": "frames/s", "n_frames": N, "ms_total": total, "kernels": res,
+           "peak_hbm_GBps": peak, "dtype": "f64",
+           "cpu_baseline": {"value": cpu, "unit": "frames/s", "cores": 1, "kind": "port",
+                            "sample": "%d frames, oracle/metrics_oracle.py (NumPy float64, one process)" % ns}}
+    print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()
