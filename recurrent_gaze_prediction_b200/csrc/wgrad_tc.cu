@@ -7,11 +7,13 @@
 // exactly the canonical MN-major SW128 layout (8 m-rows = one 1024-byte swizzle atom), so Y and X are fed to
 // tcgen05.mma straight from their row-major HBM layout — no transposed copies.  A conv tap is a row shift of the X box.
 //
-// Work decomposition ("stream-K", split-major): the row range is cut into `splits` slabs small enough that a slab of
-// Y and X stays in the 126 MB L2; unit u = split * ntiles + tile, every unit is `kps` k-steps (64 rows each) long, and
-// the linear k-step space [0, units*kps) is dealt to the persistent CTAs in equal contiguous shares.  CTAs that run
-// at the same time therefore read the same slab (L2 hits) for different output tiles, and the load is balanced to
-// one k-step.  Partial tiles are added to D with red.global.add.v4.f32.
+// Work decomposition: the row range is cut into slabs; unit u = slab * ntiles + tile is `kps` k-steps (64 rows each)
+// long.  Units are dealt ROUND-ROBIN to the persistent CTAs (round r: CTA c owns unit r*grid + c), so the CTAs that run
+// at the same time work on neighbouring units = the same one or two row slabs, which are sized to stay in the 126 MB
+// L2 while all tiles and all taps consume them (a contiguous stream-K split of the whole space would spread the CTAs
+// over ALL slabs at once: measured 15x the algorithmic DRAM reads).  The units left over after the last whole round
+// are split stream-K style (equal contiguous k-step shares), so the load is balanced to one k-step.  Partial tiles
+// are added to D with red.global.add.v4.f32.
 //
 // Warp roles as in tapgemm_tc.cu: warp 0 TMA producer, warp 1 TMEM allocator + MMA issuer, warps 2..5 epilogue;
 // two TMEM accumulator stages so the flush of one segment overlaps the main loop of the next.
@@ -42,27 +44,48 @@ struct Sched {
   int ksteps_total; // ceil(M / KB)
   int ntiles;       // ntaps * tiles_i * tiles_j
   int tiles_j, tiles_ij;
+  int rounds;       // whole-unit rounds: in round r CTA c owns unit r*grid + c (neighbouring units = same row slab -> L2 hits)
+  long long tail0;  // first linear k-step index of the stream-K tail (= rounds*grid*kps)
   long long total;  // units * kps
-  long long per;    // k-steps per CTA
+  long long per;    // tail k-steps per CTA
 };
 
 struct Seg { int tile, kb, ke; };   // output tile, absolute k-step range [kb, ke)
 
-// next segment of this CTA's share starting at linear index g (< g1); advances g
-__device__ __forceinline__ Seg next_seg(const Sched& sc, long long& g, long long g1) {
-  const long long u = g / sc.kps;
-  const int k0 = (int)(g - u * sc.kps);
-  const int split = (int)(u / sc.ntiles);
-  Seg s;
-  s.tile = (int)(u - (long long)split * sc.ntiles);
-  long long len = sc.kps - k0;
-  if (len > g1 - g) len = g1 - g;
-  s.kb = split * sc.kps + k0;
-  s.ke = s.kb + (int)len;
-  if (s.ke > sc.ksteps_total) s.ke = sc.ksteps_total;   // the last split may be short: skipped steps do no work
-  g += len;
-  return s;
-}
+// Iterates the segments of one CTA: `rounds` whole units dealt round-robin, then an equal contiguous share of the
+// remaining units' k-steps (stream-K tail).  All three warp roles walk the identical sequence.
+struct SegIter {
+  int round;
+  long long g, g1;
+  __device__ __forceinline__ SegIter(const Sched& sc) {
+    round = 0;
+    g = sc.tail0 + (long long)blockIdx.x * sc.per;
+    g1 = g + sc.per;
+    if (g1 > sc.total) g1 = sc.total;
+  }
+  __device__ __forceinline__ bool next(const Sched& sc, Seg& s) {
+    long long lin, len;
+    if (round < sc.rounds) {
+      lin = ((long long)round * gridDim.x + blockIdx.x) * sc.kps;
+      len = sc.kps;
+      ++round;
+    } else {
+      if (g >= g1) return false;
+      lin = g;
+      len = sc.kps - (g % sc.kps);
+      if (len > g1 - g) len = g1 - g;
+      g += len;
+    }
+    const long long u = lin / sc.kps;
+    const int k0 = (int)(lin - u * sc.kps);
+    const int split = (int)(u / sc.ntiles);
+    s.tile = (int)(u - (long long)split * sc.ntiles);
+    s.kb = split * sc.kps + k0;
+    s.ke = s.kb + (int)len;
+    if (s.ke > sc.ksteps_total) s.ke = sc.ksteps_total;   // the last split may be short: skipped steps do no work
+    return true;
+  }
+};
 
 __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
@@ -83,10 +106,6 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const long long g0 = (long long)blockIdx.x * sc.per;
-  long long g1 = g0 + sc.per;
-  if (g1 > sc.total) g1 = sc.total;
-
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmY) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmX) : "memory");
@@ -109,8 +128,9 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
     // ===================== TMA producer =====================
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
-      for (long long g = g0; g < g1;) {
-        const Seg s = next_seg(sc, g, g1);
+      SegIter it(sc);
+      Seg s;
+      while (it.next(sc, s)) {
         const int tap = s.tile / sc.tiles_ij;
         const int rem = s.tile - tap * sc.tiles_ij;
         const int ti = rem / sc.tiles_j, tj = rem - ti * sc.tiles_j;
@@ -138,8 +158,9 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
     constexpr uint32_t kSbo = 1024;           // next 8 m-rows: the next swizzle atom
     int stage = 0; uint32_t phase = 0;
     int acc = 0; uint32_t accphase = 0;
-    for (long long g = g0; g < g1;) {
-      const Seg s = next_seg(sc, g, g1);
+    SegIter it(sc);
+    Seg s;
+    while (it.next(sc, s)) {
       if (s.kb >= s.ke) continue;
       mbar_wait(&tempty[acc], accphase ^ 1);
       tc_fence_after();
@@ -166,8 +187,9 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
     // ===================== epilogue: TMEM -> red.global.add into D =====================
     const int lg = warp & 3;
     int acc = 0; uint32_t accphase = 0;
-    for (long long g = g0; g < g1;) {
-      const Seg s = next_seg(sc, g, g1);
+    SegIter it(sc);
+    Seg s;
+    while (it.next(sc, s)) {
       if (s.kb >= s.ke) continue;
       const int tap = s.tile / sc.tiles_ij;
       const int rem = s.tile - tap * sc.tiles_ij;
@@ -224,18 +246,24 @@ int launch(const rgp_wgrad_args& a, cudaStream_t s) {
   sc.tiles_j = a.Nx / BN;
   sc.tiles_ij = ((a.Ny + BM - 1) / BM) * sc.tiles_j;
   sc.ntiles = a.ntaps * sc.tiles_ij;
-  // slab of rows whose Y and X columns (~48 MB) stay L2-resident while every tile of the split consumes them
-  long long slab_rows = 48ll * 1024 * 1024 / (2ll * (a.Ny + a.Nx));
+  // Row slabs: CTAs of one round work on ~grid/ntiles + 1 neighbouring slabs at the same time; size the slab so that
+  // this concurrent set of Y and X rows (~64 MB) stays in the 126 MB L2 while every tile (and every tap) consumes it.
+  const int nsm = num_sms();
+  const double concurrent = (double)nsm / sc.ntiles + 1.0;
+  long long slab_rows = (long long)(64.0 * 1024 * 1024 / (2.0 * (a.Ny + a.Nx) * concurrent));
   int kps = (int)(slab_rows / KB);
-  if (kps < 16) kps = 16;
+  if (kps < 32) kps = 32;
   if (kps > sc.ksteps_total) kps = sc.ksteps_total;
   const int splits = (sc.ksteps_total + kps - 1) / kps;
   sc.kps = (sc.ksteps_total + splits - 1) / splits;
-  sc.total = (long long)splits * sc.ntiles * sc.kps;
-  long long grid = num_sms();
-  if (grid > sc.total) grid = sc.total;
-  sc.per = (sc.total + grid - 1) / grid;
-  grid = (sc.total + sc.per - 1) / sc.per;
+  const long long units = (long long)splits * sc.ntiles;
+  sc.total = units * sc.kps;
+  long long grid = nsm;
+  if (grid > units) grid = units;
+  sc.rounds = (int)(units / grid);
+  sc.tail0 = (long long)sc.rounds * grid * sc.kps;
+  const long long tail = sc.total - sc.tail0;
+  sc.per = (tail + grid - 1) / grid;
   wgrad_tc_kernel<BN><<<(int)grid, NTHREADS, C::kSmemBytes, s>>>(tmY, tmX, a, sc);
   return check_launch("wgrad_tc");
 }
