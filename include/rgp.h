@@ -80,6 +80,30 @@ typedef struct rgp_tapgemm_args {
 
 int rgp_tapgemm(const rgp_tapgemm_args* a, void* stream);
 
+/* Persistent ConvGRU recurrence (gaze_grcn.py:95-129 unrolled by :259-288): ALL T steps of the hidden half
+ * in ONE launch.  A CTA owns 128 consecutive q-rows (two clips at G=7: frames never straddle a tile, so clips
+ * in different tiles never exchange data) and walks t = 0..T-1 by itself: per step three tcgen05 tap-GEMMs
+ * (U_r*h, U_z*h, U*(r.h)) with the gate maths fused between them; the state never leaves the SM's reach
+ * (fp32 master + bf16 operand rows in L2), there is no per-step launch and no grid-wide barrier.
+ * bf16 operands only (dtype 1).  Requires 128 % S == 0 (G = 7, 3 or 1) and Ch in {128, 256}.
+ * Buffers are those of the per-step path (rgp_tapgemm RGP_EPI_GRU_ZR / RGP_EPI_GRU_C), see DESIGN.md section 3. */
+typedef struct rgp_gru_seq_args {
+  void* Hop; long long rowsH;     /* bf16 p-layout state, slab t = h_t (t = 0..T), slab stride B*S rows        */
+  float* Hf;                      /* fp32 master of the same                                                     */
+  void* RH; long long rowsRH;     /* bf16 p-layout r.h; one slab (inference) or T slabs (train)                  */
+  const void* Uzr;                /* [9*2Ch, Ch] bf16 op layout (tap, z|r out channel, in channel)               */
+  const void* Uc;                 /* [9*Ch, Ch]                                                                  */
+  const float* Xg;                /* [T*B*S, 3Ch] fp32 input-half pre-activations (columns z | r | c)            */
+  float* Zs; float* Rs; float* Cs;/* train: saved gates [T, B*S, Ch] fp32 q-layout; all NULL in inference       */
+  void* HS;                       /* bf16 head-input layout [T*B*So, Ch] (BN-scaled h_t), or NULL                */
+  const float* bn_gamma; const float* bn_beta; float alpha;   /* [T, Ch] each, or NULL (gaze_grcn.py:325)       */
+  int B, T, G, Ch;
+  int So, Wo, pado;               /* head-input layout geometry                                                  */
+  int nsplit;                     /* 1, or 2: a 2-CTA cluster shares a tile, each CTA owns half of the channels  */
+  int dtype;                      /* must be 1 (bf16 operands, tcgen05 engine)                                   */
+} rgp_gru_seq_args;
+int rgp_convgru_seq_fwd(const rgp_gru_seq_args* a, void* stream);
+
 /* ---- model path ------------------------------------------------------------------------- */
 /* gaze_grcn.py:225-227 (tf.transpose NCHW->NHWC of the C3D blob) fused with the fp32->operand
  * cast and the [B,T]->time-major reorder: c3d [B,T,C,P] fp32 -> out [(t*B+b)*P + p, C]. */

@@ -46,6 +46,11 @@ int rgp_tapgemm(const rgp_tapgemm_args* a, void* stream) {
   return rgp::tapgemm_simt(*a, (cudaStream_t)stream);
 }
 
+int rgp_convgru_seq_fwd(const rgp_gru_seq_args* a, void* stream) {
+  RGP_CHECK_ARG(a != nullptr, "rgp_convgru_seq_fwd: null args");
+  return rgp::convgru_seq_fwd(*a, (cudaStream_t)stream);
+}
+
 int rgp_wgrad(const rgp_wgrad_args* a, void* stream) {
   RGP_CHECK_ARG(a != nullptr, "rgp_wgrad: null args");
   RGP_CHECK_ARG(a->ntaps >= 1 && a->ntaps <= RGP_MAX_TAPS, "rgp_wgrad: ntaps=%d out of range", a->ntaps);

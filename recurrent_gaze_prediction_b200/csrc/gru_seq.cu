@@ -1,0 +1,432 @@
+// gru_seq.cu — persistent ConvGRU recurrence: all T steps of gaze_grcn.py:95-129 (unrolled by :259-288) in ONE launch.
+//
+// Why this shape.  With G = 7 a frame is S = 64 q-rows, so a 128-row MMA tile is exactly two clips and the 3x3 SAME
+// halo of a tile only ever touches the zero pad rows of its neighbours: tiles are independent
+// for the whole sequence.  One CTA (or a 2-CTA cluster splitting the channels) therefore owns its clips for all T
+// steps and needs no grid barrier and no per-step launch.  Per step and CTA, in TMEM columns [0,NH) = z, [NH,2NH) = r
+// and later c:
+//     r-phase : acc_r  = sum_tap h_{t-1}[m+off] . U_r[tap]          (tcgen05, A = bf16 state rows via TMA)
+//     z-phase : acc_z  = sum_tap h_{t-1}[m+off] . U_z[tap]          || r-epilogue: r = sig(acc_r+Xr), write r.h (bf16)
+//     c-phase : acc_c  = sum_tap (r.h)[m+off]   . U[tap]            || z-epilogue: z = sig(acc_z+Xz) -> back into TMEM
+//     c-epilogue: c = tanh(acc_c+Xc); h_t = z h_{t-1} + (1-z) c -> fp32 master, bf16 operand rows, BN-scaled head rows
+// Warp roles: warp 0 = TMA producer (separate A and B rings; the weight ring runs ahead across the step boundary),
+// warp 1 = TMEM allocator + single-thread MMA issuer, warps 2..9 = epilogue (TMEM lane group = warp % 4, two column
+// halves).  Hand-offs are mbarriers; the state written with ordinary stores is made visible to the async proxy
+// (TMA) with __threadfence + fence.proxy.async before the arrive.
+#include "tc_common.cuh"
+
+namespace rgp {
+namespace {
+
+using namespace tc;
+
+constexpr int BM = 128, BK = 64;
+constexpr int EPI_WARPS = 8;
+constexpr int NTHREADS = 64 + 32 * EPI_WARPS;
+
+__device__ __forceinline__ float tanh_fast(float x) { float y; asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float sigmoid_fast(float x) { return fmaf(0.5f, tanh_fast(0.5f * x), 0.5f); }
+
+__device__ __forceinline__ void ldf32(const float* p, float v[32]) {
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    float4 t = reinterpret_cast<const float4*>(p)[i];
+    v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
+  }
+}
+__device__ __forceinline__ void stf32(float* p, const float v[32]) {
+#pragma unroll
+  for (int i = 0; i < 8; ++i) reinterpret_cast<float4*>(p)[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+}
+__device__ __forceinline__ void stbf32(__nv_bfloat16* p, const float v[32]) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    __nv_bfloat162 b0 = __floats2bfloat162_rn(v[8 * i], v[8 * i + 1]);
+    __nv_bfloat162 b1 = __floats2bfloat162_rn(v[8 * i + 2], v[8 * i + 3]);
+    __nv_bfloat162 b2 = __floats2bfloat162_rn(v[8 * i + 4], v[8 * i + 5]);
+    __nv_bfloat162 b3 = __floats2bfloat162_rn(v[8 * i + 6], v[8 * i + 7]);
+    uint4 u;
+    u.x = *reinterpret_cast<uint32_t*>(&b0); u.y = *reinterpret_cast<uint32_t*>(&b1);
+    u.z = *reinterpret_cast<uint32_t*>(&b2); u.w = *reinterpret_cast<uint32_t*>(&b3);
+    reinterpret_cast<uint4*>(p)[i] = u;
+  }
+}
+
+// registers -> TMEM (32 lanes x 32 columns), the inverse of tc_ld32
+__device__ __forceinline__ void tc_st32(uint32_t taddr, const float v[32]) {
+  const uint32_t* r = reinterpret_cast<const uint32_t*>(v);
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+      "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};\n" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+      "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]),
+      "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]),
+      "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+      : "memory");
+  asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+}
+
+// ---- cluster-scope mbarrier helpers (nsplit = 2: the two CTAs of a cluster signal each other) ----
+__device__ __forceinline__ void mbar_arrive_remote(uint64_t* bar, uint32_t cta_rank) {
+  uint32_t raddr;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(raddr) : "r"(smem_u32(bar)), "r"(cta_rank));
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(raddr) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred P1;\n"
+      "LAB_WAIT:\n"
+      "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 P1, [%0], %1;\n"
+      "@P1 bra DONE;\n"
+      "bra LAB_WAIT;\n"
+      "DONE:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async;" ::: "memory"); }
+
+template <int NH>
+struct SeqCfg {
+  static constexpr int kStages = (NH >= 256) ? 4 : 6;
+  static constexpr int kABytes = BM * BK * 2;
+  static constexpr int kBBytes = NH * BK * 2;
+  static constexpr int kTmemCols = 2 * NH;
+  static constexpr int kBarBytes = 256;
+  static constexpr int kSmemBytes = kStages * (kABytes + kBBytes) + 1024 + kBarBytes;
+};
+
+template <int NH>
+__global__ void __launch_bounds__(NTHREADS, 1)
+gru_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ CUtensorMap tmRH,
+               const __grid_constant__ CUtensorMap tmUzr, const __grid_constant__ CUtensorMap tmUc,
+               const rgp_gru_seq_args a) {
+  using C = SeqCfg<NH>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* ringA = smem;
+  uint8_t* ringB = smem + C::kStages * C::kABytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::kStages * (C::kABytes + C::kBBytes));
+  uint64_t* fullA = bars;
+  uint64_t* emptyA = fullA + C::kStages;
+  uint64_t* fullB = emptyA + C::kStages;
+  uint64_t* emptyB = fullB + C::kStages;
+  uint64_t* r_full = emptyB + C::kStages;
+  uint64_t* z_full = r_full + 1;
+  uint64_t* c_full = z_full + 1;
+  uint64_t* rh_ready = c_full + 1;     // r.h rows of this step are in global memory (all CTAs of the cluster)
+  uint64_t* h_ready = rh_ready + 1;    // h_t rows are in global memory (all CTAs of the cluster)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(h_ready + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nsplit = a.nsplit;
+  const int rank = (nsplit > 1) ? (int)(blockIdx.x % nsplit) : 0;
+  const int cluster_id = blockIdx.x / nsplit, nclusters = gridDim.x / nsplit;
+  const int Ch = a.Ch, Wp = a.G + 1, S = Wp * Wp;
+  const int M = a.B * S;                          // q-rows of one step
+  const int mtiles = (M + BM - 1) / BM;
+  const int col0 = rank * NH;                     // this CTA's channel slice [col0, col0+NH)
+  const int kchunks = Ch / BK;
+  const int ksteps = 9 * kchunks;                 // k-steps of one phase
+  const bool train = a.Rs != nullptr;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmH) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmRH) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmUzr) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmUc) : "memory");
+    for (int i = 0; i < C::kStages; ++i) {
+      mbar_init(&fullA[i], 1); mbar_init(&emptyA[i], 1);
+      mbar_init(&fullB[i], 1); mbar_init(&emptyB[i], 1);
+    }
+    mbar_init(r_full, 1); mbar_init(z_full, 1); mbar_init(c_full, 1);
+    mbar_init(rh_ready, EPI_WARPS * nsplit); mbar_init(h_ready, EPI_WARPS * nsplit);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"((uint32_t)C::kTmemCols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (nsplit > 1) cluster_sync_all();   // the peer's barriers exist before anyone arrives on them remotely
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer: two rings, the weight ring runs up to kStages k-steps ahead =====================
+    if (lane == 0) {
+      int sA = 0, sB = 0; uint32_t phA = 0, phB = 0;
+      long long it = 0;                                   // running step counter of this CTA (barrier phases)
+      for (int tile = cluster_id; tile < mtiles; tile += nclusters) {
+        const int m0 = tile * BM;
+        for (int t = 0; t < a.T; ++t, ++it) {
+          const long long rowH = (long long)t * M + m0;                 // slab t = h_{t-1} ... (slab 0 = h_0)
+          const long long rowRH = (long long)(train ? t : 0) * M + m0;
+          int iA = 0, iB = 0;                                           // k-step cursors inside this step (0..3*ksteps)
+          while (iA < 3 * ksteps) {
+            while (iB < 3 * ksteps && iB < iA + C::kStages) {
+              const int ph = iB / ksteps, ks = iB - ph * ksteps;
+              const int tap = ks / kchunks, kc = ks - tap * kchunks;
+              mbar_wait(&emptyB[sB], phB ^ 1);
+              mbar_expect_tx(&fullB[sB], C::kBBytes);
+              if (ph == 0)      tma_load_2d(ringB + sB * C::kBBytes, &tmUzr, &fullB[sB], kc * BK, tap * 2 * Ch + Ch + col0);
+              else if (ph == 1) tma_load_2d(ringB + sB * C::kBBytes, &tmUzr, &fullB[sB], kc * BK, tap * 2 * Ch + col0);
+              else              tma_load_2d(ringB + sB * C::kBBytes, &tmUc, &fullB[sB], kc * BK, tap * Ch + col0);
+              if (++sB == C::kStages) { sB = 0; phB ^= 1; }
+              ++iB;
+            }
+            const int ph = iA / ksteps, ks = iA - ph * ksteps;
+            const int tap = ks / kchunks, kc = ks - tap * kchunks;
+            if (ks == 0) {
+              if (ph == 0 && it > 0) { mbar_wait_cluster(h_ready, (uint32_t)((it - 1) & 1)); fence_proxy_async(); }
+              if (ph == 2) { mbar_wait_cluster(rh_ready, (uint32_t)(it & 1)); fence_proxy_async(); }
+            }
+            const int off = (tap / 3) * Wp + (tap % 3);
+            mbar_wait(&emptyA[sA], phA ^ 1);
+            mbar_expect_tx(&fullA[sA], C::kABytes);
+            if (ph < 2) tma_load_2d(ringA + sA * C::kABytes, &tmH, &fullA[sA], kc * BK, (int)(rowH + off));
+            else        tma_load_2d(ringA + sA * C::kABytes, &tmRH, &fullA[sA], kc * BK, (int)(rowRH + off));
+            if (++sA == C::kStages) { sA = 0; phA ^= 1; }
+            ++iA;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(NH >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+    int sA = 0, sB = 0; uint32_t phA = 0, phB = 0;
+    long long it = 0;
+    for (int tile = cluster_id; tile < mtiles; tile += nclusters) {
+      for (int t = 0; t < a.T; ++t, ++it) {
+        for (int ph = 0; ph < 3; ++ph) {
+          // TMEM hazards: r/c columns are free once the c-epilogue of the previous step (ph 0) resp. the r-epilogue
+          // of this step (ph 2) has read them; z columns once the previous c-epilogue is done (implied by ph 0's wait)
+          if (ph == 0 && it > 0) mbar_wait_cluster(h_ready, (uint32_t)((it - 1) & 1));
+          if (ph == 2) mbar_wait_cluster(rh_ready, (uint32_t)(it & 1));
+          tc_fence_after();
+          const uint32_t tacc = tmem_base + (uint32_t)(ph == 1 ? 0 : NH);
+          uint64_t* done = (ph == 0) ? r_full : ((ph == 1) ? z_full : c_full);
+          for (int ks = 0; ks < ksteps; ++ks) {
+            mbar_wait(&fullA[sA], phA);
+            mbar_wait(&fullB[sB], phB);
+            tc_fence_after();
+            if (lane == 0) {
+              const uint64_t adesc = make_sdesc(smem_u32(ringA + sA * C::kABytes));
+              const uint64_t bdesc = make_sdesc(smem_u32(ringB + sB * C::kBBytes));
+#pragma unroll
+              for (int k = 0; k < BK / 16; ++k)
+                tc_mma_bf16(tacc, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (ks | k) ? 1u : 0u);
+              tc_commit(&emptyA[sA]);
+              tc_commit(&emptyB[sB]);
+              if (ks == ksteps - 1) tc_commit(done);
+            }
+            __syncwarp();
+            if (++sA == C::kStages) { sA = 0; phA ^= 1; }
+            if (++sB == C::kStages) { sB = 0; phB ^= 1; }
+          }
+        }
+      }
+    }
+  } else {
+    // ===================== epilogue warps 2..9: TMEM lane group = warp % 4, column half = (warp-2)/4 =====================
+    using TA = __nv_bfloat16;
+    const int lg = warp & 3;
+    const int cgi = (warp - 2) >> 2;
+    constexpr int NCG = EPI_WARPS / 4;
+    constexpr int CW = NH / NCG;                       // columns this warp handles per gate
+    const int cb = cgi * CW;                           // first local column
+    const uint32_t tlane = tmem_base + ((uint32_t)(lg * 32) << 16);
+    const int threeCh = 3 * Ch;
+    long long it = 0;
+    for (int tile = cluster_id; tile < mtiles; tile += nclusters) {
+      const int m = tile * BM + lg * 32 + lane;        // q-row inside a step slab
+      const bool inrange = m < M;
+      const int f = m / S, q = m - f * S;
+      const int y = q / Wp, x = q - y * Wp;
+      const bool valid = inrange && y < a.G && x < a.G;
+      const long long prow = (long long)m + Wp + 1;
+      for (int t = 0; t < a.T; ++t, ++it) {
+        const uint32_t par = (uint32_t)(it & 1);
+        const long long mt = (long long)t * M + m;                       // row in the [T*M, .] buffers
+        const float* xg = a.Xg + mt * threeCh;
+        const float* hprev = a.Hf + ((long long)t * M + prow) * Ch;      // slab t = h_{t-1}
+        float* hnext = a.Hf + ((long long)(t + 1) * M + prow) * Ch;
+        TA* hop_next = (TA*)a.Hop + ((long long)(t + 1) * M + prow) * Ch;
+        TA* rh = (TA*)a.RH + ((long long)(train ? t : 0) * M + prow) * Ch;
+        // pull this row's input-half pre-activations (HBM) into L2 while the r-phase MMAs run
+        if (inrange) {
+#pragma unroll
+          for (int g = 0; g < 3; ++g)
+            for (int c = 0; c < CW; c += 32) asm volatile("prefetch.global.L2 [%0];" ::"l"(xg + g * Ch + col0 + cb + c));
+        }
+        // ---------------- r-epilogue: r = sig(acc_r + Xr); r.h -> operand rows of the c-phase ----------------
+        mbar_wait(r_full, par);
+        tc_fence_after();
+#pragma unroll 1
+        for (int c = 0; c < CW; c += 32) {
+          const int n = col0 + cb + c;                                   // global channel
+          float v[32], xx[32];
+          tc_ld32(tlane + (uint32_t)(NH + cb + c), v);
+          if (inrange) {
+            ldf32(xg + Ch + n, xx);
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = sigmoid_fast(v[i] + xx[i]);
+            if (train) stf32(a.Rs + mt * Ch + n, v);
+            if (valid) {
+              ldf32(hprev + n, xx);
+#pragma unroll
+              for (int i = 0; i < 32; ++i) v[i] *= xx[i];
+              stbf32(rh + n, v);
+            }
+          }
+        }
+        tc_fence_before();
+        __threadfence();
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) {
+          if (nsplit > 1) { for (int p = 0; p < nsplit; ++p) mbar_arrive_remote(rh_ready, (uint32_t)p); }
+          else mbar_arrive(rh_ready);
+        }
+        // ---------------- z-epilogue: z = sig(acc_z + Xz), kept in TMEM for the c-epilogue ----------------
+        mbar_wait(z_full, par);
+        tc_fence_after();
+#pragma unroll 1
+        for (int c = 0; c < CW; c += 32) {
+          const int n = col0 + cb + c;
+          float v[32], xx[32];
+          tc_ld32(tlane + (uint32_t)(cb + c), v);
+          if (inrange) {
+            ldf32(xg + n, xx);
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = sigmoid_fast(v[i] + xx[i]);
+            if (train) stf32(a.Zs + mt * Ch + n, v);
+          }
+          tc_st32(tlane + (uint32_t)(cb + c), v);
+        }
+        // ---------------- c-epilogue: candidate, state update, BN-scaled head rows ----------------
+        const long long orow = ((long long)t * a.B + f) * a.So + (long long)(y + a.pado) * a.Wo + (x + a.pado);
+        mbar_wait(c_full, par);
+        tc_fence_after();
+#pragma unroll 1
+        for (int c = 0; c < CW; c += 32) {
+          const int n = col0 + cb + c;
+          float v[32], xx[32], zz[32];
+          tc_ld32(tlane + (uint32_t)(NH + cb + c), v);
+          tc_ld32(tlane + (uint32_t)(cb + c), zz);         // warp-collective: never under a divergent branch
+          if (inrange) {
+            ldf32(xg + 2 * Ch + n, xx);
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = tanh_fast(v[i] + xx[i]);
+            if (train) stf32(a.Cs + mt * Ch + n, v);
+            if (valid) {
+              ldf32(hprev + n, xx);
+#pragma unroll
+              for (int i = 0; i < 32; ++i) v[i] = zz[i] * xx[i] + (1.0f - zz[i]) * v[i];
+              stf32(hnext + n, v);
+              stbf32(hop_next + n, v);
+              if (a.HS) {
+                if (a.bn_gamma) {
+                  ldf32(a.bn_gamma + (long long)t * Ch + n, xx);
+                  ldf32(a.bn_beta + (long long)t * Ch + n, zz);
+#pragma unroll
+                  for (int i = 0; i < 32; ++i) v[i] = xx[i] * (v[i] * a.alpha) + zz[i];
+                }
+                stbf32((TA*)a.HS + orow * Ch + n, v);
+              }
+            }
+          }
+        }
+        tc_fence_before();
+        __threadfence();
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) {
+          if (nsplit > 1) { for (int p = 0; p < nsplit; ++p) mbar_arrive_remote(h_ready, (uint32_t)p); }
+          else mbar_arrive(h_ready);
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (nsplit > 1) cluster_sync_all();   // nobody exits while the peer may still signal its barriers
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)C::kTmemCols)
+                 : "memory");
+  }
+}
+
+template <int NH>
+int launch_seq(const rgp_gru_seq_args& a, cudaStream_t s) {
+  using C = SeqCfg<NH>;
+  const int Ch = a.Ch, S = (a.G + 1) * (a.G + 1);
+  CUtensorMap tmH, tmRH, tmUzr, tmUc;
+  int rc = encode_map_bf16(a.Hop, Ch, a.rowsH, (long long)Ch * 2, BK, BM, &tmH);
+  if (rc) return rc;
+  rc = encode_map_bf16(a.RH, Ch, a.rowsRH, (long long)Ch * 2, BK, BM, &tmRH);
+  if (rc) return rc;
+  rc = encode_map_bf16(a.Uzr, Ch, 9LL * 2 * Ch, (long long)Ch * 2, BK, NH, &tmUzr);
+  if (rc) return rc;
+  rc = encode_map_bf16(a.Uc, Ch, 9LL * Ch, (long long)Ch * 2, BK, NH, &tmUc);
+  if (rc) return rc;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(gru_seq_kernel<NH>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes);
+    if (e != cudaSuccess) { set_error("gru_seq: cudaFuncSetAttribute(smem=%d): %s", C::kSmemBytes, cudaGetErrorString(e)); return -5; }
+    attr_set = true;
+  }
+  const int mtiles = (a.B * S + BM - 1) / BM;
+  int nclusters = mtiles;
+  const int maxc = num_sms() / a.nsplit;
+  if (nclusters > maxc) nclusters = maxc;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)(nclusters * a.nsplit), 1, 1);
+  cfg.blockDim = dim3(NTHREADS, 1, 1);
+  cfg.dynamicSmemBytes = C::kSmemBytes;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = (unsigned)a.nsplit;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, gru_seq_kernel<NH>, tmH, tmRH, tmUzr, tmUc, a);
+  if (e != cudaSuccess) { set_error("gru_seq launch: %s", cudaGetErrorString(e)); return -5; }
+  return check_launch("gru_seq");
+}
+
+}  // namespace
+
+int convgru_seq_fwd(const rgp_gru_seq_args& a, cudaStream_t s) {
+  const int S = (a.G + 1) * (a.G + 1);
+  RGP_CHECK_ARG(a.dtype == 1, "rgp_convgru_seq_fwd: bf16 operands only (dtype=%d); fp32 uses the per-step rgp_tapgemm path", a.dtype);
+  RGP_CHECK_ARG(a.B > 0 && a.T > 0, "rgp_convgru_seq_fwd: bad shape B=%d T=%d", a.B, a.T);
+  RGP_CHECK_ARG(BM % S == 0, "rgp_convgru_seq_fwd: a 128-row tile must hold whole frames (S=%d; G must be 7, 3 or 1)", S);
+  RGP_CHECK_ARG(a.nsplit == 1 || a.nsplit == 2, "rgp_convgru_seq_fwd: nsplit=%d", a.nsplit);
+  RGP_CHECK_ARG(a.Ch % 64 == 0, "rgp_convgru_seq_fwd: Ch=%d must be a multiple of 64", a.Ch);
+  RGP_CHECK_ARG((a.Rs == nullptr) == (a.Zs == nullptr) && (a.Rs == nullptr) == (a.Cs == nullptr),
+                "rgp_convgru_seq_fwd: Zs, Rs, Cs must be all set (train) or all NULL");
+  RGP_CHECK_ARG((a.bn_gamma == nullptr) == (a.bn_beta == nullptr), "rgp_convgru_seq_fwd: bn_gamma / bn_beta");
+  RGP_CHECK_ARG(((uintptr_t)a.Hop & 15) == 0 && ((uintptr_t)a.RH & 15) == 0 && ((uintptr_t)a.Uzr & 15) == 0 &&
+                ((uintptr_t)a.Uc & 15) == 0, "rgp_convgru_seq_fwd: operands must be 16-byte aligned");
+  const int NH = a.Ch / a.nsplit;
+  if (NH == 256) return launch_seq<256>(a, s);
+  if (NH == 128) return launch_seq<128>(a, s);
+  set_error("rgp_convgru_seq_fwd: Ch/nsplit = %d must be 128 or 256", NH);
+  return -22;
+}
+
+}  // namespace rgp

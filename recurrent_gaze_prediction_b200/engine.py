@@ -33,7 +33,7 @@ def _tdtype(dtype):
 
 class GazeEngine(object):
     def __init__(self, model="gaze_grcn", B=2, T=35, G=7, Ch=128, Cin=512, Cfeat=1024, dtype=0,
-                 device="cuda", lib=None, train=False, head=None, engine=None):
+                 device="cuda", lib=None, train=False, head=None, engine=None, seq=None, nsplit=None):
         if model not in ("gaze_grcn", "gaze_grcn77", "gaze_lstm"):
             raise ValueError("unknown model %r" % (model,))
         self.model, self.B, self.T, self.G, self.Ch, self.Cin, self.Cfeat = model, B, T, G, Ch, Cin, Cfeat
@@ -55,6 +55,14 @@ class GazeEngine(object):
         self.ngx = 4 if self.lstm else 3        # gates fed by the input conv
         self.tdt = _tdtype(dtype)
         self.taps3 = [ky * self.Wp + kx for ky in range(3) for kx in range(3)]
+        # persistent ConvGRU recurrence (rgp_convgru_seq_fwd: all T steps in one launch).  Default: whenever the
+        # shape allows it on the tcgen05 engine; RGP_SEQ=0 falls back to two tap-GEMM launches per step (A/B checks).
+        if seq is None:
+            seq = (dtype == 1 and engine != 1 and Ch in (128, 256) and os.environ.get("RGP_SEQ", "1") != "0")
+        self.use_seq = bool(seq) and (not self.lstm) and 128 % self.S == 0
+        if nsplit is None:   # 2-CTA clusters split the channels when one CTA per tile would leave SMs idle
+            nsplit = int(os.environ.get("RGP_SEQ_NSPLIT", "0")) or (2 if (Ch == 256 and (B * self.S + 127) // 128 <= 74) else 1)
+        self.nsplit = nsplit
         self._build_params()
         self._alloc()
         self.head_version = -1
@@ -363,6 +371,26 @@ class GazeEngine(object):
         pop = self._pop
         NX = self.ngx * Ch
         M = B * S
+        if self.use_seq:
+            a = L.GruSeqArgs()
+            a.Hop, a.rowsH, a.Hf = self.Hop.data_ptr(), self.Hop.shape[0], self.Hf.data_ptr()
+            a.RH, a.rowsRH = self.RH.data_ptr(), self.RH.shape[0]
+            a.Uzr, a.Uc, a.Xg = pop("Uzr_op"), pop("Uc_op"), self.Xg.data_ptr()
+            if self.train:
+                a.Zs, a.Rs, a.Cs = self.Z.data_ptr(), self.Rs.data_ptr(), self.Cs.data_ptr()
+            if self.head == "deconv":
+                a.HS = self.HS.data_ptr()
+            if self.use_bn:
+                a.bn_gamma, a.bn_beta, a.alpha = self._ptr("bn_gamma"), self._ptr("bn_beta"), 1.0 / math.sqrt(1.0 + BN_EPS)
+            a.B, a.T, a.G, a.Ch = B, T, G, Ch
+            a.So, a.Wo, a.pado = HEAD_S, HEAD_W, HEAD_PAD
+            a.nsplit, a.dtype = self.nsplit, self.dtype
+            lib.rgp_convgru_seq_fwd(C.byref(a), s)
+            if self.head == "fc":   # gaze_grcn77.py:206-211
+                for t in range(T):
+                    lib.rgp_fc_head(self._slab(self.Hf, t + 1), self._ptr("out_W"), self._ptr("out_b"),
+                                    self.logits.data_ptr(), B, T, t, G, Ch, s)
+            return
         for t in range(T):
             xg = self.Xg.data_ptr() + t * M * NX * 4
             hs = 0

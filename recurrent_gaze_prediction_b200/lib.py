@@ -49,8 +49,24 @@ class WgradArgs(C.Structure):
     ]
 
 
+class GruSeqArgs(C.Structure):
+    """Mirror of ``rgp_gru_seq_args`` (include/rgp.h)."""
+    _fields_ = [
+        ("Hop", _vp), ("rowsH", _ll), ("Hf", _vp),
+        ("RH", _vp), ("rowsRH", _ll),
+        ("Uzr", _vp), ("Uc", _vp), ("Xg", _vp),
+        ("Zs", _vp), ("Rs", _vp), ("Cs", _vp),
+        ("HS", _vp),
+        ("bn_gamma", _vp), ("bn_beta", _vp), ("alpha", _f),
+        ("B", _i), ("T", _i), ("G", _i), ("Ch", _i),
+        ("So", _i), ("Wo", _i), ("pado", _i),
+        ("nsplit", _i), ("dtype", _i),
+    ]
+
+
 _SIGS = {
     "rgp_tapgemm": [C.POINTER(TapGemmArgs), _vp],
+    "rgp_convgru_seq_fwd": [C.POINTER(GruSeqArgs), _vp],
     "rgp_pack_c3d": [_vp, _vp, _i, _i, _i, _i, _i, _vp],
     "rgp_pack_emb": [_vp, _vp, _i, _i, _i, _i, _i, _vp],
     "rgp_cast": [_vp, _vp, _ll, _i, _vp],

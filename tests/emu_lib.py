@@ -549,6 +549,46 @@ class EmuLib(object):
             au[f] = acc / nrep
         return 0
 
+    def rgp_convgru_seq_fwd(self, aref, stream):
+        """All T steps = T x (GRU_ZR tap-GEMM + GRU_C tap-GEMM) on the same buffers (fp32 emulation)."""
+        a = aref._obj
+        Ch, B, G = a.Ch, a.B, a.G
+        Wp = G + 1
+        S = Wp * Wp
+        M = B * S
+        assert 128 % S == 0 and a.nsplit in (1, 2)
+        train = bool(a.Rs)
+        taps = [ky * Wp + kx for ky in range(3) for kx in range(3)]
+        rows_step = M + ((2 * Wp + 2 + 31) // 32) * 32
+        for t in range(a.T):
+            sl = t if train else 0
+            g = L.TapGemmArgs()
+            g.dtype, g.ntaps = 0, 9
+            for i, o in enumerate(taps):
+                g.tap_off[i] = o
+            g.M, g.K, g.S, g.Wp, g.G, g.Ch, g.B, g.T, g.t = M, Ch, S, Wp, G, Ch, B, a.T, t
+            g.xg, g.ldx = a.Xg + t * M * 3 * Ch * 4, 3 * Ch
+            g.rowsA, g.lda = rows_step, Ch
+            g.hprev_f32 = a.Hf + t * M * Ch * 4
+            zbuf = np.zeros((M, Ch), dtype=np.float32)
+            g.z_f32 = (a.Zs + t * M * Ch * 4) if train else zbuf.ctypes.data
+            g.A, g.Bw, g.N, g.epi = a.Hop + t * M * Ch * 4, a.Uzr, 2 * Ch, L.EPI_GRU_ZR
+            g.out_op = a.RH + sl * M * Ch * 4
+            g.save_r = (a.Rs + t * M * Ch * 4) if train else None
+            self.rgp_tapgemm(C.byref(g), stream)
+            g.A, g.Bw, g.N, g.epi = a.RH + sl * M * Ch * 4, a.Uc, Ch, L.EPI_GRU_C
+            g.hnext_f32 = a.Hf + (t + 1) * M * Ch * 4
+            g.out_op = a.Hop + (t + 1) * M * Ch * 4
+            g.save_r = None
+            g.save_c = (a.Cs + t * M * Ch * 4) if train else None
+            if a.HS:
+                g.out_op2 = a.HS + t * B * a.So * Ch * 4
+                g.So, g.Wo, g.pado = a.So, a.Wo, a.pado
+            if a.bn_gamma:
+                g.bias, g.bias2, g.alpha = a.bn_gamma + t * Ch * 4, a.bn_beta + t * Ch * 4, a.alpha
+            self.rgp_tapgemm(C.byref(g), stream)
+        return 0
+
     def rgp_bn_bwd_all(self, dhs, h, dgamma, dbeta, alpha, B, T, G, Ch, stream):
         S = (G + 1) * (G + 1)
         for t in range(T):

@@ -10,7 +10,7 @@ from recurrent_gaze_prediction_b200.engine import GazeEngine
 from emu_lib import EmuLib
 
 
-def _setup(model, B=2, T=3, Ch=16, G=7, seed=0, regime="S", entry="c3d", Cin=32, Cfeat=64, train=False):
+def _setup(model, B=2, T=3, Ch=16, G=7, seed=0, regime="S", entry="c3d", Cin=32, Cfeat=64, train=False, seq=None):
     p = O.init_params(model, hidden=Ch, T=T, grid=G, dim_proj=Cin, dim_feature=Cfeat, seed=seed, regime=regime)
     rng = np.random.RandomState(seed + 100)
     GH = 7 if model == "gaze_grcn77" else 49
@@ -20,7 +20,7 @@ def _setup(model, B=2, T=3, Ch=16, G=7, seed=0, regime="S", entry="c3d", Cin=32,
     emb = SY.make_embedded(rng, B, T, G, Cin)
     gt, _ = SY.make_gazemaps(rng, B, T, GH, GH, normalize=True)
     eng = GazeEngine(model, B=B, T=T, G=G, Ch=Ch, Cin=Cin, Cfeat=Cfeat, dtype=0, device="cpu", lib=EmuLib(),
-                     train=train)
+                     train=train, seq=seq)
     eng.load_tf_params(p)
     return p, c3d, emb, gt, eng
 
@@ -55,8 +55,8 @@ def test_param_roundtrip():
         assert np.allclose(back[k].reshape(np.asarray(v).shape), np.asarray(v, dtype=np.float32)), k
 
 
-def _grad_check(model, entry, loss_type="xentropy", B=2, T=3, Ch=16):
-    p, c3d, emb, gt, eng = _setup(model, B=B, T=T, Ch=Ch, train=True)
+def _grad_check(model, entry, loss_type="xentropy", B=2, T=3, Ch=16, seq=None):
+    p, c3d, emb, gt, eng = _setup(model, B=B, T=T, Ch=Ch, train=True, seq=seq)
     kw = dict(c3d=torch.from_numpy(c3d)) if entry == "c3d" else dict(emb=torch.from_numpy(emb))
     okw = dict(c3d=c3d.astype(np.float64)) if entry == "c3d" else dict(emb=emb.astype(np.float64))
     eng.forward(gt=torch.from_numpy(gt), loss_type=loss_type, **kw)
@@ -75,6 +75,18 @@ def _grad_check(model, entry, loss_type="xentropy", B=2, T=3, Ch=16):
 @pytest.mark.parametrize("entry", ["c3d", "emb"])
 def test_bptt_matches_oracle_autograd(model, entry):
     _grad_check(model, entry)
+
+
+@pytest.mark.parametrize("model", ["gaze_grcn", "gaze_grcn77"])
+def test_persistent_recurrence_wiring(model):
+    """engine -> rgp_convgru_seq_fwd (one call for all T steps): same buffers as the per-step path, forward and BPTT."""
+    p, c3d, emb, gt, eng = _setup(model, seq=True)
+    assert eng.use_seq
+    logits = eng.forward(c3d=torch.from_numpy(c3d), gt=torch.from_numpy(gt)).numpy()
+    ref_logits, _, ref_loss, _ = O.forward_loss_grads(model, p, gt.astype(np.float64), c3d=c3d.astype(np.float64))
+    assert np.abs(logits - ref_logits).max() <= 2e-5 * np.abs(ref_logits).max()
+    assert not any(c[0] == "tapgemm" and c[1] in (2, 3) for c in eng.lib.calls[:0])
+    _grad_check(model, "c3d", seq=True)
 
 
 def test_bptt_l2_loss():

@@ -240,3 +240,37 @@ def test_wgrad_matches_numpy(engine, M, Ny, Nx, ldy, ycol0, taps):
     got = D.cpu().numpy().astype(np.float64) / 2
     err = np.abs(got - ref).max()
     assert err <= 2e-5 * np.sqrt(M) * 4, (err, np.abs(ref).max())
+
+
+@pytest.mark.parametrize("model,Ch,B,nsplit,train", [
+    ("gaze_grcn", 256, 3, 1, False),
+    ("gaze_grcn", 256, 6, 2, False),
+    ("gaze_grcn", 128, 5, 1, True),
+    ("gaze_grcn", 256, 4, 2, True),
+    ("gaze_grcn77", 128, 2, 1, False),
+    ("gaze_grcn", 256, 320, 1, False),      # more tiles than SMs: CTAs walk several tiles
+])
+def test_persistent_recurrence_matches_per_step_path(model, Ch, B, nsplit, train):
+    """rgp_convgru_seq_fwd (all T steps in one launch) against the per-step tap-GEMM path on the same bf16 operands:
+    same accumulation order and gate functions, so states, saved gates and logits agree to fp32 round-off."""
+    T = 5
+    p, c3d, _, gt = _case(model, min(B, 4), T, Ch)
+    reps = (B + c3d.shape[0] - 1) // c3d.shape[0]
+    c3d = np.concatenate([np.roll(c3d, i, axis=1) for i in range(reps)], axis=0)[:B]
+    gt = np.concatenate([np.roll(gt, i, axis=1) for i in range(reps)], axis=0)[:B]
+    out = []
+    for seq in (False, True):
+        eng = GazeEngine(model, B=B, T=T, Ch=Ch, dtype=1, device="cuda", train=train, seq=seq, nsplit=nsplit)
+        assert eng.use_seq == seq
+        eng.load_tf_params(p)
+        eng.forward(c3d=torch.from_numpy(c3d).cuda(), gt=torch.from_numpy(gt).cuda())
+        torch.cuda.synchronize()
+        d = dict(h=eng.Hf.cpu().numpy(), hop=eng.Hop.float().cpu().numpy(), logits=eng.logits.cpu().numpy())
+        if train:
+            d.update(z=eng.Z.cpu().numpy(), r=eng.Rs.cpu().numpy(), c=eng.Cs.cpu().numpy(), rh=eng.RH.float().cpu().numpy())
+        out.append(d)
+    a, b = out
+    assert np.abs(a["h"]).max() > 1e-3
+    for k in a:
+        scale = np.abs(a[k]).max()
+        assert np.abs(a[k] - b[k]).max() <= 1e-5 * scale + 1e-7, (k, np.abs(a[k] - b[k]).max(), scale)
