@@ -94,15 +94,20 @@ typedef struct rgp_gru_seq_args {
   const void* Uzr;                /* [9*2Ch, Ch] bf16 op layout (tap, z|r out channel, in channel)               */
   const void* Uc;                 /* [9*Ch, Ch]                                                                  */
   const float* Xg;                /* [T*B*S, 3Ch] fp32 input-half pre-activations (columns z | r | c)            */
-  float* Zs; float* Rs; float* Cs;/* train: saved gates [T, B*S, Ch] fp32 q-layout; all NULL in inference       */
+  float* Zs; float* Rs; float* Cs;/* train: saved gates [T, B*S, Ch] fp32 q-layout each; inference: all NULL       */
   void* HS;                       /* bf16 head-input layout [T*B*So, Ch] (BN-scaled h_t), or NULL                */
   const float* bn_gamma; const float* bn_beta; float alpha;   /* [T, Ch] each, or NULL (gaze_grcn.py:325)       */
   int B, T, G, Ch;
   int So, Wo, pado;               /* head-input layout geometry                                                  */
   int nsplit;                     /* 1, or 2: a 2-CTA cluster shares a tile, each CTA owns half of the channels  */
   int dtype;                      /* must be 1 (bf16 operands, tcgen05 engine)                                   */
+  int mcast;                      /* 1, 2, 4 or 8 tiles per cluster: each CTA fetches 1/mcast of every weight box
+                                     and TMA-multicasts it to the others (nsplit*mcast <= 8)                      */
 } rgp_gru_seq_args;
 int rgp_convgru_seq_fwd(const rgp_gru_seq_args* a, void* stream);
+/* Profiling hook: phase timestamps (globaltimer ns) CTA 0 recorded during the last rgp_convgru_seq_fwd, copied to a
+ * HOST array of n <= 32*12 values laid out [step][event] (events listed in csrc/gru_seq.cu).  Synchronises the device. */
+int rgp_convgru_seq_profile(unsigned long long* host_out, int n);
 
 /* ---- model path ------------------------------------------------------------------------- */
 /* gaze_grcn.py:225-227 (tf.transpose NCHW->NHWC of the C3D blob) fused with the fp32->operand

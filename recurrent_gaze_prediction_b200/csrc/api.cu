@@ -51,6 +51,11 @@ int rgp_convgru_seq_fwd(const rgp_gru_seq_args* a, void* stream) {
   return rgp::convgru_seq_fwd(*a, (cudaStream_t)stream);
 }
 
+int rgp_convgru_seq_profile(unsigned long long* host_out, int n) {
+  RGP_CHECK_ARG(host_out != nullptr && n > 0, "rgp_convgru_seq_profile: bad arguments");
+  return rgp::convgru_seq_profile(host_out, n);
+}
+
 int rgp_wgrad(const rgp_wgrad_args* a, void* stream) {
   RGP_CHECK_ARG(a != nullptr, "rgp_wgrad: null args");
   RGP_CHECK_ARG(a->ntaps >= 1 && a->ntaps <= RGP_MAX_TAPS, "rgp_wgrad: ntaps=%d out of range", a->ntaps);

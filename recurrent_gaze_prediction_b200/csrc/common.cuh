@@ -209,5 +209,6 @@ int wgrad_simt(const rgp_wgrad_args& a, cudaStream_t s);
 int wgrad_tc(const rgp_wgrad_args& a, cudaStream_t s);
 int tapgemm_tc(const rgp_tapgemm_args& a, cudaStream_t s);
 int convgru_seq_fwd(const rgp_gru_seq_args& a, cudaStream_t s);
+int convgru_seq_profile(unsigned long long* host_out, int n);
 
 }  // namespace rgp

@@ -86,10 +86,38 @@ __device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity
       "r"(parity)
       : "memory");
 }
+// TMA tile load delivered to the same shared-memory offset (and mbarrier offset) of every CTA in cta_mask
+__device__ __forceinline__ void tma_load_2d_mc(void* smem_dst, const CUtensorMap* tmap, uint64_t* bar, int c0, int c1,
+                                               uint16_t cta_mask) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.multicast::cluster"
+      " [%0], [%1, {%3, %4}], [%2], %5;"
+      ::"r"(smem_u32(smem_dst)), "l"(tmap), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "h"(cta_mask)
+      : "memory");
+}
+// tcgen05.commit arriving on the mbarrier at the same offset in every CTA of cta_mask
+__device__ __forceinline__ void tc_commit_mc(uint64_t* bar, uint16_t cta_mask) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(smem_u32(bar)), "h"(cta_mask)
+               : "memory");
+}
 __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async;" ::: "memory"); }
+
+// Phase timestamps (globaltimer, ns) of CTA 0 for its first kTsSteps steps — read back by rgp_convgru_seq_profile().
+// Events: 0 r-phase gate open (MMA warp) | 1 r MMAs issued | 2 z MMAs issued | 3 c-phase gate open | 4 c MMAs issued |
+//         5 r_full seen (epilogue warp 2) | 6 r-epilogue done | 7 z_full seen | 8 z-epilogue done | 9 c_full seen | 10 c-epilogue done
+constexpr int kTsSteps = 32, kTsEvents = 12;
+__device__ unsigned long long g_seq_ts[kTsSteps * kTsEvents];
+__device__ __forceinline__ void stamp(bool on, long long it, int ev) {
+  if (on && it < kTsSteps) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    g_seq_ts[it * kTsEvents + ev] = t;
+  }
+}
 
 template <int NH>
 struct SeqCfg {
@@ -124,12 +152,21 @@ gru_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(h_ready + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int nsplit = a.nsplit;
-  const int rank = (nsplit > 1) ? (int)(blockIdx.x % nsplit) : 0;
-  const int cluster_id = blockIdx.x / nsplit, nclusters = gridDim.x / nsplit;
+  // cluster = mcast tiles x nsplit channel halves; CTA rank = mrank * nsplit + nrank
+  const int nsplit = a.nsplit, cs = a.mcast, csize = nsplit * cs;
+  const int crank = (int)(blockIdx.x % csize);
+  const int rank = crank % nsplit, mrank = crank / nsplit;
+  const int cluster_id = (int)(blockIdx.x / csize) * cs + mrank;      // first tile of this CTA
+  const int nclusters = (int)(gridDim.x / csize) * cs;                 // tile stride
+  uint16_t bmask = 0;                                                   // CTAs that share this CTA's weight slice
+  for (int j = 0; j < cs; ++j) bmask |= (uint16_t)(1u << (j * nsplit + rank));
+  const int peer0 = mrank * nsplit;                                     // first CTA of this tile's channel-split group
   const int Ch = a.Ch, Wp = a.G + 1, S = Wp * Wp;
   const int M = a.B * S;                          // q-rows of one step
-  const int mtiles = (M + BM - 1) / BM;
+  const int mtiles_real = (M + BM - 1) / BM;
+  // every CTA of a cluster walks the same number of tiles (weight slices are exchanged in lock-step); tiles past the
+  // end are ghosts: all rows out of range, nothing stored
+  const int mtiles = ((mtiles_real + cs - 1) / cs) * cs;
   const int col0 = rank * NH;                     // this CTA's channel slice [col0, col0+NH)
   const int kchunks = Ch / BK;
   const int ksteps = 9 * kchunks;                 // k-steps of one phase
@@ -142,7 +179,7 @@ gru_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmUc) : "memory");
     for (int i = 0; i < C::kStages; ++i) {
       mbar_init(&fullA[i], 1); mbar_init(&emptyA[i], 1);
-      mbar_init(&fullB[i], 1); mbar_init(&emptyB[i], 1);
+      mbar_init(&fullB[i], 1); mbar_init(&emptyB[i], (uint32_t)cs);
     }
     mbar_init(r_full, 1); mbar_init(z_full, 1); mbar_init(c_full, 1);
     mbar_init(rh_ready, EPI_WARPS * nsplit); mbar_init(h_ready, EPI_WARPS * nsplit);
@@ -156,7 +193,7 @@ gru_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
   }
   tc_fence_before();
   __syncthreads();
-  if (nsplit > 1) cluster_sync_all();   // the peer's barriers exist before anyone arrives on them remotely
+  if (csize > 1) cluster_sync_all();   // the peers' barriers exist before anyone arrives on them remotely
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -170,24 +207,35 @@ gru_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
         for (int t = 0; t < a.T; ++t, ++it) {
           const long long rowH = (long long)t * M + m0;                 // slab t = h_{t-1} ... (slab 0 = h_0)
           const long long rowRH = (long long)(train ? t : 0) * M + m0;
-          int iA = 0, iB = 0;                                           // k-step cursors inside this step (0..3*ksteps)
-          while (iA < 3 * ksteps) {
-            while (iB < 3 * ksteps && iB < iA + C::kStages) {
-              const int ph = iB / ksteps, ks = iB - ph * ksteps;
-              const int tap = ks / kchunks, kc = ks - tap * kchunks;
-              mbar_wait(&emptyB[sB], phB ^ 1);
-              mbar_expect_tx(&fullB[sB], C::kBBytes);
-              if (ph == 0)      tma_load_2d(ringB + sB * C::kBBytes, &tmUzr, &fullB[sB], kc * BK, tap * 2 * Ch + Ch + col0);
-              else if (ph == 1) tma_load_2d(ringB + sB * C::kBBytes, &tmUzr, &fullB[sB], kc * BK, tap * 2 * Ch + col0);
-              else              tma_load_2d(ringB + sB * C::kBBytes, &tmUc, &fullB[sB], kc * BK, tap * Ch + col0);
-              if (++sB == C::kStages) { sB = 0; phB ^= 1; }
-              ++iB;
+          int iB = 0;                                                   // weight-ring cursor (k-step inside this step)
+          auto issueB = [&]() {
+            const int ph = iB / ksteps, ks = iB - ph * ksteps;
+            const int tap = ks / kchunks, kc = ks - tap * kchunks;
+            mbar_wait_cluster(&emptyB[sB], phB ^ 1);                    // every CTA of the group has released this stage
+            mbar_expect_tx(&fullB[sB], C::kBBytes);                     // the whole box: 1/cs from each CTA of the group
+            const int brow = ((ph == 0) ? tap * 2 * Ch + Ch : ((ph == 1) ? tap * 2 * Ch : tap * Ch)) + col0;
+            const CUtensorMap* tm = (ph == 2) ? &tmUc : &tmUzr;
+            if (cs == 1) {
+              tma_load_2d(ringB + sB * C::kBBytes, tm, &fullB[sB], kc * BK, brow);
+            } else {
+              const int srows = NH / cs;                                // this CTA's slice of the box, multicast to the group
+              tma_load_2d_mc(ringB + sB * C::kBBytes + mrank * srows * (BK * 2), tm, &fullB[sB], kc * BK,
+                             brow + mrank * srows, bmask);
             }
+            if (++sB == C::kStages) { sB = 0; phB ^= 1; }
+            ++iB;
+          };
+          for (int iA = 0; iA < 3 * ksteps; ++iA) {
             const int ph = iA / ksteps, ks = iA - ph * ksteps;
             const int tap = ks / kchunks, kc = ks - tap * kchunks;
-            if (ks == 0) {
-              if (ph == 0 && it > 0) { mbar_wait_cluster(h_ready, (uint32_t)((it - 1) & 1)); fence_proxy_async(); }
-              if (ph == 2) { mbar_wait_cluster(rh_ready, (uint32_t)(it & 1)); fence_proxy_async(); }
+            const bool gate_h = (ks == 0 && ph == 0 && it > 0), gate_rh = (ks == 0 && ph == 2);
+            if (gate_h || gate_rh) {
+              // the state rows are not ready yet, the weights are: fill the weight ring while the epilogue works
+              // (its slots free up as the MMAs of the previous phase drain, which never depends on this gate)
+              while (iB < 3 * ksteps && iB < iA + C::kStages) issueB();
+              if (gate_h) mbar_wait_cluster(h_ready, (uint32_t)((it - 1) & 1));
+              else        mbar_wait_cluster(rh_ready, (uint32_t)(it & 1));
+              fence_proxy_async();
             }
             const int off = (tap / 3) * Wp + (tap % 3);
             mbar_wait(&emptyA[sA], phA ^ 1);
@@ -195,7 +243,7 @@ gru_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
             if (ph < 2) tma_load_2d(ringA + sA * C::kABytes, &tmH, &fullA[sA], kc * BK, (int)(rowH + off));
             else        tma_load_2d(ringA + sA * C::kABytes, &tmRH, &fullA[sA], kc * BK, (int)(rowRH + off));
             if (++sA == C::kStages) { sA = 0; phA ^= 1; }
-            ++iA;
+            if (iB <= iA) issueB();
           }
         }
       }
@@ -213,6 +261,7 @@ gru_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
           if (ph == 0 && it > 0) mbar_wait_cluster(h_ready, (uint32_t)((it - 1) & 1));
           if (ph == 2) mbar_wait_cluster(rh_ready, (uint32_t)(it & 1));
           tc_fence_after();
+          if (ph != 1) stamp(blockIdx.x == 0 && lane == 0, it, ph == 0 ? 0 : 3);
           const uint32_t tacc = tmem_base + (uint32_t)(ph == 1 ? 0 : NH);
           uint64_t* done = (ph == 0) ? r_full : ((ph == 1) ? z_full : c_full);
           for (int ks = 0; ks < ksteps; ++ks) {
@@ -226,13 +275,14 @@ gru_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
               for (int k = 0; k < BK / 16; ++k)
                 tc_mma_bf16(tacc, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (ks | k) ? 1u : 0u);
               tc_commit(&emptyA[sA]);
-              tc_commit(&emptyB[sB]);
+              if (cs == 1) tc_commit(&emptyB[sB]); else tc_commit_mc(&emptyB[sB], bmask);
               if (ks == ksteps - 1) tc_commit(done);
             }
             __syncwarp();
             if (++sA == C::kStages) { sA = 0; phA ^= 1; }
             if (++sB == C::kStages) { sB = 0; phB ^= 1; }
           }
+          stamp(blockIdx.x == 0 && lane == 0, it, ph == 0 ? 1 : (ph == 1 ? 2 : 4));
         }
       }
     }
@@ -269,8 +319,10 @@ gru_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
             for (int c = 0; c < CW; c += 32) asm volatile("prefetch.global.L2 [%0];" ::"l"(xg + g * Ch + col0 + cb + c));
         }
         // ---------------- r-epilogue: r = sig(acc_r + Xr); r.h -> operand rows of the c-phase ----------------
+        const bool ts_on = blockIdx.x == 0 && warp == 2 && lane == 0;
         mbar_wait(r_full, par);
         tc_fence_after();
+        stamp(ts_on, it, 5);
 #pragma unroll 1
         for (int c = 0; c < CW; c += 32) {
           const int n = col0 + cb + c;                                   // global channel
@@ -294,12 +346,14 @@ gru_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
         fence_proxy_async();
         __syncwarp();
         if (lane == 0) {
-          if (nsplit > 1) { for (int p = 0; p < nsplit; ++p) mbar_arrive_remote(rh_ready, (uint32_t)p); }
+          if (nsplit > 1) { for (int p = 0; p < nsplit; ++p) mbar_arrive_remote(rh_ready, (uint32_t)(peer0 + p)); }
           else mbar_arrive(rh_ready);
         }
+        stamp(ts_on, it, 6);
         // ---------------- z-epilogue: z = sig(acc_z + Xz), kept in TMEM for the c-epilogue ----------------
         mbar_wait(z_full, par);
         tc_fence_after();
+        stamp(ts_on, it, 7);
 #pragma unroll 1
         for (int c = 0; c < CW; c += 32) {
           const int n = col0 + cb + c;
@@ -313,10 +367,12 @@ gru_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
           }
           tc_st32(tlane + (uint32_t)(cb + c), v);
         }
+        stamp(ts_on, it, 8);
         // ---------------- c-epilogue: candidate, state update, BN-scaled head rows ----------------
         const long long orow = ((long long)t * a.B + f) * a.So + (long long)(y + a.pado) * a.Wo + (x + a.pado);
         mbar_wait(c_full, par);
         tc_fence_after();
+        stamp(ts_on, it, 9);
 #pragma unroll 1
         for (int c = 0; c < CW; c += 32) {
           const int n = col0 + cb + c;
@@ -351,16 +407,17 @@ gru_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
         fence_proxy_async();
         __syncwarp();
         if (lane == 0) {
-          if (nsplit > 1) { for (int p = 0; p < nsplit; ++p) mbar_arrive_remote(h_ready, (uint32_t)p); }
+          if (nsplit > 1) { for (int p = 0; p < nsplit; ++p) mbar_arrive_remote(h_ready, (uint32_t)(peer0 + p)); }
           else mbar_arrive(h_ready);
         }
+        stamp(ts_on, it, 10);
       }
     }
   }
 
   tc_fence_before();
   __syncthreads();
-  if (nsplit > 1) cluster_sync_all();   // nobody exits while the peer may still signal its barriers
+  if (csize > 1) cluster_sync_all();   // nobody exits while a peer may still signal its barriers or write its smem
   if (warp == 1) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)C::kTmemCols)
@@ -377,9 +434,9 @@ int launch_seq(const rgp_gru_seq_args& a, cudaStream_t s) {
   if (rc) return rc;
   rc = encode_map_bf16(a.RH, Ch, a.rowsRH, (long long)Ch * 2, BK, BM, &tmRH);
   if (rc) return rc;
-  rc = encode_map_bf16(a.Uzr, Ch, 9LL * 2 * Ch, (long long)Ch * 2, BK, NH, &tmUzr);
+  rc = encode_map_bf16(a.Uzr, Ch, 9LL * 2 * Ch, (long long)Ch * 2, BK, NH / a.mcast, &tmUzr);
   if (rc) return rc;
-  rc = encode_map_bf16(a.Uc, Ch, 9LL * Ch, (long long)Ch * 2, BK, NH, &tmUc);
+  rc = encode_map_bf16(a.Uc, Ch, 9LL * Ch, (long long)Ch * 2, BK, NH / a.mcast, &tmUc);
   if (rc) return rc;
   static bool attr_set = false;
   if (!attr_set) {
@@ -388,21 +445,30 @@ int launch_seq(const rgp_gru_seq_args& a, cudaStream_t s) {
     attr_set = true;
   }
   const int mtiles = (a.B * S + BM - 1) / BM;
-  int nclusters = mtiles;
-  const int maxc = num_sms() / a.nsplit;
-  if (nclusters > maxc) nclusters = maxc;
+  const int csize = a.nsplit * a.mcast;
+  int nclusters = (mtiles + a.mcast - 1) / a.mcast;
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3((unsigned)(nclusters * a.nsplit), 1, 1);
   cfg.blockDim = dim3(NTHREADS, 1, 1);
   cfg.dynamicSmemBytes = C::kSmemBytes;
   cfg.stream = s;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = (unsigned)a.nsplit;
+  attr[0].val.clusterDim.x = (unsigned)csize;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
+  // all clusters must be co-resident?  No: a cluster is self-contained, later clusters simply start when SMs free up.
+  // But a CTA walks several tiles only if the grid is capped, so cap it at what fits at once.
+  static int max_clusters[17] = {0};
+  if (!max_clusters[csize]) {
+    cfg.gridDim = dim3((unsigned)(csize * 64), 1, 1);
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, gru_seq_kernel<NH>, &cfg) != cudaSuccess || n <= 0) { cudaGetLastError(); n = num_sms() / csize; }
+    max_clusters[csize] = n;
+  }
+  if (nclusters > max_clusters[csize]) nclusters = max_clusters[csize];
+  cfg.gridDim = dim3((unsigned)(nclusters * csize), 1, 1);
   cudaError_t e = cudaLaunchKernelEx(&cfg, gru_seq_kernel<NH>, tmH, tmRH, tmUzr, tmUc, a);
   if (e != cudaSuccess) { set_error("gru_seq launch: %s", cudaGetErrorString(e)); return -5; }
   return check_launch("gru_seq");
@@ -410,15 +476,24 @@ int launch_seq(const rgp_gru_seq_args& a, cudaStream_t s) {
 
 }  // namespace
 
+int convgru_seq_profile(unsigned long long* host_out, int n) {
+  if (n > kTsSteps * kTsEvents) n = kTsSteps * kTsEvents;
+  cudaError_t e = cudaMemcpyFromSymbol(host_out, g_seq_ts, sizeof(unsigned long long) * n);
+  if (e != cudaSuccess) { set_error("rgp_convgru_seq_profile: %s", cudaGetErrorString(e)); return -5; }
+  return 0;
+}
+
 int convgru_seq_fwd(const rgp_gru_seq_args& a, cudaStream_t s) {
   const int S = (a.G + 1) * (a.G + 1);
   RGP_CHECK_ARG(a.dtype == 1, "rgp_convgru_seq_fwd: bf16 operands only (dtype=%d); fp32 uses the per-step rgp_tapgemm path", a.dtype);
   RGP_CHECK_ARG(a.B > 0 && a.T > 0, "rgp_convgru_seq_fwd: bad shape B=%d T=%d", a.B, a.T);
   RGP_CHECK_ARG(BM % S == 0, "rgp_convgru_seq_fwd: a 128-row tile must hold whole frames (S=%d; G must be 7, 3 or 1)", S);
   RGP_CHECK_ARG(a.nsplit == 1 || a.nsplit == 2, "rgp_convgru_seq_fwd: nsplit=%d", a.nsplit);
+  RGP_CHECK_ARG(a.mcast == 1 || a.mcast == 2 || a.mcast == 4 || a.mcast == 8, "rgp_convgru_seq_fwd: mcast=%d", a.mcast);
+  RGP_CHECK_ARG(a.nsplit * a.mcast <= 8, "rgp_convgru_seq_fwd: cluster of %d CTAs (max 8)", a.nsplit * a.mcast);
   RGP_CHECK_ARG(a.Ch % 64 == 0, "rgp_convgru_seq_fwd: Ch=%d must be a multiple of 64", a.Ch);
-  RGP_CHECK_ARG((a.Rs == nullptr) == (a.Zs == nullptr) && (a.Rs == nullptr) == (a.Cs == nullptr),
-                "rgp_convgru_seq_fwd: Zs, Rs, Cs must be all set (train) or all NULL");
+  RGP_CHECK_ARG((a.Rs == nullptr) == (a.Cs == nullptr), "rgp_convgru_seq_fwd: Rs and Cs must be both set (train) or both NULL");
+  RGP_CHECK_ARG(a.Rs == nullptr || a.Zs != nullptr, "rgp_convgru_seq_fwd: training needs Zs, Rs and Cs");
   RGP_CHECK_ARG((a.bn_gamma == nullptr) == (a.bn_beta == nullptr), "rgp_convgru_seq_fwd: bn_gamma / bn_beta");
   RGP_CHECK_ARG(((uintptr_t)a.Hop & 15) == 0 && ((uintptr_t)a.RH & 15) == 0 && ((uintptr_t)a.Uzr & 15) == 0 &&
                 ((uintptr_t)a.Uc & 15) == 0, "rgp_convgru_seq_fwd: operands must be 16-byte aligned");

@@ -33,7 +33,7 @@ def _tdtype(dtype):
 
 class GazeEngine(object):
     def __init__(self, model="gaze_grcn", B=2, T=35, G=7, Ch=128, Cin=512, Cfeat=1024, dtype=0,
-                 device="cuda", lib=None, train=False, head=None, engine=None, seq=None, nsplit=None):
+                 device="cuda", lib=None, train=False, head=None, engine=None, seq=None, nsplit=None, mcast=None):
         if model not in ("gaze_grcn", "gaze_grcn77", "gaze_lstm"):
             raise ValueError("unknown model %r" % (model,))
         self.model, self.B, self.T, self.G, self.Ch, self.Cin, self.Cfeat = model, B, T, G, Ch, Cin, Cfeat
@@ -55,14 +55,19 @@ class GazeEngine(object):
         self.ngx = 4 if self.lstm else 3        # gates fed by the input conv
         self.tdt = _tdtype(dtype)
         self.taps3 = [ky * self.Wp + kx for ky in range(3) for kx in range(3)]
-        # persistent ConvGRU recurrence (rgp_convgru_seq_fwd: all T steps in one launch).  Default: whenever the
-        # shape allows it on the tcgen05 engine; RGP_SEQ=0 falls back to two tap-GEMM launches per step (A/B checks).
+        # Persistent ConvGRU recurrence (rgp_convgru_seq_fwd: all T steps in one launch, one CTA per 128-row tile).
+        # Measured on B200 (profiles/r01_notes.md): it beats two tap-GEMM launches per step once there is about one
+        # tile per SM (3.0 vs 4.0 ms at 256 clips); below that the per-step GEMMs, which spread one step over all
+        # SMs, win.  RGP_SEQ=0/1 forces the choice (A/B checks); nsplit / mcast are the kernel's cluster options.
+        mtiles = (B * self.S + 127) // 128
         if seq is None:
-            seq = (dtype == 1 and engine != 1 and Ch in (128, 256) and os.environ.get("RGP_SEQ", "1") != "0")
+            env = os.environ.get("RGP_SEQ", "")
+            seq = (dtype == 1 and engine != 1 and Ch in (128, 256) and (env == "1" or (env != "0" and mtiles >= 100)))
         self.use_seq = bool(seq) and (not self.lstm) and 128 % self.S == 0
-        if nsplit is None:   # 2-CTA clusters split the channels when one CTA per tile would leave SMs idle
-            nsplit = int(os.environ.get("RGP_SEQ_NSPLIT", "0")) or (2 if (Ch == 256 and (B * self.S + 127) // 128 <= 74) else 1)
-        self.nsplit = nsplit
+        self.nsplit = nsplit or int(os.environ.get("RGP_SEQ_NSPLIT", "0")) or (2 if (Ch == 256 and mtiles <= 74) else 1)
+        # mcast > 1: every weight box is fetched once per cluster and TMA-multicast; measured slower (the bound is the
+        # SM's own L2->SMEM port, which multicast does not relieve), so the default is 1
+        self.mcast = mcast or int(os.environ.get("RGP_SEQ_MCAST", "0")) or 1
         self._build_params()
         self._alloc()
         self.head_version = -1
@@ -376,15 +381,16 @@ class GazeEngine(object):
             a.Hop, a.rowsH, a.Hf = self.Hop.data_ptr(), self.Hop.shape[0], self.Hf.data_ptr()
             a.RH, a.rowsRH = self.RH.data_ptr(), self.RH.shape[0]
             a.Uzr, a.Uc, a.Xg = pop("Uzr_op"), pop("Uc_op"), self.Xg.data_ptr()
+            a.Zs = self.Z.data_ptr()
             if self.train:
-                a.Zs, a.Rs, a.Cs = self.Z.data_ptr(), self.Rs.data_ptr(), self.Cs.data_ptr()
+                a.Rs, a.Cs = self.Rs.data_ptr(), self.Cs.data_ptr()
             if self.head == "deconv":
                 a.HS = self.HS.data_ptr()
             if self.use_bn:
                 a.bn_gamma, a.bn_beta, a.alpha = self._ptr("bn_gamma"), self._ptr("bn_beta"), 1.0 / math.sqrt(1.0 + BN_EPS)
             a.B, a.T, a.G, a.Ch = B, T, G, Ch
             a.So, a.Wo, a.pado = HEAD_S, HEAD_W, HEAD_PAD
-            a.nsplit, a.dtype = self.nsplit, self.dtype
+            a.nsplit, a.dtype, a.mcast = self.nsplit, self.dtype, self.mcast
             lib.rgp_convgru_seq_fwd(C.byref(a), s)
             if self.head == "fc":   # gaze_grcn77.py:206-211
                 for t in range(T):

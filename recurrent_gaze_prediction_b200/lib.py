@@ -60,13 +60,14 @@ class GruSeqArgs(C.Structure):
         ("bn_gamma", _vp), ("bn_beta", _vp), ("alpha", _f),
         ("B", _i), ("T", _i), ("G", _i), ("Ch", _i),
         ("So", _i), ("Wo", _i), ("pado", _i),
-        ("nsplit", _i), ("dtype", _i),
+        ("nsplit", _i), ("dtype", _i), ("mcast", _i),
     ]
 
 
 _SIGS = {
     "rgp_tapgemm": [C.POINTER(TapGemmArgs), _vp],
     "rgp_convgru_seq_fwd": [C.POINTER(GruSeqArgs), _vp],
+    "rgp_convgru_seq_profile": [_vp, _i],
     "rgp_pack_c3d": [_vp, _vp, _i, _i, _i, _i, _i, _vp],
     "rgp_pack_emb": [_vp, _vp, _i, _i, _i, _i, _i, _vp],
     "rgp_cast": [_vp, _vp, _ll, _i, _vp],

@@ -570,8 +570,7 @@ class EmuLib(object):
             g.xg, g.ldx = a.Xg + t * M * 3 * Ch * 4, 3 * Ch
             g.rowsA, g.lda = rows_step, Ch
             g.hprev_f32 = a.Hf + t * M * Ch * 4
-            zbuf = np.zeros((M, Ch), dtype=np.float32)
-            g.z_f32 = (a.Zs + t * M * Ch * 4) if train else zbuf.ctypes.data
+            g.z_f32 = a.Zs + sl * M * Ch * 4
             g.A, g.Bw, g.N, g.epi = a.Hop + t * M * Ch * 4, a.Uzr, 2 * Ch, L.EPI_GRU_ZR
             g.out_op = a.RH + sl * M * Ch * 4
             g.save_r = (a.Rs + t * M * Ch * 4) if train else None
