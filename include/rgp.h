@@ -167,6 +167,16 @@ int rgp_wgrad(const rgp_wgrad_args* a, void* stream);
 int rgp_gru_bwd_last(const float* dhs, const float* gamma, float alpha, const float* z, const float* c,
                      const float* hprev_f32, void* dg, int ldg, float* dhpart, int B, int G, int Ch,
                      int dtype, void* stream);
+/* ConvLSTM gate backward of ONE step (tf.gradients of gaze_lstm.py:112-133 as written).  save [B*S, 5Ch] = the
+ * (i, f, g, o, c_{t-1}) rgp_lstm_gates stored for this step; c_t comes from cnext_save (= save of step t+1) or, for
+ * the last step, from c_final (p-layout cell buffer).  dhs [B*S, Ch] = head term of dL/dh_t, dhrec [B*S, Ch] = conv^T
+ * term from step t+1 (ignored when last != 0); dc [B*S, Ch]: in dL/dc_t (ignored when last), out dL/dc_{t-1}.
+ * Outputs (operand dtype, q-layout): dg4 [B*S, 4Ch] = d(pre-activations) i|f|c|o (for W_x and dX), dhc [B*S, 3Ch] =
+ * d(hidden conv outputs) (i+c)|f|o (for W_hi, W_hf, W_ho and dh_{t-1}); peephole gradients are accumulated. */
+int rgp_lstm_gates_bwd(const float* save, const float* cnext_save, const float* c_final, const float* dhs,
+                       const float* dhrec, float* dc, const float* wci, const float* wcf, const float* wco, void* dg4,
+                       void* dhc, float* gwci, float* gwcf, float* gwco, int B, int G, int Ch, int last, int dtype,
+                       void* stream);
 /* per-tap transpose + cast: src fp32 [ntaps][R][Cc] -> dst operand dtype [ntaps][Cc][R] */
 int rgp_transpose_taps(const float* src, void* dst, int ntaps, int R, int Cc, int dtype, void* stream);
 /* head backward, data side: im2col of dlogits [B,T,49,49] into the head-input row layout:

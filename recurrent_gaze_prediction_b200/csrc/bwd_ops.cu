@@ -211,6 +211,50 @@ __global__ void __launch_bounds__(256) fc_head_bwd_kernel(const float* __restric
   if (lane == 0) atomicAdd(gb, d);
 }
 
+
+// ConvLSTM gate backward of one step (tf.gradients of gaze_lstm.py:112-133 as written: the candidate shares the
+// W_hi convolution with the input gate, the output gate peeps at the OLD cell).  One thread per (clip, position, channel).
+//   save = (i, f, g, o, c_{t-1}) of this step; cn = c_t; dh = dhs (head) + dhrec (conv^T of step t+1);
+//   dc (in: dL/dc_t from step t+1, out: dL/dc_{t-1}).
+template <typename TA>
+__global__ void __launch_bounds__(256) lstm_gates_bwd_kernel(
+    const float* __restrict__ save, const float* __restrict__ cnext_save, const float* __restrict__ c_final,
+    const float* __restrict__ dhs, const float* __restrict__ dhrec, float* __restrict__ dc,
+    const float* __restrict__ wci, const float* __restrict__ wcf, const float* __restrict__ wco,
+    TA* __restrict__ dg4, TA* __restrict__ dhc, float* __restrict__ gwci, float* __restrict__ gwcf,
+    float* __restrict__ gwco, int B, int G, int Ch, int last) {
+  const int Wp = G + 1, S = Wp * Wp, P = G * G;
+  long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (idx >= (long long)B * P * Ch) return;
+  // clips are the fastest-varying index across blocks of the same (position, channel) range only through atomics
+  int n = (int)(idx % Ch);
+  int pos = (int)(idx / Ch);
+  int b = pos / P, p = pos - b * P;
+  int y = p / G, x = p - y * G;
+  long long m = (long long)b * S + y * Wp + x;
+  const float* sv = save + m * 5 * Ch;
+  const float gi = sv[n], gf = sv[Ch + n], gg = sv[2 * Ch + n], go = sv[3 * Ch + n], cp = sv[4 * Ch + n];
+  const float cn = cnext_save ? cnext_save[m * 5 * Ch + 4 * Ch + n] : c_final[(m + Wp + 1) * Ch + n];
+  float dh = dhs[m * Ch + n];
+  float dcn = 0.f;
+  if (!last) { dh += dhrec[m * Ch + n]; dcn = dc[m * Ch + n]; }
+  const float tc = tanhf_(cn);
+  dcn += dh * go * (1.0f - tc * tc);
+  const float dpo = dh * tc * go * (1.0f - go);
+  const float dpi = dcn * gg * gi * (1.0f - gi);
+  const float dpg = dcn * gi * (1.0f - gg * gg);
+  const float dpf = dcn * cp * gf * (1.0f - gf);
+  const int pe = p * Ch + n;
+  dc[m * Ch + n] = dcn * gf + dpi * wci[pe] + dpf * wcf[pe] + dpo * wco[pe];
+  TA* g4 = dg4 + m * 4 * Ch;
+  OpT<TA>::st(g4 + n, dpi); OpT<TA>::st(g4 + Ch + n, dpf); OpT<TA>::st(g4 + 2 * Ch + n, dpg); OpT<TA>::st(g4 + 3 * Ch + n, dpo);
+  TA* hc = dhc + m * 3 * Ch;
+  OpT<TA>::st(hc + n, dpi + dpg); OpT<TA>::st(hc + Ch + n, dpf); OpT<TA>::st(hc + 2 * Ch + n, dpo);
+  atomicAdd(gwci + pe, dpi * cp);
+  atomicAdd(gwcf + pe, dpf * cp);
+  atomicAdd(gwco + pe, dpo * cp);
+}
+
 }  // namespace rgp
 
 using namespace rgp;
@@ -229,6 +273,21 @@ int rgp_gru_bwd_last(const float* dhs, const float* gamma, float alpha, const fl
               (gru_bwd_last_kernel<float><<<grid, 256, 0, s>>>(dhs, gamma, alpha, z, c, hprev_f32, (float*)dg, ldg, dhpart, B, G, Ch)),
               (gru_bwd_last_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>(dhs, gamma, alpha, z, c, hprev_f32, (__nv_bfloat16*)dg, ldg, dhpart, B, G, Ch)));
   return check_launch("rgp_gru_bwd_last");
+}
+
+int rgp_lstm_gates_bwd(const float* save, const float* cnext_save, const float* c_final, const float* dhs,
+                       const float* dhrec, float* dc, const float* wci, const float* wcf, const float* wco, void* dg4,
+                       void* dhc, float* gwci, float* gwcf, float* gwco, int B, int G, int Ch, int last, int dtype,
+                       void* stream) {
+  RGP_CHECK_ARG(cnext_save != nullptr || c_final != nullptr, "rgp_lstm_gates_bwd: need c_t (cnext_save or c_final)");
+  RGP_CHECK_ARG(last || dhrec != nullptr, "rgp_lstm_gates_bwd: dhrec is required unless this is the last time step");
+  long long total = (long long)B * G * G * Ch;
+  int grid = (int)((total + 255) / 256);
+  cudaStream_t s = (cudaStream_t)stream;
+  DISPATCH_TA(dtype,
+              (lstm_gates_bwd_kernel<float><<<grid, 256, 0, s>>>(save, cnext_save, c_final, dhs, dhrec, dc, wci, wcf, wco, (float*)dg4, (float*)dhc, gwci, gwcf, gwco, B, G, Ch, last)),
+              (lstm_gates_bwd_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>(save, cnext_save, c_final, dhs, dhrec, dc, wci, wcf, wco, (__nv_bfloat16*)dg4, (__nv_bfloat16*)dhc, gwci, gwcf, gwco, B, G, Ch, last)));
+  return check_launch("rgp_lstm_gates_bwd");
 }
 
 int rgp_transpose_taps(const float* src, void* dst, int ntaps, int R, int Cc, int dtype, void* stream) {

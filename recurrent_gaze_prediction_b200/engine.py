@@ -247,16 +247,19 @@ class GazeEngine(object):
         self.frame_loss = z(B * T)
         self.loss = z(1)
         if self.train:
-            if self.lstm:
-                raise NotImplementedError("BPTT is implemented for the ConvGRU models (gaze_grcn, gaze_grcn77); "
-                                          "gaze_lstm is forward-only in this round")
             self.dlogits = z(B, T, self.GH, self.GH)
-            self.dG = z(T * B * S, 3 * Ch, dt=tdt)          # dL/d(pre-activations), columns z | r | c
+            # dL/d(pre-activations) of the input-fed gates, columns z | r | c (GRU) or i | f | c | o (LSTM)
+            self.dG = z(T * B * S, self.ngx * Ch, dt=tdt)
             self.dhs = z(T * B * S, Ch)                     # dL/d(head input) in the recurrence q-layout
-            self.dhpart = z(B * S, Ch)
-            self.UcT = z(9 * Ch, Ch, dt=tdt)
-            self.UzrT = z(9 * Ch, 2 * Ch, dt=tdt)
-            self.WxT = z(9 * Cin, 3 * Ch, dt=tdt)
+            self.dhpart = z(B * S, Ch)                      # GRU: non-conv part of dL/dh_{t-1}; LSTM: dL/dc
+            if self.lstm:
+                self.dHc = z(T * B * S, 3 * Ch, dt=tdt)     # dL/d(hidden conv outputs), columns (i+c) | f | o
+                self.dhrec = z(B * S, Ch)                   # conv^T term of dL/dh_{t-1}
+                self.WhT = z(9 * Ch, 3 * Ch, dt=tdt)
+            else:
+                self.UcT = z(9 * Ch, Ch, dt=tdt)
+                self.UzrT = z(9 * Ch, 2 * Ch, dt=tdt)
+            self.WxT = z(9 * Cin, self.ngx * Ch, dt=tdt)
             self.dEmb = z(T * B * self.P, Cin, dt=tdt)
             if self.head == "deconv":
                 self.patches = z(T * B * HEAD_S + 128, 384, dt=tdt)
@@ -563,6 +566,30 @@ class GazeEngine(object):
                 lib.rgp_fc_head_bwd(self.dlogits.data_ptr(), self._slab(self.Hf, t + 1), self._ptr("out_W"),
                                     self._slab(self.dhs, t), g("out_W"), g("out_b"), B, T, t, G, Ch, s)
         self._mark("head_bwd")
+        btaps = [Wp + 1 - o for o in self.taps3]
+        rowsT = T * M
+        NG = self.ngx * Ch
+        if self.lstm:
+            self._backward_lstm_cell(btaps, g)
+        else:
+            self._backward_gru_cell(btaps, g, alpha)
+        # ---- projection (only when the reference entry [B,T,1024,7,7] was used)
+        if self.entry == "c3d":
+            lib.rgp_transpose_taps(self._ptr("Wx_op"), self.WxT.data_ptr(), 9, NG, Cin, self.dtype, s)
+            self._gemm(A=self.dG.data_ptr(), rowsA=rowsT, lda=NG, K=NG, Bw=self.WxT.data_ptr(), M=rowsT, N=Cin,
+                       taps=btaps, epi=L.EPI_DX_DENSE, S=S, Wp=Wp, G=G, P=P, out_op=self.dEmb.data_ptr(), ldo=Cin)
+            self._wgrad(self.dEmb.data_ptr(), Cin, 0, Cin, self.Apack.data_ptr(), self.Apack.shape[0], self.Cfeat,
+                        self.Cfeat, T * B * P, [0], g("proj_W_op"))
+            lib.rgp_colsum(self.dEmb.data_ptr(), Cin, T * B * P, Cin, g("proj_b"), self.dtype, s)
+        self._mark("proj_bwd")
+
+    def _backward_gru_cell(self, btaps, g, alpha):
+        """BPTT through the ConvGRU steps (gaze_grcn.py:108-127) and the cell's weight gradients."""
+        lib, s = self.lib, self._s()
+        B, T, S, Ch, Cin, Wp, G = self.B, self.T, self.S, self.Ch, self.Cin, self.Wp, self.G
+        M = B * S
+        rowsT = T * M
+        es = self.dG.element_size()
         # ---- transposed operand copies of the conv weights (dX = conv^T)
         lib.rgp_transpose_taps(self._ptr("Uc_op"), self.UcT.data_ptr(), 9, Ch, Ch, self.dtype, s)
         lib.rgp_transpose_taps(self._ptr("Uzr_op"), self.UzrT.data_ptr(), 9, 2 * Ch, Ch, self.dtype, s)
@@ -572,7 +599,6 @@ class GazeEngine(object):
         lib.rgp_gru_bwd_last(self._slab(self.dhs, T - 1), gam(T - 1), alpha, self.Z[T - 1].data_ptr(),
                              self.Cs[T - 1].data_ptr(), self._slab(self.Hf, T - 1), self._slab(self.dG, T - 1),
                              3 * Ch, self.dhpart.data_ptr(), B, G, Ch, self.dtype, s)
-        btaps = [Wp + 1 - o for o in self.taps3]
         for t in range(T - 1, -1, -1):
             dg_t = self._slab(self.dG, t)
             common = dict(M=M, rowsA=M, lda=3 * Ch, N=Ch, taps=btaps, S=S, Wp=Wp, G=G, Ch=Ch,
@@ -587,7 +613,6 @@ class GazeEngine(object):
                            dg=self._slab(self.dG, t - 1), ldg=3 * Ch, **common, **extra)
         self._mark("recurrence_bwd")
         # ---- weight gradients: contractions over all T*B*S rows at once
-        rowsT = T * M
         self._wgrad(self.dG.data_ptr(), 3 * Ch, 0, 2 * Ch, self.Hop.data_ptr(), self.Hop.shape[0], Ch, Ch, rowsT,
                     self.taps3, g("Uzr_op"))
         self._wgrad(self.dG.data_ptr(), 3 * Ch, 2 * Ch, Ch, self.RH.data_ptr(), self.RH.shape[0], Ch, Ch, rowsT,
@@ -595,15 +620,32 @@ class GazeEngine(object):
         self._wgrad(self.dG.data_ptr(), 3 * Ch, 0, 3 * Ch, self.Xp.data_ptr(), self.Xp.shape[0], Cin, Cin, rowsT,
                     self.taps3, g("Wx_op"))
         self._mark("wgrad_cell")
-        # ---- projection (only when the reference entry [B,T,1024,7,7] was used)
-        if self.entry == "c3d":
-            lib.rgp_transpose_taps(self._ptr("Wx_op"), self.WxT.data_ptr(), 9, 3 * Ch, Cin, self.dtype, s)
-            self._gemm(A=self.dG.data_ptr(), rowsA=rowsT, lda=3 * Ch, K=3 * Ch, Bw=self.WxT.data_ptr(), M=rowsT, N=Cin,
-                       taps=btaps, epi=L.EPI_DX_DENSE, S=S, Wp=Wp, G=G, P=P, out_op=self.dEmb.data_ptr(), ldo=Cin)
-            self._wgrad(self.dEmb.data_ptr(), Cin, 0, Cin, self.Apack.data_ptr(), self.Apack.shape[0], self.Cfeat,
-                        self.Cfeat, T * B * P, [0], g("proj_W_op"))
-            lib.rgp_colsum(self.dEmb.data_ptr(), Cin, T * B * P, Cin, g("proj_b"), self.dtype, s)
-        self._mark("proj_bwd")
+
+    def _backward_lstm_cell(self, btaps, g):
+        """BPTT through the ConvLSTM steps as written in gaze_lstm.py:112-133 (W_hi shared by the input gate and the
+        candidate, output gate peeping at the old cell, W_hc dead) and the cell's weight gradients."""
+        lib, s = self.lib, self._s()
+        B, T, S, Ch, Cin, Wp, G = self.B, self.T, self.S, self.Ch, self.Cin, self.Wp, self.G
+        M = B * S
+        rowsT = T * M
+        lib.rgp_transpose_taps(self._ptr("Wh_op"), self.WhT.data_ptr(), 9, 3 * Ch, Ch, self.dtype, s)
+        self._mark("weight_transposes")
+        for t in range(T - 1, -1, -1):
+            last = 1 if t == T - 1 else 0
+            lib.rgp_lstm_gates_bwd(self.Lsave[t].data_ptr(), 0 if last else self.Lsave[t + 1].data_ptr(),
+                                   self.Cf.data_ptr(), self._slab(self.dhs, t), self.dhrec.data_ptr(),
+                                   self.dhpart.data_ptr(), self._ptr("wci"), self._ptr("wcf"), self._ptr("wco"),
+                                   self._slab(self.dG, t), self._slab(self.dHc, t), g("wci"), g("wcf"), g("wco"),
+                                   B, G, Ch, last, self.dtype, s)
+            if t > 0:   # dL/dh_{t-1} through the three hidden convolutions
+                self._gemm(A=self._slab(self.dHc, t), rowsA=M, lda=3 * Ch, K=3 * Ch, Bw=self.WhT.data_ptr(), M=M, N=Ch,
+                           taps=btaps, epi=L.EPI_STORE_F32, out_f32=self.dhrec.data_ptr(), ldo=Ch, S=S, Wp=Wp, G=G)
+        self._mark("recurrence_bwd")
+        self._wgrad(self.dHc.data_ptr(), 3 * Ch, 0, 3 * Ch, self.Hop.data_ptr(), self.Hop.shape[0], Ch, Ch, rowsT,
+                    self.taps3, g("Wh_op"))
+        self._wgrad(self.dG.data_ptr(), 4 * Ch, 0, 4 * Ch, self.Xp.data_ptr(), self.Xp.shape[0], Cin, Cin, rowsT,
+                    self.taps3, g("Wx_op"))
+        self._mark("wgrad_cell")
 
     # ------------------------------------------------------------------ optimiser — base.py:262-297, gaze_rnn.py:435-444
     def learning_rate(self, lr0=1e-4, decay=0.8, decay_steps=500):

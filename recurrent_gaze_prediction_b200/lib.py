@@ -81,6 +81,7 @@ _SIGS = {
     "rgp_zero": [_vp, _ll, _vp],
     "rgp_wgrad": [C.POINTER(WgradArgs), _vp],
     "rgp_gru_bwd_last": [_vp, _vp, _f, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _i, _vp],
+    "rgp_lstm_gates_bwd": [_vp] * 14 + [_i, _i, _i, _i, _i, _vp],
     "rgp_transpose_taps": [_vp, _vp, _i, _i, _i, _i, _vp],
     "rgp_head_patches": [_vp, _vp, _i, _i, _i, _vp],
     "rgp_head_compose_bwd": [_vp] * 13 + [_i, _vp],

@@ -111,7 +111,7 @@ class GazePredictionGRU(ModelBase):
         B, T, G = self.local_batch, self.n_lstm_steps, getattr(c, "grid", 7)
         dev = torch.device(getattr(c, "device", "cuda"))
         dtype = 1 if getattr(c, "dtype", "bf16") == "bf16" else 0
-        train = bool(getattr(c, "trainable", True)) and self.model_name != "gaze_lstm"
+        train = bool(getattr(c, "trainable", True))
         self.engine = GazeEngine(self.model_name, B=B, T=T, G=G, Ch=getattr(c, "rnn_state_size", 128),
                                  Cin=self.dim_cnn_proj, Cfeat=c.dim_feature, dtype=dtype, device=dev, lib=self._lib,
                                  train=train)

@@ -334,6 +334,42 @@ class EmuLib(object):
         arr(dhpart, (M, Ch))[v] = dh * zz
         return 0
 
+    def rgp_lstm_gates_bwd(self, save, cnext_save, c_final, dhs, dhrec, dc, wci, wcf, wco, dg4, dhc, gwci, gwcf, gwco,
+                           B, G, Ch, last, dtype, stream):
+        assert dtype == 0
+        Wp = G + 1
+        S, P = Wp * Wp, G * G
+        M = B * S
+        pos = np.arange(B * P)
+        b, p = np.divmod(pos, P)
+        y, x = np.divmod(p, G)
+        m = b * S + y * Wp + x
+        sv = arr(save, (M, 5 * Ch))[m]
+        gi, gf, gg, go, cp = (sv[:, i * Ch:(i + 1) * Ch] for i in range(5))
+        if cnext_save:
+            cn = arr(cnext_save, (M, 5 * Ch))[m, 4 * Ch:]
+        else:
+            cn = arr(c_final, (M + Wp + 2, Ch))[m + Wp + 1]
+        dh = arr(dhs, (M, Ch))[m].copy()
+        dcb = arr(dc, (M, Ch))
+        dcn = np.zeros_like(dh)
+        if not last:
+            dh += arr(dhrec, (M, Ch))[m]
+            dcn = dcb[m].copy()
+        tc = np.tanh(cn)
+        dcn = dcn + dh * go * (1 - tc * tc)
+        dpo = dh * tc * go * (1 - go)
+        dpi = dcn * gg * gi * (1 - gi)
+        dpg = dcn * gi * (1 - gg * gg)
+        dpf = dcn * cp * gf * (1 - gf)
+        pk = [arr(w, (P, Ch))[p] for w in (wci, wcf, wco)]
+        dcb[m] = dcn * gf + dpi * pk[0] + dpf * pk[1] + dpo * pk[2]
+        arr(dg4, (M, 4 * Ch))[m] = np.concatenate([dpi, dpf, dpg, dpo], axis=1)
+        arr(dhc, (M, 3 * Ch))[m] = np.concatenate([dpi + dpg, dpf, dpo], axis=1)
+        for gw, d in ((gwci, dpi), (gwcf, dpf), (gwco, dpo)):
+            np.add.at(arr(gw, (P, Ch)), p, d * cp)
+        return 0
+
     def rgp_transpose_taps(self, src, dst, ntaps, R, Cc, dtype, stream):
         arr(dst, (ntaps, Cc, R))[:] = arr(src, (ntaps, R, Cc)).transpose(0, 2, 1)
         return 0

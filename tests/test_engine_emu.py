@@ -71,7 +71,7 @@ def _grad_check(model, entry, loss_type="xentropy", B=2, T=3, Ch=16, seq=None):
     return eng, p
 
 
-@pytest.mark.parametrize("model", ["gaze_grcn", "gaze_grcn77"])
+@pytest.mark.parametrize("model", ["gaze_grcn", "gaze_grcn77", "gaze_lstm"])
 @pytest.mark.parametrize("entry", ["c3d", "emb"])
 def test_bptt_matches_oracle_autograd(model, entry):
     _grad_check(model, entry)

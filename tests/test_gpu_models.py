@@ -67,12 +67,13 @@ def test_train_and_evaluate_entry_points(tmp_path):
     assert os.path.isfile(gen)
 
 
-def test_training_through_the_model_class_learns():
+@pytest.mark.parametrize("mod,cls", [(gaze_grcn, "GazePredictionGRCN"), (gaze_lstm, "GazePredictionLSTM")])
+def test_training_through_the_model_class_learns(mod, cls):
     """30 Adam steps on one repeated synthetic batch: the loss must fall (end-to-end sanity of fwd+BPTT+Adam)."""
     c = gaze_rnn.GRUModelConfig()
     c.n_lstm_steps, c.batch_size, c.initial_learning_rate, c.use_flip_batch = 6, 4, 1e-3, False
     ds = SY.read_synthetic_data_sets(4, 4, 4, T=6)
-    m = gaze_grcn.GazePredictionGRCN(None, ds, c)
+    m = getattr(mod, cls)(None, ds, c)
     losses = []
     for _ in range(30):
         m.single_step()
