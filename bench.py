@@ -44,6 +44,9 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel from the host instead of one CUDA graph")
     ap.add_argument("--cpu-clips", type=int, default=2)
+    ap.add_argument("--entry", default="c3d", choices=["c3d", "emb"],
+                    help="c3d: reference entry [B,T,1024,G,G]; emb: already-projected features [B,T,G,G,512] (SURVEY 8d 'L1')")
+    ap.add_argument("--head", default=None, choices=["deconv", "fc"], help="gaze-map head (default: the model's own)")
     return ap.parse_args()
 
 
@@ -162,9 +165,11 @@ def metric_name(args):
 
 
 def workload_config(args):
-    return {"workload": "%s %s, %d clips/GPU x T=%d, %dx%d grid, C3D conv5b 1024x%dx%d -> proj 512, hidden %d, "
-                        "49x49 gaze maps" % (args.model, args.mode, args.batch, args.T, args.grid, args.grid,
-                                             args.grid, args.grid, args.hidden),
+    feat = "C3D conv5b 1024x%dx%d -> proj 512" % (args.grid, args.grid) if args.entry == "c3d" else \
+        "embedded features 512x%dx%d" % (args.grid, args.grid)
+    maps = "49x49" if (args.head or ("fc" if args.model == "gaze_grcn77" else "deconv")) == "deconv" else "%dx%d" % (args.grid, args.grid)
+    return {"workload": "%s %s, %d clips/GPU x T=%d, %dx%d grid, %s, hidden %d, %s gaze maps"
+                        % (args.model, args.mode, args.batch, args.T, args.grid, args.grid, feat, args.hidden, maps),
             "clips_per_gpu": args.batch, "T": args.T, "grid": args.grid, "hidden": args.hidden,
             "l2_policy": "inputs larger than L2 (features 1.8 GB/step at the default size)",
             "parallelism": ("dp%d (clips sharded across ranks; one NCCL all-reduce of the flat fp32 gradient per step)"
@@ -195,13 +200,17 @@ def main():
     dtype = 1 if args.dtype == "bf16" else 0
     train = args.mode == "train"
     p = init_parameters(args.model, hidden=Ch, T=T, grid=G, seed=0)      # the reference's initialisers
-    eng = GazeEngine(args.model, B=B, T=T, G=G, Ch=Ch, dtype=dtype, device=dev, train=train)
+    eng = GazeEngine(args.model, B=B, T=T, G=G, Ch=Ch, dtype=dtype, device=dev, train=train, head=args.head)
+    if eng.head == "fc" and np.asarray(p["out_W"]).size != Ch:   # per-position FC head on a model whose own head is the deconv chain
+        p = dict(p)
+        p["out_W"] = np.random.RandomState(7).uniform(-0.1, 0.1, (Ch, 1)).astype(np.float32)
     eng.load_tf_params(p)
     GH = eng.GH
     # synthetic inputs: a small pool tiled to the batch (host RNG cost), distinct per rank
     rng = np.random.RandomState(1234 + rank)
     pool = min(B, 8)
-    c3d_pool = SY.make_c3d(rng, pool, T, 1024, G)
+    emb_entry = args.entry == "emb"
+    c3d_pool = SY.make_embedded(rng, pool, T, G, 512) if emb_entry else SY.make_c3d(rng, pool, T, 1024, G)
     gt_pool, _ = SY.make_gazemaps(rng, pool, T, GH, GH, normalize=True)
     reps = (B + pool - 1) // pool
     c3d_h = torch.from_numpy(np.tile(c3d_pool, (reps, 1, 1, 1, 1))[:B]).pin_memory()
@@ -212,8 +221,14 @@ def main():
 
     allreduce = (lambda t: dist.all_reduce(t, op=dist.ReduceOp.SUM)) if world > 1 else None
 
+    def fwd():
+        if emb_entry:
+            eng.forward(emb=c3d_d, gt=gt_d, global_batch=B * world)
+        else:
+            eng.forward(c3d=c3d_d, gt=gt_d, global_batch=B * world)
+
     def fwd_bwd():
-        eng.forward(c3d=c3d_d, gt=gt_d, global_batch=B * world)
+        fwd()
         if train:
             eng.backward()
 
@@ -307,7 +322,7 @@ def main():
     fl = flops_per_frame(Ch, G, lstm=eng.lstm)
     roof = None
     if rank == 0:
-        evs = eng.time_stages(c3d_d, gt_d, iters=3)
+        evs = eng.time_stages(c3d_d, gt_d, iters=3, emb=emb_entry)
         i2h_ms = evs["i2h"]
         ach = fl["i2h"] * B * T / (i2h_ms * 1e-3) / 1e12
         roof = {"kernel": "tapgemm i2h (3x3 SAME conv, all T frames, M=%d N=%d K=9x512)" % (T * B * eng.S, eng.ngx * Ch),
@@ -315,13 +330,15 @@ def main():
                 "peak_source": which + " (sustained bf16; burst %.1f)" % tf_burst, "traffic": None,
                 "ms_per_launch": i2h_ms, "stage_ms": evs}
         if train:
-            eng.forward(c3d=c3d_d, gt=gt_d, global_batch=B * world)
+            fwd()
             roof["stage_ms_bwd"] = eng.time_backward(iters=3)
 
     cpu = None
     if rank == 0 and not args.no_cpu_baseline:
         nb = args.cpu_clips
         pc = p
+        if emb_entry:
+            raise SystemExit("--entry emb has no CPU reference leg: pass --no-cpu-baseline")
         c3 = c3d_pool[:nb]
         g = gt_pool[:nb]
         cpu_reference_step(args.model, pc, c3, g, train)

@@ -461,10 +461,10 @@ class GazeEngine(object):
             fn()
         return g, self.lib.launches - n0
 
-    def time_stages(self, c3d, gt, iters=3):
+    def time_stages(self, c3d, gt, iters=3, emb=False):
         """CUDA-event time (ms, mean of `iters`) of each stage of one forward pass on the current stream."""
         names = ["embed", "i2h", "recurrence", "head", "loss"]
-        fns = [lambda: self.stage_embed(c3d), self.stage_i2h, self.stage_recurrence, self.stage_head,
+        fns = [(lambda: self.stage_embed(emb=c3d)) if emb else (lambda: self.stage_embed(c3d)), self.stage_i2h, self.stage_recurrence, self.stage_head,
                lambda: self.loss_fwd(gt)]
         acc = dict((n, 0.0) for n in names)
         for _ in range(iters):

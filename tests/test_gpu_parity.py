@@ -280,3 +280,29 @@ def test_persistent_recurrence_matches_per_step_path(model, Ch, B, nsplit, mcast
         # bf16 copies (hop, rh) may differ by one bf16 ulp where the fp32 values differ in their last bits
         tol = 2.0 ** -7 if k in ("hop", "rh") else (1e-3 if k == "logits" else 1e-5)
         assert np.abs(a[k] - b[k]).max() <= tol * scale + 1e-7, (k, np.abs(a[k] - b[k]).max(), scale)
+
+
+@pytest.mark.parametrize("dtype", [0, 1])
+def test_grid14_long_sequence_convlstm_states(dtype):
+    """BASELINE config 4 family (ConvLSTM, 14x14 grid, long T): hidden and cell states after every step against the
+    oracle's cell recurrence (gaze_lstm.py:103-133 as written).  14x14 has no reference head, so states are compared."""
+    B, T, Ch, G, Cin = 2, 16, 128, 14, 512
+    p = O.init_params("gaze_lstm", hidden=Ch, T=T, grid=G, seed=5, regime="S")
+    rng = np.random.RandomState(11)
+    emb = SY.make_embedded(rng, B, T, G, Cin)
+    pe = dict(p)
+    pe["out_W"], pe["out_b"] = np.zeros((Ch, 1)), np.zeros((1,))
+    eng = GazeEngine("gaze_lstm", B=B, T=T, G=G, Ch=Ch, dtype=dtype, device="cuda", head="fc")
+    eng.load_tf_params(pe)
+    eng.forward(emb=torch.from_numpy(emb).cuda())
+    torch.cuda.synchronize()
+    pt = {k: torch.tensor(np.asarray(v), dtype=torch.float64) for k, v in p.items() if k.startswith("ConvLSTM")}
+    state = torch.zeros(B, G, G, 2 * Ch, dtype=torch.float64)
+    x = torch.from_numpy(emb).double()
+    tol = 1e-4 if dtype == 0 else 2e-2
+    for t in range(T):
+        h, state = O.lstm_rcn_cell(x[:, t], state, pt)
+        got = eng.read_state(t + 1)[1].cpu().double()
+        assert (got - h).abs().max() <= tol * max(1.0, float(h.abs().max())), t
+    c_fin = eng.read_state(T)[0].cpu().double()
+    assert (c_fin - state[..., :Ch]).abs().max() <= tol * max(1.0, float(state.abs().max()))
