@@ -140,6 +140,80 @@ __global__ void __launch_bounds__(kThreads) resize_bicubic_kernel(const double* 
   }
 }
 
+
+// Separable form of the same arithmetic.  The oracle's inner sum row_i = sum_j wc_j * src[r0+i, c0+j] depends only on
+// (source row, output column), so a CTA that owns a strip of kResizeCT output columns computes it ONCE per source row
+// (h x CT values in shared memory) and every output pixel is then 4 multiply-adds: ~4.4x fewer fp64 operations than
+// recomputing the 4x4 stencil per pixel, operation order unchanged -> results stay bit-identical to the oracle.
+constexpr int kResizeCT = 96;
+__global__ void __launch_bounds__(kThreads) resize_bicubic_sep_kernel(const double* __restrict__ src, double* __restrict__ dst,
+                                                                      int h, int w, int oh, int ow, int nearest) {
+  extern __shared__ double simg[];                    // [h*w] image | [h*CT] row sums | [oh*4] wr | [CT*4] wc | r0[oh] | c0[CT]
+  __shared__ double scr[32];
+  double* rint = simg + h * w;
+  double* wr = rint + h * kResizeCT;
+  double* wc = wr + oh * 4;
+  int* r0s = reinterpret_cast<int*>(wc + kResizeCT * 4);
+  int* c0s = r0s + oh;
+  const int f = blockIdx.y, cbase = blockIdx.x * kResizeCT;
+  const int ct = min(kResizeCT, ow - cbase);
+  const double* s = src + (long long)f * h * w;
+  double mn = CUDART_INF, mx = -CUDART_INF;
+  for (int i = threadIdx.x; i < h * w; i += blockDim.x) {
+    const double v = s[i];
+    simg[i] = v;
+    mn = nmin(mn, v); mx = nmax(mx, v);
+  }
+  mn = block_red<MinOp>(mn, scr);
+  mx = block_red<MaxOp>(mx, scr);
+  const double sr = dD((double)h, (double)oh), sc = dD((double)w, (double)ow);
+  for (int r = threadIdx.x; r < oh; r += blockDim.x) {
+    const double rs = dS(dM(dA((double)r, 0.5), sr), 0.5), rf = floor(rs);
+    cubic_w(dS(rs, rf), wr + 4 * r);
+    r0s[r] = (int)rf - 1;
+  }
+  for (int c = threadIdx.x; c < ct; c += blockDim.x) {
+    const double cs = dS(dM(dA((double)(cbase + c), 0.5), sc), 0.5), cf = floor(cs);
+    cubic_w(dS(cs, cf), wc + 4 * c);
+    c0s[c] = (int)cf - 1;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < h * ct; i += blockDim.x) {
+    const int ri = i / ct, c = i - ri * ct;
+    const int c0 = c0s[c];
+    double row = 0.0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      int ci = c0 + j;
+      const bool ok = ci >= 0 && ci < w;
+      ci = min(max(ci, 0), w - 1);
+      double v = simg[ri * w + ci];
+      if (!nearest && !ok) v = 0.0;
+      row = dA(row, dM(wc[4 * c + j], v));
+    }
+    rint[ri * kResizeCT + c] = row;
+  }
+  __syncthreads();
+  double* d = dst + (long long)f * oh * ow;
+  for (int o = threadIdx.x; o < oh * ct; o += blockDim.x) {
+    const int r = o / ct, c = o - r * ct;
+    const int r0 = r0s[r];
+    double out = 0.0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      int ri = r0 + i;
+      const bool rok = ri >= 0 && ri < h;
+      ri = min(max(ri, 0), h - 1);
+      double row = rint[ri * kResizeCT + c];
+      if (!nearest && !rok) row = 0.0;              // every tap of an outside row is zero in 'constant' mode
+      out = dA(out, dM(wr[4 * r + i], row));
+    }
+    out = (out < mn) ? mn : out;   // np.minimum(np.maximum(out, lo), hi); NaN stays NaN
+    out = (out > mx) ? mx : out;
+    d[(long long)r * ow + cbase + c] = out;
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // cluster helpers: slice of the frame owned by this CTA, and the rank-ordered exchange of partials
 // ---------------------------------------------------------------------------------------------
@@ -166,7 +240,7 @@ __device__ __forceinline__ double cluster_gather(cg::cluster_group& cl, double* 
 // sim / cc / nss (+ min, max, n_fix of the prediction) — evaluation_metrics.py:207-236, NSS per
 // oracle/metrics_oracle.py:237-246.  pred, gt float64 [n, hw]; fix uint8 [n, hw]; out [n, 8].
 // ---------------------------------------------------------------------------------------------
-__global__ void __cluster_dims__(kCluster, 1, 1) __launch_bounds__(kThreads)
+__global__ void __cluster_dims__(kCluster, 1, 1) __launch_bounds__(kThreads, 3)
 sim_cc_nss_kernel(const double* __restrict__ pred, const double* __restrict__ gt, const uint8_t* __restrict__ fix,
                   double* __restrict__ out, int n, int hw) {
   cg::cluster_group cl = cg::this_cluster();
@@ -186,17 +260,27 @@ sim_cc_nss_kernel(const double* __restrict__ pred, const double* __restrict__ gt
       const double2* p2 = reinterpret_cast<const double2*>(p);
       const double2* g2 = reinterpret_cast<const double2*>(g);
       const uchar2* f2 = reinterpret_cast<const uchar2*>(fx);
-#pragma unroll 4
-      for (int i = sl.begin / 2 + threadIdx.x; i < sl.end / 2; i += kThreads) {
-        const double2 a = p2[i], b = g2[i];
+      auto acc1 = [&](const double2& a, const double2& b, const uchar2& m) {
         sp += a.x + a.y; sg += b.x + b.y;
         mn = nmin(mn, nmin(a.x, a.y)); mx = nmax(mx, nmax(a.x, a.y));
-        if (fx) {
-          const uchar2 m = f2[i];
-          if (m.x) { spf += a.x; nf += 1.0; }
-          if (m.y) { spf += a.y; nf += 1.0; }
+        if (m.x) { spf += a.x; nf += 1.0; }
+        if (m.y) { spf += a.y; nf += 1.0; }
+      };
+      // 4 independent 16-byte loads per array in flight per thread (HBM latency x bandwidth needs ~40 KB per SM),
+      // accumulated in index order so the result does not depend on the batching
+      const int iend = sl.end / 2;
+      int i = sl.begin / 2 + threadIdx.x;
+      for (; i + 3 * kThreads < iend; i += 4 * kThreads) {
+        double2 a[4], b[4]; uchar2 m[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          a[u] = p2[i + u * kThreads]; b[u] = g2[i + u * kThreads];
+          m[u] = fx ? f2[i + u * kThreads] : make_uchar2(0, 0);
         }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) acc1(a[u], b[u], m[u]);
       }
+      for (; i < iend; i += kThreads) acc1(p2[i], g2[i], fx ? f2[i] : make_uchar2(0, 0));
     } else {
       for (int i = sl.begin + threadIdx.x; i < sl.end; i += kThreads) {
         const double a = p[i];
@@ -219,22 +303,33 @@ sim_cc_nss_kernel(const double* __restrict__ pred, const double* __restrict__ gt
     const double mp = tsp / (double)hw, mg = tsg / (double)hw;
     // ---- pass 2 (L2): centred second moments and the histogram intersection
     double vpp = 0.0, vgg = 0.0, vpg = 0.0, ssim = 0.0;
+    // gt/sum(gt) and pred/sum(pred) as multiplications by the reciprocals (<= 1 ulp per term, 1e-16 on the sum; the
+    // special cases of np.minimum(x/0, .) are preserved: 1/0 = inf, 0*inf = NaN)
+    const double rsp = dD(1.0, tsp), rsg = dD(1.0, tsg);
     if (vec) {
       const double2* p2 = reinterpret_cast<const double2*>(p);
       const double2* g2 = reinterpret_cast<const double2*>(g);
-#pragma unroll 4
-      for (int i = sl.begin / 2 + threadIdx.x; i < sl.end / 2; i += kThreads) {
-        const double2 a = p2[i], b = g2[i];
+      auto acc2 = [&](const double2& a, const double2& b) {
         const double ax = a.x - mp, ay = a.y - mp, bx = b.x - mg, by = b.y - mg;
         vpp += ax * ax + ay * ay; vgg += bx * bx + by * by; vpg += ax * bx + ay * by;
-        ssim += nmin(dD(b.x, tsg), dD(a.x, tsp)) + nmin(dD(b.y, tsg), dD(a.y, tsp));   // np.minimum propagates NaN
+        ssim += nmin(b.x * rsg, a.x * rsp) + nmin(b.y * rsg, a.y * rsp);   // np.minimum propagates NaN
+      };
+      const int iend = sl.end / 2;
+      int i = sl.begin / 2 + threadIdx.x;
+      for (; i + 3 * kThreads < iend; i += 4 * kThreads) {
+        double2 a[4], b[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) { a[u] = p2[i + u * kThreads]; b[u] = g2[i + u * kThreads]; }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) acc2(a[u], b[u]);
       }
+      for (; i < iend; i += kThreads) acc2(p2[i], g2[i]);
     } else {
       for (int i = sl.begin + threadIdx.x; i < sl.end; i += kThreads) {
         const double a = p[i], b = g[i];
         const double ax = a - mp, bx = b - mg;
         vpp += ax * ax; vgg += bx * bx; vpg += ax * bx;
-        ssim += nmin(dD(b, tsg), dD(a, tsp));
+        ssim += nmin(b * rsg, a * rsp);
       }
     }
     vpp = block_red<SumOp>(vpp, scr); vgg = block_red<SumOp>(vgg, scr);
@@ -294,17 +389,26 @@ auc_judd_kernel(const double* __restrict__ sal, const double* __restrict__ jitte
       const double2* s2 = reinterpret_cast<const double2*>(s);
       const double2* j2 = reinterpret_cast<const double2*>(jt);
       const uchar2* f2 = reinterpret_cast<const uchar2*>(fx);
-#pragma unroll 4
-      for (int i = sl.begin / 2 + threadIdx.x; i < sl.end / 2; i += kThreads) {
-        const double2 a = s2[i];
-        double2 j = make_double2(0.0, 0.0);
-        if (hj) j = j2[i];
-        const uchar2 m = f2[i];
+      auto px1 = [&](const double2& a, const double2& j, const uchar2& m) {
         const double x0 = judd_x(a.x, j.x, hj), x1 = judd_x(a.y, j.y, hj);
         mn = nmin(mn, nmin(x0, x1)); mx = nmax(mx, nmax(x0, x1));
         if (m.x) { int k = atomicAdd(&mycount, 1); if (k < kMaxFix) myfix[k] = x0; }
         if (m.y) { int k = atomicAdd(&mycount, 1); if (k < kMaxFix) myfix[k] = x1; }
+      };
+      const int iend = sl.end / 2;
+      int i = sl.begin / 2 + threadIdx.x;
+      for (; i + 3 * kThreads < iend; i += 4 * kThreads) {      // 4 independent 16-byte loads per array in flight
+        double2 a[4], j[4]; uchar2 m[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          a[u] = s2[i + u * kThreads];
+          j[u] = hj ? j2[i + u * kThreads] : make_double2(0.0, 0.0);
+          m[u] = f2[i + u * kThreads];
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) px1(a[u], j[u], m[u]);
       }
+      for (; i < iend; i += kThreads) px1(s2[i], hj ? j2[i] : make_double2(0.0, 0.0), f2[i]);
     } else {
       for (int i = sl.begin + threadIdx.x; i < sl.end; i += kThreads) {
         const double x0 = judd_x(s[i], hj ? jt[i] : 0.0, hj);
@@ -351,8 +455,13 @@ auc_judd_kernel(const double* __restrict__ sal, const double* __restrict__ jitte
         }
       // ---- pass 2 (L2): rank every pixel against the thresholds
       const double lowest = thr[total - 1];
+      // Pixels that cannot reach the lowest threshold skip the exact division: (x-min) < lowest*range*(1-1e-12) implies
+      // RN((x-min)/range) < lowest, so the integer counts stay bit-exact (NaN / zero range fall through to the exact path).
+      const double cut = lowest * range * (1.0 - 1e-12);
       auto rank_px = [&](double x) {
-        const double v = dD(dS(x, gmn), range);
+        const double d = dS(x, gmn);
+        if (d < cut) return;
+        const double v = dD(d, range);
         if (v >= lowest) {
           int lo = 0, hi = total - 1;                // first k with thr[k] <= v
           while (lo < hi) { const int mid = (lo + hi) >> 1; if (thr[mid] <= v) hi = mid; else lo = mid + 1; }
@@ -362,11 +471,21 @@ auc_judd_kernel(const double* __restrict__ sal, const double* __restrict__ jitte
       if (vec) {
         const double2* s2 = reinterpret_cast<const double2*>(s);
         const double2* j2 = reinterpret_cast<const double2*>(jt);
-#pragma unroll 4
-        for (int i = sl.begin / 2 + threadIdx.x; i < sl.end / 2; i += kThreads) {
+        const int iend = sl.end / 2;
+        int i = sl.begin / 2 + threadIdx.x;
+        for (; i + 3 * kThreads < iend; i += 4 * kThreads) {
+          double2 a[4], j[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            a[u] = s2[i + u * kThreads];
+            j[u] = hj ? j2[i + u * kThreads] : make_double2(0.0, 0.0);
+          }
+#pragma unroll
+          for (int u = 0; u < 4; ++u) { rank_px(judd_x(a[u].x, j[u].x, hj)); rank_px(judd_x(a[u].y, j[u].y, hj)); }
+        }
+        for (; i < iend; i += kThreads) {
           const double2 a = s2[i];
-          double2 j = make_double2(0.0, 0.0);
-          if (hj) j = j2[i];
+          const double2 j = hj ? j2[i] : make_double2(0.0, 0.0);
           rank_px(judd_x(a.x, j.x, hj));
           rank_px(judd_x(a.y, j.y, hj));
         }
@@ -546,6 +665,18 @@ int rgp_resize_bicubic(const double* src, double* dst, int n, int h, int w, int 
     return 0;
   }
   const size_t bytes = (size_t)h * w * sizeof(double);
+  const size_t sep_bytes = bytes + ((size_t)h * rgp::kResizeCT + (size_t)oh * 4 + rgp::kResizeCT * 4) * sizeof(double) +
+                           ((size_t)oh + rgp::kResizeCT) * sizeof(int);
+  if (sep_bytes <= 200 * 1024) {
+    static bool attr_sep = false;
+    if (!attr_sep) {
+      cudaFuncSetAttribute(rgp::resize_bicubic_sep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+      attr_sep = true;
+    }
+    dim3 grid((ow + rgp::kResizeCT - 1) / rgp::kResizeCT, n);
+    rgp::resize_bicubic_sep_kernel<<<grid, rgp::kThreads, sep_bytes, s>>>(src, dst, h, w, oh, ow, mode_nearest);
+    return rgp::check_launch("rgp_resize_bicubic");
+  }
   const int in_smem = bytes <= 160 * 1024;
   static bool attr = false;
   if (!attr) {
