@@ -325,10 +325,26 @@ def main():
         evs = eng.time_stages(c3d_d, gt_d, iters=3, emb=emb_entry)
         i2h_ms = evs["i2h"]
         ach = fl["i2h"] * B * T / (i2h_ms * 1e-3) / 1e12
+        # DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum) from the committed ncu --set full captures
+        # of exactly this configuration; None for any other configuration
+        default_cfg = (args.model, B, T, Ch, G, args.entry, dtype) == ("gaze_grcn", 256, 35, 256, 7, "c3d", 1)
         roof = {"kernel": "tapgemm i2h (3x3 SAME conv, all T frames, M=%d N=%d K=9x512)" % (T * B * eng.S, eng.ngx * Ch),
                 "bound": "tensor", "achieved": ach, "peak": tf_sus, "unit": "TFLOP/s", "frac": ach / tf_sus,
-                "peak_source": which + " (sustained bf16; burst %.1f)" % tf_burst, "traffic": None,
+                "peak_source": which + " (sustained bf16; burst %.1f)" % tf_burst,
+                "traffic": 2.3087e9 if default_cfg else None,
+                "traffic_source": "profiles/r01_ncu_full_fwd_pass5.txt (0.596 GB read + 1.713 GB written per launch)" if default_cfg else None,
                 "ms_per_launch": i2h_ms, "stage_ms": evs}
+        # second view: the recurrence (persistent kernel when the engine picked it).  Algorithmic work per frame
+        # (SURVEY 8d): 2*3*(3G-2)^2*Ch^2 flop; bytes = read 3 gate pre-activations + write h, fp32
+        rec_ms = evs["recurrence"]
+        rec_bytes = 4.0 * Ch * G * G * 4 * B * T
+        rec = {"kernel": ("gru_seq (persistent ConvGRU recurrence, all T steps in one launch)" if eng.use_seq else
+                          "per-step tap-GEMMs (%d launches)" % (2 * T)),
+               "ms": rec_ms, "tensor_TFLOPs": fl["h2h"] * B * T / (rec_ms * 1e-3) / 1e12,
+               "tensor_frac": fl["h2h"] * B * T / (rec_ms * 1e-3) / 1e12 / tf_sus,
+               "hbm_GBps": rec_bytes / (rec_ms * 1e-3) / 1e9, "hbm_frac": rec_bytes / (rec_ms * 1e-3) / 1e9 / hbm,
+               "traffic": 3.6796e9 if (default_cfg and eng.use_seq) else None}
+        roof["recurrence"] = rec
         if train:
             fwd()
             roof["stage_ms_bwd"] = eng.time_backward(iters=3)

@@ -22,6 +22,11 @@ namespace {
 
 constexpr int kCluster = 8;
 constexpr int kThreads = 256;
+// Two-pass streaming kernels (sim/cc/NSS, AUC-Judd): 256 threads, up to 3 CTAs per SM, one cluster per frame, as many
+// clusters as SMs.  Measured alternative (one 512-thread CTA per SM, sm_count/8 clusters, so that the frames in flight
+// stay L2-resident between the passes): 2x SLOWER (sim 1.07 -> 2.22 ms, AUC-Judd 1.65 -> 3.23 ms per 1024 frames) -
+// per-frame latency (cluster syncs, block reductions), not DRAM bytes, is what the extra clusters hide.
+constexpr int kStreamThreads = 256;
 constexpr int kMaxFix = 1024;      // fixations per frame held in shared memory by the AUC kernels
 
 __device__ __forceinline__ double dA(double a, double b) { return __dadd_rn(a, b); }
@@ -240,9 +245,10 @@ __device__ __forceinline__ double cluster_gather(cg::cluster_group& cl, double* 
 // sim / cc / nss (+ min, max, n_fix of the prediction) — evaluation_metrics.py:207-236, NSS per
 // oracle/metrics_oracle.py:237-246.  pred, gt float64 [n, hw]; fix uint8 [n, hw]; out [n, 8].
 // ---------------------------------------------------------------------------------------------
-__global__ void __cluster_dims__(kCluster, 1, 1) __launch_bounds__(kThreads, 3)
+__global__ void __cluster_dims__(kCluster, 1, 1) __launch_bounds__(kStreamThreads, 3)
 sim_cc_nss_kernel(const double* __restrict__ pred, const double* __restrict__ gt, const uint8_t* __restrict__ fix,
                   double* __restrict__ out, int n, int hw) {
+  const int nt = (int)blockDim.x;
   cg::cluster_group cl = cg::this_cluster();
   __shared__ double scr[32];
   __shared__ double part1[8], part2[8], tot[16];
@@ -270,19 +276,19 @@ sim_cc_nss_kernel(const double* __restrict__ pred, const double* __restrict__ gt
       // accumulated in index order so the result does not depend on the batching
       const int iend = sl.end / 2;
       int i = sl.begin / 2 + threadIdx.x;
-      for (; i + 3 * kThreads < iend; i += 4 * kThreads) {
+      for (; i + 3 * nt < iend; i += 4 * nt) {
         double2 a[4], b[4]; uchar2 m[4];
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
-          a[u] = p2[i + u * kThreads]; b[u] = g2[i + u * kThreads];
-          m[u] = fx ? f2[i + u * kThreads] : make_uchar2(0, 0);
+          a[u] = p2[i + u * nt]; b[u] = g2[i + u * nt];
+          m[u] = fx ? f2[i + u * nt] : make_uchar2(0, 0);
         }
 #pragma unroll
         for (int u = 0; u < 4; ++u) acc1(a[u], b[u], m[u]);
       }
-      for (; i < iend; i += kThreads) acc1(p2[i], g2[i], fx ? f2[i] : make_uchar2(0, 0));
+      for (; i < iend; i += nt) acc1(p2[i], g2[i], fx ? f2[i] : make_uchar2(0, 0));
     } else {
-      for (int i = sl.begin + threadIdx.x; i < sl.end; i += kThreads) {
+      for (int i = sl.begin + threadIdx.x; i < sl.end; i += nt) {
         const double a = p[i];
         sp += a; sg += g[i]; mn = nmin(mn, a); mx = nmax(mx, a);
         if (fx && fx[i]) { spf += a; nf += 1.0; }
@@ -316,16 +322,16 @@ sim_cc_nss_kernel(const double* __restrict__ pred, const double* __restrict__ gt
       };
       const int iend = sl.end / 2;
       int i = sl.begin / 2 + threadIdx.x;
-      for (; i + 3 * kThreads < iend; i += 4 * kThreads) {
+      for (; i + 3 * nt < iend; i += 4 * nt) {
         double2 a[4], b[4];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) { a[u] = p2[i + u * kThreads]; b[u] = g2[i + u * kThreads]; }
+        for (int u = 0; u < 4; ++u) { a[u] = p2[i + u * nt]; b[u] = g2[i + u * nt]; }
 #pragma unroll
         for (int u = 0; u < 4; ++u) acc2(a[u], b[u]);
       }
-      for (; i < iend; i += kThreads) acc2(p2[i], g2[i]);
+      for (; i < iend; i += nt) acc2(p2[i], g2[i]);
     } else {
-      for (int i = sl.begin + threadIdx.x; i < sl.end; i += kThreads) {
+      for (int i = sl.begin + threadIdx.x; i < sl.end; i += nt) {
         const double a = p[i], b = g[i];
         const double ax = a - mp, bx = b - mg;
         vpp += ax * ax; vgg += bx * bx; vpg += ax * bx;
@@ -359,10 +365,11 @@ sim_cc_nss_kernel(const double* __restrict__ pred, const double* __restrict__ gt
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ double judd_x(double s, double j, bool has_j) { return has_j ? dA(s, dM(j, 1e-7)) : s; }
 
-__global__ void __cluster_dims__(kCluster, 1, 1) __launch_bounds__(kThreads)
+__global__ void __cluster_dims__(kCluster, 1, 1) __launch_bounds__(kStreamThreads, 2)
 auc_judd_kernel(const double* __restrict__ sal, const double* __restrict__ jitter, const uint8_t* __restrict__ fix,
                 double* __restrict__ thr_out, long long* __restrict__ counts, double* __restrict__ auc,
                 int n, int hw, int maxfix) {
+  const int nt = (int)blockDim.x;
   cg::cluster_group cl = cg::this_cluster();
   __shared__ double scr[32];
   __shared__ double part[4];
@@ -381,7 +388,7 @@ auc_judd_kernel(const double* __restrict__ sal, const double* __restrict__ jitte
     const double* jt = hj ? jitter + (long long)f * hw : nullptr;
     const uint8_t* fx = fix + (long long)f * hw;
     if (threadIdx.x == 0) mycount = 0;
-    for (int i = threadIdx.x; i < kMaxFix; i += kThreads) hist[i] = 0;
+    for (int i = threadIdx.x; i < kMaxFix; i += nt) hist[i] = 0;
     __syncthreads();
     // ---- pass 1 (HBM): extrema of the jittered map, values at the fixations
     double mn = CUDART_INF, mx = -CUDART_INF;
@@ -397,20 +404,20 @@ auc_judd_kernel(const double* __restrict__ sal, const double* __restrict__ jitte
       };
       const int iend = sl.end / 2;
       int i = sl.begin / 2 + threadIdx.x;
-      for (; i + 3 * kThreads < iend; i += 4 * kThreads) {      // 4 independent 16-byte loads per array in flight
+      for (; i + 3 * nt < iend; i += 4 * nt) {      // 4 independent 16-byte loads per array in flight
         double2 a[4], j[4]; uchar2 m[4];
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
-          a[u] = s2[i + u * kThreads];
-          j[u] = hj ? j2[i + u * kThreads] : make_double2(0.0, 0.0);
-          m[u] = f2[i + u * kThreads];
+          a[u] = s2[i + u * nt];
+          j[u] = hj ? j2[i + u * nt] : make_double2(0.0, 0.0);
+          m[u] = f2[i + u * nt];
         }
 #pragma unroll
         for (int u = 0; u < 4; ++u) px1(a[u], j[u], m[u]);
       }
-      for (; i < iend; i += kThreads) px1(s2[i], hj ? j2[i] : make_double2(0.0, 0.0), f2[i]);
+      for (; i < iend; i += nt) px1(s2[i], hj ? j2[i] : make_double2(0.0, 0.0), f2[i]);
     } else {
-      for (int i = sl.begin + threadIdx.x; i < sl.end; i += kThreads) {
+      for (int i = sl.begin + threadIdx.x; i < sl.end; i += nt) {
         const double x0 = judd_x(s[i], hj ? jt[i] : 0.0, hj);
         mn = nmin(mn, x0); mx = nmax(mx, x0);
         if (fx[i]) { int k = atomicAdd(&mycount, 1); if (k < kMaxFix) myfix[k] = x0; }
@@ -436,14 +443,14 @@ auc_judd_kernel(const double* __restrict__ sal, const double* __restrict__ jitte
       for (int q = 0; q < kCluster; ++q) {
         const int cq = (int)cl.map_shared_rank(part, q)[2];
         const double* lq = cl.map_shared_rank(myfix, q);
-        for (int i = threadIdx.x; i < cq; i += kThreads) thr[base + i] = dD(dS(lq[i], gmn), range);
+        for (int i = threadIdx.x; i < cq; i += nt) thr[base + i] = dD(dS(lq[i], gmn), range);
         base += cq;
       }
-      for (int i = total + threadIdx.x; i < np2; i += kThreads) thr[i] = -CUDART_INF;
+      for (int i = total + threadIdx.x; i < np2; i += nt) thr[i] = -CUDART_INF;
       __syncthreads();
       for (int k = 2; k <= np2; k <<= 1)            // bitonic sort, descending (NaN never reaches here unless range = 0)
         for (int j = k >> 1; j > 0; j >>= 1) {
-          for (int i = threadIdx.x; i < np2; i += kThreads) {
+          for (int i = threadIdx.x; i < np2; i += nt) {
             const int l = i ^ j;
             if (l > i) {
               const double a = thr[i], b = thr[l];
@@ -473,37 +480,37 @@ auc_judd_kernel(const double* __restrict__ sal, const double* __restrict__ jitte
         const double2* j2 = reinterpret_cast<const double2*>(jt);
         const int iend = sl.end / 2;
         int i = sl.begin / 2 + threadIdx.x;
-        for (; i + 3 * kThreads < iend; i += 4 * kThreads) {
+        for (; i + 3 * nt < iend; i += 4 * nt) {
           double2 a[4], j[4];
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
-            a[u] = s2[i + u * kThreads];
-            j[u] = hj ? j2[i + u * kThreads] : make_double2(0.0, 0.0);
+            a[u] = s2[i + u * nt];
+            j[u] = hj ? j2[i + u * nt] : make_double2(0.0, 0.0);
           }
 #pragma unroll
           for (int u = 0; u < 4; ++u) { rank_px(judd_x(a[u].x, j[u].x, hj)); rank_px(judd_x(a[u].y, j[u].y, hj)); }
         }
-        for (; i < iend; i += kThreads) {
+        for (; i < iend; i += nt) {
           const double2 a = s2[i];
           const double2 j = hj ? j2[i] : make_double2(0.0, 0.0);
           rank_px(judd_x(a.x, j.x, hj));
           rank_px(judd_x(a.y, j.y, hj));
         }
       } else {
-        for (int i = sl.begin + threadIdx.x; i < sl.end; i += kThreads) rank_px(judd_x(s[i], hj ? jt[i] : 0.0, hj));
+        for (int i = sl.begin + threadIdx.x; i < sl.end; i += nt) rank_px(judd_x(s[i], hj ? jt[i] : 0.0, hj));
       }
     }
     cl.sync();
     if (rank == 0) {
       if (ok) {
-        for (int k = threadIdx.x; k < total; k += kThreads) {
+        for (int k = threadIdx.x; k < total; k += nt) {
           int c = 0;
           for (int q = 0; q < kCluster; ++q) c += cl.map_shared_rank(hist, q)[k];
           hist[k] = c;                                // rank 0's own bins were read before being overwritten (same k, same thread)
         }
       }
       __syncthreads();
-      for (int k = threadIdx.x; k < maxfix; k += kThreads) {
+      for (int k = threadIdx.x; k < maxfix; k += nt) {
         thr_out[(long long)f * maxfix + k] = (ok && k < total) ? thr[k] : CUDART_NAN;
         if (!ok || k >= total) counts[(long long)f * maxfix + k] = -1;
       }
@@ -695,7 +702,7 @@ int rgp_sim_cc_nss(const double* pred, const double* gt, const uint8_t* fix, dou
   RGP_CHECK_ARG(n >= 0 && hw > 0, "rgp_sim_cc_nss: n=%d hw=%d", n, hw);
   if (n == 0) return 0;
   const int ncl = n < sm_count() ? n : sm_count();
-  rgp::sim_cc_nss_kernel<<<ncl * rgp::kCluster, rgp::kThreads, 0, (cudaStream_t)stream>>>(pred, gt, fix, out, n, hw);
+  rgp::sim_cc_nss_kernel<<<ncl * rgp::kCluster, rgp::kStreamThreads, 0, (cudaStream_t)stream>>>(pred, gt, fix, out, n, hw);
   return rgp::check_launch("rgp_sim_cc_nss");
 }
 
@@ -705,7 +712,7 @@ int rgp_auc_judd(const double* sal, const double* jitter, const uint8_t* fix, do
   RGP_CHECK_ARG(maxfix >= 1 && maxfix <= rgp::kMaxFix, "rgp_auc_judd: maxfix=%d must be in 1..%d", maxfix, rgp::kMaxFix);
   if (n == 0) return 0;
   const int ncl = n < sm_count() ? n : sm_count();
-  rgp::auc_judd_kernel<<<ncl * rgp::kCluster, rgp::kThreads, 0, (cudaStream_t)stream>>>(sal, jitter, fix, thr, counts,
+  rgp::auc_judd_kernel<<<ncl * rgp::kCluster, rgp::kStreamThreads, 0, (cudaStream_t)stream>>>(sal, jitter, fix, thr, counts,
                                                                                       auc, n, hw, maxfix);
   return rgp::check_launch("rgp_auc_judd");
 }
