@@ -229,6 +229,24 @@ int rgp_auc_sampled(const double* sal, const uint8_t* fix, const int* idx, const
                     double* auc, int* tpc, int* fpc, int n, int hw, int nrows, int nrep, double step,
                     int nthr_max, int maxfix, void* stream);
 
+/* ---- fused resize + metric (evaluation_metrics.py:246-257 followed by :42-236) --------------
+ * The same three metric kernels with the bicubic enlargement of the model-resolution map(s) [n,h,w] to the fixation
+ * map's size [oh,ow] evaluated on the fly (never written to HBM).  Every resized value is bit-identical to
+ * rgp_resize_bicubic's, so thresholds / integer counts / AUCs equal the two-step path exactly; the sums of
+ * sim / cc / NSS are taken strip-major (differences ~1e-16).  fix / jitter / idx / outputs as in the plain calls. */
+/* 1 if the strip tables of an h x w -> oh x ow enlargement fit in shared memory (else use the two-step path) */
+int rgp_metrics_fused_fits(int h, int w, int oh, int ow);
+int rgp_sim_cc_nss_resized(const double* pred_src, const double* gt_src, const uint8_t* fix, double* out,
+                           int n, int h, int w, int oh, int ow, int mode_nearest, void* stream);
+int rgp_auc_judd_resized(const double* sal_src, const double* jitter, const uint8_t* fix, double* thr,
+                         long long* counts, double* auc, int n, int h, int w, int oh, int ow, int mode_nearest,
+                         int maxfix, void* stream);
+/* minmax: per-frame (min,max) of the RESIZED map (columns 3,4 of rgp_sim_cc_nss_resized's output) */
+int rgp_auc_sampled_resized(const double* sal_src, const uint8_t* fix, const int* idx, const double* minmax,
+                            int mm_stride, double* auc, int* tpc, int* fpc, int n, int h, int w, int oh, int ow,
+                            int mode_nearest, int nrows, int nrep, double step, int nthr_max, int maxfix,
+                            void* stream);
+
 const char* rgp_last_error(void);
 int rgp_version(void);
 /* 1 if the tcgen05 engine can run on the current device (sm_100), else 0 */

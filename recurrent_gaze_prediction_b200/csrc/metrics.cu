@@ -548,34 +548,92 @@ auc_judd_kernel(const double* __restrict__ sal, const double* __restrict__ jitte
 // AUC = trapz; output = mean over repetitions.  tpc/fpc (optional) int32 [n, nrep, nthr_max]: the integer counts at
 // threshold i*step (-1 beyond the repetition's list) — the bit-exact contract.
 // ---------------------------------------------------------------------------------------------
+// FUSED: `sal` holds the SOURCE maps [n, h*w]; the value of a resized pixel is evaluated where it is gathered (the 4x4
+// stencil of resize_bicubic_kernel, same operation order -> bit-identical to the materialised map).
+// The normalised values of the negatives are gathered once into shared memory (`stash` != 0: nrows*nrep doubles fit),
+// so the per-threshold count loops do not repeat the random gathers.
+__device__ __forceinline__ double resized_at(const double* img, int h, int w, int oh, int ow, int p, int nearest,
+                                             double mn, double mx) {
+  const double sr = dD((double)h, (double)oh), sc = dD((double)w, (double)ow);
+  const int r = p / ow, c = p - r * ow;
+  const double rs = dS(dM(dA((double)r, 0.5), sr), 0.5), cs = dS(dM(dA((double)c, 0.5), sc), 0.5);
+  const double rf = floor(rs), cf = floor(cs);
+  double wr[4], wc[4];
+  cubic_w(dS(rs, rf), wr);
+  cubic_w(dS(cs, cf), wc);
+  const int r0 = (int)rf - 1, c0 = (int)cf - 1;
+  double out = 0.0;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    int ri = r0 + i;
+    const bool rok = ri >= 0 && ri < h;
+    ri = min(max(ri, 0), h - 1);
+    double row = 0.0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      int ci = c0 + j;
+      const bool ok = rok && ci >= 0 && ci < w;
+      ci = min(max(ci, 0), w - 1);
+      double v = img[ri * w + ci];
+      if (!nearest && !ok) v = 0.0;
+      row = dA(row, dM(wc[j], v));
+    }
+    out = dA(out, dM(wr[i], row));
+  }
+  out = (out < mn) ? mn : out;
+  out = (out > mx) ? mx : out;
+  return out;
+}
+
+template <bool FUSED>
 __global__ void __launch_bounds__(kThreads)
 auc_sampled_kernel(const double* __restrict__ sal, const uint8_t* __restrict__ fix, const int* __restrict__ idx,
                    const double* __restrict__ minmax, int mm_stride, double* __restrict__ auc,
                    int* __restrict__ tpc, int* __restrict__ fpc, int n, int hw, int nrows, int nrep, double step,
-                   int nthr_max, int maxfix) {
+                   int nthr_max, int maxfix, int h, int w, int ow, int nearest, int stash) {
   __shared__ double sfix[kMaxFix];
   __shared__ int pos[kMaxFix];
   __shared__ int cnt;
-  extern __shared__ double rep_auc[];   // [nrep]
+  __shared__ double scr[32];
+  extern __shared__ double rep_auc[];   // [nrep] | FUSED: source image [h*w] | stash: negatives [nrows*nrep]
+  double* simg = rep_auc + nrep;
+  double* negv = simg + (FUSED ? h * w : 0);
+  const int oh = FUSED ? hw / ow : 0;
+  const long long src_stride = FUSED ? (long long)h * w : (long long)hw;
   for (int f = blockIdx.x; f < n; f += gridDim.x) {
-    const double* s = sal + (long long)f * hw;
+    const double* s = sal + (long long)f * src_stride;
     const uint8_t* fx = fix + (long long)f * hw;
     const double mn = minmax[(long long)f * mm_stride], range = dS(minmax[(long long)f * mm_stride + 1], mn);
     __syncthreads();
     if (threadIdx.x == 0) cnt = 0;
+    double smn = CUDART_INF, smx = -CUDART_INF;      // range of the source map (the resize clips to it)
+    if (FUSED) {
+      for (int i = threadIdx.x; i < h * w; i += kThreads) {
+        const double v = s[i];
+        simg[i] = v;
+        smn = nmin(smn, v); smx = nmax(smx, v);
+      }
+      smn = block_red<MinOp>(smn, scr);
+      smx = block_red<MaxOp>(smx, scr);
+    }
     __syncthreads();
+    // normalised saliency at pixel p
+    auto sval = [&](int p) {
+      const double v = FUSED ? resized_at(simg, h, w, oh, ow, p, nearest, smn, smx) : s[p];
+      return dD(dS(v, mn), range);
+    };
     // fixation positions (16 pixels per load when the frame is 16-byte aligned)
     if ((hw & 15) == 0) {
       const uint4* f4 = reinterpret_cast<const uint4*>(fx);
       for (int i = threadIdx.x; i < hw / 16; i += kThreads) {
         const uint4 v = f4[i];
         if (v.x | v.y | v.z | v.w) {
-          const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+          const uint32_t wd[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
           for (int q = 0; q < 4; ++q)
 #pragma unroll
             for (int b = 0; b < 4; ++b)
-              if ((w[q] >> (8 * b)) & 0xffu) { int k = atomicAdd(&cnt, 1); if (k < kMaxFix) pos[k] = i * 16 + q * 4 + b; }
+              if ((wd[q] >> (8 * b)) & 0xffu) { int k = atomicAdd(&cnt, 1); if (k < kMaxFix) pos[k] = i * 16 + q * 4 + b; }
         }
       }
     } else {
@@ -585,19 +643,28 @@ auc_sampled_kernel(const double* __restrict__ sal, const uint8_t* __restrict__ f
     __syncthreads();
     const int nfix = cnt;
     const bool ok = nfix > 0 && nfix <= maxfix && nfix <= kMaxFix;
-    if (ok)
-      for (int i = threadIdx.x; i < nfix; i += kThreads) sfix[i] = dD(dS(s[pos[i]], mn), range);
+    const int* ixf = idx + (long long)f * nrows * nrep;
+    if (ok) {
+      for (int i = threadIdx.x; i < nfix; i += kThreads) sfix[i] = sval(pos[i]);
+      if (stash)                                     // absent rows: -inf never reaches a threshold, never raises the max
+        for (int k = threadIdx.x; k < nrows * nrep; k += kThreads) {
+          const int p = ixf[k];
+          negv[k] = (p >= 0) ? sval(p) : -CUDART_INF;
+        }
+    }
     __syncthreads();
     for (int rep = threadIdx.x; rep < nrep; rep += kThreads) {
       double a = CUDART_NAN;
       if (ok) {
-        const int* ix = idx + (long long)f * nrows * nrep + rep;
+        const int* ix = ixf + rep;
+        auto neg = [&](int i) {
+          if (stash) return negv[i * nrep + rep];
+          const int p = ix[(long long)i * nrep];
+          return (p >= 0) ? sval(p) : -CUDART_INF;
+        };
         double mx = -CUDART_INF;
         for (int i = 0; i < nfix; ++i) mx = nmax(mx, sfix[i]);
-        for (int i = 0; i < nrows; ++i) {
-          const int p = ix[(long long)i * nrep];
-          if (p >= 0) mx = nmax(mx, dD(dS(s[p], mn), range));
-        }
+        for (int i = 0; i < nrows; ++i) mx = nmax(mx, neg(i));
         int L = (mx > 0.0) ? (int)ceil(dD(mx, step)) : 0;       // len(np.arange(0, mx, step))
         if (L > nthr_max) L = nthr_max;
         double tp0 = 0.0, fp0 = 0.0, acc = 0.0;
@@ -606,10 +673,7 @@ auc_sampled_kernel(const double* __restrict__ sal, const uint8_t* __restrict__ f
           const double th = dM((double)t, step);
           int ct = 0, cf = 0;
           for (int i = 0; i < nfix; ++i) ct += (sfix[i] >= th) ? 1 : 0;
-          for (int i = 0; i < nrows; ++i) {
-            const int p = ix[(long long)i * nrep];
-            if (p >= 0) cf += (dD(dS(s[p], mn), range) >= th) ? 1 : 0;
-          }
+          for (int i = 0; i < nrows; ++i) cf += (neg(i) >= th) ? 1 : 0;
           if (tpc) { tpc[((long long)f * nrep + rep) * nthr_max + t] = ct; fpc[((long long)f * nrep + rep) * nthr_max + t] = cf; }
           const double tp1 = (double)ct / dn, fp1 = (double)cf / dn;
           acc += (fp1 - fp0) * (tp1 + tp0) / 2.0;
@@ -630,6 +694,390 @@ auc_sampled_kernel(const double* __restrict__ sal, const uint8_t* __restrict__ f
       for (int r = 0; r < nrep; ++r) sum += rep_auc[r];
       auc[f] = (nfix > 0 && !ok) ? -1.0 : sum / (double)nrep;   // -1: more fixations than maxfix (host raises)
     }
+  }
+}
+
+// =============================================================================================
+// Fused resize + metric kernels (the step before every metric).
+//
+// The model emits 49x49 maps; the metrics are defined on their bicubic enlargement to the fixation map's size
+// (evaluation_metrics.py:248,255).  Materialising the enlargement costs 2 x 1.38 MB of float64 per frame written and
+// read back at least twice; here it never exists: a frame goes to a cluster of 8 CTAs, each CTA owns a strip of
+// ceil(ow/8) output columns, keeps the source map (19 KB) and the separable row sums of its strip
+// (h x strip, resize_bicubic_sep_kernel's table) in shared memory, and evaluates every resized pixel as 4 multiply-adds
+// where it is consumed - in both passes.  Arithmetic and operation order per pixel are those of rgp_resize_bicubic,
+// so every resized VALUE is bit-identical to the materialised path: thresholds and integer counts do not change;
+// the sums of sim / cc / NSS are taken in a different order (strip-major), which moves them by ~1e-16.
+// What is left of the HBM traffic is the fixation map (1 B/px) and, for AUC-Judd, the host-drawn jitter (8 B/px).
+// =============================================================================================
+struct FusedGeom {
+  int h, w, oh, ow, cts;          // cts = strip width (columns per CTA)
+  size_t smem_bytes(int nmaps) const {
+    return ((size_t)h * w + (size_t)nmaps * h * cts + 1 + (size_t)oh * 4 + (size_t)cts * 4) * sizeof(double) +
+           ((size_t)oh + cts) * sizeof(int);
+  }
+};
+
+// frame-independent tables of this CTA's strip: row weights / first source row of every output row, column weights /
+// first source column of every strip column
+__device__ __forceinline__ void fused_tables(int h, int w, int oh, int ow, int cbase, int ct, double* wr, double* wc,
+                                             int* r0s, int* c0s) {
+  const double sr = dD((double)h, (double)oh), sc = dD((double)w, (double)ow);
+  for (int r = threadIdx.x; r < oh; r += blockDim.x) {
+    const double rs = dS(dM(dA((double)r, 0.5), sr), 0.5), rf = floor(rs);
+    cubic_w(dS(rs, rf), wr + 4 * r);
+    r0s[r] = (int)rf - 1;
+  }
+  for (int c = threadIdx.x; c < ct; c += blockDim.x) {
+    const double cs = dS(dM(dA((double)(cbase + c), 0.5), sc), 0.5), cf = floor(cs);
+    cubic_w(dS(cs, cf), wc + 4 * c);
+    c0s[c] = (int)cf - 1;
+  }
+}
+
+// source frame -> shared image, its (NaN-propagating) range, and the strip's row sums.  Ends with a barrier.
+__device__ __forceinline__ void fused_rowsums(const double* __restrict__ s, int h, int w, int ct, int cts, int nearest,
+                                              double* simg, double* rint, const double* wc, const int* c0s, double* scr,
+                                              double& mn, double& mx) {
+  mn = CUDART_INF; mx = -CUDART_INF;
+  __syncthreads();                                   // previous users of simg / rint are done
+  for (int i = threadIdx.x; i < h * w; i += blockDim.x) {
+    const double v = s[i];
+    simg[i] = v;
+    mn = nmin(mn, v); mx = nmax(mx, v);
+  }
+  mn = block_red<MinOp>(mn, scr);
+  mx = block_red<MaxOp>(mx, scr);
+  for (int i = threadIdx.x; i < h * ct; i += blockDim.x) {
+    const int ri = i / ct, c = i - ri * ct;
+    const int c0 = c0s[c];
+    double row = 0.0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      int ci = c0 + j;
+      const bool ok = ci >= 0 && ci < w;
+      ci = min(max(ci, 0), w - 1);
+      double v = simg[ri * w + ci];
+      if (!nearest && !ok) v = 0.0;
+      row = dA(row, dM(wc[4 * c + j], v));
+    }
+    rint[ri * cts + c] = row;
+  }
+  __syncthreads();
+}
+
+// Walk of this CTA's strip.  A thread owns ONE column of the strip and a contiguous segment of output rows: going down
+// a column, the 4 source rows an output pixel reads (row sums rint[r0..r0+3][c]) change only every oh/h (~7) rows, so
+// they live in registers and shared memory is touched once per source-row change instead of 4x per pixel; what remains
+// per pixel is the 4 multiply-adds with the row weights (two broadcast 16-byte shared loads) and the clip.
+// Rows are taken in blocks of RB: `load(r, c)` (the global reads of the block: fixation byte, jitter) is issued for the
+// whole block before the arithmetic (argument: pixel offset r*ow + c), so RB independent loads are in flight per
+// thread; `use(r, c, v, payload)` consumes
+// the resized value(s) v[NM].  Every value is computed by the operation sequence of resize_bicubic_sep_kernel.
+constexpr int kFusedThreads = 384;
+template <int NM, int RB, class P, class LoadF, class UseF>
+__device__ __forceinline__ void walk_strip(const double* const* rint, const double* wr, const int* r0s, int h, int oh,
+                                           int ow, int ct, int cts, int nearest, const double* mnv, const double* mxv,
+                                           LoadF&& load, UseF&& use) {
+  int cp = (ct + 31) & ~31;                           // column slots: whole warps, so a warp shares its row segment
+  if (cp > (int)blockDim.x) cp = (int)blockDim.x & ~31;
+  if (cp < 32) cp = 32;
+  const int nseg = max(1, (int)blockDim.x / cp);
+  const int seg = (int)threadIdx.x / cp, cl = (int)threadIdx.x - seg * cp;
+  if (seg >= nseg) return;
+  const int ra = (int)(((long long)oh * seg) / nseg), rb = (int)(((long long)oh * (seg + 1)) / nseg);
+  for (int c = cl; c < ct; c += cp) {
+    int cur = INT_MIN;
+    double tap[NM][4];
+#pragma unroll
+    for (int k = 0; k < NM; ++k)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) tap[k][i] = 0.0;
+    for (int r1 = ra; r1 < rb; r1 += RB) {
+      P pay[RB];
+      const long long off = (long long)r1 * ow + c;    // pixel offset of (r1, c) inside the strip's frame view
+#pragma unroll
+      for (int u = 0; u < RB; ++u)
+        if (r1 + u < rb) pay[u] = load(off + u * ow);
+#pragma unroll
+      for (int u = 0; u < RB; ++u) {
+        const int r = r1 + u;
+        if (r < rb) {
+          const int r0 = r0s[r];
+          if (r0 != cur) {                            // warp-uniform
+            cur = r0;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              int ri = r0 + i;
+              const bool zero = !nearest && !(ri >= 0 && ri < h);
+              ri = min(max(ri, 0), h - 1);
+#pragma unroll
+              for (int k = 0; k < NM; ++k) tap[k][i] = zero ? 0.0 : rint[k][ri * cts + c];
+            }
+          }
+          const double2 w01 = *reinterpret_cast<const double2*>(wr + 4 * r);
+          const double2 w23 = *reinterpret_cast<const double2*>(wr + 4 * r + 2);
+          double v[NM];
+#pragma unroll
+          for (int k = 0; k < NM; ++k) {
+            double out = dA(0.0, dM(w01.x, tap[k][0]));
+            out = dA(out, dM(w01.y, tap[k][1]));
+            out = dA(out, dM(w23.x, tap[k][2]));
+            out = dA(out, dM(w23.y, tap[k][3]));
+            if (out < mnv[k] || out > mxv[k]) {       // overshoot is rare: a branch, not four selects per pixel
+              out = (out < mnv[k]) ? mnv[k] : out;
+              out = (out > mxv[k]) ? mxv[k] : out;
+            }
+            v[k] = out;
+          }
+          use(r, c, v, pay[u]);
+        }
+      }
+    }
+  }
+}
+
+// carve the dynamic shared memory of a fused kernel
+struct FusedSmem {
+  double *simg, *rintA, *rintB, *wr, *wc;
+  int *r0s, *c0s;
+};
+__device__ __forceinline__ FusedSmem fused_carve(double* base, int h, int w, int oh, int cts, int nmaps) {
+  FusedSmem m;
+  m.simg = base;
+  m.rintA = m.simg + h * w;
+  m.rintB = m.rintA + h * cts;
+  m.wr = m.rintA + (size_t)nmaps * h * cts;
+  m.wr += (reinterpret_cast<uintptr_t>(m.wr) >> 3) & 1;   // 16-byte aligned: the row weights are read as double2
+  m.wc = m.wr + oh * 4;
+  m.r0s = reinterpret_cast<int*>(m.wc + cts * 4);
+  m.c0s = m.r0s + oh;
+  return m;
+}
+
+__global__ void __cluster_dims__(kCluster, 1, 1) __launch_bounds__(kFusedThreads, 2)
+sim_cc_nss_fused_kernel(const double* __restrict__ pred, const double* __restrict__ gt, const uint8_t* __restrict__ fix,
+                        double* __restrict__ out, int n, int h, int w, int oh, int ow, int cts, int nearest) {
+  extern __shared__ double fsm[];
+  cg::cluster_group cl = cg::this_cluster();
+  __shared__ double scr[32];
+  __shared__ double part1[8], part2[8], tot[16];
+  const int rank = (int)cl.block_rank();
+  const int ncl = gridDim.x / kCluster;
+  const int cbase = min(ow, rank * cts), ct = min(cts, ow - cbase);
+  const long long hw = (long long)oh * ow;
+  const FusedSmem m = fused_carve(fsm, h, w, oh, cts, 2);
+  fused_tables(h, w, oh, ow, cbase, ct, m.wr, m.wc, m.r0s, m.c0s);
+  for (int f = blockIdx.x / kCluster; f < n; f += ncl) {
+    const uint8_t* fx = fix ? fix + (long long)f * hw + cbase : nullptr;
+    double pmn, pmx, gmn, gmx;
+    fused_rowsums(pred + (long long)f * h * w, h, w, ct, cts, nearest, m.simg, m.rintA, m.wc, m.c0s, scr, pmn, pmx);
+    fused_rowsums(gt + (long long)f * h * w, h, w, ct, cts, nearest, m.simg, m.rintB, m.wc, m.c0s, scr, gmn, gmx);
+    // ---- pass 1: sums, extrema, fixation statistics of the resized maps
+    double sp = 0.0, sg = 0.0, mn = CUDART_INF, mx = -CUDART_INF, spf = 0.0, nf = 0.0;
+    bool bad = false;                                  // np.min / np.max propagate NaN: fmin/fmax + a NaN flag
+    const double* rints[2] = {m.rintA, m.rintB};
+    const double mnv[2] = {pmn, gmn}, mxv[2] = {pmx, gmx};
+    walk_strip<2, 8, uint8_t>(rints, m.wr, m.r0s, h, oh, ow, ct, cts, nearest, mnv, mxv,
+        [&](long long o) { return fx ? fx[o] : (uint8_t)0; },
+        [&](int, int, const double* v, uint8_t fm) {
+          const double a = v[0], b = v[1];
+          sp += a; sg += b;
+          if (!(a >= mn && a <= mx)) {                // a new extremum or a NaN: rare after the first few pixels
+            if (a != a) bad = true; else { mn = (a < mn) ? a : mn; mx = (a > mx) ? a : mx; }
+          }
+          if (fm) { spf += a; nf += 1.0; }
+        });
+    if (bad) { mn = CUDART_NAN; mx = CUDART_NAN; }
+    sp = block_red<SumOp>(sp, scr); sg = block_red<SumOp>(sg, scr);
+    mn = block_red<MinOp>(mn, scr); mx = block_red<MaxOp>(mx, scr);
+    spf = block_red<SumOp>(spf, scr); nf = block_red<SumOp>(nf, scr);
+    if (threadIdx.x == 0) { part1[0] = sp; part1[1] = sg; part1[2] = mn; part1[3] = mx; part1[4] = spf; part1[5] = nf; }
+    cl.sync();
+    if (threadIdx.x == 0) {
+      tot[0] = cluster_gather<SumOp>(cl, part1, 0); tot[1] = cluster_gather<SumOp>(cl, part1, 1);
+      tot[2] = cluster_gather<MinOp>(cl, part1, 2); tot[3] = cluster_gather<MaxOp>(cl, part1, 3);
+      tot[4] = cluster_gather<SumOp>(cl, part1, 4); tot[5] = cluster_gather<SumOp>(cl, part1, 5);
+    }
+    __syncthreads();
+    const double tsp = tot[0], tsg = tot[1];
+    const double mp = tsp / (double)hw, mg = tsg / (double)hw;
+    const double rsp = dD(1.0, tsp), rsg = dD(1.0, tsg);
+    // ---- pass 2: the same pixels again, recomputed from the shared-memory tables
+    double vpp = 0.0, vgg = 0.0, vpg = 0.0, ssim = 0.0;
+    // np.minimum propagates NaN.  With finite non-zero sums every term is finite (or +-inf), so a plain compare-select
+    // is exact; frames whose sums are 0 / inf / NaN (cluster-uniform) take the NaN-propagating form.
+    const bool plain = (tsp - tsp == 0.0) && (tsg - tsg == 0.0) && tsp != 0.0 && tsg != 0.0;
+    if (plain)
+      walk_strip<2, 8, int>(rints, m.wr, m.r0s, h, oh, ow, ct, cts, nearest, mnv, mxv,
+          [&](long long) { return 0; },
+          [&](int, int, const double* v, int) {
+            const double a = v[0], b = v[1];
+            const double ax = a - mp, bx = b - mg;
+            vpp += ax * ax; vgg += bx * bx; vpg += ax * bx;
+            const double x = b * rsg, y = a * rsp;
+            ssim += (y < x) ? y : x;
+          });
+    else
+      walk_strip<2, 8, int>(rints, m.wr, m.r0s, h, oh, ow, ct, cts, nearest, mnv, mxv,
+          [&](long long) { return 0; },
+          [&](int, int, const double* v, int) {
+            const double a = v[0], b = v[1];
+            const double ax = a - mp, bx = b - mg;
+            vpp += ax * ax; vgg += bx * bx; vpg += ax * bx;
+            ssim += nmin(b * rsg, a * rsp);
+          });
+    vpp = block_red<SumOp>(vpp, scr); vgg = block_red<SumOp>(vgg, scr);
+    vpg = block_red<SumOp>(vpg, scr); ssim = block_red<SumOp>(ssim, scr);
+    if (threadIdx.x == 0) { part2[0] = vpp; part2[1] = vgg; part2[2] = vpg; part2[3] = ssim; }
+    cl.sync();
+    if (rank == 0 && threadIdx.x == 0) {
+      const double tpp = cluster_gather<SumOp>(cl, part2, 0), tgg = cluster_gather<SumOp>(cl, part2, 1);
+      const double tpg = cluster_gather<SumOp>(cl, part2, 2), tsim = cluster_gather<SumOp>(cl, part2, 3);
+      double* o = out + (long long)f * 8;
+      o[0] = tsim;
+      o[1] = tpg / (sqrt(tpp) * sqrt(tgg));
+      const double sd = sqrt(tpp / (double)hw);
+      o[2] = (tot[5] > 0.0) ? ((tot[4] / tot[5]) - mp) / sd : CUDART_NAN;
+      o[3] = tot[2]; o[4] = tot[3]; o[5] = tot[5]; o[6] = tsp; o[7] = tsg;
+    }
+    cl.sync();
+  }
+}
+
+__global__ void __cluster_dims__(kCluster, 1, 1) __launch_bounds__(kStreamThreads, 2)
+auc_judd_fused_kernel(const double* __restrict__ sal, const double* __restrict__ jitter, const uint8_t* __restrict__ fix,
+                      double* __restrict__ thr_out, long long* __restrict__ counts, double* __restrict__ auc,
+                      int n, int h, int w, int oh, int ow, int cts, int nearest, int maxfix) {
+  extern __shared__ double fsm[];
+  const int nt = (int)blockDim.x;
+  cg::cluster_group cl = cg::this_cluster();
+  __shared__ double scr[32];
+  __shared__ double part[4];
+  __shared__ double myfix[kMaxFix];
+  __shared__ double thr[kMaxFix];
+  __shared__ int hist[kMaxFix];
+  __shared__ int mycount, total_s;
+  __shared__ double mnmx[2];
+  const int rank = (int)cl.block_rank();
+  const int ncl = gridDim.x / kCluster;
+  const int cbase = min(ow, rank * cts), ct = min(cts, ow - cbase);
+  const long long hw = (long long)oh * ow;
+  const bool hj = jitter != nullptr;
+  const FusedSmem m = fused_carve(fsm, h, w, oh, cts, 1);
+  fused_tables(h, w, oh, ow, cbase, ct, m.wr, m.wc, m.r0s, m.c0s);
+  for (int f = blockIdx.x / kCluster; f < n; f += ncl) {
+    const double* jt = hj ? jitter + (long long)f * hw + cbase : nullptr;
+    const uint8_t* fx = fix + (long long)f * hw + cbase;
+    double smn, smx;
+    fused_rowsums(sal + (long long)f * h * w, h, w, ct, cts, nearest, m.simg, m.rintA, m.wc, m.c0s, scr, smn, smx);
+    if (threadIdx.x == 0) mycount = 0;
+    for (int i = threadIdx.x; i < kMaxFix; i += nt) hist[i] = 0;
+    __syncthreads();
+    // ---- pass 1: extrema of the jittered resized map, values at the fixations
+    double mn = CUDART_INF, mx = -CUDART_INF;
+    bool bad = false;
+    struct JF { double j; uint8_t f; };
+    const double* rints[1] = {m.rintA};
+    walk_strip<1, 8, JF>(rints, m.wr, m.r0s, h, oh, ow, ct, cts, nearest, &smn, &smx,
+        [&](long long o) { JF p; p.j = hj ? jt[o] : 0.0; p.f = fx[o]; return p; },
+        [&](int, int, const double* v, const JF& p) {
+          const double x = judd_x(v[0], p.j, hj);
+          if (!(x >= mn && x <= mx)) {
+            if (x != x) bad = true; else { mn = (x < mn) ? x : mn; mx = (x > mx) ? x : mx; }
+          }
+          if (p.f) { int k = atomicAdd(&mycount, 1); if (k < kMaxFix) myfix[k] = x; }
+        });
+    if (bad) { mn = CUDART_NAN; mx = CUDART_NAN; }
+    mn = block_red<MinOp>(mn, scr); mx = block_red<MaxOp>(mx, scr);
+    if (threadIdx.x == 0) { part[0] = mn; part[1] = mx; part[2] = (double)mycount; }
+    cl.sync();
+    if (threadIdx.x == 0) {
+      mnmx[0] = cluster_gather<MinOp>(cl, part, 0);
+      mnmx[1] = cluster_gather<MaxOp>(cl, part, 1);
+      total_s = (int)cluster_gather<SumOp>(cl, part, 2);
+    }
+    __syncthreads();
+    const double gmn = mnmx[0], range = dS(mnmx[1], mnmx[0]);
+    const int total = total_s;
+    const bool ok = total > 0 && total <= maxfix && total <= kMaxFix;
+    int np2 = 1;
+    while (np2 < total) np2 <<= 1;
+    if (ok) {
+      int base = 0;
+      for (int q = 0; q < kCluster; ++q) {
+        const int cq = (int)cl.map_shared_rank(part, q)[2];
+        const double* lq = cl.map_shared_rank(myfix, q);
+        for (int i = threadIdx.x; i < cq; i += nt) thr[base + i] = dD(dS(lq[i], gmn), range);
+        base += cq;
+      }
+      for (int i = total + threadIdx.x; i < np2; i += nt) thr[i] = -CUDART_INF;
+      __syncthreads();
+      for (int k = 2; k <= np2; k <<= 1)
+        for (int j = k >> 1; j > 0; j >>= 1) {
+          for (int i = threadIdx.x; i < np2; i += nt) {
+            const int l = i ^ j;
+            if (l > i) {
+              const double a = thr[i], b = thr[l];
+              const bool desc = (i & k) == 0;
+              if (desc ? (a < b) : (a > b)) { thr[i] = b; thr[l] = a; }
+            }
+          }
+          __syncthreads();
+        }
+      // ---- pass 2: rank every pixel against the thresholds (jitter re-read from L2, map recomputed)
+      const double lowest = thr[total - 1];
+      const double cut = lowest * range * (1.0 - 1e-12);      // see auc_judd_kernel
+      walk_strip<1, 8, double>(rints, m.wr, m.r0s, h, oh, ow, ct, cts, nearest, &smn, &smx,
+          [&](long long o) { return hj ? jt[o] : 0.0; },
+          [&](int, int, const double* v, double j) {
+            const double x = judd_x(v[0], j, hj);
+            const double d = dS(x, gmn);
+            if (d < cut) return;
+            const double vv = dD(d, range);
+            if (vv >= lowest) {
+              int lo = 0, hi = total - 1;
+              while (lo < hi) { const int mid = (lo + hi) >> 1; if (thr[mid] <= vv) hi = mid; else lo = mid + 1; }
+              atomicAdd(&hist[lo], 1);
+            }
+          });
+    }
+    cl.sync();
+    if (rank == 0) {
+      if (ok) {
+        for (int k = threadIdx.x; k < total; k += nt) {
+          int c = 0;
+          for (int q = 0; q < kCluster; ++q) c += cl.map_shared_rank(hist, q)[k];
+          hist[k] = c;
+        }
+      }
+      __syncthreads();
+      for (int k = threadIdx.x; k < maxfix; k += nt) {
+        thr_out[(long long)f * maxfix + k] = (ok && k < total) ? thr[k] : CUDART_NAN;
+        if (!ok || k >= total) counts[(long long)f * maxfix + k] = -1;
+      }
+      if (threadIdx.x == 0) {
+        double a = CUDART_NAN;
+        if (ok) {
+          long long above = 0;
+          double tp0 = 0.0, fp0 = 0.0, acc = 0.0;
+          const double nfix = (double)total, nneg = (double)(hw - total);
+          for (int k = 0; k < total; ++k) {
+            above += hist[k];
+            counts[(long long)f * maxfix + k] = above;
+            const double tp1 = (double)(k + 1) / nfix, fp1 = (double)(above - k - 1) / nneg;
+            acc += (fp1 - fp0) * (tp1 + tp0) / 2.0;
+            tp0 = tp1; fp0 = fp1;
+          }
+          acc += (1.0 - fp0) * (1.0 + tp0) / 2.0;
+          a = acc;
+        } else if (total > 0) {
+          a = -1.0;
+        }
+        auc[f] = a;
+      }
+    }
+    cl.sync();
   }
 }
 
@@ -717,6 +1165,41 @@ int rgp_auc_judd(const double* sal, const double* jitter, const uint8_t* fix, do
   return rgp::check_launch("rgp_auc_judd");
 }
 
+namespace {
+// dynamic shared memory of the sampled-AUC kernel: rep_auc | source image (fused) | stash of the negatives (if it fits)
+int launch_auc_sampled(bool fused, const double* sal, const uint8_t* fix, const int* idx, const double* minmax,
+                       int mm_stride, double* auc, int* tpc, int* fpc, int n, int hw, int nrows, int nrep, double step,
+                       int nthr_max, int maxfix, int h, int w, int ow, int nearest, void* stream) {
+  size_t smem = ((size_t)nrep + (fused ? (size_t)h * w : 0)) * sizeof(double);
+  const size_t stash_bytes = (size_t)nrows * nrep * sizeof(double);
+  const int stash = (nrows > 0 && smem + stash_bytes <= 96 * 1024) ? 1 : 0;
+  if (stash) smem += stash_bytes;
+  if (smem > 200 * 1024) { rgp::set_error("rgp_auc_sampled: %zu bytes of shared memory needed", smem); return -22; }
+  static bool attr = false;
+  if (!attr) {
+    cudaFuncSetAttribute(rgp::auc_sampled_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    cudaFuncSetAttribute(rgp::auc_sampled_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    attr = true;
+  }
+  const int grid = n < 8 * sm_count() ? n : 8 * sm_count();
+  if (fused)
+    rgp::auc_sampled_kernel<true><<<grid, rgp::kThreads, smem, (cudaStream_t)stream>>>(
+        sal, fix, idx, minmax, mm_stride, auc, tpc, fpc, n, hw, nrows, nrep, step, nthr_max, maxfix, h, w, ow, nearest, stash);
+  else
+    rgp::auc_sampled_kernel<false><<<grid, rgp::kThreads, smem, (cudaStream_t)stream>>>(
+        sal, fix, idx, minmax, mm_stride, auc, tpc, fpc, n, hw, nrows, nrep, step, nthr_max, maxfix, 0, 0, 0, 0, stash);
+  return rgp::check_launch("rgp_auc_sampled");
+}
+
+rgp::FusedGeom fused_geom(int h, int w, int oh, int ow) {
+  rgp::FusedGeom g;
+  g.h = h; g.w = w; g.oh = oh; g.ow = ow;
+  g.cts = (ow + rgp::kCluster - 1) / rgp::kCluster;
+  return g;
+}
+constexpr size_t kFusedSmemMax = 160 * 1024;   // + <= 21 KB static in the AUC-Judd kernel
+}  // namespace
+
 int rgp_auc_sampled(const double* sal, const uint8_t* fix, const int* idx, const double* minmax, int mm_stride,
                     double* auc, int* tpc, int* fpc, int n, int hw, int nrows, int nrep, double step, int nthr_max,
                     int maxfix, void* stream) {
@@ -725,10 +1208,65 @@ int rgp_auc_sampled(const double* sal, const uint8_t* fix, const int* idx, const
   RGP_CHECK_ARG(maxfix >= 1 && maxfix <= rgp::kMaxFix, "rgp_auc_sampled: maxfix=%d must be in 1..%d", maxfix, rgp::kMaxFix);
   RGP_CHECK_ARG((tpc == nullptr) == (fpc == nullptr), "rgp_auc_sampled: tpc and fpc must both be given or both NULL");
   if (n == 0) return 0;
-  const int grid = n < 8 * sm_count() ? n : 8 * sm_count();
-  rgp::auc_sampled_kernel<<<grid, rgp::kThreads, (size_t)nrep * sizeof(double), (cudaStream_t)stream>>>(
-      sal, fix, idx, minmax, mm_stride, auc, tpc, fpc, n, hw, nrows, nrep, step, nthr_max, maxfix);
-  return rgp::check_launch("rgp_auc_sampled");
+  return launch_auc_sampled(false, sal, fix, idx, minmax, mm_stride, auc, tpc, fpc, n, hw, nrows, nrep, step, nthr_max,
+                            maxfix, 0, 0, 0, 0, stream);
+}
+
+/* ---- fused resize + metric entry points ---------------------------------------------------- */
+int rgp_metrics_fused_fits(int h, int w, int oh, int ow) {
+  if (h <= 0 || w <= 0 || oh <= 0 || ow <= 0) return 0;
+  return fused_geom(h, w, oh, ow).smem_bytes(2) <= kFusedSmemMax ? 1 : 0;
+}
+
+int rgp_sim_cc_nss_resized(const double* pred_src, const double* gt_src, const uint8_t* fix, double* out, int n, int h,
+                           int w, int oh, int ow, int mode_nearest, void* stream) {
+  RGP_CHECK_ARG(n >= 0 && h > 0 && w > 0 && oh > 0 && ow > 0, "rgp_sim_cc_nss_resized: bad shape");
+  RGP_CHECK_ARG(rgp_metrics_fused_fits(h, w, oh, ow), "rgp_sim_cc_nss_resized: %dx%d -> %dx%d does not fit the strip tables; "
+                "use rgp_resize_bicubic + rgp_sim_cc_nss", h, w, oh, ow);
+  if (n == 0) return 0;
+  const rgp::FusedGeom g = fused_geom(h, w, oh, ow);
+  static bool attr = false;
+  if (!attr) {
+    cudaFuncSetAttribute(rgp::sim_cc_nss_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFusedSmemMax);
+    attr = true;
+  }
+  const int ncl = n < sm_count() ? n : sm_count();
+  rgp::sim_cc_nss_fused_kernel<<<ncl * rgp::kCluster, rgp::kFusedThreads, g.smem_bytes(2), (cudaStream_t)stream>>>(
+      pred_src, gt_src, fix, out, n, h, w, oh, ow, g.cts, mode_nearest);
+  return rgp::check_launch("rgp_sim_cc_nss_resized");
+}
+
+int rgp_auc_judd_resized(const double* sal_src, const double* jitter, const uint8_t* fix, double* thr, long long* counts,
+                         double* auc, int n, int h, int w, int oh, int ow, int mode_nearest, int maxfix, void* stream) {
+  RGP_CHECK_ARG(n >= 0 && h > 0 && w > 0 && oh > 0 && ow > 0, "rgp_auc_judd_resized: bad shape");
+  RGP_CHECK_ARG(maxfix >= 1 && maxfix <= rgp::kMaxFix, "rgp_auc_judd_resized: maxfix=%d must be in 1..%d", maxfix, rgp::kMaxFix);
+  RGP_CHECK_ARG(rgp_metrics_fused_fits(h, w, oh, ow), "rgp_auc_judd_resized: %dx%d -> %dx%d does not fit the strip tables; "
+                "use rgp_resize_bicubic + rgp_auc_judd", h, w, oh, ow);
+  if (n == 0) return 0;
+  const rgp::FusedGeom g = fused_geom(h, w, oh, ow);
+  static bool attr = false;
+  if (!attr) {
+    cudaFuncSetAttribute(rgp::auc_judd_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFusedSmemMax);
+    attr = true;
+  }
+  const int ncl = n < sm_count() ? n : sm_count();
+  rgp::auc_judd_fused_kernel<<<ncl * rgp::kCluster, rgp::kStreamThreads, g.smem_bytes(1), (cudaStream_t)stream>>>(
+      sal_src, jitter, fix, thr, counts, auc, n, h, w, oh, ow, g.cts, mode_nearest, maxfix);
+  return rgp::check_launch("rgp_auc_judd_resized");
+}
+
+int rgp_auc_sampled_resized(const double* sal_src, const uint8_t* fix, const int* idx, const double* minmax,
+                            int mm_stride, double* auc, int* tpc, int* fpc, int n, int h, int w, int oh, int ow,
+                            int mode_nearest, int nrows, int nrep, double step, int nthr_max, int maxfix, void* stream) {
+  RGP_CHECK_ARG(n >= 0 && h > 0 && w > 0 && oh > 0 && ow > 0 && nrows >= 0 && nrep >= 1,
+                "rgp_auc_sampled_resized: n=%d %dx%d -> %dx%d nrows=%d nrep=%d", n, h, w, oh, ow, nrows, nrep);
+  RGP_CHECK_ARG(step > 0.0 && nthr_max >= 1, "rgp_auc_sampled_resized: step=%g nthr_max=%d", step, nthr_max);
+  RGP_CHECK_ARG(maxfix >= 1 && maxfix <= rgp::kMaxFix, "rgp_auc_sampled_resized: maxfix=%d must be in 1..%d", maxfix, rgp::kMaxFix);
+  RGP_CHECK_ARG((tpc == nullptr) == (fpc == nullptr), "rgp_auc_sampled_resized: tpc and fpc must both be given or both NULL");
+  RGP_CHECK_ARG((size_t)h * w * sizeof(double) <= 96 * 1024, "rgp_auc_sampled_resized: source map %dx%d too large", h, w);
+  if (n == 0) return 0;
+  return launch_auc_sampled(true, sal_src, fix, idx, minmax, mm_stride, auc, tpc, fpc, n, oh * ow, nrows, nrep, step,
+                            nthr_max, maxfix, h, w, ow, mode_nearest, stream);
 }
 
 }  // extern "C"

@@ -61,10 +61,15 @@ def shuffled_sample_index(other_flat, n_rep, n_fix):
 class MetricsEngine(object):
     """Batched device evaluation of the saliency metrics for N frames at once."""
 
-    def __init__(self, device="cuda", lib=None, chunk=256):
+    def __init__(self, device="cuda", lib=None, chunk=256, fused=True):
         self.device = torch.device(device)
         self.lib = lib if lib is not None else L.get_lib()
         self.chunk = chunk
+        # fused: the bicubic enlargement of the model maps is evaluated inside the metric kernels (rgp_*_resized) and
+        # never written to HBM.  True = where it is the faster path (measured, profiles/r01_notes.md pass 6): metric
+        # sets without AUC_Judd — the reference's AVAILABLE_METRICS; with AUC_Judd the enlarged prediction is needed
+        # twice more and the two-step path (rgp_resize_bicubic + plain kernels) wins.  "always" / False force a path.
+        self.fused = fused
 
     def _s(self):
         if self.device.type == "cuda":
@@ -126,6 +131,49 @@ class MetricsEngine(object):
                                  mm_stride, auc.data_ptr(), tpc.data_ptr() if want_counts else 0,
                                  fpc.data_ptr() if want_counts else 0, n, hw, nrows, nrep, float(step), nthr,
                                  maxfix, self._s())
+        return auc, tpc, fpc
+
+    # ------------------------------------------------------------------ fused resize + metric (csrc/metrics.cu)
+    def fused_fits(self, src_shape, out_shape):
+        return bool(self.lib.rgp_metrics_fused_fits(int(src_shape[0]), int(src_shape[1]), int(out_shape[0]),
+                                                    int(out_shape[1])))
+
+    def sim_cc_nss_resized(self, pred_src, gt_src, fix_u8, out_shape, mode="constant"):
+        n, h, w = pred_src.shape
+        oh, ow = out_shape
+        out = torch.empty(n, 8, dtype=torch.float64, device=self.device)
+        self.lib.rgp_sim_cc_nss_resized(pred_src.data_ptr(), gt_src.data_ptr(),
+                                        fix_u8.data_ptr() if fix_u8 is not None else 0, out.data_ptr(), n, h, w, oh, ow,
+                                        1 if mode == "nearest" else 0, self._s())
+        return out
+
+    def auc_judd_resized(self, sal_src, fix_u8, out_shape, jitter_f64=None, maxfix=64, mode="constant"):
+        n, h, w = sal_src.shape
+        oh, ow = out_shape
+        thr = torch.empty(n, maxfix, dtype=torch.float64, device=self.device)
+        counts = torch.empty(n, maxfix, dtype=torch.int64, device=self.device)
+        auc = torch.empty(n, dtype=torch.float64, device=self.device)
+        self.lib.rgp_auc_judd_resized(sal_src.data_ptr(), jitter_f64.data_ptr() if jitter_f64 is not None else 0,
+                                      fix_u8.data_ptr(), thr.data_ptr(), counts.data_ptr(), auc.data_ptr(), n, h, w,
+                                      oh, ow, 1 if mode == "nearest" else 0, maxfix, self._s())
+        return auc, thr, counts
+
+    def auc_sampled_resized(self, sal_src, fix_u8, idx_i32, minmax, mm_stride, out_shape, step=0.1, maxfix=64,
+                            want_counts=False, mode="constant"):
+        n, h, w = sal_src.shape
+        oh, ow = out_shape
+        _, nrows, nrep = idx_i32.shape
+        nthr = int(np.ceil(1.0 / step)) + 1
+        auc = torch.empty(n, dtype=torch.float64, device=self.device)
+        tpc = fpc = None
+        if want_counts:
+            tpc = torch.empty(n, nrep, nthr, dtype=torch.int32, device=self.device)
+            fpc = torch.empty(n, nrep, nthr, dtype=torch.int32, device=self.device)
+        self.lib.rgp_auc_sampled_resized(sal_src.data_ptr(), fix_u8.data_ptr(), idx_i32.data_ptr(), minmax.data_ptr(),
+                                         mm_stride, auc.data_ptr(), tpc.data_ptr() if want_counts else 0,
+                                         fpc.data_ptr() if want_counts else 0, n, h, w, oh, ow,
+                                         1 if mode == "nearest" else 0, nrows, nrep, float(step), nthr, maxfix,
+                                         self._s())
         return auc, tpc, fpc
 
     # ------------------------------------------------------------------ host draws (global numpy RNG, reference order)
@@ -199,13 +247,22 @@ class MetricsEngine(object):
             fx = self._dev(fix_h[sl].astype(np.uint8), torch.uint8)
             p64 = self.to_f64(p32, normalize=not pred_is_normalized)
             g64 = self.to_f64(g32, normalize=False)
-            pr = self.resize(p64, (H, W), "constant")
-            gr = self.resize(g64, (H, W), "constant")
-            stats = self.sim_cc_nss(pr, gr, fx)
+            # maps below fixation resolution: enlargement fused into the metric kernels (never materialised)
+            fused = bool(self.fused) and tuple(p64.shape[1:]) != (H, W) and self.fused_fits(p64.shape[1:], (H, W)) \
+                and (self.fused == "always" or 'AUC_Judd' not in metrics)
+            if fused:
+                stats = self.sim_cc_nss_resized(p64, g64, fx, (H, W))
+            else:
+                pr = self.resize(p64, (H, W), "constant")
+                gr = self.resize(g64, (H, W), "constant")
+                stats = self.sim_cc_nss(pr, gr, fx)
             res = {}
             if 'AUC_Judd' in metrics:
                 jd = self._dev(jitter_values[sl], torch.float64) if (jitter and jitter_values is not None) else None
-                res['AUC_Judd'], thr, cnt = self.auc_judd(pr, fx, jd, maxfix)
+                if fused:
+                    res['AUC_Judd'], thr, cnt = self.auc_judd_resized(p64, fx, (H, W), jd, maxfix)
+                else:
+                    res['AUC_Judd'], thr, cnt = self.auc_judd(pr, fx, jd, maxfix)
                 if return_counts:
                     extra.setdefault('AUC_Judd_counts', []).append(cnt.cpu().numpy())
                     extra.setdefault('AUC_Judd_thresholds', []).append(thr.cpu().numpy())
@@ -213,7 +270,11 @@ class MetricsEngine(object):
                 if name in metrics:
                     idx = self._dev(self._pad_index([np.asarray(r) for r in index[c0:c1]], n_rep), torch.int32)
                     mm = stats[:, 3:]
-                    auc, tpc, fpc = self.auc_sampled(pr, fx, idx, mm, 8, step, maxfix, want_counts=return_counts)
+                    if fused:
+                        auc, tpc, fpc = self.auc_sampled_resized(p64, fx, idx, mm, 8, (H, W), step, maxfix,
+                                                                 want_counts=return_counts)
+                    else:
+                        auc, tpc, fpc = self.auc_sampled(pr, fx, idx, mm, 8, step, maxfix, want_counts=return_counts)
                     res[name] = auc
                     if return_counts:
                         extra.setdefault(name + '_tp', []).append(tpc.cpu().numpy())

@@ -96,6 +96,9 @@ _SIGS = {
     "rgp_sim_cc_nss": [_vp, _vp, _vp, _vp, _i, _i, _vp],
     "rgp_auc_judd": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp],
     "rgp_auc_sampled": [_vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _i, _i, _i, _d, _i, _i, _vp],
+    "rgp_sim_cc_nss_resized": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp],
+    "rgp_auc_judd_resized": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp],
+    "rgp_auc_sampled_resized": [_vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _d, _i, _i, _vp],
 }
 
 
@@ -115,6 +118,8 @@ class RgpLib(object):
         self._dll.rgp_last_error.restype = C.c_char_p
         self._dll.rgp_version.restype = _i
         self._dll.rgp_has_tcgen05.restype = _i
+        self._dll.rgp_metrics_fused_fits.restype = _i
+        self._dll.rgp_metrics_fused_fits.argtypes = [_i, _i, _i, _i]
         for name, sig in _SIGS.items():
             fn = getattr(self._dll, name)
             fn.argtypes = sig
@@ -138,8 +143,12 @@ class RgpLib(object):
     def has_tcgen05(self):
         return bool(self._dll.rgp_has_tcgen05())
 
+    def rgp_metrics_fused_fits(self, h, w, oh, ow):
+        """a predicate, not a status: 1 if the fused resize+metric kernels can hold an h x w -> oh x ow enlargement"""
+        return int(self._dll.rgp_metrics_fused_fits(h, w, oh, ow))
+
     def symbols(self):
-        return sorted(list(_SIGS) + ["rgp_last_error", "rgp_version", "rgp_has_tcgen05"])
+        return sorted(list(_SIGS) + ["rgp_last_error", "rgp_version", "rgp_has_tcgen05", "rgp_metrics_fused_fits"])
 
 
 _LIB = None

@@ -585,6 +585,32 @@ class EmuLib(object):
             au[f] = acc / nrep
         return 0
 
+    # fused resize + metric entry points: the emulation materialises the enlargement and calls the plain emulation
+    def rgp_metrics_fused_fits(self, h, w, oh, ow):
+        cts = (ow + 7) // 8
+        return int((h * w + 2 * h * cts + oh * 4 + cts * 4) * 8 + (oh + cts) * 4 <= 160 * 1024)
+
+    def _enlarge(self, src, n, h, w, oh, ow, mode_nearest):
+        big = np.empty((n, oh, ow), np.float64)
+        self.rgp_resize_bicubic(src, big.ctypes.data, n, h, w, oh, ow, mode_nearest, None)
+        return big
+
+    def rgp_sim_cc_nss_resized(self, pred, gt, fix, out, n, h, w, oh, ow, mode_nearest, stream):
+        assert self.rgp_metrics_fused_fits(h, w, oh, ow)
+        p, g = self._enlarge(pred, n, h, w, oh, ow, mode_nearest), self._enlarge(gt, n, h, w, oh, ow, mode_nearest)
+        return self.rgp_sim_cc_nss(p.ctypes.data, g.ctypes.data, fix, out, n, oh * ow, stream)
+
+    def rgp_auc_judd_resized(self, sal, jitter, fix, thr, counts, auc, n, h, w, oh, ow, mode_nearest, maxfix, stream):
+        assert self.rgp_metrics_fused_fits(h, w, oh, ow)
+        s = self._enlarge(sal, n, h, w, oh, ow, mode_nearest)
+        return self.rgp_auc_judd(s.ctypes.data, jitter, fix, thr, counts, auc, n, oh * ow, maxfix, stream)
+
+    def rgp_auc_sampled_resized(self, sal, fix, idx, minmax, mm_stride, auc, tpc, fpc, n, h, w, oh, ow, mode_nearest,
+                                nrows, nrep, step, nthr_max, maxfix, stream):
+        s = self._enlarge(sal, n, h, w, oh, ow, mode_nearest)
+        return self.rgp_auc_sampled(s.ctypes.data, fix, idx, minmax, mm_stride, auc, tpc, fpc, n, oh * ow, nrows, nrep,
+                                    step, nthr_max, maxfix, stream)
+
     def rgp_convgru_seq_fwd(self, aref, stream):
         """All T steps = T x (GRU_ZR tap-GEMM + GRU_C tap-GEMM) on the same buffers (fp32 emulation)."""
         a = aref._obj

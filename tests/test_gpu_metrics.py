@@ -142,3 +142,82 @@ def test_size_independent_properties_at_scale(eng):
     r4 = eng.evaluate_batch(pred, gt, fix, metrics=("sim", "cc", "NSS", "AUC_Judd"), jitter=False)
     for m in r1:
         assert np.array_equal(r1[m], r4[m]), m
+
+
+def _vas_case(seed, N, H=360, W=480):
+    rng = np.random.RandomState(seed)
+    gt, _ = SY.make_gazemaps(rng, 1, N, 49, 49)
+    pred = (gt + 0.3 * rng.uniform(size=gt.shape)).astype(np.float32)
+    fix = SY.make_fixationmaps(rng, gt, H, W).reshape(N, H, W)
+    pred, gt = pred.reshape(N, 49, 49), gt.reshape(N, 49, 49)
+    union = (fix[rng.choice(N, min(N, 10), replace=False)] > 0).sum(0).astype(np.float64)
+    nfix = fix.reshape(N, -1).sum(1)
+    jit = rng.rand(N, H, W)
+    ridx = [rng.randint(0, H * W, [int(n), 100]) for n in nfix]
+    np.random.seed(seed + 100)
+    sidx = [EM.shuffled_sample_index(union.ravel() > 0.5, 100, int(n)) if n else np.zeros((0, 100), np.int64) for n in nfix]
+    return pred, gt, fix, union, jit, ridx, sidx
+
+
+@pytest.mark.parametrize("shape", [(360, 480), (45, 61), (100, 7)])
+def test_fused_resize_metrics_equal_two_step_path(shape):
+    """rgp_*_resized (enlargement evaluated inside the metric kernels) against rgp_resize_bicubic + the plain kernels:
+    thresholds, integer counts and AUCs identical bits; sim / cc / NSS differ only by summation order."""
+    H, W = shape
+    pred, gt, fix, union, jit, ridx, sidx = _vas_case(3, 12, H, W)
+    fix[5] = 0
+    a = EM.MetricsEngine(device="cuda", fused="always")
+    b = EM.MetricsEngine(device="cuda", fused=False)
+    assert a.fused_fits((49, 49), shape)
+    kw = dict(union=union, jitter_values=jit, rand_index=ridx, shuf_index=sidx, return_counts=True)
+    before = a.lib.launches
+    ra = a.evaluate_batch(pred, gt, fix, **kw)
+    assert a.lib.launches - before == 2 + 4            # prep x2, fused sim/cc/nss, Judd, Borji, shuffled: no resize launch
+    rb = b.evaluate_batch(pred, gt, fix, **kw)
+    for k in rb:
+        if k in ("sim", "cc", "NSS"):
+            assert np.array_equal(np.isnan(ra[k]), np.isnan(rb[k])), k
+            m = ~np.isnan(rb[k])
+            assert np.abs(ra[k][m] - rb[k][m]).max() <= 1e-13, (k, np.abs(ra[k][m] - rb[k][m]).max())
+        else:
+            assert np.array_equal(ra[k], rb[k], equal_nan=True), k
+    # the (min, max, n_fix) columns of the statistics row are exact as well
+    p64 = a.to_f64(torch.from_numpy(pred).cuda(), True)
+    g64 = a.to_f64(torch.from_numpy(gt).cuda(), False)
+    fx = torch.from_numpy(fix).cuda()
+    for mode in ("constant", "nearest"):
+        sa = a.sim_cc_nss_resized(p64, g64, fx, shape, mode).cpu().numpy()
+        sb = b.sim_cc_nss(b.resize(p64, shape, mode), b.resize(g64, shape, mode), fx).cpu().numpy()
+        assert np.array_equal(sa[:, 3:6], sb[:, 3:6])
+        assert np.allclose(sa[:, 6:], sb[:, 6:], rtol=1e-13, atol=0)
+
+
+def test_fused_path_nan_and_large_index_tensor():
+    """constant prediction (normalize_range -> NaN map) through the fused kernels; a sampled-AUC index tensor too
+    large for the shared-memory stash takes the gather-per-threshold path and gives the same counts."""
+    H, W = 120, 160
+    pred, gt, fix, union, jit, ridx, sidx = _vas_case(9, 4, H, W)
+    pred[1] = 0.25
+    a = EM.MetricsEngine(device="cuda", fused="always")
+    b = EM.MetricsEngine(device="cuda", fused=False)
+    ra = a.evaluate_batch(pred, gt, fix, metrics=("sim", "cc", "NSS", "AUC_Judd"), jitter_values=jit)
+    rb = b.evaluate_batch(pred, gt, fix, metrics=("sim", "cc", "NSS", "AUC_Judd"), jitter_values=jit)
+    for k in ("sim", "cc", "NSS"):
+        assert np.isnan(ra[k][1]), k
+        assert not np.isnan(ra[k][0]), k
+    # AUC-Judd on an all-NaN map: the reference's loop counts 0 pixels above every (NaN) threshold and integrates a
+    # finite number (evaluation_metrics.py:84-97); both device paths and the oracle reproduce that number
+    assert np.array_equal(ra["AUC_Judd"], rb["AUC_Judd"])
+    with np.errstate(invalid="ignore", divide="ignore"):
+        want = MO.saliency_score_single("AUC_Judd", pred[1].astype(np.float64), gt[1], fix[1], jitter_values=jit[1])
+    assert abs(ra["AUC_Judd"][1] - want) <= 1e-12
+    big = [np.random.RandomState(i).randint(0, H * W, [int((fix[i] > 0).sum()), 1500]) for i in range(4)]
+    x = a.evaluate_batch(pred, gt, fix, metrics=("AUC_Borji",), rand_index=big, n_rep=1500, return_counts=True)
+    y = b.evaluate_batch(pred, gt, fix, metrics=("AUC_Borji",), rand_index=big, n_rep=1500, return_counts=True)
+    for k in y:
+        assert np.array_equal(x[k], y[k], equal_nan=True), k
+    i = 0
+    S = MO.normalize_range(MO.resize_bicubic(MO.normalize_range(pred[i].astype(np.float64)), (H, W), "constant")).ravel()
+    F = (fix[i] > 0).ravel()
+    for rep, (thresholds, tpc, fpc) in enumerate(MO.borji_counts(S[F], S[big[i]], 0.1)):
+        assert np.array_equal(x["AUC_Borji_fp"][i, rep, :len(thresholds)], fpc[::-1])

@@ -121,3 +121,29 @@ def test_saliency_score_mean_and_nan_propagation():
 def test_resize_onehot_matches_reference_golden():
     assert np.array_equal(EM.resize_onehot_tensor_sparse(G["onehot_in"], (49, 49)).astype(np.uint8), G["onehot_ref"])
     assert np.array_equal(EM.normalize_range(G["nr_in"]), G["nr_ref"])
+
+
+def test_fused_and_two_step_host_paths_agree():
+    """evaluate_batch routes below-resolution maps to the rgp_*_resized entry points (fused="always") or to
+    rgp_resize_bicubic + the plain ones; over the emulation both must give the same numbers."""
+    rng = np.random.RandomState(4)
+    N, H, W = 3, 30, 44
+    pred = rng.uniform(size=(N, 7, 7)).astype(np.float32)
+    gt = rng.uniform(size=(N, 7, 7)).astype(np.float32)
+    fix = (rng.uniform(size=(N, H, W)) > 0.99).astype(np.uint8)
+    fix[1] = 0
+    union = (rng.uniform(size=(H, W)) > 0.9).astype(np.float64)
+    jit = rng.rand(N, H, W)
+    nfix = fix.reshape(N, -1).sum(1)
+    ridx = [rng.randint(0, H * W, [int(n), 20]) for n in nfix]
+    lib = EmuLib()
+    calls = []
+    for fused in ("always", False):
+        eng = EM.MetricsEngine(device="cpu", lib=lib, fused=fused)
+        np.random.seed(1)
+        calls.append(eng.evaluate_batch(pred, gt, fix, union=union, jitter_values=jit, rand_index=ridx, n_rep=20))
+    for k in calls[0]:
+        assert np.array_equal(calls[0][k], calls[1][k], equal_nan=True), k
+    assert np.isnan(calls[0]["AUC_Judd"][1]) and not np.isnan(calls[0]["AUC_Judd"][0])
+    want = MO.saliency_score_single("AUC_Judd", pred[0].astype(np.float64), gt[0], fix[0], jitter_values=jit[0])
+    assert abs(calls[0]["AUC_Judd"][0] - want) <= 1e-12
