@@ -149,6 +149,9 @@ int rgp_gradnorm_clip_adam(float* p, const float* g, float* m, float* v, long lo
                            const double* sumsq, float clip, float lr_t, float beta1, float beta2,
                            float eps, void* p_op, int dtype, void* stream);
 int rgp_zero(void* p, long long bytes, void* stream);
+/* gaze_rnn.py:504-510 (random h-flip of half the batch) on the fed device buffers: x is [n_clips, rows_per_clip, W]
+ * fp32; for each of the nsel clip indices in `clips` (device int32) every W-row is reversed in place. */
+int rgp_flip_w(float* x, const int* clips, int nsel, long long rows_per_clip, int W, void* stream);
 
 /* ---- BPTT (base.py:278-281) --------------------------------------------------------------- */
 /* Weight-gradient contraction over rows ("wgrad"):

@@ -355,6 +355,23 @@ __global__ void __launch_bounds__(256) clip_adam_kernel(float* __restrict__ p, c
 
 using namespace rgp;
 
+// gaze_rnn.py:504-510 — the random horizontal flip of half the batch, applied to the fed device buffers instead of the
+// host arrays: for every selected clip, each row of W consecutive floats (the last axis of [clip, rows, W]) is
+// reversed in place.  One thread per row; a row of 7 (C3D) or 49 (gaze map) floats is read and written by its owner only.
+namespace rgp {
+namespace {
+__global__ void flip_w_kernel(float* __restrict__ x, const int* __restrict__ clips, int nsel, long long rows_per_clip, int W) {
+  const long long total = (long long)nsel * rows_per_clip;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int k = (int)(i / rows_per_clip);
+    const long long r = i - (long long)k * rows_per_clip;
+    float* row = x + ((long long)clips[k] * rows_per_clip + r) * W;
+    for (int a = 0, b = W - 1; a < b; ++a, --b) { const float t = row[a]; row[a] = row[b]; row[b] = t; }
+  }
+}
+}  // namespace
+}  // namespace rgp
+
 extern "C" {
 
 int rgp_pack_c3d(const float* c3d, void* out, int B, int T, int C, int P, int dtype, void* stream) {
@@ -459,6 +476,16 @@ int rgp_gradnorm_clip_adam(float* p, const float* g, float* m, float* v, long lo
     clip_adam_kernel<__nv_bfloat16><<<grid, 256, 0, (cudaStream_t)stream>>>(p, g, m, v, n, sumsq, clip, lr_t, beta1,
                                                                              beta2, eps, (__nv_bfloat16*)p_op);
   return check_launch("rgp_gradnorm_clip_adam");
+}
+
+int rgp_flip_w(float* x, const int* clips, int nsel, long long rows_per_clip, int W, void* stream) {
+  RGP_CHECK_ARG(nsel >= 0 && rows_per_clip > 0 && W > 0, "rgp_flip_w: nsel=%d rows=%lld W=%d", nsel, rows_per_clip, W);
+  if (nsel == 0) return 0;
+  const long long total = (long long)nsel * rows_per_clip;
+  int grid = (int)((total + 255) / 256);
+  if (grid > 148 * 16) grid = 148 * 16;
+  rgp::flip_w_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, clips, nsel, rows_per_clip, W);
+  return check_launch("rgp_flip_w");
 }
 
 int rgp_zero(void* p, long long bytes, void* stream) {

@@ -33,10 +33,18 @@ def _tdtype(dtype):
 
 class GazeEngine(object):
     def __init__(self, model="gaze_grcn", B=2, T=35, G=7, Ch=128, Cin=512, Cfeat=1024, dtype=0,
-                 device="cuda", lib=None, train=False, head=None, engine=None, seq=None, nsplit=None, mcast=None):
+                 device="cuda", lib=None, train=False, head=None, engine=None, seq=None, nsplit=None, mcast=None,
+                 T_params=None):
         if model not in ("gaze_grcn", "gaze_grcn77", "gaze_lstm"):
             raise ValueError("unknown model %r" % (model,))
         self.model, self.B, self.T, self.G, self.Ch, self.Cin, self.Cfeat = model, B, T, G, Ch, Cin, Cfeat
+        # Chunked long clips (extract_map.py:65,148-238 runs 105-step clips): the engine processes T frames per pass,
+        # the model owns T_params >= T per-time-step parameter sets (the frozen-BN (gamma_t, beta_t) of
+        # gaze_grcn.py:325); `t0` is the clip time of the chunk's first frame.  Inference only.
+        self.Tp = T_params or T
+        self.t0 = 0
+        if self.Tp != T and train:
+            raise ValueError("chunked time (T_params != T) is an inference feature; BPTT needs the whole clip")
         if engine is None:   # RGP_ENGINE=1 forces the FMA engine for bf16 operands (debug / A-B checks)
             engine = int(os.environ.get("RGP_ENGINE", "0"))
         self.dtype, self.train, self.engine = dtype, train, engine
@@ -99,8 +107,8 @@ class GazeEngine(object):
             spec["out_W"] = (Ch,)
         spec["out_b"] = (1,)
         if self.use_bn:
-            spec["bn_gamma"] = (T, Ch)
-            spec["bn_beta"] = (T, Ch)
+            spec["bn_gamma"] = (self.Tp, Ch)
+            spec["bn_beta"] = (self.Tp, Ch)
         self.spec = spec
         self.offsets = OrderedDict()
         off = 0
@@ -290,13 +298,14 @@ class GazeEngine(object):
         self.lib.rgp_tapgemm(C.byref(a), self._s())
 
     # ------------------------------------------------------------------ forward
-    def forward(self, c3d=None, emb=None, gt=None, loss_type="xentropy", global_batch=None, carry_state=False):
+    def forward(self, c3d=None, emb=None, gt=None, loss_type="xentropy", global_batch=None, carry_state=False, t0=0):
         """c3d [B,T,Cfeat,G,G] fp32 (reference entry, gaze_grcn.py:173) or emb [B,T,G,G,Cin] fp32
         (already-projected features).  Returns logits [B,T,GH,GW]; with gt also fills probs and loss.
         carry_state=True starts from the state left in slab 0 by set_initial_state() / carry_last_state()
         (cell-level API, chunked long clips) instead of h_0 = 0 (gaze_grcn.py:262)."""
         if not carry_state and self._state_dirty:
             self.reset_state()
+        self.t0 = t0            # clip time of this chunk's first frame (selects the per-time-step BN parameters)
         self.stage_embed(c3d, emb)
         self.stage_i2h()
         self.stage_recurrence(zero_cell=not carry_state)
@@ -375,6 +384,7 @@ class GazeEngine(object):
         """(a4/a6/a7) the T-step recurrence: gaze_grcn.py:259-288, gaze_lstm.py:260-286."""
         lib, s = self.lib, self._s()
         B, T, S, Ch, Wp, G = self.B, self.T, self.S, self.Ch, self.Wp, self.G
+        assert 0 <= self.t0 and self.t0 + T <= self.Tp, "chunk [t0, t0+T) outside the model's %d time steps" % self.Tp
         es = self.Hop.element_size()
         pop = self._pop
         NX = self.ngx * Ch
@@ -390,7 +400,8 @@ class GazeEngine(object):
             if self.head == "deconv":
                 a.HS = self.HS.data_ptr()
             if self.use_bn:
-                a.bn_gamma, a.bn_beta, a.alpha = self._ptr("bn_gamma"), self._ptr("bn_beta"), 1.0 / math.sqrt(1.0 + BN_EPS)
+                a.bn_gamma, a.bn_beta = self._ptr("bn_gamma") + self.t0 * Ch * 4, self._ptr("bn_beta") + self.t0 * Ch * 4
+                a.alpha = 1.0 / math.sqrt(1.0 + BN_EPS)
             a.B, a.T, a.G, a.Ch = B, T, G, Ch
             a.So, a.Wo, a.pado = HEAD_S, HEAD_W, HEAD_PAD
             a.nsplit, a.dtype, a.mcast = self.nsplit, self.dtype, self.mcast
@@ -425,7 +436,8 @@ class GazeEngine(object):
                            **common)
                 extra = {}
                 if self.use_bn:
-                    extra = dict(bias=self._ptr("bn_gamma") + t * Ch * 4, bias2=self._ptr("bn_beta") + t * Ch * 4,
+                    tb = self.t0 + t
+                    extra = dict(bias=self._ptr("bn_gamma") + tb * Ch * 4, bias2=self._ptr("bn_beta") + tb * Ch * 4,
                                  alpha=1.0 / math.sqrt(1.0 + BN_EPS))
                 self._gemm(A=self._slab(self.RH, sl), Bw=pop("Uc_op"), N=Ch, epi=L.EPI_GRU_C,
                            hnext_f32=self._slab(self.Hf, t + 1), out_op=self._slab(self.Hop, t + 1), out_op2=hs,

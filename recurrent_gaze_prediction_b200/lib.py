@@ -79,6 +79,7 @@ _SIGS = {
     "rgp_sumsq": [_vp, _ll, _vp, _vp],
     "rgp_gradnorm_clip_adam": [_vp, _vp, _vp, _vp, _ll, _vp, _f, _f, _f, _f, _f, _vp, _i, _vp],
     "rgp_zero": [_vp, _ll, _vp],
+    "rgp_flip_w": [_vp, _vp, _i, _ll, _i, _vp],
     "rgp_wgrad": [C.POINTER(WgradArgs), _vp],
     "rgp_gru_bwd_last": [_vp, _vp, _f, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _i, _vp],
     "rgp_lstm_gates_bwd": [_vp] * 14 + [_i, _i, _i, _i, _i, _vp],

@@ -112,9 +112,18 @@ class GazePredictionGRU(ModelBase):
         dev = torch.device(getattr(c, "device", "cuda"))
         dtype = 1 if getattr(c, "dtype", "bf16") == "bf16" else 0
         train = bool(getattr(c, "trainable", True))
-        self.engine = GazeEngine(self.model_name, B=B, T=T, G=G, Ch=getattr(c, "rnn_state_size", 128),
+        # chunk_steps: long clips (extract_map.py:65 runs T = 105) go through the engine `chunk_steps` frames at a time
+        # with the recurrent state carried between chunks; activations are sized for one chunk.  Inference only.
+        self.chunk_steps = getattr(c, "chunk_steps", None) or None
+        Tc = self.chunk_steps or T
+        if self.chunk_steps is not None:
+            if train:
+                raise ValueError("chunk_steps is an inference option (set config.trainable = False)")
+            if T % Tc != 0:
+                raise ValueError("n_lstm_steps=%d is not a multiple of chunk_steps=%d" % (T, Tc))
+        self.engine = GazeEngine(self.model_name, B=B, T=Tc, G=G, Ch=getattr(c, "rnn_state_size", 128),
                                  Cin=self.dim_cnn_proj, Cfeat=c.dim_feature, dtype=dtype, device=dev, lib=self._lib,
-                                 train=train)
+                                 train=train, T_params=T)
         GH = self.engine.GH
         if (self.gazemap_height, self.gazemap_width) != (GH, GH):
             raise ValueError("%s predicts %dx%d gaze maps, not %dx%d" % (self.model_name, GH, GH, self.gazemap_height,
@@ -127,8 +136,13 @@ class GazePredictionGRU(ModelBase):
         self.c3d_input = z(B, T, c.dim_feature, G, G)                # gaze_rnn.py:118-121
         self.gt_gazemap = z(B, T, GH, GH)                            # gaze_rnn.py:122-126
         self.dropout_keep_prob = 1.0                                 # never fires in GRCN / LSTM
-        self.predicted_gazemaps_logit = self.engine.logits           # gaze_rnn.py:156
-        self.predicted_gazemaps = self.engine.probs if c.loss_type in ('xentropy', 'KLD') else self.engine.logits
+        if self.chunk_steps is None:
+            self.predicted_gazemaps_logit = self.engine.logits       # gaze_rnn.py:156
+            probs = self.engine.probs
+        else:
+            self.predicted_gazemaps_logit, probs = z(B, T, GH, GH), z(B, T, GH, GH)
+        self._probs = probs
+        self.predicted_gazemaps = probs if c.loss_type in ('xentropy', 'KLD') else self.predicted_gazemaps_logit
         self.loss = self.engine.loss
         if c.loss_type not in LOSS_TYPES:
             raise NotImplementedError(str(c.loss_type))             # gaze_rnn.py:405-406
@@ -186,8 +200,30 @@ class GazePredictionGRU(ModelBase):
         self.c3d_input.copy_(self._c3d_host, non_blocking=True)
         self.gt_gazemap.copy_(self._gt_host, non_blocking=True)
 
+    def _flip_fed(self, clip_indices):
+        """gaze_rnn.py:507-509 on the device placeholders: reverse the W axis of c3d_input and gt_gazemap for the
+        chosen clips (global clip indices; this rank flips the ones that fell into its shard)."""
+        lo = self.rank * self.local_batch
+        mine = np.asarray([i - lo for i in clip_indices if lo <= i < lo + self.local_batch], dtype=np.int32)
+        if mine.size == 0:
+            return
+        e = self.engine
+        idx = torch.from_numpy(mine).to(e.device)
+        s = torch.cuda.current_stream(e.device).cuda_stream if e.device.type == "cuda" else 0
+        T, G, GH, GW = self.n_lstm_steps, e.G, self.gazemap_height, self.gazemap_width
+        self._lib_handle().rgp_flip_w(self.c3d_input.data_ptr(), idx.data_ptr(), int(mine.size),
+                                      T * self.dim_feature * G, G, s)
+        self._lib_handle().rgp_flip_w(self.gt_gazemap.data_ptr(), idx.data_ptr(), int(mine.size), T * GH, GW, s)
+
+    def _lib_handle(self):
+        return self.engine.lib
+
     def run(self, train=False):
         """One pass over the fed placeholders: forward + loss (+ BPTT + clip/Adam when train).  Returns the loss."""
+        if self.chunk_steps is not None:
+            if train:
+                raise RuntimeError("a chunked model cannot train")
+            return self._run_chunked()
         self.engine.forward(c3d=self.c3d_input, gt=self.gt_gazemap, loss_type=self.config.loss_type,
                             global_batch=self.batch_size)
         if train:
@@ -201,6 +237,36 @@ class GazePredictionGRU(ModelBase):
             loss = float(t.cpu()[0])
         return loss
 
+    def _run_chunked(self):
+        """The clip in chunks of `chunk_steps` frames: the state left by chunk k (h_T, and the LSTM cell) is the initial
+        state of chunk k+1 and `t0` selects the per-time-step BN parameters, so the result equals the one-pass model's."""
+        e, Tc = self.engine, self.chunk_steps
+        loss, nchunks = 0.0, self.n_lstm_steps // Tc
+        for k in range(nchunks):
+            t0 = k * Tc
+            e.forward(c3d=self.c3d_input[:, t0:t0 + Tc].contiguous(), gt=self.gt_gazemap[:, t0:t0 + Tc].contiguous(),
+                      loss_type=self.config.loss_type, global_batch=self.batch_size, carry_state=k > 0, t0=t0)
+            self.predicted_gazemaps_logit[:, t0:t0 + Tc].copy_(e.logits)
+            self._probs[:, t0:t0 + Tc].copy_(e.probs)
+            loss += float(e.loss.cpu()[0]) / nchunks       # each chunk's loss is a mean over B*chunk_steps frames
+            e.carry_last_state()
+        e.reset_state()
+        if self.world_size > 1 and self._allreduce is not None:
+            t = torch.tensor([loss], dtype=torch.float32, device=e.device)
+            self._allreduce(t)
+            loss = float(t.cpu()[0])
+        return loss
+
+    def predict(self, batch_c3d):
+        """The inference call the reference's extract_map.py:210-217 wishes the model had
+        (`session.run([model.predicted_gazemaps], {model.c3d_input: ..})`): c3d [batch_size, T, 1024, 7, 7] host array
+        -> gaze maps [local clips, T, GH, GW] (probabilities for xentropy / KLD, raw maps for l2) as a NumPy array."""
+        B, T = self.batch_size, self.n_lstm_steps
+        GH, GW = self.gazemap_height, self.gazemap_width
+        self._feed(batch_c3d, np.zeros((B, T, GH, GW), dtype=np.float32))
+        self.run(train=False)
+        return self.predicted_gazemaps.cpu().numpy()
+
     def single_step(self, train_mode=True, dataset=None):
         """gaze_rnn.py:483-565."""
         _start_time = time.time()
@@ -211,15 +277,19 @@ class GazePredictionGRU(ModelBase):
         batch_c3d = np.reshape(batch_c3d, [self.batch_size, -1, self.dim_feature, self.engine.G, self.engine.G])
         if self.config.loss_type in ('xentropy', 'KLD'):
             batch_maps = normalize_probability_map(batch_maps)
+        flip = None
         if train_mode and self.config.use_flip_batch:        # gaze_rnn.py:504-510 (global numpy RNG, same draw)
             batch_size = len(batch_images)
-            indices = np.random.choice(batch_size, batch_size // 2, replace=False)
+            flip = np.random.choice(batch_size, batch_size // 2, replace=False)
+            # images and fixation maps are not consumed by the step (gaze_grcn.py:173-376 never reads the frames):
+            # their host arrays are flipped as in the reference; the two tensors the step DOES consume — C3D features
+            # and gaze maps — are flipped on the device after the copy (rgp_flip_w), not in host memory
             if batch_images.shape[2] > 1:
-                batch_images[indices, :] = batch_images[indices, :, :, ::-1, :]
-            batch_maps[indices, :] = batch_maps[indices, :, :, ::-1]
-            batch_c3d[indices, :] = batch_c3d[indices, :, :, :, ::-1]
-            batch_fixmaps[indices, :] = batch_fixmaps[indices, :, :, ::-1]
+                batch_images[flip, :] = batch_images[flip, :, :, ::-1, :]
+            batch_fixmaps[flip, :] = batch_fixmaps[flip, :, :, ::-1]
         self._feed(batch_c3d, batch_maps)
+        if flip is not None:
+            self._flip_fed(flip)
         loss = self.run(train=train_mode)
         self.last_loss = loss
         step = self.current_step

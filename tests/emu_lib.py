@@ -181,6 +181,13 @@ class EmuLib(object):
         arr(dst, (n,))[:] = arr(src, (n,))
         return 0
 
+    def rgp_flip_w(self, x, clips, nsel, rows_per_clip, W, stream):
+        idx = arr(clips, (nsel,), np.int32)
+        for k in idx:
+            a = arr(int(x) + int(k) * rows_per_clip * W * 4, (rows_per_clip, W))
+            a[:] = a[:, ::-1].copy()
+        return 0
+
     def rgp_zero(self, p, nbytes, stream):
         C.memset(int(p), 0, int(nbytes))
         return 0

@@ -79,3 +79,54 @@ def test_training_through_the_model_class_learns(mod, cls):
         m.single_step()
         losses.append(m.last_loss)
     assert losses[-1] < losses[0] - 0.05, (losses[0], losses[-1])
+
+
+@pytest.mark.parametrize("B,hidden", [(2, 128), (256, 256)])
+def test_long_clip_extraction_chunked_equals_one_pass(tmp_path, B, hidden):
+    """extract_map.py (n_lstm_steps = 105): three 35-frame chunks with the recurrent state carried between them against
+    one 105-frame pass.  Same kernels on the same numbers -> identical bits.  B = 256 takes the persistent recurrence
+    kernel (its stateful chunking), B = 2 the per-step GEMMs."""
+    from recurrent_gaze_prediction_b200.models import extract_map as XM
+    T = 105 if B == 2 else 15
+    Tc = 35 if B == 2 else 5
+    argv = ["--model", "gaze_grcn", "--dataset", "synthetic", "--batch_size", str(B), "--n_lstm_steps", str(T),
+            "--hidden", str(hidden), "--num_clips", str(B), "--out_dir", str(tmp_path)]
+    args1 = XM.make_parser().parse_args(argv + ["--chunk_steps", "0"])
+    args2 = XM.make_parser().parse_args(argv + ["--chunk_steps", str(Tc)])
+    one = XM.load_model(args1)
+    chk = XM.load_model(args2)
+    assert one.chunk_steps is None and chk.chunk_steps == Tc and chk.engine.T == Tc and chk.engine.Tp == T
+    assert chk.engine.use_seq == (B == 256)
+    g = one.engine.view("bn_gamma")
+    g.copy_(torch.linspace(0.5, 1.5, g.numel(), device=g.device).view_as(g))
+    chk.engine.params.copy_(one.engine.params)
+    one.engine.refresh_operands()
+    chk.engine.refresh_operands()
+    clips = list(XM.iter_clips(args1))
+    r1 = XM.extract(one, clips)
+    r2 = XM.extract(chk, clips, out_dir=str(tmp_path))
+    assert len(r1) == B
+    for name, c3d in clips[:4] + clips[-2:]:
+        n = min(T, len(c3d))
+        assert r1[name][0].shape == (n, 49, 49) and r1[name][1].shape == (n, 7, 7)
+        assert np.array_equal(r1[name][0], r2[name][0]), name
+        assert np.allclose(r1[name][0].sum(axis=(1, 2)), 1.0, atol=1e-4)
+    assert os.path.isfile(os.path.join(str(tmp_path), clips[0][0], clips[0][0] + ".gazemap.npy"))
+
+
+def test_device_flip_matches_host_flip():
+    """gaze_rnn.py:504-510: the W-axis flip of the chosen clips, done on the fed device buffers (rgp_flip_w)."""
+    from recurrent_gaze_prediction_b200 import lib as L
+    lib = L.get_lib()
+    rng = np.random.RandomState(0)
+    for shape in ((6, 5, 1024, 7, 7), (6, 5, 49, 49), (3, 2, 4, 1), (5, 3, 8)):
+        x = rng.standard_normal(shape).astype(np.float32)
+        sel = np.array([4, 1, 2][:min(3, shape[0])], dtype=np.int32)
+        want = x.copy()
+        want[sel] = want[sel][..., ::-1]
+        d = torch.from_numpy(x).cuda()
+        idx = torch.from_numpy(sel).cuda()
+        lib.rgp_flip_w(d.data_ptr(), idx.data_ptr(), len(sel), int(np.prod(shape[1:-1])), shape[-1],
+                       torch.cuda.current_stream().cuda_stream)
+        assert np.array_equal(d.cpu().numpy(), want), shape
+    lib.rgp_flip_w(d.data_ptr(), idx.data_ptr(), 0, 1, 1, 0)          # nothing selected: no-op

@@ -193,3 +193,45 @@ def test_network_builders_match_oracle(mod, cls, model, GH):
     O.recurrent_network(model, O.to_torch(p), c3d=torch.from_numpy(c3d).double(), net=onet)
     assert torch.allclose(net['c3d_embedded'].double(), onet['c3d_embedded'], atol=1e-4)
     assert torch.allclose(net['rcn_outputs'][-1].double(), onet['rcn_outputs'][-1], atol=1e-4)
+
+
+@pytest.mark.parametrize("Model", [gaze_grcn.GazePredictionGRCN, gaze_lstm.GazePredictionLSTM])
+def test_chunked_long_clip_equals_one_pass(Model, tmp_path):
+    """extract_map.py:65,148-238: long clips run `chunk_steps` frames at a time with the state (and the per-time-step
+    BN parameters' time offset) carried between chunks; the gaze maps equal the one-pass model's."""
+    from recurrent_gaze_prediction_b200.models import extract_map as XM
+    lib = EmuLib()
+    T, B = 6, 2
+    c1, c2 = small_config(T=T, B=B), small_config(T=T, B=B)
+    c1.trainable = c2.trainable = False
+    c2.chunk_steps = 2
+    one = Model({'lib': lib}, data(T=T), c1)
+    chk = Model({'lib': lib}, data(T=T), c2)
+    assert chk.engine.T == 2 and chk.engine.Tp == T and one.engine.T == T
+    if one.engine.use_bn:          # distinct BN parameters per time step, so a wrong time offset would show
+        g = one.engine.view("bn_gamma")
+        g.copy_(torch.linspace(0.5, 1.5, g.numel()).view_as(g))
+        one.engine.view("bn_beta").copy_(torch.linspace(-0.2, 0.2, g.numel()).view_as(g))
+    chk.engine.params.copy_(one.engine.params)
+    chk.engine.refresh_operands()
+    one.engine.refresh_operands()
+    rng = np.random.RandomState(3)
+    clips = [("a", SY.make_c3d(rng, 1, 4, dim_feature=64)[0]), ("b", SY.make_c3d(rng, 1, 6, dim_feature=64)[0]),
+             ("c", SY.make_c3d(rng, 1, 9, dim_feature=64)[0])]           # short (padded), exact, long (cut)
+    r1 = XM.extract(one, clips)
+    r2 = XM.extract(chk, clips, out_dir=str(tmp_path))
+    for name, n in (("a", 4), ("b", 6), ("c", 6)):
+        g49, g7 = r1[name]
+        assert g49.shape == (n, 49, 49) and g7.shape == (n, 7, 7)
+        assert np.allclose(g49.sum(axis=(1, 2)), 1.0, atol=1e-5)                     # probabilities
+        assert np.allclose(r2[name][0], g49, rtol=1e-6, atol=1e-9), name
+        assert np.allclose(g7, g49.reshape(n, 7, 7, 7, 7).mean(axis=(2, 4)))
+        assert np.array_equal(np.load(os.path.join(str(tmp_path), name, name + ".gazemap.49.npy")), r2[name][0])
+        assert np.load(os.path.join(str(tmp_path), name, name + ".gazemap.npy")).shape == (n, 7, 7)
+    # a second batch through the same chunked model starts from h_0 = 0 again
+    again = XM.extract(chk, clips[:1])
+    assert np.array_equal(again["a"][0], r2["a"][0])
+    with pytest.raises(ValueError):
+        bad = small_config(T=T, B=B)
+        bad.chunk_steps = 2                    # trainable model
+        Model({'lib': lib}, data(T=T), bad)
