@@ -204,6 +204,25 @@ int rgp_colsum(const void* X, int ld, int M, int N, float* out, int dtype, void*
 int rgp_fc_head_bwd(const float* dlogits, const float* h_f32, const float* out_W, float* dhs,
                     float* gout_W, float* gout_b, int B, int T, int t, int G, int Ch, void* stream);
 
+/* ---- dense-GRU variant: models/gaze_rnn.py:283-359 ------------------------------------------
+ * Its contractions are plain GEMMs on rgp_tapgemm (ntaps = 1, RGP_EPI_STORE_F32) with widths padded to the engine's
+ * granularity (padded weights zero; padded state columns stay zero); these four calls are the element-wise glue.
+ * Cell arithmetic = tf.nn.rnn_cell.GRUCell (TF >= 1.2): [r,u] = sig([x,h].Wg + bg); c = tanh([x, r*h].Wc + bc);
+ * h' = u*h + (1-u)*c.  Parity unpinned at that library boundary (oracle/model_oracle.py dense_gru_cell). */
+/* gaze_rnn.py:296-304,335-338: X[r, pos*Cp + c] = acc[(r*P + pos)*ldacc + c] + bias[c] (flatten order y,x,c), columns
+ * P*Cp..ldx-1 zero; X operand dtype [rows, ldx] */
+int rgp_dense_pack(const float* acc, int ldacc, const float* bias, void* X, int ldx, long long rows, int P, int Cp,
+                   int dtype, void* stream);
+/* xg [M, ldx] fp32 = input halves (columns r | u | c, each Hp wide); hg [M, 2Hp] fp32 = h . Wh_gates; bias_g [2Hp];
+ * h_f32 [M, Hp].  Writes rh_op [M, Hp] operand dtype (r*h) and u_out [M, Hp] fp32. */
+int rgp_dense_gru_ru(const float* xg, int ldx, const float* hg, const float* bias_g, const float* h_f32, void* rh_op,
+                     float* u_out, int M, int H, int Hp, int dtype, void* stream);
+/* hc [M, Hp] fp32 = (r*h) . Wh_cand; bias_c [Hp]; writes h' as fp32 master [M, Hp] and operand copy */
+int rgp_dense_gru_c(const float* xg, int ldx, const float* hc, const float* bias_c, const float* u, const float* h_f32,
+                    float* hnext_f32, void* hnext_op, int M, int H, int Hp, int dtype, void* stream);
+/* gaze_rnn.py:346-359: logits[b, t, j] = acc[(t*B + b)*ldacc + j] + bias[j], j < N */
+int rgp_dense_logits(const float* acc, int ldacc, const float* bias, float* logits, int B, int T, int N, void* stream);
+
 /* ---- saliency metrics: evaluation_metrics.py -------------------------------------------- */
 /* All metric arithmetic is IEEE float64 with explicit round-to-nearest operations (no FMA contraction):
  * thresholds and integer counts are a bit-exact contract with NumPy's float64 evaluation.

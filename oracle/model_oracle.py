@@ -145,6 +145,64 @@ def recurrent_network(model, p, c3d=None, emb=None, net=None):
     return logits
 
 
+# ----------------------------------------------------------------------------
+# Dense-GRU variant — models/gaze_rnn.py:211-361.  PARITY UNPINNED: the cell arithmetic lives in
+# tf.nn.rnn_cell.GRUCell (un-vendored, version unpinned); restated here from the published TF >= 1.2 cell:
+#   [r, u] = sigmoid([x, h] . W_gates + b_gates)   (b_gates initialised to 1)
+#   c      = tanh([x, r*h] . W_cand + b_cand)      (b_cand initialised to 0)
+#   h'     = u*h + (1-u)*c
+# The ShallowNet frame-saliency branch (:252-276) is built by the reference but never reaches the prediction
+# (its concat entry is commented out, :333), so it is not part of this path.
+# ----------------------------------------------------------------------------
+def dense_gru_cell(x, h, p):
+    H = h.shape[1]
+    gates = torch.sigmoid(torch.cat([x, h], 1) @ p["RNN/gru_cell/gates/kernel"] + p["RNN/gru_cell/gates/bias"])
+    r, u = gates[:, :H], gates[:, H:]
+    c = torch.tanh(torch.cat([x, r * h], 1) @ p["RNN/gru_cell/candidate/kernel"] + p["RNN/gru_cell/candidate/bias"])
+    return u * h + (1.0 - u) * c
+
+
+def dense_gru_network(p, c3d, GH=None, GW=None):
+    """gaze_rnn.py:283-359: 1x1 projection 1024 -> dim_cnn_proj (32) per position, the [7,7,32] map flattened (y, x, c
+    order) as the input of one dense GRU of 7*7*32 + 49 = 1617 units, proj_out [1617, GH*GW] per step."""
+    B, T = c3d.shape[:2]
+    if GH is None:
+        GH = GW = int(round(math.sqrt(p["proj_out_W"].shape[1])))
+    emb = project_c3d(c3d, p)                                   # [B,T,7,7,32]
+    H = p["RNN/gru_cell/candidate/bias"].shape[0]
+    h = emb.new_zeros(B, H)
+    maps = []
+    for i in range(T):
+        h = dense_gru_cell(emb[:, i].reshape(B, -1), h, p)
+        maps.append((h @ p["proj_out_W"] + p["proj_out_b"]).reshape(B, GH, GW))
+    return torch.stack(maps).permute(1, 0, 2, 3)
+
+
+def init_params_dense(dim_proj=32, grid=7, dim_feature=1024, GH=49, GW=49, seed=0, kernel_scale=1.0):
+    """Variables of the dense variant in creation order (gaze_rnn.py:294-321): proj_c3d_W/b U(-0.1,0.1); the GRUCell's
+    gates / candidate kernels (the reference asks for an "orthogonal" initializer by name, :315) and biases (1 / 0);
+    proj_out_W U(-0.1,0.1), proj_out_b zeros."""
+    rng = np.random.RandomState(seed)
+    I = grid * grid * dim_proj
+    H = I + grid * grid                                         # gaze_rnn.py:243-246
+    p = OrderedDict()
+    p["proj_c3d_W"] = rng.uniform(-0.1, 0.1, size=(dim_feature, dim_proj))
+    p["proj_c3d_b"] = rng.uniform(-0.1, 0.1, size=(dim_proj,))
+
+    def orth(rows, cols):
+        q, r = np.linalg.qr(rng.standard_normal((max(rows, cols), min(rows, cols))))
+        q = q * np.sign(np.diag(r))
+        return (q if rows >= cols else q.T) * kernel_scale
+
+    p["RNN/gru_cell/gates/kernel"] = orth(I + H, 2 * H)
+    p["RNN/gru_cell/gates/bias"] = np.ones(2 * H)
+    p["RNN/gru_cell/candidate/kernel"] = orth(I + H, H)
+    p["RNN/gru_cell/candidate/bias"] = np.zeros(H)
+    p["proj_out_W"] = rng.uniform(-0.1, 0.1, size=(H, GH * GW))
+    p["proj_out_b"] = np.zeros(GH * GW)
+    return p
+
+
 def softmax_2d(logits):
     """model_util.py:61-64 applied per frame as gaze_rnn.py:149-159."""
     B, T, H, W = logits.shape
@@ -263,7 +321,7 @@ def forward_loss_grads(model, p_np, gt, c3d=None, emb=None, loss_type="xentropy"
     p = to_torch(p_np, dtype, requires_grad=True)
     tc = None if c3d is None else torch.tensor(c3d, dtype=dtype)
     te = None if emb is None else torch.tensor(emb, dtype=dtype)
-    logits = recurrent_network(model, p, c3d=tc, emb=te)
+    logits = dense_gru_network(p, tc) if model == "gaze_rnn" else recurrent_network(model, p, c3d=tc, emb=te)
     loss = loss_fn(logits, torch.tensor(gt, dtype=dtype), loss_type)
     names = [k for k in p if not (emb is not None and k.startswith("proj_c3d"))]
     grads = torch.autograd.grad(loss, [p[k] for k in names], allow_unused=True)

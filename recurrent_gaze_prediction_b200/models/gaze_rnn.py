@@ -8,8 +8,9 @@ a :class:`GazeEngine`: "placeholders" (``c3d_input``, ``frame_images``, ``gt_gaz
 clip/Adam) pass of hand-written kernels on the model's CUDA stream.
 
 The class named GazePredictionGRU in the reference is itself the *dense* GRU variant (parity
-unpinned, lowest priority); here it only carries the shared machinery and refuses to build a network — use the
-GRCN / GRCN77 / LSTM subclasses.
+unpinned at the tf.nn.rnn_cell.GRUCell boundary): instantiated directly it builds that network on
+:class:`DenseGruEngine` (forward / loss / generate / evaluate; no training).  The GRCN / GRCN77 / LSTM subclasses
+carry the hot path.
 """
 from __future__ import annotations
 
@@ -105,8 +106,7 @@ class GazePredictionGRU(ModelBase):
     def build_model(self):
         """gaze_rnn.py:108-209: inputs, network, loss."""
         if self.model_name is None:
-            raise NotImplementedError("the dense GRU variant (gaze_rnn.py:241-351) is not part of the B200 hot path; "
-                                      "use GazePredictionGRCN / GazePredictionLSTM")
+            return self._build_dense_model()
         c = self.config
         B, T, G = self.local_batch, self.n_lstm_steps, getattr(c, "grid", 7)
         dev = torch.device(getattr(c, "device", "cuda"))
@@ -149,6 +149,42 @@ class GazePredictionGRU(ModelBase):
         pin = dev.type == "cuda"
         self._c3d_host = torch.zeros(B, T, c.dim_feature, G, G, dtype=torch.float32, pin_memory=pin)
         self._gt_host = torch.zeros(B, T, GH, GH, dtype=torch.float32, pin_memory=pin)
+
+    def _build_dense_model(self):
+        """The class as the reference defines it: the dense GRU variant (gaze_rnn.py:211-361) —
+        forward, loss, generate / evaluate; training is not built (see DenseGruEngine)."""
+        from ..dense_engine import DenseGruEngine
+        from .model_util import init_parameters_dense
+        c = self.config
+        B, T, G = self.local_batch, self.n_lstm_steps, getattr(c, "grid", 7)
+        dev = torch.device(getattr(c, "device", "cuda"))
+        dtype = 1 if getattr(c, "dtype", "bf16") == "bf16" else 0
+        GH, GW = self.gazemap_height, self.gazemap_width
+        if GH != GW:
+            raise ValueError("square gaze maps only")
+        if bool(getattr(c, "trainable", True)):
+            raise NotImplementedError("the dense GRU variant (gaze_rnn.py:211-361) is built for inference / evaluation "
+                                      "only: set config.trainable = False, or train GazePredictionGRCN / GazePredictionLSTM")
+        self.dim_cnn_proj = getattr(c, "dim_cnn_proj_dense", 32)              # gaze_rnn.py:239 (XXX FIXME there)
+        self.chunk_steps = None
+        self.engine = DenseGruEngine(B=B, T=T, G=G, Cp=self.dim_cnn_proj, Cfeat=c.dim_feature, GH=GH, dtype=dtype,
+                                     device=dev, lib=self._lib)
+        self.engine.load_tf_params(init_parameters_dense(dim_proj=self.dim_cnn_proj, grid=G, dim_feature=c.dim_feature,
+                                                         GH=GH, GW=GW, seed=getattr(c, "seed", 0)))
+        z = lambda *s: torch.zeros(*s, dtype=torch.float32, device=dev)
+        self.frame_images = None
+        self.c3d_input = z(B, T, c.dim_feature, G, G)
+        self.gt_gazemap = z(B, T, GH, GW)
+        self.dropout_keep_prob = 1.0       # gaze_rnn.py:128 placeholder_with_default(1.0); 0.5 is fed only while training (:529)
+        self.predicted_gazemaps_logit = self.engine.logits
+        self._probs = self.engine.probs
+        self.predicted_gazemaps = self._probs if c.loss_type in ('xentropy', 'KLD') else self.engine.logits
+        self.loss = self.engine.loss
+        if c.loss_type not in LOSS_TYPES:
+            raise NotImplementedError(str(c.loss_type))
+        pin = dev.type == "cuda"
+        self._c3d_host = torch.zeros(B, T, c.dim_feature, G, G, dtype=torch.float32, pin_memory=pin)
+        self._gt_host = torch.zeros(B, T, GH, GW, dtype=torch.float32, pin_memory=pin)
 
     @staticmethod
     def create_loss_and_summary(predicted_gazemaps, gt_gazemap, loss_type='xentropy', lib=None):

@@ -71,3 +71,29 @@ def init_parameters(model="gaze_grcn", hidden=128, T=35, grid=7, dim_proj=512, d
         p["bn_gamma"] = np.ones((T, hidden))
         p["bn_beta"] = np.zeros((T, hidden))
     return p
+
+
+def init_parameters_dense(dim_proj=32, grid=7, dim_feature=1024, GH=49, GW=49, seed=0):
+    """Variables of the dense GRU variant (gaze_rnn.py:294-321) under their TF names, in creation order:
+    proj_c3d_W/b U(-0.1,0.1); RNN/gru_cell/{gates,candidate}/{kernel,bias} (orthogonal kernels — the reference names the
+    initializer "orthogonal" at :315 — biases 1 / 0 as tf.nn.rnn_cell.GRUCell creates them); proj_out_W U(-0.1,0.1),
+    proj_out_b zeros."""
+    rng = np.random.RandomState(seed)
+    I = grid * grid * dim_proj
+    H = I + grid * grid                                         # gaze_rnn.py:243-246: 7*7*32 + 7*7 = 1617
+    p = OrderedDict()
+    p["proj_c3d_W"] = rng.uniform(-0.1, 0.1, size=(dim_feature, dim_proj))
+    p["proj_c3d_b"] = rng.uniform(-0.1, 0.1, size=(dim_proj,))
+
+    def orth(rows, cols):
+        q, r = np.linalg.qr(rng.standard_normal((max(rows, cols), min(rows, cols))))
+        q = q * np.sign(np.diag(r))
+        return q if rows >= cols else q.T
+
+    p["RNN/gru_cell/gates/kernel"] = orth(I + H, 2 * H)
+    p["RNN/gru_cell/gates/bias"] = np.ones(2 * H)
+    p["RNN/gru_cell/candidate/kernel"] = orth(I + H, H)
+    p["RNN/gru_cell/candidate/bias"] = np.zeros(H)
+    p["proj_out_W"] = rng.uniform(-0.1, 0.1, size=(H, GH * GW))
+    p["proj_out_b"] = np.zeros(GH * GW)
+    return p

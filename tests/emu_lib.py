@@ -459,6 +459,41 @@ class EmuLib(object):
                     arr(gb, (1,))[0] += d
         return 0
 
+    # -------------------------------------------------------------- dense-GRU glue (csrc/dense_gru.cu)
+    def rgp_dense_pack(self, acc, ldacc, bias, X, ldx, rows, P, Cp, dtype, stream):
+        a = arr(acc, (rows * P, ldacc))[:, :Cp] + arr(bias, (Cp,))[None, :]
+        x = arr(X, (rows, ldx))
+        x[:] = 0.0
+        x[:, :P * Cp] = a.reshape(rows, P * Cp)
+        return 0
+
+    def rgp_dense_gru_ru(self, xg, ldx, hg, bias_g, h, rh, u_out, M, H, Hp, dtype, stream):
+        x, g, b, hh = arr(xg, (M, ldx)), arr(hg, (M, 2 * Hp)), arr(bias_g, (2 * Hp,)), arr(h, (M, Hp))
+        r = _sig(x[:, :H] + g[:, :H] + b[:H])
+        u = _sig(x[:, Hp:Hp + H] + g[:, Hp:Hp + H] + b[Hp:Hp + H])
+        o, uo = arr(rh, (M, Hp)), arr(u_out, (M, Hp))
+        o[:] = 0.0
+        uo[:] = 0.0
+        o[:, :H] = r * hh[:, :H]
+        uo[:, :H] = u
+        return 0
+
+    def rgp_dense_gru_c(self, xg, ldx, hc, bias_c, u, h, hn, hn_op, M, H, Hp, dtype, stream):
+        x, c_, b = arr(xg, (M, ldx)), arr(hc, (M, Hp)), arr(bias_c, (Hp,))
+        uu, hh = arr(u, (M, Hp)), arr(h, (M, Hp))
+        c = np.tanh(x[:, 2 * Hp:2 * Hp + H] + c_[:, :H] + b[:H]).astype(np.float32)
+        v = np.zeros((M, Hp), np.float32)
+        v[:, :H] = uu[:, :H] * hh[:, :H] + (1.0 - uu[:, :H]) * c
+        arr(hn, (M, Hp))[:] = v
+        if int(hn_op) != int(hn):
+            arr(hn_op, (M, Hp))[:] = v
+        return 0
+
+    def rgp_dense_logits(self, acc, ldacc, bias, logits, B, T, N, stream):
+        a = arr(acc, (T * B, ldacc))[:, :N] + arr(bias, (N,))[None, :]
+        arr(logits, (B, T, N))[:] = a.reshape(T, B, N).transpose(1, 0, 2)
+        return 0
+
     # -------------------------------------------------------------- saliency metrics (csrc/metrics.cu)
     # NumPy float64 restatements of the KERNELS' algorithms (rank-by-search for Judd, per-repetition
     # count loops for the sampled AUCs), so the host wrapper in evaluation_metrics.py is checked on CPU.

@@ -130,3 +130,30 @@ def test_device_flip_matches_host_flip():
                        torch.cuda.current_stream().cuda_stream)
         assert np.array_equal(d.cpu().numpy(), want), shape
     lib.rgp_flip_w(d.data_ptr(), idx.data_ptr(), 0, 1, 1, 0)          # nothing selected: no-op
+
+
+@pytest.mark.parametrize("dtype,tol,B", [("fp32", 1e-4, 3), ("bf16", 2e-2, 3), ("bf16", 2e-2, 130)])
+def test_dense_gru_variant_on_gpu(dtype, tol, B):
+    """SURVEY row a24 at the reference's sizes (1617 units, proj_out to 49x49): gaze maps against the oracle's
+    restatement of the tf GRUCell (fp32 1e-4 / bf16 2e-2 relative to the map's peak, as for the GRCN path)."""
+    from recurrent_gaze_prediction_b200.dense_engine import DenseGruEngine
+    rng = np.random.RandomState(1)
+    T = 4
+    p = O.init_params_dense(seed=3)
+    e = DenseGruEngine(B=B, T=T, dtype=0 if dtype == "fp32" else 1)
+    assert (e.H, e.Ip, e.Hp, e.Np) == (1617, 1600, 1664, 2432)
+    e.load_tf_params(p)
+    c3d = SY.make_c3d(rng, B, T)
+    gt = O.normalize_probability_map(SY.make_gazemaps(rng, B, T, 49, 49)[0]).astype(np.float32)
+    e.forward(c3d=torch.from_numpy(c3d).cuda(), gt=torch.from_numpy(gt).cuda())
+    nb = min(B, 4)                                             # the oracle on the first clips (clips are independent)
+    _, ref_probs, _, _ = O.forward_loss_grads("gaze_rnn", p, gt[:nb].astype(np.float64), c3d=c3d[:nb].astype(np.float64))
+    probs = e.probs.cpu().numpy()[:nb]
+    rel = np.abs(probs - ref_probs).max(axis=(2, 3)) / ref_probs.max(axis=(2, 3))
+    assert rel.max() <= tol, rel.max()
+    assert np.isfinite(float(e.loss.cpu()[0]))
+    assert float(e.Hf[:, e.H:].abs().max()) == 0.0
+    if B == 130:                                               # last clips too (second M tile of the per-step GEMMs)
+        _, ref2, _, _ = O.forward_loss_grads("gaze_rnn", p, gt[-2:].astype(np.float64), c3d=c3d[-2:].astype(np.float64))
+        rel = np.abs(e.probs.cpu().numpy()[-2:] - ref2).max(axis=(2, 3)) / ref2.max(axis=(2, 3))
+        assert rel.max() <= tol, rel.max()

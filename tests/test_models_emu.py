@@ -135,7 +135,7 @@ def test_loss_builder_and_errors():
     c.loss_type = "hinge"
     with pytest.raises(NotImplementedError):
         gaze_grcn.GazePredictionGRCN({'lib': lib}, data(), c)
-    with pytest.raises(NotImplementedError):                     # the dense GRU variant is out of scope
+    with pytest.raises(NotImplementedError):                     # the dense GRU variant does not train (inference only)
         gaze_rnn.GazePredictionGRU({'lib': lib}, data(), small_config())
     c = small_config(B=4)
     with pytest.raises(ValueError):
@@ -235,3 +235,50 @@ def test_chunked_long_clip_equals_one_pass(Model, tmp_path):
         bad = small_config(T=T, B=B)
         bad.chunk_steps = 2                    # trainable model
         Model({'lib': lib}, data(T=T), bad)
+
+
+def test_dense_gru_variant_matches_oracle():
+    """SURVEY row a24 (gaze_rnn.py:211-361): the class named GazePredictionGRU is the dense GRU variant; forward, loss,
+    checkpoint layout and generate() against the oracle's restatement of tf.nn.rnn_cell.GRUCell (parity unpinned at
+    that library boundary)."""
+    from recurrent_gaze_prediction_b200.dense_engine import DenseGruEngine
+    rng = np.random.RandomState(0)
+    B, T = 3, 4
+    p = O.init_params_dense(dim_proj=4, dim_feature=16, GH=7, GW=7, seed=2, kernel_scale=1.5)
+    p["RNN/gru_cell/gates/bias"] = 1.0 + 0.3 * rng.standard_normal(p["RNN/gru_cell/gates/bias"].shape)
+    p["RNN/gru_cell/candidate/bias"] = 0.3 * rng.standard_normal(p["RNN/gru_cell/candidate/bias"].shape)
+    p["proj_out_b"] = 0.1 * rng.standard_normal(p["proj_out_b"].shape)
+    e = DenseGruEngine(B=B, T=T, Cp=4, Cfeat=16, GH=7, dtype=0, device="cpu", lib=EmuLib())
+    assert (e.I, e.H, e.Ip, e.Hp, e.Np) == (196, 245, 256, 256, 128)
+    e.load_tf_params(p)
+    back = e.op_to_tf(e.params.numpy())
+    for k in p:
+        assert np.allclose(back[k], np.asarray(p[k], np.float32)), k
+    c3d = SY.make_c3d(rng, B, T, dim_feature=16)
+    gt = O.normalize_probability_map(SY.make_gazemaps(rng, B, T, 7, 7)[0]).astype(np.float32)
+    logits = e.forward(c3d=torch.from_numpy(c3d), gt=torch.from_numpy(gt)).numpy()
+    ref, ref_probs, ref_loss, _ = O.forward_loss_grads("gaze_rnn", p, gt.astype(np.float64), c3d=c3d.astype(np.float64))
+    assert np.abs(logits - ref).max() <= 1e-4 * max(1.0, np.abs(ref).max())
+    assert np.abs(e.probs.numpy() - ref_probs).max() <= 1e-5
+    assert abs(float(e.loss[0]) - ref_loss) <= 1e-5 * abs(ref_loss)
+    assert np.all(e.Hf.numpy()[:, e.H:] == 0.0)                  # padded state columns stay exactly zero
+    # real sizes of the reference: 7*7*32 + 49 = 1617 units, padded 1600 / 1664 / 2432
+    big = DenseGruEngine.__new__(DenseGruEngine)
+    big.P, big.Cp = 49, 32
+    assert (49 * 32 + 49, (49 * 32 + 63) // 64 * 64, (1617 + 127) // 128 * 128, (2401 + 127) // 128 * 128) == (1617, 1600, 1664, 2432)
+
+
+def test_dense_gru_model_class_contract():
+    c = small_config(T=3, B=2)
+    c.dim_cnn_proj_dense = 4
+    c.trainable = False
+    ds = data(T=3)
+    m = gaze_rnn.GazePredictionGRU({'lib': EmuLib()}, ds, c)
+    assert type(m.engine).__name__ == "DenseGruEngine" and m.train_op is None
+    assert tuple(m.predicted_gazemaps.shape) == (2, 3, 49, 49)
+    assert m.single_step(train_mode=False) == 0 and np.isfinite(m.last_loss)
+    with pytest.raises(RuntimeError):
+        m.single_step(train_mode=True)
+    ret = m.generate(ds.valid, max_instances=2)
+    assert ret['pred_gazemap_list'].shape == (6, 49, 49)
+    assert np.allclose(ret['pred_gazemap_list'].sum(axis=(1, 2)), 1.0, atol=1e-5)
