@@ -290,20 +290,43 @@ struct Cfg {
   static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/ + kEpiScratchBytes;
 };
 
-template <int BN>
+// Resident-A-slab mode (SLAB = true).  Every tap of a tap GEMM reads the SAME rows shifted by tap_off, so per
+// (tile, k-chunk) the rows [m0 + min_off, m0 + max_off + 128) are fetched ONCE as one TMA box ("slab", <= 256 rows x
+// 128 bytes, SWIZZLE_128B) and the MMAs of all taps take their A operand from inside it: descriptor start address =
+// slab + (tap_off - min_off) * 128.  A start row that is not a multiple of the 8-row swizzle atom is legal because the
+// hardware applies the 128-byte swizzle to absolute shared-memory address bits (probed on B200: csrc/debug_umma.cu,
+// tools/umma_rowoff_probe.py - exact results for every offset with the descriptor's base-offset field left 0).
+// Only the per-tap weight boxes still stream: L2->SMEM traffic per k-chunk drops from ntaps*(16 KB + W) to
+// slab + ntaps*W (i2h: 432 -> 307 KB, head: 352 -> 117 KB).
+struct SlabCfg {
+  int rows;      // slab rows (multiple of 8)
+  int bytes;     // slab slot bytes (rows * 128 rounded up to 1024)
+  int min_off;   // smallest tap offset
+  int nw;        // weight-ring stages
+};
+constexpr int kSlabSlots = 2;
+constexpr int kSmemBudget = 227 * 1024;
+
+template <int BN, bool SLAB>
 __global__ void __launch_bounds__(NTHREADS, 1)
 tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                  const rgp_tapgemm_args a) {
+                  const rgp_tapgemm_args a, const SlabCfg sc) {
   using C = Cfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::kStages * C::kStageBytes);
+  constexpr int kWBytes = BN * BK * 2;
+  const int nstage = SLAB ? sc.nw : C::kStages;          // barrier pairs of the (weight) ring
+  const int ring_bytes = SLAB ? sc.nw * kWBytes + kSlabSlots * sc.bytes : C::kStages * C::kStageBytes;
+  uint8_t* slab0 = smem + (SLAB ? sc.nw * kWBytes : 0);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + ring_bytes);
   uint64_t* full = bars;
-  uint64_t* empty = bars + C::kStages;
-  uint64_t* tfull = bars + 2 * C::kStages;
+  uint64_t* empty = bars + nstage;
+  uint64_t* tfull = bars + 2 * nstage;
   uint64_t* tempty = tfull + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
-  float* scr_base = reinterpret_cast<float*>(smem + C::kStages * C::kStageBytes + 256);
+  uint64_t* afull = tempty + 2;                          // SLAB only
+  uint64_t* aempty = afull + kSlabSlots;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aempty + kSlabSlots);
+  float* scr_base = reinterpret_cast<float*>(smem + ring_bytes + 256);
   RowLite* rl_base = reinterpret_cast<RowLite*>(scr_base + 4 * 32 * kScrLd);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -315,8 +338,10 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
-    for (int i = 0; i < C::kStages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    for (int i = 0; i < nstage; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 4); }
+    if (SLAB)
+      for (int i = 0; i < kSlabSlots; ++i) { mbar_init(&afull[i], 1); mbar_init(&aempty[i], 1); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -332,7 +357,26 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 
   if (warp == 0) {
     // ===================== TMA producer =====================
-    if (lane == 0) {
+    if (SLAB && lane == 0) {
+      int ws = 0; uint32_t wph = 0;
+      int as = 0; uint32_t aph = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int mt = tile / ntiles, nt = tile - mt * ntiles;
+        const int m0 = mt * BM, n0 = nt * BN;
+        for (int kc = 0; kc < kchunks; ++kc) {
+          mbar_wait(&aempty[as], aph ^ 1);
+          mbar_expect_tx(&afull[as], (uint32_t)sc.rows * BK * 2);
+          tma_load_2d(slab0 + as * sc.bytes, &tmA, &afull[as], kc * BK, m0 + sc.min_off);
+          for (int tap = 0; tap < a.ntaps; ++tap) {
+            mbar_wait(&empty[ws], wph ^ 1);
+            mbar_expect_tx(&full[ws], kWBytes);
+            tma_load_2d(smem + ws * kWBytes, &tmB, &full[ws], kc * BK, tap * a.N + n0);
+            if (++ws == sc.nw) { ws = 0; wph ^= 1; }
+          }
+          if (++as == kSlabSlots) { as = 0; aph ^= 1; }
+        }
+      }
+    } else if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         const int mt = tile / ntiles, nt = tile - mt * ntiles;
@@ -354,11 +398,40 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     // instruction descriptor: D=f32, A=B=bf16, both K-major, N=BN, M=128
     constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
     int stage = 0; uint32_t phase = 0;
+    int aslot = 0; uint32_t aphase = 0;
     int acc = 0; uint32_t accphase = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       mbar_wait(&tempty[acc], accphase ^ 1);
       tc_fence_after();
       const uint32_t tacc = tmem_base + (uint32_t)(acc * C::kAccStride);
+      if (SLAB) {
+        // stage / phase walk the weight ring here; aslot / aphase the slab slots
+        for (int kc = 0; kc < kchunks; ++kc) {
+          mbar_wait(&afull[aslot], aphase);
+          for (int tap = 0; tap < a.ntaps; ++tap) {
+            mbar_wait(&full[stage], phase);
+            tc_fence_after();
+            if (lane == 0) {
+              const uint32_t sa = smem_u32(slab0 + aslot * sc.bytes) + (uint32_t)(a.tap_off[tap] - sc.min_off) * (BK * 2);
+              const uint32_t sb = smem_u32(smem + stage * kWBytes);
+              const uint64_t adesc = make_sdesc(sa), bdesc = make_sdesc(sb);
+#pragma unroll
+              for (int k = 0; k < BK / 16; ++k)
+                tc_mma_bf16(tacc, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (kc | tap | k) ? 1u : 0u);
+              tc_commit(&empty[stage]);
+              if (tap == a.ntaps - 1) {
+                tc_commit(&aempty[aslot]);
+                if (kc == kchunks - 1) tc_commit(&tfull[acc]);
+              }
+            }
+            __syncwarp();
+            if (++stage == sc.nw) { stage = 0; phase ^= 1; }
+          }
+          if (++aslot == kSlabSlots) { aslot = 0; aphase ^= 1; }
+        }
+        if (++acc == 2) { acc = 0; accphase ^= 1; }
+        continue;
+      }
       for (int ks = 0; ks < ksteps; ++ks) {
         mbar_wait(&full[stage], phase);
         tc_fence_after();
@@ -481,24 +554,57 @@ int make_map(const void* base, long long rows, int ld, int K, int boxrows, CUten
   return tc::encode_map_bf16(base, K, rows, (long long)ld * 2, BK, boxrows, out);
 }
 
+// RGP_SLAB=0 switches the resident-A-slab mode off (A/B timing)
+bool slab_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("RGP_SLAB");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v == 1;
+}
+
 template <int BN>
 int launch(const rgp_tapgemm_args& a, cudaStream_t s) {
   using C = Cfg<BN>;
+  // slab geometry: all taps of the tile inside one TMA box of <= 256 rows
+  SlabCfg sc{0, 0, 0, 0};
+  bool slab = false;
+  // narrow tiles (the N = 48 head GEMM) are bound by MMA issue / barrier latency, not by operand traffic: measured
+  // 0.905 ms with per-tap boxes vs 0.951 ms with the slab (profiles/r01_notes.md pass 7), so they keep the old path
+  if (a.ntaps > 1 && BN >= 128 && slab_enabled()) {
+    int mn = a.tap_off[0], mx = a.tap_off[0];
+    for (int i = 1; i < a.ntaps; ++i) { mn = a.tap_off[i] < mn ? a.tap_off[i] : mn; mx = a.tap_off[i] > mx ? a.tap_off[i] : mx; }
+    sc.rows = (BM + (mx - mn) + 7) & ~7;
+    sc.bytes = (sc.rows * BK * 2 + 1023) & ~1023;
+    sc.min_off = mn;
+    const int fixed = 1024 + 256 + kEpiScratchBytes + kSlabSlots * sc.bytes;
+    sc.nw = (kSmemBudget - fixed) / (BN * BK * 2);
+    if (sc.nw > 8) sc.nw = 8;
+    slab = sc.rows <= 256 && sc.nw >= 3;
+  }
   CUtensorMap tmA, tmB;
-  int rc = make_map(a.A, a.rowsA, a.lda, a.K, BM, &tmA);
+  int rc = make_map(a.A, a.rowsA, a.lda, a.K, slab ? sc.rows : BM, &tmA);
   if (rc) return rc;
   rc = make_map(a.Bw, (long long)a.ntaps * a.N, a.K, a.K, BN, &tmB);
   if (rc) return rc;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(tapgemm_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes);
+    cudaError_t e = cudaFuncSetAttribute(tapgemm_tc_kernel<BN, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(tapgemm_tc_kernel<BN, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget);
     if (e != cudaSuccess) { set_error("cudaFuncSetAttribute(smem=%d): %s", C::kSmemBytes, cudaGetErrorString(e)); return -5; }
     attr_set = true;
   }
   const int mtiles = (a.M + BM - 1) / BM, ntiles = a.N / BN;
   int grid = mtiles * ntiles;
   if (grid > num_sms()) grid = num_sms();
-  tapgemm_tc_kernel<BN><<<grid, NTHREADS, C::kSmemBytes, s>>>(tmA, tmB, a);
+  if (slab) {
+    const int smem_bytes = sc.nw * BN * BK * 2 + kSlabSlots * sc.bytes + 1024 + 256 + kEpiScratchBytes;
+    tapgemm_tc_kernel<BN, true><<<grid, NTHREADS, smem_bytes, s>>>(tmA, tmB, a, sc);
+  } else {
+    tapgemm_tc_kernel<BN, false><<<grid, NTHREADS, C::kSmemBytes, s>>>(tmA, tmB, a, sc);
+  }
   return check_launch("tapgemm_tc");
 }
 

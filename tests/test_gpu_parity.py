@@ -255,8 +255,10 @@ def test_wgrad_matches_numpy(engine, M, Ny, Nx, ldy, ycol0, taps):
     ("gaze_grcn", 256, 320, 1, 4, False),   # more tiles than SMs: CTAs walk several tiles
 ])
 def test_persistent_recurrence_matches_per_step_path(model, Ch, B, nsplit, mcast, train):
-    """rgp_convgru_seq_fwd (all T steps in one launch) against the per-step tap-GEMM path on the same bf16 operands:
-    same accumulation order and gate functions, so states, saved gates and logits agree to fp32 round-off."""
+    """rgp_convgru_seq_fwd (all T steps in one launch) against the per-step tap-GEMM path on the same bf16 operands and
+    gate functions.  The two accumulate in different orders (persistent kernel: tap-major; per-step slab GEMM: k-chunk
+    major), so pre-activations differ in their last fp32 bits; where that flips the bf16 rounding of a state element the
+    next step sees a one-ulp different operand.  States therefore agree to a fraction of a bf16 ulp, not to fp32 ulps."""
     T = 5
     p, c3d, _, gt = _case(model, min(B, 4), T, Ch)
     reps = (B + c3d.shape[0] - 1) // c3d.shape[0]
@@ -278,7 +280,7 @@ def test_persistent_recurrence_matches_per_step_path(model, Ch, B, nsplit, mcast
     for k in a:
         scale = np.abs(a[k]).max()
         # bf16 copies (hop, rh) may differ by one bf16 ulp where the fp32 values differ in their last bits
-        tol = 2.0 ** -7 if k in ("hop", "rh") else (1e-3 if k == "logits" else 1e-5)
+        tol = 2.0 ** -7 if k in ("hop", "rh") else (2e-3 if k == "logits" else 1e-3)
         assert np.abs(a[k] - b[k]).max() <= tol * scale + 1e-7, (k, np.abs(a[k] - b[k]).max(), scale)
 
 
