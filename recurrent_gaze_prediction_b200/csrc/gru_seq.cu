@@ -86,6 +86,20 @@ __device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity
       "r"(parity)
       : "memory");
 }
+// non-blocking probe of a barrier phase
+__device__ __forceinline__ bool mbar_test_cluster(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n"
+      ".reg .pred P1;\n"
+      "mbarrier.test_wait.parity.acquire.cluster.shared::cta.b64 P1, [%1], %2;\n"
+      "selp.u32 %0, 1, 0, P1;\n"
+      "}\n"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
 // TMA tile load delivered to the same shared-memory offset (and mbarrier offset) of every CTA in cta_mask
 __device__ __forceinline__ void tma_load_2d_mc(void* smem_dst, const CUtensorMap* tmap, uint64_t* bar, int c0, int c1,
                                                uint16_t cta_mask) {
@@ -119,14 +133,25 @@ __device__ __forceinline__ void stamp(bool on, long long it, int ev) {
   }
 }
 
+// State operand = a resident slab (same idea as the slab mode of tapgemm_tc.cu).  The 9 taps of the 3x3 conv read the
+// tile's rows shifted by ky*Wp + kx <= 2*Wp + 2, so per k-chunk ONE box of kSlabRows rows holds the operand of all
+// taps; the MMA's A descriptor starts at slab + off*128 (any row: the 128-byte swizzle acts on absolute smem address
+// bits, probed in csrc/debug_umma.cu).  The slab holds ALL k-chunks of the state (Ch/64 boxes) and is filled twice per
+// step: h_{t-1} (used by the r- and z-phase) and r.h (c-phase); box kc of r.h is fetched as soon as the z-phase has
+// issued its last MMA on box kc.  L2->SMEM traffic per step: 3*36 state boxes of 16 KB (1.7 MB) -> 2*Ch/64 boxes of
+// 19 KB (0.15 MB); only the weights (3.5 MB at Ch = 256) still stream.  k-steps run k-chunk-major (kc, tap).
+constexpr int kSlabRows = 152;                       // 128 + 2*Wp + 2 = 146 at G = 7, rounded to the 8-row atom
+constexpr int kSlabBoxBytes = kSlabRows * BK * 2;    // 19456 = 19 * 1024
+constexpr int kMaxKChunks = 4;                       // Ch <= 256
+
 template <int NH>
 struct SeqCfg {
   static constexpr int kStages = (NH >= 256) ? 4 : 6;
-  static constexpr int kABytes = BM * BK * 2;
+  static constexpr int kABytes = kMaxKChunks * kSlabBoxBytes;       // the slab
   static constexpr int kBBytes = NH * BK * 2;
   static constexpr int kTmemCols = 2 * NH;
   static constexpr int kBarBytes = 256;
-  static constexpr int kSmemBytes = kStages * (kABytes + kBBytes) + 1024 + kBarBytes;
+  static constexpr int kSmemBytes = kABytes + kStages * kBBytes + 1024 + kBarBytes;
 };
 
 template <int NH>
@@ -137,12 +162,12 @@ gru_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
   using C = SeqCfg<NH>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint8_t* ringA = smem;
-  uint8_t* ringB = smem + C::kStages * C::kABytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::kStages * (C::kABytes + C::kBBytes));
-  uint64_t* fullA = bars;
-  uint64_t* emptyA = fullA + C::kStages;
-  uint64_t* fullB = emptyA + C::kStages;
+  uint8_t* slab = smem;                                // kchunks boxes of kSlabRows x 64 bf16
+  uint8_t* ringB = smem + C::kABytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::kABytes + C::kStages * C::kBBytes);
+  uint64_t* fullA = bars;                              // per slab box (kMaxKChunks)
+  uint64_t* emptyA = fullA + kMaxKChunks;
+  uint64_t* fullB = emptyA + kMaxKChunks;
   uint64_t* emptyB = fullB + C::kStages;
   uint64_t* r_full = emptyB + C::kStages;
   uint64_t* z_full = r_full + 1;
@@ -177,10 +202,8 @@ gru_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmRH) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmUzr) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmUc) : "memory");
-    for (int i = 0; i < C::kStages; ++i) {
-      mbar_init(&fullA[i], 1); mbar_init(&emptyA[i], 1);
-      mbar_init(&fullB[i], 1); mbar_init(&emptyB[i], (uint32_t)cs);
-    }
+    for (int i = 0; i < kMaxKChunks; ++i) { mbar_init(&fullA[i], 1); mbar_init(&emptyA[i], 1); }
+    for (int i = 0; i < C::kStages; ++i) { mbar_init(&fullB[i], 1); mbar_init(&emptyB[i], (uint32_t)cs); }
     mbar_init(r_full, 1); mbar_init(z_full, 1); mbar_init(c_full, 1);
     mbar_init(rh_ready, EPI_WARPS * nsplit); mbar_init(h_ready, EPI_WARPS * nsplit);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -200,7 +223,7 @@ gru_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
   if (warp == 0) {
     // ===================== TMA producer: two rings, the weight ring runs up to kStages k-steps ahead =====================
     if (lane == 0) {
-      int sA = 0, sB = 0; uint32_t phA = 0, phB = 0;
+      int sB = 0; uint32_t phB = 0;
       long long it = 0;                                   // running step counter of this CTA (barrier phases)
       for (int tile = cluster_id; tile < mtiles; tile += nclusters) {
         const int m0 = tile * BM;
@@ -210,7 +233,7 @@ gru_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
           int iB = 0;                                                   // weight-ring cursor (k-step inside this step)
           auto issueB = [&]() {
             const int ph = iB / ksteps, ks = iB - ph * ksteps;
-            const int tap = ks / kchunks, kc = ks - tap * kchunks;
+            const int kc = ks / 9, tap = ks - kc * 9;                   // k-chunk-major
             mbar_wait_cluster(&emptyB[sB], phB ^ 1);                    // every CTA of the group has released this stage
             mbar_expect_tx(&fullB[sB], C::kBBytes);                     // the whole box: 1/cs from each CTA of the group
             const int brow = ((ph == 0) ? tap * 2 * Ch + Ch : ((ph == 1) ? tap * 2 * Ch : tap * Ch)) + col0;
@@ -225,25 +248,46 @@ gru_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
             if (++sB == C::kStages) { sB = 0; phB ^= 1; }
             ++iB;
           };
-          for (int iA = 0; iA < 3 * ksteps; ++iA) {
-            const int ph = iA / ksteps, ks = iA - ph * ksteps;
-            const int tap = ks / kchunks, kc = ks - tap * kchunks;
-            const bool gate_h = (ks == 0 && ph == 0 && it > 0), gate_rh = (ks == 0 && ph == 2);
-            if (gate_h || gate_rh) {
-              // the state rows are not ready yet, the weights are: fill the weight ring while the epilogue works
-              // (its slots free up as the MMAs of the previous phase drain, which never depends on this gate)
-              while (iB < 3 * ksteps && iB < iA + C::kStages) issueB();
-              if (gate_h) mbar_wait_cluster(h_ready, (uint32_t)((it - 1) & 1));
-              else        mbar_wait_cluster(rh_ready, (uint32_t)(it & 1));
-              fence_proxy_async();
+          // (1) while the c-epilogue of the previous step still holds the state gate: r-phase weights into the slots the
+          //     previous c-phase frees (their release never depends on the gate)
+          while (iB < C::kStages) issueB();
+          if (it > 0) { mbar_wait_cluster(h_ready, (uint32_t)((it - 1) & 1)); fence_proxy_async(); }
+          // (2) h_{t-1}: all k-chunks of the slab (box kc was released by the previous c-phase: release parity 1)
+          for (int kc = 0; kc < kchunks; ++kc) {
+            mbar_wait(&emptyA[kc], 1);
+            mbar_expect_tx(&fullA[kc], kSlabBoxBytes);
+            tma_load_2d(slab + kc * kSlabBoxBytes, &tmH, &fullA[kc], kc * BK, (int)rowH);
+          }
+          // (3) the weights of the three phases in ring order, and r.h box kc as soon as (a) the r-epilogue has published
+          //     the rows (rh_ready) and (b) the z-phase has issued its last MMA on box kc (release parity 0).  Both are
+          //     polled between weight issues; only when the weight ring is full of c-phase stages that cannot drain
+          //     without r.h (kStages ahead) does the producer block on them.
+          int nextRH = 0;
+          bool rh_ok = false;
+          auto loadRH = [&]() {
+            mbar_expect_tx(&fullA[nextRH], kSlabBoxBytes);
+            tma_load_2d(slab + nextRH * kSlabBoxBytes, &tmRH, &fullA[nextRH], nextRH * BK, (int)rowRH);
+            ++nextRH;
+          };
+          while (iB < 3 * ksteps) {
+            if (nextRH < kchunks) {
+              if (iB >= 2 * ksteps + C::kStages) {                    // must have r.h before more c-phase weights
+                if (!rh_ok) { mbar_wait_cluster(rh_ready, (uint32_t)(it & 1)); fence_proxy_async(); rh_ok = true; }
+                mbar_wait(&emptyA[nextRH], 0);
+                loadRH();
+                continue;
+              }
+              if (iB >= ksteps + 9 * (nextRH + 1)) {                  // the z-phase weights that free box nextRH are issued
+                if (!rh_ok && mbar_test_cluster(rh_ready, (uint32_t)(it & 1))) { fence_proxy_async(); rh_ok = true; }
+                if (rh_ok && mbar_test_cluster(&emptyA[nextRH], 0)) { loadRH(); continue; }
+              }
             }
-            const int off = (tap / 3) * Wp + (tap % 3);
-            mbar_wait(&emptyA[sA], phA ^ 1);
-            mbar_expect_tx(&fullA[sA], C::kABytes);
-            if (ph < 2) tma_load_2d(ringA + sA * C::kABytes, &tmH, &fullA[sA], kc * BK, (int)(rowH + off));
-            else        tma_load_2d(ringA + sA * C::kABytes, &tmRH, &fullA[sA], kc * BK, (int)(rowRH + off));
-            if (++sA == C::kStages) { sA = 0; phA ^= 1; }
-            if (iB <= iA) issueB();
+            issueB();
+          }
+          while (nextRH < kchunks) {                                    // (never taken: the ring forces r.h before the end)
+            if (!rh_ok) { mbar_wait_cluster(rh_ready, (uint32_t)(it & 1)); fence_proxy_async(); rh_ok = true; }
+            mbar_wait(&emptyA[nextRH], 0);
+            loadRH();
           }
         }
       }
@@ -251,7 +295,7 @@ gru_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
     constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(NH >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
-    int sA = 0, sB = 0; uint32_t phA = 0, phB = 0;
+    int sB = 0; uint32_t phB = 0;
     long long it = 0;
     for (int tile = cluster_id; tile < mtiles; tile += nclusters) {
       for (int t = 0; t < a.T; ++t, ++it) {
@@ -265,21 +309,24 @@ gru_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
           const uint32_t tacc = tmem_base + (uint32_t)(ph == 1 ? 0 : NH);
           uint64_t* done = (ph == 0) ? r_full : ((ph == 1) ? z_full : c_full);
           for (int ks = 0; ks < ksteps; ++ks) {
-            mbar_wait(&fullA[sA], phA);
+            const int kc = ks / 9, tap = ks - kc * 9;
+            // slab box kc: fill 2*it (h_{t-1}, completes barrier phase parity 0) serves ph 0 and 1, fill 2*it+1 (r.h,
+            // parity 1) serves ph 2
+            if (tap == 0 && ph != 1) mbar_wait(&fullA[kc], ph == 0 ? 0u : 1u);
             mbar_wait(&fullB[sB], phB);
             tc_fence_after();
             if (lane == 0) {
-              const uint64_t adesc = make_sdesc(smem_u32(ringA + sA * C::kABytes));
+              const int off = (tap / 3) * Wp + (tap % 3);
+              const uint64_t adesc = make_sdesc(smem_u32(slab + kc * kSlabBoxBytes) + (uint32_t)off * (BK * 2));
               const uint64_t bdesc = make_sdesc(smem_u32(ringB + sB * C::kBBytes));
 #pragma unroll
               for (int k = 0; k < BK / 16; ++k)
                 tc_mma_bf16(tacc, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (ks | k) ? 1u : 0u);
-              tc_commit(&emptyA[sA]);
+              if (tap == 8 && ph != 0) tc_commit(&emptyA[kc]);     // last use of this box by the z-phase / the c-phase
               if (cs == 1) tc_commit(&emptyB[sB]); else tc_commit_mc(&emptyB[sB], bmask);
               if (ks == ksteps - 1) tc_commit(done);
             }
             __syncwarp();
-            if (++sA == C::kStages) { sA = 0; phA ^= 1; }
             if (++sB == C::kStages) { sB = 0; phB ^= 1; }
           }
           stamp(blockIdx.x == 0 && lane == 0, it, ph == 0 ? 1 : (ph == 1 ? 2 : 4));
@@ -430,9 +477,9 @@ int launch_seq(const rgp_gru_seq_args& a, cudaStream_t s) {
   using C = SeqCfg<NH>;
   const int Ch = a.Ch, S = (a.G + 1) * (a.G + 1);
   CUtensorMap tmH, tmRH, tmUzr, tmUc;
-  int rc = encode_map_bf16(a.Hop, Ch, a.rowsH, (long long)Ch * 2, BK, BM, &tmH);
+  int rc = encode_map_bf16(a.Hop, Ch, a.rowsH, (long long)Ch * 2, BK, kSlabRows, &tmH);
   if (rc) return rc;
-  rc = encode_map_bf16(a.RH, Ch, a.rowsRH, (long long)Ch * 2, BK, BM, &tmRH);
+  rc = encode_map_bf16(a.RH, Ch, a.rowsRH, (long long)Ch * 2, BK, kSlabRows, &tmRH);
   if (rc) return rc;
   rc = encode_map_bf16(a.Uzr, Ch, 9LL * 2 * Ch, (long long)Ch * 2, BK, NH / a.mcast, &tmUzr);
   if (rc) return rc;
@@ -491,7 +538,9 @@ int convgru_seq_fwd(const rgp_gru_seq_args& a, cudaStream_t s) {
   RGP_CHECK_ARG(a.nsplit == 1 || a.nsplit == 2, "rgp_convgru_seq_fwd: nsplit=%d", a.nsplit);
   RGP_CHECK_ARG(a.mcast == 1 || a.mcast == 2 || a.mcast == 4 || a.mcast == 8, "rgp_convgru_seq_fwd: mcast=%d", a.mcast);
   RGP_CHECK_ARG(a.nsplit * a.mcast <= 8, "rgp_convgru_seq_fwd: cluster of %d CTAs (max 8)", a.nsplit * a.mcast);
-  RGP_CHECK_ARG(a.Ch % 64 == 0, "rgp_convgru_seq_fwd: Ch=%d must be a multiple of 64", a.Ch);
+  RGP_CHECK_ARG(a.Ch % 64 == 0 && a.Ch / 64 <= kMaxKChunks, "rgp_convgru_seq_fwd: Ch=%d must be a multiple of 64, at most %d",
+                a.Ch, 64 * kMaxKChunks);
+  RGP_CHECK_ARG(128 + 2 * (a.G + 1) + 2 <= kSlabRows, "rgp_convgru_seq_fwd: G=%d does not fit the state slab", a.G);
   RGP_CHECK_ARG((a.Rs == nullptr) == (a.Cs == nullptr), "rgp_convgru_seq_fwd: Rs and Cs must be both set (train) or both NULL");
   RGP_CHECK_ARG(a.Rs == nullptr || a.Zs != nullptr, "rgp_convgru_seq_fwd: training needs Zs, Rs and Cs");
   RGP_CHECK_ARG((a.bn_gamma == nullptr) == (a.bn_beta == nullptr), "rgp_convgru_seq_fwd: bn_gamma / bn_beta");
