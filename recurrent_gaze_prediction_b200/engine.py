@@ -64,13 +64,14 @@ class GazeEngine(object):
         self.tdt = _tdtype(dtype)
         self.taps3 = [ky * self.Wp + kx for ky in range(3) for kx in range(3)]
         # Persistent ConvGRU recurrence (rgp_convgru_seq_fwd: all T steps in one launch, one CTA per 128-row tile).
-        # Measured on B200 (profiles/r01_notes.md): it beats two tap-GEMM launches per step once there is about one
-        # tile per SM (3.0 vs 4.0 ms at 256 clips); below that the per-step GEMMs, which spread one step over all
-        # SMs, win.  RGP_SEQ=0/1 forces the choice (A/B checks); nsplit / mcast are the kernel's cluster options.
+        # Measured on B200 (profiles/r01_notes.md): with the resident state slab it beats two tap-GEMM launches per step
+        # from 64 tiles up (128 clips, 2-CTA channel split: 2.18 vs 2.81 ms; 256 clips: 2.63 vs 3.9 ms); below that the
+        # per-step GEMMs, which spread one step over all SMs, are kept.  RGP_SEQ=0/1 forces the choice (A/B checks);
+        # nsplit / mcast are the kernel's cluster options.
         mtiles = (B * self.S + 127) // 128
         if seq is None:
             env = os.environ.get("RGP_SEQ", "")
-            seq = (dtype == 1 and engine != 1 and Ch in (128, 256) and (env == "1" or (env != "0" and mtiles >= 100)))
+            seq = (dtype == 1 and engine != 1 and Ch in (128, 256) and (env == "1" or (env != "0" and mtiles >= 64)))
         self.use_seq = bool(seq) and (not self.lstm) and 128 % self.S == 0
         self.nsplit = nsplit or int(os.environ.get("RGP_SEQ_NSPLIT", "0")) or (2 if (Ch == 256 and mtiles <= 74) else 1)
         # mcast > 1: every weight box is fetched once per cluster and TMA-multicast; measured slower (the bound is the
