@@ -7,24 +7,42 @@ namespace rgp {
 // ---------------------------------------------------------------------------------------------
 // pack: gaze_grcn.py:225-227 (NCHW -> NHWC transpose of the C3D blob) + cast + time-major reorder
 // ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void st4_op(float* p, float a, float b, float c, float d) {
+  *reinterpret_cast<float4*>(p) = make_float4(a, b, c, d);
+}
+__device__ __forceinline__ void st4_op(__nv_bfloat16* p, float a, float b, float c, float d) {
+  __nv_bfloat162 lo = __floats2bfloat162_rn(a, b), hi = __floats2bfloat162_rn(c, d);
+  uint2 u;
+  u.x = *reinterpret_cast<uint32_t*>(&lo);
+  u.y = *reinterpret_cast<uint32_t*>(&hi);
+  *reinterpret_cast<uint2*>(p) = u;
+}
+
+// One CTA = one frame x 64 channels.  In: 64 x P floats, contiguous (16-byte loads, copied linearly into shared memory:
+// conflict-free).  Out: P rows x 64 channels; a thread converts 4 consecutive channels of one position (4 shared reads at
+// stride P, 2-way bank conflicts) and stores them as one 8-byte (bf16) / 16-byte (fp32) word, so a warp writes two full
+// 128-byte row segments per instruction instead of 64 bytes of 2-byte stores.
 template <typename TA>
 __global__ void __launch_bounds__(256) pack_c3d_kernel(const float* __restrict__ c3d, TA* __restrict__ out,
                                                         int B, int T, int C, int P) {
-  extern __shared__ float tile[];  // [64][P+1]
+  extern __shared__ float tile[];  // [64][P]
   const int f_in = blockIdx.x;     // b*T + t
   const int b = f_in / T, t = f_in - b * T;
   const int c0 = blockIdx.y * 64;
   const float* src = c3d + ((long long)f_in * C + c0) * P;
   const int n = 64 * P;
-  for (int i = threadIdx.x; i < n; i += 256) {
-    int c = i / P, p = i - c * P;
-    tile[c * (P + 1) + p] = src[i];
+  if (((n | (int)(((long long)f_in * C + c0) * P)) & 3) == 0) {
+    const float4* s4 = reinterpret_cast<const float4*>(src);
+    float4* t4 = reinterpret_cast<float4*>(tile);
+    for (int i = threadIdx.x; i < n / 4; i += 256) t4[i] = s4[i];
+  } else {
+    for (int i = threadIdx.x; i < n; i += 256) tile[i] = src[i];
   }
   __syncthreads();
   TA* dst = out + ((long long)(t * B + b) * P) * C + c0;
-  for (int i = threadIdx.x; i < n; i += 256) {
-    int p = i >> 6, c = i & 63;
-    OpT<TA>::st(dst + (long long)p * C + c, tile[c * (P + 1) + p]);
+  for (int i = threadIdx.x; i < 16 * P; i += 256) {
+    const int p = i >> 4, c = (i & 15) * 4;
+    st4_op(dst + (long long)p * C + c, tile[c * P + p], tile[(c + 1) * P + p], tile[(c + 2) * P + p], tile[(c + 3) * P + p]);
   }
 }
 
@@ -377,7 +395,7 @@ extern "C" {
 int rgp_pack_c3d(const float* c3d, void* out, int B, int T, int C, int P, int dtype, void* stream) {
   RGP_CHECK_ARG(C % 64 == 0, "rgp_pack_c3d: C=%d must be a multiple of 64", C);
   dim3 grid(B * T, C / 64);
-  size_t sm = (size_t)64 * (P + 1) * sizeof(float);
+  size_t sm = (size_t)64 * P * sizeof(float);
   if (sm > 48 * 1024) {
     cudaFuncSetAttribute(pack_c3d_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
     cudaFuncSetAttribute(pack_c3d_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
