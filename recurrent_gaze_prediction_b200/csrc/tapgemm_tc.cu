@@ -488,6 +488,60 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           q.m = r.m; q.flags = (r.inrange ? 1 : 0) | (r.valid ? 2 : 0); q.prow = r.prow; q.orow = r.orow;
           rl[lane] = q;
         }
+        if (quad && (a.epi == RGP_EPI_STORE_F32 || a.epi == RGP_EPI_PROJ)) {
+          // Pure-store epilogues (i2h pre-activations, projection): the 8 rows a lane serves are the same for every
+          // 32-column chunk of the tile, so their destination pointers are formed once per tile and a chunk is
+          // TMEM -> scratch transpose -> 8 x (16-byte scratch read, [bias,] one 16-/8-byte store): ~110 instructions
+          // instead of the ~460 of the generic quad path (row records re-read from shared memory and a switch on the
+          // epilogue kind per store) - the projection was bound by exactly that (ncu: 70 % of all samples there).
+          __syncwarp();
+          const int rr = lane >> 3, cg = (lane & 7) * 4;
+          const bool proj = a.epi == RGP_EPI_PROJ;
+          char* rowp[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const RowLite q = rl[4 * j + rr];
+            rowp[j] = nullptr;
+            if (q.flags & 1)
+              rowp[j] = proj ? reinterpret_cast<char*>((__nv_bfloat16*)a.out_op + q.orow * a.ldo + n0 + cg)
+                             : reinterpret_cast<char*>(a.out_f32 + (long long)q.m * a.ldo + n0 + cg);
+          }
+          if (proj) {
+#pragma unroll 1
+            for (int c = 0; c < BN; c += 32) {
+              float v[32];
+              tc_ld32(tbase + (uint32_t)c, v);
+#pragma unroll
+              for (int i = 0; i < 8; ++i)
+                st4(scr + lane * kScrLd + 4 * i, make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]));
+              __syncwarp();
+              const float4 g = a.bias ? ld4(a.bias + n0 + c + cg) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                float4 t = ld4(scr + (4 * j + rr) * kScrLd + cg);
+                t.x += g.x; t.y += g.y; t.z += g.z; t.w += g.w;
+                if (rowp[j]) st_bf16x4(reinterpret_cast<__nv_bfloat16*>(rowp[j]) + c, t);
+              }
+              __syncwarp();
+            }
+          } else {
+#pragma unroll 1
+            for (int c = 0; c < BN; c += 32) {
+              float v[32];
+              tc_ld32(tbase + (uint32_t)c, v);
+#pragma unroll
+              for (int i = 0; i < 8; ++i)
+                st4(scr + lane * kScrLd + 4 * i, make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]));
+              __syncwarp();
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const float4 t = ld4(scr + (4 * j + rr) * kScrLd + cg);
+                if (rowp[j]) st4(reinterpret_cast<float*>(rowp[j]) + c, t);
+              }
+              __syncwarp();
+            }
+          }
+        } else
 #pragma unroll 1
         for (int c = 0; c < BN; c += 32) {
           float v[32];
