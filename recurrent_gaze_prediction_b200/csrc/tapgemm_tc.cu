@@ -577,12 +577,37 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           }
         }
       } else {
+        if (BN == 48 && a.epi == RGP_EPI_HEAD && a.N == 48) {
+          // composed head (gaze_grcn.py:326-366): the 36 classes of a row are the 6x6 pixel block at (6a-3, 6b-3).
+          // All 48 accumulators are read first, then the block is written with compile-time offsets - no per-element
+          // switch / division (the generic element path made this GEMM epilogue-bound).
+          float v[48];
+          tc_ld16(tbase, v);
+          tc_ld16(tbase + 16u, v + 16);
+          tc_ld16(tbase + 32u, v + 32);
+          if (r.inrange && r.valid) {
+            const float bias = a.bias[0];
+            float* o = a.out_f32 + r.obase;
+#pragma unroll
+            for (int ry = 0; ry < 6; ++ry) {
+              const int Y = r.hy + ry;
+              if (Y >= 0 && Y < 49) {
+#pragma unroll
+                for (int rx = 0; rx < 6; ++rx) {
+                  const int X = r.hx + rx;
+                  if (X >= 0 && X < 49) o[Y * 49 + X] = v[ry * 6 + rx] + bias;
+                }
+              }
+            }
+          }
+        } else {
 #pragma unroll 1
-        for (int c = 0; c < BN; c += 16) {
-          float v[16];
-          tc_ld16(tbase + (uint32_t)c, v);
+          for (int c = 0; c < BN; c += 16) {
+            float v[16];
+            tc_ld16(tbase + (uint32_t)c, v);
 #pragma unroll 4
-          for (int i = 0; i < 16; ++i) epi_elem<__nv_bfloat16>(a, r, n0 + c + i, v[i]);
+            for (int i = 0; i < 16; ++i) epi_elem<__nv_bfloat16>(a, r, n0 + c + i, v[i]);
+          }
         }
       }
       tc_fence_before();
