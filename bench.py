@@ -128,9 +128,22 @@ def cpu_reference_step(model, p, c3d, gt, train=False):
     return float(loss), probs
 
 
+def use_all_host_threads():
+    """torchrun exports OMP_NUM_THREADS=1 to every rank; the CPU legs are meant to use every host core this process may
+    run on (the other ranks do no CPU work while rank 0 times the reference)."""
+    try:
+        n = len(os.sched_getaffinity(0))
+    except AttributeError:
+        n = os.cpu_count() or 1
+    if torch.get_num_threads() < n:
+        torch.set_num_threads(n)
+    return torch.get_num_threads()
+
+
 def run_reference(args, rank, world):
     if rank != 0:
         return
+    use_all_host_threads()
     from oracle import model_oracle as O
     from recurrent_gaze_prediction_b200 import synthetic as SY
     B = args.cpu_clips
@@ -357,6 +370,7 @@ def main():
             raise SystemExit("--entry emb has no CPU reference leg: pass --no-cpu-baseline")
         c3 = c3d_pool[:nb]
         g = gt_pool[:nb]
+        use_all_host_threads()
         cpu_reference_step(args.model, pc, c3, g, train)
         t0 = time.perf_counter()
         n = 0
