@@ -23,6 +23,17 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+# torchrun exports OMP_NUM_THREADS=1 to every rank before Python starts, and the OpenMP / oneDNN pools are sized from it
+# at import time.  The reference arm (rank 0 alone does CPU work) is meant to use every host core: lift the cap before
+# torch is imported.
+if "reference" in sys.argv and os.environ.get("RANK", "0") == "0":
+    try:
+        _ncores = len(os.sched_getaffinity(0))
+    except AttributeError:
+        _ncores = os.cpu_count() or 1
+    for _k in ("OMP_NUM_THREADS", "MKL_NUM_THREADS"):
+        os.environ[_k] = str(_ncores)
+
 import numpy as np
 import torch
 
