@@ -29,28 +29,41 @@ __device__ __forceinline__ float tanh_fast(float x) { float y; asm("tanh.approx.
 __device__ __forceinline__ float sigmoid_fast(float x) { return fmaf(0.5f, tanh_fast(0.5f * x), 0.5f); }
 
 // ---- vectorised row-chunk epilogue helpers (one thread = one output row, 32 consecutive columns) ----
+// 256-bit accesses (sm_100: LDG/STG.E.ENL2.256): a thread-per-row warp access touches 32 different lines per instruction,
+// so an epilogue array costs its instruction count x 32 L1 tag lookups - 256-bit words halve that against float4
+// (measured in the persistent kernel: c-epilogue 20 -> 14 us).  The `vec` condition of the callers guarantees 32-byte
+// aligned row starts.
+__device__ __forceinline__ void ld8(const float* p, float* v) {
+  asm volatile("ld.global.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7])
+               : "l"(p)
+               : "memory");
+}
+__device__ __forceinline__ void st8(float* p, const float* v) {
+  asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]),
+               "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7])
+               : "memory");
+}
 __device__ __forceinline__ void ldf32(const float* p, float v[32]) {
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    float4 t = reinterpret_cast<const float4*>(p)[i];
-    v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
-  }
+  for (int i = 0; i < 4; ++i) ld8(p + 8 * i, v + 8 * i);
 }
 __device__ __forceinline__ void stf32(float* p, const float v[32]) {
 #pragma unroll
-  for (int i = 0; i < 8; ++i) reinterpret_cast<float4*>(p)[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+  for (int i = 0; i < 4; ++i) st8(p + 8 * i, v + 8 * i);
 }
 __device__ __forceinline__ void stbf32(__nv_bfloat16* p, const float v[32]) {
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    __nv_bfloat162 b0 = __floats2bfloat162_rn(v[8 * i], v[8 * i + 1]);
-    __nv_bfloat162 b1 = __floats2bfloat162_rn(v[8 * i + 2], v[8 * i + 3]);
-    __nv_bfloat162 b2 = __floats2bfloat162_rn(v[8 * i + 4], v[8 * i + 5]);
-    __nv_bfloat162 b3 = __floats2bfloat162_rn(v[8 * i + 6], v[8 * i + 7]);
-    uint4 u;
-    u.x = *reinterpret_cast<uint32_t*>(&b0); u.y = *reinterpret_cast<uint32_t*>(&b1);
-    u.z = *reinterpret_cast<uint32_t*>(&b2); u.w = *reinterpret_cast<uint32_t*>(&b3);
-    reinterpret_cast<uint4*>(p)[i] = u;
+  for (int i = 0; i < 2; ++i) {
+    uint32_t u[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      __nv_bfloat162 b = __floats2bfloat162_rn(v[16 * i + 2 * j], v[16 * i + 2 * j + 1]);
+      u[j] = *reinterpret_cast<uint32_t*>(&b);
+    }
+    asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p + 16 * i), "r"(u[0]), "r"(u[1]), "r"(u[2]),
+                 "r"(u[3]), "r"(u[4]), "r"(u[5]), "r"(u[6]), "r"(u[7])
+                 : "memory");
   }
 }
 
@@ -454,7 +467,7 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     // ===================== epilogue (warps 2..5 -> TMEM lane groups (warp % 4)) =====================
     const int lg = warp & 3;
     int acc = 0; uint32_t accphase = 0;
-    const bool vec = (a.N % 32 == 0) && (a.ldo % 8 == 0) && (a.ldx % 4 == 0) && (a.Ch % 32 == 0) && (a.ldg % 8 == 0);
+    const bool vec = (a.N % 32 == 0) && (a.ldo % 16 == 0) && (a.ldx % 8 == 0) && (a.Ch % 32 == 0) && (a.ldg % 16 == 0);
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const int mt = tile / ntiles, nt = tile - mt * ntiles;
       const int m0 = mt * BM, n0 = nt * BN;
