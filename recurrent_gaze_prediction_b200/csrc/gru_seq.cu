@@ -186,7 +186,8 @@ gru_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
   uint64_t* c_full = z_full + 1;
   uint64_t* rh_ready = c_full + 1;     // r.h rows of this step are in global memory (all CTAs of the cluster)
   uint64_t* h_ready = rh_ready + 1;    // h_t rows are in global memory (all CTAs of the cluster)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(h_ready + 1);
+  uint64_t* z_free = h_ready + 1;      // the z columns of TMEM (they carry h_t through the c-epilogue's tail) are read out
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(z_free + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // cluster = mcast tiles x nsplit channel halves; CTA rank = mrank * nsplit + nrank
@@ -218,6 +219,7 @@ gru_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
     for (int i = 0; i < C::kStages; ++i) { mbar_init(&fullB[i], 1); mbar_init(&emptyB[i], (uint32_t)cs); }
     mbar_init(r_full, 1); mbar_init(z_full, 1); mbar_init(c_full, 1);
     mbar_init(rh_ready, EPI_WARPS * nsplit); mbar_init(h_ready, EPI_WARPS * nsplit);
+    mbar_init(z_free, EPI_WARPS);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -316,6 +318,7 @@ gru_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
           // of this step (ph 2) has read them; z columns once the previous c-epilogue is done (implied by ph 0's wait)
           if (ph == 0 && it > 0) mbar_wait_cluster(h_ready, (uint32_t)((it - 1) & 1));
           if (ph == 2) mbar_wait_cluster(rh_ready, (uint32_t)(it & 1));
+          if (ph == 1 && it > 0) mbar_wait(z_free, (uint32_t)((it - 1) & 1));   // tail of the previous c-epilogue
           tc_fence_after();
           if (ph != 1) stamp(blockIdx.x == 0 && lane == 0, it, ph == 0 ? 0 : 3);
           const uint32_t tacc = tmem_base + (uint32_t)(ph == 1 ? 0 : NH);
@@ -432,6 +435,10 @@ gru_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
         mbar_wait(c_full, par);
         tc_fence_after();
         stamp(ts_on, it, 9);
+        // The next step's MMAs need only the bf16 operand rows of h_t.  Critical part: candidate, state update, operand
+        // rows (and the saved candidate when training); h_t itself is parked in the z columns of TMEM (z is dead once h_t
+        // is formed).  The tail - fp32 master rows and the BN-scaled head rows - is written from there after h_ready has
+        // been signalled, i.e. under the r-phase MMAs of step t+1; z_free orders it before that step's z-phase.
 #pragma unroll 1
         for (int c = 0; c < CW; c += 32) {
           const int n = col0 + cb + c;
@@ -447,19 +454,10 @@ gru_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
               ldf32(hprev + n, xx);
 #pragma unroll
               for (int i = 0; i < 32; ++i) v[i] = zz[i] * xx[i] + (1.0f - zz[i]) * v[i];
-              stf32(hnext + n, v);
               stbf32(hop_next + n, v);
-              if (a.HS) {
-                if (a.bn_gamma) {
-                  ldf32(a.bn_gamma + (long long)t * Ch + n, xx);
-                  ldf32(a.bn_beta + (long long)t * Ch + n, zz);
-#pragma unroll
-                  for (int i = 0; i < 32; ++i) v[i] = xx[i] * (v[i] * a.alpha) + zz[i];
-                }
-                stbf32((TA*)a.HS + orow * Ch + n, v);
-              }
             }
           }
+          tc_st32(tlane + (uint32_t)(cb + c), v);
         }
         tc_fence_before();
         __threadfence();
@@ -470,6 +468,31 @@ gru_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
           else mbar_arrive(h_ready);
         }
         stamp(ts_on, it, 10);
+        // ---------------- tail of the c-epilogue (off the critical path) ----------------
+        tc_fence_after();
+#pragma unroll 1
+        for (int c = 0; c < CW; c += 32) {
+          const int n = col0 + cb + c;
+          float v[32], xx[32];
+          tc_ld32(tlane + (uint32_t)(cb + c), v);
+          if (valid) {
+            stf32(hnext + n, v);
+            if (a.HS) {
+              if (a.bn_gamma) {
+                ldf32(a.bn_gamma + (long long)t * Ch + n, xx);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] = xx[i] * (v[i] * a.alpha);
+                ldf32(a.bn_beta + (long long)t * Ch + n, xx);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] += xx[i];
+              }
+              stbf32((TA*)a.HS + orow * Ch + n, v);
+            }
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(z_free);
       }
     }
   }
