@@ -356,7 +356,7 @@ def main():
                 "bound": "tensor", "achieved": ach, "peak": tf_sus, "unit": "TFLOP/s", "frac": ach / tf_sus,
                 "peak_source": which + " (sustained bf16; burst %.1f)" % tf_burst,
                 "traffic": 2.3048e9 if default_cfg else None,
-                "traffic_source": "profiles/r01_ncu_full_fwd_pass9.txt (0.595 GB read + 1.710 GB written per launch)" if default_cfg else None,
+                "traffic_source": "profiles/r01_ncu_full_fwd_pass17.txt (0.595 GB read + 1.710 GB written per launch)" if default_cfg else None,
                 "ms_per_launch": i2h_ms, "stage_ms": evs}
         # second view: the recurrence (persistent kernel when the engine picked it).  Algorithmic work per frame
         # (SURVEY 8d): 2*3*(3G-2)^2*Ch^2 flop; bytes = read 3 gate pre-activations + write h, fp32
@@ -367,7 +367,7 @@ def main():
                "ms": rec_ms, "tensor_TFLOPs": fl["h2h"] * B * T / (rec_ms * 1e-3) / 1e12,
                "tensor_frac": fl["h2h"] * B * T / (rec_ms * 1e-3) / 1e12 / tf_sus,
                "hbm_GBps": rec_bytes / (rec_ms * 1e-3) / 1e9, "hbm_frac": rec_bytes / (rec_ms * 1e-3) / 1e9 / hbm,
-               "traffic": 3.6109e9 if (default_cfg and eng.use_seq) else None}
+               "traffic": 3.5349e9 if (default_cfg and eng.use_seq) else None}
         roof["recurrence"] = rec
         if train:
             fwd()
