@@ -316,8 +316,11 @@ struct SlabCfg {
   int bytes;     // slab slot bytes (rows * 128 rounded up to 1024)
   int min_off;   // smallest tap offset
   int nw;        // weight-ring stages
+  int slots;     // slab slots (k-chunks of A in flight)
 };
-constexpr int kSlabSlots = 2;
+constexpr int kSlabMaxSlots = 4;
+constexpr int kSlabBarBytes = 512;     // (2 * nw + 8) mbarriers + the TMEM slot, nw <= kSlabMaxW
+constexpr int kSlabMaxW = 24;
 constexpr int kSmemBudget = 227 * 1024;
 
 template <int BN, bool SLAB>
@@ -329,7 +332,7 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   constexpr int kWBytes = BN * BK * 2;
   const int nstage = SLAB ? sc.nw : C::kStages;          // barrier pairs of the (weight) ring
-  const int ring_bytes = SLAB ? sc.nw * kWBytes + kSlabSlots * sc.bytes : C::kStages * C::kStageBytes;
+  const int ring_bytes = SLAB ? sc.nw * kWBytes + sc.slots * sc.bytes : C::kStages * C::kStageBytes;
   uint8_t* slab0 = smem + (SLAB ? sc.nw * kWBytes : 0);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + ring_bytes);
   uint64_t* full = bars;
@@ -337,9 +340,9 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   uint64_t* tfull = bars + 2 * nstage;
   uint64_t* tempty = tfull + 2;
   uint64_t* afull = tempty + 2;                          // SLAB only
-  uint64_t* aempty = afull + kSlabSlots;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aempty + kSlabSlots);
-  float* scr_base = reinterpret_cast<float*>(smem + ring_bytes + 256);
+  uint64_t* aempty = afull + kSlabMaxSlots;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aempty + kSlabMaxSlots);
+  float* scr_base = reinterpret_cast<float*>(smem + ring_bytes + (SLAB ? kSlabBarBytes : 256));
   RowLite* rl_base = reinterpret_cast<RowLite*>(scr_base + 4 * 32 * kScrLd);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -354,7 +357,7 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     for (int i = 0; i < nstage; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 4); }
     if (SLAB)
-      for (int i = 0; i < kSlabSlots; ++i) { mbar_init(&afull[i], 1); mbar_init(&aempty[i], 1); }
+      for (int i = 0; i < kSlabMaxSlots; ++i) { mbar_init(&afull[i], 1); mbar_init(&aempty[i], 1); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -386,7 +389,7 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             tma_load_2d(smem + ws * kWBytes, &tmB, &full[ws], kc * BK, tap * a.N + n0);
             if (++ws == sc.nw) { ws = 0; wph ^= 1; }
           }
-          if (++as == kSlabSlots) { as = 0; aph ^= 1; }
+          if (++as == sc.slots) { as = 0; aph ^= 1; }
         }
       }
     } else if (lane == 0) {
@@ -440,7 +443,7 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             __syncwarp();
             if (++stage == sc.nw) { stage = 0; phase ^= 1; }
           }
-          if (++aslot == kSlabSlots) { aslot = 0; aphase ^= 1; }
+          if (++aslot == sc.slots) { aslot = 0; aphase ^= 1; }
         }
         if (++acc == 2) { acc = 0; accphase ^= 1; }
         continue;
@@ -660,19 +663,21 @@ template <int BN>
 int launch(const rgp_tapgemm_args& a, cudaStream_t s) {
   using C = Cfg<BN>;
   // slab geometry: all taps of the tile inside one TMA box of <= 256 rows
-  SlabCfg sc{0, 0, 0, 0};
+  SlabCfg sc{0, 0, 0, 0, 2};
   bool slab = false;
-  // narrow tiles (the N = 48 head GEMM) are bound by MMA issue / barrier latency, not by operand traffic: measured
-  // 0.905 ms with per-tap boxes vs 0.951 ms with the slab (profiles/r01_notes.md pass 7), so they keep the old path
+  // Narrow tiles (the N = 48 head GEMM) keep the per-tap boxes: they are bound by the cost of their small MMAs (~150 clk per
+  // 128x48x16 MMA, 580 clk per k-step whatever the operand traffic), measured 0.87 ms per-tap vs 0.95 ms slab with an 8-stage
+  // weight ring and 0.93 ms with 24 stages and 4 slab slots (profiles/r01_notes.md passes 7 and 18).
   if (a.ntaps > 1 && BN >= 128 && slab_enabled()) {
     int mn = a.tap_off[0], mx = a.tap_off[0];
     for (int i = 1; i < a.ntaps; ++i) { mn = a.tap_off[i] < mn ? a.tap_off[i] : mn; mx = a.tap_off[i] > mx ? a.tap_off[i] : mx; }
     sc.rows = (BM + (mx - mn) + 7) & ~7;
     sc.bytes = (sc.rows * BK * 2 + 1023) & ~1023;
     sc.min_off = mn;
-    const int fixed = 1024 + 256 + kEpiScratchBytes + kSlabSlots * sc.bytes;
+    sc.slots = (BN <= 64) ? kSlabMaxSlots : 2;      // narrow tiles finish a k-chunk faster than a slab load takes
+    const int fixed = 1024 + kSlabBarBytes + kEpiScratchBytes + sc.slots * sc.bytes;
     sc.nw = (kSmemBudget - fixed) / (BN * BK * 2);
-    if (sc.nw > 8) sc.nw = 8;
+    if (sc.nw > kSlabMaxW) sc.nw = kSlabMaxW;
     slab = sc.rows <= 256 && sc.nw >= 3;
   }
   CUtensorMap tmA, tmB;
@@ -692,7 +697,7 @@ int launch(const rgp_tapgemm_args& a, cudaStream_t s) {
   int grid = mtiles * ntiles;
   if (grid > num_sms()) grid = num_sms();
   if (slab) {
-    const int smem_bytes = sc.nw * BN * BK * 2 + kSlabSlots * sc.bytes + 1024 + 256 + kEpiScratchBytes;
+    const int smem_bytes = sc.nw * BN * BK * 2 + sc.slots * sc.bytes + 1024 + kSlabBarBytes + kEpiScratchBytes;
     tapgemm_tc_kernel<BN, true><<<grid, NTHREADS, smem_bytes, s>>>(tmA, tmB, a, sc);
   } else {
     tapgemm_tc_kernel<BN, false><<<grid, NTHREADS, C::kSmemBytes, s>>>(tmA, tmB, a, sc);
