@@ -575,9 +575,13 @@ class GazeEngine(object):
                 lib.rgp_bn_bwd_all(self.dhs.data_ptr(), self._slab(self.Hf, 1), g("bn_gamma"), g("bn_beta"), alpha,
                                    B, T, G, Ch, s)
         else:
-            for t in range(T):
-                lib.rgp_fc_head_bwd(self.dlogits.data_ptr(), self._slab(self.Hf, t + 1), self._ptr("out_W"),
-                                    self._slab(self.dhs, t), g("out_W"), g("out_b"), B, T, t, G, Ch, s)
+            if 256 % Ch == 0:
+                lib.rgp_fc_head_bwd_all(self.dlogits.data_ptr(), self._slab(self.Hf, 1), self._ptr("out_W"),
+                                        self.dhs.data_ptr(), g("out_W"), g("out_b"), B, T, G, Ch, s)
+            else:
+                for t in range(T):
+                    lib.rgp_fc_head_bwd(self.dlogits.data_ptr(), self._slab(self.Hf, t + 1), self._ptr("out_W"),
+                                        self._slab(self.dhs, t), g("out_W"), g("out_b"), B, T, t, G, Ch, s)
         self._mark("head_bwd")
         btaps = [Wp + 1 - o for o in self.taps3]
         rowsT = T * M

@@ -91,6 +91,7 @@ _SIGS = {
     "rgp_bn_bwd_all": [_vp, _vp, _vp, _vp, _f, _i, _i, _i, _i, _vp],
     "rgp_colsum": [_vp, _i, _i, _i, _vp, _i, _vp],
     "rgp_fc_head_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp],
+    "rgp_fc_head_bwd_all": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
     # dense-GRU variant (gaze_rnn.py:283-359)
     "rgp_dense_pack": [_vp, _i, _vp, _vp, _i, _ll, _i, _i, _i, _vp],
     "rgp_dense_gru_ru": [_vp, _i, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],

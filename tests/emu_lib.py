@@ -692,6 +692,13 @@ class EmuLib(object):
             self.rgp_tapgemm(C.byref(g), stream)
         return 0
 
+    def rgp_fc_head_bwd_all(self, dl, h1, w, dhs, gw, gb, B, T, G, Ch, stream):
+        S = (G + 1) * (G + 1)
+        for t in range(T):
+            off = t * B * S * Ch * 4
+            self.rgp_fc_head_bwd(dl, int(h1) + off, w, int(dhs) + off, gw, gb, B, T, t, G, Ch, stream)
+        return 0
+
     def rgp_bn_bwd_all(self, dhs, h, dgamma, dbeta, alpha, B, T, G, Ch, stream):
         S = (G + 1) * (G + 1)
         for t in range(T):

@@ -308,3 +308,45 @@ def test_grid14_long_sequence_convlstm_states(dtype):
         assert (got - h).abs().max() <= tol * max(1.0, float(h.abs().max())), t
     c_fin = eng.read_state(T)[0].cpu().double()
     assert (c_fin - state[..., :Ch]).abs().max() <= tol * max(1.0, float(state.abs().max()))
+
+
+def test_fc_head_backward_all_steps_matches_per_step_and_numpy():
+    """rgp_fc_head_bwd_all (one launch for all T) against the per-step kernel and a float64 numpy statement of the same
+    per-position FC backward: dhs[t, m] = dlogit * w, gW = sum dlogit * h, gb = sum dlogit."""
+    lib = L.get_lib()
+    B, T, G, Ch = 3, 5, 14, 128
+    Wp, S = G + 1, (G + 1) ** 2
+    M = B * S
+    rng = np.random.RandomState(3)
+    dl = torch.from_numpy(rng.randn(B, T, G, G).astype(np.float32)).cuda()
+    h = torch.from_numpy(rng.randn((T + 1) * M + Wp + 2, Ch).astype(np.float32)).cuda()
+    w = torch.from_numpy(rng.randn(Ch).astype(np.float32)).cuda()
+    out = []
+    for batched in (False, True):
+        dhs = torch.zeros(T * M, Ch, device="cuda")
+        gw, gb = torch.zeros(Ch, device="cuda"), torch.zeros(1, device="cuda")
+        h1 = h.data_ptr() + M * Ch * 4
+        if batched:
+            lib.rgp_fc_head_bwd_all(dl.data_ptr(), h1, w.data_ptr(), dhs.data_ptr(), gw.data_ptr(), gb.data_ptr(), B, T, G, Ch, 0)
+        else:
+            for t in range(T):
+                lib.rgp_fc_head_bwd(dl.data_ptr(), h1 + t * M * Ch * 4, w.data_ptr(), dhs.data_ptr() + t * M * Ch * 4,
+                                    gw.data_ptr(), gb.data_ptr(), B, T, t, G, Ch, 0)
+        torch.cuda.synchronize()
+        out.append((dhs.cpu().numpy(), gw.cpu().numpy().astype(np.float64), gb.cpu().numpy().astype(np.float64)))
+    assert np.array_equal(out[0][0], out[1][0])
+    hn, dn, wn = h.cpu().numpy().astype(np.float64), dl.cpu().numpy().astype(np.float64), w.cpu().numpy().astype(np.float64)
+    gw_ref, gb_ref = np.zeros(Ch), 0.0
+    dhs_ref = np.zeros((T * M, Ch))
+    for t in range(T):
+        for b in range(B):
+            for y in range(G):
+                m = t * M + b * S + y * Wp + np.arange(G)
+                d = dn[b, t, y]
+                dhs_ref[m] = d[:, None] * wn[None]
+                gw_ref += d @ hn[M + m + Wp + 1]
+                gb_ref += d.sum()
+    assert np.abs(out[1][0] - dhs_ref).max() <= 1e-6 * np.abs(dhs_ref).max()
+    for gw_, gb_ in (out[0][1:], out[1][1:]):
+        assert np.abs(gw_ - gw_ref).max() <= 1e-4 * np.abs(gw_ref).max() + 1e-4
+        assert abs(gb_[0] - gb_ref) <= 1e-4 * abs(gb_ref) + 1e-3
