@@ -62,19 +62,54 @@ def parse():
 
 
 class ClockSampler(object):
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+    """SM clock and throttle reasons sampled DURING the timed region (B200_PROFILING.md's clocks line).  The sampler is
+    started before the warm-up so it is already producing rows when the timed region opens (an `nvidia-smi -lms` child
+    needs > 100 ms to print its first row, longer than ten inference steps); rows are time-stamped and only those inside
+    [mark(), stop()] are reported.  Source: NVML (the library nvidia-smi reads) polled every 5 ms from a thread, else an
+    `nvidia-smi --query-gpu ... -lms 20` child."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+    BITS = [0x8, 0x40, 0x20, 0x4]      # nvmlClocksThrottleReason{HwSlowdown, HwThermalSlowdown, SwThermalSlowdown, SwPowerCap}
 
     def __init__(self, index=0):
-        self.index, self.rows, self.proc = index, [], None
+        self.index, self.rows, self.proc, self.source = index, [], None, None
+        self.t0, self.run = None, False
 
     def start(self):
         try:
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            idx = self.index
+            if vis and all(x.strip().isdigit() for x in vis.split(",")):
+                idx = int(vis.split(",")[self.index])
+            h = pynvml.nvmlDeviceGetHandleByIndex(idx)
+            mx = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+            reasons = getattr(pynvml, "nvmlDeviceGetCurrentClocksEventReasons", None) or pynvml.nvmlDeviceGetCurrentClocksThrottleReasons
+            pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM), reasons(h)
+
+            def poll():
+                while self.run:
+                    try:
+                        m = int(reasons(h))
+                        self.rows.append((time.perf_counter(), float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)), mx,
+                                          [n for n, b in zip(self.NAMES, self.BITS) if m & b]))
+                    except Exception:
+                        pass
+                    time.sleep(0.005)
+            self.run, self.source = True, "nvml"
+            self.th = threading.Thread(target=poll, daemon=True)
+            self.th.start()
+            return
+        except Exception:
+            pass
+        try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.source = "nvidia-smi"
             self.th = threading.Thread(target=self._read, daemon=True)
             self.th.start()
         except Exception:
@@ -82,29 +117,36 @@ class ClockSampler(object):
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
-
-    def stop(self):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=2)
-        except Exception:
-            self.proc.kill()
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+            r = [x.strip() for x in line.split(",")]
             try:
-                sm.append(float(r[0])); mx.append(float(r[1]))
-                for nm, v in zip(names, r[3:7]):
-                    if v.lower().startswith("active"):
-                        reasons.add(nm)
+                self.rows.append((time.perf_counter(), float(r[0]), float(r[1]),
+                                  [n for n, v in zip(self.NAMES, r[2:6]) if v.lower().startswith("active")]))
             except Exception:
                 pass
+
+    def mark(self):
+        """the timed region opens here"""
+        self.t0 = time.perf_counter()
+
+    def stop(self):
+        t1 = time.perf_counter()
+        if self.source is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "samples": 0, "reasons": ["nvml and nvidia-smi unavailable"]}
+        self.run = False
+        if self.proc is not None:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+        rows = [r for r in list(self.rows) if self.t0 is None or self.t0 <= r[0] <= t1]
+        window = "timed region"
+        if not rows:                      # region shorter than one sampling period: the warm-up ran the same kernels
+            rows, window = list(self.rows), "warm-up + timed region"
+        sm, mx = [r[1] for r in rows], [r[2] for r in rows]
+        reasons = sorted(set(n for r in rows for n in r[3]))
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+                "samples": len(sm), "reasons": reasons, "source": self.source, "window": window}
 
 
 def peaks():
@@ -306,12 +348,14 @@ def main():
         torch.cuda.synchronize()
 
     def timed(fn, steps, warmup, sample_clocks=False):
-        for _ in range(warmup):
-            fn()
-        barrier()
         cs = ClockSampler(local) if sample_clocks else None
         if cs:
             cs.start()
+        for _ in range(warmup):
+            fn()
+        barrier()
+        if cs:
+            cs.mark()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         l0 = eng.lib.launches
         if graph is not None:
