@@ -138,6 +138,66 @@ __global__ void __launch_bounds__(256) lstm_gates_kernel(const float* __restrict
   }
 }
 
+// The same, one thread per 4 consecutive channels (Ch % 4 == 0, ldx % 4 == 0): 16-byte loads and stores, element arithmetic
+// unchanged.  The scalar kernel moved ~70 MB per step at 2.8 TB/s (24.8 us per step at 64 clips x 14x14 x 128).
+template <typename TA>
+__global__ void __launch_bounds__(256) lstm_gates_v4_kernel(const float* __restrict__ xg, int ldx,
+                                                             const float* __restrict__ hconv,
+                                                             const float* __restrict__ wci, const float* __restrict__ wcf,
+                                                             const float* __restrict__ wco, float* __restrict__ c_f32,
+                                                             float* __restrict__ h_f32, TA* __restrict__ h_op_next,
+                                                             TA* __restrict__ hs_op, int B, int G, int Ch, int So, int Wo,
+                                                             int pado, float* __restrict__ save) {
+  const int Wp = G + 1, S = Wp * Wp, P = G * G, C4 = Ch >> 2;
+  long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (idx >= (long long)B * P * C4) return;
+  const int n = (int)(idx % C4) * 4;
+  const int pos = (int)(idx / C4);
+  const int b = pos / P, p = pos - b * P;
+  const int y = p / G, x = p - y * G;
+  const long long m = (long long)b * S + y * Wp + x;
+  const long long prow = m + Wp + 1;
+  const float* xr = xg + m * ldx + n;
+  const float* hr = hconv + m * 3 * Ch + n;
+  const int pe = p * Ch + n;
+  const float4 cp4 = *reinterpret_cast<const float4*>(c_f32 + prow * Ch + n);
+  const float4 xi4 = *reinterpret_cast<const float4*>(xr), xf4 = *reinterpret_cast<const float4*>(xr + Ch);
+  const float4 xc4 = *reinterpret_cast<const float4*>(xr + 2 * Ch), xo4 = *reinterpret_cast<const float4*>(xr + 3 * Ch);
+  const float4 hi4 = *reinterpret_cast<const float4*>(hr), hf4 = *reinterpret_cast<const float4*>(hr + Ch);
+  const float4 ho4 = *reinterpret_cast<const float4*>(hr + 2 * Ch);
+  const float4 wi4 = *reinterpret_cast<const float4*>(wci + pe), wf4 = *reinterpret_cast<const float4*>(wcf + pe);
+  const float4 wo4 = *reinterpret_cast<const float4*>(wco + pe);
+  const float cp[4] = {cp4.x, cp4.y, cp4.z, cp4.w}, xi[4] = {xi4.x, xi4.y, xi4.z, xi4.w}, xf[4] = {xf4.x, xf4.y, xf4.z, xf4.w};
+  const float xc[4] = {xc4.x, xc4.y, xc4.z, xc4.w}, xo[4] = {xo4.x, xo4.y, xo4.z, xo4.w}, hi[4] = {hi4.x, hi4.y, hi4.z, hi4.w};
+  const float hf[4] = {hf4.x, hf4.y, hf4.z, hf4.w}, ho[4] = {ho4.x, ho4.y, ho4.z, ho4.w}, wi[4] = {wi4.x, wi4.y, wi4.z, wi4.w};
+  const float wf[4] = {wf4.x, wf4.y, wf4.z, wf4.w}, wo[4] = {wo4.x, wo4.y, wo4.z, wo4.w};
+  float gi[4], gf[4], gg[4], go[4], cn[4], hn[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    gi[j] = sigmoidf_(xi[j] + hi[j] + wi[j] * cp[j]);
+    gf[j] = sigmoidf_(xf[j] + hf[j] + wf[j] * cp[j]);
+    gg[j] = tanhf_(xc[j] + hi[j]);
+    cn[j] = gf[j] * cp[j] + gi[j] * gg[j];
+    go[j] = sigmoidf_(xo[j] + ho[j] + wo[j] * cp[j]);
+    hn[j] = tanhf_(cn[j]) * go[j];
+  }
+  *reinterpret_cast<float4*>(c_f32 + prow * Ch + n) = make_float4(cn[0], cn[1], cn[2], cn[3]);
+  *reinterpret_cast<float4*>(h_f32 + prow * Ch + n) = make_float4(hn[0], hn[1], hn[2], hn[3]);
+  st4_op(h_op_next + prow * Ch + n, hn[0], hn[1], hn[2], hn[3]);
+  if (hs_op) {
+    const long long orow = (long long)b * So + (y + pado) * Wo + (x + pado);
+    st4_op(hs_op + orow * Ch + n, hn[0], hn[1], hn[2], hn[3]);
+  }
+  if (save) {
+    float* sv = save + m * 5 * Ch + n;
+    *reinterpret_cast<float4*>(sv) = make_float4(gi[0], gi[1], gi[2], gi[3]);
+    *reinterpret_cast<float4*>(sv + Ch) = make_float4(gf[0], gf[1], gf[2], gf[3]);
+    *reinterpret_cast<float4*>(sv + 2 * Ch) = make_float4(gg[0], gg[1], gg[2], gg[3]);
+    *reinterpret_cast<float4*>(sv + 3 * Ch) = make_float4(go[0], go[1], go[2], go[3]);
+    *reinterpret_cast<float4*>(sv + 4 * Ch) = cp4;
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // Head weight composition (weight space).  The head of gaze_grcn.py:326-366 is linear:
 // deconv 5x5/s3 (Ch->64) o deconv 5x5/s2 (64->32) o deconv 7x7/s1 SAME (32->12) o FC 12->1.
@@ -435,6 +495,20 @@ int rgp_lstm_gates(const float* xg, int ldx, const float* hconv, const float* wc
                    const float* wco, float* c_f32, float* h_f32, void* h_op_next, void* hs_op, int B, int G,
                    int Ch, int So, int Wo, int pado, int dtype, float* save, void* stream) {
   long long total = (long long)B * G * G * Ch;
+  const auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+  if (Ch % 4 == 0 && ldx % 4 == 0 && al16(xg) && al16(hconv) && al16(wci) && al16(wcf) && al16(wco) && al16(c_f32) &&
+      al16(h_f32) && al16(h_op_next) && al16(hs_op) && al16(save)) {
+    int grid4 = (int)((total / 4 + 255) / 256);
+    if (dtype == 0)
+      lstm_gates_v4_kernel<float><<<grid4, 256, 0, (cudaStream_t)stream>>>(xg, ldx, hconv, wci, wcf, wco, c_f32, h_f32,
+                                                                           (float*)h_op_next, (float*)hs_op, B, G, Ch, So,
+                                                                           Wo, pado, save);
+    else
+      lstm_gates_v4_kernel<__nv_bfloat16><<<grid4, 256, 0, (cudaStream_t)stream>>>(
+          xg, ldx, hconv, wci, wcf, wco, c_f32, h_f32, (__nv_bfloat16*)h_op_next, (__nv_bfloat16*)hs_op, B, G, Ch, So,
+          Wo, pado, save);
+    return check_launch("rgp_lstm_gates");
+  }
   int grid = (int)((total + 255) / 256);
   if (dtype == 0)
     lstm_gates_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>(xg, ldx, hconv, wci, wcf, wco, c_f32, h_f32,
