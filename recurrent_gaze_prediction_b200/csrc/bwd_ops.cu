@@ -282,6 +282,81 @@ __global__ void __launch_bounds__(256) lstm_gates_bwd_kernel(
   atomicAdd(gwco + pe, dpo * cp);
 }
 
+// The same with one thread per (group of 4 clips, position, 4 consecutive channels): 16-byte accesses, and the peephole
+// gradients of the 4 clips are summed in registers before they leave as 12 atomics per thread (the scalar kernel issues 3 per
+// element, B-way contended).  Element arithmetic unchanged.
+__device__ __forceinline__ void st4_ta(float* p, const float* v) { *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]); }
+__device__ __forceinline__ void st4_ta(__nv_bfloat16* p, const float* v) {
+  __nv_bfloat162 lo = __floats2bfloat162_rn(v[0], v[1]), hi = __floats2bfloat162_rn(v[2], v[3]);
+  uint2 u;
+  u.x = *reinterpret_cast<uint32_t*>(&lo);
+  u.y = *reinterpret_cast<uint32_t*>(&hi);
+  *reinterpret_cast<uint2*>(p) = u;
+}
+__device__ __forceinline__ void ld4f(const float* p, float* v) {
+  const float4 t = *reinterpret_cast<const float4*>(p);
+  v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+}
+template <typename TA>
+__global__ void __launch_bounds__(256) lstm_gates_bwd_v4_kernel(
+    const float* __restrict__ save, const float* __restrict__ cnext_save, const float* __restrict__ c_final,
+    const float* __restrict__ dhs, const float* __restrict__ dhrec, float* __restrict__ dc,
+    const float* __restrict__ wci, const float* __restrict__ wcf, const float* __restrict__ wco,
+    TA* __restrict__ dg4, TA* __restrict__ dhc, float* __restrict__ gwci, float* __restrict__ gwcf,
+    float* __restrict__ gwco, int B, int G, int Ch, int last) {
+  const int Wp = G + 1, S = Wp * Wp, P = G * G, C4 = Ch >> 2, BG = (B + 3) >> 2;
+  long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (idx >= (long long)BG * P * C4) return;
+  const int n = (int)(idx % C4) * 4;
+  const int pos = (int)(idx / C4);
+  const int p = pos % P, b0 = (pos / P) * 4;
+  const int y = p / G, x = p - y * G;
+  const int pe = p * Ch + n;
+  float wi[4], wf[4], wo[4], ai[4] = {0.f, 0.f, 0.f, 0.f}, af[4] = {0.f, 0.f, 0.f, 0.f}, ao[4] = {0.f, 0.f, 0.f, 0.f};
+  ld4f(wci + pe, wi); ld4f(wcf + pe, wf); ld4f(wco + pe, wo);
+#pragma unroll
+  for (int bb = 0; bb < 4; ++bb) {
+    const int b = b0 + bb;
+    if (b >= B) break;
+    const long long m = (long long)b * S + y * Wp + x;
+    const float* sv = save + m * 5 * Ch + n;
+    float gi[4], gf[4], gg[4], go[4], cp[4], cn[4], dh[4], dcn[4] = {0.f, 0.f, 0.f, 0.f};
+    ld4f(sv, gi); ld4f(sv + Ch, gf); ld4f(sv + 2 * Ch, gg); ld4f(sv + 3 * Ch, go); ld4f(sv + 4 * Ch, cp);
+    if (cnext_save) ld4f(cnext_save + m * 5 * Ch + 4 * Ch + n, cn); else ld4f(c_final + (m + Wp + 1) * Ch + n, cn);
+    ld4f(dhs + m * Ch + n, dh);
+    if (!last) {
+      float dr[4];
+      ld4f(dhrec + m * Ch + n, dr); ld4f(dc + m * Ch + n, dcn);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) dh[j] += dr[j];
+    }
+    float dpi[4], dpf[4], dpg[4], dpo[4], dco[4], dig[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float tc = tanhf_(cn[j]);
+      dcn[j] += dh[j] * go[j] * (1.0f - tc * tc);
+      dpo[j] = dh[j] * tc * go[j] * (1.0f - go[j]);
+      dpi[j] = dcn[j] * gg[j] * gi[j] * (1.0f - gi[j]);
+      dpg[j] = dcn[j] * gi[j] * (1.0f - gg[j] * gg[j]);
+      dpf[j] = dcn[j] * cp[j] * gf[j] * (1.0f - gf[j]);
+      dco[j] = dcn[j] * gf[j] + dpi[j] * wi[j] + dpf[j] * wf[j] + dpo[j] * wo[j];
+      dig[j] = dpi[j] + dpg[j];
+      ai[j] += dpi[j] * cp[j]; af[j] += dpf[j] * cp[j]; ao[j] += dpo[j] * cp[j];
+    }
+    st4_ta(dc + m * Ch + n, dco);
+    TA* g4 = dg4 + m * 4 * Ch + n;
+    st4_ta(g4, dpi); st4_ta(g4 + Ch, dpf); st4_ta(g4 + 2 * Ch, dpg); st4_ta(g4 + 3 * Ch, dpo);
+    TA* hc = dhc + m * 3 * Ch + n;
+    st4_ta(hc, dig); st4_ta(hc + Ch, dpf); st4_ta(hc + 2 * Ch, dpo);
+  }
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    atomicAdd(gwci + pe + j, ai[j]);
+    atomicAdd(gwcf + pe + j, af[j]);
+    atomicAdd(gwco + pe + j, ao[j]);
+  }
+}
+
 }  // namespace rgp
 
 using namespace rgp;
@@ -309,8 +384,18 @@ int rgp_lstm_gates_bwd(const float* save, const float* cnext_save, const float* 
   RGP_CHECK_ARG(cnext_save != nullptr || c_final != nullptr, "rgp_lstm_gates_bwd: need c_t (cnext_save or c_final)");
   RGP_CHECK_ARG(last || dhrec != nullptr, "rgp_lstm_gates_bwd: dhrec is required unless this is the last time step");
   long long total = (long long)B * G * G * Ch;
-  int grid = (int)((total + 255) / 256);
   cudaStream_t s = (cudaStream_t)stream;
+  const auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+  if (Ch % 4 == 0 && al16(save) && al16(cnext_save) && al16(c_final) && al16(dhs) && al16(dhrec) && al16(dc) && al16(wci) &&
+      al16(wcf) && al16(wco) && al16(dg4) && al16(dhc) && al16(gwci) && al16(gwcf) && al16(gwco)) {
+    long long t4 = (long long)((B + 3) / 4) * G * G * (Ch / 4);
+    int grid4 = (int)((t4 + 255) / 256);
+    DISPATCH_TA(dtype,
+                (lstm_gates_bwd_v4_kernel<float><<<grid4, 256, 0, s>>>(save, cnext_save, c_final, dhs, dhrec, dc, wci, wcf, wco, (float*)dg4, (float*)dhc, gwci, gwcf, gwco, B, G, Ch, last)),
+                (lstm_gates_bwd_v4_kernel<__nv_bfloat16><<<grid4, 256, 0, s>>>(save, cnext_save, c_final, dhs, dhrec, dc, wci, wcf, wco, (__nv_bfloat16*)dg4, (__nv_bfloat16*)dhc, gwci, gwcf, gwco, B, G, Ch, last)));
+    return check_launch("rgp_lstm_gates_bwd");
+  }
+  int grid = (int)((total + 255) / 256);
   DISPATCH_TA(dtype,
               (lstm_gates_bwd_kernel<float><<<grid, 256, 0, s>>>(save, cnext_save, c_final, dhs, dhrec, dc, wci, wcf, wco, (float*)dg4, (float*)dhc, gwci, gwcf, gwco, B, G, Ch, last)),
               (lstm_gates_bwd_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>(save, cnext_save, c_final, dhs, dhrec, dc, wci, wcf, wco, (__nv_bfloat16*)dg4, (__nv_bfloat16*)dhc, gwci, gwcf, gwco, B, G, Ch, last)));
