@@ -43,22 +43,41 @@ __global__ void __launch_bounds__(256) transpose_taps_kernel(const float* __rest
   }
 }
 
-// patches[(t*B+b)*100 + (i+3)*10 + (j+3), u*19+v] = dlogits[b,t,6i+u-3,6j+v-3]; one CTA per (frame, position)
+__device__ __forceinline__ void st4_ta(float* p, const float* v) { *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]); }
+__device__ __forceinline__ void st4_ta(__nv_bfloat16* p, const float* v) {
+  __nv_bfloat162 lo = __floats2bfloat162_rn(v[0], v[1]), hi = __floats2bfloat162_rn(v[2], v[3]);
+  uint2 u;
+  u.x = *reinterpret_cast<uint32_t*>(&lo);
+  u.y = *reinterpret_cast<uint32_t*>(&hi);
+  *reinterpret_cast<uint2*>(p) = u;
+}
+__device__ __forceinline__ void ld4f(const float* p, float* v) {
+  const float4 t = *reinterpret_cast<const float4*>(p);
+  v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+}
+// patches[(t*B+b)*100 + (i+3)*10 + (j+3), u*19+v] = dlogits[b,t,6i+u-3,6j+v-3]
+// One CTA per frame: the 2401-float gradient map is staged in shared memory once, every thread then builds 4 consecutive
+// patch elements and stores them as one 8-byte (bf16) / 16-byte (fp32) word.
 template <typename TA>
-__global__ void __launch_bounds__(128) head_patches_kernel(const float* __restrict__ dl, TA* __restrict__ patches, int B, int T) {
-  const int pos = blockIdx.x % 49, f = blockIdx.x / 49;   // f = t*B + b
-  const int i = pos / 7, j = pos - i * 7;
+__global__ void __launch_bounds__(256) head_patches_kernel(const float* __restrict__ dl, TA* __restrict__ patches, int B, int T) {
+  __shared__ float src[2404];
+  const int f = blockIdx.x;   // f = t*B + b
   const int t = f / B, b = f - t * B;
-  const float* src = dl + ((long long)b * T + t) * 2401;
-  TA* dst = patches + ((long long)f * 100 + (i + 3) * 10 + (j + 3)) * 384;
-  for (int k = threadIdx.x; k < 384; k += 128) {
-    float v = 0.f;
-    if (k < 361) {
-      int u = k / 19, w = k - u * 19;
-      int Y = 6 * i + u - 3, X = 6 * j + w - 3;
-      if (Y >= 0 && Y < 49 && X >= 0 && X < 49) v = src[Y * 49 + X];
+  const float* g = dl + ((long long)b * T + t) * 2401;
+  for (int k = threadIdx.x; k < 2401; k += 256) src[k] = g[k];
+  __syncthreads();
+  for (int it = threadIdx.x; it < 49 * 96; it += 256) {
+    const int pos = it / 96, k0 = (it - pos * 96) * 4;
+    const int i = pos / 7, j = pos - i * 7;
+    float v[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int k = k0 + q;
+      const int u = k / 19, w = k - u * 19;
+      const int Y = 6 * i + u - 3, X = 6 * j + w - 3;
+      v[q] = (k < 361 && Y >= 0 && Y < 49 && X >= 0 && X < 49) ? src[Y * 49 + X] : 0.f;
     }
-    OpT<TA>::st(dst + k, v);
+    st4_ta(patches + ((long long)f * 100 + (i + 3) * 10 + (j + 3)) * 384 + k0, v);
   }
 }
 
@@ -112,19 +131,26 @@ __global__ void cb_dw2_kernel(const float* __restrict__ dw23, const float* __res
       acc = fmaf(dw23[((k2 + k3) * 11 + (l2 + l3)) * 64 + m], w3f[(k3 * 7 + l3) * 32 + e], acc);
   gw2[idx] += acc;
 }
-__global__ void cb_dw3f_kernel(const float* __restrict__ dw23, const float* __restrict__ w2, float* __restrict__ dw3f) {
-  int idx = blockIdx.x * blockDim.x + threadIdx.x;   // (k3,l3,e): 49*32
+// one warp per (k3,l3,e): lanes run over the 64 mid channels (coalesced), 25 taps, shuffle reduction.  The earlier
+// thread-per-output form ran 1600 serial FMAs on 1568 threads with 256-byte lane strides (222 us per pass).
+__global__ void __launch_bounds__(256) cb_dw3f_kernel(const float* __restrict__ dw23, const float* __restrict__ w2, float* __restrict__ dw3f) {
+  const int idx = (blockIdx.x * 256 + threadIdx.x) >> 5, lane = threadIdx.x & 31;   // (k3,l3,e): 49*32
   if (idx >= 49 * 32) return;
-  int e = idx & 31, kl = idx >> 5;
-  int k3 = kl / 7, l3 = kl - k3 * 7;
-  float acc = 0.f;
-  for (int k2 = 0; k2 < 5; ++k2)
-    for (int l2 = 0; l2 < 5; ++l2) {
-      const float* a = dw23 + ((k2 + k3) * 11 + (l2 + l3)) * 64;
-      const float* b = w2 + ((k2 * 5 + l2) * 32 + e) * 64;
-      for (int m = 0; m < 64; ++m) acc = fmaf(a[m], b[m], acc);
-    }
-  dw3f[idx] = acc;
+  const int e = idx & 31, kl = idx >> 5;
+  const int k3 = kl / 7, l3 = kl - k3 * 7;
+  float acc0 = 0.f, acc1 = 0.f;
+#pragma unroll 5
+  for (int t = 0; t < 25; ++t) {
+    const int k2 = t / 5, l2 = t - k2 * 5;
+    const float* a = dw23 + ((k2 + k3) * 11 + (l2 + l3)) * 64;
+    const float* b = w2 + (t * 32 + e) * 64;
+    acc0 = fmaf(a[lane], b[lane], acc0);
+    acc1 = fmaf(a[lane + 32], b[lane + 32], acc1);
+  }
+  float acc = acc0 + acc1;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if (lane == 0) dw3f[idx] = acc;
 }
 __global__ void cb_dw3_kernel(const float* __restrict__ dw3f, const float* __restrict__ w3, const float* __restrict__ ow,
                               float* __restrict__ gw3, float* __restrict__ gow) {
@@ -188,6 +214,48 @@ __global__ void __launch_bounds__(256) colsum_kernel(const TA* __restrict__ X, i
   if (w == 0 && c < N) {
     for (int k = 1; k < 8; ++k) acc += sm[k][threadIdx.x];
     atomicAdd(out + c, acc);
+  }
+}
+
+// 16-byte loads: a lane owns 16/sizeof(TA) consecutive columns, a warp a 512-byte row segment, the 8 warps of a CTA stride rows.
+template <typename TA>
+__global__ void __launch_bounds__(256) colsum_vec_kernel(const TA* __restrict__ X, int ld, int M, int N, float* __restrict__ out) {
+  constexpr int V = 16 / (int)sizeof(TA);
+  __shared__ float sm[8][32 * V];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int c = (blockIdx.x * 32 + lane) * V;
+  float acc[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) acc[j] = 0.f;
+  if (c < N) {
+    int m = blockIdx.y * 8 + w;
+    const int step = 8 * gridDim.y;
+    for (; m + step < M; m += 2 * step) {      // two rows in flight
+      const uint4 u0 = *reinterpret_cast<const uint4*>(X + (long long)m * ld + c);
+      const uint4 u1 = *reinterpret_cast<const uint4*>(X + (long long)(m + step) * ld + c);
+      const TA* e0 = reinterpret_cast<const TA*>(&u0);
+      const TA* e1 = reinterpret_cast<const TA*>(&u1);
+#pragma unroll
+      for (int j = 0; j < V; ++j) acc[j] += OpT<TA>::ld(e0 + j) + OpT<TA>::ld(e1 + j);
+    }
+    if (m < M) {
+      const uint4 u0 = *reinterpret_cast<const uint4*>(X + (long long)m * ld + c);
+      const TA* e0 = reinterpret_cast<const TA*>(&u0);
+#pragma unroll
+      for (int j = 0; j < V; ++j) acc[j] += OpT<TA>::ld(e0 + j);
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < V; ++j) sm[w][lane * V + j] = acc[j];
+  __syncthreads();
+  for (int i = threadIdx.x; i < 32 * V; i += 256) {
+    const int cc = blockIdx.x * 32 * V + i;
+    if (cc < N) {
+      float a = 0.f;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) a += sm[k][i];
+      atomicAdd(out + cc, a);
+    }
   }
 }
 
@@ -285,18 +353,6 @@ __global__ void __launch_bounds__(256) lstm_gates_bwd_kernel(
 // The same with one thread per (group of 4 clips, position, 4 consecutive channels): 16-byte accesses, and the peephole
 // gradients of the 4 clips are summed in registers before they leave as 12 atomics per thread (the scalar kernel issues 3 per
 // element, B-way contended).  Element arithmetic unchanged.
-__device__ __forceinline__ void st4_ta(float* p, const float* v) { *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]); }
-__device__ __forceinline__ void st4_ta(__nv_bfloat16* p, const float* v) {
-  __nv_bfloat162 lo = __floats2bfloat162_rn(v[0], v[1]), hi = __floats2bfloat162_rn(v[2], v[3]);
-  uint2 u;
-  u.x = *reinterpret_cast<uint32_t*>(&lo);
-  u.y = *reinterpret_cast<uint32_t*>(&hi);
-  *reinterpret_cast<uint2*>(p) = u;
-}
-__device__ __forceinline__ void ld4f(const float* p, float* v) {
-  const float4 t = *reinterpret_cast<const float4*>(p);
-  v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
-}
 template <typename TA>
 __global__ void __launch_bounds__(256) lstm_gates_bwd_v4_kernel(
     const float* __restrict__ save, const float* __restrict__ cnext_save, const float* __restrict__ c_final,
@@ -412,9 +468,9 @@ int rgp_transpose_taps(const float* src, void* dst, int ntaps, int R, int Cc, in
 
 int rgp_head_patches(const float* dlogits, void* patches, int B, int T, int dtype, void* stream) {
   cudaStream_t s = (cudaStream_t)stream;
-  int grid = B * T * 49;
-  DISPATCH_TA(dtype, (head_patches_kernel<float><<<grid, 128, 0, s>>>(dlogits, (float*)patches, B, T)),
-              (head_patches_kernel<__nv_bfloat16><<<grid, 128, 0, s>>>(dlogits, (__nv_bfloat16*)patches, B, T)));
+  int grid = B * T;
+  DISPATCH_TA(dtype, (head_patches_kernel<float><<<grid, 256, 0, s>>>(dlogits, (float*)patches, B, T)),
+              (head_patches_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>(dlogits, (__nv_bfloat16*)patches, B, T)));
   return check_launch("rgp_head_patches");
 }
 
@@ -433,7 +489,7 @@ int rgp_head_compose_bwd(const float* dw123, const float* w1, const float* w2, c
   cb_dw1_kernel<<<(25 * 64 * Ch + 255) / 256, 256, 0, s>>>(dw123, w23, gw1, Ch);
   cb_dw23_kernel<<<(121 * 64 * 32 + 255) / 256, 256, 0, s>>>(dw123, w1, dw23, Ch);
   cb_dw2_kernel<<<(25 * 32 * 64 + 255) / 256, 256, 0, s>>>(dw23, w3f, gw2);
-  cb_dw3f_kernel<<<(49 * 32 + 255) / 256, 256, 0, s>>>(dw23, w2, dw3f);
+  cb_dw3f_kernel<<<(49 * 32 * 32 + 255) / 256, 256, 0, s>>>(dw23, w2, dw3f);
   cb_dw3_kernel<<<(49 * 12 * 32 + 255) / 256, 256, 0, s>>>(dw3f, w3, out_w, gw3, gout_w);
   return check_launch("rgp_head_compose_bwd");
 }
@@ -461,8 +517,18 @@ int rgp_colsum(const void* X, int ld, int M, int N, float* out, int dtype, void*
   int gy = (M + 511) / 512;
   if (gy > 296) gy = 296;
   if (gy < 1) gy = 1;
-  dim3 grid((N + 31) / 32, gy);
   cudaStream_t s = (cudaStream_t)stream;
+  const int V = dtype == 0 ? 4 : 8;
+  if (N % V == 0 && ld % V == 0 && (reinterpret_cast<uintptr_t>(X) & 15) == 0) {
+    int gyv = (M + 255) / 256;
+    if (gyv > 592) gyv = 592;
+    if (gyv < 1) gyv = 1;
+    dim3 gridv((N + 32 * V - 1) / (32 * V), gyv);
+    DISPATCH_TA(dtype, (colsum_vec_kernel<float><<<gridv, 256, 0, s>>>((const float*)X, ld, M, N, out)),
+                (colsum_vec_kernel<__nv_bfloat16><<<gridv, 256, 0, s>>>((const __nv_bfloat16*)X, ld, M, N, out)));
+    return check_launch("rgp_colsum");
+  }
+  dim3 grid((N + 31) / 32, gy);
   DISPATCH_TA(dtype, (colsum_kernel<float><<<grid, 256, 0, s>>>((const float*)X, ld, M, N, out)),
               (colsum_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>((const __nv_bfloat16*)X, ld, M, N, out)));
   return check_launch("rgp_colsum");
