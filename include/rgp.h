@@ -120,6 +120,9 @@ int rgp_cast(const float* src, void* dst, long long n, int dtype, void* stream);
 /* gaze_grcn77.py:206-211: logits[b,t,y,x] = h . out_W + out_b from the p-layout fp32 state */
 int rgp_fc_head(const float* h_f32, const float* out_W, const float* out_b, float* logits,
                 int B, int T, int t, int G, int Ch, void* stream);
+/* the same for all T steps in one launch: h1_f32 = slab of h_1 (slab t = h_{t+1}); Ch % 4 == 0, 16-byte aligned */
+int rgp_fc_head_all(const float* h1_f32, const float* out_W, const float* out_b, float* logits, int B, int T, int G,
+                    int Ch, void* stream);
 /* ConvLSTM gate maths, gaze_lstm.py:112-133 (bugs preserved), after the hidden conv GEMM */
 int rgp_lstm_gates(const float* xg, int ldx, const float* hconv, const float* wci, const float* wcf,
                    const float* wco, float* c_f32, float* h_f32, void* h_op_next, void* hs_op,

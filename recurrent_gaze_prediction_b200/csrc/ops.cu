@@ -91,6 +91,30 @@ __global__ void __launch_bounds__(256) fc_head_kernel(const float* __restrict__ 
   if (lane == 0) logits[((long long)b * T + t) * P + p] = s + bias[0];
 }
 
+// The same for all T steps in one launch (h1 = slab of h_1; slab t holds h_{t+1}); 16-byte loads, Ch % 4 == 0.
+__global__ void __launch_bounds__(256) fc_head_all_kernel(const float* __restrict__ h1, const float* __restrict__ w,
+                                                           const float* __restrict__ bias, float* __restrict__ logits,
+                                                           int B, int T, int G, int Ch) {
+  const int Wp = G + 1, S = Wp * Wp, P = G * G;
+  const long long BP = (long long)B * P;
+  const long long warp = ((long long)blockIdx.x * 256 + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (warp >= (long long)T * BP) return;
+  const int t = (int)(warp / BP);
+  const int r = (int)(warp - (long long)t * BP);
+  const int b = r / P, p = r - b * P;
+  const int y = p / G, x = p - y * G;
+  const float* hr = h1 + (((long long)t * B + b) * S + (y + 1) * Wp + (x + 1)) * Ch;
+  float s = 0.f;
+  for (int c = lane * 4; c < Ch; c += 128) {
+    const float4 a = *reinterpret_cast<const float4*>(hr + c), ww = *reinterpret_cast<const float4*>(w + c);
+    s = fmaf(a.x, ww.x, s); s = fmaf(a.y, ww.y, s); s = fmaf(a.z, ww.z, s); s = fmaf(a.w, ww.w, s);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if (lane == 0) logits[((long long)b * T + t) * P + p] = s + bias[0];
+}
+
 // ---------------------------------------------------------------------------------------------
 // ConvLSTM gates — gaze_lstm.py:112-133, literally (candidate reuses the W_hi conv; output gate
 // peeps at the OLD cell; peepholes are full [G,G,Ch] tensors).
@@ -489,6 +513,18 @@ int rgp_fc_head(const float* h_f32, const float* out_W, const float* out_b, floa
   int grid = (warps * 32 + 255) / 256;
   fc_head_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(h_f32, out_W, out_b, logits, B, T, t, G, Ch);
   return check_launch("rgp_fc_head");
+}
+
+int rgp_fc_head_all(const float* h1_f32, const float* out_W, const float* out_b, float* logits, int B, int T, int G,
+                    int Ch, void* stream) {
+  RGP_CHECK_ARG(Ch > 0 && Ch % 4 == 0, "rgp_fc_head_all: Ch=%d must be a multiple of 4", Ch);
+  RGP_CHECK_ARG(B > 0 && T > 0 && G > 0, "rgp_fc_head_all: B=%d T=%d G=%d", B, T, G);
+  RGP_CHECK_ARG(((reinterpret_cast<uintptr_t>(h1_f32) | reinterpret_cast<uintptr_t>(out_W)) & 15) == 0,
+                "rgp_fc_head_all: h1_f32 and out_W must be 16-byte aligned%s", "");
+  const long long warps = (long long)T * B * G * G;
+  const long long grid = (warps * 32 + 255) / 256;
+  fc_head_all_kernel<<<(unsigned)grid, 256, 0, (cudaStream_t)stream>>>(h1_f32, out_W, out_b, logits, B, T, G, Ch);
+  return check_launch("rgp_fc_head_all");
 }
 
 int rgp_lstm_gates(const float* xg, int ldx, const float* hconv, const float* wci, const float* wcf,

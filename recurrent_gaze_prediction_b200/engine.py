@@ -408,9 +408,7 @@ class GazeEngine(object):
             a.nsplit, a.dtype, a.mcast = self.nsplit, self.dtype, self.mcast
             lib.rgp_convgru_seq_fwd(C.byref(a), s)
             if self.head == "fc":   # gaze_grcn77.py:206-211
-                for t in range(T):
-                    lib.rgp_fc_head(self._slab(self.Hf, t + 1), self._ptr("out_W"), self._ptr("out_b"),
-                                    self.logits.data_ptr(), B, T, t, G, Ch, s)
+                self._fc_head_all(s)
             return
         for t in range(T):
             xg = self.Xg.data_ptr() + t * M * NX * 4
@@ -444,7 +442,17 @@ class GazeEngine(object):
                            hnext_f32=self._slab(self.Hf, t + 1), out_op=self._slab(self.Hop, t + 1), out_op2=hs,
                            So=HEAD_S, Wo=HEAD_W, pado=HEAD_PAD, save_c=self.Cs[t].data_ptr() if self.train else 0,
                            **common, **extra)
-            if self.head == "fc":   # gaze_grcn77.py:206-211
+        if self.head == "fc":   # gaze_grcn77.py:206-211
+            self._fc_head_all(s)
+
+    def _fc_head_all(self, s):
+        """per-position FC head on the fp32 states of all T steps (they stay resident in Hf): one launch"""
+        lib, B, T, G, Ch = self.lib, self.B, self.T, self.G, self.Ch
+        if Ch % 4 == 0:
+            lib.rgp_fc_head_all(self._slab(self.Hf, 1), self._ptr("out_W"), self._ptr("out_b"),
+                                self.logits.data_ptr(), B, T, G, Ch, s)
+        else:
+            for t in range(T):
                 lib.rgp_fc_head(self._slab(self.Hf, t + 1), self._ptr("out_W"), self._ptr("out_b"),
                                 self.logits.data_ptr(), B, T, t, G, Ch, s)
 

@@ -72,6 +72,7 @@ _SIGS = {
     "rgp_pack_emb": [_vp, _vp, _i, _i, _i, _i, _i, _vp],
     "rgp_cast": [_vp, _vp, _ll, _i, _vp],
     "rgp_fc_head": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp],
+    "rgp_fc_head_all": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
     "rgp_lstm_gates": [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp, _vp],
     "rgp_head_compose": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp],
     "rgp_softmax_xent_fwd_bwd": [_vp, _vp, _vp, _vp, _vp, _i, _i, _f, _i, _vp],

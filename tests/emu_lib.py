@@ -692,6 +692,12 @@ class EmuLib(object):
             self.rgp_tapgemm(C.byref(g), stream)
         return 0
 
+    def rgp_fc_head_all(self, h1, w, b, logits, B, T, G, Ch, stream):
+        S = (G + 1) * (G + 1)
+        for t in range(T):
+            self.rgp_fc_head(int(h1) + t * B * S * Ch * 4, w, b, logits, B, T, t, G, Ch, stream)
+        return 0
+
     def rgp_fc_head_bwd_all(self, dl, h1, w, dhs, gw, gb, B, T, G, Ch, stream):
         S = (G + 1) * (G + 1)
         for t in range(T):
