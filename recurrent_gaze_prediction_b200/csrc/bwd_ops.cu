@@ -201,6 +201,52 @@ __global__ void __launch_bounds__(256) bn_bwd_kernel(const float* __restrict__ d
   }
 }
 
+// 16-byte form: a lane owns 4 consecutive channels, a warp 128 channels of a row, two rows in flight per warp (Ch % 4 == 0)
+__global__ void __launch_bounds__(256) bn_bwd_v4_kernel(const float* __restrict__ dhs, const float* __restrict__ h,
+                                                         float* __restrict__ dgamma, float* __restrict__ dbeta, float alpha,
+                                                         int B, int G, int Ch) {
+  __shared__ float sg[8][128], sb[8][128];
+  const int Wp = G + 1, S = Wp * Wp, P = G * G;
+  dhs += (long long)blockIdx.z * B * S * Ch;
+  h += (long long)blockIdx.z * B * S * Ch;
+  dgamma += (long long)blockIdx.z * Ch;
+  dbeta += (long long)blockIdx.z * Ch;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int c = blockIdx.x * 128 + lane * 4;
+  float ag[4] = {0.f, 0.f, 0.f, 0.f}, ab[4] = {0.f, 0.f, 0.f, 0.f};
+  if (c < Ch) {
+    const int step = 8 * gridDim.y, n = B * P;
+    for (int pos = blockIdx.y * 8 + w; pos < n; pos += 2 * step) {
+      const int pos2 = pos + step < n ? pos + step : pos;
+      const float k2 = pos + step < n ? 1.f : 0.f;
+      const int b = pos / P, p = pos - b * P, y = p / G, x = p - y * G;
+      const int b2 = pos2 / P, p2 = pos2 - b2 * P, y2 = p2 / G, x2 = p2 - y2 * G;
+      const long long m = (long long)b * S + y * Wp + x, m2 = (long long)b2 * S + y2 * Wp + x2;
+      float d[4], d2[4], hh[4], hh2[4];
+      ld4f(dhs + m * Ch + c, d); ld4f(dhs + m2 * Ch + c, d2);
+      ld4f(h + (m + Wp + 1) * Ch + c, hh); ld4f(h + (m2 + Wp + 1) * Ch + c, hh2);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        ag[j] = fmaf(d[j], hh[j], ag[j]); ab[j] += d[j];
+        ag[j] = fmaf(k2 * d2[j], hh2[j], ag[j]); ab[j] += k2 * d2[j];
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 4; ++j) { sg[w][lane * 4 + j] = ag[j]; sb[w][lane * 4 + j] = ab[j]; }
+  __syncthreads();
+  if (threadIdx.x < 128) {
+    const int cc = blockIdx.x * 128 + threadIdx.x;
+    if (cc < Ch) {
+      float a = 0.f, bsum = 0.f;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) { a += sg[k][threadIdx.x]; bsum += sb[k][threadIdx.x]; }
+      atomicAdd(dgamma + cc, a * alpha);
+      atomicAdd(dbeta + cc, bsum);
+    }
+  }
+}
+
 template <typename TA>
 __global__ void __launch_bounds__(256) colsum_kernel(const TA* __restrict__ X, int ld, int M, int N, float* __restrict__ out) {
   __shared__ float sm[8][32];
@@ -505,6 +551,14 @@ int rgp_bn_bwd(const float* dhs, const float* h_f32, float* dgamma, float* dbeta
 
 int rgp_bn_bwd_all(const float* dhs, const float* h_f32, float* dgamma, float* dbeta, float alpha, int B, int T, int G,
                    int Ch, void* stream) {
+  if (Ch % 4 == 0 && ((reinterpret_cast<uintptr_t>(dhs) | reinterpret_cast<uintptr_t>(h_f32)) & 15) == 0) {
+    int gyv = (B * G * G + 31) / 32;
+    if (gyv > 32) gyv = 32;
+    if (gyv < 1) gyv = 1;
+    dim3 gridv((Ch + 127) / 128, gyv, T);
+    bn_bwd_v4_kernel<<<gridv, 256, 0, (cudaStream_t)stream>>>(dhs, h_f32, dgamma, dbeta, alpha, B, G, Ch);
+    return check_launch("rgp_bn_bwd_all");
+  }
   int gy = (B * G * G + 63) / 64;
   if (gy > 16) gy = 16;
   if (gy < 1) gy = 1;
