@@ -206,7 +206,7 @@ int rgp_colsum(const void* X, int ld, int M, int N, float* out, int dtype, void*
 /* gaze_grcn77.py:206-211 backward: dhs[m,c] = dlogit*out_W[c]; gout_W[c] += sum dlogit*h; gout_b += sum dlogit */
 int rgp_fc_head_bwd(const float* dlogits, const float* h_f32, const float* out_W, float* dhs,
                     float* gout_W, float* gout_b, int B, int T, int t, int G, int Ch, void* stream);
-/* the same for all T steps in one launch: h1_f32 = slab of h_1 (slab t = h_{t+1}), dhs [T*B*S, Ch]; Ch must divide 256 */
+/* the same for all T steps in one launch: h1_f32 = slab of h_1 (slab t = h_{t+1}), dhs [T*B*S, Ch]; Ch/4 must divide 256, pointers 16-byte aligned */
 int rgp_fc_head_bwd_all(const float* dlogits, const float* h1_f32, const float* out_W, float* dhs,
                         float* gout_W, float* gout_b, int B, int T, int G, int Ch, void* stream);
 

@@ -583,7 +583,7 @@ class GazeEngine(object):
                 lib.rgp_bn_bwd_all(self.dhs.data_ptr(), self._slab(self.Hf, 1), g("bn_gamma"), g("bn_beta"), alpha,
                                    B, T, G, Ch, s)
         else:
-            if 256 % Ch == 0:
+            if Ch % 4 == 0 and 256 % (Ch // 4) == 0:
                 lib.rgp_fc_head_bwd_all(self.dlogits.data_ptr(), self._slab(self.Hf, 1), self._ptr("out_W"),
                                         self.dhs.data_ptr(), g("out_W"), g("out_b"), B, T, G, Ch, s)
             else:
