@@ -72,6 +72,9 @@ class ClockSampler(object):
          "clocks_event_reasons.sw_power_cap")
     NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
     BITS = [0x8, 0x40, 0x20, 0x4]      # nvmlClocksThrottleReason{HwSlowdown, HwThermalSlowdown, SwThermalSlowdown, SwPowerCap}
+    # the remaining NVML reason bits, reported too so that a clock below max is never left unexplained
+    NVML_NAMES = NAMES + ["applications_clocks_setting", "sync_boost", "hw_power_brake_slowdown", "display_clock_setting"]
+    NVML_BITS = BITS + [0x2, 0x10, 0x80, 0x100]
 
     def __init__(self, index=0):
         self.index, self.rows, self.proc, self.source = index, [], None, None
@@ -95,7 +98,7 @@ class ClockSampler(object):
                     try:
                         m = int(reasons(h))
                         self.rows.append((time.perf_counter(), float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)), mx,
-                                          [n for n, b in zip(self.NAMES, self.BITS) if m & b]))
+                                          [n for n, b in zip(self.NVML_NAMES, self.NVML_BITS) if m & b]))
                     except Exception:
                         pass
                     time.sleep(0.005)
