@@ -111,3 +111,35 @@ def test_data_parallel_two_ranks_equals_single_process(tmp_path):
     mask[off:off + n] = False                 # zero-gradient parameter: Adam amplifies summation-order noise
     assert np.abs(z["params"][mask] - ref[mask]).max() <= 2e-5
     assert np.abs(z["pred"] - ret['pred_gazemap_list']).max() <= 1e-6
+
+
+def test_bench_clock_sampler_reports_only_rows_inside_the_timed_region():
+    """bench.py's ClockSampler: rows are time-stamped, mark() opens the timed region, stop() reports the median clock and
+    the reasons of the rows inside it; a region shorter than one sampling period falls back to warm-up + region rows."""
+    import importlib.util
+    import sys
+    import time
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    argv, sys.argv = sys.argv, ["bench.py"]
+    try:
+        spec = importlib.util.spec_from_file_location("bench_under_test", os.path.join(root, "bench.py"))
+        bench = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(bench)
+    finally:
+        sys.argv = argv
+    cs = bench.ClockSampler(0)
+    cs.source = "nvml"
+    now = time.perf_counter()
+    cs.rows = [(now - 2.0, 1200.0, 1965.0, ["sw_power_cap"]), (now - 1.5, 1300.0, 1965.0, [])]   # warm-up rows
+    cs.t0 = now - 1.0
+    cs.rows += [(now - 0.8, 1965.0, 1965.0, []), (now - 0.5, 1950.0, 1965.0, ["sw_thermal_slowdown"]), (now - 0.2, 1965.0, 1965.0, [])]
+    out = cs.stop()
+    assert out["samples"] == 3 and out["sm_mhz"] == 1965.0 and out["sm_max_mhz"] == 1965.0
+    assert out["reasons"] == ["sw_thermal_slowdown"] and out["window"] == "timed region"
+    cs2 = bench.ClockSampler(0)
+    cs2.source = "nvml"
+    cs2.rows = [(now - 2.0, 1200.0, 1965.0, ["sw_power_cap"])]
+    cs2.t0 = time.perf_counter()
+    out2 = cs2.stop()
+    assert out2["samples"] == 1 and out2["window"] == "warm-up + timed region" and out2["reasons"] == ["sw_power_cap"]
+    assert bench.ClockSampler(0).stop()["samples"] == 0
