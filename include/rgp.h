@@ -113,6 +113,9 @@ int rgp_convgru_seq_profile(unsigned long long* host_out, int n);
 /* gaze_grcn.py:225-227 (tf.transpose NCHW->NHWC of the C3D blob) fused with the fp32->operand
  * cast and the [B,T]->time-major reorder: c3d [B,T,C,P] fp32 -> out [(t*B+b)*P + p, C]. */
 int rgp_pack_c3d(const float* c3d, void* out, int B, int T, int C, int P, int dtype, void* stream);
+/* the same with the fed features in src_dtype (0 fp32 as the reference feeds them, gaze_rnn.py:520-531; 1 bf16: half the
+ * host->device bytes — the bf16 engine rounds the features to bf16 in this pass anyway, so `out` is bit-identical) */
+int rgp_pack_c3d_src(const void* c3d, int src_dtype, void* out, int B, int T, int C, int P, int dtype, void* stream);
 /* embedded features [B,T,G,G,C] fp32 (BASELINE 'L1' entry, after the projection) -> p-layout */
 int rgp_pack_emb(const float* emb, void* out, int B, int T, int G, int C, int dtype, void* stream);
 /* fp32 -> operand dtype cast of a flat buffer (weights after an optimiser step) */
@@ -151,6 +154,17 @@ int rgp_sumsq(const float* g, long long n, double* sumsq, void* stream);
 int rgp_gradnorm_clip_adam(float* p, const float* g, float* m, float* v, long long n,
                            const double* sumsq, float clip, float lr_t, float beta1, float beta2,
                            float eps, void* p_op, int dtype, void* stream);
+/* The optimiser schedule evaluated ON THE DEVICE (gaze_rnn.py:439-443 tf.train.exponential_decay(staircase) + the
+ * bias-corrected step size tf.train.AdamOptimizer forms in its python wrapper), so that one captured CUDA graph of
+ * fwd + BPTT + clip + Adam replays a CORRECT schedule: step[0] (int64, device) = global_step = updates applied so far;
+ * lr0[0] (double, device) = initial_learning_rate (the host rewrites it when decay_learning_rate() is called).
+ * Writes sched[0] = lr_t = lr*sqrt(1-beta2^t)/(1-beta1^t) with t = step+1, sched[1] = lr = lr0*decay^floor(step/decay_steps),
+ * then advances step[0] to t.  rgp_gradnorm_clip_adam_dev is rgp_gradnorm_clip_adam with lr_t read from sched[0]. */
+int rgp_adam_schedule(long long* step, const double* lr0, double decay, int decay_steps, double beta1, double beta2,
+                      float* sched, void* stream);
+int rgp_gradnorm_clip_adam_dev(float* p, const float* g, float* m, float* v, long long n, const double* sumsq,
+                               float clip, const float* lr_t_dev, float beta1, float beta2, float eps, void* p_op,
+                               int dtype, void* stream);
 int rgp_zero(void* p, long long bytes, void* stream);
 /* gaze_rnn.py:504-510 (random h-flip of half the batch) on the fed device buffers: x is [n_clips, rows_per_clip, W]
  * fp32; for each of the nsel clip indices in `clips` (device int32) every W-row is reversed in place. */

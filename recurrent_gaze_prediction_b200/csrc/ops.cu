@@ -1,5 +1,6 @@
 // ops.cu — bandwidth-bound kernels of the RGP path: layout packing, gate maths of the ConvLSTM,
 // head weight composition, spatial softmax + loss, gradient norm + clip + TF-Adam.
+#include <mutex>
 #include "common.cuh"
 
 namespace rgp {
@@ -22,21 +23,35 @@ __device__ __forceinline__ void st4_op(__nv_bfloat16* p, float a, float b, float
 // conflict-free).  Out: P rows x 64 channels; a thread converts 4 consecutive channels of one position (4 shared reads at
 // stride P, 2-way bank conflicts) and stores them as one 8-byte (bf16) / 16-byte (fp32) word, so a warp writes two full
 // 128-byte row segments per instruction instead of 64 bytes of 2-byte stores.
-template <typename TA>
-__global__ void __launch_bounds__(256) pack_c3d_kernel(const float* __restrict__ c3d, TA* __restrict__ out,
+//
+// TS = type of the fed features: float (the reference feeds fp32, gaze_rnn.py:520-531) or bf16 (half the host->device
+// bytes; the bf16 engine rounds the features to bf16 here anyway, so the packed operand is bit-identical).
+template <typename TA, typename TS>
+__global__ void __launch_bounds__(256) pack_c3d_kernel(const TS* __restrict__ c3d, TA* __restrict__ out,
                                                         int B, int T, int C, int P) {
   extern __shared__ float tile[];  // [64][P]
   const int f_in = blockIdx.x;     // b*T + t
   const int b = f_in / T, t = f_in - b * T;
   const int c0 = blockIdx.y * 64;
-  const float* src = c3d + ((long long)f_in * C + c0) * P;
+  const TS* src = c3d + ((long long)f_in * C + c0) * P;
   const int n = 64 * P;
-  if (((n | (int)(((long long)f_in * C + c0) * P)) & 3) == 0) {
+  if (sizeof(TS) == 4 && ((n | (int)(((long long)f_in * C + c0) * P)) & 3) == 0) {
     const float4* s4 = reinterpret_cast<const float4*>(src);
     float4* t4 = reinterpret_cast<float4*>(tile);
     for (int i = threadIdx.x; i < n / 4; i += 256) t4[i] = s4[i];
+  } else if (sizeof(TS) == 2 && ((n | (int)(((long long)f_in * C + c0) * P)) & 7) == 0) {
+    const uint4* s8 = reinterpret_cast<const uint4*>(src);       // 8 bf16 per 16-byte load
+    for (int i = threadIdx.x; i < n / 8; i += 256) {
+      const uint4 u = s8[i];
+      const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        tile[8 * i + 2 * j] = __uint_as_float(w[j] << 16);
+        tile[8 * i + 2 * j + 1] = __uint_as_float(w[j] & 0xffff0000u);
+      }
+    }
   } else {
-    for (int i = threadIdx.x; i < n; i += 256) tile[i] = src[i];
+    for (int i = threadIdx.x; i < n; i += 256) tile[i] = OpT<TS>::ld(src + i);
   }
   __syncthreads();
   TA* dst = out + ((long long)(t * B + b) * P) * C + c0;
@@ -375,10 +390,14 @@ __global__ void __launch_bounds__(1024) reduce_sum_kernel(const float* __restric
 // result does not depend on scheduling.  The scratch is library-static: calls must not overlap on different
 // streams of one process (include/rgp.h: one stream per model instance).
 constexpr int kRedBlocks = 296;
-__device__ double g_red_part[kRedBlocks];
-__device__ unsigned int g_red_count = 0;
+constexpr int kRedSlots = 16;            // concurrent streams served without sharing scratch (host side: red_slot())
+__device__ double g_red_part_all[kRedSlots][kRedBlocks];
+__device__ unsigned int g_red_count_all[kRedSlots] = {0};
 
-__global__ void __launch_bounds__(512) reduce_sum_big_kernel(const float* __restrict__ x, long long n, float* __restrict__ out) {
+__global__ void __launch_bounds__(512) reduce_sum_big_kernel(const float* __restrict__ x, long long n, float* __restrict__ out,
+                                                             int slot) {
+  double* g_red_part = g_red_part_all[slot];
+  unsigned int& g_red_count = g_red_count_all[slot];
   __shared__ double red[16];
   __shared__ bool last;
   const long long per = ((n / 4 + gridDim.x - 1) / gridDim.x) * 4;         // float4-aligned contiguous share per CTA
@@ -434,11 +453,30 @@ __global__ void __launch_bounds__(256) sumsq_kernel(const float* __restrict__ g,
   }
 }
 
+// gaze_rnn.py:439-443 + the python wrapper of tf.train.AdamOptimizer [TF-lib], evaluated ON THE DEVICE so that a captured
+// CUDA graph of the training step replays a correct schedule: state[0] = global_step (number of updates applied).
+//   lr   = lr0 * decay^floor(step / decay_steps)        (tf.train.exponential_decay, staircase)
+//   lr_t = lr * sqrt(1 - beta2^t) / (1 - beta1^t),  t = step + 1
+// sched[0] = lr_t (consumed by clip_adam_kernel), sched[1] = lr; then global_step <- t.  One thread, double arithmetic.
+__global__ void adam_schedule_kernel(long long* __restrict__ step, const double* __restrict__ lr0, double decay,
+                                     int decay_steps, double beta1, double beta2, float* __restrict__ sched) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  const long long s0 = step[0];
+  const double t = (double)(s0 + 1);
+  const double lr = lr0[0] * pow(decay, (double)(s0 / (decay_steps > 0 ? decay_steps : 1)));
+  const double lr_t = lr * sqrt(1.0 - pow(beta2, t)) / (1.0 - pow(beta1, t));
+  sched[0] = (float)lr_t;
+  sched[1] = (float)lr;
+  step[0] = s0 + 1;
+}
+
 template <typename TA>
 __global__ void __launch_bounds__(256) clip_adam_kernel(float* __restrict__ p, const float* __restrict__ g,
                                                          float* __restrict__ m, float* __restrict__ v, long long n,
-                                                         const double* __restrict__ sumsq, float clip, float lr_t,
+                                                         const double* __restrict__ sumsq, float clip, float lr_host,
+                                                         const float* __restrict__ lr_dev,
                                                          float b1, float b2, float eps, TA* __restrict__ p_op) {
+  const float lr_t = lr_dev ? lr_dev[0] : lr_host;
   const float norm = (float)sqrt(sumsq[0]);
   const float scale = clip > 0.f ? clip / fmaxf(norm, clip) : 1.0f;
   long long i = (long long)blockIdx.x * 256 + threadIdx.x;
@@ -474,19 +512,63 @@ __global__ void flip_w_kernel(float* __restrict__ x, const int* __restrict__ cli
 }  // namespace
 }  // namespace rgp
 
-extern "C" {
-
-int rgp_pack_c3d(const float* c3d, void* out, int B, int T, int C, int P, int dtype, void* stream) {
-  RGP_CHECK_ARG(C % 64 == 0, "rgp_pack_c3d: C=%d must be a multiple of 64", C);
+// ---- host helpers of the entry points below (C++ linkage)
+template <typename TA, typename TS>
+static int launch_pack_c3d(const void* c3d, void* out, int B, int T, int C, int P, void* stream) {
   dim3 grid(B * T, C / 64);
   size_t sm = (size_t)64 * P * sizeof(float);
-  if (sm > 48 * 1024) {
-    cudaFuncSetAttribute(pack_c3d_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-    cudaFuncSetAttribute(pack_c3d_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-  }
-  if (dtype == 0) pack_c3d_kernel<float><<<grid, 256, sm, (cudaStream_t)stream>>>(c3d, (float*)out, B, T, C, P);
-  else pack_c3d_kernel<__nv_bfloat16><<<grid, 256, sm, (cudaStream_t)stream>>>(c3d, (__nv_bfloat16*)out, B, T, C, P);
+  if (sm > 48 * 1024) cudaFuncSetAttribute(pack_c3d_kernel<TA, TS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+  pack_c3d_kernel<TA, TS><<<grid, 256, sm, (cudaStream_t)stream>>>((const TS*)c3d, (TA*)out, B, T, C, P);
   return check_launch("rgp_pack_c3d");
+}
+
+// The partial-sum scratch of the large reduction is keyed by (device, stream): two engines on different streams (or
+// devices: __device__ arrays are per device already) never share a slot.  More than kRedSlots live streams on one
+// device fall back to the single-CTA kernel, which needs no scratch.
+static int red_slot(void* stream) {
+  static std::mutex mu;
+  static void* owner[64][kRedSlots] = {};
+  static int used[64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  dev &= 63;
+  std::lock_guard<std::mutex> g(mu);
+  for (int i = 0; i < used[dev]; ++i)
+    if (owner[dev][i] == stream) return i;
+  if (used[dev] < kRedSlots) { owner[dev][used[dev]] = stream; return used[dev]++; }
+  return -1;
+}
+
+static int launch_clip_adam(float* p, const float* g, float* m, float* v, long long n, const double* sumsq, float clip,
+                            float lr_t, const float* lr_dev, float beta1, float beta2, float eps, void* p_op, int dtype,
+                            void* stream) {
+  int grid = (int)((n + 1023) / 1024);
+  if (grid > 148 * 8) grid = 148 * 8;
+  if (grid < 1) grid = 1;
+  if (dtype == 0 || p_op == nullptr)
+    clip_adam_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>(p, g, m, v, n, sumsq, clip, lr_t, lr_dev, beta1, beta2,
+                                                                     eps, (float*)p_op);
+  else
+    clip_adam_kernel<__nv_bfloat16><<<grid, 256, 0, (cudaStream_t)stream>>>(p, g, m, v, n, sumsq, clip, lr_t, lr_dev, beta1,
+                                                                             beta2, eps, (__nv_bfloat16*)p_op);
+  return check_launch("rgp_gradnorm_clip_adam");
+}
+
+extern "C" {
+
+int rgp_pack_c3d_src(const void* c3d, int src_dtype, void* out, int B, int T, int C, int P, int dtype, void* stream) {
+  RGP_CHECK_ARG(C % 64 == 0, "rgp_pack_c3d: C=%d must be a multiple of 64", C);
+  RGP_CHECK_ARG(src_dtype == 0 || src_dtype == 1, "rgp_pack_c3d_src: src_dtype=%d (0 fp32, 1 bf16)", src_dtype);
+  RGP_CHECK_ARG((size_t)64 * P * sizeof(float) <= 200 * 1024, "rgp_pack_c3d: P=%d positions per frame do not fit in shared memory", P);
+  if (src_dtype == 0)
+    return dtype == 0 ? launch_pack_c3d<float, float>(c3d, out, B, T, C, P, stream)
+                      : launch_pack_c3d<__nv_bfloat16, float>(c3d, out, B, T, C, P, stream);
+  return dtype == 0 ? launch_pack_c3d<float, __nv_bfloat16>(c3d, out, B, T, C, P, stream)
+                    : launch_pack_c3d<__nv_bfloat16, __nv_bfloat16>(c3d, out, B, T, C, P, stream);
+}
+
+int rgp_pack_c3d(const float* c3d, void* out, int B, int T, int C, int P, int dtype, void* stream) {
+  return rgp_pack_c3d_src(c3d, 0, out, B, T, C, P, dtype, stream);
 }
 
 int rgp_pack_emb(const float* emb, void* out, int B, int T, int G, int C, int dtype, void* stream) {
@@ -579,7 +661,8 @@ int rgp_softmax_xent_fwd_bwd(const float* logits, const float* gt, float* probs,
 }
 
 int rgp_reduce_sum(const float* x, long long n, float* out, void* stream) {
-  if (n > (1 << 16)) reduce_sum_big_kernel<<<kRedBlocks, 512, 0, (cudaStream_t)stream>>>(x, n, out);
+  const int slot = (n > (1 << 16)) ? red_slot(stream) : -1;
+  if (slot >= 0) reduce_sum_big_kernel<<<kRedBlocks, 512, 0, (cudaStream_t)stream>>>(x, n, out, slot);
   else reduce_sum_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(x, n, out);
   return check_launch("rgp_reduce_sum");
 }
@@ -594,16 +677,22 @@ int rgp_sumsq(const float* g, long long n, double* sumsq, void* stream) {
 
 int rgp_gradnorm_clip_adam(float* p, const float* g, float* m, float* v, long long n, const double* sumsq, float clip,
                            float lr_t, float beta1, float beta2, float eps, void* p_op, int dtype, void* stream) {
-  int grid = (int)((n + 1023) / 1024);
-  if (grid > 148 * 8) grid = 148 * 8;
-  if (grid < 1) grid = 1;
-  if (dtype == 0 || p_op == nullptr)
-    clip_adam_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>(p, g, m, v, n, sumsq, clip, lr_t, beta1, beta2, eps,
-                                                                     (float*)p_op);
-  else
-    clip_adam_kernel<__nv_bfloat16><<<grid, 256, 0, (cudaStream_t)stream>>>(p, g, m, v, n, sumsq, clip, lr_t, beta1,
-                                                                             beta2, eps, (__nv_bfloat16*)p_op);
-  return check_launch("rgp_gradnorm_clip_adam");
+  return launch_clip_adam(p, g, m, v, n, sumsq, clip, lr_t, nullptr, beta1, beta2, eps, p_op, dtype, stream);
+}
+
+int rgp_gradnorm_clip_adam_dev(float* p, const float* g, float* m, float* v, long long n, const double* sumsq, float clip,
+                               const float* lr_t_dev, float beta1, float beta2, float eps, void* p_op, int dtype,
+                               void* stream) {
+  RGP_CHECK_ARG(lr_t_dev != nullptr, "rgp_gradnorm_clip_adam_dev: lr_t_dev is NULL%s", "");
+  return launch_clip_adam(p, g, m, v, n, sumsq, clip, 0.f, lr_t_dev, beta1, beta2, eps, p_op, dtype, stream);
+}
+
+int rgp_adam_schedule(long long* step, const double* lr0, double decay, int decay_steps, double beta1, double beta2,
+                      float* sched, void* stream) {
+  RGP_CHECK_ARG(step && lr0 && sched, "rgp_adam_schedule: null pointer%s", "");
+  RGP_CHECK_ARG(decay_steps > 0, "rgp_adam_schedule: decay_steps=%d", decay_steps);
+  adam_schedule_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(step, lr0, decay, decay_steps, beta1, beta2, sched);
+  return check_launch("rgp_adam_schedule");
 }
 
 int rgp_flip_w(float* x, const int* clips, int nsel, long long rows_per_clip, int W, void* stream) {

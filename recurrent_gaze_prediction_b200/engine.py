@@ -31,6 +31,52 @@ def _tdtype(dtype):
     return torch.float32 if dtype == 0 else torch.bfloat16
 
 
+class StepGraph(object):
+    """One batch through the hot path as ONE CUDA-graph submission: forward + loss, and for train=True also BPTT +
+    global-norm clip + TF-Adam with the schedule evaluated on the device (rgp_adam_schedule), so every replay is a correct
+    optimiser step.  With a data-parallel `allreduce` the collective stays outside the captured region:
+    graph(fwd + BPTT) -> NCCL all-reduce of the flat gradient -> graph(clip + Adam)   (base.py:287-297: the norm is of the
+    GLOBAL gradient).  `fwd` is a callable issuing the forward on the engine's fixed input buffers.
+    The warm-up run that precedes the capture is undone (parameters, moments and global_step restored), so building the
+    graph does not train."""
+
+    def __init__(self, eng, fwd, train=False, allreduce=None, opt=None):
+        self.eng, self.train, self.allreduce = eng, bool(train), allreduce
+        opt = dict(opt or {})
+        opt.pop("allreduce", None)
+
+        def fwd_bwd():
+            fwd()
+            if train:
+                eng.backward()
+
+        def update():
+            eng.optimizer_step(**opt)
+
+        def whole():
+            fwd_bwd()
+            update()
+
+        snap = eng.snapshot_train_state() if train else None
+        self.g2 = None
+        if train and allreduce is not None:
+            self.g1, n1 = eng.make_graph(fwd_bwd)
+            self.g2, n2 = eng.make_graph(update)
+            self.kernels = n1 + n2
+        else:
+            self.g1, self.kernels = eng.make_graph(whole if train else fwd_bwd)
+        if snap is not None:
+            eng.restore_train_state(snap)
+
+    def replay(self):
+        self.g1.replay()
+        if self.g2 is not None:
+            self.allreduce(self.eng.grads)
+            self.g2.replay()
+        if self.train:
+            self.eng.note_replayed_steps(1)
+
+
 class GazeEngine(object):
     def __init__(self, model="gaze_grcn", B=2, T=35, G=7, Ch=128, Cin=512, Cfeat=1024, dtype=0,
                  device="cuda", lib=None, train=False, head=None, engine=None, seq=None, nsplit=None, mcast=None,
@@ -126,6 +172,13 @@ class GazeEngine(object):
             self.adam_m = torch.zeros(off, dtype=torch.float32, device=dev)
             self.adam_v = torch.zeros(off, dtype=torch.float32, device=dev)
             self.sumsq = torch.zeros(1, dtype=torch.float64, device=dev)
+            # optimiser schedule state ON THE DEVICE (rgp_adam_schedule): global_step, initial learning rate, and the
+            # (lr_t, lr) pair the Adam kernel reads — a captured graph of the training step replays a correct schedule
+            self.step_dev = torch.zeros(1, dtype=torch.int64, device=dev)
+            self.lr0_dev = torch.zeros(1, dtype=torch.float64, device=dev)
+            self.sched = torch.zeros(2, dtype=torch.float32, device=dev)
+            self._lr0_host = None
+            self._step = 0
 
     def view(self, name, buf=None):
         off, n = self.offsets[name]
@@ -276,7 +329,6 @@ class GazeEngine(object):
                 self.dw123 = z(384, Ch)
                 self.dw23 = z(121 * 64)
                 self.dw3f = z(49 * 32)
-            self.step = 0
 
     def _slab(self, buf, t):
         """device address of the B*S-row slab t of a flat [rows, C] buffer"""
@@ -300,7 +352,7 @@ class GazeEngine(object):
 
     # ------------------------------------------------------------------ forward
     def forward(self, c3d=None, emb=None, gt=None, loss_type="xentropy", global_batch=None, carry_state=False, t0=0):
-        """c3d [B,T,Cfeat,G,G] fp32 (reference entry, gaze_grcn.py:173) or emb [B,T,G,G,Cin] fp32
+        """c3d [B,T,Cfeat,G,G] fp32 or bf16 (reference entry, gaze_grcn.py:173) or emb [B,T,G,G,Cin] fp32
         (already-projected features).  Returns logits [B,T,GH,GW]; with gt also fills probs and loss.
         carry_state=True starts from the state left in slab 0 by set_initial_state() / carry_last_state()
         (cell-level API, chunked long clips) instead of h_0 = 0 (gaze_grcn.py:262)."""
@@ -324,8 +376,11 @@ class GazeEngine(object):
         lib, s = self.lib, self._s()
         B, T, S, Cin, Wp, G = self.B, self.T, self.S, self.Cin, self.Wp, self.G
         if c3d is not None:
-            assert tuple(c3d.shape) == (B, T, self.Cfeat, G, G) and c3d.dtype == torch.float32
-            lib.rgp_pack_c3d(c3d.data_ptr(), self.Apack.data_ptr(), B, T, self.Cfeat, self.P, self.dtype, s)
+            # fp32 as the reference feeds them (gaze_rnn.py:520-531), or bf16: half the host->device bytes, and since the
+            # bf16 engine rounds the features to bf16 in this very pass, the packed operand is bit-identical
+            assert tuple(c3d.shape) == (B, T, self.Cfeat, G, G) and c3d.dtype in (torch.float32, torch.bfloat16)
+            lib.rgp_pack_c3d_src(c3d.data_ptr(), 1 if c3d.dtype == torch.bfloat16 else 0, self.Apack.data_ptr(), B, T,
+                                 self.Cfeat, self.P, self.dtype, s)
             self._gemm(A=self.Apack.data_ptr(), rowsA=T * B * self.P, lda=self.Cfeat, Bw=self._pop("proj_W_op"),
                        M=T * B * self.P, N=Cin, K=self.Cfeat, taps=[0], epi=L.EPI_PROJ, P=self.P, G=G,
                        So=S, Wo=Wp, pado=1, out_op=self.Xp.data_ptr(), ldo=Cin, bias=self._ptr("proj_b"))
@@ -482,6 +537,20 @@ class GazeEngine(object):
             fn()
         return g, self.lib.launches - n0
 
+    def snapshot_train_state(self):
+        return (self.params.clone(), self.params_op.clone(), self.adam_m.clone(), self.adam_v.clone(), self._step,
+                self.param_version)
+
+    def restore_train_state(self, snap):
+        p, po, m, v, step, ver = snap
+        self.params.copy_(p)
+        if self.params_op is not self.params:
+            self.params_op.copy_(po)
+        self.adam_m.copy_(m)
+        self.adam_v.copy_(v)
+        self.step = step
+        self.param_version = ver + 1          # anything derived from the parameters (composed head) is stale
+
     def time_stages(self, c3d, gt, iters=3, emb=False):
         """CUDA-event time (ms, mean of `iters`) of each stage of one forward pass on the current stream."""
         names = ["embed", "i2h", "recurrence", "head", "loss"]
@@ -500,7 +569,10 @@ class GazeEngine(object):
         return acc
 
     def _compose_head(self):
-        if self.head_version == self.param_version:
+        # under a graph capture of a TRAINING step the composition must be part of the graph (the parameters change
+        # at every replay), whatever the host-side version counters say at capture time
+        capturing = self.device.type == "cuda" and torch.cuda.is_current_stream_capturing()
+        if self.head_version == self.param_version and not (capturing and self.train):
             return
         self.lib.rgp_head_compose(self._ptr("w1"), self._ptr("w2"), self._ptr("w3"), self._ptr("out_W"),
                                   self.w3f.data_ptr(), self.w23.data_ptr(), self.w123.data_ptr(),
@@ -673,22 +745,58 @@ class GazeEngine(object):
         self._mark("wgrad_cell")
 
     # ------------------------------------------------------------------ optimiser — base.py:262-297, gaze_rnn.py:435-444
+    @property
+    def step(self):
+        """global_step = optimiser updates applied so far.  The authoritative copy lives on the device (step_dev,
+        advanced by rgp_adam_schedule inside the — possibly graph-captured — step); this host mirror is advanced by
+        optimizer_step() / note_replayed_steps() and never needs a device read."""
+        return getattr(self, "_step", 0)
+
+    @step.setter
+    def step(self, v):
+        self._step = int(v)
+        if self.train:
+            self.step_dev.fill_(int(v))
+
+    def step_on_device(self):
+        """the device's own global_step (synchronises; tests / checkpoint sanity)"""
+        return int(self.step_dev.cpu()[0])
+
+    def note_replayed_steps(self, n=1):
+        """a captured graph containing optimizer_step() was replayed n times: advance the host mirror"""
+        self._step += int(n)
+        self.param_version += int(n)
+
     def learning_rate(self, lr0=1e-4, decay=0.8, decay_steps=500):
         return lr0 * decay ** (self.step // decay_steps)
 
-    def optimizer_step(self, lr0=1e-4, decay=0.8, clip=10.0, beta1=0.9, beta2=0.999, eps=1e-8, allreduce=None):
+    def set_lr0(self, lr0):
+        """initial learning rate (x decay_learning_rate's factor) -> the device scalar the schedule kernel reads; a
+        host-to-device write only when the value changes (never inside a graph capture)"""
+        if self._lr0_host != float(lr0):
+            if self.device.type == "cuda" and torch.cuda.is_current_stream_capturing():
+                raise RuntimeError("the learning rate changed inside a CUDA-graph capture: call set_lr0() before capturing")
+            self.lr0_dev.fill_(float(lr0))
+            self._lr0_host = float(lr0)
+
+    def optimizer_step(self, lr0=1e-4, decay=0.8, clip=10.0, beta1=0.9, beta2=0.999, eps=1e-8, allreduce=None,
+                       decay_steps=500):
         """clip_by_global_norm + TF-Adam on the flat buffers.  `allreduce(grads)` (optional) sums the gradient
-        over data-parallel ranks first: the norm must be taken over the GLOBAL gradient (base.py:287-297)."""
+        over data-parallel ranks first: the norm must be taken over the GLOBAL gradient (base.py:287-297).
+        The staircase learning rate and Adam's bias-corrected step size are formed on the device from the device-side
+        global_step (rgp_adam_schedule), so this call is graph-capturable with a correct schedule."""
         lib, s = self.lib, self._s()
         if allreduce is not None:
             allreduce(self.grads)
+        self.set_lr0(lr0)
         lib.rgp_zero(self.sumsq.data_ptr(), 8, s)
         lib.rgp_sumsq(self.grads.data_ptr(), self.nparams, self.sumsq.data_ptr(), s)
-        t = self.step + 1
-        lr = self.learning_rate(lr0, decay)
-        lr_t = lr * math.sqrt(1.0 - beta2 ** t) / (1.0 - beta1 ** t)
-        lib.rgp_gradnorm_clip_adam(self.params.data_ptr(), self.grads.data_ptr(), self.adam_m.data_ptr(),
-                                   self.adam_v.data_ptr(), self.nparams, self.sumsq.data_ptr(), clip, lr_t, beta1,
-                                   beta2, eps, self.params_op.data_ptr() if self.dtype != 0 else 0, self.dtype, s)
-        self.step += 1
-        self.param_version += 1
+        lib.rgp_adam_schedule(self.step_dev.data_ptr(), self.lr0_dev.data_ptr(), float(decay), int(decay_steps),
+                              float(beta1), float(beta2), self.sched.data_ptr(), s)
+        lib.rgp_gradnorm_clip_adam_dev(self.params.data_ptr(), self.grads.data_ptr(), self.adam_m.data_ptr(),
+                                       self.adam_v.data_ptr(), self.nparams, self.sumsq.data_ptr(), clip,
+                                       self.sched.data_ptr(), beta1, beta2, eps,
+                                       self.params_op.data_ptr() if self.dtype != 0 else 0, self.dtype, s)
+        if not (self.device.type == "cuda" and torch.cuda.is_current_stream_capturing()):
+            self._step += 1
+            self.param_version += 1

@@ -69,6 +69,7 @@ _SIGS = {
     "rgp_convgru_seq_fwd": [C.POINTER(GruSeqArgs), _vp],
     "rgp_convgru_seq_profile": [_vp, _i],
     "rgp_pack_c3d": [_vp, _vp, _i, _i, _i, _i, _i, _vp],
+    "rgp_pack_c3d_src": [_vp, _i, _vp, _i, _i, _i, _i, _i, _vp],
     "rgp_pack_emb": [_vp, _vp, _i, _i, _i, _i, _i, _vp],
     "rgp_cast": [_vp, _vp, _ll, _i, _vp],
     "rgp_fc_head": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp],
@@ -79,6 +80,8 @@ _SIGS = {
     "rgp_reduce_sum": [_vp, _ll, _vp, _vp],
     "rgp_sumsq": [_vp, _ll, _vp, _vp],
     "rgp_gradnorm_clip_adam": [_vp, _vp, _vp, _vp, _ll, _vp, _f, _f, _f, _f, _f, _vp, _i, _vp],
+    "rgp_adam_schedule": [_vp, _vp, _d, _i, _d, _d, _vp, _vp],
+    "rgp_gradnorm_clip_adam_dev": [_vp, _vp, _vp, _vp, _ll, _vp, _f, _vp, _f, _f, _f, _vp, _i, _vp],
     "rgp_zero": [_vp, _ll, _vp],
     "rgp_flip_w": [_vp, _vp, _i, _ll, _i, _vp],
     "rgp_wgrad": [C.POINTER(WgradArgs), _vp],

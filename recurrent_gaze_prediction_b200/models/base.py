@@ -99,40 +99,69 @@ class ModelBase(object):
                 self.engine.adam_v.copy_(torch.from_numpy(z["__adam_v__"]))
             if "__global_step__" in z.files and self.engine.train:
                 self.engine.step = int(z["__global_step__"])
+            if "__lr_scale__" in z.files:          # decay_learning_rate()'s accumulated factor (base.py:398-404)
+                self._lr_scale = float(z["__lr_scale__"])
         log.info(" [Checkpoint] Successfully loaded from %s", checkpoint_path)
 
     def save_model_checkpoint(self, checkpoint_dir):
+        """base.py:240-253.  Data-parallel ranks hold identical parameters: rank 0 alone writes (to a temporary file
+        that is atomically renamed into place, so a reader never sees a partial archive), then all ranks meet at a
+        barrier so nobody reloads before the file exists."""
         model_name = type(self).__name__ or "Model"
         checkpoint_dir = os.path.join(checkpoint_dir, "model")
-        os.makedirs(checkpoint_dir, exist_ok=True)
         step = self.current_step
         fname = "%s-%d.npz" % (model_name, step)
         checkpoint_path = os.path.join(checkpoint_dir, fname)
-        variables = self.engine.op_to_tf(self.engine.params.cpu().numpy())
-        extra = {"__global_step__": np.int64(step)}
-        if self.engine.train:
-            extra["__adam_m__"] = self.engine.adam_m.cpu().numpy()
-            extra["__adam_v__"] = self.engine.adam_v.cpu().numpy()
-        np.savez(checkpoint_path, **variables, **extra)
-        with open(os.path.join(checkpoint_dir, "checkpoint"), "w") as fp:
-            fp.write(fname + "\n")
-        log.info(" [Checkpoint] Saved checkpoints into %s !" % checkpoint_path)
+        rank, world = int(getattr(self, "rank", 0)), int(getattr(self, "world_size", 1))
+        if rank == 0:
+            os.makedirs(checkpoint_dir, exist_ok=True)
+            variables = self.engine.op_to_tf(self.engine.params.cpu().numpy())
+            extra = {"__global_step__": np.int64(step), "__lr_scale__": np.float64(self._lr_scale)}
+            if self.engine.train:
+                extra["__adam_m__"] = self.engine.adam_m.cpu().numpy()
+                extra["__adam_v__"] = self.engine.adam_v.cpu().numpy()
+            tmp = checkpoint_path + ".tmp-%d.npz" % os.getpid()
+            np.savez(tmp, **variables, **extra)
+            os.replace(tmp, checkpoint_path)
+            state_tmp = os.path.join(checkpoint_dir, "checkpoint.tmp-%d" % os.getpid())
+            with open(state_tmp, "w") as fp:
+                fp.write(fname + "\n")
+            os.replace(state_tmp, os.path.join(checkpoint_dir, "checkpoint"))
+            log.info(" [Checkpoint] Saved checkpoints into %s !" % checkpoint_path)
+        if world > 1:
+            import torch.distributed as dist
+            if dist.is_available() and dist.is_initialized():
+                dist.barrier()
         return checkpoint_path
 
     # ---------------------------------------------------------------- training loop (base.py:330-359)
     def fit(self):
+        """base.py:330-359.  With config.prefetch the NEXT training batch is fetched, normalised and uploaded while the
+        current step runs on the GPU (the step is submitted asynchronously; the loss is read only when it is logged).
+        The order of every draw from the global numpy RNG is the reference's: a step that is followed by an evaluation
+        (which draws jitter / negative samples) does not prefetch across it."""
         log.info("Initial Learning Rate = %.6f" % self.current_learning_rate)
         assert self.current_learning_rate > 0
         self.reload_checkpoint()
+        c = self.config
+        pipelined = bool(getattr(c, "prefetch", False)) and hasattr(self, "prefetch") and \
+            getattr(self, "chunk_steps", None) is None and getattr(self.engine, "device", None) is not None and \
+            self.engine.device.type == "cuda"
         step = 0
-        while step <= self.config.max_steps:
-            step = self.single_step(train_mode=True)
+        have_next = False
+        while step <= c.max_steps:
+            nxt = self.current_step + 1
+            crosses_eval = np.mod(nxt, c.steps_per_evaluation) == 0
+            want_next = pipelined and nxt <= c.max_steps and not crosses_eval
+            step = self.single_step(train_mode=True, _prefetched=have_next, _prefetch_next=want_next) if pipelined \
+                else self.single_step(train_mode=True)
+            have_next = want_next
             assert step > 0
-            if np.mod(step, self.config.steps_per_checkpoint) == 0 and self.train_dir:
+            if np.mod(step, c.steps_per_checkpoint) == 0 and self.train_dir:
                 self.save_model_checkpoint(self.train_dir)
-            if np.mod(step, self.config.steps_per_validation) == 0:
+            if np.mod(step, c.steps_per_validation) == 0:
                 _ = self.single_step(train_mode=False)
-            if np.mod(step, self.config.steps_per_evaluation) == 0:
+            if np.mod(step, c.steps_per_evaluation) == 0:
                 self.generate_and_evaluate(self.data_sets.valid)
 
     def report_evaluate_summary(self, batch_scores):

@@ -20,7 +20,7 @@ import time
 import numpy as np
 import torch
 
-from ..engine import GazeEngine, LOSS_TYPES
+from ..engine import GazeEngine, LOSS_TYPES, StepGraph
 from .. import lib as L
 from .. import evaluation_metrics as EM
 from .base import BaseModelConfig, ModelBase
@@ -60,7 +60,12 @@ class GRUModelConfig(BaseModelConfig):
         self.dtype = 'bf16'           # 'bf16': tcgen05 engine, fp32 accumulate; 'fp32': CUDA-core engine
         self.device = 'cuda'
         self.seed = 0
-        self.learning_rate_decay_steps = 500
+        self.learning_rate_decay_steps = 500      # gaze_rnn.py:440 hard-codes 500
+        # execution options of the B200 path
+        self.cuda_graph = True        # one CUDA-graph submission per step (fwd [+ BPTT + clip/Adam]) instead of ~80-900 launches
+        self.prefetch = True          # fit(): batch k+1 is prepared on the host and uploaded while step k runs
+        self.feature_dtype = 'fp32'   # dtype of the fed C3D features: 'fp32' (reference) or 'bf16' (half the H2D bytes;
+                                      # bit-identical results on the bf16 engine, which rounds the features anyway)
 
 
 def _shard(x, rank, world):
@@ -132,8 +137,9 @@ class GazePredictionGRU(ModelBase):
                                                    dim_proj=self.dim_cnn_proj, dim_feature=c.dim_feature,
                                                    seed=getattr(c, "seed", 0)))
         z = lambda *s: torch.zeros(*s, dtype=torch.float32, device=dev)
+        fdt = {'fp32': torch.float32, 'bf16': torch.bfloat16}[getattr(c, "feature_dtype", 'fp32')]
         self.frame_images = None                                     # unused by the RGP path (gaze_grcn.py:173-376 never reads it)
-        self.c3d_input = z(B, T, c.dim_feature, G, G)                # gaze_rnn.py:118-121
+        self.c3d_input = torch.zeros(B, T, c.dim_feature, G, G, dtype=fdt, device=dev)   # gaze_rnn.py:118-121
         self.gt_gazemap = z(B, T, GH, GH)                            # gaze_rnn.py:122-126
         self.dropout_keep_prob = 1.0                                 # never fires in GRCN / LSTM
         if self.chunk_steps is None:
@@ -146,9 +152,21 @@ class GazePredictionGRU(ModelBase):
         self.loss = self.engine.loss
         if c.loss_type not in LOSS_TYPES:
             raise NotImplementedError(str(c.loss_type))             # gaze_rnn.py:405-406
+        self._alloc_staging(dev, fdt)
+
+    def _alloc_staging(self, dev, fdt=torch.float32):
+        """pinned host staging for batches that arrive as ordinary (pageable) arrays, the pinned loss slot, and the
+        double-buffered upload path used by fit() (pipeline.PrefetchFeeder)"""
         pin = dev.type == "cuda"
-        self._c3d_host = torch.zeros(B, T, c.dim_feature, G, G, dtype=torch.float32, pin_memory=pin)
-        self._gt_host = torch.zeros(B, T, GH, GH, dtype=torch.float32, pin_memory=pin)
+        self._c3d_host = torch.zeros(tuple(self.c3d_input.shape), dtype=fdt, pin_memory=pin)
+        self._gt_host = torch.zeros(tuple(self.gt_gazemap.shape), dtype=torch.float32, pin_memory=pin)
+        self._loss_host = torch.zeros(1, dtype=torch.float32, pin_memory=pin)
+        self._loss_event = torch.cuda.Event() if pin else None
+        self._loss_pending = False
+        self._last_loss = float("nan")
+        self._graphs = {}
+        self._feeder = None
+        self._gather_buf = None
 
     def _build_dense_model(self):
         """The class as the reference defines it: the dense GRU variant (gaze_rnn.py:211-361) —
@@ -182,9 +200,7 @@ class GazePredictionGRU(ModelBase):
         self.loss = self.engine.loss
         if c.loss_type not in LOSS_TYPES:
             raise NotImplementedError(str(c.loss_type))
-        pin = dev.type == "cuda"
-        self._c3d_host = torch.zeros(B, T, c.dim_feature, G, G, dtype=torch.float32, pin_memory=pin)
-        self._gt_host = torch.zeros(B, T, GH, GW, dtype=torch.float32, pin_memory=pin)
+        self._alloc_staging(dev)
 
     @staticmethod
     def create_loss_and_summary(predicted_gazemaps, gt_gazemap, loss_type='xentropy', lib=None):
@@ -212,29 +228,65 @@ class GazePredictionGRU(ModelBase):
             self.learning_rate_decay ** (step // getattr(c, "learning_rate_decay_steps", 500))
 
     def build_train_op(self):
+        method = getattr(self.config, "optimization_method", 'adam')
+        if method not in ('adam', 'rmsprop', 'sgd'):
+            raise ValueError('Invalid optimization method!')                  # base.py:268-275
+        if method != 'adam' and getattr(self.engine, "train", False):
+            # base.py:270-273 offers RMSProp(momentum 0.9) and Momentum(0.9); every entry point of the reference sets
+            # 'adam' (gaze_rnn.py:57) and only the Adam update is built here — refuse rather than silently run Adam
+            raise NotImplementedError("optimization_method=%r: only 'adam' (the reference's setting, gaze_rnn.py:57) is "
+                                      "built on the B200 path" % method)
         self.global_step = 0
         self.learning_rate = self.current_learning_rate
-        self.train_op = self._train_step if self.engine.train else None
+        self.train_op = self._train_step if getattr(self.engine, "train", False) else None
         self.no_op = lambda: None        # the ShallowNet train-op of the reference is a no_op (gaze_rnn.py:459-466)
+
+    def _opt_kwargs(self):
+        return dict(lr0=self.initial_learning_rate * self._lr_scale, decay=self.learning_rate_decay,
+                    clip=self.max_grad_norm, decay_steps=int(getattr(self.config, "learning_rate_decay_steps", 500)))
 
     def _train_step(self):
         self.engine.backward()
-        self.engine.optimizer_step(lr0=self.initial_learning_rate * self._lr_scale, decay=self.learning_rate_decay,
-                                   clip=self.max_grad_norm, allreduce=self._allreduce)
+        self.engine.optimizer_step(allreduce=self._allreduce, **self._opt_kwargs())
         self.global_step = self.engine.step
 
     # ---------------------------------------------------------------- feeding ("session.run")
-    def _feed(self, batch_c3d, batch_maps):
-        """host batch (global batch_size clips) -> this rank's shard -> pinned staging -> device placeholders"""
-        c3d = np.reshape(batch_c3d, [self.batch_size, -1, self.dim_feature, self.engine.G, self.engine.G])
+    @staticmethod
+    def _as_host_tensor(x, dtype=None):
+        """NumPy array or CPU tensor -> contiguous CPU tensor (no copy when it already is one of the right dtype)"""
+        t = x if isinstance(x, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(x))
+        if dtype is not None and t.dtype != dtype:
+            t = t.to(dtype)
+        return t.contiguous()
+
+    def _stage(self, batch_c3d, batch_maps, stage=None):
+        """host batch (global batch_size clips; NumPy arrays or CPU tensors) -> this rank's shard as PINNED host tensors
+        of the placeholders' dtypes.  A shard that already lives in pinned memory with the right dtype is used in
+        place (no staging copy: the H2D engine reads it directly); anything else goes through the model's pinned
+        staging buffers."""
+        G = self.engine.G
+        c3d = batch_c3d if isinstance(batch_c3d, torch.Tensor) else np.asarray(batch_c3d)
+        c3d = c3d.reshape(self.batch_size, -1, self.dim_feature, G, G)
         c3d = _shard(c3d, self.rank, self.world_size)
-        maps = _shard(np.asarray(batch_maps, dtype=np.float32), self.rank, self.world_size)
+        maps = batch_maps if isinstance(batch_maps, torch.Tensor) else np.asarray(batch_maps, dtype=np.float32)
+        maps = _shard(maps, self.rank, self.world_size)
         if c3d.shape[1] != self.n_lstm_steps:
             raise ValueError("clip length %d != n_lstm_steps %d" % (c3d.shape[1], self.n_lstm_steps))
-        self._c3d_host.copy_(torch.from_numpy(np.ascontiguousarray(c3d, dtype=np.float32)))
-        self._gt_host.copy_(torch.from_numpy(np.ascontiguousarray(maps)))
-        self.c3d_input.copy_(self._c3d_host, non_blocking=True)
-        self.gt_gazemap.copy_(self._gt_host, non_blocking=True)
+        out = []
+        for x, buf in zip((c3d, maps), stage or (self._c3d_host, self._gt_host)):
+            t = x if isinstance(x, torch.Tensor) else torch.from_numpy(x)
+            if t.dtype == buf.dtype and t.is_contiguous() and buf.is_pinned() and t.is_pinned():
+                out.append(t.view(buf.shape))
+            else:
+                buf.copy_(t.reshape(buf.shape))              # converts dtype (fp32 -> bf16 features) on the host
+                out.append(buf)
+        return out
+
+    def _feed(self, batch_c3d, batch_maps):
+        """-> device placeholders (asynchronous copies on the model's stream)"""
+        c3d_h, gt_h = self._stage(batch_c3d, batch_maps)
+        self.c3d_input.copy_(c3d_h, non_blocking=True)
+        self.gt_gazemap.copy_(gt_h, non_blocking=True)
 
     def _flip_fed(self, clip_indices):
         """gaze_rnn.py:507-509 on the device placeholders: reverse the W axis of c3d_input and gt_gazemap for the
@@ -254,24 +306,70 @@ class GazePredictionGRU(ModelBase):
     def _lib_handle(self):
         return self.engine.lib
 
-    def run(self, train=False):
-        """One pass over the fed placeholders: forward + loss (+ BPTT + clip/Adam when train).  Returns the loss."""
+    def _use_graph(self):
+        e = self.engine
+        return (bool(getattr(self.config, "cuda_graph", True)) and e.device.type == "cuda" and self.chunk_steps is None
+                and self.model_name is not None)
+
+    def _forward_fed(self):
+        self.engine.forward(c3d=self.c3d_input, gt=self.gt_gazemap, loss_type=self.config.loss_type,
+                            global_batch=self.batch_size)
+
+    def _step_graph(self, train):
+        """the captured step for this mode; re-captured when the optimiser hyper-parameters baked into the graph (clip,
+        decay) change — the learning rate itself is a device scalar and needs no re-capture"""
+        key = ("train", self.max_grad_norm, self.learning_rate_decay) if train else ("infer",)
+        g = self._graphs.get(key)
+        if g is None:
+            if train and self.train_op is None:
+                raise RuntimeError("this model was built without a train op")
+            g = StepGraph(self.engine, self._forward_fed, train=train, allreduce=self._allreduce if train else None,
+                          opt=self._opt_kwargs() if train else None)
+            self._graphs[key] = g
+        return g
+
+    def run(self, train=False, sync=True):
+        """One pass over the fed placeholders: forward + loss (+ BPTT + clip/Adam when train) — one CUDA-graph submission
+        (config.cuda_graph), else eager launches.  sync=True returns the loss (a device->host read); sync=False leaves
+        the read pending (``last_loss`` collects it) so that the host can prepare the next batch meanwhile."""
         if self.chunk_steps is not None:
             if train:
                 raise RuntimeError("a chunked model cannot train")
             return self._run_chunked()
-        self.engine.forward(c3d=self.c3d_input, gt=self.gt_gazemap, loss_type=self.config.loss_type,
-                            global_batch=self.batch_size)
-        if train:
-            if self.train_op is None:
-                raise RuntimeError("this model was built without a train op")
-            self.train_op()
-        loss = float(self.engine.loss.cpu()[0])
+        if self._use_graph():
+            if train:
+                self.engine.set_lr0(self.initial_learning_rate * self._lr_scale)
+            self._step_graph(train).replay()
+            if train:
+                self.global_step = self.engine.step
+        else:
+            self._forward_fed()
+            if train:
+                if self.train_op is None:
+                    raise RuntimeError("this model was built without a train op")
+                self.train_op()
+        loss_dev = self.engine.loss
         if self.world_size > 1 and self._allreduce is not None:
-            t = self.engine.loss.clone()
-            self._allreduce(t)          # local losses are already scaled by 1/(B_global*T): the sum is the global loss
-            loss = float(t.cpu()[0])
-        return loss
+            loss_dev = self.engine.loss.clone()
+            self._allreduce(loss_dev)   # local losses are already scaled by 1/(B_global*T): the sum is the global loss
+        if self._loss_event is None:
+            self._last_loss, self._loss_pending = float(loss_dev.cpu()[0]), False
+            return self._last_loss
+        self._loss_host.copy_(loss_dev, non_blocking=True)
+        self._loss_event.record(torch.cuda.current_stream(self.engine.device))
+        self._loss_pending = True
+        return self.last_loss if sync else None
+
+    @property
+    def last_loss(self):
+        if self._loss_pending:
+            self._loss_event.synchronize()
+            self._last_loss, self._loss_pending = float(self._loss_host[0]), False
+        return self._last_loss
+
+    @last_loss.setter
+    def last_loss(self, v):
+        self._last_loss, self._loss_pending = float(v), False
 
     def _run_chunked(self):
         """The clip in chunks of `chunk_steps` frames: the state left by chunk k (h_T, and the LSTM cell) is the initial
@@ -293,28 +391,62 @@ class GazePredictionGRU(ModelBase):
             loss = float(t.cpu()[0])
         return loss
 
-    def predict(self, batch_c3d):
+    def predict(self, batch_c3d, out=None):
         """The inference call the reference's extract_map.py:210-217 wishes the model had
         (`session.run([model.predicted_gazemaps], {model.c3d_input: ..})`): c3d [batch_size, T, 1024, 7, 7] host array
-        -> gaze maps [local clips, T, GH, GW] (probabilities for xentropy / KLD, raw maps for l2) as a NumPy array."""
-        B, T = self.batch_size, self.n_lstm_steps
-        GH, GW = self.gazemap_height, self.gazemap_width
-        self._feed(batch_c3d, np.zeros((B, T, GH, GW), dtype=np.float32))
-        self.run(train=False)
-        return self.predicted_gazemaps.cpu().numpy()
+        (NumPy, or a CPU tensor — pinned memory is read in place by the copy engine; bf16 features are accepted when
+        config.feature_dtype == 'bf16') -> gaze maps [local clips, T, GH, GW] (probabilities for xentropy / KLD, raw maps
+        for l2).  `out`: optional pinned CPU tensor that receives the maps (returned as such, after synchronising);
+        default: a fresh NumPy array."""
+        c3d_h, _ = self._stage(batch_c3d, self._gt_host)
+        self.c3d_input.copy_(c3d_h, non_blocking=True)
+        self.run(train=False, sync=False)
+        if out is None:
+            return self.predicted_gazemaps.cpu().numpy()
+        out.copy_(self.predicted_gazemaps, non_blocking=True)
+        torch.cuda.current_stream(self.engine.device).synchronize()
+        return out
 
-    def single_step(self, train_mode=True, dataset=None):
-        """gaze_rnn.py:483-565."""
-        _start_time = time.time()
-        if dataset is None:
-            dataset = self.data_sets.train if train_mode else self.data_sets.valid
+    # ---------------------------------------------------------------- pipelined feeding (fit / benchmark loops)
+    def _get_feeder(self):
+        if self._feeder is None:
+            from ..pipeline import PrefetchFeeder
+            self._feeder = PrefetchFeeder([self.c3d_input, self.gt_gazemap], device=self.engine.device)
+        return self._feeder
+
+    def prefetch(self, batch_c3d, batch_maps, flip=None):
+        """Start uploading a host batch on the copy stream while the current step runs (double-buffered: at most two
+        batches in flight).  `acquire()` then makes it the fed batch.  Pinned inputs are read in place and must stay
+        untouched until acquire(); pageable inputs are copied through one of two pinned staging sets first."""
+        f = self._get_feeder()
+        k = f.n_prefetched % f.slots
+        if not hasattr(self, "_pf_stage"):
+            pin = self._c3d_host.is_pinned()
+            self._pf_stage = [(torch.zeros(tuple(self._c3d_host.shape), dtype=self._c3d_host.dtype, pin_memory=pin),
+                               torch.zeros(tuple(self._gt_host.shape), dtype=torch.float32, pin_memory=pin))
+                              for _ in range(f.slots)]
+            self._pf_flip = [None] * f.slots
+        f.free[k].synchronize()                      # the slot's previous upload has been consumed
+        self._pf_flip[k] = flip
+        f.prefetch(self._stage(batch_c3d, batch_maps, stage=self._pf_stage[k]))
+
+    def acquire(self):
+        """the oldest prefetched batch becomes the content of the device placeholders (+ its flip, gaze_rnn.py:504-510)"""
+        f = self._get_feeder()
+        k = f.n_acquired % f.slots
+        f.acquire()
+        if self._pf_flip[k] is not None:
+            self._flip_fed(self._pf_flip[k])
+
+    def _host_batch(self, dataset, train_mode):
+        """gaze_rnn.py:487-510: fetch, reshape, normalise the gaze maps, draw the flip (global numpy RNG, same draw)."""
         batch_images, batch_maps, batch_fixmaps, batch_c3d, batch_pupil, batch_clipnames = dataset.next_batch(self.batch_size)
         assert batch_images.dtype == np.float32
         batch_c3d = np.reshape(batch_c3d, [self.batch_size, -1, self.dim_feature, self.engine.G, self.engine.G])
         if self.config.loss_type in ('xentropy', 'KLD'):
             batch_maps = normalize_probability_map(batch_maps)
         flip = None
-        if train_mode and self.config.use_flip_batch:        # gaze_rnn.py:504-510 (global numpy RNG, same draw)
+        if train_mode and self.config.use_flip_batch:        # gaze_rnn.py:504-510
             batch_size = len(batch_images)
             flip = np.random.choice(batch_size, batch_size // 2, replace=False)
             # images and fixation maps are not consumed by the step (gaze_grcn.py:173-376 never reads the frames):
@@ -323,14 +455,30 @@ class GazePredictionGRU(ModelBase):
             if batch_images.shape[2] > 1:
                 batch_images[flip, :] = batch_images[flip, :, :, ::-1, :]
             batch_fixmaps[flip, :] = batch_fixmaps[flip, :, :, ::-1]
-        self._feed(batch_c3d, batch_maps)
-        if flip is not None:
-            self._flip_fed(flip)
-        loss = self.run(train=train_mode)
-        self.last_loss = loss
+        return batch_c3d, batch_maps, flip
+
+    def single_step(self, train_mode=True, dataset=None, _prefetched=False, _prefetch_next=False):
+        """gaze_rnn.py:483-565.  (_prefetched / _prefetch_next are fit()'s pipelining hooks: the batch of this step was
+        uploaded during the previous one / the next training batch is prepared and uploaded while this step runs.)"""
+        _start_time = time.time()
+        if dataset is None:
+            dataset = self.data_sets.train if train_mode else self.data_sets.valid
+        if _prefetched:
+            self.acquire()
+        else:
+            batch_c3d, batch_maps, flip = self._host_batch(dataset, train_mode)
+            self._feed(batch_c3d, batch_maps)
+            if flip is not None:
+                self._flip_fed(flip)
+        step = self.current_step + (1 if train_mode else 0)
+        want_log = (not train_mode) or np.mod(step, self.config.steps_per_logprint) == 0
+        self.run(train=train_mode, sync=False)               # asynchronous: the loss read stays pending
+        if _prefetch_next:
+            self.prefetch(*self._host_batch(self.data_sets.train, True))
         step = self.current_step
-        _end_time = time.time()
-        if (not train_mode) or np.mod(step, self.config.steps_per_logprint) == 0:
+        if want_log:
+            loss = self.last_loss                            # device -> host read (synchronises)
+            _end_time = time.time()
             epoch = float(step * self.batch_size) / max(1, len(self.data_sets.train))
             (log.info if train_mode else log.warning)(
                 " [%5s epoch %.1f / step %4d] %sbatch total-loss: %.5f, target-loss: %.5f "
@@ -357,13 +505,8 @@ class GazePredictionGRU(ModelBase):
             if self.config.loss_type == 'xentropy':
                 batch_maps = normalize_probability_map(batch_maps)
             self._feed(batch_c3d, batch_maps)
-            self.run(train=False)
-            gazes = self.predicted_gazemaps.cpu().numpy()
-            if self.world_size > 1:        # final gather of the shards: every rank returns all frames
-                import torch.distributed as dist
-                parts = [None] * self.world_size
-                dist.all_gather_object(parts, gazes)
-                gazes = np.concatenate(parts, axis=0)
+            self.run(train=False, sync=False)
+            gazes = self._gather_maps(self.predicted_gazemaps)
             c3ds.extend(batch_c3d)
             pred.extend(gazes)
             gts.extend(batch_maps)
@@ -380,6 +523,19 @@ class GazePredictionGRU(ModelBase):
             assert len(fixs) == len(pred)
         return {'pred_gazemap_list': pred, 'gt_gazemap_list': gts, 'images_list': images,
                 'fixationmap_list': fixs, 'clipname_list': names, 'c3d_list': c3ds}
+
+    def _gather_maps(self, maps_dev):
+        """[local clips, T, GH, GW] device maps -> NumPy maps of ALL ranks' clips in rank order (the final
+        gather of data-parallel inference): one all-gather of the device tensor into a preallocated device buffer
+        (NCCL over NVLink on GPUs) and one device->host copy — no pickling."""
+        if self.world_size == 1:
+            return maps_dev.cpu().numpy()
+        import torch.distributed as dist
+        shape = (self.world_size * maps_dev.shape[0],) + tuple(maps_dev.shape[1:])     # rank-major concatenation
+        if self._gather_buf is None or tuple(self._gather_buf.shape) != shape:
+            self._gather_buf = torch.empty(shape, dtype=maps_dev.dtype, device=maps_dev.device)
+        dist.all_gather_into_tensor(self._gather_buf, maps_dev.contiguous())
+        return self._gather_buf.cpu().numpy()
 
     def evaluate(self, pred_gazemap_list, gt_gazemap_list, fixationmap_list, images_list, **_ignored):
         """gaze_rnn.py:653-674.  (`**_ignored` absorbs the extra keys generate() returns — the reference raises a

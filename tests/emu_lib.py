@@ -14,7 +14,7 @@ import numpy as np
 from recurrent_gaze_prediction_b200 import lib as L
 
 _CT = {np.float32: C.c_float, np.float64: C.c_double, np.int32: C.c_int, np.int64: C.c_longlong,
-       np.uint8: C.c_ubyte}
+       np.uint8: C.c_ubyte, np.int16: C.c_short}
 
 
 def arr(ptr, shape, dtype=np.float32):
@@ -165,6 +165,15 @@ class EmuLib(object):
         dst[:] = src.transpose(1, 0, 3, 2)
         return 0
 
+    def rgp_pack_c3d_src(self, c3d, src_dtype, out, B, T, Cc, P, dtype, stream):
+        if src_dtype == 0:
+            return self.rgp_pack_c3d(c3d, out, B, T, Cc, P, dtype, stream)
+        import torch
+        raw = arr(c3d, (B, T, Cc, P), np.int16)                     # bf16 bit patterns
+        src = torch.from_numpy(raw.copy()).view(torch.bfloat16).float().numpy()
+        arr(out, (T, B, P, Cc))[:] = src.transpose(1, 0, 3, 2)
+        return 0
+
     def rgp_pack_emb(self, emb, out, B, T, G, Cc, dtype, stream):
         Wp = G + 1
         S = Wp * Wp
@@ -305,6 +314,21 @@ class EmuLib(object):
         V[:] = b2 * V + (1 - b2) * gg * gg
         P[:] = P - lr_t * Mm / (np.sqrt(V) + eps)
         return 0
+
+    def rgp_adam_schedule(self, step, lr0, decay, decay_steps, b1, b2, sched, stream):
+        st = arr(step, (1,), np.int64)
+        s0 = int(st[0])
+        lr = float(arr(lr0, (1,), np.float64)[0]) * decay ** (s0 // decay_steps)
+        t = s0 + 1
+        out = arr(sched, (2,))
+        out[0] = lr * math.sqrt(1.0 - b2 ** t) / (1.0 - b1 ** t)
+        out[1] = lr
+        st[0] = t
+        return 0
+
+    def rgp_gradnorm_clip_adam_dev(self, p, g, m, v, n, sumsq, clip, lr_t_dev, b1, b2, eps, p_op, dtype, stream):
+        return self.rgp_gradnorm_clip_adam(p, g, m, v, n, sumsq, clip, float(arr(lr_t_dev, (1,))[0]), b1, b2, eps, p_op,
+                                           dtype, stream)
 
     # -------------------------------------------------------------- BPTT
     def rgp_wgrad(self, aref, stream):
