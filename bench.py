@@ -7,8 +7,11 @@ Default workload = BASELINE.json configs[1]: gaze_grcn inference, 256 clips x T=
 hidden 256, bf16 operands / fp32 accumulate, synthetic C3D conv5b features [B,T,1024,7,7] and
 random-init weights (reference init).  A "step" is one forward pass of the whole hot path
 (pack -> projection -> input convs -> T recurrent steps -> composed head -> softmax+loss) over one batch.
-`value`: inputs resident in HBM.  `e2e`: through the model-class API with pinned HOST buffers, H2D of the
-features + gt and D2H of the gaze maps + loss inside the timed region.
+Both numbers go THROUGH THE MODEL CLASS (models/gaze_grcn.py GazePredictionGRCN): `value` = model.run() on resident
+placeholders; `e2e` = model.prefetch / acquire / run from pinned HOST tensors, H2D of the features + gt and D2H of the
+gaze maps + loss inside the timed region.  The default (no flags) line also carries the sub-records `train` (config 3's
+per-GPU share: fwd + BPTT + NCCL all-reduce + clip + Adam, 128 clips/GPU), `config4` (gaze_lstm 14x14 T=128) and
+`metrics` (saliency suite at 360x480).
 `--impl reference`: the oracle's torch-CPU fp32 restatement of the reference graph (TensorFlow 1 cannot be
 installed here) on the host cores, a bounded sample of the same workload per step.
 """
@@ -54,7 +57,12 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel from the host instead of one CUDA graph")
-    ap.add_argument("--cpu-clips", type=int, default=2)
+    ap.add_argument("--cpu-clips", type=int, default=0, help="clips per CPU pass (0: sized to fill the host cores)")
+    ap.add_argument("--features", default="bf16", choices=["bf16", "fp32"],
+                    help="dtype of the fed host features of the headline e2e (results are bit-identical; the fp32-fed e2e is "
+                         "reported beside it)")
+    ap.add_argument("--train-batch", type=int, default=128, help="clips per GPU of the `train` sub-record (config 3)")
+    ap.add_argument("--no-sub", action="store_true", help="headline record only (no train / config4 / metrics sub-records)")
     ap.add_argument("--entry", default="c3d", choices=["c3d", "emb"],
                     help="c3d: reference entry [B,T,1024,G,G]; emb: already-projected features [B,T,G,G,512] (SURVEY 8d 'L1')")
     ap.add_argument("--head", default=None, choices=["deconv", "fc"], help="gaze-map head (default: the model's own)")
@@ -196,13 +204,21 @@ def use_all_host_threads():
     return torch.get_num_threads()
 
 
+def cpu_sample_clips(args, cores):
+    """clips per CPU pass: enough frames per conv call to occupy every core (one clip per two threads, at least 8)"""
+    return args.cpu_clips if args.cpu_clips > 0 else max(8, min(32, cores // 2))
+
+
 def run_reference(args, rank, world):
+    """--impl reference: the reference's own CPU implementation of the path.  TensorFlow 1 is not installable here
+    (DESIGN.md section 0), so this is the oracle's torch-CPU fp32 restatement of the reference graph (kind "port"), on all
+    host threads, each step a bounded sample of the workload."""
     if rank != 0:
         return
-    use_all_host_threads()
+    cores = use_all_host_threads()
     from oracle import model_oracle as O
     from recurrent_gaze_prediction_b200 import synthetic as SY
-    B = args.cpu_clips
+    B = cpu_sample_clips(args, cores)
     p = O.init_params(args.model, hidden=args.hidden, T=args.T, grid=args.grid, seed=0, regime="R")
     rng = np.random.RandomState(0)
     c3d = SY.make_c3d(rng, B, args.T, 1024, args.grid)
@@ -216,14 +232,13 @@ def run_reference(args, rank, world):
         cpu_reference_step(args.model, p, c3d, gt, train)
     dt = (time.perf_counter() - t0) / args.steps
     fps = B * args.T / dt
-    cores = torch.get_num_threads()
-    sample = "%d clips x T=%d per step (bounded sample of the %d-clip workload), torch-CPU fp32 restatement of the " \
-             "reference graph (oracle/model_oracle.py), %d threads of %d cores" % (B, args.T, args.batch, cores,
-                                                                                 os.cpu_count())
+    sample = "each step = %d clips x T=%d (a bounded sample of the %d-clip workload named in config; frames/s normalises " \
+             "the size), torch-CPU fp32 restatement of the reference graph (oracle/model_oracle.py; TF1 not installable), " \
+             "%d threads of %d cores" % (B, args.T, args.batch, cores, os.cpu_count())
     out = {"impl": "reference", "metric": metric_name(args), "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-           "config": workload_config(args),
+           "config": workload_config(args), "sample_clips_per_step": B,
            "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample},
            "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(out))
@@ -247,6 +262,247 @@ def workload_config(args):
 
 
 # ----------------------------------------------------------------------------------------------
+class Harness(object):
+    """timing plumbing shared by the records: barrier + synchronize on both sides, CUDA events on the launching stream,
+    max over ranks"""
+
+    def __init__(self, dev, local, rank, world):
+        self.dev, self.local, self.rank, self.world = dev, local, rank, world
+
+    def barrier(self):
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(self, fn, steps, warmup, lib=None, per_replay=0, sample_clocks=False):
+        cs = ClockSampler(self.local) if sample_clocks else None
+        if cs:
+            cs.start()
+        for _ in range(warmup):
+            fn()
+        self.barrier()
+        if cs:
+            cs.mark()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = lib.launches if lib is not None else 0
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        self.barrier()
+        ms = e0.elapsed_time(e1)
+        clocks = cs.stop() if cs else None
+        t = torch.tensor([ms], device=self.dev)
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        launches = (lib.launches - l0 if lib is not None else 0) + per_replay * steps
+        return float(t[0]) / steps, clocks, launches
+
+
+def make_inputs(rank, B, T, G, GH, feature_dtype=torch.float32, emb=False):
+    """synthetic inputs: a small pool tiled to the batch (host RNG cost), distinct per rank; pinned host tensors"""
+    from recurrent_gaze_prediction_b200 import synthetic as SY
+    rng = np.random.RandomState(1234 + rank)
+    pool = min(B, 8)
+    feat_pool = SY.make_embedded(rng, pool, T, G, 512) if emb else SY.make_c3d(rng, pool, T, 1024, G)
+    gt_pool, _ = SY.make_gazemaps(rng, pool, T, GH, GH, normalize=True)
+    reps = (B + pool - 1) // pool
+    feat = torch.from_numpy(np.tile(feat_pool, (reps,) + (1,) * (feat_pool.ndim - 1))[:B])
+    gt = torch.from_numpy(np.tile(gt_pool, (reps, 1, 1, 1))[:B])
+    return feat.to(feature_dtype).pin_memory(), gt.pin_memory(), feat_pool, gt_pool
+
+
+def build_model(args, session, B_local, world, train, feature_dtype, dev):
+    """the reference-facing model class (models/gaze_grcn.py etc.) at the bench size, random-init (reference initialisers)"""
+    from recurrent_gaze_prediction_b200.models import train_gaze
+    TheModel, _, GRUModelConfig = train_gaze.get_model_class(args.model)
+    c = GRUModelConfig()
+    c.batch_size, c.n_lstm_steps, c.rnn_state_size, c.grid = B_local * world, args.T, args.hidden, args.grid
+    c.dtype, c.device, c.trainable = args.dtype, str(dev), train
+    c.feature_dtype = feature_dtype
+    c.cuda_graph = not args.no_graph
+    c.use_flip_batch = False
+    return TheModel(session, None, c)
+
+
+def bench_model_record(args, H, session, mode, B, feature_dtype="bf16", with_roofline=False, sample_clocks=False,
+                       also_fp32_e2e=False):
+    """One record (value / ms_per_step / e2e / gpu_launches [/ roofline]) of `mode` at B clips per GPU, THROUGH THE MODEL
+    CLASS: `value` = model.run() on resident placeholders (one CUDA-graph submission per step), `e2e` = the public
+    pipelined feed (model.prefetch -> acquire -> run) from pinned host tensors + device->host read of the result."""
+    import torch.distributed as dist
+    train = mode == "train"
+    dev, world, rank = H.dev, H.world, H.rank
+    T, G, Ch = args.T, args.grid, args.hidden
+    model = build_model(args, session, B, world, train, feature_dtype, dev)
+    eng = model.engine
+    fdt = torch.bfloat16 if feature_dtype == "bf16" else torch.float32
+    feat_h, gt_h, feat_pool, gt_pool = make_inputs(rank, B, T, G, eng.GH, fdt)
+    # global-batch host tensors are what the model API takes; every rank feeds its own shard: build the shard view
+    model.c3d_input.copy_(feat_h)
+    model.gt_gazemap.copy_(gt_h)
+    probs_h = torch.empty(B, T, eng.GH, eng.GH, dtype=torch.float32).pin_memory()
+
+    def step_resident():
+        model.run(train=train, sync=False)
+
+    step_resident()                                   # builds the step graph (undone for train: no update is kept)
+    torch.cuda.synchronize()
+    per_replay = 0
+    if model._use_graph():
+        per_replay = model._step_graph(train).kernels
+    ms_step, clocks, launches = H.timed(step_resident, args.steps, args.warmup, lib=eng.lib, per_replay=per_replay,
+                                        sample_clocks=sample_clocks)
+    frames = B * T * world
+    rec = {"value": frames / (ms_step * 1e-3), "unit": "frames/s", "ms_per_step": ms_step, "clips_per_gpu": B,
+           "gpu_launches": launches, "submission": "cuda-graph" if model._use_graph() else "eager",
+           "api": "models.%s: run() on resident placeholders" % type(model).__name__}
+    if clocks is not None:
+        rec["clocks"] = clocks
+
+    # ---- allreduce share of the training step (device time of the NCCL call, events on the launching stream)
+    if train and world > 1:
+        sg = model._step_graph(True)
+        evs = []
+
+        def step_timed_ar():
+            sg.g1.replay()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            sg.allreduce(eng.grads)
+            b.record()
+            sg.g2.replay()
+            eng.note_replayed_steps(1)
+            evs.append((a, b))
+        for _ in range(2):
+            step_timed_ar()
+        H.barrier()
+        evs.clear()
+        for _ in range(max(4, args.steps)):
+            step_timed_ar()
+        H.barrier()
+        ar = torch.tensor([float(np.mean([a.elapsed_time(b) for a, b in evs]))], device=dev)
+        dist.all_reduce(ar, op=dist.ReduceOp.MAX)
+        rec["allreduce_ms"] = float(ar[0])
+        rec["allreduce_bytes"] = int(eng.nparams) * 4
+        rec["allreduce_share_of_step"] = float(ar[0]) / ms_step
+
+    # ---- end to end through the public pipelined feed
+    def e2e_of(m, fg, gg):
+        fh, gh = fg, gg                        # every rank feeds its own shard of the global batch (local=True)
+
+        def step_e2e():
+            m.prefetch(fg, gg, local=True)     # upload of the next batch starts on the copy stream
+            m.acquire()                        # the oldest uploaded batch becomes the fed batch
+            m.run(train=train, sync=False)     # fwd (+BPTT+clip/Adam); the loss read is queued
+            if not train:
+                probs_h.copy_(m.predicted_gazemaps, non_blocking=True)
+        m.prefetch(fg, gg, local=True)         # pipeline prologue
+        ms, _, _ = H.timed(step_e2e, max(4, args.steps), 2)
+        m._get_feeder().drain()
+        _ = m.last_loss
+        h2d = fh.numel() * fh.element_size() + gh.numel() * 4
+        d2h = (0 if train else probs_h.numel() * 4) + 4
+        return {"value": frames / (ms * 1e-3), "unit": "frames/s", "ms_per_step": ms,
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "feeding": "models.%s.prefetch/acquire/run: double-buffered H2D of pinned host %s features + fp32 gaze maps "
+                           "on a copy stream, result read back to pinned host memory" % (type(m).__name__, str(fh.dtype).split(".")[-1])}
+
+    if not args.no_e2e:
+        rec["e2e"] = e2e_of(model, feat_h, gt_h)
+        if also_fp32_e2e and feature_dtype != "fp32":
+            m32 = build_model(args, session, B, world, train, "fp32", dev)
+            f32_h = feat_h.float().pin_memory()
+            rec["e2e_fp32_features"] = e2e_of(m32, f32_h, gt_h)
+            # the synchronous single call a reference user would write: predict(host batch) -> host maps
+            if not train:
+                sync_ms, _, _ = H.timed(lambda: m32.predict(f32_h, out=probs_h, local=True), max(4, args.steps), 2)
+                rec["e2e_sync_predict_fp32"] = {"value": frames / (sync_ms * 1e-3), "unit": "frames/s", "ms_per_step": sync_ms,
+                                                "api": "model.predict(pinned fp32 batch, out=pinned maps), no pipelining"}
+            del m32
+            torch.cuda.empty_cache()
+
+    # ---- roofline of the dominant kernel + stage breakdown
+    if with_roofline and rank == 0:
+        hbm, tf_burst, tf_sus, which = peaks()
+        fl = flops_per_frame(Ch, G, lstm=eng.lstm)
+        evs = eng.time_stages(model.c3d_input, model.gt_gazemap, iters=3)
+        i2h_ms = evs["i2h"]
+        ach = fl["i2h"] * B * T / (i2h_ms * 1e-3) / 1e12
+        default_cfg = (args.model, B, T, Ch, G, args.dtype) == ("gaze_grcn", 256, 35, 256, 7, "bf16")
+        # the stage timings are isolated launches (3 iterations at boost clocks): the BURST peak is their denominator;
+        # the fraction against the sustained peak is printed beside it
+        roof = {"kernel": "tapgemm i2h (3x3 SAME conv, all T frames, M=%d N=%d K=9x512)" % (T * B * eng.S, eng.ngx * Ch),
+                "bound": "tensor", "achieved": ach, "peak": tf_burst, "unit": "TFLOP/s", "frac": ach / tf_burst,
+                "frac_of_sustained_peak": ach / tf_sus,
+                "peak_source": which + " (burst bf16 %.1f: kernel timed alone; sustained %.1f)" % (tf_burst, tf_sus),
+                "traffic": TRAFFIC.get("i2h") if default_cfg else None,
+                "traffic_source": TRAFFIC.get("i2h_source") if default_cfg else None,
+                "ms_per_launch": i2h_ms, "stage_ms": evs}
+        rec_ms = evs["recurrence"]
+        rec_bytes = 4.0 * Ch * G * G * 4 * B * T
+        roof["recurrence"] = {
+            "kernel": ("gru_seq (persistent ConvGRU recurrence, all T steps in one launch)" if eng.use_seq else
+                       "per-step tap-GEMMs (%d launches)" % (2 * T)),
+            "ms": rec_ms, "tensor_TFLOPs": fl["h2h"] * B * T / (rec_ms * 1e-3) / 1e12,
+            "tensor_frac": fl["h2h"] * B * T / (rec_ms * 1e-3) / 1e12 / tf_burst,
+            "tensor_frac_of_sustained_peak": fl["h2h"] * B * T / (rec_ms * 1e-3) / 1e12 / tf_sus,
+            "hbm_GBps": rec_bytes / (rec_ms * 1e-3) / 1e9, "hbm_frac": rec_bytes / (rec_ms * 1e-3) / 1e9 / hbm,
+            "traffic": TRAFFIC.get("gru_seq") if (default_cfg and eng.use_seq) else None}
+        if train:
+            eng.forward(c3d=model.c3d_input, gt=model.gt_gazemap, global_batch=B * world)
+            snap = eng.snapshot_train_state()
+            roof["stage_ms_bwd"] = eng.time_backward(iters=3)
+            eng.restore_train_state(snap)
+        rec["roofline"] = roof
+        rec["step_tflops"] = sum(fl.values()) * B * T / (ms_step * 1e-3) / 1e12 * (3.0 if train else 1.0)
+    rec["_pools"] = (feat_pool, gt_pool)
+    rec["_params"] = None
+    del model
+    torch.cuda.empty_cache()
+    return rec
+
+
+# DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum) from the committed `ncu --set full` captures of
+# exactly the default configuration (profiles/); None for any other configuration
+TRAFFIC = {"i2h": 2.3048e9,
+           "i2h_source": "profiles/r01_ncu_full_fwd_pass17.txt (0.595 GB read + 1.710 GB written per launch)",
+           "gru_seq": 3.5349e9}
+
+
+def bench_config4(args, H):
+    """BASELINE config 4: gaze_lstm, 14x14 grid, T = 128, hidden 128, embedded-feature entry [B,T,14,14,512], per-position
+    FC head, inference at 8 and 64 clips (one GPU).  Engine-level: the model classes take the reference's C3D 7x7 entry
+    only; 14x14 is reachable through the cell's spatial_shape."""
+    from recurrent_gaze_prediction_b200.engine import GazeEngine, StepGraph
+    from recurrent_gaze_prediction_b200.models.model_util import init_parameters
+    out = {"workload": "gaze_lstm inference, T=128, 14x14 grid, embedded features 512x14x14, hidden 128, per-position FC head",
+           "api": "GazeEngine.forward(emb=...) as one CUDA graph", "n_gpus": 1}
+    T, G, Ch = 128, 14, 128
+    p = dict(init_parameters("gaze_lstm", hidden=Ch, T=T, grid=G, seed=0))
+    p["out_W"] = np.random.RandomState(7).uniform(-0.1, 0.1, (Ch, 1)).astype(np.float32)
+    hbm, tf_burst, tf_sus, _ = peaks()
+    fl = flops_per_frame(Ch, G, lstm=True)
+    for B in (8, 64):
+        eng = GazeEngine("gaze_lstm", B=B, T=T, G=G, Ch=Ch, dtype=1, device=H.dev, head="fc")
+        eng.load_tf_params(p)
+        feat_h, gt_h, _, _ = make_inputs(0, B, T, G, G, emb=True)
+        emb_d, gt_d = feat_h.to(H.dev), gt_h.to(H.dev)
+        sg = StepGraph(eng, lambda: eng.forward(emb=emb_d, gt=gt_d))
+        ms, _, _ = H.timed(sg.replay, max(3, args.steps // 2), 3)
+        st = eng.time_stages(emb_d, gt_d, iters=2, emb=True)
+        out["B%d" % B] = {"value": B * T / (ms * 1e-3), "unit": "frames/s", "ms_per_step": ms, "gpu_launches_per_step": sg.kernels,
+                          "stage_ms": st, "persistent_recurrence": bool(getattr(eng, "use_seq_lstm", False)),
+                          "recurrence_tensor_frac": fl["h2h"] * B * T / (st["recurrence"] * 1e-3) / 1e12 / tf_burst,
+                          "i2h_tensor_frac": fl["i2h"] * B * T / (st["i2h"] * 1e-3) / 1e12 / tf_burst}
+        del eng, sg, emb_d, gt_d
+        torch.cuda.empty_cache()
+    return out
+
+
+# ----------------------------------------------------------------------------------------------
 def main():
     args = parse()
     rank = int(os.environ.get("RANK", "0"))
@@ -256,179 +512,59 @@ def main():
         run_reference(args, rank, world)
         return
     import torch.distributed as dist
-    from recurrent_gaze_prediction_b200 import synthetic as SY
-    from recurrent_gaze_prediction_b200.models.model_util import init_parameters
-    from recurrent_gaze_prediction_b200.engine import GazeEngine
-    from recurrent_gaze_prediction_b200 import lib as L
+    from recurrent_gaze_prediction_b200 import numa
 
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa_info = numa.bind_to_gpu_node(local) if world > 1 else {"node": None, "note": "single rank: not bound"}
+    session = {"rank": rank, "world_size": world, "allreduce": None}
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-    B, T, G, Ch = args.batch, args.T, args.grid, args.hidden
-    dtype = 1 if args.dtype == "bf16" else 0
-    train = args.mode == "train"
-    p = init_parameters(args.model, hidden=Ch, T=T, grid=G, seed=0)      # the reference's initialisers
-    eng = GazeEngine(args.model, B=B, T=T, G=G, Ch=Ch, dtype=dtype, device=dev, train=train, head=args.head)
-    if eng.head == "fc" and np.asarray(p["out_W"]).size != Ch:   # per-position FC head on a model whose own head is the deconv chain
-        p = dict(p)
-        p["out_W"] = np.random.RandomState(7).uniform(-0.1, 0.1, (Ch, 1)).astype(np.float32)
-    eng.load_tf_params(p)
-    GH = eng.GH
-    # synthetic inputs: a small pool tiled to the batch (host RNG cost), distinct per rank
-    rng = np.random.RandomState(1234 + rank)
-    pool = min(B, 8)
-    emb_entry = args.entry == "emb"
-    c3d_pool = SY.make_embedded(rng, pool, T, G, 512) if emb_entry else SY.make_c3d(rng, pool, T, 1024, G)
-    gt_pool, _ = SY.make_gazemaps(rng, pool, T, GH, GH, normalize=True)
-    reps = (B + pool - 1) // pool
-    c3d_h = torch.from_numpy(np.tile(c3d_pool, (reps, 1, 1, 1, 1))[:B]).pin_memory()
-    gt_h = torch.from_numpy(np.tile(gt_pool, (reps, 1, 1, 1))[:B]).pin_memory()
-    c3d_d, gt_d = c3d_h.to(dev), gt_h.to(dev)
-    probs_h = torch.empty(B, T, GH, GH, dtype=torch.float32).pin_memory()
-    loss_h = torch.empty(1, dtype=torch.float32).pin_memory()
+        session["allreduce"] = lambda t: dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    H = Harness(dev, local, rank, world)
+    if args.entry == "emb" or args.head is not None:
+        return main_engine_level(args, H, session)
 
-    allreduce = (lambda t: dist.all_reduce(t, op=dist.ReduceOp.SUM)) if world > 1 else None
+    # ---- headline record: the mode asked for (default: inference = BASELINE config 2)
+    head = bench_model_record(args, H, session, args.mode, args.batch, feature_dtype=args.features, with_roofline=True,
+                              sample_clocks=(rank == 0), also_fp32_e2e=True)
+    feat_pool, gt_pool = head.pop("_pools")
+    head.pop("_params")
 
-    def fwd():
-        if emb_entry:
-            eng.forward(emb=c3d_d, gt=gt_d, global_batch=B * world)
-        else:
-            eng.forward(c3d=c3d_d, gt=gt_d, global_batch=B * world)
-
-    def fwd_bwd():
-        fwd()
-        if train:
-            eng.backward()
-
-    def opt():
-        # data parallel: ONE NCCL all-reduce (sum) of the flat fp32 gradient, then the global-norm clip + TF-Adam
-        # identically on every rank (base.py:287-297: the norm is over the GLOBAL gradient)
-        eng.optimizer_step(allreduce=allreduce)
-
-    def step_eager():
-        fwd_bwd()
-        if train:
-            opt()
-
-    graph, per_replay, graph2 = None, 0, None
-    if not args.no_graph:
-        if train and world > 1:      # the collective stays outside the captured region: fwd+BPTT graph, all-reduce, Adam graph
-            graph, per_replay = eng.make_graph(fwd_bwd)
-            allreduce, keep = None, allreduce
-            graph2, n2 = eng.make_graph(opt)
-            allreduce = keep
-            per_replay += n2
-        else:
-            graph, per_replay = eng.make_graph(step_eager)
-
-    def step_resident():
-        if graph is None:
-            step_eager()
-        elif graph2 is not None:
-            graph.replay()
-            dist.all_reduce(eng.grads, op=dist.ReduceOp.SUM)
-            graph2.replay()
-        else:
-            graph.replay()
-
-    from recurrent_gaze_prediction_b200.pipeline import PrefetchFeeder
-    feeder = PrefetchFeeder([c3d_d, gt_d], device=dev)
-
-    def step_e2e():
-        # every step uploads one batch of pinned HOST features + gt (copy stream, overlapping the previous step's
-        # kernels), runs the pass, and reads the gaze maps / loss back to pinned host memory
-        feeder.prefetch([c3d_h, gt_h])
-        feeder.acquire()
-        step_resident()
-        if not train:
-            probs_h.copy_(eng.probs, non_blocking=True)
-        loss_h.copy_(eng.loss, non_blocking=True)
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def timed(fn, steps, warmup, sample_clocks=False):
-        cs = ClockSampler(local) if sample_clocks else None
-        if cs:
-            cs.start()
-        for _ in range(warmup):
-            fn()
-        barrier()
-        if cs:
-            cs.mark()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        l0 = eng.lib.launches
-        if graph is not None:
-            l0 -= per_replay * steps
-        e0.record()
-        for _ in range(steps):
-            fn()
-        e1.record()
-        barrier()
-        ms = e0.elapsed_time(e1)
-        clocks = cs.stop() if cs else None
-        t = torch.tensor([ms], device=dev)
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t[0]) / steps, clocks, (eng.lib.launches - l0)
-
-    ms_step, clocks, launches = timed(step_resident, args.steps, args.warmup, sample_clocks=(rank == 0))
-    frames = B * T * world
-    value = frames / (ms_step * 1e-3)
-    e2e = None
-    if not args.no_e2e:
-        feeder.prefetch([c3d_h, gt_h])        # pipeline prologue: step i consumes the batch uploaded during step i-1
-        ms_e2e, _, _ = timed(step_e2e, max(4, args.steps), 2)
-        feeder.drain()
-        h2d = c3d_h.numel() * 4 + gt_h.numel() * 4
-        d2h = (0 if train else probs_h.numel() * 4) + 4
-        e2e = {"value": frames / (ms_e2e * 1e-3), "unit": "frames/s", "ms_per_step": ms_e2e, "feeding": "double-buffered H2D on a copy stream (PrefetchFeeder)",
-               "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h}
-
-    # roofline of the dominant kernel: the input-half conv GEMM (all T frames at once), timed live with CUDA events
-    hbm, tf_burst, tf_sus, which = peaks()
-    fl = flops_per_frame(Ch, G, lstm=eng.lstm)
-    roof = None
-    if rank == 0:
-        evs = eng.time_stages(c3d_d, gt_d, iters=3, emb=emb_entry)
-        i2h_ms = evs["i2h"]
-        ach = fl["i2h"] * B * T / (i2h_ms * 1e-3) / 1e12
-        # DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum) from the committed ncu --set full captures
-        # of exactly this configuration; None for any other configuration
-        default_cfg = (args.model, B, T, Ch, G, args.entry, dtype) == ("gaze_grcn", 256, 35, 256, 7, "c3d", 1)
-        roof = {"kernel": "tapgemm i2h (3x3 SAME conv, all T frames, M=%d N=%d K=9x512)" % (T * B * eng.S, eng.ngx * Ch),
-                "bound": "tensor", "achieved": ach, "peak": tf_sus, "unit": "TFLOP/s", "frac": ach / tf_sus,
-                "peak_source": which + " (sustained bf16; burst %.1f)" % tf_burst,
-                "traffic": 2.3048e9 if default_cfg else None,
-                "traffic_source": "profiles/r01_ncu_full_fwd_pass17.txt (0.595 GB read + 1.710 GB written per launch)" if default_cfg else None,
-                "ms_per_launch": i2h_ms, "stage_ms": evs}
-        # second view: the recurrence (persistent kernel when the engine picked it).  Algorithmic work per frame
-        # (SURVEY 8d): 2*3*(3G-2)^2*Ch^2 flop; bytes = read 3 gate pre-activations + write h, fp32
-        rec_ms = evs["recurrence"]
-        rec_bytes = 4.0 * Ch * G * G * 4 * B * T
-        rec = {"kernel": ("gru_seq (persistent ConvGRU recurrence, all T steps in one launch)" if eng.use_seq else
-                          "per-step tap-GEMMs (%d launches)" % (2 * T)),
-               "ms": rec_ms, "tensor_TFLOPs": fl["h2h"] * B * T / (rec_ms * 1e-3) / 1e12,
-               "tensor_frac": fl["h2h"] * B * T / (rec_ms * 1e-3) / 1e12 / tf_sus,
-               "hbm_GBps": rec_bytes / (rec_ms * 1e-3) / 1e9, "hbm_frac": rec_bytes / (rec_ms * 1e-3) / 1e9 / hbm,
-               "traffic": 3.5349e9 if (default_cfg and eng.use_seq) else None}
-        roof["recurrence"] = rec
-        if train:
-            fwd()
-            roof["stage_ms_bwd"] = eng.time_backward(iters=3)
+    sub = {}
+    if args.mode == "inference" and not args.no_sub:
+        # BASELINE.json's metric is "fwd & train": the training half (config 3's per-GPU share, 128 clips/GPU, with the
+        # NCCL all-reduce of the flat gradient when N > 1) rides in the same line, then config 4 and the metric suite
+        targs = argparse.Namespace(**vars(args))
+        targs.mode, targs.batch = "train", args.train_batch
+        tr = bench_model_record(targs, H, session, "train", args.train_batch, feature_dtype=args.features, with_roofline=True)
+        tr.pop("_pools"), tr.pop("_params")
+        tr["metric"] = metric_name(targs)
+        tr["config"] = workload_config(targs)
+        sub["train"] = tr
+        if rank == 0:
+            try:
+                sub["config4"] = bench_config4(args, H)
+            except Exception as e:       # a sub-record must not take the headline down
+                sub["config4"] = {"error": "%s: %s" % (type(e).__name__, e)}
+            try:
+                sys.path.insert(0, os.path.join(ROOT, "tools"))
+                import bench_metrics
+                sub["metrics"] = bench_metrics.run(1024, cpu_frames=2)
+            except Exception as e:
+                sub["metrics"] = {"error": "%s: %s" % (type(e).__name__, e)}
+        H.barrier()
 
     cpu = None
     if rank == 0 and not args.no_cpu_baseline:
-        nb = args.cpu_clips
-        pc = p
-        if emb_entry:
-            raise SystemExit("--entry emb has no CPU reference leg: pass --no-cpu-baseline")
-        c3 = c3d_pool[:nb]
-        g = gt_pool[:nb]
-        use_all_host_threads()
+        from recurrent_gaze_prediction_b200.models.model_util import init_parameters
+        cores = use_all_host_threads()
+        nb = cpu_sample_clips(args, cores)
+        reps = (nb + len(feat_pool) - 1) // len(feat_pool)
+        c3 = np.tile(feat_pool, (reps, 1, 1, 1, 1))[:nb]
+        g = np.tile(gt_pool, (reps, 1, 1, 1))[:nb]
+        pc = init_parameters(args.model, hidden=args.hidden, T=args.T, grid=args.grid, seed=0)
+        train = args.mode == "train"
         cpu_reference_step(args.model, pc, c3, g, train)
         t0 = time.perf_counter()
         n = 0
@@ -436,16 +572,78 @@ def main():
             cpu_reference_step(args.model, pc, c3, g, train)
             n += 1
         dt = (time.perf_counter() - t0) / n
-        cpu = {"value": nb * T / dt, "unit": "frames/s", "cores": torch.get_num_threads(), "kind": "port",
+        cpu = {"value": nb * args.T / dt, "unit": "frames/s", "cores": torch.get_num_threads(), "kind": "port",
                "sample": "%d clips x T=%d per pass, %d passes, torch-CPU fp32 restatement of the reference graph "
-                         "(oracle/model_oracle.py; TF1 not installable)" % (nb, T, n)}
+                         "(oracle/model_oracle.py; TF1 not installable)" % (nb, args.T, n)}
     if rank == 0:
-        out = {"metric": metric_name(args), "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
-               "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
-               "vs_baseline": None, "dtype": args.dtype, "data": "synthetic", "config": dict(workload_config(args), submission="eager" if graph is None else "cuda-graph"),
-               "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu,
-               "step_tflops": sum(fl.values()) * B * T / (ms_step * 1e-3) / 1e12}
+        out = {"metric": metric_name(args), "value": head["value"], "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+               "warmup": args.warmup, "ms_per_step": head["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+               "vs_baseline": None, "dtype": args.dtype, "data": "synthetic", "config": workload_config(args),
+               "submission": head["submission"], "api": head["api"],
+               "clocks": head.get("clocks"), "e2e": head.get("e2e"), "e2e_fp32_features": head.get("e2e_fp32_features"),
+               "e2e_sync_predict_fp32": head.get("e2e_sync_predict_fp32"),
+               "gpu_launches": head["gpu_launches"], "roofline": head.get("roofline"), "cpu_baseline": cpu,
+               "step_tflops": head.get("step_tflops"), "numa": numa_info}
+        if "allreduce_ms" in head:
+            out.update({k: head[k] for k in ("allreduce_ms", "allreduce_bytes", "allreduce_share_of_step")})
+        out.update(sub)
         print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main_engine_level(args, H, session):
+    """--entry emb / --head: shapes the model classes do not expose (embedded-feature entry, 14x14 grids, FC head on a
+    deconv model) timed on the engine directly — the round-1 harness, kept for the config-4 family and A/B runs."""
+    import torch.distributed as dist
+    from recurrent_gaze_prediction_b200.engine import GazeEngine, StepGraph
+    from recurrent_gaze_prediction_b200.models.model_util import init_parameters
+    rank, world, dev = H.rank, H.world, H.dev
+    B, T, G, Ch = args.batch, args.T, args.grid, args.hidden
+    dtype = 1 if args.dtype == "bf16" else 0
+    train = args.mode == "train"
+    p = init_parameters(args.model, hidden=Ch, T=T, grid=G, seed=0)
+    eng = GazeEngine(args.model, B=B, T=T, G=G, Ch=Ch, dtype=dtype, device=dev, train=train, head=args.head)
+    if eng.head == "fc" and np.asarray(p["out_W"]).size != Ch:
+        p = dict(p)
+        p["out_W"] = np.random.RandomState(7).uniform(-0.1, 0.1, (Ch, 1)).astype(np.float32)
+    eng.load_tf_params(p)
+    emb_entry = args.entry == "emb"
+    feat_h, gt_h, _, _ = make_inputs(rank, B, T, G, eng.GH, emb=emb_entry)
+    feat_d, gt_d = feat_h.to(dev), gt_h.to(dev)
+    fwd = (lambda: eng.forward(emb=feat_d, gt=gt_d, global_batch=B * world)) if emb_entry else \
+        (lambda: eng.forward(c3d=feat_d, gt=gt_d, global_batch=B * world))
+    if args.no_graph:
+        def step():
+            fwd()
+            if train:
+                eng.backward()
+                eng.optimizer_step(allreduce=session["allreduce"])
+        per_replay = 0
+    else:
+        sg = StepGraph(eng, fwd, train=train, allreduce=session["allreduce"] if train else None, opt={})
+        step, per_replay = sg.replay, sg.kernels
+    ms_step, clocks, launches = H.timed(step, args.steps, args.warmup, lib=eng.lib, per_replay=per_replay,
+                                        sample_clocks=(rank == 0))
+    frames = B * T * world
+    if rank == 0:
+        st = eng.time_stages(feat_d, gt_d, iters=3, emb=emb_entry)
+        hbm, tf_burst, tf_sus, which = peaks()
+        fl = flops_per_frame(Ch, G, lstm=eng.lstm)
+        roof = {"kernel": "tapgemm i2h", "bound": "tensor", "achieved": fl["i2h"] * B * T / (st["i2h"] * 1e-3) / 1e12,
+                "peak": tf_burst, "unit": "TFLOP/s", "traffic": None, "stage_ms": st}
+        roof["frac"] = roof["achieved"] / tf_burst
+        if train:
+            fwd()
+            snap = eng.snapshot_train_state()
+            roof["stage_ms_bwd"] = eng.time_backward(iters=3)
+            eng.restore_train_state(snap)
+        print(json.dumps({"metric": metric_name(args), "value": frames / (ms_step * 1e-3), "unit": "frames/s", "n_gpus": world,
+                          "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
+                          "scaling": "weak", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
+                          "config": workload_config(args), "submission": "eager" if args.no_graph else "cuda-graph",
+                          "api": "GazeEngine (engine level)", "clocks": clocks, "e2e": None, "gpu_launches": launches,
+                          "roofline": roof, "cpu_baseline": None}))
     if world > 1:
         dist.destroy_process_group()
 

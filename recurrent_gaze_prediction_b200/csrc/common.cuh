@@ -12,6 +12,21 @@ namespace rgp {
 void set_error(const char* fmt, ...);
 int check_launch(const char* what);
 
+// Per-DEVICE one-time setup (cudaFuncSetAttribute is a per-device attribute; the SM count and the occupancy of a
+// cluster shape differ per device): a flag / value slot per device ordinal of the calling thread's current device.
+constexpr int kMaxDevices = 64;
+inline int current_device() {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  return (dev >= 0 && dev < kMaxDevices) ? dev : 0;
+}
+struct PerDeviceFlag {
+  volatile char done[kMaxDevices];
+  // true when this device still needs its setup (idempotent setup: a racing second thread merely repeats it)
+  bool need() const { return !done[current_device()]; }
+  void set() { done[current_device()] = 1; }
+};
+
 #define RGP_CHECK_ARG(cond, ...)                 \
   do {                                           \
     if (!(cond)) {                               \

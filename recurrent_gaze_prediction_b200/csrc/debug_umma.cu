@@ -5,6 +5,9 @@
 // is then issued with the A descriptor's start address = slab + off*128 (+ k*32 per K16 step) and the descriptor's
 // base-offset field (bits 49-51) = mode ? ((start >> 7) & 7) : 0.  The host compares D with a CPU product
 // (tools/umma_rowoff_probe.py).  Not part of the product path; not declared in include/rgp.h.
+// Not part of the product library: compiled only when the build defines RGP_BUILD_PROBES
+// (RGP_BUILD_PROBES=1 python -c "import __graft_entry__ as g; g.build(force=True)").
+#ifdef RGP_BUILD_PROBES
 #include <cuda_bf16.h>
 #include "tc_common.cuh"
 
@@ -82,3 +85,5 @@ extern "C" int rgp_debug_umma_rowoff(const void* A, int rows, const void* B, flo
   umma_rowoff_kernel<<<1, 128, smem, (cudaStream_t)stream>>>(tmA, tmB, D, rows, off, mode);
   return check_launch("rgp_debug_umma_rowoff");
 }
+
+#endif  // RGP_BUILD_PROBES

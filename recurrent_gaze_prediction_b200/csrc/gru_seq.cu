@@ -520,11 +520,11 @@ int launch_seq(const rgp_gru_seq_args& a, cudaStream_t s) {
   if (rc) return rc;
   rc = encode_map_bf16(a.Uc, Ch, 9LL * Ch, (long long)Ch * 2, BK, NH / a.mcast, &tmUc);
   if (rc) return rc;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static PerDeviceFlag attr_set = {};
+  if (attr_set.need()) {
     cudaError_t e = cudaFuncSetAttribute(gru_seq_kernel<NH>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes);
     if (e != cudaSuccess) { set_error("gru_seq: cudaFuncSetAttribute(smem=%d): %s", C::kSmemBytes, cudaGetErrorString(e)); return -5; }
-    attr_set = true;
+    attr_set.set();
   }
   const int mtiles = (a.B * S + BM - 1) / BM;
   const int csize = a.nsplit * a.mcast;
@@ -542,7 +542,8 @@ int launch_seq(const rgp_gru_seq_args& a, cudaStream_t s) {
   cfg.numAttrs = 1;
   // all clusters must be co-resident?  No: a cluster is self-contained, later clusters simply start when SMs free up.
   // But a CTA walks several tiles only if the grid is capped, so cap it at what fits at once.
-  static int max_clusters[17] = {0};
+  static int max_clusters_dev[kMaxDevices][17] = {{0}};
+  int* max_clusters = max_clusters_dev[current_device()];
   if (!max_clusters[csize]) {
     cfg.gridDim = dim3((unsigned)(csize * 64), 1, 1);
     int n = 0;

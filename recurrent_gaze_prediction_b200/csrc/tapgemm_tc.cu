@@ -685,13 +685,13 @@ int launch(const rgp_tapgemm_args& a, cudaStream_t s) {
   if (rc) return rc;
   rc = make_map(a.Bw, (long long)a.ntaps * a.N, a.K, a.K, BN, &tmB);
   if (rc) return rc;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static PerDeviceFlag attr_set = {};
+  if (attr_set.need()) {
     cudaError_t e = cudaFuncSetAttribute(tapgemm_tc_kernel<BN, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes);
     if (e == cudaSuccess)
       e = cudaFuncSetAttribute(tapgemm_tc_kernel<BN, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget);
     if (e != cudaSuccess) { set_error("cudaFuncSetAttribute(smem=%d): %s", C::kSmemBytes, cudaGetErrorString(e)); return -5; }
-    attr_set = true;
+    attr_set.set();
   }
   const int mtiles = (a.M + BM - 1) / BM, ntiles = a.N / BN;
   int grid = mtiles * ntiles;
@@ -760,12 +760,13 @@ int encode_map_bf16(const void* base, long long dim0, long long dim1, long long 
 }
 
 int num_sms() {
-  static int n = 0;
+  static int cache[kMaxDevices] = {0};
+  const int dev = current_device();
+  int n = cache[dev];
   if (!n) {
-    int dev = 0;
-    cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
     if (n <= 0) n = 148;
+    cache[dev] = n;
   }
   return n;
 }

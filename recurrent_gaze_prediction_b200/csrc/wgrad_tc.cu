@@ -235,11 +235,11 @@ int launch(const rgp_wgrad_args& a, cudaStream_t s) {
   if (rc) return rc;
   rc = encode_map_bf16(X, a.Nx, a.rowsX, (long long)a.ldx * 2, CH, KB, &tmX);
   if (rc) return rc;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static PerDeviceFlag attr_set = {};
+  if (attr_set.need()) {
     cudaError_t e = cudaFuncSetAttribute(wgrad_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes);
     if (e != cudaSuccess) { set_error("cudaFuncSetAttribute(wgrad smem=%d): %s", C::kSmemBytes, cudaGetErrorString(e)); return -5; }
-    attr_set = true;
+    attr_set.set();
   }
   Sched sc;
   sc.ksteps_total = (a.M + KB - 1) / KB;

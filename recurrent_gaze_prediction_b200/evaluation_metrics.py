@@ -199,7 +199,7 @@ class MetricsEngine(object):
         for m in metrics:
             if m not in ALL_METRICS:
                 raise ValueError("Unknown metric : %s" % m)
-        fix_h = np.asarray(fix.cpu() if isinstance(fix, torch.Tensor) else fix)
+        fix_h = _dense(fix.cpu() if isinstance(fix, torch.Tensor) else fix)
         fix_h = (fix_h > 0.5) if fix_h.dtype != np.bool_ else fix_h
         N, H, W = fix_h.shape
         if len(pred) != N or len(gt) != N:
@@ -311,11 +311,21 @@ def _as_maps(x):
     return np.asarray(x, dtype=np.float32)[None]
 
 
+def _dense(x):
+    """evaluation_metrics.py:240: `if scipy.sparse.issparse(fixation_map): fixation_map = fixation_map.toarray()` — the
+    reference's loaders emit sparse fixation maps (crc_input_data_seq.py:277-321).  Also accepts a list of them."""
+    if hasattr(x, "toarray"):
+        return x.toarray()
+    if isinstance(x, (list, tuple)) and len(x) and hasattr(x[0], "toarray"):
+        return np.stack([f.toarray() for f in x])
+    return np.asarray(x)
+
+
 def _one(metric, fixation_map, saliency_map, gt_map=None, **kw):
     """single pre-normalised-or-not frame through the batch path with `saliency_map` used as is
     (the standalone AUC_* / similarity / cc entry points take maps that are already prepared)."""
     eng = kw.pop("engine", None) or default_engine()
-    fixation_map = np.asarray(fixation_map)
+    fixation_map = _dense(fixation_map)
     sal = np.asarray(saliency_map, dtype=np.float64)
     F = fixation_map > 0.5
     dev = eng.device
@@ -366,10 +376,11 @@ def AUC_Borji(fixation_map, saliency_map, n_rep=100, step_size=0.1, rand_sampler
 
 def AUC_shuffled(fixation_map, saliency_map, other_map, n_rep=100, step_size=0.1, rand_index=None, engine=None):
     """evaluation_metrics.py:167-204."""
-    other_map = np.asarray(other_map) > 0.5
-    if other_map.shape != np.asarray(fixation_map).shape:
+    other_map = _dense(other_map) > 0.5
+    fixation_map = _dense(fixation_map)
+    if other_map.shape != fixation_map.shape:
         raise ValueError('other_map.shape != fixation_map.shape')
-    F = np.asarray(fixation_map) > 0.5
+    F = fixation_map > 0.5
     n_fix = int(F.sum())
     if n_fix == 0:
         print('no fixation to predict')
@@ -414,7 +425,9 @@ def saliency_score_single(metric, pred_map, gt_map, fixation_map, other_map_unio
         kw['jitter_values'] = np.asarray(rand['jitter_values'], dtype=np.float64)[None]
     if 'rand_index' in rand and rand['rand_index'] is not None:
         kw['rand_index' if metric == 'AUC_Borji' else 'shuf_index'] = [np.asarray(rand['rand_index'])]
-    fixation_map = np.asarray(fixation_map)
+    fixation_map = _dense(fixation_map)
+    if other_map_union is not None:
+        other_map_union = _dense(other_map_union)
     if metric in ('AUC_Judd', 'AUC_Borji', 'AUC_shuffled', 'NSS') and not np.any(fixation_map > 0.5):
         if metric != 'NSS':
             print('no fixation to predict')
@@ -428,9 +441,9 @@ def other_map_union(fixation_maps, M=10):
     """evaluation_metrics.py:280-287: OR-count of M randomly chosen frames' fixations (global RNG)."""
     if len(fixation_maps) < M:
         raise AssertionError("need at least %d fixation maps" % M)
-    u = np.zeros(np.asarray(fixation_maps[0]).shape)
+    u = np.zeros(_dense(fixation_maps[0]).shape)
     for i in random.choice(range(len(fixation_maps)), M, replace=False):
-        u += (np.asarray(fixation_maps[i]) > 0).astype(np.int64)
+        u += (_dense(fixation_maps[i]) > 0).astype(np.int64)
     return u
 
 
@@ -442,5 +455,5 @@ def saliency_score(metric, pred_maps, gt_maps, fixation_maps, engine=None):
     eng = engine or default_engine()
     union = other_map_union(fixation_maps)
     r = eng.evaluate_batch(np.asarray(pred_maps, dtype=np.float32), np.asarray(gt_maps, dtype=np.float32),
-                           np.asarray(fixation_maps), union=union, metrics=(metric,))
+                           _dense(fixation_maps), union=union, metrics=(metric,))
     return float(np.mean(r[metric]))

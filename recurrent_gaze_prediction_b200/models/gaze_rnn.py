@@ -259,17 +259,22 @@ class GazePredictionGRU(ModelBase):
             t = t.to(dtype)
         return t.contiguous()
 
-    def _stage(self, batch_c3d, batch_maps, stage=None):
-        """host batch (global batch_size clips; NumPy arrays or CPU tensors) -> this rank's shard as PINNED host tensors
-        of the placeholders' dtypes.  A shard that already lives in pinned memory with the right dtype is used in
-        place (no staging copy: the H2D engine reads it directly); anything else goes through the model's pinned
-        staging buffers."""
+    def _stage(self, batch_c3d, batch_maps, stage=None, local=False):
+        """host batch (NumPy arrays or CPU tensors) -> this rank's shard as PINNED host tensors of the placeholders'
+        dtypes.  The batch is the GLOBAL one (batch_size clips, as the reference's next_batch returns it) of which this
+        rank keeps its slice, or — local=True — already this rank's own `local_batch` clips (a data-parallel loader that
+        reads only its shard).  A shard that already lives in pinned memory with the right dtype is used in place (no
+        staging copy: the H2D engine reads it directly); anything else goes through pinned staging buffers."""
         G = self.engine.G
+        nb = self.local_batch if local else self.batch_size
         c3d = batch_c3d if isinstance(batch_c3d, torch.Tensor) else np.asarray(batch_c3d)
-        c3d = c3d.reshape(self.batch_size, -1, self.dim_feature, G, G)
-        c3d = _shard(c3d, self.rank, self.world_size)
+        c3d = c3d.reshape(nb, -1, self.dim_feature, G, G)
         maps = batch_maps if isinstance(batch_maps, torch.Tensor) else np.asarray(batch_maps, dtype=np.float32)
-        maps = _shard(maps, self.rank, self.world_size)
+        if len(maps) != nb:
+            raise ValueError("gaze maps for %d clips, features for %d" % (len(maps), nb))
+        if not local:
+            c3d = _shard(c3d, self.rank, self.world_size)
+            maps = _shard(maps, self.rank, self.world_size)
         if c3d.shape[1] != self.n_lstm_steps:
             raise ValueError("clip length %d != n_lstm_steps %d" % (c3d.shape[1], self.n_lstm_steps))
         out = []
@@ -282,9 +287,9 @@ class GazePredictionGRU(ModelBase):
                 out.append(buf)
         return out
 
-    def _feed(self, batch_c3d, batch_maps):
+    def _feed(self, batch_c3d, batch_maps, local=False):
         """-> device placeholders (asynchronous copies on the model's stream)"""
-        c3d_h, gt_h = self._stage(batch_c3d, batch_maps)
+        c3d_h, gt_h = self._stage(batch_c3d, batch_maps, local=local)
         self.c3d_input.copy_(c3d_h, non_blocking=True)
         self.gt_gazemap.copy_(gt_h, non_blocking=True)
 
@@ -391,14 +396,15 @@ class GazePredictionGRU(ModelBase):
             loss = float(t.cpu()[0])
         return loss
 
-    def predict(self, batch_c3d, out=None):
+    def predict(self, batch_c3d, out=None, local=False):
         """The inference call the reference's extract_map.py:210-217 wishes the model had
         (`session.run([model.predicted_gazemaps], {model.c3d_input: ..})`): c3d [batch_size, T, 1024, 7, 7] host array
         (NumPy, or a CPU tensor — pinned memory is read in place by the copy engine; bf16 features are accepted when
         config.feature_dtype == 'bf16') -> gaze maps [local clips, T, GH, GW] (probabilities for xentropy / KLD, raw maps
         for l2).  `out`: optional pinned CPU tensor that receives the maps (returned as such, after synchronising);
         default: a fresh NumPy array."""
-        c3d_h, _ = self._stage(batch_c3d, self._gt_host)
+        c3d_h, _ = self._stage(batch_c3d, self._gt_host, local=True) if local else \
+            self._stage(batch_c3d, np.zeros((self.batch_size,) + tuple(self._gt_host.shape[1:]), dtype=np.float32))
         self.c3d_input.copy_(c3d_h, non_blocking=True)
         self.run(train=False, sync=False)
         if out is None:
@@ -414,7 +420,7 @@ class GazePredictionGRU(ModelBase):
             self._feeder = PrefetchFeeder([self.c3d_input, self.gt_gazemap], device=self.engine.device)
         return self._feeder
 
-    def prefetch(self, batch_c3d, batch_maps, flip=None):
+    def prefetch(self, batch_c3d, batch_maps, flip=None, local=False):
         """Start uploading a host batch on the copy stream while the current step runs (double-buffered: at most two
         batches in flight).  `acquire()` then makes it the fed batch.  Pinned inputs are read in place and must stay
         untouched until acquire(); pageable inputs are copied through one of two pinned staging sets first."""
@@ -428,7 +434,7 @@ class GazePredictionGRU(ModelBase):
             self._pf_flip = [None] * f.slots
         f.free[k].synchronize()                      # the slot's previous upload has been consumed
         self._pf_flip[k] = flip
-        f.prefetch(self._stage(batch_c3d, batch_maps, stage=self._pf_stage[k]))
+        f.prefetch(self._stage(batch_c3d, batch_maps, stage=self._pf_stage[k], local=local))
 
     def acquire(self):
         """the oldest prefetched batch becomes the content of the device placeholders (+ its flip, gaze_rnn.py:504-510)"""

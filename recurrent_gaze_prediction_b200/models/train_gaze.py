@@ -47,6 +47,9 @@ def make_session(gpus=1, device=None):
     dev = device or ("cuda:%d" % local)
     if dev.startswith("cuda"):
         torch.cuda.set_device(local)
+        if world > 1:        # pinned staging buffers on the NUMA node of this rank's GPU (best effort)
+            from .. import numa
+            sess["numa"] = numa.bind_to_gpu_node(local)
     if world > 1:
         import torch.distributed as dist
         if not dist.is_initialized():

@@ -147,3 +147,23 @@ def test_fused_and_two_step_host_paths_agree():
     assert np.isnan(calls[0]["AUC_Judd"][1]) and not np.isnan(calls[0]["AUC_Judd"][0])
     want = MO.saliency_score_single("AUC_Judd", pred[0].astype(np.float64), gt[0], fix[0], jitter_values=jit[0])
     assert abs(calls[0]["AUC_Judd"][0] - want) <= 1e-12
+
+
+def test_sparse_fixation_maps_are_accepted():
+    """evaluation_metrics.py:240: scipy.sparse fixation maps (what the reference's loaders emit,
+    crc_input_data_seq.py:277-321) give the same scores as their dense form."""
+    import scipy.sparse as sp
+    eng = EM.MetricsEngine(device="cpu", lib=EmuLib())
+    pred, gt, fix, union = G["s49_pred"], G["s49_gt"], G["s49_fix"], G["s49_union"]
+    i = 0
+    ridx = np.random.RandomState(3).randint(0, 2401, [int((fix[i] > 0.5).sum()), 100])
+    for metric, kw in (("sim", {}), ("NSS", {}), ("AUC_Borji", dict(rand_index=ridx))):
+        a = EM.saliency_score_single(metric, pred[i], gt[i], sp.csr_matrix(fix[i]), sp.csr_matrix(union), engine=eng, **kw)
+        b = EM.saliency_score_single(metric, pred[i], gt[i], fix[i], union, engine=eng, **kw)
+        assert a == b, metric
+    keep = [k for k in range(12) if k != 5]
+    np.random.seed(4)
+    a = EM.saliency_score("cc", list(pred[keep]), list(gt[keep]), [sp.csr_matrix(fix[k]) for k in keep], engine=eng)
+    np.random.seed(4)
+    b = EM.saliency_score("cc", list(pred[keep]), list(gt[keep]), list(fix[keep]), engine=eng)
+    assert a == b

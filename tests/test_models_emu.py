@@ -282,3 +282,58 @@ def test_dense_gru_model_class_contract():
     ret = m.generate(ds.valid, max_instances=2)
     assert ret['pred_gazemap_list'].shape == (6, 49, 49)
     assert np.allclose(ret['pred_gazemap_list'].sum(axis=(1, 2)), 1.0, atol=1e-5)
+
+
+def test_optimisation_method_and_device_side_schedule(tmp_path):
+    """base.py:268-275: an unknown optimisation method is a ValueError; rmsprop / sgd exist in the reference but no entry
+    point selects them — refused, not silently replaced by Adam.  The staircase learning rate and Adam's bias correction
+    are evaluated by rgp_adam_schedule from the engine's own step counter, with the config's decay interval."""
+    lib = EmuLib()
+    for method, exc in (("adagrad", ValueError), ("rmsprop", NotImplementedError), ("sgd", NotImplementedError)):
+        c = small_config()
+        c.optimization_method = method
+        with pytest.raises(exc):
+            gaze_grcn.GazePredictionGRCN({'lib': lib}, data(), c)
+    c = small_config()
+    c.learning_rate_decay_steps, c.learning_rate_decay, c.train_dir = 2, 0.5, str(tmp_path)
+    m = gaze_grcn.GazePredictionGRCN({'lib': lib}, data(), c)
+    np.random.seed(0)
+    lrs = []
+    for k in range(5):
+        m.single_step()
+        lrs.append(float(m.engine.sched[1]))
+        assert int(m.engine.step_dev[0]) == k + 1 == m.current_step
+        t = k + 1
+        want = lrs[-1] * np.sqrt(1 - 0.999 ** t) / (1 - 0.9 ** t)
+        assert abs(float(m.engine.sched[0]) - want) <= 2e-7 * want
+    assert np.allclose(lrs, [1e-2, 1e-2, 5e-3, 5e-3, 2.5e-3], rtol=1e-6)
+    assert abs(m.current_learning_rate - 1e-2 * 0.5 ** 2) < 1e-12        # the logged rate follows the same staircase
+    m.decay_learning_rate(0.1)
+    m.single_step()
+    assert abs(float(m.engine.sched[1]) - 2.5e-4) <= 1e-9
+    # the decay factor survives a checkpoint round trip (it used to be lost: a resumed run got the undecayed rate)
+    path = m.save_model_checkpoint(c.train_dir)
+    m2 = gaze_grcn.GazePredictionGRCN({'lib': lib}, data(), c)
+    m2.load_model_from_checkpoint_file(path)
+    assert abs(m2._lr_scale - 0.1) < 1e-15 and m2.current_step == 6 and int(m2.engine.step_dev[0]) == 6
+    assert not [f for f in os.listdir(os.path.join(c.train_dir, "model")) if ".tmp" in f]
+
+
+def test_bf16_fed_features_and_pinned_inputs_contract():
+    """config.feature_dtype = 'bf16': the placeholder and the staging buffers are bf16; fp32 host batches are rounded
+    on the host, bf16 CPU tensors are taken as they are; the maps equal those of a model fed the rounded fp32 features."""
+    lib = EmuLib()
+    c1, c2 = small_config(), small_config()
+    c1.trainable = c2.trainable = False
+    c2.feature_dtype = 'bf16'
+    m1 = gaze_grcn.GazePredictionGRCN({'lib': lib}, data(), c1)
+    m2 = gaze_grcn.GazePredictionGRCN({'lib': lib}, data(), c2)
+    assert m2.c3d_input.dtype == torch.bfloat16 and m1.c3d_input.dtype == torch.float32
+    rng = np.random.RandomState(0)
+    c3d = SY.make_c3d(rng, 4, 3, 64, 7)
+    rounded = torch.from_numpy(c3d).to(torch.bfloat16)
+    a = m1.predict(rounded.float().numpy())
+    b = m2.predict(c3d)                      # fp32 batch, rounded by the model
+    d = m2.predict(rounded)                  # bf16 CPU tensor
+    assert np.array_equal(a, b) and np.array_equal(a, d)
+    assert a.shape == (4, 3, 49, 49) and np.allclose(a.sum(axis=(2, 3)), 1.0, atol=1e-5)

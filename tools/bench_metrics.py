@@ -1,7 +1,13 @@
 #!/usr/bin/env python
 """Saliency-metric kernels at VAS scale (BASELINE config 5): N frames, 49x49 model maps scored against 360x480
-fixation maps.  Prints one JSON line: frames/s of the full suite, per-kernel CUDA-event time and achieved HBM GB/s
-(algorithmic bytes: float64 pred + gt, uint8 fix per pixel), and the NumPy oracle on a bounded sample beside it."""
+fixation maps.  Prints one JSON line: frames/s of the full suite, per-kernel CUDA-event time and achieved HBM GB/s, and
+the NumPy oracle on a bounded sample beside it.
+
+Two byte counts per map kernel, both stated in the output:
+  * "frac_hbm" — against SURVEY.md 8(d)'s ALGORITHMIC figure: one pass over pred (4) + gt (4) + fix (1) = 9 B/px
+    (1 555 200 B per 360x480 frame); this is the roofline fraction the north star's ">= 70 % of HBM" refers to;
+  * "input_GBps" — the bytes the kernel's float64 INPUT arrays really hold (8 + 8 + 1 = 17 B/px on the two-step path):
+    explains the time, is not the roofline claim."""
 import json
 import os
 import sys
@@ -28,8 +34,8 @@ def ev_time(fn, iters=5):
     return e0.elapsed_time(e1) / iters
 
 
-def main():
-    N, H, W = int(os.environ.get("N", 1024)), 360, 480
+def run(N=1024, cpu_frames=4):
+    H, W = 360, 480
     rng = np.random.RandomState(0)
     base, _ = SY.make_gazemaps(rng, 8, 8, 49, 49)
     base = base.reshape(64, 49, 49)
@@ -52,18 +58,21 @@ def main():
     res = {}
     peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] if os.path.exists(
         os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
+    # (name, call, SURVEY-8d algorithmic bytes, bytes of the kernel's real input/output arrays)
     cases = [
-        ("prep", lambda: eng.to_f64(p32, True), N * 49 * 49 * 12),
-        ("resize_bicubic(49->360x480)", lambda: eng.resize(p64, (H, W)), N * (49 * 49 * 8 + hw * 8)),
-        ("sim_cc_nss", lambda: eng.sim_cc_nss(pr, gr, fx), N * hw * 17),
-        ("auc_judd", lambda: eng.auc_judd(pr, fx, jit, maxfix), N * hw * 17),
-        ("auc_sampled(borji)", lambda: eng.auc_sampled(pr, fx, idx, stats[:, 3:], 8, 0.1, maxfix), N * (hw + maxfix * 100 * 12)),
+        ("prep", lambda: eng.to_f64(p32, True), N * 49 * 49 * 12, N * 49 * 49 * 12),
+        ("resize_bicubic(49->360x480)", lambda: eng.resize(p64, (H, W)), N * (49 * 49 * 4 + hw * 4), N * (49 * 49 * 8 + hw * 8)),
+        ("sim_cc_nss", lambda: eng.sim_cc_nss(pr, gr, fx), N * hw * 9, N * hw * 17),
+        ("auc_judd", lambda: eng.auc_judd(pr, fx, jit, maxfix), N * hw * 5, N * hw * 17),
+        ("auc_sampled(borji)", lambda: eng.auc_sampled(pr, fx, idx, stats[:, 3:], 8, 0.1, maxfix), N * (hw + maxfix * 100 * 8),
+         N * (hw + maxfix * 100 * 12)),
     ]
     total = 0.0
-    for name, fn, nbytes in cases:
+    for name, fn, nbytes, inbytes in cases:
         ms = ev_time(fn)
         total += ms
-        res[name] = {"ms": ms, "GBps": nbytes / ms / 1e6, "frac_hbm": nbytes / ms / 1e6 / peak}
+        res[name] = {"ms": ms, "GBps": nbytes / ms / 1e6, "frac_hbm": nbytes / ms / 1e6 / peak,
+                     "input_GBps": inbytes / ms / 1e6}
     total += res["resize_bicubic(49->360x480)"]["ms"]        # gt is resized too
     two_step_total = total
     # fused path (the default of evaluate_batch): the enlargement is evaluated inside the metric kernels.
@@ -72,10 +81,10 @@ def main():
     src = 49 * 49 * 8
     fused_cases = [
         ("prep", lambda: eng.to_f64(p32, True), N * 49 * 49 * 12, N * 49 * 49 * 12),
-        ("sim_cc_nss_resized", lambda: eng.sim_cc_nss_resized(p64, g64, fx, (H, W)), N * hw * 17, N * (2 * src + hw)),
-        ("auc_judd_resized", lambda: eng.auc_judd_resized(p64, fx, (H, W), jit, maxfix), N * hw * 17, N * (src + hw * 9)),
+        ("sim_cc_nss_resized", lambda: eng.sim_cc_nss_resized(p64, g64, fx, (H, W)), N * hw * 9, N * (2 * src + hw)),
+        ("auc_judd_resized", lambda: eng.auc_judd_resized(p64, fx, (H, W), jit, maxfix), N * hw * 5, N * (src + hw * 9)),
         ("auc_sampled_resized(borji)", lambda: eng.auc_sampled_resized(p64, fx, idx, stats[:, 3:], 8, (H, W), 0.1, maxfix),
-         N * (hw + maxfix * 100 * 12), N * (src + hw + maxfix * 100 * 4)),
+         N * (hw + maxfix * 100 * 8), N * (src + hw + maxfix * 100 * 4)),
     ]
     total = 0.0
     fres = {}
@@ -89,7 +98,7 @@ def main():
     fres["sim_cc_nss_resized"]["fp64_Gops"] = N * hw * (2 * 2 * 10 + 24) / fres["sim_cc_nss_resized"]["ms"] / 1e6
     # NumPy oracle (the reference's algorithm, float64) on a bounded sample
     from oracle import metrics_oracle as MO
-    ns = 4
+    ns = cpu_frames
     t0 = time.perf_counter()
     for i in range(ns):
         jv = np.random.RandomState(i).rand(H, W)
@@ -110,9 +119,15 @@ def main():
                "fused_ms": 2 * fres["prep"]["ms"] + fres["sim_cc_nss_resized"]["ms"]
                + 2 * fres["auc_sampled_resized(borji)"]["ms"]},
            "peak_hbm_GBps": peak, "dtype": "f64",
+           "algorithmic_bytes": "SURVEY 8(d): pred 4 + gt 4 + fix 1 = 9 B/px for sim/cc/NSS (1 555 200 B per 360x480 frame); "
+                                "pred 4 + fix 1 = 5 B/px for AUC-Judd; fix 1 B/px + 8 B per gathered negative for the sampled AUCs",
            "cpu_baseline": {"value": cpu, "unit": "frames/s", "cores": 1, "kind": "port",
                             "sample": "%d frames, oracle/metrics_oracle.py (NumPy float64, one process)" % ns}}
-    print(json.dumps(out))
+    return out
+
+
+def main():
+    print(json.dumps(run(int(os.environ.get("N", 1024)))))
 
 
 if __name__ == "__main__":
