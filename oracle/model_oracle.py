@@ -203,6 +203,121 @@ def init_params_dense(dim_proj=32, grid=7, dim_feature=1024, GH=49, GW=49, seed=
     return p
 
 
+# ----------------------------------------------------------------------------
+# Cascade (BASELINE config 5) — models/gaze_grcn_cascade.py:189-452.
+#
+# As written the file cannot build its graph: the top cell is declared with dim_feature = 64 + 1 (:346-347) and fed
+# the 64-channel up-sampled map (:379; the concat with the ShallowNet frame saliency that would supply channel 65 is
+# commented out, :366-374) - tf.nn.conv2d rejects the channel mismatch.  Two readings, both restated here:
+#   (A) default: the top cell takes the 64 channels it is fed (dim_feature = 64);
+#   (B) frm_sal given: the commented-out concat is live, the cell sees [up-sampled 64 | frame saliency 1] = 65
+#       channels (the ShallowNet that produces frm_sal, models/saliency_shallownet.py, is outside the path: its map
+#       is an input here).
+# Everything else is literal: bottom ConvGRU 256 units without BN (:286-312), ONE 11x11 / stride-7 SAME transposed
+# conv 7 -> 49, 256 -> 64 (:314-336), 5x5 ConvGRU with 3 units on 49x49 (:343-379), per step two maxout FCs
+# 7203 -> 4802 -relu-> max of halves 2401 -> 4802 -relu-> max of halves 2401 (:383-420; dropout on fc1 only, identity
+# at keep_prob 1), prediction = that vector as [49,49] with NO softmax (:422-424), loss = sum_t l2_loss / (B*T)
+# (:427-441).
+# ----------------------------------------------------------------------------
+def conv2d_transpose_same_strided(x, w, stride):
+    """tf.nn.conv2d_transpose(..., strides=[1,s,s,1], padding='SAME') with output = input * s: the gradient of a SAME
+    strided conv [TF-lib]: pad_total = k - s (k >= s), pad_before = pad_total // 2;
+    out[b, i*s + ki - pad_before, j*s + kj - pad_before, co] += x[b,i,j,ci] * w[ki,kj,co,ci].
+    Used at models/gaze_grcn_cascade.py:326-331 (k = 11, s = 7: pad 2 | 2)."""
+    kh = w.shape[0]
+    pad_total = max(kh - stride, 0)
+    pb = pad_total // 2
+    y = F.conv_transpose2d(x.permute(0, 3, 1, 2), w.permute(3, 2, 0, 1), stride=stride, padding=0)
+    H = x.shape[1] * stride
+    y = y[:, :, pb:pb + H, pb:pb + H]
+    return y.permute(0, 2, 3, 1)
+
+
+def maxout_fc(x, W, b):
+    """fully_connected(x, 4802, activation_fn=None) -> relu -> split(1, 2, .) -> maximum  (gaze_grcn_cascade.py:388-420)."""
+    y = torch.relu(x @ W + b)
+    half = y.shape[1] // 2
+    return torch.maximum(y[:, :half], y[:, half:])
+
+
+def cascade_network(p, c3d, frm_sal=None, net=None):
+    """create_gazeprediction_network of gaze_grcn_cascade.py:189-452 (keep_prob = 1).  c3d [B,T,1024,7,7];
+    frm_sal [B,T,49,49] or None (reading A).  Returns the predicted maps [B,T,49,49] (not logits: no softmax)."""
+    if net is None:
+        net = {}
+    emb = project_c3d(c3d, p)
+    B, T = emb.shape[:2]
+    bot = {k.split("/", 1)[1]: v for k, v in p.items() if k.startswith("RCNBottom/")}
+    top = {k.split("/", 1)[1]: v for k, v in p.items() if k.startswith("RCNGaze/")}
+    ch = bot["GRU_Conv_Uz"].shape[-1]
+    state = emb.new_zeros(B, 7, 7, ch)
+    outs = []
+    for i in range(T):                                  # :293-312
+        out, state = gru_rcn_cell(emb[:, i], state, bot)
+        outs.append(out)
+    net["rcn_outputs"] = outs
+    ups = [conv2d_transpose_same_strided(o, p["Upsampling/weight"], 7) for o in outs]   # :323-331
+    net["rcn_upsampled_outputs"] = ups
+    units = top["GRU_Conv_Uz"].shape[-1]
+    sg = emb.new_zeros(B, 49, 49, units)
+    maps, tops = [], []
+    for i in range(T):                                  # :358-424
+        x = ups[i] if frm_sal is None else torch.cat([ups[i], frm_sal[:, i, :, :, None]], dim=3)
+        og, sg = gru_rcn_cell(x, sg, top)
+        tops.append(og)
+        m1 = maxout_fc(og.reshape(B, -1), p["LastProjection/fc1/weights"], p["LastProjection/fc1/bias"])
+        m2 = maxout_fc(m1, p["LastProjection/fc2/weights"], p["LastProjection/fc2/bias"])
+        maps.append(m2.reshape(B, 49, 49))
+    net["top_outputs"] = tops
+    pred = torch.stack(maps).permute(1, 0, 2, 3)        # :449
+    net["predicted_gazemaps"] = pred
+    return pred
+
+
+def cascade_loss(pred, gt):
+    """gaze_grcn_cascade.py:427-441: sum over t of tf.nn.l2_loss(pred_t - gt_t) (= sum of squares / 2), / (B*T)."""
+    B, T = pred.shape[:2]
+    return 0.5 * ((pred - gt) ** 2).sum() / float(B * T)
+
+
+def _xavier_uniform_fc(rng, fan_in, fan_out):
+    """xavier_initializer(uniform=True) on a [fan_in, fan_out] matrix [TF-lib]."""
+    lim = math.sqrt(6.0 / (fan_in + fan_out))
+    return rng.uniform(-lim, lim, size=(fan_in, fan_out))
+
+
+def init_params_cascade(hidden=256, top_in=64, units=3, dim_proj=512, dim_feature=1024, seed=0, regime="R",
+                        stddev_scale=None, fc_bias_scale=0.0):
+    """Variables of the cascade in the reference's creation order (gaze_grcn_cascade.py): proj_c3d_W/b (:268-269),
+    RCNBottom cell (:52-81 via :287), Upsampling/weight [11,11,64,256] Xavier (:317-321), RCNGaze cell 5x5 with
+    `top_in` input channels (64 = reading A, 65 = reading B) and 3 units (:346-351), then on the first time step
+    LastProjection/fc1 weights [7203,4802] Xavier + bias 0, fc2 weights [2401,4802] + bias 0 (:388-411).
+    fc_bias_scale > 0 draws the biases from N(0, scale) AFTER all other variables (parity tests: a zero bias would
+    not exercise the bias path)."""
+    rng = np.random.RandomState(seed)
+    sc = REGIMES[regime][0] if stddev_scale is None else stddev_scale
+    p = OrderedDict()
+    p["proj_c3d_W"] = rng.uniform(-0.1, 0.1, size=(dim_feature, dim_proj))
+    p["proj_c3d_b"] = rng.uniform(-0.1, 0.1, size=(dim_proj,))
+
+    def cell(scope, k, cin, n):
+        for nm, ci in (("Wz", cin), ("Uz", n), ("Wr", cin), ("Ur", n), ("W", cin), ("U", n)):
+            p[scope + "/GRU_Conv_" + nm] = _trunc_normal(rng, (k, k, ci, n), 1e-4 * sc)
+
+    cell("RCNBottom", 3, dim_proj, hidden)
+    p["Upsampling/weight"] = _xavier_uniform_conv(rng, (11, 11, 64, hidden))
+    cell("RCNGaze", 5, top_in, units)
+    n_in = 49 * 49 * units
+    p["LastProjection/fc1/weights"] = _xavier_uniform_fc(rng, n_in, 4802)
+    p["LastProjection/fc1/bias"] = np.zeros(4802)
+    p["LastProjection/fc2/weights"] = _xavier_uniform_fc(rng, 2401, 4802)
+    p["LastProjection/fc2/bias"] = np.zeros(4802)
+    if fc_bias_scale > 0:
+        p["LastProjection/fc1/bias"] = fc_bias_scale * rng.standard_normal(4802)
+        p["LastProjection/fc2/bias"] = fc_bias_scale * rng.standard_normal(4802)
+    return p
+
+
 def softmax_2d(logits):
     """model_util.py:61-64 applied per frame as gaze_rnn.py:149-159."""
     B, T, H, W = logits.shape

@@ -181,7 +181,10 @@ def _conv2d(x, filter, strides, padding, name=None, **kw):
 
 
 def _conv2d_transpose(value, filter, output_shape, strides, padding="SAME", name=None, **kw):
-    y = O.conv2d_transpose(value, filter, int(strides[1]), padding)
+    if padding == "SAME" and int(strides[1]) > 1:
+        y = O.conv2d_transpose_same_strided(value, filter, int(strides[1]))
+    else:
+        y = O.conv2d_transpose(value, filter, int(strides[1]), padding)
     assert list(y.shape) == [int(s) for s in output_shape], (y.shape, output_shape)
     return y
 
@@ -191,7 +194,7 @@ def _xw_plus_b(x, w, b, name=None):
 
 
 def _dropout(x, keep_prob, **kw):
-    assert float(keep_prob) == 1.0, "reference graphs feed keep_prob=1.0 (SURVEY Q2)"
+    assert float(keep_prob) == 1.0, "reference graphs are run at keep_prob=1.0 (SURVEY Q2; cascade: inference)"
     return x
 
 
@@ -232,6 +235,52 @@ def _xavier_initializer_conv2d(uniform=True, **kw):
     return lambda shape: O._xavier_uniform_conv(STATE["rng"], shape)
 
 
+def _xavier_initializer(uniform=True, **kw):
+    assert uniform
+    return lambda shape: O._xavier_uniform_fc(STATE["rng"], int(shape[0]), int(shape[1]))
+
+
+def _constant_initializer(value=0.0, **kw):
+    return lambda shape: np.full(tuple(int(s) for s in shape), float(value))
+
+
+_FC_VARS = {}
+
+
+def _fully_connected(x, num_output_units, activation_fn=None, weight_init=None, bias_init=None, name=None, **kw):
+    """tf.contrib.layers fully_connected of the pre-1.0 API the cascade calls (gaze_grcn_cascade.py:388-411):
+    variables <scope>/<name>/weights [in, out] and <scope>/<name>/bias [out], created on the first call and reused
+    afterwards (the reference calls reuse_variables() for i > 0); y = x.W + b, then activation_fn."""
+    key = "/".join(STATE["scope"] + [str(name)])
+    if key not in _FC_VARS or _FC_VARS[key][2] is not STATE["variables"]:
+        w = _register(str(name) + "/weights", _t(weight_init((int(x.shape[1]), int(num_output_units)))))
+        b = _register(str(name) + "/bias", _t(bias_init((int(num_output_units),))))
+        _FC_VARS[key] = (w, b, STATE["variables"])
+    w, b, _ = _FC_VARS[key]
+    y = x @ w + b
+    return activation_fn(y) if activation_fn is not None else y
+
+
+def _relu(x, name=None):
+    return torch.relu(x)
+
+
+def maximum(a, b, name=None):
+    return torch.maximum(a, b)
+
+
+def _noop(*a, **k):
+    return None
+
+
+def reduce_min(x, axis=None, keep_dims=False, **kw):
+    return x.min() if axis is None else torch.amin(x, dim=tuple(axis) if isinstance(axis, (list, tuple)) else axis, keepdim=keep_dims)
+
+
+def reduce_max(x, axis=None, keep_dims=False, **kw):
+    return x.max() if axis is None else torch.amax(x, dim=tuple(axis) if isinstance(axis, (list, tuple)) else axis, keepdim=keep_dims)
+
+
 def install():
     """Put the stand-in modules into sys.modules so the reference files import unmodified."""
     tf = types.ModuleType("tensorflow")
@@ -240,7 +289,8 @@ def install():
         variable_scope=variable_scope, get_variable_scope=get_variable_scope, get_variable=get_variable,
         transpose=transpose, reshape=reshape, concat=concat, split=split, stack=stack, pack=pack,
         zeros=zeros, placeholder=placeholder, add=add, div=div, reduce_sum=reduce_sum,
-        sigmoid=sigmoid, tanh=tanh, float32=DT,
+        sigmoid=sigmoid, tanh=tanh, float32=DT, maximum=maximum, reduce_min=reduce_min, reduce_max=reduce_max, constant_initializer=_constant_initializer,
+        scalar_summary=_noop, image_summary=_noop, merge_summary=_noop, get_collection=_noop,
     ).items():
         setattr(tf, k, v)
     nn = types.ModuleType("tensorflow.nn")
@@ -252,14 +302,16 @@ def install():
     nn.softmax_cross_entropy_with_logits = _softmax_xent
     nn.l2_loss = _l2_loss
     nn.sigmoid, nn.tanh = sigmoid, tanh
+    nn.relu = _relu
     nn.rnn_cell = types.SimpleNamespace(RNNCell=_RNNCell)
     tf.nn = nn
     tf.layers = types.SimpleNamespace(batch_normalization=_batch_normalization)
-    inits = types.SimpleNamespace(xavier_initializer_conv2d=_xavier_initializer_conv2d)
+    inits = types.SimpleNamespace(xavier_initializer_conv2d=_xavier_initializer_conv2d,
+                                  xavier_initializer=_xavier_initializer)
     contrib_layers = types.ModuleType("tensorflow.contrib.layers.python.layers")
     contrib_layers.initializers = inits
     contrib_layers.convolution2d = None
-    contrib_layers.fully_connected = None
+    contrib_layers.fully_connected = _fully_connected
     mods = {"tensorflow": tf, "tensorflow.nn": nn,
             "tensorflow.contrib": types.ModuleType("tensorflow.contrib"),
             "tensorflow.contrib.layers": types.ModuleType("tensorflow.contrib.layers"),
@@ -292,7 +344,15 @@ def install():
     mb.ModelBase, mb.BaseModelConfig = ModelBase, BaseModelConfig
     mods["models.base"] = mb
     ss = types.ModuleType("models.saliency_shallownet")
-    ss.SaliencyModel = object
+
+    class SaliencyModel(object):
+        # models/saliency_shallownet.py (frame-wise ShallowNet) is not on the path: the cascade builds it
+        # (gaze_grcn_cascade.py:240-245) but its map never reaches the prediction (the concat is commented out,
+        # :366-374) and only feeds an image summary; a zero map of the right shape stands in.
+        @staticmethod
+        def create_shallownet(images, scope=None, dropout=False, **kw):
+            return torch.zeros(int(images.shape[0]), 49, 49, dtype=DT)
+    ss.SaliencyModel = SaliencyModel
     mods["models.saliency_shallownet"] = ss
     from oracle.gen_golden_metrics import import_reference_metrics  # skimage stub + evaluation_metrics
     import_reference_metrics()

@@ -114,3 +114,51 @@ def test_normalize_probability_map():
     t = rng.uniform(size=(2, 3, 4, 4)).astype(np.float32)
     n = O.normalize_probability_map(t)
     assert np.allclose(n.sum(axis=(2, 3)), 1, atol=1e-6) and n.dtype == np.float32
+
+
+def test_cascade_oracle_matches_reference_graph_run():
+    """oracle.cascade_network against the reference's gaze_grcn_cascade.py create_gazeprediction_network run over the
+    shim (oracle/gen_golden_model.py run_cascade: reading A of the 65-vs-64 channel bug): variable draw bit-for-bit,
+    bottom states, up-sampled maps, predicted maps and the l2 loss."""
+    g = _load("gaze_grcn_cascade")
+    B, T = int(g["B"]), int(g["T"])
+    rng = np.random.RandomState(int(g["input_seed"]))
+    c3d = SY.make_c3d(rng, B, T).astype(np.float64)
+    gt, _ = SY.make_gazemaps(rng, B, T, 49, 49, normalize=False)
+    p = O.init_params_cascade(seed=int(g["seed"]), stddev_scale=float(g["stddev_scale"]))
+    names = [str(n) for n in g["var_names"]]
+    assert names == list(p.keys())                       # same variables, same creation order
+    for nm in names:
+        a = np.asarray(p[nm], dtype=np.float64)
+        assert list(a.shape) == list(g["var/%s/shape" % nm]), nm
+        a = a.ravel()
+        assert np.array_equal(a[g["var/%s/idx" % nm]], g["var/%s/samp" % nm]), nm
+        assert abs(a.sum() - g["var/%s/sum" % nm][0]) <= 1e-9 * max(1, abs(a.sum()))
+    net = {}
+    with torch.no_grad():
+        pred = O.cascade_network(O.to_torch(p), torch.tensor(c3d), net=net)
+        loss = float(O.cascade_loss(pred, torch.tensor(gt.astype(np.float64))))
+    assert np.allclose(net["rcn_outputs"][-1].numpy(), g["rcn_last"], rtol=1e-10, atol=1e-14)
+    up = net["rcn_upsampled_outputs"][-1].numpy().ravel()
+    assert abs(up.sum() - g["up_fp"][0]) <= 1e-9 * max(1.0, abs(up.sum()))
+    assert abs(np.sqrt((up * up).sum()) - g["up_fp"][1]) <= 1e-10 * g["up_fp"][1]
+    assert np.allclose(pred.numpy(), g["pred"], rtol=1e-10, atol=1e-13)
+    assert pred.numpy().max() > 1e-3                      # the maxout chain is alive at this scale
+    assert abs(loss - float(g["loss_l2"])) <= 1e-10 * abs(loss)
+
+
+def test_strided_same_transposed_conv_against_naive_definition():
+    """tf.nn.conv2d_transpose(k=11, stride 7, SAME) 7 -> 49 (gaze_grcn_cascade.py:326-331)."""
+    rng = np.random.RandomState(0)
+    x = rng.standard_normal((1, 7, 7, 3))
+    w = rng.standard_normal((11, 11, 2, 3))
+    y = O.conv2d_transpose_same_strided(torch.tensor(x), torch.tensor(w), 7).numpy()
+    out = np.zeros((1, 49, 49, 2))
+    for i in range(7):
+        for j in range(7):
+            for ki in range(11):
+                for kj in range(11):
+                    oy, ox = i * 7 + ki - 2, j * 7 + kj - 2
+                    if 0 <= oy < 49 and 0 <= ox < 49:
+                        out[:, oy, ox, :] += x[:, i, j, :] @ w[ki, kj].T
+    assert np.allclose(y, out, atol=1e-12)
