@@ -481,6 +481,7 @@ def bench_config4(args, H):
     out = {"workload": "gaze_lstm inference, T=128, 14x14 grid, embedded features 512x14x14, hidden 128, per-position FC head",
            "api": "GazeEngine.forward(emb=...) as one CUDA graph", "n_gpus": 1}
     T, G, Ch = 128, 14, 128
+    H = Harness(H.dev, H.local, 0, 1)      # rank 0 runs this record alone: no barrier / max over ranks with the others
     p = dict(init_parameters("gaze_lstm", hidden=Ch, T=T, grid=G, seed=0))
     p["out_W"] = np.random.RandomState(7).uniform(-0.1, 0.1, (Ch, 1)).astype(np.float32)
     hbm, tf_burst, tf_sus, _ = peaks()
@@ -519,7 +520,9 @@ def main():
     numa_info = numa.bind_to_gpu_node(local) if world > 1 else {"node": None, "note": "single rank: not bound"}
     session = {"rank": rank, "world_size": world, "allreduce": None}
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        import datetime
+        # a rank that dies must fail the others within minutes, not after NCCL's default 10-minute watchdog
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=240))
         session["allreduce"] = lambda t: dist.all_reduce(t, op=dist.ReduceOp.SUM)
     H = Harness(dev, local, rank, world)
     if args.entry == "emb" or args.head is not None:

@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define RGP_MAX_TAPS 16
+#define RGP_MAX_TAPS 32   /* 25 = the 5x5 top cell of the cascade (gaze_grcn_cascade.py:346-351) */
 
 /* epilogue selectors of rgp_tapgemm */
 enum {
@@ -37,7 +37,12 @@ enum {
   RGP_EPI_BWD_RH = 7,      /* acc = d(r.h): dpre_r = acc*h*r(1-r) -> dG[:,Ch:2Ch]; dhpart += acc*r     */
   RGP_EPI_BWD_H = 8,       /* acc = convT(dpre_z,dpre_r): dh = acc + dhpart + head term; gate backward of step t-1 */
   RGP_EPI_DHS = 9,         /* head backward: store fp32 acc at the recurrence q-row of the head-layout row */
-  RGP_EPI_DX_DENSE = 10    /* store operand dtype at the dense row f*P + y*G + x (valid rows only)     */
+  RGP_EPI_DX_DENSE = 10,   /* store operand dtype at the dense row f*P + y*G + x (valid rows only)     */
+  /* cascade (gaze_grcn_cascade.py:317-336): the 11x11 / stride-7 SAME transposed conv 7x7 -> 49x49 as a 4-tap GEMM over the
+   * 8x8 p-layout rows of h_t.  Row (a,b) of frame f and column n = (ry*7+rx)*P + co is output pixel
+   * (oy,ox) = (7a+ry-2, 7b+rx-2), channel co; it is stored (operand dtype) at row f*So + (oy+2)*Wo + (ox+2) of out_op
+   * (leading dimension ldo) - the zero-bordered operand layout of the 5x5 top cell; columns n >= 49*P are padding. */
+  RGP_EPI_UP7 = 11
 };
 
 /* One "tap GEMM":  acc[m,n] = sum_tap sum_k A[m + tap_off[tap], k] * Bw[tap*N + n, k]
@@ -242,6 +247,30 @@ int rgp_dense_gru_c(const float* xg, int ldx, const float* hc, const float* bias
                     float* hnext_f32, void* hnext_op, int M, int H, int Hp, int dtype, void* stream);
 /* gaze_rnn.py:346-359: logits[b, t, j] = acc[(t*B + b)*ldacc + j] + bias[j], j < N */
 int rgp_dense_logits(const float* acc, int ldacc, const float* bias, float* logits, int B, int T, int N, void* stream);
+
+/* ---- cascade top level: models/gaze_grcn_cascade.py:343-424 ---------------------------
+ * Persistent 5x5 ConvGRU with 3 units on the 49x49 grid (:346-351,379; cell arithmetic :95-129): ALL T steps in one
+ * launch, one CTA per clip, the state (49*49*3 floats) and r.h live in shared memory for the whole sequence; only the
+ * input-half pre-activations are read and the per-step outputs written.  fp32 arithmetic on the CUDA cores for both
+ * operand dtypes (P = 2401, Ch = 3: a bandwidth kernel, not a GEMM).
+ *   xg    [T*B*So, ldx] fp32: input-half pre-activations (rgp_tapgemm, 25 taps) at q-row f*So + y*Wo + x, f = t*B + b,
+ *         columns z(3) | r(3) | c(3);
+ *   uzr   [25][3][6] fp32 (tap ky*5+kx, input unit, output z0..2 r0..2) ; uc [25][3][3] fp32;
+ *   sal / wsal (both or neither; reading B of the 65-channel declaration, :346-347): sal [B,T,49,49] fp32 frame
+ *         saliency, wsal [25][9] fp32 = the 65th input channel's kernels (z|r|c) - its 5x5 conv is added to xg here;
+ *   state [B, 7203] fp32 or NULL: in = h_0 when carry != 0 (else h_0 = 0, :353), out = h_T;
+ *   og_op [T*B, ldo] operand dtype: row f = h_t flattened (y, x, unit) as tf.reshape(output_g, [B,-1]) does (:384) -
+ *         the A operand of the first maxout FC; h_f32 (optional) [T*B, 7203] fp32 the same values. */
+int rgp_topgru_seq_fwd(const float* xg, int ldx, int So, int Wo, const float* uzr, const float* uc, const float* sal,
+                       const float* wsal, float* state, int carry, void* og_op, int ldo, float* h_f32, int B, int T,
+                       int dtype, void* stream);
+/* gaze_grcn_cascade.py:388-420: bias + relu + maxout of one FC layer whose GEMM output y [rows, ldy] fp32 keeps the two
+ * halves tf.split(1, 2, .) separates at columns [0, n) and [half, half + n):
+ *   v[r, j] = max(relu(y[r, j] + bias[j]), relu(y[r, half + j] + bias[half + j])),  j < n.
+ * out_op (operand dtype [rows, ldo], next layer's A operand) and / or out_maps (fp32 [B, T, n]: row r = t*B + b is
+ * written to clip b, step t - the predicted gaze maps, :422-424,449) receive v. */
+int rgp_maxout(const float* y, int ldy, const float* bias, int half, int n, void* out_op, int ldo, float* out_maps,
+               int B, int T, int dtype, void* stream);
 
 /* ---- saliency metrics: evaluation_metrics.py -------------------------------------------- */
 /* All metric arithmetic is IEEE float64 with explicit round-to-nearest operations (no FMA contraction):

@@ -1,0 +1,235 @@
+// cascade.cu — top level of the cascade model: models/gaze_grcn_cascade.py:343-424.
+//
+//   topgru_seq_kernel : the 5x5 ConvGRU with 3 units on the 49x49 grid (:346-351,379; cell :95-129), all T steps in
+//                       one launch, one CTA per clip, state and r.h resident in shared memory for the whole sequence.
+//   maxout_kernel     : bias + relu + max of the two halves of a maxout FC (:388-420) after its GEMM.
+//
+// The two GEMM-shaped pieces around them run on the tap-GEMM engines: the 11x11 / stride-7 transposed conv as a 4-tap
+// GEMM (RGP_EPI_UP7), the input half of the top cell as a 25-tap GEMM, the two FCs as plain GEMMs.
+#include "common.cuh"
+
+namespace rgp {
+namespace {
+
+constexpr int GT = 49;              // top grid
+constexpr int NU = 3;               // units of the top cell
+constexpr int KT = 5;               // its kernel
+constexpr int PW = GT + KT - 1;     // 53: zero-bordered plane width in shared memory
+constexpr int PLANE = PW * PW;      // 2809
+constexpr int NPIX = GT * GT;       // 2401
+constexpr int TOP_THREADS = 512;
+constexpr int PPT = (NPIX + TOP_THREADS - 1) / TOP_THREADS;   // 5 pixels per thread
+
+__device__ __forceinline__ float sigm(float x) { return 1.0f / (1.0f + expf(-x)); }
+
+template <typename TA>
+__global__ void __launch_bounds__(TOP_THREADS, 1)
+topgru_seq_kernel(const float* __restrict__ xg, int ldx, int So, int Wo, const float* __restrict__ uzr,
+                  const float* __restrict__ uc, const float* __restrict__ sal, const float* __restrict__ wsal,
+                  float* __restrict__ state, int carry, TA* __restrict__ og_op, int ldo, float* __restrict__ h_f32,
+                  int B, int T) {
+  extern __shared__ float sm[];
+  float* hs = sm;                          // [NU][PLANE]   h_{t-1}, zero border of 2
+  float* rhs = hs + NU * PLANE;            // [NU][PLANE]   r . h_{t-1}
+  float* ss = rhs + NU * PLANE;            // [PLANE]       frame saliency (reading B), zero border
+  float* wzr = ss + PLANE;                 // [25][NU][6]
+  float* wc = wzr + 25 * NU * 6;           // [25][NU][NU]
+  float* ws = wc + 25 * NU * NU;           // [25][9]
+  const int b = blockIdx.x, tid = threadIdx.x;
+
+  for (int i = tid; i < (2 * NU + 1) * PLANE; i += TOP_THREADS) sm[i] = 0.f;
+  for (int i = tid; i < 25 * NU * 6; i += TOP_THREADS) wzr[i] = uzr[i];
+  for (int i = tid; i < 25 * NU * NU; i += TOP_THREADS) wc[i] = uc[i];
+  if (sal)
+    for (int i = tid; i < 25 * 9; i += TOP_THREADS) ws[i] = wsal[i];
+  __syncthreads();
+  if (carry && state)
+    for (int i = tid; i < NPIX * NU; i += TOP_THREADS) {
+      const int p = i / NU, u = i - p * NU, y = p / GT, x = p - y * GT;
+      hs[u * PLANE + (y + 2) * PW + x + 2] = state[(long long)b * NPIX * NU + i];
+    }
+  __syncthreads();
+
+  for (int t = 0; t < T; ++t) {
+    const long long f = (long long)t * B + b;
+    const float* xf = xg + f * So * ldx;
+    if (sal) {
+      const float* sf = sal + ((long long)b * T + t) * NPIX;
+      for (int p = tid; p < NPIX; p += TOP_THREADS) {
+        const int y = p / GT, x = p - y * GT;
+        ss[(y + 2) * PW + x + 2] = sf[p];
+      }
+      __syncthreads();
+    }
+    float z[PPT][NU], xc[PPT][NU];
+    // ---- phase A: z, r and r.h  (gaze_grcn_cascade.py:108-119)
+#pragma unroll
+    for (int k = 0; k < PPT; ++k) {
+      const int p = tid + k * TOP_THREADS;
+      if (p < NPIX) {
+        const int y = p / GT, x = p - y * GT;
+        const float* xp = xf + (long long)(y * Wo + x) * ldx;
+        const float4 x0 = *reinterpret_cast<const float4*>(xp);
+        const float4 x1 = *reinterpret_cast<const float4*>(xp + 4);
+        float acc[6] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y};
+        xc[k][0] = x1.z; xc[k][1] = x1.w; xc[k][2] = xp[8];
+        const int base = y * PW + x;
+#pragma unroll 5
+        for (int tap = 0; tap < 25; ++tap) {
+          const int o = base + (tap / KT) * PW + (tap % KT);
+          const float* w = wzr + tap * NU * 6;
+#pragma unroll
+          for (int u = 0; u < NU; ++u) {
+            const float hv = hs[u * PLANE + o];
+#pragma unroll
+            for (int j = 0; j < 6; ++j) acc[j] = fmaf(hv, w[u * 6 + j], acc[j]);
+          }
+          if (sal) {
+            const float sv = ss[o];
+            const float* q = ws + tap * 9;
+#pragma unroll
+            for (int j = 0; j < 6; ++j) acc[j] = fmaf(sv, q[j], acc[j]);
+#pragma unroll
+            for (int j = 0; j < NU; ++j) xc[k][j] = fmaf(sv, q[6 + j], xc[k][j]);
+          }
+        }
+        const int c = base + 2 * PW + 2;
+#pragma unroll
+        for (int u = 0; u < NU; ++u) {
+          z[k][u] = sigm(acc[u]);
+          rhs[u * PLANE + c] = sigm(acc[NU + u]) * hs[u * PLANE + c];
+        }
+      }
+    }
+    __syncthreads();
+    // ---- phase B: candidate and state update  (:122-127)
+    float hn[PPT][NU];
+#pragma unroll
+    for (int k = 0; k < PPT; ++k) {
+      const int p = tid + k * TOP_THREADS;
+      if (p < NPIX) {
+        const int y = p / GT, x = p - y * GT;
+        float acc[NU] = {xc[k][0], xc[k][1], xc[k][2]};
+        const int base = y * PW + x;
+#pragma unroll 5
+        for (int tap = 0; tap < 25; ++tap) {
+          const int o = base + (tap / KT) * PW + (tap % KT);
+          const float* w = wc + tap * NU * NU;
+#pragma unroll
+          for (int u = 0; u < NU; ++u) {
+            const float rv = rhs[u * PLANE + o];
+#pragma unroll
+            for (int j = 0; j < NU; ++j) acc[j] = fmaf(rv, w[u * NU + j], acc[j]);
+          }
+        }
+        const int c = base + 2 * PW + 2;
+#pragma unroll
+        for (int u = 0; u < NU; ++u) {
+          const float cv = tanhf(acc[u]);
+          hn[k][u] = z[k][u] * hs[u * PLANE + c] + (1.0f - z[k][u]) * cv;
+        }
+      }
+    }
+    __syncthreads();      // every read of h_{t-1} is done
+#pragma unroll
+    for (int k = 0; k < PPT; ++k) {
+      const int p = tid + k * TOP_THREADS;
+      if (p < NPIX) {
+        const int y = p / GT, x = p - y * GT;
+        const int c = (y + 2) * PW + x + 2;
+#pragma unroll
+        for (int u = 0; u < NU; ++u) {
+          hs[u * PLANE + c] = hn[k][u];
+          OpT<TA>::st(og_op + f * ldo + p * NU + u, hn[k][u]);       // tf.reshape(output_g, [B,-1]): (y, x, unit)
+          if (h_f32) h_f32[f * (NPIX * NU) + p * NU + u] = hn[k][u];
+        }
+      }
+    }
+    __syncthreads();
+  }
+  if (state)
+    for (int i = tid; i < NPIX * NU; i += TOP_THREADS) {
+      const int p = i / NU, u = i - p * NU, y = p / GT, x = p - y * GT;
+      state[(long long)b * NPIX * NU + i] = hs[u * PLANE + (y + 2) * PW + x + 2];
+    }
+}
+
+template <typename TA>
+__global__ void __launch_bounds__(256) maxout_kernel(const float* __restrict__ y, int ldy, const float* __restrict__ bias,
+                                                     int half, int n, TA* __restrict__ out_op, int ldo,
+                                                     float* __restrict__ out_maps, int B, int T) {
+  const long long total = (long long)B * T * n;
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
+    const long long r = i / n;
+    const int j = (int)(i - r * n);
+    const float a = fmaxf(y[r * ldy + j] + bias[j], 0.f);
+    const float c = fmaxf(y[r * ldy + half + j] + bias[half + j], 0.f);
+    const float v = fmaxf(a, c);
+    if (out_op) OpT<TA>::st(out_op + r * ldo + j, v);
+    if (out_maps) {
+      const long long t = r / B, b = r - t * B;      // rows are time-major
+      out_maps[(b * T + t) * n + j] = v;
+    }
+  }
+}
+
+constexpr int kTopSmem = ((2 * NU + 1) * PLANE + 25 * NU * 6 + 25 * NU * NU + 25 * 9) * (int)sizeof(float);
+
+template <typename TA>
+int launch_topgru(const float* xg, int ldx, int So, int Wo, const float* uzr, const float* uc, const float* sal,
+                  const float* wsal, float* state, int carry, void* og_op, int ldo, float* h_f32, int B, int T,
+                  cudaStream_t s) {
+  static PerDeviceFlag attr_set = {};
+  if (attr_set.need()) {
+    cudaError_t e = cudaFuncSetAttribute(topgru_seq_kernel<TA>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTopSmem);
+    if (e != cudaSuccess) { set_error("rgp_topgru_seq_fwd: cudaFuncSetAttribute(%d): %s", kTopSmem, cudaGetErrorString(e)); return -5; }
+    attr_set.set();
+  }
+  topgru_seq_kernel<TA><<<B, TOP_THREADS, kTopSmem, s>>>(xg, ldx, So, Wo, uzr, uc, sal, wsal, state, carry, (TA*)og_op,
+                                                        ldo, h_f32, B, T);
+  return check_launch("rgp_topgru_seq_fwd");
+}
+
+}  // namespace
+}  // namespace rgp
+
+using namespace rgp;
+
+extern "C" {
+
+int rgp_topgru_seq_fwd(const float* xg, int ldx, int So, int Wo, const float* uzr, const float* uc, const float* sal,
+                       const float* wsal, float* state, int carry, void* og_op, int ldo, float* h_f32, int B, int T,
+                       int dtype, void* stream) {
+  RGP_CHECK_ARG(xg && uzr && uc && og_op, "rgp_topgru_seq_fwd: null pointer%s", "");
+  RGP_CHECK_ARG(B > 0 && T > 0, "rgp_topgru_seq_fwd: B=%d T=%d", B, T);
+  RGP_CHECK_ARG(ldx >= 9 && ldx % 4 == 0 && (reinterpret_cast<uintptr_t>(xg) & 15) == 0,
+                "rgp_topgru_seq_fwd: ldx=%d must be a multiple of 4 (>= 9) and xg 16-byte aligned", ldx);
+  RGP_CHECK_ARG(Wo >= GT + 2 && So >= (GT - 1) * Wo + GT, "rgp_topgru_seq_fwd: So=%d Wo=%d too small for a 49x49 grid", So, Wo);
+  RGP_CHECK_ARG(ldo >= NPIX * NU, "rgp_topgru_seq_fwd: ldo=%d < 7203", ldo);
+  RGP_CHECK_ARG((sal == nullptr) == (wsal == nullptr), "rgp_topgru_seq_fwd: sal and wsal go together%s", "");
+  RGP_CHECK_ARG(dtype == 0 || dtype == 1, "rgp_topgru_seq_fwd: dtype %d", dtype);
+  if (dtype == 0)
+    return launch_topgru<float>(xg, ldx, So, Wo, uzr, uc, sal, wsal, state, carry, og_op, ldo, h_f32, B, T,
+                                (cudaStream_t)stream);
+  return launch_topgru<__nv_bfloat16>(xg, ldx, So, Wo, uzr, uc, sal, wsal, state, carry, og_op, ldo, h_f32, B, T,
+                                      (cudaStream_t)stream);
+}
+
+int rgp_maxout(const float* y, int ldy, const float* bias, int half, int n, void* out_op, int ldo, float* out_maps,
+               int B, int T, int dtype, void* stream) {
+  RGP_CHECK_ARG(y && bias && (out_op || out_maps), "rgp_maxout: null pointer%s", "");
+  RGP_CHECK_ARG(n > 0 && n <= half && half + n <= ldy, "rgp_maxout: n=%d half=%d ldy=%d", n, half, ldy);
+  RGP_CHECK_ARG(B > 0 && T > 0, "rgp_maxout: B=%d T=%d", B, T);
+  RGP_CHECK_ARG(!out_op || ldo >= n, "rgp_maxout: ldo=%d < n=%d", ldo, n);
+  const long long total = (long long)B * T * n;
+  int grid = (int)((total + 255) / 256);
+  if (grid > 148 * 16) grid = 148 * 16;
+  if (dtype == 0)
+    maxout_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>(y, ldy, bias, half, n, (float*)out_op, ldo, out_maps, B, T);
+  else
+    maxout_kernel<__nv_bfloat16><<<grid, 256, 0, (cudaStream_t)stream>>>(y, ldy, bias, half, n, (__nv_bfloat16*)out_op,
+                                                                        ldo, out_maps, B, T);
+  return check_launch("rgp_maxout");
+}
+
+}  // extern "C"

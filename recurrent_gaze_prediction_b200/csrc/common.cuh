@@ -89,6 +89,14 @@ __device__ __forceinline__ RowInfo make_row(const rgp_tapgemm_args& a, int m) {
     case RGP_EPI_STORE_OP:
       r.valid = true;
       break;
+    case RGP_EPI_UP7: {   // rows = the 8x8 p-layout blocks (a,b) of the bottom state; hy, hx = 7a, 7b (operand coordinates)
+      int f = m / a.S, q = m - f * a.S;
+      int ya = q / a.Wp, xb = q - ya * a.Wp;
+      r.valid = true;
+      r.obase = (long long)f * a.So;
+      r.hy = 7 * ya; r.hx = 7 * xb;
+      break;
+    }
     case RGP_EPI_DHS: {   // M rows in the head-input layout (S=100, Wp=10, data at +3,+3) -> recurrence q-row
       int f = m / a.S, q = m - f * a.S;
       int ya = q / a.Wp, xb = q - ya * a.Wp;
@@ -206,6 +214,17 @@ __device__ __forceinline__ void epi_elem(const rgp_tapgemm_args& a, const RowInf
     }
     case RGP_EPI_DX_DENSE: {
       if (r.valid) OpT<TA>::st((TA*)a.out_op + r.orow * a.ldo + n, acc);
+      break;
+    }
+    case RGP_EPI_UP7: {   // gaze_grcn_cascade.py:326-331: column n = (ry*7+rx)*P + co -> pixel (7a+ry-2, 7b+rx-2)
+      const int pix = n / a.P;
+      if (pix < 49) {
+        const int co = n - pix * a.P;
+        const int ry = pix / 7, rx = pix - ry * 7;
+        const int Y = r.hy + ry, X = r.hx + rx;             // operand coordinates = pixel + 2
+        if (Y >= 2 && Y < 51 && X >= 2 && X < 51)
+          OpT<TA>::st((TA*)a.out_op + (r.obase + (long long)Y * a.Wo + X) * a.ldo + co, acc);
+      }
       break;
     }
     case RGP_EPI_HEAD: {  // composed head: class n = ry*6+rx -> logits[b,t,6a+ry-3,6b+rx-3]

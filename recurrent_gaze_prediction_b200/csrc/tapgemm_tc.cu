@@ -183,6 +183,17 @@ __device__ __forceinline__ void epi_row32(const rgp_tapgemm_args& a, const RowIn
       case RGP_EPI_STORE_OP:
         stbf32((TA*)a.out_op + (long long)r.m * a.ldo + n0, v);
         return;
+      case RGP_EPI_UP7: {      // 32 consecutive channels of one pixel (P % 32 == 0): one 64-byte store
+        if (a.P % 32 != 0) break;
+        const int pix = n0 / a.P;
+        if (pix >= 49) return;
+        const int co = n0 - pix * a.P;
+        const int ry = pix / 7, rx = pix - ry * 7;
+        const int Y = r.hy + ry, X = r.hx + rx;
+        if (Y >= 2 && Y < 51 && X >= 2 && X < 51)
+          stbf32((TA*)a.out_op + (r.obase + (long long)Y * a.Wo + X) * a.ldo + co, v);
+        return;
+      }
       case RGP_EPI_STORE_OP_P:
         if (r.valid) stbf32((TA*)a.out_op + r.prow * a.ldo + n0, v);
         return;
@@ -312,7 +323,9 @@ struct Cfg {
 // Only the per-tap weight boxes still stream: L2->SMEM traffic per k-chunk drops from ntaps*(16 KB + W) to
 // slab + ntaps*W (i2h: 432 -> 307 KB, head: 352 -> 117 KB).
 struct SlabCfg {
-  int rows;      // slab rows (multiple of 8)
+  int rows;      // slab rows (multiple of 8 * nbox)
+  int nbox;      // TMA boxes per slab (a box is <= 256 rows): rows / nbox rows each, stacked in shared memory
+  int boxrows;
   int bytes;     // slab slot bytes (rows * 128 rounded up to 1024)
   int min_off;   // smallest tap offset
   int nw;        // weight-ring stages
@@ -382,7 +395,9 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         for (int kc = 0; kc < kchunks; ++kc) {
           mbar_wait(&aempty[as], aph ^ 1);
           mbar_expect_tx(&afull[as], (uint32_t)sc.rows * BK * 2);
-          tma_load_2d(slab0 + as * sc.bytes, &tmA, &afull[as], kc * BK, m0 + sc.min_off);
+          for (int bx = 0; bx < sc.nbox; ++bx)     // boxrows % 8 == 0: every box starts on a swizzle-atom boundary
+            tma_load_2d(slab0 + as * sc.bytes + bx * sc.boxrows * (BK * 2), &tmA, &afull[as], kc * BK,
+                        m0 + sc.min_off + bx * sc.boxrows);
           for (int tap = 0; tap < a.ntaps; ++tap) {
             mbar_wait(&empty[ws], wph ^ 1);
             mbar_expect_tx(&full[ws], kWBytes);
@@ -663,25 +678,29 @@ template <int BN>
 int launch(const rgp_tapgemm_args& a, cudaStream_t s) {
   using C = Cfg<BN>;
   // slab geometry: all taps of the tile inside one TMA box of <= 256 rows
-  SlabCfg sc{0, 0, 0, 0, 2};
+  SlabCfg sc{0, 1, 0, 0, 0, 0, 2};
   bool slab = false;
   // Narrow tiles (the N = 48 head GEMM) keep the per-tap boxes: they are bound by the cost of their small MMAs (~150 clk per
   // 128x48x16 MMA, 580 clk per k-step whatever the operand traffic), measured 0.87 ms per-tap vs 0.95 ms slab with an 8-stage
   // weight ring and 0.93 ms with 24 stages and 4 slab slots (profiles/r01_notes.md passes 7 and 18).
-  if (a.ntaps > 1 && BN >= 128 && slab_enabled()) {
+  // ... except many-tap narrow GEMMs (the cascade's 5x5 top cell: 25 taps, N = 16, K = 64): there the per-tap A boxes
+  // (25 x 16 KB per 128 rows) are the whole cost and the slab (128 + 4*51+4 rows, two TMA boxes) removes them.
+  if (a.ntaps > 1 && (BN >= 128 || a.ntaps > 16) && slab_enabled()) {
     int mn = a.tap_off[0], mx = a.tap_off[0];
     for (int i = 1; i < a.ntaps; ++i) { mn = a.tap_off[i] < mn ? a.tap_off[i] : mn; mx = a.tap_off[i] > mx ? a.tap_off[i] : mx; }
     sc.rows = (BM + (mx - mn) + 7) & ~7;
+    if (sc.rows > 256) { sc.nbox = 2; sc.rows = (sc.rows + 15) & ~15; }
+    sc.boxrows = sc.rows / sc.nbox;
     sc.bytes = (sc.rows * BK * 2 + 1023) & ~1023;
     sc.min_off = mn;
     sc.slots = (BN <= 64) ? kSlabMaxSlots : 2;      // narrow tiles finish a k-chunk faster than a slab load takes
     const int fixed = 1024 + kSlabBarBytes + kEpiScratchBytes + sc.slots * sc.bytes;
     sc.nw = (kSmemBudget - fixed) / (BN * BK * 2);
     if (sc.nw > kSlabMaxW) sc.nw = kSlabMaxW;
-    slab = sc.rows <= 256 && sc.nw >= 3;
+    slab = sc.boxrows <= 256 && sc.nw >= 3;
   }
   CUtensorMap tmA, tmB;
-  int rc = make_map(a.A, a.rowsA, a.lda, a.K, slab ? sc.rows : BM, &tmA);
+  int rc = make_map(a.A, a.rowsA, a.lda, a.K, slab ? sc.boxrows : BM, &tmA);
   if (rc) return rc;
   rc = make_map(a.Bw, (long long)a.ntaps * a.N, a.K, a.K, BN, &tmB);
   if (rc) return rc;

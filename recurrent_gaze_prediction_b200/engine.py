@@ -97,7 +97,11 @@ class GazeEngine(object):
         self.device = torch.device(device)
         self.lib = lib if lib is not None else L.get_lib()
         self.lstm = model == "gaze_lstm"
+        # head: "deconv" (gaze_grcn.py:292-366), "fc" (gaze_grcn77.py:206-211) or "none" (the cascade's bottom level,
+        # gaze_grcn_cascade.py:286-312: the states h_1..h_T are the product, CascadeEngine consumes them)
         self.head = head or ("fc" if model == "gaze_grcn77" else "deconv")
+        if self.head not in ("deconv", "fc", "none"):
+            raise ValueError("unknown head %r" % (self.head,))
         if self.head == "deconv" and G != 7:
             raise ValueError("the transposed-conv head (gaze_grcn.py:326-358) is defined for a 7x7 grid only")
         self.use_bn = (model == "gaze_grcn" and self.head == "deconv")
@@ -150,9 +154,10 @@ class GazeEngine(object):
             spec["w2"] = (5, 5, 32, 64)
             spec["w3"] = (7, 7, 12, 32)
             spec["out_W"] = (12,)
-        else:
+        elif self.head == "fc":
             spec["out_W"] = (Ch,)
-        spec["out_b"] = (1,)
+        if self.head != "none":
+            spec["out_b"] = (1,)
         if self.use_bn:
             spec["bn_gamma"] = (self.Tp, Ch)
             spec["bn_beta"] = (self.Tp, Ch)
@@ -217,8 +222,9 @@ class GazeEngine(object):
             host["w1"] = np.asarray(p["Upsampling/weight1"], dtype=np.float32)
             host["w2"] = np.asarray(p["Upsampling/weight2"], dtype=np.float32)
             host["w3"] = np.asarray(p["Upsampling/weight3"], dtype=np.float32)
-        host["out_W"] = np.asarray(p["out_W"], dtype=np.float32).reshape(-1)
-        host["out_b"] = np.asarray(p["out_b"], dtype=np.float32).reshape(-1)
+        if self.head != "none":
+            host["out_W"] = np.asarray(p["out_W"], dtype=np.float32).reshape(-1)
+            host["out_b"] = np.asarray(p["out_b"], dtype=np.float32).reshape(-1)
         if self.use_bn:
             host["bn_gamma"] = np.asarray(p["bn_gamma"], dtype=np.float32)
             host["bn_beta"] = np.asarray(p["bn_beta"], dtype=np.float32)
@@ -261,9 +267,10 @@ class GazeEngine(object):
             out["Upsampling/weight2"] = get("w2").copy()
             out["Upsampling/weight3"] = get("w3").copy()
             out["out_W"] = get("out_W").reshape(12, 1).copy()
-        else:
+        elif self.head == "fc":
             out["out_W"] = get("out_W").reshape(Ch, 1).copy()
-        out["out_b"] = get("out_b").copy()
+        if self.head != "none":
+            out["out_b"] = get("out_b").copy()
         if self.use_bn:
             out["bn_gamma"] = get("bn_gamma").copy()
             out["bn_beta"] = get("bn_beta").copy()

@@ -10,9 +10,9 @@ from __future__ import annotations
 import ctypes as C
 import os
 
-RGP_MAX_TAPS = 16
+RGP_MAX_TAPS = 32
 (EPI_STORE_F32, EPI_PROJ, EPI_GRU_ZR, EPI_GRU_C, EPI_HEAD, EPI_STORE_OP_P, EPI_STORE_OP,
- EPI_BWD_RH, EPI_BWD_H, EPI_DHS, EPI_DX_DENSE) = range(11)
+ EPI_BWD_RH, EPI_BWD_H, EPI_DHS, EPI_DX_DENSE, EPI_UP7) = range(12)
 
 _vp, _i, _ll, _f, _d = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_double
 
@@ -101,6 +101,9 @@ _SIGS = {
     "rgp_dense_gru_ru": [_vp, _i, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
     "rgp_dense_gru_c": [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
     "rgp_dense_logits": [_vp, _i, _vp, _vp, _i, _i, _i, _vp],
+    # cascade top level (gaze_grcn_cascade.py:343-424)
+    "rgp_topgru_seq_fwd": [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _vp, _i, _i, _i, _vp],
+    "rgp_maxout": [_vp, _i, _vp, _i, _i, _vp, _i, _vp, _i, _i, _i, _vp],
     # saliency metrics (evaluation_metrics.py)
     "rgp_metrics_prep": [_vp, _vp, _i, _i, _i, _vp],
     "rgp_resize_bicubic": [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp],
