@@ -503,6 +503,62 @@ def bench_config4(args, H):
     return out
 
 
+def bench_config5(args, H):
+    """BASELINE config 5: the cascade (gaze_grcn_cascade.py: bottom ConvGRU 256 -> 11x11/s7 transposed conv -> 5x5
+    ConvGRU on 49x49 -> two maxout FCs) through its model class, inference at 64 clips x T=35, bf16; then the saliency
+    suite (sim, cc, NSS, AUC-Judd, AUC-Borji, shuffled AUC) of 1024 of ITS predicted maps against 360x480 fixation maps
+    through MetricsEngine.evaluate_batch (the product's evaluation call)."""
+    from recurrent_gaze_prediction_b200 import evaluation_metrics as EM
+    from recurrent_gaze_prediction_b200 import synthetic as SY
+    H = Harness(H.dev, H.local, 0, 1)
+    B, T = 64, 35
+    cargs = argparse.Namespace(**vars(args))
+    cargs.model, cargs.batch, cargs.T, cargs.grid, cargs.mode = "gaze_grcn_cascade", B, T, 7, "inference"
+    model = build_model(cargs, {"rank": 0, "world_size": 1, "allreduce": None}, B, 1, False, "bf16", H.dev)
+    eng = model.engine
+    feat_h, gt_h, _, gt_pool = make_inputs(0, B, T, 7, 49, torch.bfloat16)
+    model.c3d_input.copy_(feat_h)
+    model.gt_gazemap.copy_(gt_h)
+    model.run(train=False, sync=True)
+    ms, _, _ = H.timed(lambda: model.run(train=False, sync=False), max(4, args.steps), 3)
+    st = eng.time_stages(model.c3d_input, model.gt_gazemap, iters=3)
+    out = {"workload": "gaze_grcn_cascade inference, %d clips x T=%d, C3D 1024x7x7 -> bottom ConvGRU 256 -> 49x49x64 -> 5x5 "
+                       "ConvGRU (3 units) -> maxout FCs 7203-4802-2401-4802-2401, bf16 operands" % (B, T),
+           "api": "models.gaze_grcn_cascade.GazePredictionGRCN: run() on resident placeholders (one CUDA graph)",
+           "value": B * T / (ms * 1e-3), "unit": "frames/s", "ms_per_step": ms, "clips_per_gpu": B, "n_gpus": 1,
+           "gpu_launches": model._step_graph(False).kernels, "stage_ms": st,
+           "note": "the reference defines the cascade on the 7x7 C3D grid (its 11x11 / stride-7 transposed conv maps 7 -> 49); "
+                   "a 14x14 cascade does not exist in it"}
+    # ---- full saliency evaluation of the cascade's own maps at VAS scale
+    N = 1024
+    pred = model.predicted_gazemaps.reshape(B * T, 49, 49)[:N].float().cpu().numpy()
+    rng = np.random.RandomState(3)
+    reps = (N + gt_pool.shape[0] * T - 1) // (gt_pool.shape[0] * T)
+    gtm = np.tile(gt_pool.reshape(-1, 49, 49), (reps, 1, 1))[:N]
+    fix64 = SY.make_fixationmaps(rng, gtm[:64, None], 360, 480).reshape(64, 360, 480)
+    fix = np.tile(fix64, (N // 64, 1, 1))
+    union = (fix64[:10].sum(axis=0) > 0).astype(np.uint8)
+    me = EM.MetricsEngine(device=H.dev, chunk=N)
+    mets = ("sim", "cc", "NSS", "AUC_Judd", "AUC_Borji", "AUC_shuffled")
+    np.random.seed(0)
+    r = me.evaluate_batch(pred, gtm, fix, union=union, metrics=mets)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(3):
+        np.random.seed(0)
+        r = me.evaluate_batch(pred, gtm, fix, union=union, metrics=mets)
+    torch.cuda.synchronize()
+    dt = (time.perf_counter() - t0) / 3
+    out["evaluation"] = {"call": "MetricsEngine.evaluate_batch(pred[1024,49,49], gt, fix[1024,360,480], union, metrics=%s), "
+                                 "host arrays in, host scores out (H2D of the fixation maps and the host-drawn random index "
+                                 "tensors included)" % (mets,),
+                         "frames_per_s": N / dt, "ms_per_1024_frames": dt * 1e3,
+                         "mean_scores": {k: float(np.nanmean(v)) for k, v in r.items()}}
+    del model
+    torch.cuda.empty_cache()
+    return out
+
+
 # ----------------------------------------------------------------------------------------------
 def main():
     args = parse()
@@ -550,6 +606,10 @@ def main():
                 sub["config4"] = bench_config4(args, H)
             except Exception as e:       # a sub-record must not take the headline down
                 sub["config4"] = {"error": "%s: %s" % (type(e).__name__, e)}
+            try:
+                sub["config5"] = bench_config5(args, H)
+            except Exception as e:
+                sub["config5"] = {"error": "%s: %s" % (type(e).__name__, e)}
             try:
                 sys.path.insert(0, os.path.join(ROOT, "tools"))
                 import bench_metrics

@@ -101,21 +101,30 @@ class CascadeEngine(object):
             n = int(np.prod(shp))
             self.offsets[k] = (off, n)
             off += _pad(n, 64)
-        self.nparams = off
-        self.params = torch.zeros(off, dtype=torch.float32, device=self.device)
-        self.params_op = self.params if self.dtype == 0 else torch.zeros(off, dtype=self.tdt, device=self.device)
+        self.ntop = off
+        self.tparams = torch.zeros(off, dtype=torch.float32, device=self.device)
+        self.tparams_op = self.tparams if self.dtype == 0 else torch.zeros(off, dtype=self.tdt, device=self.device)
+
+    @property
+    def nparams(self):
+        return self.bottom.nparams + self.ntop
+
+    @property
+    def params(self):
+        """bottom-level and top-level flat parameter buffers, concatenated (a copy: checkpoints, inspection)"""
+        return torch.cat([self.bottom.params, self.tparams])
 
     def _ptr(self, name, buf=None):
         off, _ = self.offsets[name]
-        buf = self.params if buf is None else buf
+        buf = self.tparams if buf is None else buf
         return buf.data_ptr() + off * buf.element_size()
 
     def _pop(self, name):
-        return self._ptr(name, self.params_op)
+        return self._ptr(name, self.tparams_op)
 
     def view(self, name, buf=None):
         off, n = self.offsets[name]
-        buf = self.params if buf is None else buf
+        buf = self.tparams if buf is None else buf
         return buf[off:off + n].view(*self.spec[name])
 
     def load_tf_params(self, p):
@@ -155,16 +164,47 @@ class CascadeEngine(object):
             op[:NH, :kin] = W[:, :NH].T
             op[NHP:NHP + NH, :kin] = W[:, NH:].T
             host[nm + "_b"][:NH], host[nm + "_b"][NHP:NHP + NH] = b[:NH], b[NH:]
-        flat = np.zeros(self.nparams, dtype=np.float32)
+        flat = np.zeros(self.ntop, dtype=np.float32)
         for k, v in host.items():
             off, n = self.offsets[k]
             flat[off:off + n] = v.reshape(-1)
-        self.params.copy_(torch.from_numpy(flat))
+        self.tparams.copy_(torch.from_numpy(flat))
         self.refresh_operands()
+
+    def op_to_tf(self, flat):
+        """Inverse of load_tf_params on a flat host array laid out like `params` (bottom | top)."""
+        flat = np.asarray(flat)
+        nb = self.bottom.nparams
+        out = OrderedDict()
+        for k, v in self.bottom.op_to_tf(flat[:nb]).items():
+            out[("RCNBottom/" + k) if k.startswith("GRU_Conv_") else k] = v
+        top = flat[nb:]
+        g = lambda k: top[self.offsets[k][0]:self.offsets[k][0] + self.offsets[k][1]].reshape(self.spec[k])
+        up = g("up_op").reshape(4, UPN, self.Ch)
+        wu = np.zeros((11, 11, UPC, self.Ch), dtype=flat.dtype)
+        for di in range(2):
+            for dj in range(2):
+                ny, nx = (7 if di == 0 else 4), (7 if dj == 0 else 4)
+                blk = up[di * 2 + dj, :49 * UPC].reshape(7, 7, UPC, self.Ch)
+                wu[7 * di:7 * di + ny, 7 * dj:7 * dj + nx] = blk[:ny, :nx]
+        out["Upsampling/weight"] = wu
+        wx = np.zeros((5, 5, self.top_in, 3 * NU), dtype=flat.dtype)
+        wx[:, :, :UPC, :] = g("Wtx_op").reshape(25, 16, UPC)[:, :3 * NU, :].transpose(0, 2, 1).reshape(5, 5, UPC, 3 * NU)
+        if self.top_in == UPC + 1:
+            wx[:, :, UPC, :] = g("wsal").reshape(5, 5, 3 * NU)
+        uzr, uc = g("uzr").reshape(5, 5, NU, 2 * NU), g("uc").reshape(5, 5, NU, NU)
+        for nm, w in (("Wz", wx[..., :NU]), ("Uz", uzr[..., :NU]), ("Wr", wx[..., NU:2 * NU]), ("Ur", uzr[..., NU:]),
+                      ("W", wx[..., 2 * NU:]), ("U", uc)):
+            out["RCNGaze/GRU_Conv_" + nm] = np.ascontiguousarray(w)
+        for nm, kin in (("fc1", NFLAT), ("fc2", NH)):
+            op, b = g(nm + "_op"), g(nm + "_b")
+            out["LastProjection/%s/weights" % nm] = np.concatenate([op[:NH, :kin].T, op[NHP:NHP + NH, :kin].T], axis=1)
+            out["LastProjection/%s/bias" % nm] = np.concatenate([b[:NH], b[NHP:NHP + NH]])
+        return out
 
     def refresh_operands(self):
         if self.dtype != 0:
-            self.lib.rgp_cast(self.params.data_ptr(), self.params_op.data_ptr(), self.nparams, self.dtype, self._s())
+            self.lib.rgp_cast(self.tparams.data_ptr(), self.tparams_op.data_ptr(), self.ntop, self.dtype, self._s())
 
     # ------------------------------------------------------------------ buffers
     def _alloc(self):

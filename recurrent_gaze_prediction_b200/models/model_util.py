@@ -97,3 +97,32 @@ def init_parameters_dense(dim_proj=32, grid=7, dim_feature=1024, GH=49, GW=49, s
     p["proj_out_W"] = rng.uniform(-0.1, 0.1, size=(H, GH * GW))
     p["proj_out_b"] = np.zeros(GH * GW)
     return p
+
+
+def xavier_uniform(rng, fan_in, fan_out):
+    """tf.contrib.layers.xavier_initializer(uniform=True) on a [fan_in, fan_out] matrix (gaze_grcn_cascade.py:390,405)."""
+    lim = math.sqrt(6.0 / (fan_in + fan_out))
+    return rng.uniform(-lim, lim, size=(fan_in, fan_out))
+
+
+def init_parameters_cascade(hidden=256, top_in=64, units=3, dim_proj=512, dim_feature=1024, seed=0, stddev=1e-4):
+    """Variables of the cascade (gaze_grcn_cascade.py) under scope-qualified TF names, in creation order: proj_c3d_W/b
+    U(-0.1,0.1) (:268-269); RCNBottom cell, 3x3, truncated normal sigma=1e-4 (:52-81 via :287); Upsampling/weight
+    [11,11,64,hidden] Xavier-uniform (:317-321); RCNGaze cell, 5x5, `top_in` input channels, 3 units (:346-351: declared
+    65, fed 64 - see cascade_engine.py); LastProjection/fc1 [7203,4802] and fc2 [2401,4802] Xavier-uniform with zero
+    biases (:388-411)."""
+    rng = np.random.RandomState(seed)
+    p = OrderedDict()
+    p["proj_c3d_W"] = rng.uniform(-0.1, 0.1, size=(dim_feature, dim_proj))
+    p["proj_c3d_b"] = rng.uniform(-0.1, 0.1, size=(dim_proj,))
+    for scope, k, cin, n in (("RCNBottom", 3, dim_proj, hidden), (None, 0, 0, 0), ("RCNGaze", 5, top_in, units)):
+        if scope is None:
+            p["Upsampling/weight"] = xavier_uniform_conv2d(rng, (11, 11, 64, hidden))
+            continue
+        for nm, ci in (("Wz", cin), ("Uz", n), ("Wr", cin), ("Ur", n), ("W", cin), ("U", n)):
+            p[scope + "/GRU_Conv_" + nm] = truncated_normal(rng, (k, k, ci, n), stddev)
+    p["LastProjection/fc1/weights"] = xavier_uniform(rng, 49 * 49 * units, 4802)
+    p["LastProjection/fc1/bias"] = np.zeros(4802)
+    p["LastProjection/fc2/weights"] = xavier_uniform(rng, 2401, 4802)
+    p["LastProjection/fc2/bias"] = np.zeros(4802)
+    return p

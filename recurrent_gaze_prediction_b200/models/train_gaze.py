@@ -30,6 +30,8 @@ def get_model_class(name):
         from .gaze_grcn77 import GazePredictionGRCN as TheModel, CONSTANTS, GRUModelConfig
     elif name == 'gaze_lstm':
         from .gaze_lstm import GazePredictionLSTM as TheModel, CONSTANTS, GRUModelConfig
+    elif name == 'gaze_grcn_cascade':
+        from .gaze_grcn_cascade import GazePredictionGRCN as TheModel, CONSTANTS, GRUModelConfig
     else:
         raise NotImplementedError(name)
     return TheModel, CONSTANTS, GRUModelConfig

@@ -84,6 +84,17 @@ class EmuLib(object):
                 ok = (ya < 9) & (xb < 9) & (Y >= 0) & (Y < 49) & (X >= 0) & (X < 49)
                 out[b[ok], t[ok], Y[ok], X[ok]] = acc[ok, n] + bias
             return 0
+        if e == L.EPI_UP7:       # gaze_grcn_cascade.py:326-331 as a 4-tap GEMM over the 8x8 p-layout blocks
+            f, q = np.divmod(rows, a.S)
+            ya, xb = np.divmod(q, a.Wp)
+            nrows = (int(f.max()) + 1) * a.So
+            out = arr(a.out_op, (nrows, a.ldo))
+            for pix in range(49):
+                ry, rx = divmod(pix, 7)
+                Y, X = 7 * ya + ry, 7 * xb + rx
+                ok = (Y >= 2) & (Y < 51) & (X >= 2) & (X < 51)
+                out[(f * a.So + Y * a.Wo + X)[ok], :a.P] = acc[ok, pix * a.P:(pix + 1) * a.P]
+            return 0
         if e == L.EPI_DHS:
             f, q = np.divmod(rows, a.S)
             ya, xb = np.divmod(q, a.Wp)
@@ -157,6 +168,57 @@ class EmuLib(object):
                 out2[orow[valid]] = v
             return 0
         raise NotImplementedError(e)
+
+    # -------------------------------------------------------------- cascade top level (gaze_grcn_cascade.py:343-424)
+    def rgp_topgru_seq_fwd(self, xg, ldx, So, Wo, uzr, uc, sal, wsal, state, carry, og_op, ldo, h_f32, B, T, dtype, stream):
+        assert dtype == 0
+        X = arr(xg, (T * B * So, ldx))
+        Wzr, Wc = arr(uzr, (25, 3, 6)).astype(np.float64), arr(uc, (25, 3, 3)).astype(np.float64)
+        og = arr(og_op, (T * B, ldo))
+        hf = arr(h_f32, (T * B, 7203)) if h_f32 else None
+        ws = arr(wsal, (25, 9)).astype(np.float64) if sal else None
+        S = arr(sal, (B, T, 49, 49)) if sal else None
+        yy, xx = np.mgrid[0:49, 0:49]
+        for b in range(B):
+            h = np.zeros((49, 49, 3))
+            if carry and state:
+                h = arr(state, (B, 7203))[b].reshape(49, 49, 3).astype(np.float64)
+            for t in range(T):
+                f = t * B + b
+                x9 = X[f * So + yy * Wo + xx][:, :, :9].astype(np.float64)
+                if S is not None:
+                    sp = np.pad(S[b, t].astype(np.float64), 2)
+                    for tap in range(25):
+                        ky, kx = divmod(tap, 5)
+                        x9 = x9 + sp[ky:ky + 49, kx:kx + 49, None] * ws[tap][None, None, :]
+                hp = np.pad(h, ((2, 2), (2, 2), (0, 0)))
+                a = x9[:, :, :6].copy()
+                for tap in range(25):
+                    ky, kx = divmod(tap, 5)
+                    a += hp[ky:ky + 49, kx:kx + 49, :] @ Wzr[tap]
+                z, r = 1 / (1 + np.exp(-a[:, :, :3])), 1 / (1 + np.exp(-a[:, :, 3:]))
+                rp = np.pad(r * h, ((2, 2), (2, 2), (0, 0)))
+                c = x9[:, :, 6:9].copy()
+                for tap in range(25):
+                    ky, kx = divmod(tap, 5)
+                    c += rp[ky:ky + 49, kx:kx + 49, :] @ Wc[tap]
+                h = z * h + (1 - z) * np.tanh(c)
+                og[f, :7203] = h.reshape(-1)
+                if hf is not None:
+                    hf[f] = h.reshape(-1)
+            if state:
+                arr(state, (B, 7203))[b] = h.reshape(-1)
+        return 0
+
+    def rgp_maxout(self, y, ldy, bias, half, n, out_op, ldo, out_maps, B, T, dtype, stream):
+        Y = arr(y, (B * T, ldy))
+        bb = arr(bias, (half + n,))
+        v = np.maximum(np.maximum(Y[:, :n] + bb[:n], 0), np.maximum(Y[:, half:half + n] + bb[half:half + n], 0))
+        if out_op:
+            arr(out_op, (B * T, ldo))[:, :n] = v
+        if out_maps:
+            arr(out_maps, (B, T, n))[:] = v.reshape(T, B, n).transpose(1, 0, 2)
+        return 0
 
     # -------------------------------------------------------------- elementwise
     def rgp_pack_c3d(self, c3d, out, B, T, Cc, P, dtype, stream):

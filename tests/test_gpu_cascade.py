@@ -1,0 +1,61 @@
+"""GPU parity of the cascade (BASELINE config 5 model; gaze_grcn_cascade.py:189-452) against the float64 oracle:
+fp32 engine 1e-4, bf16 tcgen05 engine 2e-2 of each map's peak (the north star's bars), per stage."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import model_oracle as O
+from recurrent_gaze_prediction_b200 import synthetic as SY
+from recurrent_gaze_prediction_b200.cascade_engine import CascadeEngine
+
+pytestmark = pytest.mark.gpu
+TOL = {0: 1e-4, 1: 2e-2}
+
+
+def _run(dtype, B, T, top_in, seq=None, seed=3):
+    p = O.init_params_cascade(top_in=top_in, seed=seed, regime="S", fc_bias_scale=0.05)
+    rng = np.random.RandomState(5)
+    c3d = SY.make_c3d(rng, B, T)
+    gt, _ = SY.make_gazemaps(rng, B, T, 49, 49)
+    sal = rng.uniform(size=(B, T, 49, 49)).astype(np.float32) if top_in == 65 else None
+    eng = CascadeEngine(B=B, T=T, dtype=dtype, device="cuda", top_in=top_in, keep_top_states=True, seq=seq)
+    eng.load_tf_params(p)
+    pred = eng.forward(c3d=torch.from_numpy(c3d).cuda(), gt=torch.from_numpy(gt).cuda(),
+                       frm_sal=None if sal is None else torch.from_numpy(sal).cuda())
+    torch.cuda.synchronize()
+    net = {}
+    with torch.no_grad():
+        ref = O.cascade_network(O.to_torch(p), torch.tensor(c3d, dtype=torch.float64),
+                                frm_sal=None if sal is None else torch.tensor(sal, dtype=torch.float64), net=net)
+        ref_loss = float(O.cascade_loss(ref, torch.tensor(gt, dtype=torch.float64)))
+    return eng, pred.cpu().numpy(), ref.numpy(), ref_loss, net
+
+
+@pytest.mark.parametrize("dtype,top_in,B,T", [(0, 64, 2, 3), (1, 64, 2, 3), (0, 65, 2, 2), (1, 65, 3, 4), (1, 64, 5, 35)])
+def test_cascade_forward_vs_oracle(dtype, top_in, B, T):
+    eng, pred, ref, ref_loss, net = _run(dtype, B, T, top_in)
+    tol = TOL[dtype]
+    # intermediate tensors: this repo's own bars - max over ~12 k saturated state elements per step, 2x the map bar for
+    # bf16 (measured 2.1e-2 at T = 35, flat in t); the north-star bar applies to the predicted maps below
+    stol = tol if dtype == 0 else 2 * tol
+    for t in range(T):
+        h_ref = net["rcn_outputs"][t].numpy()
+        assert np.abs(eng.read_state(t + 1).cpu().numpy() - h_ref).max() <= stol * max(1.0, np.abs(h_ref).max()), ("bottom", t)
+        u_ref = net["rcn_upsampled_outputs"][t].numpy()
+        assert np.abs(eng.read_upsampled(t).cpu().numpy() - u_ref).max() <= stol * np.abs(u_ref).max(), ("upsample", t)
+        g_ref = net["top_outputs"][t].numpy()
+        assert np.abs(eng.read_top_state(t).cpu().numpy() - g_ref).max() <= stol * max(1.0, np.abs(g_ref).max()), ("top", t)
+    err = np.abs(pred - ref).max(axis=(2, 3)) / ref.max(axis=(2, 3))
+    assert ref.max() > 1e-3
+    assert err.max() <= tol, err.max(axis=0)
+    assert abs(float(eng.loss.cpu()[0]) - ref_loss) <= tol * abs(ref_loss)
+
+
+def test_cascade_persistent_bottom_matches_per_step():
+    """the bottom level through the persistent gru_seq kernel (the choice at bench batch sizes) == per-step GEMMs"""
+    a = _run(1, 4, 6, 64, seq=True)
+    b = _run(1, 4, 6, 64, seq=False)
+    assert a[0].use_seq and not b[0].use_seq
+    assert np.abs(a[1] - b[1]).max() <= 2e-2 * np.abs(b[1]).max()
+    err = np.abs(a[1] - a[2]).max(axis=(2, 3)) / a[2].max(axis=(2, 3))
+    assert err.max() <= 2e-2
