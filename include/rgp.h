@@ -114,6 +114,38 @@ int rgp_convgru_seq_fwd(const rgp_gru_seq_args* a, void* stream);
  * HOST array of n <= 32*12 values laid out [step][event] (events listed in csrc/gru_seq.cu).  Synchronises the device. */
 int rgp_convgru_seq_profile(unsigned long long* host_out, int n);
 
+/* Persistent ConvLSTM recurrence (gaze_lstm.py:103-133 as written, unrolled by :260-286): ALL T steps in ONE launch, for
+ * any grid (frames may straddle the 128-row tiles: 14x14, BASELINE config 4).  CTA (tile, split) owns 128 q-rows and
+ * Ch/nsplit = 16 channels of all three hidden convolutions for the whole sequence: its slice of W_h (9 taps x 3 gates x
+ * 16 output channels x Ch, 110 KB at Ch = 128) is loaded into shared memory ONCE and stays there; per step it fetches
+ * the 128 + 2*Wp+2 state rows it needs as one TMA slab, runs 9 x Ch/16 tcgen05 MMAs (N = 48) into TMEM and applies the
+ * gate maths in the epilogue (cell state in registers, peepholes in shared memory).  A step's halo rows come from the
+ * two neighbouring tiles: tiles publish "step t written" through per-tile counters in `flags` (release/acquire at gpu
+ * scope + async-proxy fences), so there is no grid-wide barrier and no per-step launch.  All CTAs must be co-resident
+ * (cooperative launch): mtiles * nsplit <= SMs.  bf16 operands (dtype 1) only.
+ * Buffers are those of the per-step path (rgp_tapgemm STORE_F32 + rgp_lstm_gates). */
+typedef struct rgp_lstm_seq_args {
+  void* Hop; long long rowsH;     /* bf16 p-layout state, slab t = h_t (t = 0..T), slab stride B*S rows                  */
+  float* Hf;                      /* fp32 master of the same                                                               */
+  float* Cf;                      /* fp32 cell, p-layout [B*S + tail, Ch]: in = c_0, out = c_T                             */
+  const void* Wh;                 /* [9*3Ch, Ch] bf16 op layout: row tap*3Ch + gate*Ch + out channel (gates i | f | o)     */
+  const float* Xg;                /* [T*B*S, 4Ch] fp32 input-half pre-activations, columns i | f | c | o                   */
+  const float* wci; const float* wcf; const float* wco;   /* peepholes [G, G, Ch] fp32                                    */
+  void* HS;                       /* bf16 head-input layout [T*B*So, Ch] or NULL                                           */
+  float* save;                    /* train: [T, B*S, 5Ch] fp32 (i, f, g, o, c_{t-1}) as rgp_lstm_gates stores it, or NULL   */
+  int* flags;                     /* workspace: mtiles + 1 int32, ZEROED by the caller before every launch; after the launch
+                                     flags[mtiles] != 0 reports a dependency time-out (results invalid)                  */
+  int B, T, G, Ch;
+  int So, Wo, pado;
+  int dtype;                      /* must be 1                                                                             */
+} rgp_lstm_seq_args;
+int rgp_convlstm_seq_fwd(const rgp_lstm_seq_args* a, void* stream);
+/* 1 if rgp_convlstm_seq_fwd can run this shape on the current device (all mtiles * Ch/16 CTAs co-resident), else 0 */
+int rgp_convlstm_seq_fits(int B, int G, int Ch);
+/* Profiling hook: phase timestamps (globaltimer ns) CTA 0 recorded during the last rgp_convlstm_seq_fwd, copied to a
+ * HOST array of n <= 32*8 values laid out [step][event] (events listed in csrc/lstm_seq.cu).  Synchronises the device. */
+int rgp_convlstm_seq_profile(unsigned long long* host_out, int n);
+
 /* ---- model path ------------------------------------------------------------------------- */
 /* gaze_grcn.py:225-227 (tf.transpose NCHW->NHWC of the C3D blob) fused with the fp32->operand
  * cast and the [B,T]->time-major reorder: c3d [B,T,C,P] fp32 -> out [(t*B+b)*P + p, C]. */

@@ -1,0 +1,371 @@
+// lstm_seq.cu — persistent ConvLSTM recurrence: all T steps of gaze_lstm.py:103-133 (unrolled by :260-286) in ONE launch,
+// for any grid (BASELINE config 4: 14x14, T = 128, where a frame is 225 q-rows and straddles the 128-row MMA tiles).
+//
+// CTA (tile, split) owns 128 q-rows x NC = 16 channels of ALL THREE hidden convolutions (W_hi, W_hf, W_ho - the
+// candidate reuses W_hi and W_hc is dead in the reference, gaze_lstm.py:112-133) for the whole sequence:
+//   * its slice of W_h - 9 taps x Ch/64 k-chunks x (3 gates x 16 rows) x 128 B = 110 KB at Ch = 128 - is fetched ONCE by TMA
+//     and stays in shared memory ("recurrent weights resident in SMEM");
+//   * per step: the 128 + 2*Wp+2 state rows the tile's 9 taps touch arrive as one TMA slab per k-chunk (tap = constant row
+//     shift inside the slab, same trick as tapgemm_tc.cu / gru_seq.cu), 9 x Ch/16 tcgen05 MMAs (M = 128, N = 48, K = 16)
+//     accumulate i | f | o into 48 TMEM columns, and the epilogue (one thread = one row) applies the gate maths with the
+//     cell state kept in REGISTERS for all T steps and the peepholes in shared memory;
+//   * the halo rows of a step come from the two neighbouring tiles.  Every CTA bumps its tile's counter in `flags`
+//     (release, gpu scope) after its rows of h_t are in global memory; the producer of tile i waits until tiles i-1, i,
+//     i+1 have all nsplit splits of step t (acquire), then fences the async proxy and issues the slab TMA.  No grid-wide
+//     barrier, no per-step launch.  All CTAs are co-resident (cooperative launch), so the waits cannot dead-lock; a
+//     bounded spin reports a time-out through flags[mtiles] instead of hanging.
+// Warp roles: warp 0 = dependency wait + TMA producer, warp 1 = TMEM allocator + single-thread MMA issuer, warps 2..5 =
+// epilogue (TMEM lane group = warp % 4).
+#include "tc_common.cuh"
+
+namespace rgp {
+namespace lstmseq {
+
+using namespace tc;
+
+constexpr int BM = 128, BK = 64;
+constexpr int NC = 16;                    // channels per CTA
+constexpr int NG = 3 * NC;                // MMA N: i | f | o
+constexpr int NTHREADS = 192;
+constexpr int kMaxSlabRows = 160;         // 128 + 2*15 + 2 at G = 14
+constexpr int kMaxKch = 2;                // Ch <= 128: the weight slice must fit in shared memory
+constexpr int kWTileBytes = NG * BK * 2;  // 6144: one (tap, k-chunk) B operand
+constexpr int kSlabBytes = kMaxSlabRows * BK * 2;   // 20480
+constexpr int kTmemCols = 64;
+constexpr long long kSpinLimit = 4000000000LL;      // clock64 ticks (~2 s) before a dependency wait gives up
+
+// single-MUFU gates as everywhere on the bf16 engine (rel. error ~2^-11, below the 2^-9 rounding of the bf16 operands): the
+// accurate forms cost ~1700 instructions per thread and step, on the critical path of every step
+__device__ __forceinline__ float tanh_fast(float x) { float y; asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float sigm(float x) { return fmaf(0.5f, tanh_fast(0.5f * x), 0.5f); }
+// generic-proxy stores to GLOBAL memory -> async-proxy (TMA) reads: the .global form orders only that state space
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.global;" ::: "memory"); }
+__device__ __forceinline__ int ld_acquire(const int* p) {
+  int v;
+  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void red_release_add(int* p, int v) {
+  asm volatile("red.release.gpu.global.add.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void ld8(const float* p, float* v) {
+  asm volatile("ld.global.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7])
+               : "l"(p));
+}
+__device__ __forceinline__ void st8(float* p, const float* v) {
+  asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]),
+               "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7])
+               : "memory");
+}
+__device__ __forceinline__ void stbf16x16(__nv_bfloat16* p, const float v[16]) {
+  uint32_t u[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    __nv_bfloat162 b = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+    u[j] = *reinterpret_cast<uint32_t*>(&b);
+  }
+  asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(u[0]), "r"(u[1]), "r"(u[2]), "r"(u[3]),
+               "r"(u[4]), "r"(u[5]), "r"(u[6]), "r"(u[7])
+               : "memory");
+}
+
+// Phase timestamps (globaltimer ns) of CTA 0 for its first kTsSteps steps - rgp_convlstm_seq_profile().  Events:
+// 0 dependencies satisfied (producer) | 1 slab TMA issued | 2 last slab box landed (MMA warp) | 3 MMAs issued |
+// 4 accumulator seen by the epilogue | 5 gates done, operand rows stored | 6 fences + CTA barrier done (counter bumped)
+constexpr int kTsSteps = 32, kTsEvents = 8;
+__device__ unsigned long long g_lstm_ts[kTsSteps * kTsEvents];
+__device__ __forceinline__ void stamp(bool on, int t, int ev) {
+  if (on && t < kTsSteps) {
+    unsigned long long v;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(v));
+    g_lstm_ts[t * kTsEvents + ev] = v;
+  }
+}
+
+constexpr int kSmemW = 9 * kMaxKch * kWTileBytes;           // 110592
+constexpr int kSmemSlab = kMaxKch * kSlabBytes;             // 40960
+constexpr int kSmemPeep = 3 * NC * BM * (int)sizeof(float); // 24576
+constexpr int kSmemBytes = kSmemW + kSmemSlab + kSmemPeep + 256 + 1024;
+
+__global__ void __launch_bounds__(NTHREADS, 1)
+lstm_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ CUtensorMap tmW,
+                const rgp_lstm_seq_args a, const int slab_rows) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* wsm = smem;                                   // [tap][kc] tiles of 48 rows x 128 B (i | f | o)
+  uint8_t* slab = smem + kSmemW;                         // [kc] slab_rows x 128 B
+  float* peep = reinterpret_cast<float*>(smem + kSmemW + kSmemSlab);   // [gate][channel][row]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kSmemW + kSmemSlab + kSmemPeep);
+  uint64_t* wfull = bars;
+  uint64_t* fullA = bars + 1;                            // [kMaxKch]
+  uint64_t* acc_full = fullA + kMaxKch;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int Ch = a.Ch, G = a.G, Wp = G + 1, S = Wp * Wp;
+  const int nsplit = Ch / NC;
+  const int tile = (int)(blockIdx.x / nsplit), split = (int)(blockIdx.x % nsplit);
+  const int ch0 = split * NC;
+  const int M = a.B * S;
+  const int mtiles = (M + BM - 1) / BM;
+  const int m0 = tile * BM;
+  const int kch = Ch / BK;
+  int* const err = a.flags + mtiles;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmH) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmW) : "memory");
+    mbar_init(wfull, 1);
+    for (int i = 0; i < kMaxKch; ++i) mbar_init(&fullA[i], 1);
+    mbar_init(acc_full, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"((uint32_t)kTmemCols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== dependency wait + TMA producer =====================
+    if (lane == 0) {
+      // the weight slice, once: 9 taps x kch k-chunks x 3 gates, boxes of 16 rows x 64 columns
+      mbar_expect_tx(wfull, (uint32_t)(9 * kch * kWTileBytes));
+      for (int tap = 0; tap < 9; ++tap)
+        for (int kc = 0; kc < kch; ++kc)
+          for (int g = 0; g < 3; ++g)
+            tma_load_2d(wsm + (tap * kch + kc) * kWTileBytes + g * (NC * BK * 2), &tmW, wfull, kc * BK,
+                        tap * 3 * Ch + g * Ch + ch0);
+    }
+    // lanes 0..2 watch the counters of tiles (tile-1, tile, tile+1) in parallel: one L2 round trip per poll, not three
+    const int nb = tile - 1 + lane;
+    const bool watch = lane < 3 && nb >= 0 && nb < mtiles;
+    bool dead = false;
+    for (int t = 0; t < a.T; ++t) {
+      if (t > 0 && !dead) {
+        const int need = nsplit * t;
+        const long long t0 = clock64();
+        for (;;) {
+          const bool ok = !watch || ld_acquire(a.flags + nb) >= need;
+          if (__all_sync(0xffffffffu, ok)) break;
+          bool bad = false;
+          if (lane == 0) {
+            bad = ld_acquire(err) != 0;
+            if (!bad && clock64() - t0 > kSpinLimit) { atomicExch(err, 1); bad = true; }
+          }
+          if (__any_sync(0xffffffffu, bad)) { dead = true; break; }
+        }
+      }
+      if (lane == 0) {
+        stamp(blockIdx.x == 0, t, 0);
+        fence_proxy_async();        // the neighbours' generic-proxy stores of h_t, observed above, before the async-proxy read
+        for (int kc = 0; kc < kch; ++kc) {
+          mbar_expect_tx(&fullA[kc], (uint32_t)(slab_rows * BK * 2));
+          tma_load_2d(slab + kc * kSlabBytes, &tmH, &fullA[kc], kc * BK, t * M + m0);
+        }
+        stamp(blockIdx.x == 0, t, 1);
+      }
+      __syncwarp();
+      // the slab of step t+1 may only be overwritten after this step's MMAs: they complete before acc_full, which the
+      // epilogue awaits before it bumps this tile's counter, which the wait above includes (nb == tile)
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(NG >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+    mbar_wait(wfull, 0);
+    for (int t = 0; t < a.T; ++t) {
+      const uint32_t par = (uint32_t)(t & 1);
+      for (int kc = 0; kc < kch; ++kc) {
+        mbar_wait(&fullA[kc], par);
+        tc_fence_after();
+        if (lane == 0) {
+          if (kc == kch - 1) stamp(blockIdx.x == 0, t, 2);
+          for (int tap = 0; tap < 9; ++tap) {
+            const int off = (tap / 3) * Wp + (tap % 3);
+            const uint64_t adesc = make_sdesc(smem_u32(slab + kc * kSlabBytes) + (uint32_t)off * (BK * 2));
+            const uint64_t bdesc = make_sdesc(smem_u32(wsm + (tap * kch + kc) * kWTileBytes));
+#pragma unroll
+            for (int k = 0; k < BK / 16; ++k)
+              tc_mma_bf16(tmem_base, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (kc | tap | k) ? 1u : 0u);
+          }
+          if (kc == kch - 1) { tc_commit(acc_full); stamp(blockIdx.x == 0, t, 3); }
+        }
+        __syncwarp();
+      }
+    }
+  } else {
+    // ===================== epilogue warps 2..5: one thread = one q-row, NC channels =====================
+    using TA = __nv_bfloat16;
+    const int lg = warp & 3;
+    const int lrow = lg * 32 + lane;
+    const int m = m0 + lrow;
+    const bool inrange = m < M;
+    const int f = m / S, q = m - f * S;
+    const int y = q / Wp, x = q - y * Wp;
+    const bool valid = inrange && y < G && x < G;
+    const long long prow = (long long)m + Wp + 1;
+    const uint32_t tlane = tmem_base + ((uint32_t)(lg * 32) << 16);
+    // peepholes of this row -> shared memory [gate][channel][row] (read back by the same thread: no barrier needed)
+    {
+      const int p = y * G + x;
+      const float* pw[3] = {a.wci, a.wcf, a.wco};
+#pragma unroll
+      for (int g = 0; g < 3; ++g)
+#pragma unroll
+        for (int j = 0; j < NC; ++j) peep[(g * NC + j) * BM + lrow] = valid ? pw[g][(long long)p * Ch + ch0 + j] : 0.f;
+    }
+    float c[NC];
+#pragma unroll
+    for (int j = 0; j < NC; ++j) c[j] = 0.f;
+    if (valid) { ld8(a.Cf + prow * Ch + ch0, c); ld8(a.Cf + prow * Ch + ch0 + 8, c + 8); }
+    const int fourCh = 4 * Ch;
+    for (int t = 0; t < a.T; ++t) {
+      const long long mt = (long long)t * M + m;
+      // input-half pre-activations of this row: requested before the accumulator is awaited
+      float xi[NC], xf[NC], xc[NC], xo[NC];
+      if (valid) {
+        const float* xr = a.Xg + mt * fourCh + ch0;
+        ld8(xr, xi); ld8(xr + 8, xi + 8);
+        ld8(xr + Ch, xf); ld8(xr + Ch + 8, xf + 8);
+        ld8(xr + 2 * Ch, xc); ld8(xr + 2 * Ch + 8, xc + 8);
+        ld8(xr + 3 * Ch, xo); ld8(xr + 3 * Ch + 8, xo + 8);
+      }
+      mbar_wait(acc_full, (uint32_t)(t & 1));
+      tc_fence_after();
+      const bool ts_on = blockIdx.x == 0 && warp == 2 && lane == 0;
+      stamp(ts_on, t, 4);
+      float hi[NC], hf[NC], ho[NC];
+      tc_ld16(tlane, hi);
+      tc_ld16(tlane + 16u, hf);
+      tc_ld16(tlane + 32u, ho);
+      tc_fence_before();
+      float gi[NC], gf[NC], gg[NC], go[NC], hn[NC], cp[NC];
+      long long rn = 0;
+      if (valid) {
+#pragma unroll
+        for (int j = 0; j < NC; ++j) {           // gaze_lstm.py:112-133 as written: W_hi shared by i and the candidate,
+          cp[j] = c[j];                          // the output gate peeps at the OLD cell
+          gi[j] = sigm(xi[j] + hi[j] + peep[(0 * NC + j) * BM + lrow] * cp[j]);
+          gf[j] = sigm(xf[j] + hf[j] + peep[(1 * NC + j) * BM + lrow] * cp[j]);
+          gg[j] = tanh_fast(xc[j] + hi[j]);
+          c[j] = gf[j] * cp[j] + gi[j] * gg[j];
+          go[j] = sigm(xo[j] + ho[j] + peep[(2 * NC + j) * BM + lrow] * cp[j]);
+          hn[j] = tanh_fast(c[j]) * go[j];
+        }
+        rn = ((long long)(t + 1) * M + prow) * Ch + ch0;                     // slab t+1 = h_{t+1}
+        stbf16x16((TA*)a.Hop + rn, hn);      // the only rows the next step's MMAs read: published first
+      }
+      stamp(ts_on, t, 5);
+      // publish: every thread hands its operand rows of h_{t+1} to the async proxy, the CTA barrier orders all 128
+      // threads' stores before ONE release at gpu scope (cumulative over what the barrier made visible to thread 0) -
+      // one fence per CTA and step instead of 128 (measured: 1.8 us of the 7.4 us step were the per-thread fences)
+      fence_proxy_async();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (warp == 2 && lane == 0) { __threadfence(); red_release_add(a.flags + tile, 1); }
+      stamp(ts_on, t, 6);
+      // tail, off the critical path: fp32 master, head rows, training saves
+      if (valid) {
+        st8(a.Hf + rn, hn); st8(a.Hf + rn + 8, hn + 8);
+        if (a.HS) {
+          const long long orow = ((long long)t * a.B + f) * a.So + (long long)(y + a.pado) * a.Wo + (x + a.pado);
+          stbf16x16((TA*)a.HS + orow * Ch + ch0, hn);
+        }
+        if (a.save) {
+          float* sv = a.save + mt * 5 * Ch + ch0;
+          st8(sv, gi); st8(sv + 8, gi + 8);
+          st8(sv + Ch, gf); st8(sv + Ch + 8, gf + 8);
+          st8(sv + 2 * Ch, gg); st8(sv + 2 * Ch + 8, gg + 8);
+          st8(sv + 3 * Ch, go); st8(sv + 3 * Ch + 8, go + 8);
+          st8(sv + 4 * Ch, cp); st8(sv + 4 * Ch + 8, cp + 8);
+        }
+      }
+    }
+    if (valid) { st8(a.Cf + prow * Ch + ch0, c); st8(a.Cf + prow * Ch + ch0 + 8, c + 8); }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)kTmemCols)
+                 : "memory");
+  }
+}
+
+int slab_rows_of(int G) { return (BM + 2 * (G + 1) + 2 + 7) & ~7; }
+
+bool shape_ok(int B, int G, int Ch) {
+  if (B <= 0 || G <= 0 || (Ch != 64 && Ch != 128)) return false;
+  if (slab_rows_of(G) > kMaxSlabRows) return false;
+  const int S = (G + 1) * (G + 1);
+  const long long mtiles = ((long long)B * S + BM - 1) / BM;
+  return mtiles * (Ch / NC) <= num_sms();
+}
+
+}  // namespace lstmseq
+using namespace lstmseq;
+
+int convlstm_seq_fwd(const rgp_lstm_seq_args& a, cudaStream_t s) {
+  RGP_CHECK_ARG(a.dtype == 1, "rgp_convlstm_seq_fwd: bf16 operands only (dtype=%d)", a.dtype);
+  RGP_CHECK_ARG(a.T > 0, "rgp_convlstm_seq_fwd: T=%d", a.T);
+  RGP_CHECK_ARG(shape_ok(a.B, a.G, a.Ch), "rgp_convlstm_seq_fwd: B=%d G=%d Ch=%d does not fit (Ch 64 or 128, G <= 14, "
+                "tiles * Ch/16 <= SMs): use the per-step path", a.B, a.G, a.Ch);
+  RGP_CHECK_ARG(a.Hop && a.Hf && a.Cf && a.Wh && a.Xg && a.wci && a.wcf && a.wco && a.flags, "rgp_convlstm_seq_fwd: null pointer%s", "");
+  RGP_CHECK_ARG(((uintptr_t)a.Hop & 31) == 0 && ((uintptr_t)a.Hf & 31) == 0 && ((uintptr_t)a.Cf & 31) == 0 &&
+                ((uintptr_t)a.Xg & 31) == 0 && ((uintptr_t)a.Wh & 15) == 0 && ((uintptr_t)a.HS & 31) == 0 &&
+                ((uintptr_t)a.save & 31) == 0, "rgp_convlstm_seq_fwd: buffers must be 32-byte aligned%s", "");
+  const int Ch = a.Ch, S = (a.G + 1) * (a.G + 1);
+  const int srows = slab_rows_of(a.G);
+  CUtensorMap tmH, tmW;
+  int rc = tc::encode_map_bf16(a.Hop, Ch, a.rowsH, (long long)Ch * 2, BK, srows, &tmH);
+  if (rc) return rc;
+  rc = tc::encode_map_bf16(a.Wh, Ch, 27LL * Ch, (long long)Ch * 2, BK, NC, &tmW);
+  if (rc) return rc;
+  static PerDeviceFlag attr_set = {};
+  if (attr_set.need()) {
+    cudaError_t e = cudaFuncSetAttribute(lstm_seq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+    if (e != cudaSuccess) { set_error("lstm_seq: cudaFuncSetAttribute(smem=%d): %s", kSmemBytes, cudaGetErrorString(e)); return -5; }
+    attr_set.set();
+  }
+  const int mtiles = (a.B * S + BM - 1) / BM;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)(mtiles * (Ch / NC)), 1, 1);
+  cfg.blockDim = dim3(NTHREADS, 1, 1);
+  cfg.dynamicSmemBytes = kSmemBytes;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeCooperative;     // co-residency of all CTAs is what makes the counter waits safe
+  attr[0].val.cooperative = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, lstm_seq_kernel, tmH, tmW, a, srows);
+  if (e != cudaSuccess) { set_error("lstm_seq launch: %s", cudaGetErrorString(e)); return -5; }
+  return check_launch("lstm_seq");
+}
+
+}  // namespace rgp
+
+extern "C" {
+
+int rgp_convlstm_seq_fwd(const rgp_lstm_seq_args* a, void* stream) {
+  RGP_CHECK_ARG(a != nullptr, "rgp_convlstm_seq_fwd: null args%s", "");
+  return rgp::convlstm_seq_fwd(*a, (cudaStream_t)stream);
+}
+
+int rgp_convlstm_seq_fits(int B, int G, int Ch) { return rgp::lstmseq::shape_ok(B, G, Ch) ? 1 : 0; }
+
+int rgp_convlstm_seq_profile(unsigned long long* host_out, int n) {
+  RGP_CHECK_ARG(host_out != nullptr && n > 0, "rgp_convlstm_seq_profile: bad arguments%s", "");
+  if (n > rgp::lstmseq::kTsSteps * rgp::lstmseq::kTsEvents) n = rgp::lstmseq::kTsSteps * rgp::lstmseq::kTsEvents;
+  cudaError_t e = cudaMemcpyFromSymbol(host_out, rgp::lstmseq::g_lstm_ts, sizeof(unsigned long long) * n);
+  if (e != cudaSuccess) { rgp::set_error("rgp_convlstm_seq_profile: %s", cudaGetErrorString(e)); return -5; }
+  return 0;
+}
+
+}  // extern "C"

@@ -119,10 +119,18 @@ class GazeEngine(object):
         # per-step GEMMs, which spread one step over all SMs, are kept.  RGP_SEQ=0/1 forces the choice (A/B checks);
         # nsplit / mcast are the kernel's cluster options.
         mtiles = (B * self.S + 127) // 128
+        seq_arg = seq
         if seq is None:
             env = os.environ.get("RGP_SEQ", "")
             seq = (dtype == 1 and engine != 1 and Ch in (128, 256) and (env == "1" or (env != "0" and mtiles >= 64)))
         self.use_seq = bool(seq) and (not self.lstm) and 128 % self.S == 0
+        # Persistent ConvLSTM recurrence (rgp_convlstm_seq_fwd: all T steps in one launch, any grid; W_h slices resident in
+        # shared memory, tiles exchange their halo rows through per-tile counters).  Taken whenever all its CTAs
+        # (tiles x Ch/16) are co-resident - the small-batch, latency-bound regime (14x14: up to 10 clips; 7x7: up to 36).
+        fits = getattr(self.lib, "rgp_convlstm_seq_fits", None)
+        self.use_seq_lstm = bool(self.lstm and seq_arg is not False and engine != 1 and fits is not None and
+                                 (dtype == 1 or seq_arg is True) and fits(B, G, Ch) and
+                                 os.environ.get("RGP_SEQ", "") != "0")
         self.nsplit = nsplit or int(os.environ.get("RGP_SEQ_NSPLIT", "0")) or (2 if (Ch == 256 and mtiles <= 74) else 1)
         # mcast > 1: every weight box is fetched once per cluster and TMA-multicast; measured slower (the bound is the
         # SM's own L2->SMEM port, which multicast does not relieve), so the default is 1
@@ -298,6 +306,7 @@ class GazeEngine(object):
         if self.lstm:
             self.Cf = z(self.rows_step, Ch)
             self.Hconv = z(B * S, 3 * Ch)
+            self.seq_flags = torch.zeros((B * S + 127) // 128 + 1, dtype=torch.int32, device=dev)
             self.Lsave = z(T, B * S, 5 * Ch) if self.train else None
         else:
             self.RH = z(nsl * B * S + self.tail, Ch, dt=tdt)
@@ -472,6 +481,23 @@ class GazeEngine(object):
             if self.head == "fc":   # gaze_grcn77.py:206-211
                 self._fc_head_all(s)
             return
+        if self.use_seq_lstm:
+            if zero_cell:
+                lib.rgp_zero(self.Cf.data_ptr(), self.Cf.numel() * 4, s)
+            lib.rgp_zero(self.seq_flags.data_ptr(), self.seq_flags.numel() * 4, s)
+            a = L.LstmSeqArgs()
+            a.Hop, a.rowsH, a.Hf, a.Cf = self.Hop.data_ptr(), self.Hop.shape[0], self.Hf.data_ptr(), self.Cf.data_ptr()
+            a.Wh, a.Xg = pop("Wh_op"), self.Xg.data_ptr()
+            a.wci, a.wcf, a.wco = self._ptr("wci"), self._ptr("wcf"), self._ptr("wco")
+            a.HS = self.HS.data_ptr() if self.head == "deconv" else 0
+            a.save = self.Lsave.data_ptr() if self.train else 0
+            a.flags = self.seq_flags.data_ptr()
+            a.B, a.T, a.G, a.Ch = B, T, G, Ch
+            a.So, a.Wo, a.pado, a.dtype = HEAD_S, HEAD_W, HEAD_PAD, self.dtype
+            lib.rgp_convlstm_seq_fwd(C.byref(a), s)
+            if self.head == "fc":
+                self._fc_head_all(s)
+            return
         for t in range(T):
             xg = self.Xg.data_ptr() + t * M * NX * 4
             hs = 0
@@ -506,6 +532,11 @@ class GazeEngine(object):
                            **common, **extra)
         if self.head == "fc":   # gaze_grcn77.py:206-211
             self._fc_head_all(s)
+
+    def seq_timed_out(self):
+        """True if the last persistent ConvLSTM launch gave up waiting for a neighbouring tile (synchronises; the kernel
+        never hangs: it reports through the last counter and the pass's results are then invalid)"""
+        return bool(self.use_seq_lstm and int(self.seq_flags[-1].cpu()) != 0)
 
     def _fc_head_all(self, s):
         """per-position FC head on the fp32 states of all T steps (they stay resident in Hf): one launch"""

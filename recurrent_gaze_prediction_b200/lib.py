@@ -64,10 +64,22 @@ class GruSeqArgs(C.Structure):
     ]
 
 
+class LstmSeqArgs(C.Structure):
+    """Mirror of ``rgp_lstm_seq_args`` (include/rgp.h)."""
+    _fields_ = [
+        ("Hop", _vp), ("rowsH", _ll), ("Hf", _vp), ("Cf", _vp), ("Wh", _vp), ("Xg", _vp),
+        ("wci", _vp), ("wcf", _vp), ("wco", _vp), ("HS", _vp), ("save", _vp), ("flags", _vp),
+        ("B", _i), ("T", _i), ("G", _i), ("Ch", _i),
+        ("So", _i), ("Wo", _i), ("pado", _i), ("dtype", _i),
+    ]
+
+
 _SIGS = {
     "rgp_tapgemm": [C.POINTER(TapGemmArgs), _vp],
     "rgp_convgru_seq_fwd": [C.POINTER(GruSeqArgs), _vp],
     "rgp_convgru_seq_profile": [_vp, _i],
+    "rgp_convlstm_seq_fwd": [C.POINTER(LstmSeqArgs), _vp],
+    "rgp_convlstm_seq_profile": [_vp, _i],
     "rgp_pack_c3d": [_vp, _vp, _i, _i, _i, _i, _i, _vp],
     "rgp_pack_c3d_src": [_vp, _i, _vp, _i, _i, _i, _i, _i, _vp],
     "rgp_pack_emb": [_vp, _vp, _i, _i, _i, _i, _i, _vp],
@@ -134,6 +146,8 @@ class RgpLib(object):
         self._dll.rgp_has_tcgen05.restype = _i
         self._dll.rgp_metrics_fused_fits.restype = _i
         self._dll.rgp_metrics_fused_fits.argtypes = [_i, _i, _i, _i]
+        self._dll.rgp_convlstm_seq_fits.restype = _i
+        self._dll.rgp_convlstm_seq_fits.argtypes = [_i, _i, _i]
         for name, sig in _SIGS.items():
             fn = getattr(self._dll, name)
             fn.argtypes = sig
@@ -161,8 +175,13 @@ class RgpLib(object):
         """a predicate, not a status: 1 if the fused resize+metric kernels can hold an h x w -> oh x ow enlargement"""
         return int(self._dll.rgp_metrics_fused_fits(h, w, oh, ow))
 
+    def rgp_convlstm_seq_fits(self, B, G, Ch):
+        """a predicate: 1 if the persistent ConvLSTM kernel can hold this shape (all its CTAs co-resident)"""
+        return int(self._dll.rgp_convlstm_seq_fits(B, G, Ch))
+
     def symbols(self):
-        return sorted(list(_SIGS) + ["rgp_last_error", "rgp_version", "rgp_has_tcgen05", "rgp_metrics_fused_fits"])
+        return sorted(list(_SIGS) + ["rgp_last_error", "rgp_version", "rgp_has_tcgen05", "rgp_metrics_fused_fits",
+                                     "rgp_convlstm_seq_fits"])
 
 
 _LIB = None

@@ -778,6 +778,36 @@ class EmuLib(object):
             self.rgp_tapgemm(C.byref(g), stream)
         return 0
 
+    def rgp_convlstm_seq_fits(self, B, G, Ch):
+        return 1 if (Ch % 16 == 0 and G <= 14 and ((B * (G + 1) ** 2 + 127) // 128) * (Ch // 16) <= 148) else 0
+
+    def rgp_convlstm_seq_fwd(self, aref, stream):
+        """all T steps of the ConvLSTM recurrence: per step the hidden conv (3 gates) + rgp_lstm_gates, as the per-step path"""
+        a = aref._obj
+        B, T, G, Ch = a.B, a.T, a.G, a.Ch
+        Wp = G + 1
+        S = Wp * Wp
+        M = B * S
+        H = arr(a.Hop, (a.rowsH, Ch))
+        Wh = arr(a.Wh, (9 * 3 * Ch, Ch)).astype(np.float64)
+        flags = arr(a.flags, ((M + 127) // 128 + 1,), np.int32)
+        assert not flags.any(), "the caller zeroes the counters before every launch"
+        rows = np.arange(M)
+        hconv = np.zeros((M, 3 * Ch), dtype=np.float32)
+        for t in range(T):
+            acc = np.zeros((M, 3 * Ch))
+            for tap in range(9):
+                r = t * M + rows + (tap // 3) * Wp + (tap % 3)
+                acc += H[r].astype(np.float64) @ Wh[tap * 3 * Ch:(tap + 1) * 3 * Ch].T
+            hconv[:] = acc
+            es = 4
+            self.rgp_lstm_gates(a.Xg + t * M * 4 * Ch * 4, 4 * Ch, hconv.ctypes.data, a.wci, a.wcf, a.wco, a.Cf,
+                                a.Hf + (t + 1) * M * Ch * 4, a.Hop + (t + 1) * M * Ch * es,
+                                (a.HS + t * B * a.So * Ch * es) if a.HS else 0, B, G, Ch, a.So, a.Wo, a.pado, a.dtype,
+                                (a.save + t * M * 5 * Ch * 4) if a.save else 0, stream)
+            flags[:-1] += Ch // 16
+        return 0
+
     def rgp_fc_head_all(self, h1, w, b, logits, B, T, G, Ch, stream):
         S = (G + 1) * (G + 1)
         for t in range(T):

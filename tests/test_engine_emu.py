@@ -114,3 +114,22 @@ def test_clip_adam_steps_match_oracle():
         got = eng.op_to_tf(eng.params.numpy())
         for k, r in zip(names, params):
             assert np.allclose(got[k].reshape(r.shape), r, rtol=2e-4, atol=1e-7), (step, k)
+
+
+@pytest.mark.parametrize("G,B,head", [(7, 3, None), (14, 2, "fc")])
+def test_persistent_convlstm_orchestration_matches_per_step(G, B, head):
+    """engine wiring of rgp_convlstm_seq_fwd (buffers, counters zeroed per launch, training saves) == the per-step path"""
+    outs = []
+    for seq in (True, False):
+        p = O.init_params("gaze_lstm", hidden=16, T=3, grid=G, dim_proj=32, dim_feature=64, seed=0, regime="S", head=head)
+        rng = np.random.RandomState(5)
+        emb = SY.make_embedded(rng, B, 3, G, 32)
+        eng = GazeEngine("gaze_lstm", B=B, T=3, G=G, Ch=16, Cin=32, Cfeat=64, dtype=0, device="cpu", lib=EmuLib(),
+                         train=True, seq=seq, head=head)
+        assert eng.use_seq_lstm == seq
+        eng.load_tf_params(p)
+        for _ in range(2):       # twice: the counters are re-zeroed, the cell restarts from zero
+            logits = eng.forward(emb=torch.from_numpy(emb)).numpy().copy()
+        outs.append((logits, eng.Lsave.numpy().copy(), eng.read_state()[0].numpy().copy()))
+    for x, y in zip(*outs):
+        assert np.allclose(x, y, rtol=1e-6, atol=1e-7)

@@ -203,3 +203,45 @@ def test_config3_training_step_T35_hidden256_vs_oracle():
                 assert worst[k] <= 5e-2, (seq, k, worst[k])
         out["seq%s" % seq] = worst
     _report("config3_grads_T35_Ch256_bf16", **out)
+
+
+@pytest.mark.parametrize("G,B,T,head,train", [(14, 8, 128, "fc", False), (14, 2, 16, "fc", True), (7, 28, 35, None, False),
+                                                (7, 5, 6, None, True), (14, 10, 8, "fc", False)])
+def test_persistent_convlstm_matches_per_step_path_and_oracle(G, B, T, head, train):
+    """rgp_convlstm_seq_fwd (all T steps in one launch, W_h slices resident in shared memory, halo exchange through
+    per-tile counters) against the per-step path (h2h tap-GEMM + gate kernel per step) on the same inputs - states,
+    cell, maps, training saves - and, at config 4's own size (14x14, T = 128, 8 clips), against the float64 oracle."""
+    Ch = 128
+    p = O.init_params("gaze_lstm", hidden=Ch, T=T, grid=G, seed=5, regime="S", head=head)
+    rng = np.random.RandomState(11)
+    emb = SY.make_embedded(rng, B, T, G, 512)
+    GH = G if head == "fc" else 49
+    gt, _ = SY.make_gazemaps(rng, B, T, GH, GH, normalize=True)
+    res = []
+    for seq in (True, False):
+        eng = GazeEngine("gaze_lstm", B=B, T=T, G=G, Ch=Ch, dtype=1, device="cuda", head=head, train=train, seq=seq)
+        assert eng.use_seq_lstm == seq
+        eng.load_tf_params(p)
+        for _ in range(2):
+            eng.forward(emb=torch.from_numpy(emb).cuda(), gt=torch.from_numpy(gt).cuda())
+        torch.cuda.synchronize()
+        assert not eng.seq_timed_out()
+        c, h = eng.read_state()
+        res.append(dict(probs=eng.probs.cpu().numpy(), c=c.cpu().numpy(), h=h.cpu().numpy(),
+                        hmid=eng.read_state(max(1, T // 2))[1].cpu().numpy(),
+                        save=eng.Lsave.cpu().numpy() if train else None))
+    a, b = res
+    # same arithmetic up to the summation order of the MMAs and tanh.approx-free gates on both sides: bf16-rounding level
+    for k in ("h", "hmid", "c"):
+        assert np.abs(a[k] - b[k]).max() <= 2e-2 * max(1.0, np.abs(b[k]).max()), k
+    assert np.abs(a["probs"] - b["probs"]).max() <= 2e-2 * b["probs"].max()
+    if train:
+        assert np.abs(a["save"] - b["save"]).max() <= 2e-2 * max(1.0, np.abs(b["save"]).max())
+    if T == 128:
+        with torch.no_grad():
+            lg = O.recurrent_network("gaze_lstm", O.to_torch(p), emb=torch.tensor(emb, dtype=torch.float64))
+            ref = O.softmax_2d(lg).numpy()
+        err = _map_err(a["probs"], ref)
+        _report("config4_gaze_lstm_G14_T128_B8_persistent", max_map_err=float(err.max()), tol=2e-2,
+                map_err_per_t=[float(x) for x in err.max(axis=0)])
+        assert err.max() <= 2e-2, err.max()
