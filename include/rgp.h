@@ -270,13 +270,32 @@ int rgp_fc_head_bwd_all(const float* dlogits, const float* h1_f32, const float* 
  * P*Cp..ldx-1 zero; X operand dtype [rows, ldx] */
 int rgp_dense_pack(const float* acc, int ldacc, const float* bias, void* X, int ldx, long long rows, int P, int Cp,
                    int dtype, void* stream);
+/* the same followed by tf.nn.dropout(keep_prob) (gaze_rnn.py:302-303; fed 0.5 while training, :529): kept elements are
+ * scaled by 1/keep_prob.  The mask is a counter-based hash of (seed, element index) - reproducible, never stored;
+ * rgp_dense_unpack re-derives it.  keep_prob = 1 is rgp_dense_pack. */
+int rgp_dense_pack_dropout(const float* acc, int ldacc, const float* bias, void* X, int ldx, long long rows, int P,
+                           int Cp, float keep_prob, unsigned long long seed, int dtype, void* stream);
 /* xg [M, ldx] fp32 = input halves (columns r | u | c, each Hp wide); hg [M, 2Hp] fp32 = h . Wh_gates; bias_g [2Hp];
- * h_f32 [M, Hp].  Writes rh_op [M, Hp] operand dtype (r*h) and u_out [M, Hp] fp32. */
+ * h_f32 [M, Hp].  Writes rh_op [M, Hp] operand dtype (r*h), u_out [M, Hp] fp32 and (training, else NULL) r_save [M, Hp]. */
 int rgp_dense_gru_ru(const float* xg, int ldx, const float* hg, const float* bias_g, const float* h_f32, void* rh_op,
-                     float* u_out, int M, int H, int Hp, int dtype, void* stream);
-/* hc [M, Hp] fp32 = (r*h) . Wh_cand; bias_c [Hp]; writes h' as fp32 master [M, Hp] and operand copy */
+                     float* u_out, float* r_save, int M, int H, int Hp, int dtype, void* stream);
+/* hc [M, Hp] fp32 = (r*h) . Wh_cand; bias_c [Hp]; writes h' as fp32 master [M, Hp] and operand copy, and (training, else
+ * NULL) the candidate c_save [M, Hp] */
 int rgp_dense_gru_c(const float* xg, int ldx, const float* hc, const float* bias_c, const float* u, const float* h_f32,
-                    float* hnext_f32, void* hnext_op, int M, int H, int Hp, int dtype, void* stream);
+                    float* hnext_f32, void* hnext_op, float* c_save, int M, int H, int Hp, int dtype, void* stream);
+/* ---- BPTT of the dense variant (base.py:278-281 tf.gradients over gaze_rnn.py:283-359) -------------------------
+ * dlogits [B, T, N] fp32 -> time-major operand rows dL [(t*B + b), Np] (zero padded) */
+int rgp_dense_dlogits(const float* dlogits, void* out, int B, int T, int N, int Np, int dtype, void* stream);
+/* one step, first half: dh = dh_head + dh_rec (dh_rec may be NULL: last step) is dL/dh'.  Writes dpre_u = dh (h - c) u (1-u)
+ * and dpre_c = dh (1-u)(1-c^2) into dG[:, Hp:2Hp] / dG[:, 2Hp:3Hp] (dG [M, 3Hp] operand dtype) and dhpart = dh u. */
+int rgp_dense_gru_bwd_c(const float* dh_head, const float* dh_rec, const float* u, const float* c, const float* hprev,
+                        void* dG, float* dhpart, int M, int H, int Hp, int dtype, void* stream);
+/* second half, after drh = dpre_c . Wc_h^T: dpre_r = drh h r (1-r) into dG[:, 0:Hp]; dhpart += drh r */
+int rgp_dense_gru_bwd_r(const float* drh, const float* r, const float* hprev, void* dG, float* dhpart, int M, int H,
+                        int Hp, int dtype, void* stream);
+/* backward of rgp_dense_pack[_dropout]: dacc[(r*P + pos), c] = dX[r, pos*Cp + c] (x mask / keep_prob), operand dtype */
+int rgp_dense_unpack(const float* dX, int ldx, void* dacc, long long rows, int P, int Cp, float keep_prob,
+                     unsigned long long seed, int dtype, void* stream);
 /* gaze_rnn.py:346-359: logits[b, t, j] = acc[(t*B + b)*ldacc + j] + bias[j], j < N */
 int rgp_dense_logits(const float* acc, int ldacc, const float* bias, float* logits, int B, int T, int N, void* stream);
 

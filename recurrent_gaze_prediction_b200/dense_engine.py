@@ -6,8 +6,14 @@ Every contraction is a plain GEMM on the tap-GEMM engines (``rgp_tapgemm`` with 
 input halves of all three gate blocks for all T frames at once, two small GEMMs per step for the recurrent halves, and
 the output projection for all T at once.  Widths are padded to the engine's granularity (I 1568 -> 1600, H 1617 -> 1664,
 GH*GW 2401 -> 2432) with zero weights; the padded state columns stay exactly zero.  The element-wise glue is
-``csrc/dense_gru.cu``.  Forward / inference and the loss only: the reference trains this variant through
-``tf.gradients`` over ``tf.nn.rnn_cell.GRUCell``; its BPTT is not built here.
+``csrc/dense_gru.cu``.
+
+Training (``train=True``; the reference trains this variant through ``tf.gradients`` over ``tf.nn.rnn_cell.GRUCell``,
+``gaze_rnn.py:447-478`` + ``base.py:262-297``): hand-written BPTT on the same engines - the output projection's dX / dW for
+all T at once, per step (reverse time) two element-wise gate-backward kernels around two transposed-weight GEMMs, then
+the cell's weight gradients as three row contractions over all T*B rows (``rgp_wgrad``), dX of the input halves, the
+projection's gradients; clip + TF-Adam through :class:`TrainStateMixin`.  Dropout on the embedded features
+(``:302-303``, keep_prob 0.5 while training ``:529``) is a counter-based mask re-derived in the backward pass.
 
 The ShallowNet frame-saliency branch the reference also builds (``:252-276``) never reaches the prediction — its entry in
 the RNN input concat is commented out (``:333``) — so ``frame_images`` is not consumed.
@@ -21,14 +27,14 @@ import numpy as np
 import torch
 
 from . import lib as L
-from .engine import LOSS_TYPES, _tdtype
+from .engine import LOSS_TYPES, TrainStateMixin, _tdtype
 
 
 def _pad(n, m):
     return (n + m - 1) // m * m
 
 
-class DenseGruEngine(object):
+class DenseGruEngine(TrainStateMixin):
     model = "gaze_rnn"
     lstm = False
     use_bn = False
@@ -36,8 +42,6 @@ class DenseGruEngine(object):
 
     def __init__(self, B=2, T=35, G=7, Cp=32, Cfeat=1024, GH=49, dtype=0, device="cuda", lib=None, train=False,
                  engine=None):
-        if train:
-            raise NotImplementedError("the dense GRU variant is forward-only here (BPTT of gaze_rnn.py:283-359 is not built)")
         self.B, self.T, self.G, self.Cp, self.Cfeat, self.GH = B, T, G, Cp, Cfeat, GH
         self.P = G * G
         self.I = self.P * Cp                       # gaze_rnn.py:244
@@ -45,12 +49,15 @@ class DenseGruEngine(object):
         self.Ch = self.H
         self.N = GH * GH
         self.Ip, self.Hp, self.Np = _pad(self.I, 64), _pad(self.H, 128), _pad(self.N, 128)
-        self.dtype, self.train, self.engine = dtype, False, engine or 0
+        self.dtype, self.train, self.engine = dtype, bool(train), engine or 0
+        self.keep_prob, self.dropout_seed = 1.0, 0          # set per step by the model class while training
+        self.param_version = 0
         self.device = torch.device(device)
         self.lib = lib if lib is not None else L.get_lib()
         self.tdt = _tdtype(dtype)
-        self.step = 0
         self._build_params()
+        if self.train:
+            self._alloc_train_state()
         self._alloc()
 
     # ------------------------------------------------------------------ parameters (flat fp32 + operand copy)
@@ -114,6 +121,29 @@ class DenseGruEngine(object):
         self.params.copy_(torch.from_numpy(flat))
         self.refresh_operands()
 
+    def pad_mask(self):
+        """1 where a flat-buffer element is a real parameter, 0 in the zero padding (padded rows / columns of the op
+        layouts).  The padding's gradients are exactly zero, so Adam never moves it; used by tests."""
+        m = {k: np.zeros(s, dtype=np.float32) for k, s in self.spec.items()}
+        I, H, Hp, N = self.I, self.H, self.Hp, self.N
+        m["proj_W_op"][:] = 1
+        m["proj_b"][:] = 1
+        for blk in range(3):
+            m["Wx_op"][blk * Hp:blk * Hp + H, :I] = 1
+        m["Whg_op"][:H, :H] = 1
+        m["Whg_op"][Hp:Hp + H, :H] = 1
+        m["Whc_op"][:H, :H] = 1
+        m["bias_g"][:H] = 1
+        m["bias_g"][Hp:Hp + H] = 1
+        m["bias_c"][:H] = 1
+        m["out_W_op"][:N, :H] = 1
+        m["out_b"][:N] = 1
+        flat = np.zeros(self.nparams, dtype=np.float32)
+        for k, v in m.items():
+            off, n = self.offsets[k]
+            flat[off:off + n] = v.reshape(-1)
+        return flat
+
     def op_to_tf(self, flat):
         I, H, Hp, N = self.I, self.H, self.Hp, self.N
         flat = np.asarray(flat)
@@ -135,6 +165,7 @@ class DenseGruEngine(object):
     def refresh_operands(self):
         if self.dtype != 0:
             self.lib.rgp_cast(self.params.data_ptr(), self.params_op.data_ptr(), self.nparams, self.dtype, self._s())
+        self.param_version += 1
 
     # ------------------------------------------------------------------ buffers
     def _alloc(self):
@@ -152,7 +183,8 @@ class DenseGruEngine(object):
         else:
             self.Hf = z((T + 1) * B, self.Hp)
             self.Hop = z((T + 1) * B + 256, self.Hp, dt=self.tdt)
-        self.RH = z(_pad(B, 128) + 128, self.Hp, dt=self.tdt)
+        # r*h: one slab (inference) or one per step (training: the X operand of dW_candidate)
+        self.RH = z((T * B if self.train else 0) + _pad(B, 128) + 128, self.Hp, dt=self.tdt)
         self.Hg = z(B, 2 * self.Hp)
         self.Hc = z(B, self.Hp)
         self.U = z(B, self.Hp)
@@ -161,19 +193,34 @@ class DenseGruEngine(object):
         self.probs = z(B, T, self.GH, self.GH)
         self.frame_loss = z(B * T)
         self.loss = z(1)
+        if self.train:
+            Hp, Ip, Np = self.Hp, self.Ip, self.Np
+            self.Us, self.Rs, self.Cs = z(T * B, Hp), z(T * B, Hp), z(T * B, Hp)      # saved gates of every step
+            self.dlogits = z(B, T, self.GH, self.GH)
+            self.dL = z(rows, Np, dt=self.tdt)                 # dlogits as time-major operand rows
+            self.dHhead = z(T * B, Hp)                         # dL . W_out^T: head term of dL/dh_{t+1}
+            self.dG = z(rows, 3 * Hp, dt=self.tdt)             # d(pre-activations) r | u | c of every step
+            self.dhA, self.dhB = z(B, Hp), z(B, Hp)            # dL/dh (recurrent part), ping-pong
+            self.drh = z(B, Hp)
+            self.dX = z(T * B, Ip)
+            self.dPacc = z(T * B * self.P + 128, self.Cp, dt=self.tdt)
+            self.outWT = z(Hp, Np, dt=self.tdt)                # transposed operand copies (dX = dY . W)
+            self.WhcT = z(Hp, Hp, dt=self.tdt)
+            self.WhgT = z(Hp, 2 * Hp, dt=self.tdt)
+            self.WxT = z(Ip, 3 * Hp, dt=self.tdt)
 
     def _s(self):
         if self.device.type == "cuda":
             return torch.cuda.current_stream(self.device).cuda_stream
         return 0
 
-    def _gemm(self, A, rowsA, lda, Bw, M, N, K, out, ldo):
+    def _gemm(self, A, rowsA, lda, Bw, M, N, K, out, ldo, accumulate=0):
         a = L.TapGemmArgs()
         a.dtype, a.engine = self.dtype, self.engine
         a.ntaps = 1
         a.tap_off[0] = 0
         a.A, a.rowsA, a.lda, a.Bw, a.M, a.N, a.K = A, rowsA, lda, Bw, M, N, K
-        a.epi, a.out_f32, a.ldo = L.EPI_STORE_F32, out, ldo
+        a.epi, a.out_f32, a.ldo, a.accumulate = L.EPI_STORE_F32, out, ldo, accumulate
         a.S, a.Wp, a.G = 1, 1, 1
         self.lib.rgp_tapgemm(C.byref(a), self._s())
 
@@ -192,8 +239,8 @@ class DenseGruEngine(object):
         lib.rgp_pack_c3d(c3d.data_ptr(), self.Apack.data_ptr(), B, T, self.Cfeat, P, self.dtype, s)
         self._gemm(self.Apack.data_ptr(), self.Apack.shape[0], self.Cfeat, self._pop("proj_W_op"), T * B * P, Cp,
                    self.Cfeat, self.Pacc.data_ptr(), Cp)
-        lib.rgp_dense_pack(self.Pacc.data_ptr(), Cp, self._ptr("proj_b"), self.X.data_ptr(), Ip, T * B, P, Cp,
-                           self.dtype, s)
+        lib.rgp_dense_pack_dropout(self.Pacc.data_ptr(), Cp, self._ptr("proj_b"), self.X.data_ptr(), Ip, T * B, P, Cp,
+                                   float(self.keep_prob), int(self.dropout_seed), self.dtype, s)
         # (2) input halves of r | u | c for all T frames at once
         self._gemm(self.X.data_ptr(), self.X.shape[0], Ip, self._pop("Wx_op"), T * B, 3 * Hp, Ip, self.Xg.data_ptr(),
                    3 * Hp)
@@ -206,12 +253,17 @@ class DenseGruEngine(object):
             hf = self.Hf.data_ptr() + t * B * Hp * 4
             hop = self.Hop.data_ptr() + t * B * Hp * es
             xg = self.Xg.data_ptr() + t * B * 3 * Hp * 4
+            sl = t * B * Hp * 4
+            u = (self.Us.data_ptr() + sl) if self.train else self.U.data_ptr()
+            rh = self.RH.data_ptr() + (t * B * Hp * es if self.train else 0)
+            rh_rows = self.RH.shape[0] - (t * B if self.train else 0)
             self._gemm(hop, rowsH - t * B, Hp, self._pop("Whg_op"), B, 2 * Hp, Hp, self.Hg.data_ptr(), 2 * Hp)
-            lib.rgp_dense_gru_ru(xg, 3 * Hp, self.Hg.data_ptr(), self._ptr("bias_g"), hf, self.RH.data_ptr(),
-                                 self.U.data_ptr(), B, H, Hp, self.dtype, s)
-            self._gemm(self.RH.data_ptr(), self.RH.shape[0], Hp, self._pop("Whc_op"), B, Hp, Hp, self.Hc.data_ptr(), Hp)
-            lib.rgp_dense_gru_c(xg, 3 * Hp, self.Hc.data_ptr(), self._ptr("bias_c"), self.U.data_ptr(), hf,
-                                hf + B * Hp * 4, hop + B * Hp * es, B, H, Hp, self.dtype, s)
+            lib.rgp_dense_gru_ru(xg, 3 * Hp, self.Hg.data_ptr(), self._ptr("bias_g"), hf, rh, u,
+                                 (self.Rs.data_ptr() + sl) if self.train else 0, B, H, Hp, self.dtype, s)
+            self._gemm(rh, rh_rows, Hp, self._pop("Whc_op"), B, Hp, Hp, self.Hc.data_ptr(), Hp)
+            lib.rgp_dense_gru_c(xg, 3 * Hp, self.Hc.data_ptr(), self._ptr("bias_c"), u, hf,
+                                hf + B * Hp * 4, hop + B * Hp * es, (self.Cs.data_ptr() + sl) if self.train else 0,
+                                B, H, Hp, self.dtype, s)
         # (4) proj_out for all T at once (gaze_rnn.py:346-359)
         self._gemm(self.Hop.data_ptr() + B * Hp * es, rowsH - B, Hp, self._pop("out_W_op"), T * B, self.Np, Hp,
                    self.Oacc.data_ptr(), self.Np)
@@ -226,7 +278,8 @@ class DenseGruEngine(object):
             raise NotImplementedError(str(loss_type))
         assert tuple(gt.shape) == tuple(self.logits.shape) and gt.dtype == torch.float32
         n, hw = self.B * self.T, self.N
-        self.lib.rgp_softmax_xent_fwd_bwd(self.logits.data_ptr(), gt.data_ptr(), self.probs.data_ptr(), 0,
+        self.lib.rgp_softmax_xent_fwd_bwd(self.logits.data_ptr(), gt.data_ptr(), self.probs.data_ptr(),
+                                          self.dlogits.data_ptr() if self.train else 0,
                                           self.frame_loss.data_ptr(), n, hw, 1.0 / ((global_batch or self.B) * self.T),
                                           LOSS_TYPES[loss_type], self._s())
         self.lib.rgp_reduce_sum(self.frame_loss.data_ptr(), n, self.loss.data_ptr(), self._s())
@@ -235,3 +288,65 @@ class DenseGruEngine(object):
     def read_state(self, t=None):
         t = self.T if t is None else t
         return self.Hf[t * self.B:(t + 1) * self.B, :self.H].contiguous()
+
+    # ------------------------------------------------------------------ backward (BPTT) — base.py:278-281
+    def _wgrad(self, Y, ldy, ycol0, Ny, X, rowsX, ldx, Nx, M, D):
+        a = L.WgradArgs()
+        a.Y, a.ldy, a.ycol0, a.Ny = Y, ldy, ycol0, Ny
+        a.X, a.rowsX, a.ldx, a.xcol0, a.Nx = X, rowsX, ldx, 0, Nx
+        a.M, a.ntaps = M, 1
+        a.tap_off[0] = 0
+        a.D, a.dtype, a.engine = D, self.dtype, self.engine
+        self.lib.rgp_wgrad(C.byref(a), self._s())
+
+    def backward(self):
+        """Hand-written BPTT of the last forward(gt=...): fills self.grads (flat, op layouts).  dL/dlogits =
+        (softmax - gt)/(B*T) was written by the fused softmax / loss kernel."""
+        assert self.train, "construct the engine with train=True"
+        lib, s = self.lib, self._s()
+        B, T, P, Cp, Hp, Ip, H, Np, N = self.B, self.T, self.P, self.Cp, self.Hp, self.Ip, self.H, self.Np, self.N
+        es = self.Hop.element_size()
+        M = T * B
+        g = lambda name: self._ptr(name, self.grads)
+        lib.rgp_zero(self.grads.data_ptr(), self.grads.numel() * 4, s)
+        # transposed operand copies of the weights (dX = dY . W for a forward Y = X . W^T)
+        lib.rgp_transpose_taps(self._ptr("out_W_op"), self.outWT.data_ptr(), 1, Np, Hp, self.dtype, s)
+        lib.rgp_transpose_taps(self._ptr("Whc_op"), self.WhcT.data_ptr(), 1, Hp, Hp, self.dtype, s)
+        lib.rgp_transpose_taps(self._ptr("Whg_op"), self.WhgT.data_ptr(), 1, 2 * Hp, Hp, self.dtype, s)
+        lib.rgp_transpose_taps(self._ptr("Wx_op"), self.WxT.data_ptr(), 1, 3 * Hp, Ip, self.dtype, s)
+        # ---- output projection (gaze_rnn.py:346-348), all T at once
+        lib.rgp_dense_dlogits(self.dlogits.data_ptr(), self.dL.data_ptr(), B, T, N, Np, self.dtype, s)
+        h1 = self.Hop.data_ptr() + B * Hp * es                       # slab t+1 = h_{t+1}: the projection's input rows
+        self._wgrad(self.dL.data_ptr(), Np, 0, Np, h1, self.Hop.shape[0] - B, Hp, Hp, M, g("out_W_op"))
+        lib.rgp_colsum(self.dL.data_ptr(), Np, M, Np, g("out_b"), self.dtype, s)
+        self._gemm(self.dL.data_ptr(), self.dL.shape[0], Np, self.outWT.data_ptr(), M, Hp, Np, self.dHhead.data_ptr(), Hp)
+        # ---- the recurrence, backwards in time (tf.nn.rnn_cell.GRUCell)
+        dh_rec, dh_next = 0, self.dhA
+        for t in range(T - 1, -1, -1):
+            sl = t * B * Hp * 4
+            hprev = self.Hf.data_ptr() + sl                              # slab t = h_t, the step's input state
+            dG_t = self.dG.data_ptr() + t * B * 3 * Hp * es
+            lib.rgp_dense_gru_bwd_c(self.dHhead.data_ptr() + sl, dh_rec, self.Us.data_ptr() + sl, self.Cs.data_ptr() + sl,
+                                    hprev, dG_t, dh_next.data_ptr(), B, H, Hp, self.dtype, s)
+            self._gemm(dG_t + 2 * Hp * es, self.dG.shape[0] - t * B, 3 * Hp, self.WhcT.data_ptr(), B, Hp, Hp,
+                       self.drh.data_ptr(), Hp)
+            lib.rgp_dense_gru_bwd_r(self.drh.data_ptr(), self.Rs.data_ptr() + sl, hprev, dG_t, dh_next.data_ptr(), B, H, Hp,
+                                    self.dtype, s)
+            if t > 0:
+                self._gemm(dG_t, self.dG.shape[0] - t * B, 3 * Hp, self.WhgT.data_ptr(), B, Hp, 2 * Hp,
+                           dh_next.data_ptr(), Hp, accumulate=1)
+            dh_rec = dh_next.data_ptr()
+            dh_next = self.dhB if dh_next is self.dhA else self.dhA
+        # ---- weight gradients of the cell: row contractions over all T*B rows
+        self._wgrad(self.dG.data_ptr(), 3 * Hp, 0, 3 * Hp, self.X.data_ptr(), self.X.shape[0], Ip, Ip, M, g("Wx_op"))
+        self._wgrad(self.dG.data_ptr(), 3 * Hp, 0, 2 * Hp, self.Hop.data_ptr(), self.Hop.shape[0], Hp, Hp, M, g("Whg_op"))
+        self._wgrad(self.dG.data_ptr(), 3 * Hp, 2 * Hp, Hp, self.RH.data_ptr(), self.RH.shape[0], Hp, Hp, M, g("Whc_op"))
+        lib.rgp_colsum(self.dG.data_ptr(), 3 * Hp, M, 2 * Hp, g("bias_g"), self.dtype, s)
+        lib.rgp_colsum(self.dG.data_ptr() + 2 * Hp * es, 3 * Hp, M, Hp, g("bias_c"), self.dtype, s)
+        # ---- input rows -> projection (gaze_rnn.py:294-304)
+        self._gemm(self.dG.data_ptr(), self.dG.shape[0], 3 * Hp, self.WxT.data_ptr(), M, Ip, 3 * Hp, self.dX.data_ptr(), Ip)
+        lib.rgp_dense_unpack(self.dX.data_ptr(), Ip, self.dPacc.data_ptr(), M, P, Cp, float(self.keep_prob),
+                             int(self.dropout_seed), self.dtype, s)
+        self._wgrad(self.dPacc.data_ptr(), Cp, 0, Cp, self.Apack.data_ptr(), self.Apack.shape[0], self.Cfeat, self.Cfeat,
+                    M * P, g("proj_W_op"))
+        lib.rgp_colsum(self.dPacc.data_ptr(), Cp, M * P, Cp, g("proj_b"), self.dtype, s)

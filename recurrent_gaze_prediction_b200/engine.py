@@ -77,7 +77,115 @@ class StepGraph(object):
             self.eng.note_replayed_steps(1)
 
 
-class GazeEngine(object):
+class TrainStateMixin(object):
+    """Flat-buffer training state shared by the engines (GazeEngine, DenseGruEngine): gradient / Adam-moment buffers with
+    the parameter buffer's offsets, the device-side optimiser schedule, clip + TF-Adam (base.py:262-297,
+    gaze_rnn.py:435-444), CUDA-graph capture of a step and the snapshot that undoes a capture's warm-up run.  Expects
+    self.params / params_op / nparams / dtype / device / lib / train / param_version and self._s()."""
+
+    def _alloc_train_state(self):
+        dev, off = self.device, self.nparams
+        self.grads = torch.zeros(off, dtype=torch.float32, device=dev)
+        self.adam_m = torch.zeros(off, dtype=torch.float32, device=dev)
+        self.adam_v = torch.zeros(off, dtype=torch.float32, device=dev)
+        self.sumsq = torch.zeros(1, dtype=torch.float64, device=dev)
+        # optimiser schedule state ON THE DEVICE (rgp_adam_schedule): global_step, initial learning rate, and the
+        # (lr_t, lr) pair the Adam kernel reads — a captured graph of the training step replays a correct schedule
+        self.step_dev = torch.zeros(1, dtype=torch.int64, device=dev)
+        self.lr0_dev = torch.zeros(1, dtype=torch.float64, device=dev)
+        self.sched = torch.zeros(2, dtype=torch.float32, device=dev)
+        self._lr0_host = None
+        self._step = 0
+
+    def make_graph(self, fn):
+        """Capture the launches fn() issues into a CUDA graph (one submission per step instead of ~80
+        launches: the recurrence is launch-bound at small batch).  Returns (graph, kernels_per_replay)."""
+        dev = self.device
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            fn()      # warm-up outside capture: function attributes, tensor-map cache, head composition
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        g = torch.cuda.CUDAGraph()
+        n0 = self.lib.launches
+        with torch.cuda.graph(g):
+            fn()
+        return g, self.lib.launches - n0
+
+    def snapshot_train_state(self):
+        return (self.params.clone(), self.params_op.clone(), self.adam_m.clone(), self.adam_v.clone(), self._step,
+                self.param_version)
+
+    def restore_train_state(self, snap):
+        p, po, m, v, step, ver = snap
+        self.params.copy_(p)
+        if self.params_op is not self.params:
+            self.params_op.copy_(po)
+        self.adam_m.copy_(m)
+        self.adam_v.copy_(v)
+        self.step = step
+        self.param_version = ver + 1          # anything derived from the parameters (composed head) is stale
+
+    # ------------------------------------------------------------------ optimiser — base.py:262-297, gaze_rnn.py:435-444
+    @property
+    def step(self):
+        """global_step = optimiser updates applied so far.  The authoritative copy lives on the device (step_dev,
+        advanced by rgp_adam_schedule inside the — possibly graph-captured — step); this host mirror is advanced by
+        optimizer_step() / note_replayed_steps() and never needs a device read."""
+        return getattr(self, "_step", 0)
+
+    @step.setter
+    def step(self, v):
+        self._step = int(v)
+        if self.train:
+            self.step_dev.fill_(int(v))
+
+    def step_on_device(self):
+        """the device's own global_step (synchronises; tests / checkpoint sanity)"""
+        return int(self.step_dev.cpu()[0])
+
+    def note_replayed_steps(self, n=1):
+        """a captured graph containing optimizer_step() was replayed n times: advance the host mirror"""
+        self._step += int(n)
+        self.param_version += int(n)
+
+    def learning_rate(self, lr0=1e-4, decay=0.8, decay_steps=500):
+        return lr0 * decay ** (self.step // decay_steps)
+
+    def set_lr0(self, lr0):
+        """initial learning rate (x decay_learning_rate's factor) -> the device scalar the schedule kernel reads; a
+        host-to-device write only when the value changes (never inside a graph capture)"""
+        if self._lr0_host != float(lr0):
+            if self.device.type == "cuda" and torch.cuda.is_current_stream_capturing():
+                raise RuntimeError("the learning rate changed inside a CUDA-graph capture: call set_lr0() before capturing")
+            self.lr0_dev.fill_(float(lr0))
+            self._lr0_host = float(lr0)
+
+    def optimizer_step(self, lr0=1e-4, decay=0.8, clip=10.0, beta1=0.9, beta2=0.999, eps=1e-8, allreduce=None,
+                       decay_steps=500):
+        """clip_by_global_norm + TF-Adam on the flat buffers.  `allreduce(grads)` (optional) sums the gradient
+        over data-parallel ranks first: the norm must be taken over the GLOBAL gradient (base.py:287-297).
+        The staircase learning rate and Adam's bias-corrected step size are formed on the device from the device-side
+        global_step (rgp_adam_schedule), so this call is graph-capturable with a correct schedule."""
+        lib, s = self.lib, self._s()
+        if allreduce is not None:
+            allreduce(self.grads)
+        self.set_lr0(lr0)
+        lib.rgp_zero(self.sumsq.data_ptr(), 8, s)
+        lib.rgp_sumsq(self.grads.data_ptr(), self.nparams, self.sumsq.data_ptr(), s)
+        lib.rgp_adam_schedule(self.step_dev.data_ptr(), self.lr0_dev.data_ptr(), float(decay), int(decay_steps),
+                              float(beta1), float(beta2), self.sched.data_ptr(), s)
+        lib.rgp_gradnorm_clip_adam_dev(self.params.data_ptr(), self.grads.data_ptr(), self.adam_m.data_ptr(),
+                                       self.adam_v.data_ptr(), self.nparams, self.sumsq.data_ptr(), clip,
+                                       self.sched.data_ptr(), beta1, beta2, eps,
+                                       self.params_op.data_ptr() if self.dtype != 0 else 0, self.dtype, s)
+        if not (self.device.type == "cuda" and torch.cuda.is_current_stream_capturing()):
+            self._step += 1
+            self.param_version += 1
+
+
+class GazeEngine(TrainStateMixin):
     def __init__(self, model="gaze_grcn", B=2, T=35, G=7, Ch=128, Cin=512, Cfeat=1024, dtype=0,
                  device="cuda", lib=None, train=False, head=None, engine=None, seq=None, nsplit=None, mcast=None,
                  T_params=None):
@@ -181,17 +289,7 @@ class GazeEngine(object):
         self.params = torch.zeros(off, dtype=torch.float32, device=dev)
         self.params_op = self.params if self.dtype == 0 else torch.zeros(off, dtype=self.tdt, device=dev)
         if self.train:
-            self.grads = torch.zeros(off, dtype=torch.float32, device=dev)
-            self.adam_m = torch.zeros(off, dtype=torch.float32, device=dev)
-            self.adam_v = torch.zeros(off, dtype=torch.float32, device=dev)
-            self.sumsq = torch.zeros(1, dtype=torch.float64, device=dev)
-            # optimiser schedule state ON THE DEVICE (rgp_adam_schedule): global_step, initial learning rate, and the
-            # (lr_t, lr) pair the Adam kernel reads — a captured graph of the training step replays a correct schedule
-            self.step_dev = torch.zeros(1, dtype=torch.int64, device=dev)
-            self.lr0_dev = torch.zeros(1, dtype=torch.float64, device=dev)
-            self.sched = torch.zeros(2, dtype=torch.float32, device=dev)
-            self._lr0_host = None
-            self._step = 0
+            self._alloc_train_state()
 
     def view(self, name, buf=None):
         off, n = self.offsets[name]
@@ -559,36 +657,6 @@ class GazeEngine(object):
                    M=self.T * self.B * HEAD_S, N=48, K=self.Ch, taps=taps, epi=L.EPI_HEAD, S=HEAD_S, Wp=HEAD_W,
                    G=9, B=self.B, T=self.T, out_f32=self.logits.data_ptr(), bias=self._ptr("out_b"))
 
-    def make_graph(self, fn):
-        """Capture the launches fn() issues into a CUDA graph (one submission per step instead of ~80
-        launches: the recurrence is launch-bound at small batch).  Returns (graph, kernels_per_replay)."""
-        dev = self.device
-        side = torch.cuda.Stream(device=dev)
-        side.wait_stream(torch.cuda.current_stream(dev))
-        with torch.cuda.stream(side):
-            fn()      # warm-up outside capture: function attributes, tensor-map cache, head composition
-        torch.cuda.current_stream(dev).wait_stream(side)
-        torch.cuda.synchronize(dev)
-        g = torch.cuda.CUDAGraph()
-        n0 = self.lib.launches
-        with torch.cuda.graph(g):
-            fn()
-        return g, self.lib.launches - n0
-
-    def snapshot_train_state(self):
-        return (self.params.clone(), self.params_op.clone(), self.adam_m.clone(), self.adam_v.clone(), self._step,
-                self.param_version)
-
-    def restore_train_state(self, snap):
-        p, po, m, v, step, ver = snap
-        self.params.copy_(p)
-        if self.params_op is not self.params:
-            self.params_op.copy_(po)
-        self.adam_m.copy_(m)
-        self.adam_v.copy_(v)
-        self.step = step
-        self.param_version = ver + 1          # anything derived from the parameters (composed head) is stale
-
     def time_stages(self, c3d, gt, iters=3, emb=False):
         """CUDA-event time (ms, mean of `iters`) of each stage of one forward pass on the current stream."""
         names = ["embed", "i2h", "recurrence", "head", "loss"]
@@ -782,59 +850,3 @@ class GazeEngine(object):
                     self.taps3, g("Wx_op"))
         self._mark("wgrad_cell")
 
-    # ------------------------------------------------------------------ optimiser — base.py:262-297, gaze_rnn.py:435-444
-    @property
-    def step(self):
-        """global_step = optimiser updates applied so far.  The authoritative copy lives on the device (step_dev,
-        advanced by rgp_adam_schedule inside the — possibly graph-captured — step); this host mirror is advanced by
-        optimizer_step() / note_replayed_steps() and never needs a device read."""
-        return getattr(self, "_step", 0)
-
-    @step.setter
-    def step(self, v):
-        self._step = int(v)
-        if self.train:
-            self.step_dev.fill_(int(v))
-
-    def step_on_device(self):
-        """the device's own global_step (synchronises; tests / checkpoint sanity)"""
-        return int(self.step_dev.cpu()[0])
-
-    def note_replayed_steps(self, n=1):
-        """a captured graph containing optimizer_step() was replayed n times: advance the host mirror"""
-        self._step += int(n)
-        self.param_version += int(n)
-
-    def learning_rate(self, lr0=1e-4, decay=0.8, decay_steps=500):
-        return lr0 * decay ** (self.step // decay_steps)
-
-    def set_lr0(self, lr0):
-        """initial learning rate (x decay_learning_rate's factor) -> the device scalar the schedule kernel reads; a
-        host-to-device write only when the value changes (never inside a graph capture)"""
-        if self._lr0_host != float(lr0):
-            if self.device.type == "cuda" and torch.cuda.is_current_stream_capturing():
-                raise RuntimeError("the learning rate changed inside a CUDA-graph capture: call set_lr0() before capturing")
-            self.lr0_dev.fill_(float(lr0))
-            self._lr0_host = float(lr0)
-
-    def optimizer_step(self, lr0=1e-4, decay=0.8, clip=10.0, beta1=0.9, beta2=0.999, eps=1e-8, allreduce=None,
-                       decay_steps=500):
-        """clip_by_global_norm + TF-Adam on the flat buffers.  `allreduce(grads)` (optional) sums the gradient
-        over data-parallel ranks first: the norm must be taken over the GLOBAL gradient (base.py:287-297).
-        The staircase learning rate and Adam's bias-corrected step size are formed on the device from the device-side
-        global_step (rgp_adam_schedule), so this call is graph-capturable with a correct schedule."""
-        lib, s = self.lib, self._s()
-        if allreduce is not None:
-            allreduce(self.grads)
-        self.set_lr0(lr0)
-        lib.rgp_zero(self.sumsq.data_ptr(), 8, s)
-        lib.rgp_sumsq(self.grads.data_ptr(), self.nparams, self.sumsq.data_ptr(), s)
-        lib.rgp_adam_schedule(self.step_dev.data_ptr(), self.lr0_dev.data_ptr(), float(decay), int(decay_steps),
-                              float(beta1), float(beta2), self.sched.data_ptr(), s)
-        lib.rgp_gradnorm_clip_adam_dev(self.params.data_ptr(), self.grads.data_ptr(), self.adam_m.data_ptr(),
-                                       self.adam_v.data_ptr(), self.nparams, self.sumsq.data_ptr(), clip,
-                                       self.sched.data_ptr(), beta1, beta2, eps,
-                                       self.params_op.data_ptr() if self.dtype != 0 else 0, self.dtype, s)
-        if not (self.device.type == "cuda" and torch.cuda.is_current_stream_capturing()):
-            self._step += 1
-            self.param_version += 1

@@ -110,8 +110,13 @@ _SIGS = {
     "rgp_fc_head_bwd_all": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
     # dense-GRU variant (gaze_rnn.py:283-359)
     "rgp_dense_pack": [_vp, _i, _vp, _vp, _i, _ll, _i, _i, _i, _vp],
-    "rgp_dense_gru_ru": [_vp, _i, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
-    "rgp_dense_gru_c": [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
+    "rgp_dense_pack_dropout": [_vp, _i, _vp, _vp, _i, _ll, _i, _i, _f, C.c_ulonglong, _i, _vp],
+    "rgp_dense_gru_ru": [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
+    "rgp_dense_gru_c": [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
+    "rgp_dense_dlogits": [_vp, _vp, _i, _i, _i, _i, _i, _vp],
+    "rgp_dense_gru_bwd_c": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
+    "rgp_dense_gru_bwd_r": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
+    "rgp_dense_unpack": [_vp, _i, _vp, _ll, _i, _i, _f, C.c_ulonglong, _i, _vp],
     "rgp_dense_logits": [_vp, _i, _vp, _vp, _i, _i, _i, _vp],
     # cascade top level (gaze_grcn_cascade.py:343-424)
     "rgp_topgru_seq_fwd": [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _vp, _i, _i, _i, _vp],

@@ -170,7 +170,8 @@ class GazePredictionGRU(ModelBase):
 
     def _build_dense_model(self):
         """The class as the reference defines it: the dense GRU variant (gaze_rnn.py:211-361) —
-        forward, loss, generate / evaluate; training is not built (see DenseGruEngine)."""
+        forward, loss, BPTT + clip/Adam (eager launches), generate / evaluate.  Dropout on the embedded features is live
+        while training (keep_prob 0.5, gaze_rnn.py:302-303,529) and off otherwise."""
         from ..dense_engine import DenseGruEngine
         from .model_util import init_parameters_dense
         c = self.config
@@ -180,13 +181,11 @@ class GazePredictionGRU(ModelBase):
         GH, GW = self.gazemap_height, self.gazemap_width
         if GH != GW:
             raise ValueError("square gaze maps only")
-        if bool(getattr(c, "trainable", True)):
-            raise NotImplementedError("the dense GRU variant (gaze_rnn.py:211-361) is built for inference / evaluation "
-                                      "only: set config.trainable = False, or train GazePredictionGRCN / GazePredictionLSTM")
+        train = bool(getattr(c, "trainable", True))
         self.dim_cnn_proj = getattr(c, "dim_cnn_proj_dense", 32)              # gaze_rnn.py:239 (XXX FIXME there)
         self.chunk_steps = None
         self.engine = DenseGruEngine(B=B, T=T, G=G, Cp=self.dim_cnn_proj, Cfeat=c.dim_feature, GH=GH, dtype=dtype,
-                                     device=dev, lib=self._lib)
+                                     device=dev, lib=self._lib, train=train)
         self.engine.load_tf_params(init_parameters_dense(dim_proj=self.dim_cnn_proj, grid=G, dim_feature=c.dim_feature,
                                                          GH=GH, GW=GW, seed=getattr(c, "seed", 0)))
         z = lambda *s: torch.zeros(*s, dtype=torch.float32, device=dev)
@@ -341,6 +340,9 @@ class GazePredictionGRU(ModelBase):
             if train:
                 raise RuntimeError("a chunked model cannot train")
             return self._run_chunked()
+        if self.model_name is None:          # dense variant: live dropout while training (gaze_rnn.py:529 feeds 0.5)
+            self.engine.keep_prob = float(getattr(self.config, "dropout_keep_prob_train", 0.5)) if train else 1.0
+            self.engine.dropout_seed = (int(getattr(self.config, "seed", 0)) << 32) + int(self.current_step)
         if self._use_graph():
             if train:
                 self.engine.set_lr0(self.initial_learning_rate * self._lr_scale)

@@ -546,14 +546,45 @@ class EmuLib(object):
         return 0
 
     # -------------------------------------------------------------- dense-GRU glue (csrc/dense_gru.cu)
+    @staticmethod
+    def _dropout_keep(seed, idx, keep_prob):
+        """the counter-based hash of csrc/dense_gru.cu dropout_keep (splitmix64 finaliser), vectorised"""
+        with np.errstate(over="ignore"):
+            z = np.uint64(seed) + np.uint64(0x9E3779B97F4A7C15) * (idx.astype(np.uint64) + np.uint64(1))
+            z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+            z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+            z = z ^ (z >> np.uint64(31))
+        return (z >> np.uint64(40)).astype(np.float32) * np.float32(1.0 / 16777216.0) < np.float32(keep_prob)
+
     def rgp_dense_pack(self, acc, ldacc, bias, X, ldx, rows, P, Cp, dtype, stream):
+        return self.rgp_dense_pack_dropout(acc, ldacc, bias, X, ldx, rows, P, Cp, 1.0, 0, dtype, stream)
+
+    def rgp_dense_pack_dropout(self, acc, ldacc, bias, X, ldx, rows, P, Cp, keep_prob, seed, dtype, stream):
         a = arr(acc, (rows * P, ldacc))[:, :Cp] + arr(bias, (Cp,))[None, :]
         x = arr(X, (rows, ldx))
         x[:] = 0.0
-        x[:, :P * Cp] = a.reshape(rows, P * Cp)
+        v = a.reshape(rows, P * Cp)
+        if keep_prob < 1.0:
+            idx = (np.arange(rows)[:, None] * ldx + np.arange(P * Cp)[None, :])
+            v = np.where(self._dropout_keep(seed, idx, keep_prob), v * np.float32(1.0 / keep_prob), np.float32(0))
+        x[:, :P * Cp] = v
         return 0
 
-    def rgp_dense_gru_ru(self, xg, ldx, hg, bias_g, h, rh, u_out, M, H, Hp, dtype, stream):
+    def rgp_dense_unpack(self, dX, ldx, dacc, rows, P, Cp, keep_prob, seed, dtype, stream):
+        v = arr(dX, (rows, ldx))[:, :P * Cp].copy()
+        if keep_prob < 1.0:
+            idx = (np.arange(rows)[:, None] * ldx + np.arange(P * Cp)[None, :])
+            v = np.where(self._dropout_keep(seed, idx, keep_prob), v * np.float32(1.0 / keep_prob), np.float32(0))
+        arr(dacc, (rows * P, Cp))[:] = v.reshape(rows * P, Cp)
+        return 0
+
+    def rgp_dense_dlogits(self, dlogits, out, B, T, N, Np, dtype, stream):
+        o = arr(out, (T * B, Np))
+        o[:] = 0.0
+        o[:, :N] = arr(dlogits, (B, T, N)).transpose(1, 0, 2).reshape(T * B, N)
+        return 0
+
+    def rgp_dense_gru_ru(self, xg, ldx, hg, bias_g, h, rh, u_out, r_save, M, H, Hp, dtype, stream):
         x, g, b, hh = arr(xg, (M, ldx)), arr(hg, (M, 2 * Hp)), arr(bias_g, (2 * Hp,)), arr(h, (M, Hp))
         r = _sig(x[:, :H] + g[:, :H] + b[:H])
         u = _sig(x[:, Hp:Hp + H] + g[:, Hp:Hp + H] + b[Hp:Hp + H])
@@ -562,9 +593,13 @@ class EmuLib(object):
         uo[:] = 0.0
         o[:, :H] = r * hh[:, :H]
         uo[:, :H] = u
+        if r_save:
+            rs = arr(r_save, (M, Hp))
+            rs[:] = 0.0
+            rs[:, :H] = r
         return 0
 
-    def rgp_dense_gru_c(self, xg, ldx, hc, bias_c, u, h, hn, hn_op, M, H, Hp, dtype, stream):
+    def rgp_dense_gru_c(self, xg, ldx, hc, bias_c, u, h, hn, hn_op, c_save, M, H, Hp, dtype, stream):
         x, c_, b = arr(xg, (M, ldx)), arr(hc, (M, Hp)), arr(bias_c, (Hp,))
         uu, hh = arr(u, (M, Hp)), arr(h, (M, Hp))
         c = np.tanh(x[:, 2 * Hp:2 * Hp + H] + c_[:, :H] + b[:H]).astype(np.float32)
@@ -573,6 +608,32 @@ class EmuLib(object):
         arr(hn, (M, Hp))[:] = v
         if int(hn_op) != int(hn):
             arr(hn_op, (M, Hp))[:] = v
+        if c_save:
+            cs = arr(c_save, (M, Hp))
+            cs[:] = 0.0
+            cs[:, :H] = c
+        return 0
+
+    def rgp_dense_gru_bwd_c(self, dh_head, dh_rec, u, c, hprev, dG, dhpart, M, H, Hp, dtype, stream):
+        dh = arr(dh_head, (M, Hp))[:, :H].copy()
+        if dh_rec:
+            dh += arr(dh_rec, (M, Hp))[:, :H]
+        uu, cc, hp = arr(u, (M, Hp))[:, :H], arr(c, (M, Hp))[:, :H], arr(hprev, (M, Hp))[:, :H]
+        g = arr(dG, (M, 3 * Hp))
+        g[:, Hp:] = 0.0
+        g[:, Hp:Hp + H] = dh * (hp - cc) * uu * (1 - uu)
+        g[:, 2 * Hp:2 * Hp + H] = dh * (1 - uu) * (1 - cc * cc)
+        d = arr(dhpart, (M, Hp))
+        d[:] = 0.0
+        d[:, :H] = dh * uu
+        return 0
+
+    def rgp_dense_gru_bwd_r(self, drh, r, hprev, dG, dhpart, M, H, Hp, dtype, stream):
+        d, rr, hp = arr(drh, (M, Hp))[:, :H], arr(r, (M, Hp))[:, :H], arr(hprev, (M, Hp))[:, :H]
+        g = arr(dG, (M, 3 * Hp))
+        g[:, :Hp] = 0.0
+        g[:, :H] = d * hp * rr * (1 - rr)
+        arr(dhpart, (M, Hp))[:, :H] += d * rr
         return 0
 
     def rgp_dense_logits(self, acc, ldacc, bias, logits, B, T, N, stream):

@@ -157,3 +157,48 @@ def test_dense_gru_variant_on_gpu(dtype, tol, B):
         _, ref2, _, _ = O.forward_loss_grads("gaze_rnn", p, gt[-2:].astype(np.float64), c3d=c3d[-2:].astype(np.float64))
         rel = np.abs(e.probs.cpu().numpy()[-2:] - ref2).max(axis=(2, 3)) / ref2.max(axis=(2, 3))
         assert rel.max() <= tol, rel.max()
+
+
+@pytest.mark.parametrize("dtype,tol", [("fp32", 1e-3), ("bf16", 5e-2)])
+def test_dense_gru_training_on_gpu(dtype, tol):
+    """SURVEY row a24, training half (gaze_rnn.py:447-478): hand-written BPTT of the dense variant at the reference's
+    sizes against torch autograd on the float64 oracle (per tensor, relative to its largest gradient: fp32 1e-3, bf16
+    5e-2 - the bars of the GRCN BPTT tests), then clip + Adam steps through the model class with live dropout."""
+    from recurrent_gaze_prediction_b200.dense_engine import DenseGruEngine
+    from recurrent_gaze_prediction_b200.models import gaze_rnn
+    rng = np.random.RandomState(2)
+    B, T = 3, 4
+    p = O.init_params_dense(seed=3)
+    e = DenseGruEngine(B=B, T=T, dtype=0 if dtype == "fp32" else 1, train=True)
+    e.load_tf_params(p)
+    c3d = SY.make_c3d(rng, B, T)
+    gt = O.normalize_probability_map(SY.make_gazemaps(rng, B, T, 49, 49)[0]).astype(np.float32)
+    e.forward(c3d=torch.from_numpy(c3d).cuda(), gt=torch.from_numpy(gt).cuda())
+    e.backward()
+    torch.cuda.synchronize()
+    got = e.op_to_tf(e.grads.cpu().numpy())
+    _, _, ref_loss, ref = O.forward_loss_grads("gaze_rnn", p, gt.astype(np.float64), c3d=c3d.astype(np.float64))
+    assert abs(float(e.loss.cpu()[0]) - ref_loss) <= (1e-5 if dtype == "fp32" else 2e-2) * abs(ref_loss)
+    for k, r in ref.items():
+        a = got[k].reshape(r.shape).astype(np.float64)
+        assert np.abs(a - r).max() <= tol * max(np.abs(r).max(), 1e-30), (k, np.abs(a - r).max(), np.abs(r).max())
+    assert float(e.grads[torch.from_numpy(e.pad_mask() == 0).cuda()].abs().max()) == 0.0
+    # dropout: forward mask == backward mask (the gradient of the dropped inputs' projection rows is exactly zero)
+    e.keep_prob, e.dropout_seed = 0.5, 77
+    e.forward(c3d=torch.from_numpy(c3d).cuda(), gt=torch.from_numpy(gt).cuda())
+    e.backward()
+    X = e.X[:T * B, :e.I].float().cpu().numpy()
+    dP = e.dPacc[:T * B * e.P].float().cpu().numpy().reshape(T * B, e.I)
+    frac = (X != 0).mean()
+    assert 0.45 < frac < 0.55 and not dP[X == 0].any() and np.abs(dP[X != 0]).max() > 0
+    # the model class trains it
+    c = gaze_rnn.GRUModelConfig()
+    c.n_lstm_steps, c.batch_size, c.dtype, c.initial_learning_rate, c.steps_per_logprint = T, 2, dtype, 1e-3, 1000
+    ds = SY.read_synthetic_data_sets(6, 6, 6, T=T)
+    m = gaze_rnn.GazePredictionGRU(None, ds, c)
+    p0 = m.engine.params.clone()
+    losses = []
+    for k in range(3):
+        assert m.single_step(train_mode=True) == k + 1
+        losses.append(m.last_loss)
+    assert all(np.isfinite(losses)) and float((m.engine.params - p0).abs().max()) > 1e-4

@@ -135,8 +135,6 @@ def test_loss_builder_and_errors():
     c.loss_type = "hinge"
     with pytest.raises(NotImplementedError):
         gaze_grcn.GazePredictionGRCN({'lib': lib}, data(), c)
-    with pytest.raises(NotImplementedError):                     # the dense GRU variant does not train (inference only)
-        gaze_rnn.GazePredictionGRU({'lib': lib}, data(), small_config())
     c = small_config(B=4)
     with pytest.raises(ValueError):
         gaze_grcn.GazePredictionGRCN({'lib': lib, 'world_size': 3}, data(), c)
@@ -268,6 +266,50 @@ def test_dense_gru_variant_matches_oracle():
     assert (49 * 32 + 49, (49 * 32 + 63) // 64 * 64, (1617 + 127) // 128 * 128, (2401 + 127) // 128 * 128) == (1617, 1600, 1664, 2432)
 
 
+@pytest.mark.parametrize("keep_prob", [1.0, 0.5])
+def test_dense_gru_bptt_matches_oracle_autograd(keep_prob):
+    """BPTT of the dense variant (dense_engine.backward) against torch autograd on the oracle's restatement; with dropout
+    the engine's own counter-based mask (read back from the packed input rows) is replayed on the oracle."""
+    from recurrent_gaze_prediction_b200.dense_engine import DenseGruEngine
+    rng = np.random.RandomState(1)
+    B, T = 3, 4
+    p = O.init_params_dense(dim_proj=4, dim_feature=16, GH=7, GW=7, seed=2, kernel_scale=1.5)
+    p["RNN/gru_cell/gates/bias"] = 1.0 + 0.3 * rng.standard_normal(p["RNN/gru_cell/gates/bias"].shape)
+    p["RNN/gru_cell/candidate/bias"] = 0.3 * rng.standard_normal(p["RNN/gru_cell/candidate/bias"].shape)
+    e = DenseGruEngine(B=B, T=T, Cp=4, Cfeat=16, GH=7, dtype=0, device="cpu", lib=EmuLib(), train=True)
+    e.load_tf_params(p)
+    e.keep_prob, e.dropout_seed = keep_prob, 12345
+    c3d = SY.make_c3d(rng, B, T, dim_feature=16)
+    gt = O.normalize_probability_map(SY.make_gazemaps(rng, B, T, 7, 7)[0]).astype(np.float32)
+    e.forward(c3d=torch.from_numpy(c3d), gt=torch.from_numpy(gt))
+    e.backward()
+    got = e.op_to_tf(e.grads.numpy())
+    # oracle with the same mask on the embedded features
+    pt = O.to_torch(p, requires_grad=True)
+    emb = O.project_c3d(torch.tensor(c3d, dtype=torch.float64), pt)               # [B,T,7,7,4]
+    X = e.X.numpy()[:T * B, :e.I].reshape(T, B, 7, 7, 4).transpose(1, 0, 2, 3, 4)
+    if keep_prob < 1.0:
+        mask = torch.tensor((X != 0).astype(np.float64)) / keep_prob
+        frac = float((X != 0).mean())
+        assert 0.4 < frac < 0.6
+        emb = emb * mask
+    H = p["RNN/gru_cell/candidate/bias"].shape[0]
+    h = emb.new_zeros(B, H)
+    maps = []
+    for i in range(T):
+        h = O.dense_gru_cell(emb[:, i].reshape(B, -1), h, pt)
+        maps.append((h @ pt["proj_out_W"] + pt["proj_out_b"]).reshape(B, 7, 7))
+    logits = torch.stack(maps).permute(1, 0, 2, 3)
+    loss = O.loss_fn(logits, torch.tensor(gt, dtype=torch.float64))
+    assert abs(float(e.loss[0]) - float(loss)) <= 1e-5 * abs(float(loss))
+    grads = torch.autograd.grad(loss, [pt[k] for k in p])
+    for k, gr in zip(p, grads):
+        r = gr.numpy()
+        assert np.abs(got[k] - r).max() <= 2e-4 * max(np.abs(r).max(), 1e-12), k
+    # nothing leaks into the zero padding of the op layouts
+    assert np.all(e.grads.numpy()[e.pad_mask() == 0] == 0.0)
+
+
 def test_dense_gru_model_class_contract():
     c = small_config(T=3, B=2)
     c.dim_cnn_proj_dense = 4
@@ -282,6 +324,20 @@ def test_dense_gru_model_class_contract():
     ret = m.generate(ds.valid, max_instances=2)
     assert ret['pred_gazemap_list'].shape == (6, 49, 49)
     assert np.allclose(ret['pred_gazemap_list'].sum(axis=(1, 2)), 1.0, atol=1e-5)
+    # trainable (the reference trains this class: gaze_rnn.py:447-478): steps run, dropout live, loss finite and moving
+    c.trainable = True
+    c.initial_learning_rate = 1e-2
+    mt = gaze_rnn.GazePredictionGRU({'lib': EmuLib()}, ds, c)
+    assert mt.train_op is not None
+    p0 = mt.engine.params.clone()
+    for k in range(2):
+        assert mt.single_step(train_mode=True) == k + 1
+    assert mt.engine.keep_prob == 0.5 and np.isfinite(mt.last_loss)
+    moved = (mt.engine.params - p0).abs().numpy()
+    mask = mt.engine.pad_mask()
+    assert moved[mask > 0].max() > 1e-4 and moved[mask == 0].max() == 0.0        # the zero padding never moves
+    mt.single_step(train_mode=False)
+    assert mt.engine.keep_prob == 1.0
 
 
 def test_optimisation_method_and_device_side_schedule(tmp_path):

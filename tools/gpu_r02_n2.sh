@@ -2,6 +2,12 @@
 # round 2: the driver's N=2 launch (torchrun, one rank per GPU): default bench line with the train sub-record (NCCL all-reduce), reference arm
 mkdir -p gpurun_out
 cd "$GRAFT_REPO_ROOT" 2>/dev/null || true
-timeout 600 python -m pytest tests/test_gpu_optimizer.py tests/test_gpu_baseline_configs.py -m gpu -q > gpurun_out/r02n2_pytest.log 2>&1; echo "pytest rc=$?"; tail -8 gpurun_out/r02n2_pytest.log
-timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 > gpurun_out/r02n2_bench.json 2> gpurun_out/r02n2_bench.err; echo "bench rc=$?"; tail -5 gpurun_out/r02n2_bench.err; head -c 1500 gpurun_out/r02n2_bench.json
-timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29512 bench.py --impl reference --gpus 2 --steps 3 --warmup 1 > gpurun_out/r02n2_ref.json 2> gpurun_out/r02n2_ref.err; echo "ref rc=$?"; head -c 400 gpurun_out/r02n2_ref.json
+timeout 420 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 > gpurun_out/r02n2_bench.json 2> gpurun_out/r02n2_bench.err; echo "bench rc=$?"; tail -5 gpurun_out/r02n2_bench.err | cut -c1-300
+python - <<'PY'
+import json
+d=json.loads(open('gpurun_out/r02n2_bench.json').read().strip().splitlines()[-1])
+print("n_gpus", d["n_gpus"], "value", d["value"], "e2e", d["e2e"]["value"])
+t=d["train"]; print("train", t["value"], t["ms_per_step"], "allreduce_ms", t.get("allreduce_ms"), "e2e", t["e2e"]["value"])
+print("config4", {k:(v.get("value"), v.get("persistent_recurrence")) for k,v in d["config4"].items() if isinstance(v,dict)})
+print("config5", d["config5"].get("value"), d["config5"].get("error"))
+PY
