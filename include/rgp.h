@@ -81,6 +81,11 @@ typedef struct rgp_tapgemm_args {
   const float* dhs;             /* [M, Ch] fp32 q-layout: dL/d(head input) of the step whose gates are differentiated */
   const float* save_z;          /* [M, Ch] saved z of that step */
   void* dg; int ldg;            /* dL/d(pre-activations) [M, 3Ch] operand dtype, columns z | r | c */
+  /* Dense-M mode of a 3x3 SAME convolution (RGP_EPI_STORE_F32, 9 taps in (ky,kx) order, tcgen05 engine only): M counts only
+   * the G*G real positions of each frame (M = frames * G*G instead of frames * S: 49 instead of 64 rows per 7x7 frame).  A
+   * is the same p-layout operand (S, Wp, G describe it); each tap's A tile is fetched by a TMA im2col load with hardware
+   * zero fill at the frame borders, and row m = f*G*G + y*G + x is stored at the q-row f*S + y*Wp + x of out_f32. */
+  int im2col;
 } rgp_tapgemm_args;
 
 int rgp_tapgemm(const rgp_tapgemm_args* a, void* stream);

@@ -88,6 +88,12 @@ __device__ __forceinline__ RowInfo make_row(const rgp_tapgemm_args& a, int m) {
     case RGP_EPI_STORE_F32:
     case RGP_EPI_STORE_OP:
       r.valid = true;
+      if (a.im2col) {        // dense-M conv: row m = f*G*G + y*G + x is stored at the q-row f*S + y*Wp + x
+        const int P = a.G * a.G;
+        const int f = m / P, p = m - f * P;
+        const int y = p / a.G, x = p - y * a.G;
+        r.m = f * a.S + y * a.Wp + x;
+      }
       break;
     case RGP_EPI_UP7: {   // rows = the 8x8 p-layout blocks (a,b) of the bottom state; hy, hx = 7a, 7b (operand coordinates)
       int f = m / a.S, q = m - f * a.S;

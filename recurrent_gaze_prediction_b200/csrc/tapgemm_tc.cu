@@ -418,7 +418,14 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           uint8_t* sa = smem + stage * C::kStageBytes;
           uint8_t* sb = sa + BM * BK * 2;
           mbar_expect_tx(&full[stage], C::kStageBytes);
-          tma_load_2d(sa, &tmA, &full[stage], kc * BK, m0 + a.tap_off[tap]);
+          if (a.im2col) {            // dense-M conv: 128 consecutive real positions from m0, tap (ky, kx) as the im2col offset
+            const int P = a.G * a.G;
+            const int fn = m0 / P, rem = m0 - fn * P;
+            const int hy = rem / a.G, wx = rem - hy * a.G;
+            tma_load_im2col_4d(sa, &tmA, &full[stage], kc * BK, wx - 1, hy - 1, fn, (uint16_t)(tap % 3), (uint16_t)(tap / 3));
+          } else {
+            tma_load_2d(sa, &tmA, &full[stage], kc * BK, m0 + a.tap_off[tap]);
+          }
           tma_load_2d(sb, &tmB, &full[stage], kc * BK, tap * a.N + n0);
           if (++stage == C::kStages) { stage = 0; phase ^= 1; }
         }
@@ -685,7 +692,7 @@ int launch(const rgp_tapgemm_args& a, cudaStream_t s) {
   // weight ring and 0.93 ms with 24 stages and 4 slab slots (profiles/r01_notes.md passes 7 and 18).
   // ... except many-tap narrow GEMMs (the cascade's 5x5 top cell: 25 taps, N = 16, K = 64): there the per-tap A boxes
   // (25 x 16 KB per 128 rows) are the whole cost and the slab (128 + 4*51+4 rows, two TMA boxes) removes them.
-  if (a.ntaps > 1 && (BN >= 128 || a.ntaps > 16) && slab_enabled()) {
+  if (a.ntaps > 1 && (BN >= 128 || a.ntaps > 16) && slab_enabled() && !a.im2col) {
     int mn = a.tap_off[0], mx = a.tap_off[0];
     for (int i = 1; i < a.ntaps; ++i) { mn = a.tap_off[i] < mn ? a.tap_off[i] : mn; mx = a.tap_off[i] > mx ? a.tap_off[i] : mx; }
     sc.rows = (BM + (mx - mn) + 7) & ~7;
@@ -700,7 +707,14 @@ int launch(const rgp_tapgemm_args& a, cudaStream_t s) {
     slab = sc.boxrows <= 256 && sc.nw >= 3;
   }
   CUtensorMap tmA, tmB;
-  int rc = make_map(a.A, a.rowsA, a.lda, a.K, slab ? sc.boxrows : BM, &tmA);
+  int rc;
+  if (a.im2col) {
+    const long long frames = a.M / (a.G * a.G);
+    rc = tc::encode_map_im2col_bf16((const __nv_bfloat16*)a.A + (long long)(a.Wp + 1) * a.lda, a.K, a.G, frames, a.lda, a.Wp,
+                                    a.S, 1, BM, &tmA);
+  } else {
+    rc = make_map(a.A, a.rowsA, a.lda, a.K, slab ? sc.boxrows : BM, &tmA);
+  }
   if (rc) return rc;
   rc = make_map(a.Bw, (long long)a.ntaps * a.N, a.K, a.K, BN, &tmB);
   if (rc) return rc;
@@ -778,6 +792,33 @@ int encode_map_bf16(const void* base, long long dim0, long long dim1, long long 
   return 0;
 }
 
+int encode_map_im2col_bf16(const void* base, int C, int G, long long frames, int ld, int Wp, int S, int pad, int pixels,
+                           CUtensorMap* out) {
+  static PFN_cuTensorMapEncodeIm2col_v12000 fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_cuTensorMapEncodeIm2col_v12000>(p);
+  });
+  if (!fn) { set_error("cuTensorMapEncodeIm2col not available from the driver"); return -38; }
+  cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)G, (cuuint64_t)G, (cuuint64_t)frames};
+  cuuint64_t strides[3] = {(cuuint64_t)ld * 2, (cuuint64_t)Wp * ld * 2, (cuuint64_t)S * ld * 2};
+  // bounding box of the base pixel (the filter's top-left position): [-pad, G - 1 + pad - (k-1)] = [-pad, G-1-pad]
+  int lower[2] = {-pad, -pad}, upper[2] = {-pad, -pad};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, lower, upper, 64,
+                  (cuuint32_t)pixels, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeIm2col failed (%d) base=%p C=%d G=%d frames=%lld ld=%d", (int)r, base, C, G, frames, ld);
+    return -5;
+  }
+  return 0;
+}
+
 int num_sms() {
   static int cache[kMaxDevices] = {0};
   const int dev = current_device();
@@ -794,6 +835,10 @@ int num_sms() {
 
 int tapgemm_tc(const rgp_tapgemm_args& a, cudaStream_t s) {
   RGP_CHECK_ARG(a.K % BK == 0, "tapgemm_tc: K=%d must be a multiple of %d", a.K, BK);
+  if (a.im2col)
+    RGP_CHECK_ARG(a.ntaps == 9 && a.epi == RGP_EPI_STORE_F32 && !a.accumulate && a.G > 0 && a.M % (a.G * a.G) == 0 &&
+                  a.N % 32 == 0 && a.S >= (a.G + 1) * a.Wp - 1 && a.Wp > a.G,
+                  "tapgemm_tc: im2col mode is a 3x3 SAME conv with RGP_EPI_STORE_F32 (ntaps=%d epi=%d M=%d G=%d)", a.ntaps, a.epi, a.M, a.G);
   RGP_CHECK_ARG(a.lda % 8 == 0, "tapgemm_tc: lda=%d must be a multiple of 8 (16-byte TMA stride)", a.lda);
   RGP_CHECK_ARG(((uintptr_t)a.A & 15) == 0 && ((uintptr_t)a.Bw & 15) == 0, "tapgemm_tc: operands must be 16-byte aligned");
   const int mtiles = (a.M + BM - 1) / BM;

@@ -505,9 +505,14 @@ class GazeEngine(TrainStateMixin):
     def stage_i2h(self):
         """(a3) input half of every gate for all T frames at once: gaze_grcn.py:108-109,112-113,122-123."""
         NX = self.ngx * self.Ch
+        # Dense-M mode on the tcgen05 engine: only the G*G real positions of a frame are GEMM rows (49 instead of the 64
+        # p-layout rows at G = 7: -23 % MMA work), each tap's A tile comes from a TMA im2col load with hardware zero fill at
+        # the frame borders; rows land at the same q-rows of Xg.  RGP_IM2COL=0 restores the slab path (A/B runs).
+        dense = (self.dtype == 1 and self.engine != 1 and NX % 32 == 0 and os.environ.get("RGP_IM2COL", "1") != "0")
         self._gemm(A=self.Xp.data_ptr(), rowsA=self.Xp.shape[0], lda=self.Cin, Bw=self._pop("Wx_op"),
-                   M=self.T * self.B * self.S, N=NX, K=self.Cin, taps=self.taps3, epi=L.EPI_STORE_F32,
-                   out_f32=self.Xg.data_ptr(), ldo=NX, S=self.S, Wp=self.Wp, G=self.G)
+                   M=self.T * self.B * (self.P if dense else self.S), N=NX, K=self.Cin, taps=self.taps3,
+                   epi=L.EPI_STORE_F32, out_f32=self.Xg.data_ptr(), ldo=NX, S=self.S, Wp=self.Wp, G=self.G,
+                   im2col=1 if dense else 0)
 
     # ---- recurrent state access (zero_state / cell-level API: gaze_grcn.py:132-146, gaze_lstm.py:136-148)
     def _pview(self, buf, t):

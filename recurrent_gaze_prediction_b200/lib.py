@@ -35,6 +35,7 @@ class TapGemmArgs(C.Structure):
         ("save_r", _vp), ("save_c", _vp),
         ("bias", _vp), ("bias2", _vp), ("alpha", _f),
         ("dhpart", _vp), ("dhs", _vp), ("save_z", _vp), ("dg", _vp), ("ldg", _i),
+        ("im2col", _i),
     ]
 
 

@@ -350,3 +350,27 @@ def test_fc_head_backward_all_steps_matches_per_step_and_numpy():
     for gw_, gb_ in (out[0][1:], out[1][1:]):
         assert np.abs(gw_ - gw_ref).max() <= 1e-4 * np.abs(gw_ref).max() + 1e-4
         assert abs(gb_[0] - gb_ref) <= 1e-4 * abs(gb_ref) + 1e-3
+
+
+@pytest.mark.parametrize("G,B,T,Ch,lstm", [(7, 3, 5, 128, False), (7, 37, 7, 256, False), (14, 2, 3, 128, True)])
+def test_i2h_im2col_dense_rows_equal_slab_path(G, B, T, Ch, lstm, monkeypatch):
+    """The input-half conv for all T frames in dense-M mode (TMA im2col loads, only the G*G real positions are GEMM rows)
+    against the padded slab path: same pre-activations at every real position (fp32 accumulation order differs: 1e-5 of
+    the tensor's scale), pad rows of Xg untouched (zero)."""
+    import os
+    model = "gaze_lstm" if lstm else "gaze_grcn77"
+    p = O.init_params(model, hidden=Ch, T=T, grid=G, seed=4, regime="S", head="fc")
+    emb = torch.from_numpy(SY.make_embedded(np.random.RandomState(3), B, T, G, 512)).cuda()
+    out = []
+    for flag in ("1", "0"):
+        monkeypatch.setenv("RGP_IM2COL", flag)
+        eng = GazeEngine(model, B=B, T=T, G=G, Ch=Ch, dtype=1, device="cuda", head="fc")
+        eng.load_tf_params(p)
+        eng.stage_embed(emb=emb)
+        eng.stage_i2h()
+        torch.cuda.synchronize()
+        out.append(eng.Xg.view(T * B, eng.Wp, eng.Wp, -1).cpu().numpy())
+    a, b = out
+    scale = np.abs(b[:, :G, :G]).max()
+    assert np.abs(a[:, :G, :G] - b[:, :G, :G]).max() <= 1e-5 * scale
+    assert not a[:, G].any() and not a[:, :, G].any()          # dense mode never writes the pad row / column
