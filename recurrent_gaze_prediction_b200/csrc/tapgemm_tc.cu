@@ -330,6 +330,7 @@ struct SlabCfg {
   int min_off;   // smallest tap offset
   int nw;        // weight-ring stages
   int slots;     // slab slots (k-chunks of A in flight)
+  int tg;        // taps per weight stage (narrow tiles: one TMA box of tg*BN rows and ONE barrier round trip per tg taps)
 };
 constexpr int kSlabMaxSlots = 4;
 constexpr int kSlabBarBytes = 512;     // (2 * nw + 8) mbarriers + the TMEM slot, nw <= kSlabMaxW
@@ -344,9 +345,10 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   constexpr int kWBytes = BN * BK * 2;
+  const int wstage = SLAB ? sc.tg * kWBytes : kWBytes;   // bytes of one weight stage (tg taps)
   const int nstage = SLAB ? sc.nw : C::kStages;          // barrier pairs of the (weight) ring
-  const int ring_bytes = SLAB ? sc.nw * kWBytes + sc.slots * sc.bytes : C::kStages * C::kStageBytes;
-  uint8_t* slab0 = smem + (SLAB ? sc.nw * kWBytes : 0);
+  const int ring_bytes = SLAB ? sc.nw * wstage + sc.slots * sc.bytes : C::kStages * C::kStageBytes;
+  uint8_t* slab0 = smem + (SLAB ? sc.nw * wstage : 0);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + ring_bytes);
   uint64_t* full = bars;
   uint64_t* empty = bars + nstage;
@@ -398,10 +400,10 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           for (int bx = 0; bx < sc.nbox; ++bx)     // boxrows % 8 == 0: every box starts on a swizzle-atom boundary
             tma_load_2d(slab0 + as * sc.bytes + bx * sc.boxrows * (BK * 2), &tmA, &afull[as], kc * BK,
                         m0 + sc.min_off + bx * sc.boxrows);
-          for (int tap = 0; tap < a.ntaps; ++tap) {
+          for (int tap = 0; tap < a.ntaps; tap += sc.tg) {     // tg > 1 only when N == BN: the taps' rows are contiguous
             mbar_wait(&empty[ws], wph ^ 1);
-            mbar_expect_tx(&full[ws], kWBytes);
-            tma_load_2d(smem + ws * kWBytes, &tmB, &full[ws], kc * BK, tap * a.N + n0);
+            mbar_expect_tx(&full[ws], (uint32_t)wstage);       // rows past the last tap are out of bounds: zero filled
+            tma_load_2d(smem + ws * wstage, &tmB, &full[ws], kc * BK, tap * a.N + n0);
             if (++ws == sc.nw) { ws = 0; wph ^= 1; }
           }
           if (++as == sc.slots) { as = 0; aph ^= 1; }
@@ -446,18 +448,21 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         // stage / phase walk the weight ring here; aslot / aphase the slab slots
         for (int kc = 0; kc < kchunks; ++kc) {
           mbar_wait(&afull[aslot], aphase);
-          for (int tap = 0; tap < a.ntaps; ++tap) {
+          for (int tap0 = 0; tap0 < a.ntaps; tap0 += sc.tg) {
             mbar_wait(&full[stage], phase);
             tc_fence_after();
             if (lane == 0) {
-              const uint32_t sa = smem_u32(slab0 + aslot * sc.bytes) + (uint32_t)(a.tap_off[tap] - sc.min_off) * (BK * 2);
-              const uint32_t sb = smem_u32(smem + stage * kWBytes);
-              const uint64_t adesc = make_sdesc(sa), bdesc = make_sdesc(sb);
+              const int tend = (tap0 + sc.tg < a.ntaps) ? tap0 + sc.tg : a.ntaps;
+              for (int tap = tap0; tap < tend; ++tap) {
+                const uint32_t sa = smem_u32(slab0 + aslot * sc.bytes) + (uint32_t)(a.tap_off[tap] - sc.min_off) * (BK * 2);
+                const uint32_t sb = smem_u32(smem + stage * wstage) + (uint32_t)(tap - tap0) * kWBytes;
+                const uint64_t adesc = make_sdesc(sa), bdesc = make_sdesc(sb);
 #pragma unroll
-              for (int k = 0; k < BK / 16; ++k)
-                tc_mma_bf16(tacc, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (kc | tap | k) ? 1u : 0u);
+                for (int k = 0; k < BK / 16; ++k)
+                  tc_mma_bf16(tacc, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (kc | tap | k) ? 1u : 0u);
+              }
               tc_commit(&empty[stage]);
-              if (tap == a.ntaps - 1) {
+              if (tend == a.ntaps) {
                 tc_commit(&aempty[aslot]);
                 if (kc == kchunks - 1) tc_commit(&tfull[acc]);
               }
@@ -685,14 +690,18 @@ template <int BN>
 int launch(const rgp_tapgemm_args& a, cudaStream_t s) {
   using C = Cfg<BN>;
   // slab geometry: all taps of the tile inside one TMA box of <= 256 rows
-  SlabCfg sc{0, 1, 0, 0, 0, 0, 2};
+  SlabCfg sc{0, 1, 0, 0, 0, 0, 2, 1};
   bool slab = false;
   // Narrow tiles (the N = 48 head GEMM) keep the per-tap boxes: they are bound by the cost of their small MMAs (~150 clk per
   // 128x48x16 MMA, 580 clk per k-step whatever the operand traffic), measured 0.87 ms per-tap vs 0.95 ms slab with an 8-stage
   // weight ring and 0.93 ms with 24 stages and 4 slab slots (profiles/r01_notes.md passes 7 and 18).
   // ... except many-tap narrow GEMMs (the cascade's 5x5 top cell: 25 taps, N = 16, K = 64): there the per-tap A boxes
   // (25 x 16 KB per 128 rows) are the whole cost and the slab (128 + 4*51+4 rows, two TMA boxes) removes them.
-  if (a.ntaps > 1 && (BN >= 128 || a.ntaps > 16) && slab_enabled() && !a.im2col) {
+  // Narrow tiles (N = 48 head, N = 16 top cell of the cascade) are bound by the MMA warp's per-k-step barrier round trip,
+  // not by bytes (measured: per-tap boxes 0.87 ms, slab with one barrier per tap 0.93-0.95 ms): when N == BN the weight rows
+  // of consecutive taps are contiguous, so ONE TMA box / barrier serves tg = 256 / BN taps (16 or 64 MMAs per wait).
+  const bool group = BN <= 64 && a.N == BN && BN % 8 == 0 && a.ntaps >= 4;
+  if (a.ntaps > 1 && (BN >= 128 || group) && slab_enabled() && !a.im2col) {
     int mn = a.tap_off[0], mx = a.tap_off[0];
     for (int i = 1; i < a.ntaps; ++i) { mn = a.tap_off[i] < mn ? a.tap_off[i] : mn; mx = a.tap_off[i] > mx ? a.tap_off[i] : mx; }
     sc.rows = (BM + (mx - mn) + 7) & ~7;
@@ -701,8 +710,10 @@ int launch(const rgp_tapgemm_args& a, cudaStream_t s) {
     sc.bytes = (sc.rows * BK * 2 + 1023) & ~1023;
     sc.min_off = mn;
     sc.slots = (BN <= 64) ? kSlabMaxSlots : 2;      // narrow tiles finish a k-chunk faster than a slab load takes
+    if (group) { sc.tg = 256 / BN; if (sc.tg > a.ntaps) sc.tg = a.ntaps; }
+    if (sc.slots * sc.bytes > 120 * 1024) sc.slots = 2;
     const int fixed = 1024 + kSlabBarBytes + kEpiScratchBytes + sc.slots * sc.bytes;
-    sc.nw = (kSmemBudget - fixed) / (BN * BK * 2);
+    sc.nw = (kSmemBudget - fixed) / (sc.tg * BN * BK * 2);
     if (sc.nw > kSlabMaxW) sc.nw = kSlabMaxW;
     slab = sc.boxrows <= 256 && sc.nw >= 3;
   }
@@ -716,7 +727,7 @@ int launch(const rgp_tapgemm_args& a, cudaStream_t s) {
     rc = make_map(a.A, a.rowsA, a.lda, a.K, slab ? sc.boxrows : BM, &tmA);
   }
   if (rc) return rc;
-  rc = make_map(a.Bw, (long long)a.ntaps * a.N, a.K, a.K, BN, &tmB);
+  rc = make_map(a.Bw, (long long)a.ntaps * a.N, a.K, a.K, (slab ? sc.tg : 1) * BN, &tmB);
   if (rc) return rc;
   static PerDeviceFlag attr_set = {};
   if (attr_set.need()) {
@@ -730,7 +741,7 @@ int launch(const rgp_tapgemm_args& a, cudaStream_t s) {
   int grid = mtiles * ntiles;
   if (grid > num_sms()) grid = num_sms();
   if (slab) {
-    const int smem_bytes = sc.nw * BN * BK * 2 + sc.slots * sc.bytes + 1024 + kSlabBarBytes + kEpiScratchBytes;
+    const int smem_bytes = sc.nw * sc.tg * BN * BK * 2 + sc.slots * sc.bytes + 1024 + kSlabBarBytes + kEpiScratchBytes;
     tapgemm_tc_kernel<BN, true><<<grid, NTHREADS, smem_bytes, s>>>(tmA, tmB, a, sc);
   } else {
     tapgemm_tc_kernel<BN, false><<<grid, NTHREADS, C::kSmemBytes, s>>>(tmA, tmB, a, sc);
