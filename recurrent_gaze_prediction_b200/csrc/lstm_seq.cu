@@ -27,6 +27,7 @@ constexpr int BM = 128, BK = 64;
 constexpr int NC = 16;                    // channels per CTA
 constexpr int NG = 3 * NC;                // MMA N: i | f | o
 constexpr int NTHREADS = 192;
+constexpr int NTHREADS_MULTI = 192;      // (two alternating epilogue groups of four warps were measured SLOWER: 5.21 vs 4.85 ms)
 constexpr int kMaxSlabRows = 160;         // 128 + 2*15 + 2 at G = 14
 constexpr int kMaxKch = 2;                // Ch <= 128: the weight slice must fit in shared memory
 constexpr int kWTileBytes = NG * BK * 2;  // 6144: one (tap, k-chunk) B operand
@@ -298,6 +299,241 @@ lstm_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Multi-tile variant: more tiles than co-resident (tile, split) CTAs (14x14 at 64 clips: 113 tiles x 8 splits).  The grid is
+// R row groups x nsplit splits with R = SMs / nsplit; CTA (g, split) keeps ITS split's weight slice resident and walks the
+// tiles g, g+R, g+2R, ... of every step in that order.  Item (t, k) = tile k of step t; dependencies of an item are the
+// step-(t-1) items of its tile and the two neighbours, all earlier in every CTA's program order, so the counter waits
+// cannot cycle.  Pipelining inside a CTA: two slab buffers and two TMEM accumulators - the slab of item i+1 loads while
+// the MMAs of item i run, the MMAs of item i+1 run while the epilogue of item i does the gate maths.  The cell state
+// lives in global memory (fp32, own rows / channels only: no hazard), the peepholes of the CTA's 16 channels are a
+// [gate][channel][position] table in shared memory.
+// ---------------------------------------------------------------------------------------------------------------------
+constexpr int kMaxP = 196;                                     // G <= 14
+constexpr int kSmemPeepTab = 3 * NC * kMaxP * (int)sizeof(float);   // 37632
+constexpr int kSmemBytesMulti = kSmemW + 2 * kSmemSlab + kSmemPeepTab + 256 + 1024;
+
+__global__ void __launch_bounds__(NTHREADS_MULTI, 1)
+lstm_seq_multi_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ CUtensorMap tmW,
+                      const rgp_lstm_seq_args a, const int slab_rows, const int R) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* wsm = smem;
+  uint8_t* slab = smem + kSmemW;                          // [buf][kc]
+  float* peep = reinterpret_cast<float*>(smem + kSmemW + 2 * kSmemSlab);   // [gate][channel][position]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kSmemW + 2 * kSmemSlab + kSmemPeepTab);
+  uint64_t* wfull = bars;
+  uint64_t* fullA = bars + 1;                             // [buf][kMaxKch]
+  uint64_t* slab_free = fullA + 2 * kMaxKch;              // [buf]: the MMAs that read the buffer have completed
+  uint64_t* acc_full = slab_free + 2;                     // [buf]
+  uint64_t* acc_free = acc_full + 2;                      // [buf]: the epilogue has read the accumulator out of TMEM
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_free + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int Ch = a.Ch, G = a.G, Wp = G + 1, S = Wp * Wp, P = G * G;
+  const int nsplit = Ch / NC;
+  const int grp = (int)(blockIdx.x / nsplit), split = (int)(blockIdx.x % nsplit);
+  const int ch0 = split * NC;
+  const int M = a.B * S;
+  const int mtiles = (M + BM - 1) / BM;
+  const int ntl = (mtiles - grp + R - 1) / R;             // tiles of this CTA: grp, grp + R, ...
+  const int kch = Ch / BK;
+  int* const err = a.flags + mtiles;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmH) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmW) : "memory");
+    mbar_init(wfull, 1);
+    for (int i = 0; i < 2 * kMaxKch; ++i) mbar_init(&fullA[i], 1);
+    for (int i = 0; i < 2; ++i) { mbar_init(&slab_free[i], 1); mbar_init(&acc_full[i], 1); mbar_init(&acc_free[i], 4); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"(128u)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  // peephole table of this CTA's channels
+  for (int i = threadIdx.x; i < 3 * NC * P; i += NTHREADS_MULTI) {
+    const int g = i / (NC * P), r = i - g * (NC * P), j = r / P, p = r - j * P;
+    const float* pw = g == 0 ? a.wci : (g == 1 ? a.wcf : a.wco);
+    peep[(g * NC + j) * kMaxP + p] = pw[(long long)p * Ch + ch0 + j];
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== dependency wait + TMA producer =====================
+    if (lane == 0) {
+      mbar_expect_tx(wfull, (uint32_t)(9 * kch * kWTileBytes));
+      for (int tap = 0; tap < 9; ++tap)
+        for (int kc = 0; kc < kch; ++kc)
+          for (int g = 0; g < 3; ++g)
+            tma_load_2d(wsm + (tap * kch + kc) * kWTileBytes + g * (NC * BK * 2), &tmW, wfull, kc * BK,
+                        tap * 3 * Ch + g * Ch + ch0);
+    }
+    bool dead = false;
+    long long it = 0;
+    for (int t = 0; t < a.T; ++t) {
+      for (int k = 0; k < ntl; ++k, ++it) {
+        const int tile = grp + k * R;
+        const int buf = (int)(it & 1);
+        const int nb = tile - 1 + lane;
+        const bool watch = lane < 3 && nb >= 0 && nb < mtiles;
+        if (t > 0 && !dead) {
+          const int need = nsplit * t;
+          const long long t0 = clock64();
+          for (;;) {
+            const bool ok = !watch || ld_acquire(a.flags + nb) >= need;
+            if (__all_sync(0xffffffffu, ok)) break;
+            bool bad = false;
+            if (lane == 0) {
+              bad = ld_acquire(err) != 0;
+              if (!bad && clock64() - t0 > kSpinLimit) { atomicExch(err, 1); bad = true; }
+            }
+            if (__any_sync(0xffffffffu, bad)) { dead = true; break; }
+          }
+        }
+        if (lane == 0) {
+          if (it >= 2) mbar_wait(&slab_free[buf], (uint32_t)(((it >> 1) - 1) & 1));   // MMAs of item it-2 are done
+          fence_proxy_async();
+          for (int kc = 0; kc < kch; ++kc) {
+            mbar_expect_tx(&fullA[buf * kMaxKch + kc], (uint32_t)(slab_rows * BK * 2));
+            tma_load_2d(slab + (buf * kMaxKch + kc) * kSlabBytes, &tmH, &fullA[buf * kMaxKch + kc], kc * BK,
+                        t * M + tile * BM);
+          }
+        }
+        __syncwarp();
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(NG >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+    mbar_wait(wfull, 0);
+    const long long nitems = (long long)a.T * ntl;
+    for (long long it = 0; it < nitems; ++it) {
+      const int buf = (int)(it & 1);
+      const uint32_t par = (uint32_t)((it >> 1) & 1);
+      if (it >= 2) mbar_wait(&acc_free[buf], par ^ 1);        // the epilogue of item it-2 has read this accumulator
+      tc_fence_after();
+      const uint32_t tacc = tmem_base + (uint32_t)(buf * 64);
+      for (int kc = 0; kc < kch; ++kc) {
+        mbar_wait(&fullA[buf * kMaxKch + kc], par);
+        tc_fence_after();
+        if (lane == 0) {
+          for (int tap = 0; tap < 9; ++tap) {
+            const int off = (tap / 3) * Wp + (tap % 3);
+            const uint64_t adesc = make_sdesc(smem_u32(slab + (buf * kMaxKch + kc) * kSlabBytes) + (uint32_t)off * (BK * 2));
+            const uint64_t bdesc = make_sdesc(smem_u32(wsm + (tap * kch + kc) * kWTileBytes));
+#pragma unroll
+            for (int kk = 0; kk < BK / 16; ++kk)
+              tc_mma_bf16(tacc, adesc + (uint64_t)(2 * kk), bdesc + (uint64_t)(2 * kk), idesc, (kc | tap | kk) ? 1u : 0u);
+          }
+          if (kc == kch - 1) { tc_commit(&slab_free[buf]); tc_commit(&acc_full[buf]); }
+        }
+        __syncwarp();
+      }
+    }
+  } else {
+    // ===================== epilogue warps 2..5: items in order, accumulator buffer = it & 1 =====================
+    using TA = __nv_bfloat16;
+    const int lg = warp & 3;
+    const int lrow = lg * 32 + lane;
+    const int fourCh = 4 * Ch;
+    const long long nitems = (long long)a.T * ntl;
+    for (long long it = 0; it < nitems; ++it) {
+      const int t = (int)(it / ntl), k = (int)(it - (long long)t * ntl);
+      const int tile = grp + k * R;
+      const int buf = (int)(it & 1);
+      const int m = tile * BM + lrow;
+      const bool inrange = m < M;
+      const int f = m / S, q = m - f * S;
+      const int y = q / Wp, x = q - y * Wp;
+      const bool valid = inrange && y < G && x < G;
+      const long long prow = (long long)m + Wp + 1;
+      const long long mt = (long long)t * M + m;
+      const int p = y * G + x;
+      float xi[NC], xf[NC], xc[NC], xo[NC], c[NC];
+      if (valid) {
+        const float* xr = a.Xg + mt * fourCh + ch0;
+        ld8(xr, xi); ld8(xr + 8, xi + 8);
+        ld8(xr + Ch, xf); ld8(xr + Ch + 8, xf + 8);
+        ld8(xr + 2 * Ch, xc); ld8(xr + 2 * Ch + 8, xc + 8);
+        ld8(xr + 3 * Ch, xo); ld8(xr + 3 * Ch + 8, xo + 8);
+      }
+      // the cell of this row: stored by this same thread one step ago (program order)
+      if (valid) { ld8(a.Cf + prow * Ch + ch0, c); ld8(a.Cf + prow * Ch + ch0 + 8, c + 8); }
+      {   // the NEXT item: pull its pre-activation row from HBM into L2 now
+        const long long it2 = it + 1;
+        if (it2 < nitems) {
+          const int t2 = (int)(it2 / ntl), k2 = (int)(it2 - (long long)t2 * ntl);
+          const int m2 = (grp + k2 * R) * BM + lrow;
+          if (m2 < M) {
+            const float* x2 = a.Xg + ((long long)t2 * M + m2) * fourCh + ch0;
+#pragma unroll
+            for (int g = 0; g < 4; ++g) asm volatile("prefetch.global.L2 [%0];" ::"l"(x2 + g * Ch));
+          }
+        }
+      }
+      mbar_wait(&acc_full[buf], (uint32_t)((it >> 1) & 1));
+      tc_fence_after();
+      const uint32_t tlane = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(buf * 64);
+      float hi[NC], hf[NC], ho[NC];
+      tc_ld16(tlane, hi);
+      tc_ld16(tlane + 16u, hf);
+      tc_ld16(tlane + 32u, ho);
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_free[buf]);
+      float gi[NC], gf[NC], gg[NC], go[NC], hn[NC], cp[NC];
+      long long rn = 0;
+      if (valid) {
+#pragma unroll
+        for (int j = 0; j < NC; ++j) {
+          cp[j] = c[j];
+          gi[j] = sigm(xi[j] + hi[j] + peep[(0 * NC + j) * kMaxP + p] * cp[j]);
+          gf[j] = sigm(xf[j] + hf[j] + peep[(1 * NC + j) * kMaxP + p] * cp[j]);
+          gg[j] = tanh_fast(xc[j] + hi[j]);
+          c[j] = gf[j] * cp[j] + gi[j] * gg[j];
+          go[j] = sigm(xo[j] + ho[j] + peep[(2 * NC + j) * kMaxP + p] * cp[j]);
+          hn[j] = tanh_fast(c[j]) * go[j];
+        }
+        rn = ((long long)(t + 1) * M + prow) * Ch + ch0;
+        stbf16x16((TA*)a.Hop + rn, hn);
+      }
+      fence_proxy_async();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (warp == 2 && lane == 0) { __threadfence(); red_release_add(a.flags + tile, 1); }
+      if (valid) {
+        st8(a.Cf + prow * Ch + ch0, c); st8(a.Cf + prow * Ch + ch0 + 8, c + 8);
+        st8(a.Hf + rn, hn); st8(a.Hf + rn + 8, hn + 8);
+        if (a.HS) {
+          const long long orow = ((long long)t * a.B + f) * a.So + (long long)(y + a.pado) * a.Wo + (x + a.pado);
+          stbf16x16((TA*)a.HS + orow * Ch + ch0, hn);
+        }
+        if (a.save) {
+          float* sv = a.save + mt * 5 * Ch + ch0;
+          st8(sv, gi); st8(sv + 8, gi + 8);
+          st8(sv + Ch, gf); st8(sv + Ch + 8, gf + 8);
+          st8(sv + 2 * Ch, gg); st8(sv + 2 * Ch + 8, gg + 8);
+          st8(sv + 3 * Ch, go); st8(sv + 3 * Ch + 8, go + 8);
+          st8(sv + 4 * Ch, cp); st8(sv + 4 * Ch + 8, cp + 8);
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(128u) : "memory");
+  }
+}
+
 int slab_rows_of(int G) { return (BM + 2 * (G + 1) + 2 + 7) & ~7; }
 
 bool shape_ok(int B, int G, int Ch) {
@@ -305,7 +541,10 @@ bool shape_ok(int B, int G, int Ch) {
   if (slab_rows_of(G) > kMaxSlabRows) return false;
   const int S = (G + 1) * (G + 1);
   const long long mtiles = ((long long)B * S + BM - 1) / BM;
-  return mtiles * (Ch / NC) <= num_sms();
+  if (mtiles * (Ch / NC) <= num_sms()) return true;            // one (tile, split) CTA each
+  // multi-tile variant: R = SMs / nsplit row groups walk the tiles; bounded so that a step stays short (<= 16 tiles per CTA)
+  const int R = num_sms() / (Ch / NC);
+  return R >= 1 && G <= 14 && mtiles <= 16LL * R;
 }
 
 }  // namespace lstmseq
@@ -315,7 +554,7 @@ int convlstm_seq_fwd(const rgp_lstm_seq_args& a, cudaStream_t s) {
   RGP_CHECK_ARG(a.dtype == 1, "rgp_convlstm_seq_fwd: bf16 operands only (dtype=%d)", a.dtype);
   RGP_CHECK_ARG(a.T > 0, "rgp_convlstm_seq_fwd: T=%d", a.T);
   RGP_CHECK_ARG(shape_ok(a.B, a.G, a.Ch), "rgp_convlstm_seq_fwd: B=%d G=%d Ch=%d does not fit (Ch 64 or 128, G <= 14, "
-                "tiles * Ch/16 <= SMs): use the per-step path", a.B, a.G, a.Ch);
+                "tiles <= 16 * SMs / (Ch/16)): use the per-step path", a.B, a.G, a.Ch);
   RGP_CHECK_ARG(a.Hop && a.Hf && a.Cf && a.Wh && a.Xg && a.wci && a.wcf && a.wco && a.flags, "rgp_convlstm_seq_fwd: null pointer%s", "");
   RGP_CHECK_ARG(((uintptr_t)a.Hop & 31) == 0 && ((uintptr_t)a.Hf & 31) == 0 && ((uintptr_t)a.Cf & 31) == 0 &&
                 ((uintptr_t)a.Xg & 31) == 0 && ((uintptr_t)a.Wh & 15) == 0 && ((uintptr_t)a.HS & 31) == 0 &&
@@ -334,17 +573,28 @@ int convlstm_seq_fwd(const rgp_lstm_seq_args& a, cudaStream_t s) {
     attr_set.set();
   }
   const int mtiles = (a.B * S + BM - 1) / BM;
+  const bool multi = mtiles * (Ch / NC) > num_sms();
+  const int R = num_sms() / (Ch / NC);
+  if (multi) {
+    static PerDeviceFlag attr2 = {};
+    if (attr2.need()) {
+      cudaError_t e = cudaFuncSetAttribute(lstm_seq_multi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytesMulti);
+      if (e != cudaSuccess) { set_error("lstm_seq_multi: cudaFuncSetAttribute(smem=%d): %s", kSmemBytesMulti, cudaGetErrorString(e)); return -5; }
+      attr2.set();
+    }
+  }
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3((unsigned)(mtiles * (Ch / NC)), 1, 1);
-  cfg.blockDim = dim3(NTHREADS, 1, 1);
-  cfg.dynamicSmemBytes = kSmemBytes;
+  cfg.gridDim = dim3((unsigned)((multi ? R : mtiles) * (Ch / NC)), 1, 1);
+  cfg.blockDim = dim3(multi ? NTHREADS_MULTI : NTHREADS, 1, 1);
+  cfg.dynamicSmemBytes = multi ? kSmemBytesMulti : kSmemBytes;
   cfg.stream = s;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeCooperative;     // co-residency of all CTAs is what makes the counter waits safe
   attr[0].val.cooperative = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, lstm_seq_kernel, tmH, tmW, a, srows);
+  cudaError_t e = multi ? cudaLaunchKernelEx(&cfg, lstm_seq_multi_kernel, tmH, tmW, a, srows, R)
+                        : cudaLaunchKernelEx(&cfg, lstm_seq_kernel, tmH, tmW, a, srows);
   if (e != cudaSuccess) { set_error("lstm_seq launch: %s", cudaGetErrorString(e)); return -5; }
   return check_launch("lstm_seq");
 }

@@ -840,7 +840,8 @@ class EmuLib(object):
         return 0
 
     def rgp_convlstm_seq_fits(self, B, G, Ch):
-        return 1 if (Ch % 16 == 0 and G <= 14 and ((B * (G + 1) ** 2 + 127) // 128) * (Ch // 16) <= 148) else 0
+        tiles = (B * (G + 1) ** 2 + 127) // 128
+        return 1 if (Ch % 16 == 0 and G <= 14 and tiles <= 16 * max(1, 148 // (Ch // 16))) else 0
 
     def rgp_convlstm_seq_fwd(self, aref, stream):
         """all T steps of the ConvLSTM recurrence: per step the hidden conv (3 gates) + rgp_lstm_gates, as the per-step path"""

@@ -206,7 +206,11 @@ def test_config3_training_step_T35_hidden256_vs_oracle():
 
 
 @pytest.mark.parametrize("G,B,T,head,train", [(14, 8, 128, "fc", False), (14, 2, 16, "fc", True), (7, 28, 35, None, False),
-                                                (7, 5, 6, None, True), (14, 10, 8, "fc", False)])
+                                                (7, 5, 6, None, True), (14, 10, 8, "fc", False),
+                                                # more tiles than co-resident CTAs: the multi-tile variant (R row groups
+                                                # walk the tiles of every step; two slab buffers / accumulators)
+                                                (14, 64, 12, "fc", False), (14, 21, 7, "fc", True), (7, 200, 5, None, False),
+                                                (14, 11, 128, "fc", False)])
 def test_persistent_convlstm_matches_per_step_path_and_oracle(G, B, T, head, train):
     """rgp_convlstm_seq_fwd (all T steps in one launch, W_h slices resident in shared memory, halo exchange through
     per-tile counters) against the per-step path (h2h tap-GEMM + gate kernel per step) on the same inputs - states,
