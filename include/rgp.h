@@ -113,6 +113,9 @@ typedef struct rgp_gru_seq_args {
   int dtype;                      /* must be 1 (bf16 operands, tcgen05 engine)                                   */
   int mcast;                      /* 1, 2, 4 or 8 tiles per cluster: each CTA fetches 1/mcast of every weight box
                                      and TMA-multicasts it to the others (nsplit*mcast <= 8)                      */
+  int ntile;                      /* 0 / 1: one 128-row tile per CTA; 2 (needs Ch/nsplit = 128, mcast = 1): a CTA walks two
+                                     tiles for its channel half, every streamed weight box feeds both (half the L2->SMEM
+                                     bytes per MMA)                                                                 */
 } rgp_gru_seq_args;
 int rgp_convgru_seq_fwd(const rgp_gru_seq_args* a, void* stream);
 /* Profiling hook: phase timestamps (globaltimer ns) CTA 0 recorded during the last rgp_convgru_seq_fwd, copied to a

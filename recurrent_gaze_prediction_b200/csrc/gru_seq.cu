@@ -156,30 +156,36 @@ constexpr int kSlabRows = 152;                       // 128 + 2*Wp + 2 = 146 at 
 constexpr int kSlabBoxBytes = kSlabRows * BK * 2;    // 19456 = 19 * 1024
 constexpr int kMaxKChunks = 4;                       // Ch <= 256
 
-template <int NH>
+// NT = tiles per CTA.  NT = 2 (with the 2-CTA channel split, NH = 128): a CTA walks TWO 128-row tiles for its half of the
+// channels, so every weight box it streams (16 KB) feeds the MMAs of both tiles - the bytes the SM pulls through its
+// L2->SMEM port per MMA are halved (what cta_group::2 would give), which is what bounded the MMA phases (16-18 us against
+// 9.7 us of tensor work).  TMEM: tile tl uses columns [tl*2NH, tl*2NH + 2NH) (z | r/c), 512 columns in all.
+template <int NH, int NT>
 struct SeqCfg {
-  static constexpr int kStages = (NH >= 256) ? 4 : 6;
-  static constexpr int kABytes = kMaxKChunks * kSlabBoxBytes;       // the slab
+  static constexpr int kStages = (NH >= 256 || NT == 2) ? 4 : 6;
+  static constexpr int kABytes = NT * kMaxKChunks * kSlabBoxBytes;  // the slab(s): box index = kc * NT + tl
   static constexpr int kBBytes = NH * BK * 2;
-  static constexpr int kTmemCols = 2 * NH;
-  static constexpr int kBarBytes = 256;
+  static constexpr int kTmemCols = NT * 2 * NH;
+  static constexpr int kBarBytes = 512;
   static constexpr int kSmemBytes = kABytes + kStages * kBBytes + 1024 + kBarBytes;
 };
 
-template <int NH>
+template <int NH, int NT>
 __global__ void __launch_bounds__(NTHREADS, 1)
 gru_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ CUtensorMap tmRH,
                const __grid_constant__ CUtensorMap tmUzr, const __grid_constant__ CUtensorMap tmUc,
                const rgp_gru_seq_args a) {
-  using C = SeqCfg<NH>;
+  using C = SeqCfg<NH, NT>;
+  constexpr int kBoxes = NT * kMaxKChunks;
+  constexpr int TM = NT * BM;                          // q-rows per CTA
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint8_t* slab = smem;                                // kchunks boxes of kSlabRows x 64 bf16
+  uint8_t* slab = smem;                                // NT * kchunks boxes of kSlabRows x 64 bf16 (box = kc * NT + tl)
   uint8_t* ringB = smem + C::kABytes;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::kABytes + C::kStages * C::kBBytes);
-  uint64_t* fullA = bars;                              // per slab box (kMaxKChunks)
-  uint64_t* emptyA = fullA + kMaxKChunks;
-  uint64_t* fullB = emptyA + kMaxKChunks;
+  uint64_t* fullA = bars;                              // per slab box
+  uint64_t* emptyA = fullA + kBoxes;
+  uint64_t* fullB = emptyA + kBoxes;
   uint64_t* emptyB = fullB + C::kStages;
   uint64_t* r_full = emptyB + C::kStages;
   uint64_t* z_full = r_full + 1;
@@ -201,7 +207,7 @@ gru_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
   const int peer0 = mrank * nsplit;                                     // first CTA of this tile's channel-split group
   const int Ch = a.Ch, Wp = a.G + 1, S = Wp * Wp;
   const int M = a.B * S;                          // q-rows of one step
-  const int mtiles_real = (M + BM - 1) / BM;
+  const int mtiles_real = (M + TM - 1) / TM;
   // every CTA of a cluster walks the same number of tiles (weight slices are exchanged in lock-step); tiles past the
   // end are ghosts: all rows out of range, nothing stored
   const int mtiles = ((mtiles_real + cs - 1) / cs) * cs;
@@ -215,7 +221,7 @@ gru_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmRH) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmUzr) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmUc) : "memory");
-    for (int i = 0; i < kMaxKChunks; ++i) { mbar_init(&fullA[i], 1); mbar_init(&emptyA[i], 1); }
+    for (int i = 0; i < kBoxes; ++i) { mbar_init(&fullA[i], 1); mbar_init(&emptyA[i], 1); }
     for (int i = 0; i < C::kStages; ++i) { mbar_init(&fullB[i], 1); mbar_init(&emptyB[i], (uint32_t)cs); }
     mbar_init(r_full, 1); mbar_init(z_full, 1); mbar_init(c_full, 1);
     mbar_init(rh_ready, EPI_WARPS * nsplit); mbar_init(h_ready, EPI_WARPS * nsplit);
@@ -240,7 +246,8 @@ gru_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
       int sB = 0; uint32_t phB = 0;
       long long it = 0;                                   // running step counter of this CTA (barrier phases)
       for (int tile = cluster_id; tile < mtiles; tile += nclusters) {
-        const int m0 = tile * BM;
+        const int m0 = tile * TM;
+        const int nboxes = NT * kchunks;
         for (int t = 0; t < a.T; ++t, ++it) {
           const long long rowH = (long long)t * M + m0;                 // slab t = h_{t-1} ... (slab 0 = h_0)
           const long long rowRH = (long long)(train ? t : 0) * M + m0;
@@ -267,10 +274,10 @@ gru_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
           while (iB < C::kStages) issueB();
           if (it > 0) { mbar_wait_cluster(h_ready, (uint32_t)((it - 1) & 1)); fence_proxy_async(); }
           // (2) h_{t-1}: all k-chunks of the slab (box kc was released by the previous c-phase: release parity 1)
-          for (int kc = 0; kc < kchunks; ++kc) {
-            mbar_wait(&emptyA[kc], 1);
-            mbar_expect_tx(&fullA[kc], kSlabBoxBytes);
-            tma_load_2d(slab + kc * kSlabBoxBytes, &tmH, &fullA[kc], kc * BK, (int)rowH);
+          for (int bx = 0; bx < nboxes; ++bx) {
+            mbar_wait(&emptyA[bx], 1);
+            mbar_expect_tx(&fullA[bx], kSlabBoxBytes);
+            tma_load_2d(slab + bx * kSlabBoxBytes, &tmH, &fullA[bx], (bx / NT) * BK, (int)rowH + (bx % NT) * BM);
           }
           // (3) the weights of the three phases in ring order, and r.h box kc as soon as (a) the r-epilogue has published
           //     the rows (rh_ready) and (b) the z-phase has issued its last MMA on box kc (release parity 0).  Both are
@@ -280,25 +287,25 @@ gru_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
           bool rh_ok = false;
           auto loadRH = [&]() {
             mbar_expect_tx(&fullA[nextRH], kSlabBoxBytes);
-            tma_load_2d(slab + nextRH * kSlabBoxBytes, &tmRH, &fullA[nextRH], nextRH * BK, (int)rowRH);
+            tma_load_2d(slab + nextRH * kSlabBoxBytes, &tmRH, &fullA[nextRH], (nextRH / NT) * BK, (int)rowRH + (nextRH % NT) * BM);
             ++nextRH;
           };
           while (iB < 3 * ksteps) {
-            if (nextRH < kchunks) {
+            if (nextRH < nboxes) {
               if (iB >= 2 * ksteps + C::kStages) {                    // must have r.h before more c-phase weights
                 if (!rh_ok) { mbar_wait_cluster(rh_ready, (uint32_t)(it & 1)); fence_proxy_async(); rh_ok = true; }
                 mbar_wait(&emptyA[nextRH], 0);
                 loadRH();
                 continue;
               }
-              if (iB >= ksteps + 9 * (nextRH + 1)) {                  // the z-phase weights that free box nextRH are issued
+              if (iB >= ksteps + 9 * (nextRH / NT + 1)) {             // the z-phase weights that free box nextRH are issued
                 if (!rh_ok && mbar_test_cluster(rh_ready, (uint32_t)(it & 1))) { fence_proxy_async(); rh_ok = true; }
                 if (rh_ok && mbar_test_cluster(&emptyA[nextRH], 0)) { loadRH(); continue; }
               }
             }
             issueB();
           }
-          while (nextRH < kchunks) {                                    // (never taken: the ring forces r.h before the end)
+          while (nextRH < nboxes) {                                     // (never taken: the ring forces r.h before the end)
             if (!rh_ok) { mbar_wait_cluster(rh_ready, (uint32_t)(it & 1)); fence_proxy_async(); rh_ok = true; }
             mbar_wait(&emptyA[nextRH], 0);
             loadRH();
@@ -325,19 +332,25 @@ gru_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
           uint64_t* done = (ph == 0) ? r_full : ((ph == 1) ? z_full : c_full);
           for (int ks = 0; ks < ksteps; ++ks) {
             const int kc = ks / 9, tap = ks - kc * 9;
-            // slab box kc: fill 2*it (h_{t-1}, completes barrier phase parity 0) serves ph 0 and 1, fill 2*it+1 (r.h,
+            // slab box (kc, tl): fill 2*it (h_{t-1}, completes barrier phase parity 0) serves ph 0 and 1, fill 2*it+1 (r.h,
             // parity 1) serves ph 2
-            if (tap == 0 && ph != 1) mbar_wait(&fullA[kc], ph == 0 ? 0u : 1u);
+            if (tap == 0 && ph != 1)
+              for (int tl = 0; tl < NT; ++tl) mbar_wait(&fullA[kc * NT + tl], ph == 0 ? 0u : 1u);
             mbar_wait(&fullB[sB], phB);
             tc_fence_after();
             if (lane == 0) {
               const int off = (tap / 3) * Wp + (tap % 3);
-              const uint64_t adesc = make_sdesc(smem_u32(slab + kc * kSlabBoxBytes) + (uint32_t)off * (BK * 2));
               const uint64_t bdesc = make_sdesc(smem_u32(ringB + sB * C::kBBytes));
 #pragma unroll
-              for (int k = 0; k < BK / 16; ++k)
-                tc_mma_bf16(tacc, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (ks | k) ? 1u : 0u);
-              if (tap == 8 && ph != 0) tc_commit(&emptyA[kc]);     // last use of this box by the z-phase / the c-phase
+              for (int tl = 0; tl < NT; ++tl) {                    // one weight box, NT tiles
+                const uint64_t adesc = make_sdesc(smem_u32(slab + (kc * NT + tl) * kSlabBoxBytes) + (uint32_t)off * (BK * 2));
+#pragma unroll
+                for (int k = 0; k < BK / 16; ++k)
+                  tc_mma_bf16(tacc + (uint32_t)(tl * 2 * NH), adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc,
+                              (ks | k) ? 1u : 0u);
+              }
+              if (tap == 8 && ph != 0)                             // last use of these boxes by the z-phase / the c-phase
+                for (int tl = 0; tl < NT; ++tl) tc_commit(&emptyA[kc * NT + tl]);
               if (cs == 1) tc_commit(&emptyB[sB]); else tc_commit_mc(&emptyB[sB], bmask);
               if (ks == ksteps - 1) tc_commit(done);
             }
@@ -354,13 +367,15 @@ gru_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
     const int lg = warp & 3;
     const int cgi = (warp - 2) >> 2;
     constexpr int NCG = EPI_WARPS / 4;
-    constexpr int CW = NH / NCG;                       // columns this warp handles per gate
-    const int cb = cgi * CW;                           // first local column
-    const uint32_t tlane = tmem_base + ((uint32_t)(lg * 32) << 16);
+    // NT = 1: the two warps of a lane group split the columns; NT = 2: they take one tile each, all NH columns
+    constexpr int CW = (NT == 2) ? NH : NH / NCG;      // columns this warp handles per gate
+    const int tl_e = (NT == 2) ? cgi : 0;              // this warp's tile
+    const int cb = (NT == 2) ? 0 : cgi * CW;           // first local column
+    const uint32_t tlane = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(tl_e * 2 * NH);
     const int threeCh = 3 * Ch;
     long long it = 0;
     for (int tile = cluster_id; tile < mtiles; tile += nclusters) {
-      const int m = tile * BM + lg * 32 + lane;        // q-row inside a step slab
+      const int m = tile * TM + tl_e * BM + lg * 32 + lane;        // q-row inside a step slab
       const bool inrange = m < M;
       const int f = m / S, q = m - f * S;
       const int y = q / Wp, x = q - y * Wp;
@@ -507,9 +522,9 @@ gru_seq_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ 
   }
 }
 
-template <int NH>
+template <int NH, int NT>
 int launch_seq(const rgp_gru_seq_args& a, cudaStream_t s) {
-  using C = SeqCfg<NH>;
+  using C = SeqCfg<NH, NT>;
   const int Ch = a.Ch, S = (a.G + 1) * (a.G + 1);
   CUtensorMap tmH, tmRH, tmUzr, tmUc;
   int rc = encode_map_bf16(a.Hop, Ch, a.rowsH, (long long)Ch * 2, BK, kSlabRows, &tmH);
@@ -522,11 +537,11 @@ int launch_seq(const rgp_gru_seq_args& a, cudaStream_t s) {
   if (rc) return rc;
   static PerDeviceFlag attr_set = {};
   if (attr_set.need()) {
-    cudaError_t e = cudaFuncSetAttribute(gru_seq_kernel<NH>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes);
+    cudaError_t e = cudaFuncSetAttribute(gru_seq_kernel<NH, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes);
     if (e != cudaSuccess) { set_error("gru_seq: cudaFuncSetAttribute(smem=%d): %s", C::kSmemBytes, cudaGetErrorString(e)); return -5; }
     attr_set.set();
   }
-  const int mtiles = (a.B * S + BM - 1) / BM;
+  const int mtiles = (a.B * S + NT * BM - 1) / (NT * BM);
   const int csize = a.nsplit * a.mcast;
   int nclusters = (mtiles + a.mcast - 1) / a.mcast;
   cudaLaunchConfig_t cfg = {};
@@ -547,12 +562,12 @@ int launch_seq(const rgp_gru_seq_args& a, cudaStream_t s) {
   if (!max_clusters[csize]) {
     cfg.gridDim = dim3((unsigned)(csize * 64), 1, 1);
     int n = 0;
-    if (cudaOccupancyMaxActiveClusters(&n, gru_seq_kernel<NH>, &cfg) != cudaSuccess || n <= 0) { cudaGetLastError(); n = num_sms() / csize; }
+    if (cudaOccupancyMaxActiveClusters(&n, gru_seq_kernel<NH, NT>, &cfg) != cudaSuccess || n <= 0) { cudaGetLastError(); n = num_sms() / csize; }
     max_clusters[csize] = n;
   }
   if (nclusters > max_clusters[csize]) nclusters = max_clusters[csize];
   cfg.gridDim = dim3((unsigned)(nclusters * csize), 1, 1);
-  cudaError_t e = cudaLaunchKernelEx(&cfg, gru_seq_kernel<NH>, tmH, tmRH, tmUzr, tmUc, a);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, gru_seq_kernel<NH, NT>, tmH, tmRH, tmUzr, tmUc, a);
   if (e != cudaSuccess) { set_error("gru_seq launch: %s", cudaGetErrorString(e)); return -5; }
   return check_launch("gru_seq");
 }
@@ -583,8 +598,10 @@ int convgru_seq_fwd(const rgp_gru_seq_args& a, cudaStream_t s) {
   RGP_CHECK_ARG(((uintptr_t)a.Hop & 15) == 0 && ((uintptr_t)a.RH & 15) == 0 && ((uintptr_t)a.Uzr & 15) == 0 &&
                 ((uintptr_t)a.Uc & 15) == 0, "rgp_convgru_seq_fwd: operands must be 16-byte aligned");
   const int NH = a.Ch / a.nsplit;
-  if (NH == 256) return launch_seq<256>(a, s);
-  if (NH == 128) return launch_seq<128>(a, s);
+  RGP_CHECK_ARG(a.ntile == 0 || a.ntile == 1 || (a.ntile == 2 && NH == 128 && a.mcast == 1),
+                "rgp_convgru_seq_fwd: ntile=%d needs Ch/nsplit = 128 and mcast = 1", a.ntile);
+  if (NH == 256) return launch_seq<256, 1>(a, s);
+  if (NH == 128) return a.ntile == 2 ? launch_seq<128, 2>(a, s) : launch_seq<128, 1>(a, s);
   set_error("rgp_convgru_seq_fwd: Ch/nsplit = %d must be 128 or 256", NH);
   return -22;
 }

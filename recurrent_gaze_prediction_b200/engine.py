@@ -188,7 +188,7 @@ class TrainStateMixin(object):
 class GazeEngine(TrainStateMixin):
     def __init__(self, model="gaze_grcn", B=2, T=35, G=7, Ch=128, Cin=512, Cfeat=1024, dtype=0,
                  device="cuda", lib=None, train=False, head=None, engine=None, seq=None, nsplit=None, mcast=None,
-                 T_params=None):
+                 T_params=None, ntile=None):
         if model not in ("gaze_grcn", "gaze_grcn77", "gaze_lstm"):
             raise ValueError("unknown model %r" % (model,))
         self.model, self.B, self.T, self.G, self.Ch, self.Cin, self.Cfeat = model, B, T, G, Ch, Cin, Cfeat
@@ -240,6 +240,13 @@ class GazeEngine(TrainStateMixin):
                                  (dtype == 1 or seq_arg is True) and fits(B, G, Ch) and
                                  os.environ.get("RGP_SEQ", "") != "0")
         self.nsplit = nsplit or int(os.environ.get("RGP_SEQ_NSPLIT", "0")) or (2 if (Ch == 256 and mtiles <= 74) else 1)
+        # Two tiles per CTA (ntile = 2, with the 2-CTA channel split): every streamed weight box feeds the MMAs of two tiles,
+        # halving the bytes an SM pulls through its L2->SMEM port per MMA.  Parity-tested; MEASURED SLOWER at the bench batch
+        # (recurrence 2.98 vs 2.29 ms at 256 clips, gpurun_out/r02p11_*): the phases are not bound by the weight stream
+        # alone, and the channel split adds two cross-CTA hand-offs per step.  Off by default (RGP_SEQ_NTILE=2 / ntile=2).
+        self.ntile = ntile or int(os.environ.get("RGP_SEQ_NTILE", "0")) or 1
+        if self.ntile == 2:
+            self.nsplit = 2
         # mcast > 1: every weight box is fetched once per cluster and TMA-multicast; measured slower (the bound is the
         # SM's own L2->SMEM port, which multicast does not relieve), so the default is 1
         self.mcast = mcast or int(os.environ.get("RGP_SEQ_MCAST", "0")) or 1
@@ -579,7 +586,7 @@ class GazeEngine(TrainStateMixin):
                 a.alpha = 1.0 / math.sqrt(1.0 + BN_EPS)
             a.B, a.T, a.G, a.Ch = B, T, G, Ch
             a.So, a.Wo, a.pado = HEAD_S, HEAD_W, HEAD_PAD
-            a.nsplit, a.dtype, a.mcast = self.nsplit, self.dtype, self.mcast
+            a.nsplit, a.dtype, a.mcast, a.ntile = self.nsplit, self.dtype, self.mcast, self.ntile
             lib.rgp_convgru_seq_fwd(C.byref(a), s)
             if self.head == "fc":   # gaze_grcn77.py:206-211
                 self._fc_head_all(s)

@@ -61,7 +61,7 @@ class GruSeqArgs(C.Structure):
         ("bn_gamma", _vp), ("bn_beta", _vp), ("alpha", _f),
         ("B", _i), ("T", _i), ("G", _i), ("Ch", _i),
         ("So", _i), ("Wo", _i), ("pado", _i),
-        ("nsplit", _i), ("dtype", _i), ("mcast", _i),
+        ("nsplit", _i), ("dtype", _i), ("mcast", _i), ("ntile", _i),
     ]
 
 

@@ -244,17 +244,21 @@ def test_wgrad_matches_numpy(engine, M, Ny, Nx, ldy, ycol0, taps):
     assert err <= 2e-5 * np.sqrt(M) * 4, (err, np.abs(ref).max())
 
 
-@pytest.mark.parametrize("model,Ch,B,nsplit,mcast,train", [
-    ("gaze_grcn", 256, 3, 1, 1, False),
-    ("gaze_grcn", 256, 6, 2, 1, False),
-    ("gaze_grcn", 128, 5, 1, 2, True),      # 3 tiles in clusters of 2: one ghost tile
-    ("gaze_grcn", 256, 4, 2, 2, True),
-    ("gaze_grcn", 256, 14, 2, 4, True),     # 8-CTA clusters: 4 tiles x 2 channel halves, one ghost tile
-    ("gaze_grcn", 256, 18, 1, 8, False),
-    ("gaze_grcn77", 128, 2, 1, 4, False),
-    ("gaze_grcn", 256, 320, 1, 4, False),   # more tiles than SMs: CTAs walk several tiles
+@pytest.mark.parametrize("model,Ch,B,nsplit,mcast,train,ntile", [
+    ("gaze_grcn", 256, 3, 1, 1, False, 1),
+    ("gaze_grcn", 256, 6, 2, 1, False, 1),
+    ("gaze_grcn", 128, 5, 1, 2, True, 1),      # 3 tiles in clusters of 2: one ghost tile
+    ("gaze_grcn", 256, 4, 2, 2, True, 1),
+    ("gaze_grcn", 256, 14, 2, 4, True, 1),     # 8-CTA clusters: 4 tiles x 2 channel halves, one ghost tile
+    ("gaze_grcn", 256, 18, 1, 8, False, 1),
+    ("gaze_grcn77", 128, 2, 1, 4, False, 1),
+    ("gaze_grcn", 256, 320, 1, 4, False, 1),   # more tiles than SMs: CTAs walk several tiles
+    ("gaze_grcn", 256, 8, 2, 1, False, 2),     # two tiles per CTA (every weight box feeds both), channel split 2
+    ("gaze_grcn", 256, 5, 2, 1, True, 2),      # odd number of tiles: the second tile of the last pair is half / out of range
+    ("gaze_grcn", 256, 2, 2, 1, True, 2),      # a single tile: the pair's second tile is a ghost
+    ("gaze_grcn", 256, 600, 2, 1, False, 2),   # 150 pairs on 74 clusters: CTAs walk several pairs
 ])
-def test_persistent_recurrence_matches_per_step_path(model, Ch, B, nsplit, mcast, train):
+def test_persistent_recurrence_matches_per_step_path(model, Ch, B, nsplit, mcast, train, ntile):
     """rgp_convgru_seq_fwd (all T steps in one launch) against the per-step tap-GEMM path on the same bf16 operands and
     gate functions.  The two accumulate in different orders (persistent kernel: tap-major; per-step slab GEMM: k-chunk
     major), so pre-activations differ in their last fp32 bits; where that flips the bf16 rounding of a state element the
@@ -266,8 +270,9 @@ def test_persistent_recurrence_matches_per_step_path(model, Ch, B, nsplit, mcast
     gt = np.concatenate([np.roll(gt, i, axis=1) for i in range(reps)], axis=0)[:B]
     out = []
     for seq in (False, True):
-        eng = GazeEngine(model, B=B, T=T, Ch=Ch, dtype=1, device="cuda", train=train, seq=seq, nsplit=nsplit, mcast=mcast)
-        assert eng.use_seq == seq
+        eng = GazeEngine(model, B=B, T=T, Ch=Ch, dtype=1, device="cuda", train=train, seq=seq, nsplit=nsplit, mcast=mcast,
+                         ntile=ntile)
+        assert eng.use_seq == seq and eng.ntile == ntile
         eng.load_tf_params(p)
         eng.forward(c3d=torch.from_numpy(c3d).cuda(), gt=torch.from_numpy(gt).cuda())
         torch.cuda.synchronize()
