@@ -554,6 +554,17 @@ def bench_config5(args, H):
                                  "tensors included)" % (mets,),
                          "frames_per_s": N / dt, "ms_per_1024_frames": dt * 1e3,
                          "mean_scores": {k: float(np.nanmean(v)) for k, v in r.items()}}
+    # the same call with the opt-in device generator (jitter / Borji negatives drawn on the device, not NumPy's global stream)
+    r2 = me.evaluate_batch(pred, gtm, fix, union=union, metrics=mets, rng="device", seed=1)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(3):
+        r2 = me.evaluate_batch(pred, gtm, fix, union=union, metrics=mets, rng="device", seed=1)
+    torch.cuda.synchronize()
+    dt2 = (time.perf_counter() - t0) / 3
+    out["evaluation_device_rng"] = {"call": "the same with rng='device' (statistically equivalent draws, not NumPy's stream)",
+                                    "frames_per_s": N / dt2, "ms_per_1024_frames": dt2 * 1e3,
+                                    "mean_scores": {k: float(np.nanmean(v)) for k, v in r2.items()}}
     del model
     torch.cuda.empty_cache()
     return out

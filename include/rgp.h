@@ -377,6 +377,14 @@ int rgp_auc_sampled_resized(const double* sal_src, const uint8_t* fix, const int
                             int mode_nearest, int nrows, int nrep, double step, int nthr_max, int maxfix,
                             void* stream);
 
+/* ---- opt-in device random numbers for the evaluation (csrc/rng.cu): statistically equivalent to, NOT stream-identical with,
+ * the NumPy global-RNG draws of evaluation_metrics.py:78-79 (jitter) and :148 (Borji negatives) ------------------------ */
+/* out[0..n) = uniform doubles in [0,1), a counter-based hash of (seed, index); out 16-byte aligned */
+int rgp_fill_uniform_f64(double* out, long long n, unsigned long long seed, void* stream);
+/* out [nframes, nrows, nrep] int32: rows r < nfix[f] uniform pixels in [0, npix), rows r >= nfix[f] = -1 (absent) */
+int rgp_fill_randint_rows(int* out, const int* nfix, int nframes, int nrows, int nrep, int npix, unsigned long long seed,
+                          void* stream);
+
 const char* rgp_last_error(void);
 int rgp_version(void);
 /* 1 if the tcgen05 engine can run on the current device (sm_100), else 0 */

@@ -122,6 +122,8 @@ _SIGS = {
     # cascade top level (gaze_grcn_cascade.py:343-424)
     "rgp_topgru_seq_fwd": [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _vp, _i, _i, _i, _vp],
     "rgp_maxout": [_vp, _i, _vp, _i, _i, _vp, _i, _vp, _i, _i, _i, _vp],
+    "rgp_fill_uniform_f64": [_vp, _ll, C.c_ulonglong, _vp],
+    "rgp_fill_randint_rows": [_vp, _vp, _i, _i, _i, _i, C.c_ulonglong, _vp],
     # saliency metrics (evaluation_metrics.py)
     "rgp_metrics_prep": [_vp, _vp, _i, _i, _i, _vp],
     "rgp_resize_bicubic": [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp],

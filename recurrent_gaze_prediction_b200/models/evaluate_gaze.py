@@ -58,7 +58,7 @@ def frame_unions(fixationmaps, M=10):
     return out
 
 
-def score_frames(pred_gazemaps, gt_gazemaps, fixationmaps, engine=None):
+def score_frames(pred_gazemaps, gt_gazemaps, fixationmaps, engine=None, rng="numpy"):
     """All handle_frame metrics for all frames.  Frames are grouped by fixation-map shape (original-scale fixation
     maps may differ per clip) and by union; sim / cc / Borji / Judd go through in one batch per shape."""
     eng = engine or EM.default_engine()
@@ -72,13 +72,13 @@ def score_frames(pred_gazemaps, gt_gazemaps, fixationmaps, engine=None):
         pred = np.asarray([pred_gazemaps[i] for i in idx], dtype=np.float32)
         gt = np.asarray([gt_gazemaps[i] for i in idx], dtype=np.float32)
         fix = np.asarray([fixationmaps[i] for i in idx])
-        r = eng.evaluate_batch(pred, gt, fix, metrics=('sim', 'cc', 'AUC_Borji', 'AUC_Judd'))
+        r = eng.evaluate_batch(pred, gt, fix, metrics=('sim', 'cc', 'AUC_Borji', 'AUC_Judd'), rng=rng)
         for m in r:
             scores[m][idx] = r[m]
         for j, i in enumerate(idx):           # the shuffled AUC has a different union per frame
             if (fix[j] > 0.5).any():
                 r = eng.evaluate_batch(pred[j:j + 1], gt[j:j + 1], fix[j:j + 1], union=unions[i],
-                                       metrics=('AUC_shuffled',))
+                                       metrics=('AUC_shuffled',), rng=rng, seed=i)
                 scores['AUC_shuffled'][i] = r['AUC_shuffled'][0]
     return scores
 
@@ -91,7 +91,8 @@ def run_evaluation(model, args, data_sets, out_dir):
     pred, gt, fix = np.asarray(ret['pred_gazemap_list']), np.asarray(ret['gt_gazemap_list']), ret['fixationmap_list']
     n_images = len(pred)
     assert n_images == len(gt) == len(fix)
-    scores = score_frames(pred, gt, fix, engine=EM.MetricsEngine(device=model.engine.device, lib=model._lib))
+    scores = score_frames(pred, gt, fix, engine=EM.MetricsEngine(device=model.engine.device, lib=model._lib),
+                          rng="device" if getattr(args, "fast_rng", False) else "numpy")
     os.makedirs(out_dir, exist_ok=True)
     overall_txt_path = os.path.join(out_dir, 'overall.txt')
     with open(overall_txt_path, 'w') as fp:
@@ -149,6 +150,8 @@ def make_parser():
     parser.add_argument('--num_frames', type=int, default=1500)
     parser.add_argument('-j', '--jobs', type=int, default=10, help='accepted for compatibility; frames are batched on the GPU')
     parser.add_argument('--embed', action='store_true')
+    parser.add_argument('--fast_rng', action='store_true',
+                        help="draw the AUC jitter / negatives on the device (statistically equivalent, not NumPy's global stream)")
     # additions
     parser.add_argument('--hidden', default=128, type=int)
     parser.add_argument('--grid', default=7, type=int)

@@ -70,6 +70,12 @@ def bind_to_gpu_node(local_rank=0):
     node = _read("/sys/bus/pci/devices/%s/numa_node" % bid)
     if node is None or int(node) < 0:
         out["note"] = "sysfs reports no NUMA node for %s" % bid
+        # Topology unknown (virtualised PCI): at least do not let every rank's pinned staging pages land on the node the
+        # ranks happened to start on - interleave new pages over all nodes this process may allocate from.
+        nodes = _online_nodes()
+        if len(nodes) > 1:
+            rc = _set_mempolicy(3, nodes)                      # MPOL_INTERLEAVE
+            out["mem_policy"] = ("interleave over nodes %s" % nodes) if rc == 0 else "set_mempolicy(interleave) errno %d" % rc
         return out
     node = int(node)
     out["node"] = node
@@ -98,6 +104,27 @@ def bind_to_gpu_node(local_rank=0):
     except Exception as e:       # no libc / syscall filtered
         out["mem_policy"] = "unavailable (%s)" % e
     return out
+
+
+def _online_nodes():
+    s = _read("/sys/devices/system/node/online")
+    return sorted(_parse_cpulist(s)) if s else []
+
+
+def _set_mempolicy(mode, nodes):
+    """set_mempolicy(mode, nodemask of `nodes`); returns 0 or errno (never raises)"""
+    try:
+        libc = ctypes.CDLL(None, use_errno=True)
+        nbits = 1024
+        wbits = 8 * ctypes.sizeof(ctypes.c_ulong)
+        mask = (ctypes.c_ulong * (nbits // wbits))()
+        for n in nodes:
+            mask[n // wbits] |= 1 << (n % wbits)
+        nr = 237 if os.uname().machine == "aarch64" else 238
+        rc = libc.syscall(nr, mode, mask, nbits)
+        return 0 if rc == 0 else (ctypes.get_errno() or -1)
+    except Exception:
+        return -1
 
 
 def _fmt(cpus):

@@ -775,6 +775,27 @@ class EmuLib(object):
         return 0
 
     # fused resize + metric entry points: the emulation materialises the enlargement and calls the plain emulation
+    @staticmethod
+    def _mix64(seed, idx):
+        with np.errstate(over="ignore"):
+            z = np.uint64(seed) + np.uint64(0x9E3779B97F4A7C15) * (idx.astype(np.uint64) + np.uint64(1))
+            z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+            z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+            return z ^ (z >> np.uint64(31))
+
+    def rgp_fill_uniform_f64(self, out, n, seed, stream):
+        z = self._mix64(seed, np.arange(n))
+        arr(out, (n,), np.float64)[:] = (z >> np.uint64(11)).astype(np.float64) * (1.0 / 9007199254740992.0)
+        return 0
+
+    def rgp_fill_randint_rows(self, out, nfix, nframes, nrows, nrep, npix, seed, stream):
+        z = self._mix64(seed, np.arange(nframes * nrows * nrep))
+        v = np.array([(int(x) * npix) >> 64 for x in z], dtype=np.int32).reshape(nframes, nrows, nrep)
+        nf = arr(nfix, (nframes,), np.int32)
+        v[np.arange(nrows)[None, :, None] >= nf[:, None, None] + np.zeros((1, 1, nrep), dtype=np.int64)] = -1
+        arr(out, (nframes, nrows, nrep), np.int32)[:] = v
+        return 0
+
     def rgp_metrics_fused_fits(self, h, w, oh, ow):
         cts = (ow + 7) // 8
         return int((h * w + 2 * h * cts + oh * 4 + cts * 4) * 8 + (oh + cts) * 4 <= 160 * 1024)

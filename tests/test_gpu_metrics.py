@@ -221,3 +221,45 @@ def test_fused_path_nan_and_large_index_tensor():
     F = (fix[i] > 0).ravel()
     for rep, (thresholds, tpc, fpc) in enumerate(MO.borji_counts(S[F], S[big[i]], 0.1)):
         assert np.array_equal(x["AUC_Borji_fp"][i, rep, :len(thresholds)], fpc[::-1])
+
+
+def test_device_rng_kernels_and_fast_evaluation_mode():
+    """csrc/rng.cu: the counter-based generator equals its NumPy restatement (tests/emu_lib.py) bit for bit, stays in
+    range, and evaluate_batch(rng="device") leaves the deterministic metrics untouched while the sampled AUCs agree with
+    the reference-stream path to sampling noise."""
+    import ctypes as C
+    from emu_lib import EmuLib
+    from recurrent_gaze_prediction_b200 import lib as L
+    lib = L.get_lib()
+    n = 100001
+    u = torch.empty(n + 1, dtype=torch.float64, device="cuda")
+    s = torch.cuda.current_stream().cuda_stream
+    lib.rgp_fill_uniform_f64(u.data_ptr(), n, 1234567, s)
+    ref = np.zeros(n, dtype=np.float64)
+    EmuLib().rgp_fill_uniform_f64(ref.ctypes.data, n, 1234567, 0)
+    got = u[:n].cpu().numpy()
+    assert np.array_equal(got, ref) and got.min() >= 0.0 and got.max() < 1.0 and abs(got.mean() - 0.5) < 5e-3
+    nfix = torch.tensor([3, 0, 7, 1], dtype=torch.int32, device="cuda")
+    idx = torch.empty(4, 7, 10, dtype=torch.int32, device="cuda")
+    lib.rgp_fill_randint_rows(idx.data_ptr(), nfix.data_ptr(), 4, 7, 10, 172800, 99, s)
+    ri = np.zeros((4, 7, 10), dtype=np.int32)
+    nf = nfix.cpu().numpy()
+    EmuLib().rgp_fill_randint_rows(ri.ctypes.data, nf.ctypes.data, 4, 7, 10, 172800, 99, 0)
+    g = idx.cpu().numpy()
+    assert np.array_equal(g, ri) and (g[1] == -1).all() and (g[0, :3] >= 0).all() and (g[0, 3:] == -1).all() and g.max() < 172800
+    # the evaluation call
+    rng = np.random.RandomState(3)
+    gt, _ = SY.make_gazemaps(rng, 8, 4, 49, 49)
+    gt = gt.reshape(32, 49, 49)
+    pred = (gt + 0.3 * rng.uniform(size=gt.shape)).astype(np.float32)
+    fix = SY.make_fixationmaps(rng, gt[:, None], 120, 160).reshape(32, 120, 160)
+    union = (fix[:10].sum(axis=0) > 0).astype(np.uint8)
+    eng = EM.MetricsEngine(device="cuda")
+    np.random.seed(1)
+    a = eng.evaluate_batch(pred, gt, fix, union=union)
+    b = eng.evaluate_batch(pred, gt, fix, union=union, rng="device", seed=4)
+    for m in ("sim", "cc", "NSS"):
+        assert np.array_equal(a[m], b[m], equal_nan=True)
+    for m in ("AUC_Judd", "AUC_Borji", "AUC_shuffled"):
+        ok = np.isfinite(a[m])
+        assert np.abs(a[m][ok] - b[m][ok]).max() < 0.08, m

@@ -167,3 +167,32 @@ def test_sparse_fixation_maps_are_accepted():
     np.random.seed(4)
     b = EM.saliency_score("cc", list(pred[keep]), list(gt[keep]), list(fix[keep]), engine=eng)
     assert a == b
+
+
+def test_device_rng_mode_is_statistically_equivalent():
+    """rng="device" (opt-in): jitter / Borji negatives / shuffled picks from the counter-based device generator instead of
+    NumPy's global stream - the deterministic metrics are untouched, the sampled AUCs agree with the reference-stream path
+    to sampling noise, and the call no longer consumes the global RNG."""
+    from recurrent_gaze_prediction_b200 import evaluation_metrics as EM
+    from recurrent_gaze_prediction_b200 import synthetic as SY
+    rng = np.random.RandomState(3)
+    gt, _ = SY.make_gazemaps(rng, 6, 2, 49, 49)
+    gt = gt.reshape(12, 49, 49)
+    pred = (gt + 0.3 * rng.uniform(size=gt.shape)).astype(np.float32)
+    fix = SY.make_fixationmaps(rng, gt[:, None], 49, 49).reshape(12, 49, 49)
+    union = (fix[:6].sum(axis=0) > 0).astype(np.uint8)
+    eng = EM.MetricsEngine(device="cpu", lib=EmuLib())
+    np.random.seed(5)
+    a = eng.evaluate_batch(pred, gt, fix, union=union)
+    state = np.random.get_state()[1].copy()
+    b = eng.evaluate_batch(pred, gt, fix, union=union, rng="device", seed=9)
+    assert np.array_equal(np.random.get_state()[1], state)             # the global stream was not consumed
+    c = eng.evaluate_batch(pred, gt, fix, union=union, rng="device", seed=9)
+    for m in ("sim", "cc", "NSS"):
+        assert np.array_equal(a[m], b[m], equal_nan=True)
+    for m in ("AUC_Judd", "AUC_Borji", "AUC_shuffled"):
+        assert np.array_equal(b[m], c[m], equal_nan=True)               # reproducible from the seed
+        ok = np.isfinite(a[m])
+        assert np.abs(a[m][ok] - b[m][ok]).max() < 0.08, m              # sampling noise of 100 repetitions
+    with pytest.raises(ValueError):
+        eng.evaluate_batch(pred, gt, fix, union=union, rng="philox")
