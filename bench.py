@@ -503,6 +503,30 @@ def bench_config4(args, H):
     return out
 
 
+def bench_reference_batch(args, H):
+    """The reference's own training configuration (train_gaze.py:74-75 batch 28; gaze_rnn.py:50 T = 42; hidden 128,
+    gaze_grcn.py:211) through the model class on one GPU: one CUDA-graph submission per step against eager launches (the
+    path is launch-bound at this size), and inference."""
+    H1 = Harness(H.dev, H.local, 0, 1)
+    out = {"workload": "gaze_grcn, batch 28 x T=42, hidden 128 (the reference's train_gaze.py configuration), bf16 operands",
+           "api": "models.GazePredictionGRCN.run() on resident placeholders", "n_gpus": 1}
+    for mode in ("train", "inference"):
+        for graph in (True, False):
+            a = argparse.Namespace(**vars(args))
+            a.model, a.batch, a.T, a.hidden, a.grid, a.mode, a.no_graph = "gaze_grcn", 28, 42, 128, 7, mode, not graph
+            model = build_model(a, {"rank": 0, "world_size": 1, "allreduce": None}, 28, 1, mode == "train", "bf16", H.dev)
+            feat_h, gt_h, _, _ = make_inputs(0, 28, 42, 7, 49, torch.bfloat16)
+            model.c3d_input.copy_(feat_h)
+            model.gt_gazemap.copy_(gt_h)
+            step = lambda: model.run(train=(mode == "train"), sync=False)
+            step()
+            ms, _, _ = H1.timed(step, max(4, args.steps), 3)
+            out["%s_%s" % (mode, "graph" if graph else "eager")] = {"ms_per_step": ms, "frames_per_s": 28 * 42 / (ms * 1e-3)}
+            del model
+            torch.cuda.empty_cache()
+    return out
+
+
 def bench_config5(args, H):
     """BASELINE config 5: the cascade (gaze_grcn_cascade.py: bottom ConvGRU 256 -> 11x11/s7 transposed conv -> 5x5
     ConvGRU on 49x49 -> two maxout FCs) through its model class, inference at 64 clips x T=35, bf16; then the saliency
@@ -613,6 +637,10 @@ def main():
         tr["config"] = workload_config(targs)
         sub["train"] = tr
         if rank == 0:
+            try:
+                sub["reference_batch"] = bench_reference_batch(args, H)
+            except Exception as e:
+                sub["reference_batch"] = {"error": "%s: %s" % (type(e).__name__, e)}
             try:
                 sub["config4"] = bench_config4(args, H)
             except Exception as e:       # a sub-record must not take the headline down
