@@ -32,7 +32,7 @@ topgru_seq_kernel(const float* __restrict__ xg, int ldx, int So, int Wo, const f
   float* hs = sm;                          // [NU][PLANE]   h_{t-1}, zero border of 2
   float* rhs = hs + NU * PLANE;            // [NU][PLANE]   r . h_{t-1}
   float* ss = rhs + NU * PLANE;            // [PLANE]       frame saliency (reading B), zero border
-  float* wzr = ss + PLANE;                 // [25][NU][6]
+  float* wzr = ss + PLANE + 1;             // [25][NU][6]  (+1: 7 * 2809 floats is odd, the float2 reads below need 8-byte alignment)
   float* wc = wzr + 25 * NU * 6;           // [25][NU][NU]
   float* ws = wc + 25 * NU * NU;           // [25][9]
   const int b = blockIdx.x, tid = threadIdx.x;
@@ -62,70 +62,96 @@ topgru_seq_kernel(const float* __restrict__ xg, int ldx, int So, int Wo, const f
       __syncthreads();
     }
     float z[PPT][NU], xc[PPT][NU];
+    // Tap-outer loops: the 18 (9) weights of a tap are read from shared memory ONCE per thread and applied to its ~5
+    // pixels from registers.  (Pixel-outer, 21 LDS per pixel and tap, the kernel was bound by the LDS pipe: 33 us per step.)
+    int base[PPT];
+    bool live[PPT];
     // ---- phase A: z, r and r.h  (gaze_grcn_cascade.py:108-119)
+    float acc[PPT][6];
 #pragma unroll
     for (int k = 0; k < PPT; ++k) {
       const int p = tid + k * TOP_THREADS;
-      if (p < NPIX) {
-        const int y = p / GT, x = p - y * GT;
-        const float* xp = xf + (long long)(y * Wo + x) * ldx;
-        const float4 x0 = *reinterpret_cast<const float4*>(xp);
-        const float4 x1 = *reinterpret_cast<const float4*>(xp + 4);
-        float acc[6] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y};
-        xc[k][0] = x1.z; xc[k][1] = x1.w; xc[k][2] = xp[8];
-        const int base = y * PW + x;
-#pragma unroll 5
-        for (int tap = 0; tap < 25; ++tap) {
-          const int o = base + (tap / KT) * PW + (tap % KT);
-          const float* w = wzr + tap * NU * 6;
+      live[k] = p < NPIX;
+      const int pc = live[k] ? p : 0;
+      const int y = pc / GT, x = pc - y * GT;
+      base[k] = y * PW + x;
+      const float* xp = xf + (long long)(y * Wo + x) * ldx;
+      const float4 x0 = *reinterpret_cast<const float4*>(xp);
+      const float4 x1 = *reinterpret_cast<const float4*>(xp + 4);
+      acc[k][0] = x0.x; acc[k][1] = x0.y; acc[k][2] = x0.z; acc[k][3] = x0.w; acc[k][4] = x1.x; acc[k][5] = x1.y;
+      xc[k][0] = x1.z; xc[k][1] = x1.w; xc[k][2] = xp[8];
+    }
+#pragma unroll 1
+    for (int tap = 0; tap < 25; ++tap) {
+      const int to = (tap / KT) * PW + (tap % KT);
+      float w[NU * 6];
 #pragma unroll
-          for (int u = 0; u < NU; ++u) {
-            const float hv = hs[u * PLANE + o];
+      for (int i = 0; i < NU * 6; i += 2) {
+        const float2 v = *reinterpret_cast<const float2*>(wzr + tap * NU * 6 + i);
+        w[i] = v.x; w[i + 1] = v.y;
+      }
 #pragma unroll
-            for (int j = 0; j < 6; ++j) acc[j] = fmaf(hv, w[u * 6 + j], acc[j]);
-          }
-          if (sal) {
-            const float sv = ss[o];
-            const float* q = ws + tap * 9;
-#pragma unroll
-            for (int j = 0; j < 6; ++j) acc[j] = fmaf(sv, q[j], acc[j]);
-#pragma unroll
-            for (int j = 0; j < NU; ++j) xc[k][j] = fmaf(sv, q[6 + j], xc[k][j]);
-          }
-        }
-        const int c = base + 2 * PW + 2;
+      for (int k = 0; k < PPT; ++k) {
+        const int o = base[k] + to;
 #pragma unroll
         for (int u = 0; u < NU; ++u) {
-          z[k][u] = sigm(acc[u]);
-          rhs[u * PLANE + c] = sigm(acc[NU + u]) * hs[u * PLANE + c];
+          const float hv = hs[u * PLANE + o];
+#pragma unroll
+          for (int j = 0; j < 6; ++j) acc[k][j] = fmaf(hv, w[u * 6 + j], acc[k][j]);
+        }
+      }
+      if (sal) {
+        float q[9];
+#pragma unroll
+        for (int i = 0; i < 9; ++i) q[i] = ws[tap * 9 + i];
+#pragma unroll
+        for (int k = 0; k < PPT; ++k) {
+          const float sv = ss[base[k] + to];
+#pragma unroll
+          for (int j = 0; j < 6; ++j) acc[k][j] = fmaf(sv, q[j], acc[k][j]);
+#pragma unroll
+          for (int j = 0; j < NU; ++j) xc[k][j] = fmaf(sv, q[6 + j], xc[k][j]);
+        }
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < PPT; ++k) {
+      if (live[k]) {
+        const int c = base[k] + 2 * PW + 2;
+#pragma unroll
+        for (int u = 0; u < NU; ++u) {
+          z[k][u] = sigm(acc[k][u]);
+          rhs[u * PLANE + c] = sigm(acc[k][NU + u]) * hs[u * PLANE + c];
         }
       }
     }
     __syncthreads();
     // ---- phase B: candidate and state update  (:122-127)
     float hn[PPT][NU];
+#pragma unroll 1
+    for (int tap = 0; tap < 25; ++tap) {
+      const int to = (tap / KT) * PW + (tap % KT);
+      float w[NU * NU];
 #pragma unroll
-    for (int k = 0; k < PPT; ++k) {
-      const int p = tid + k * TOP_THREADS;
-      if (p < NPIX) {
-        const int y = p / GT, x = p - y * GT;
-        float acc[NU] = {xc[k][0], xc[k][1], xc[k][2]};
-        const int base = y * PW + x;
-#pragma unroll 5
-        for (int tap = 0; tap < 25; ++tap) {
-          const int o = base + (tap / KT) * PW + (tap % KT);
-          const float* w = wc + tap * NU * NU;
+      for (int i = 0; i < NU * NU; ++i) w[i] = wc[tap * NU * NU + i];
 #pragma unroll
-          for (int u = 0; u < NU; ++u) {
-            const float rv = rhs[u * PLANE + o];
-#pragma unroll
-            for (int j = 0; j < NU; ++j) acc[j] = fmaf(rv, w[u * NU + j], acc[j]);
-          }
-        }
-        const int c = base + 2 * PW + 2;
+      for (int k = 0; k < PPT; ++k) {
+        const int o = base[k] + to;
 #pragma unroll
         for (int u = 0; u < NU; ++u) {
-          const float cv = tanhf(acc[u]);
+          const float rv = rhs[u * PLANE + o];
+#pragma unroll
+          for (int j = 0; j < NU; ++j) xc[k][j] = fmaf(rv, w[u * NU + j], xc[k][j]);
+        }
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < PPT; ++k) {
+      if (live[k]) {
+        const int c = base[k] + 2 * PW + 2;
+#pragma unroll
+        for (int u = 0; u < NU; ++u) {
+          const float cv = tanhf(xc[k][u]);
           hn[k][u] = z[k][u] * hs[u * PLANE + c] + (1.0f - z[k][u]) * cv;
         }
       }
@@ -173,7 +199,7 @@ __global__ void __launch_bounds__(256) maxout_kernel(const float* __restrict__ y
   }
 }
 
-constexpr int kTopSmem = ((2 * NU + 1) * PLANE + 25 * NU * 6 + 25 * NU * NU + 25 * 9) * (int)sizeof(float);
+constexpr int kTopSmem = ((2 * NU + 1) * PLANE + 1 + 25 * NU * 6 + 25 * NU * NU + 25 * 9) * (int)sizeof(float);
 
 template <typename TA>
 int launch_topgru(const float* xg, int ldx, int So, int Wo, const float* uzr, const float* uc, const float* sal,
