@@ -84,7 +84,9 @@ typedef struct rgp_tapgemm_args {
   /* Dense-M mode of a 3x3 SAME convolution (RGP_EPI_STORE_F32, 9 taps in (ky,kx) order, tcgen05 engine only): M counts only
    * the G*G real positions of each frame (M = frames * G*G instead of frames * S: 49 instead of 64 rows per 7x7 frame).  A
    * is the same p-layout operand (S, Wp, G describe it); each tap's A tile is fetched by a TMA im2col load with hardware
-   * zero fill at the frame borders, and row m = f*G*G + y*G + x is stored at the q-row f*S + y*Wp + x of out_f32. */
+   * zero fill at the frame borders, and row m = f*G*G + y*G + x is stored at the q-row f*S + y*Wp + x of out_f32.
+   * im2col = 2: the TRANSPOSE of that convolution (BPTT: dX of the input half) with RGP_EPI_DX_DENSE - A is the q-layout
+   * gradient (zero at the pad positions), tap (ky,kx) reads position (y+1-ky, x+1-kx), row m is stored at dense row m. */
   int im2col;
 } rgp_tapgemm_args;
 

@@ -112,6 +112,11 @@ __device__ __forceinline__ RowInfo make_row(const rgp_tapgemm_args& a, int m) {
       break;
     }
     default: {
+      if (a.im2col && a.epi == RGP_EPI_DX_DENSE) {   // dense-M transposed conv: row m IS the dense row f*P + y*G + x
+        r.valid = true;
+        r.orow = m;
+        break;
+      }
       int f = m / a.S, q = m - f * a.S;
       int y = q / a.Wp, x = q - y * a.Wp;
       r.valid = (y < a.G) && (x < a.G);

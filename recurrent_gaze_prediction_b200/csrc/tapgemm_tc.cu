@@ -424,7 +424,9 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             const int P = a.G * a.G;
             const int fn = m0 / P, rem = m0 - fn * P;
             const int hy = rem / a.G, wx = rem - hy * a.G;
-            tma_load_im2col_4d(sa, &tmA, &full[stage], kc * BK, wx - 1, hy - 1, fn, (uint16_t)(tap % 3), (uint16_t)(tap / 3));
+            // im2col == 2: the transposed conv of the backward pass - tap (ky, kx) reads pixel (x + 1 - kx, y + 1 - ky)
+            const int ox = a.im2col == 2 ? 2 - tap % 3 : tap % 3, oy = a.im2col == 2 ? 2 - tap / 3 : tap / 3;
+            tma_load_im2col_4d(sa, &tmA, &full[stage], kc * BK, wx - 1, hy - 1, fn, (uint16_t)ox, (uint16_t)oy);
           } else {
             tma_load_2d(sa, &tmA, &full[stage], kc * BK, m0 + a.tap_off[tap]);
           }
@@ -721,8 +723,9 @@ int launch(const rgp_tapgemm_args& a, cudaStream_t s) {
   int rc;
   if (a.im2col) {
     const long long frames = a.M / (a.G * a.G);
-    rc = tc::encode_map_im2col_bf16((const __nv_bfloat16*)a.A + (long long)(a.Wp + 1) * a.lda, a.K, a.G, frames, a.lda, a.Wp,
-                                    a.S, 1, BM, &tmA);
+    // im2col == 1: A is a p-layout operand (pixel (0,0) at row Wp+1); == 2: a q-layout gradient (pixel (0,0) at row 0)
+    const long long row0 = a.im2col == 2 ? 0 : (a.Wp + 1);
+    rc = tc::encode_map_im2col_bf16((const __nv_bfloat16*)a.A + row0 * a.lda, a.K, a.G, frames, a.lda, a.Wp, a.S, 1, BM, &tmA);
   } else {
     rc = make_map(a.A, a.rowsA, a.lda, a.K, slab ? sc.boxrows : BM, &tmA);
   }
@@ -847,9 +850,11 @@ int num_sms() {
 int tapgemm_tc(const rgp_tapgemm_args& a, cudaStream_t s) {
   RGP_CHECK_ARG(a.K % BK == 0, "tapgemm_tc: K=%d must be a multiple of %d", a.K, BK);
   if (a.im2col)
-    RGP_CHECK_ARG(a.ntaps == 9 && a.epi == RGP_EPI_STORE_F32 && !a.accumulate && a.G > 0 && a.M % (a.G * a.G) == 0 &&
-                  a.N % 32 == 0 && a.S >= (a.G + 1) * a.Wp - 1 && a.Wp > a.G,
-                  "tapgemm_tc: im2col mode is a 3x3 SAME conv with RGP_EPI_STORE_F32 (ntaps=%d epi=%d M=%d G=%d)", a.ntaps, a.epi, a.M, a.G);
+    RGP_CHECK_ARG(a.ntaps == 9 && !a.accumulate && a.G > 0 && a.M % (a.G * a.G) == 0 && a.N % 32 == 0 &&
+                  a.S >= (a.G + 1) * a.Wp - 1 && a.Wp > a.G &&
+                  ((a.im2col == 1 && a.epi == RGP_EPI_STORE_F32) || (a.im2col == 2 && a.epi == RGP_EPI_DX_DENSE)),
+                  "tapgemm_tc: im2col mode is a 3x3 SAME conv: 1 + RGP_EPI_STORE_F32 (forward) or 2 + RGP_EPI_DX_DENSE (its "
+                  "transpose) (im2col=%d ntaps=%d epi=%d M=%d G=%d)", a.im2col, a.ntaps, a.epi, a.M, a.G);
   RGP_CHECK_ARG(a.lda % 8 == 0, "tapgemm_tc: lda=%d must be a multiple of 8 (16-byte TMA stride)", a.lda);
   RGP_CHECK_ARG(((uintptr_t)a.A & 15) == 0 && ((uintptr_t)a.Bw & 15) == 0, "tapgemm_tc: operands must be 16-byte aligned");
   const int mtiles = (a.M + BM - 1) / BM;

@@ -791,8 +791,10 @@ class GazeEngine(TrainStateMixin):
         # ---- projection (only when the reference entry [B,T,1024,7,7] was used)
         if self.entry == "c3d":
             lib.rgp_transpose_taps(self._ptr("Wx_op"), self.WxT.data_ptr(), 9, NG, Cin, self.dtype, s)
-            self._gemm(A=self.dG.data_ptr(), rowsA=rowsT, lda=NG, K=NG, Bw=self.WxT.data_ptr(), M=rowsT, N=Cin,
-                       taps=btaps, epi=L.EPI_DX_DENSE, S=S, Wp=Wp, G=G, P=P, out_op=self.dEmb.data_ptr(), ldo=Cin)
+            dense = (self.dtype == 1 and self.engine != 1 and os.environ.get("RGP_IM2COL", "1") != "0")
+            self._gemm(A=self.dG.data_ptr(), rowsA=rowsT, lda=NG, K=NG, Bw=self.WxT.data_ptr(),
+                       M=T * B * P if dense else rowsT, N=Cin, taps=btaps, epi=L.EPI_DX_DENSE, S=S, Wp=Wp, G=G, P=P,
+                       out_op=self.dEmb.data_ptr(), ldo=Cin, im2col=2 if dense else 0)
             self._wgrad(self.dEmb.data_ptr(), Cin, 0, Cin, self.Apack.data_ptr(), self.Apack.shape[0], self.Cfeat,
                         self.Cfeat, T * B * P, [0], g("proj_W_op"))
             lib.rgp_colsum(self.dEmb.data_ptr(), Cin, T * B * P, Cin, g("proj_b"), self.dtype, s)
