@@ -124,6 +124,15 @@ int rgp_convgru_seq_fwd(const rgp_gru_seq_args* a, void* stream);
  * HOST array of n <= 32*12 values laid out [step][event] (events listed in csrc/gru_seq.cu).  Synchronises the device. */
 int rgp_convgru_seq_profile(unsigned long long* host_out, int n);
 
+/* Small-batch persistent ConvGRU (same cell, gaze_grcn.py:95-129 / :259-288; csrc/lstm_seq.cu): CTA (tile, split) owns 128
+ * q-rows x 16 channels for all T steps, its slices of U_z | U_r and U (110 KB at hidden 128, the reference's own width) stay in
+ * shared memory, h and z of its rows in registers; the two halo exchanges of a step (r.h, then h_t) go through per-tile
+ * counters (no grid barrier, cooperative launch).  For the batches rgp_convgru_seq_fwd is too coarse for (tiles * Ch/16 <=
+ * SMs: up to 36 clips at 7x7; the reference trains at 28).  Same argument struct (nsplit / mcast / ntile ignored); `flags`:
+ * workspace of 2 * mtiles + 1 int32, ZEROED by the caller before every launch (flags[mtiles] != 0 afterwards = time-out). */
+int rgp_convgru_seq_small_fwd(const rgp_gru_seq_args* a, int* flags, void* stream);
+int rgp_convgru_seq_small_fits(int B, int G, int Ch);
+
 /* Persistent ConvLSTM recurrence (gaze_lstm.py:103-133 as written, unrolled by :260-286): ALL T steps in ONE launch, for
  * any grid (frames may straddle the 128-row tiles: 14x14, BASELINE config 4).  CTA (tile, split) owns 128 q-rows and
  * Ch/nsplit = 16 channels of all three hidden convolutions for the whole sequence: its slice of W_h (9 taps x 3 gates x

@@ -534,6 +534,250 @@ lstm_seq_multi_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_cons
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Small-batch persistent ConvGRU (gaze_grcn.py:95-129 unrolled by :259-288) with the same structure: CTA (tile, split) owns
+// 128 q-rows x 16 channels, its slices of U_z | U_r (9 taps x Ch/64 x 32 rows) and U (x 16 rows) - 110 KB at hidden 128, the
+// reference's own width (gaze_grcn.py:211) - stay in shared memory, the state h and the update gate z of its rows live in
+// registers.  A GRU step has TWO exchanges (r.h must be complete on the halo before the candidate's conv): phase ZR
+// (N = 32) -> r.h rows published through flags[0..mtiles) ; phase C (N = 16) -> h_t rows published through
+// flags[mtiles+1..2*mtiles+1).  Serves the batches the tile-independent gru_seq kernel is too coarse for (the reference
+// trains at 28 clips: 14 tiles x 8 splits = 112 CTAs; there the per-step path is two launches of ~12 us per step).
+// ---------------------------------------------------------------------------------------------------------------------
+constexpr int kZRTileBytes = 2 * NC * BK * 2;     // 4096: z rows | r rows of one (tap, k-chunk)
+constexpr int kCTileBytes = NC * BK * 2;          // 2048
+constexpr int kSmemGruW = 9 * kMaxKch * (kZRTileBytes + kCTileBytes);   // 110592
+constexpr int kSmemBytesGru = kSmemGruW + kSmemSlab + 256 + 1024;
+
+__device__ __forceinline__ bool wait_tiles(const int* flags, int tile, int mtiles, int need, int* err, int lane, bool& dead) {
+  // lanes 0..2 watch tiles (tile-1, tile, tile+1); returns when all show `need` (or the launch has been declared dead)
+  const int nb = tile - 1 + lane;
+  const bool watch = lane < 3 && nb >= 0 && nb < mtiles;
+  if (dead) return false;
+  const long long t0 = clock64();
+  for (;;) {
+    const bool ok = !watch || ld_acquire(flags + nb) >= need;
+    if (__all_sync(0xffffffffu, ok)) return true;
+    bool bad = false;
+    if (lane == 0) {
+      bad = ld_acquire(err) != 0;
+      if (!bad && clock64() - t0 > kSpinLimit) { atomicExch(err, 1); bad = true; }
+    }
+    if (__any_sync(0xffffffffu, bad)) { dead = true; return false; }
+  }
+}
+
+__global__ void __launch_bounds__(NTHREADS, 1)
+gru_small_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant__ CUtensorMap tmRH,
+                 const __grid_constant__ CUtensorMap tmUzr, const __grid_constant__ CUtensorMap tmUc,
+                 const rgp_gru_seq_args a, int* const flags, const int slab_rows) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* wzr = smem;                                            // [tap][kc] 32 rows x 128 B
+  uint8_t* wc = smem + 9 * kMaxKch * kZRTileBytes;                // [tap][kc] 16 rows x 128 B
+  uint8_t* slab = smem + kSmemGruW;                               // [kc] slab_rows x 128 B
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kSmemGruW + kSmemSlab);
+  uint64_t* wfull = bars;
+  uint64_t* fullH = bars + 1;                                     // [kMaxKch] h_{t-1} slab
+  uint64_t* fullR = fullH + kMaxKch;                              // [kMaxKch] r.h slab
+  uint64_t* zr_full = fullR + kMaxKch;
+  uint64_t* c_full = zr_full + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(c_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int Ch = a.Ch, G = a.G, Wp = G + 1, S = Wp * Wp;
+  const int nsplit = Ch / NC;
+  const int tile = (int)(blockIdx.x / nsplit), split = (int)(blockIdx.x % nsplit);
+  const int ch0 = split * NC;
+  const int M = a.B * S;
+  const int mtiles = (M + BM - 1) / BM;
+  const int m0 = tile * BM;
+  const int kch = Ch / BK;
+  int* const flagsR = flags;                   // [mtiles]  r.h of step t published
+  int* const err = flags + mtiles;
+  int* const flagsH = flags + mtiles + 1;      // [mtiles]  h_t published
+  const bool train = a.Rs != nullptr;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmH) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmRH) : "memory");
+    mbar_init(wfull, 1);
+    for (int i = 0; i < kMaxKch; ++i) { mbar_init(&fullH[i], 1); mbar_init(&fullR[i], 1); }
+    mbar_init(zr_full, 1); mbar_init(c_full, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"((uint32_t)kTmemCols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== dependency waits + TMA producer =====================
+    if (lane == 0) {
+      mbar_expect_tx(wfull, (uint32_t)(9 * kch * (kZRTileBytes + kCTileBytes)));
+      for (int tap = 0; tap < 9; ++tap)
+        for (int kc = 0; kc < kch; ++kc) {
+          for (int g = 0; g < 2; ++g)
+            tma_load_2d(wzr + (tap * kch + kc) * kZRTileBytes + g * (NC * BK * 2), &tmUzr, wfull, kc * BK,
+                        tap * 2 * Ch + g * Ch + ch0);
+          tma_load_2d(wc + (tap * kch + kc) * kCTileBytes, &tmUc, wfull, kc * BK, tap * Ch + ch0);
+        }
+    }
+    bool dead = false;
+    for (int t = 0; t < a.T; ++t) {
+      if (t > 0) wait_tiles(flagsH, tile, mtiles, nsplit * t, err, lane, dead);
+      if (lane == 0) {
+        fence_proxy_async();
+        for (int kc = 0; kc < kch; ++kc) {
+          mbar_expect_tx(&fullH[kc], (uint32_t)(slab_rows * BK * 2));
+          tma_load_2d(slab + kc * kSlabBytes, &tmH, &fullH[kc], kc * BK, t * M + m0);
+        }
+      }
+      __syncwarp();
+      // r.h of this step: complete on the tile and both neighbours (their ZR MMAs, which read the h slab, are done too)
+      wait_tiles(flagsR, tile, mtiles, nsplit * (t + 1), err, lane, dead);
+      if (lane == 0) {
+        fence_proxy_async();
+        for (int kc = 0; kc < kch; ++kc) {
+          mbar_expect_tx(&fullR[kc], (uint32_t)(slab_rows * BK * 2));
+          tma_load_2d(slab + kc * kSlabBytes, &tmRH, &fullR[kc], kc * BK, (train ? t : 0) * M + m0);
+        }
+      }
+      __syncwarp();
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    constexpr uint32_t idesc_zr = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)((2 * NC) >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+    constexpr uint32_t idesc_c = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(NC >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+    mbar_wait(wfull, 0);
+    for (int t = 0; t < a.T; ++t) {
+      const uint32_t par = (uint32_t)(t & 1);
+      for (int ph = 0; ph < 2; ++ph) {
+        for (int kc = 0; kc < kch; ++kc) {
+          mbar_wait(ph == 0 ? &fullH[kc] : &fullR[kc], par);
+          tc_fence_after();
+          if (lane == 0) {
+            for (int tap = 0; tap < 9; ++tap) {
+              const int off = (tap / 3) * Wp + (tap % 3);
+              const uint64_t adesc = make_sdesc(smem_u32(slab + kc * kSlabBytes) + (uint32_t)off * (BK * 2));
+              const uint64_t bdesc = make_sdesc(smem_u32(ph == 0 ? wzr + (tap * kch + kc) * kZRTileBytes
+                                                                 : wc + (tap * kch + kc) * kCTileBytes));
+#pragma unroll
+              for (int k = 0; k < BK / 16; ++k)
+                tc_mma_bf16(tmem_base + (uint32_t)(ph == 0 ? 0 : 32), adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k),
+                            ph == 0 ? idesc_zr : idesc_c, (kc | tap | k) ? 1u : 0u);
+            }
+            if (kc == kch - 1) tc_commit(ph == 0 ? zr_full : c_full);
+          }
+          __syncwarp();
+        }
+      }
+    }
+  } else {
+    // ===================== epilogue warps 2..5: one thread = one q-row, NC channels; h and z in registers ==========
+    using TA = __nv_bfloat16;
+    const int lg = warp & 3;
+    const int lrow = lg * 32 + lane;
+    const int m = m0 + lrow;
+    const bool inrange = m < M;
+    const int f = m / S, q = m - f * S;
+    const int y = q / Wp, x = q - y * Wp;
+    const bool valid = inrange && y < G && x < G;
+    const long long prow = (long long)m + Wp + 1;
+    const uint32_t tlane = tmem_base + ((uint32_t)(lg * 32) << 16);
+    const int threeCh = 3 * Ch;
+    float h[NC];
+#pragma unroll
+    for (int j = 0; j < NC; ++j) h[j] = 0.f;
+    if (valid) { ld8(a.Hf + prow * Ch + ch0, h); ld8(a.Hf + prow * Ch + ch0 + 8, h + 8); }      // h_0 (slab 0)
+    for (int t = 0; t < a.T; ++t) {
+      const long long mt = (long long)t * M + m;
+      float xz[NC], xr[NC], xc[NC];
+      if (valid) {
+        const float* xp = a.Xg + mt * threeCh + ch0;
+        ld8(xp, xz); ld8(xp + 8, xz + 8);
+        ld8(xp + Ch, xr); ld8(xp + Ch + 8, xr + 8);
+        ld8(xp + 2 * Ch, xc); ld8(xp + 2 * Ch + 8, xc + 8);
+      }
+      // ---------------- phase ZR: z, r ; r.h rows -> the candidate conv's operand ----------------
+      mbar_wait(zr_full, (uint32_t)(t & 1));
+      tc_fence_after();
+      float z[NC], r[NC];
+      tc_ld16(tlane, z);
+      tc_ld16(tlane + 16u, r);
+      tc_fence_before();
+      if (valid) {
+        float rh[NC];
+#pragma unroll
+        for (int j = 0; j < NC; ++j) {
+          z[j] = sigm(z[j] + xz[j]);
+          r[j] = sigm(r[j] + xr[j]);
+          rh[j] = r[j] * h[j];
+        }
+        stbf16x16((TA*)a.RH + ((long long)(train ? t : 0) * M + prow) * Ch + ch0, rh);
+      }
+      fence_proxy_async();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (warp == 2 && lane == 0) { __threadfence(); red_release_add(flagsR + tile, 1); }
+      if (train && valid) {
+        st8(a.Zs + mt * Ch + ch0, z); st8(a.Zs + mt * Ch + ch0 + 8, z + 8);
+        st8(a.Rs + mt * Ch + ch0, r); st8(a.Rs + mt * Ch + ch0 + 8, r + 8);
+      }
+      // ---------------- phase C: candidate, state update ----------------
+      mbar_wait(c_full, (uint32_t)(t & 1));
+      tc_fence_after();
+      float c[NC];
+      tc_ld16(tlane + 32u, c);
+      tc_fence_before();
+      long long rn = 0;
+      if (valid) {
+#pragma unroll
+        for (int j = 0; j < NC; ++j) {
+          c[j] = tanh_fast(c[j] + xc[j]);
+          h[j] = z[j] * h[j] + (1.0f - z[j]) * c[j];
+        }
+        rn = ((long long)(t + 1) * M + prow) * Ch + ch0;
+        stbf16x16((TA*)a.Hop + rn, h);
+      }
+      fence_proxy_async();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (warp == 2 && lane == 0) { __threadfence(); red_release_add(flagsH + tile, 1); }
+      if (valid) {        // tail: fp32 master, saved candidate, BN-scaled head rows (gaze_grcn.py:325)
+        st8(a.Hf + rn, h); st8(a.Hf + rn + 8, h + 8);
+        if (train) { st8(a.Cs + mt * Ch + ch0, c); st8(a.Cs + mt * Ch + ch0 + 8, c + 8); }
+        if (a.HS) {
+          float v[NC];
+          if (a.bn_gamma) {
+            float g8[NC], b8[NC];
+            ld8(a.bn_gamma + (long long)t * Ch + ch0, g8); ld8(a.bn_gamma + (long long)t * Ch + ch0 + 8, g8 + 8);
+            ld8(a.bn_beta + (long long)t * Ch + ch0, b8); ld8(a.bn_beta + (long long)t * Ch + ch0 + 8, b8 + 8);
+#pragma unroll
+            for (int j = 0; j < NC; ++j) v[j] = g8[j] * (h[j] * a.alpha) + b8[j];
+          } else {
+#pragma unroll
+            for (int j = 0; j < NC; ++j) v[j] = h[j];
+          }
+          const long long orow = ((long long)t * a.B + f) * a.So + (long long)(y + a.pado) * a.Wo + (x + a.pado);
+          stbf16x16((TA*)a.HS + orow * Ch + ch0, v);
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)kTmemCols)
+                 : "memory");
+  }
+}
+
 int slab_rows_of(int G) { return (BM + 2 * (G + 1) + 2 + 7) & ~7; }
 
 bool shape_ok(int B, int G, int Ch) {
@@ -547,8 +791,61 @@ bool shape_ok(int B, int G, int Ch) {
   return R >= 1 && G <= 14 && mtiles <= 16LL * R;
 }
 
+bool gru_small_ok(int B, int G, int Ch) {
+  if (B <= 0 || G <= 0 || (Ch != 64 && Ch != 128)) return false;
+  if (slab_rows_of(G) > kMaxSlabRows) return false;
+  const int S = (G + 1) * (G + 1);
+  const long long mtiles = ((long long)B * S + BM - 1) / BM;
+  return mtiles * (Ch / NC) <= num_sms();
+}
+
 }  // namespace lstmseq
 using namespace lstmseq;
+
+int convgru_seq_small_fwd(const rgp_gru_seq_args& a, int* flags, cudaStream_t s) {
+  RGP_CHECK_ARG(a.dtype == 1, "rgp_convgru_seq_small_fwd: bf16 operands only (dtype=%d)", a.dtype);
+  RGP_CHECK_ARG(a.T > 0 && gru_small_ok(a.B, a.G, a.Ch), "rgp_convgru_seq_small_fwd: B=%d G=%d Ch=%d T=%d does not fit (Ch 64 or "
+                "128, G <= 14, tiles * Ch/16 <= SMs)", a.B, a.G, a.Ch, a.T);
+  RGP_CHECK_ARG(a.Hop && a.Hf && a.RH && a.Uzr && a.Uc && a.Xg && flags, "rgp_convgru_seq_small_fwd: null pointer%s", "");
+  RGP_CHECK_ARG((a.Rs == nullptr) == (a.Cs == nullptr) && (a.Rs == nullptr || a.Zs != nullptr),
+                "rgp_convgru_seq_small_fwd: training needs Zs, Rs and Cs%s", "");
+  RGP_CHECK_ARG((a.bn_gamma == nullptr) == (a.bn_beta == nullptr), "rgp_convgru_seq_small_fwd: bn_gamma / bn_beta%s", "");
+  RGP_CHECK_ARG(((uintptr_t)a.Hop & 31) == 0 && ((uintptr_t)a.Hf & 31) == 0 && ((uintptr_t)a.RH & 31) == 0 &&
+                ((uintptr_t)a.Xg & 31) == 0 && ((uintptr_t)a.HS & 31) == 0 && ((uintptr_t)a.Zs & 31) == 0 &&
+                ((uintptr_t)a.Rs & 31) == 0 && ((uintptr_t)a.Cs & 31) == 0 && ((uintptr_t)a.bn_gamma & 31) == 0 &&
+                ((uintptr_t)a.bn_beta & 31) == 0, "rgp_convgru_seq_small_fwd: buffers must be 32-byte aligned%s", "");
+  const int Ch = a.Ch, S = (a.G + 1) * (a.G + 1);
+  const int srows = slab_rows_of(a.G);
+  CUtensorMap tmH, tmRH, tmUzr, tmUc;
+  int rc = tc::encode_map_bf16(a.Hop, Ch, a.rowsH, (long long)Ch * 2, BK, srows, &tmH);
+  if (rc) return rc;
+  rc = tc::encode_map_bf16(a.RH, Ch, a.rowsRH, (long long)Ch * 2, BK, srows, &tmRH);
+  if (rc) return rc;
+  rc = tc::encode_map_bf16(a.Uzr, Ch, 18LL * Ch, (long long)Ch * 2, BK, NC, &tmUzr);
+  if (rc) return rc;
+  rc = tc::encode_map_bf16(a.Uc, Ch, 9LL * Ch, (long long)Ch * 2, BK, NC, &tmUc);
+  if (rc) return rc;
+  static PerDeviceFlag attr_set = {};
+  if (attr_set.need()) {
+    cudaError_t e = cudaFuncSetAttribute(gru_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytesGru);
+    if (e != cudaSuccess) { set_error("gru_small: cudaFuncSetAttribute(smem=%d): %s", kSmemBytesGru, cudaGetErrorString(e)); return -5; }
+    attr_set.set();
+  }
+  const int mtiles = (a.B * S + BM - 1) / BM;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)(mtiles * (Ch / NC)), 1, 1);
+  cfg.blockDim = dim3(NTHREADS, 1, 1);
+  cfg.dynamicSmemBytes = kSmemBytesGru;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeCooperative;
+  attr[0].val.cooperative = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, gru_small_kernel, tmH, tmRH, tmUzr, tmUc, a, flags, srows);
+  if (e != cudaSuccess) { set_error("gru_small launch: %s", cudaGetErrorString(e)); return -5; }
+  return check_launch("gru_small");
+}
 
 int convlstm_seq_fwd(const rgp_lstm_seq_args& a, cudaStream_t s) {
   RGP_CHECK_ARG(a.dtype == 1, "rgp_convlstm_seq_fwd: bf16 operands only (dtype=%d)", a.dtype);
@@ -607,6 +904,13 @@ int rgp_convlstm_seq_fwd(const rgp_lstm_seq_args* a, void* stream) {
   RGP_CHECK_ARG(a != nullptr, "rgp_convlstm_seq_fwd: null args%s", "");
   return rgp::convlstm_seq_fwd(*a, (cudaStream_t)stream);
 }
+
+int rgp_convgru_seq_small_fwd(const rgp_gru_seq_args* a, int* flags, void* stream) {
+  RGP_CHECK_ARG(a != nullptr, "rgp_convgru_seq_small_fwd: null args%s", "");
+  return rgp::convgru_seq_small_fwd(*a, flags, (cudaStream_t)stream);
+}
+
+int rgp_convgru_seq_small_fits(int B, int G, int Ch) { return rgp::lstmseq::gru_small_ok(B, G, Ch) ? 1 : 0; }
 
 int rgp_convlstm_seq_fits(int B, int G, int Ch) { return rgp::lstmseq::shape_ok(B, G, Ch) ? 1 : 0; }
 

@@ -231,7 +231,14 @@ class GazeEngine(TrainStateMixin):
         if seq is None:
             env = os.environ.get("RGP_SEQ", "")
             seq = (dtype == 1 and engine != 1 and Ch in (128, 256) and (env == "1" or (env != "0" and mtiles >= 64)))
-        self.use_seq = bool(seq) and (not self.lstm) and 128 % self.S == 0
+        self.use_seq = bool(seq) and seq != "small" and (not self.lstm) and 128 % self.S == 0
+        # Small-batch persistent ConvGRU (rgp_convgru_seq_small_fwd: weight slices resident in shared memory, two counter
+        # exchanges per step) - the regime below gru_seq's 64 tiles where all tiles x Ch/16 CTAs are co-resident (hidden 128:
+        # up to 36 clips at 7x7, the reference's batch 28).
+        gfits = getattr(self.lib, "rgp_convgru_seq_small_fits", None)
+        self.use_seq_small = bool((not self.lstm) and (not self.use_seq) and seq_arg is not False and engine != 1 and
+                                  gfits is not None and (dtype == 1 or seq_arg == "small") and gfits(B, G, Ch) and
+                                  os.environ.get("RGP_SEQ", "") != "0")
         # Persistent ConvLSTM recurrence (rgp_convlstm_seq_fwd: all T steps in one launch, any grid; W_h slices resident in
         # shared memory, tiles exchange their halo rows through per-tile counters).  Taken whenever all its CTAs
         # (tiles x Ch/16) are co-resident - the small-batch, latency-bound regime (14x14: up to 10 clips; 7x7: up to 36).
@@ -415,6 +422,7 @@ class GazeEngine(TrainStateMixin):
             self.Lsave = z(T, B * S, 5 * Ch) if self.train else None
         else:
             self.RH = z(nsl * B * S + self.tail, Ch, dt=tdt)
+            self.seq_flags = torch.zeros(2 * ((B * S + 127) // 128) + 1, dtype=torch.int32, device=dev)
             self.Z = z(nsl, B * S, Ch)
             self.Rs = z(T, B * S, Ch) if self.train else None
             self.Cs = z(T, B * S, Ch) if self.train else None
@@ -571,7 +579,7 @@ class GazeEngine(TrainStateMixin):
         pop = self._pop
         NX = self.ngx * Ch
         M = B * S
-        if self.use_seq:
+        if self.use_seq or self.use_seq_small:
             a = L.GruSeqArgs()
             a.Hop, a.rowsH, a.Hf = self.Hop.data_ptr(), self.Hop.shape[0], self.Hf.data_ptr()
             a.RH, a.rowsRH = self.RH.data_ptr(), self.RH.shape[0]
@@ -587,7 +595,11 @@ class GazeEngine(TrainStateMixin):
             a.B, a.T, a.G, a.Ch = B, T, G, Ch
             a.So, a.Wo, a.pado = HEAD_S, HEAD_W, HEAD_PAD
             a.nsplit, a.dtype, a.mcast, a.ntile = self.nsplit, self.dtype, self.mcast, self.ntile
-            lib.rgp_convgru_seq_fwd(C.byref(a), s)
+            if self.use_seq_small:
+                lib.rgp_zero(self.seq_flags.data_ptr(), self.seq_flags.numel() * 4, s)
+                lib.rgp_convgru_seq_small_fwd(C.byref(a), self.seq_flags.data_ptr(), s)
+            else:
+                lib.rgp_convgru_seq_fwd(C.byref(a), s)
             if self.head == "fc":   # gaze_grcn77.py:206-211
                 self._fc_head_all(s)
             return
@@ -646,7 +658,11 @@ class GazeEngine(TrainStateMixin):
     def seq_timed_out(self):
         """True if the last persistent ConvLSTM launch gave up waiting for a neighbouring tile (synchronises; the kernel
         never hangs: it reports through the last counter and the pass's results are then invalid)"""
-        return bool(self.use_seq_lstm and int(self.seq_flags[-1].cpu()) != 0)
+        if self.use_seq_lstm:
+            return int(self.seq_flags[-1].cpu()) != 0
+        if getattr(self, "use_seq_small", False):
+            return int(self.seq_flags[(self.B * self.S + 127) // 128].cpu()) != 0
+        return False
 
     def _fc_head_all(self, s):
         """per-position FC head on the fp32 states of all T steps (they stay resident in Hf): one launch"""

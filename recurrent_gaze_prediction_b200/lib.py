@@ -79,6 +79,7 @@ _SIGS = {
     "rgp_tapgemm": [C.POINTER(TapGemmArgs), _vp],
     "rgp_convgru_seq_fwd": [C.POINTER(GruSeqArgs), _vp],
     "rgp_convgru_seq_profile": [_vp, _i],
+    "rgp_convgru_seq_small_fwd": [C.POINTER(GruSeqArgs), _vp, _vp],
     "rgp_convlstm_seq_fwd": [C.POINTER(LstmSeqArgs), _vp],
     "rgp_convlstm_seq_profile": [_vp, _i],
     "rgp_pack_c3d": [_vp, _vp, _i, _i, _i, _i, _i, _vp],
@@ -156,6 +157,8 @@ class RgpLib(object):
         self._dll.rgp_metrics_fused_fits.argtypes = [_i, _i, _i, _i]
         self._dll.rgp_convlstm_seq_fits.restype = _i
         self._dll.rgp_convlstm_seq_fits.argtypes = [_i, _i, _i]
+        self._dll.rgp_convgru_seq_small_fits.restype = _i
+        self._dll.rgp_convgru_seq_small_fits.argtypes = [_i, _i, _i]
         for name, sig in _SIGS.items():
             fn = getattr(self._dll, name)
             fn.argtypes = sig
@@ -187,9 +190,13 @@ class RgpLib(object):
         """a predicate: 1 if the persistent ConvLSTM kernel can hold this shape (all its CTAs co-resident)"""
         return int(self._dll.rgp_convlstm_seq_fits(B, G, Ch))
 
+    def rgp_convgru_seq_small_fits(self, B, G, Ch):
+        """a predicate: 1 if the small-batch persistent ConvGRU kernel can hold this shape"""
+        return int(self._dll.rgp_convgru_seq_small_fits(B, G, Ch))
+
     def symbols(self):
         return sorted(list(_SIGS) + ["rgp_last_error", "rgp_version", "rgp_has_tcgen05", "rgp_metrics_fused_fits",
-                                     "rgp_convlstm_seq_fits"])
+                                     "rgp_convlstm_seq_fits", "rgp_convgru_seq_small_fits"])
 
 
 _LIB = None

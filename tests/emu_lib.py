@@ -821,14 +821,14 @@ class EmuLib(object):
         return self.rgp_auc_sampled(s.ctypes.data, fix, idx, minmax, mm_stride, auc, tpc, fpc, n, oh * ow, nrows, nrep,
                                     step, nthr_max, maxfix, stream)
 
-    def rgp_convgru_seq_fwd(self, aref, stream):
+    def rgp_convgru_seq_fwd(self, aref, stream, any_grid=False):
         """All T steps = T x (GRU_ZR tap-GEMM + GRU_C tap-GEMM) on the same buffers (fp32 emulation)."""
         a = aref._obj
         Ch, B, G = a.Ch, a.B, a.G
         Wp = G + 1
         S = Wp * Wp
         M = B * S
-        assert 128 % S == 0 and a.nsplit in (1, 2)
+        assert (any_grid or 128 % S == 0) and a.nsplit in (1, 2)
         train = bool(a.Rs)
         taps = [ky * Wp + kx for ky in range(3) for kx in range(3)]
         rows_step = M + ((2 * Wp + 2 + 31) // 32) * 32
@@ -859,6 +859,19 @@ class EmuLib(object):
                 g.bias, g.bias2, g.alpha = a.bn_gamma + t * Ch * 4, a.bn_beta + t * Ch * 4, a.alpha
             self.rgp_tapgemm(C.byref(g), stream)
         return 0
+
+    def rgp_convgru_seq_small_fits(self, B, G, Ch):
+        return 1 if (Ch % 16 == 0 and G <= 14 and ((B * (G + 1) ** 2 + 127) // 128) * (Ch // 16) <= 148) else 0
+
+    def rgp_convgru_seq_small_fwd(self, aref, flags, stream):
+        a = aref._obj
+        mt = (a.B * (a.G + 1) ** 2 + 127) // 128
+        fl = arr(flags, (2 * mt + 1,), np.int32)
+        assert not fl.any(), "the caller zeroes the counters before every launch"
+        rc = self.rgp_convgru_seq_fwd(aref, stream, any_grid=True)
+        fl[:mt] += a.T * (a.Ch // 16)
+        fl[mt + 1:] += a.T * (a.Ch // 16)
+        return rc
 
     def rgp_convlstm_seq_fits(self, B, G, Ch):
         tiles = (B * (G + 1) ** 2 + 127) // 128

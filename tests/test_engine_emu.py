@@ -133,3 +133,20 @@ def test_persistent_convlstm_orchestration_matches_per_step(G, B, head):
         outs.append((logits, eng.Lsave.numpy().copy(), eng.read_state()[0].numpy().copy()))
     for x, y in zip(*outs):
         assert np.allclose(x, y, rtol=1e-6, atol=1e-7)
+
+
+@pytest.mark.parametrize("G,B,model", [(7, 3, "gaze_grcn"), (14, 2, "gaze_grcn77")])
+def test_small_batch_persistent_convgru_orchestration_matches_per_step(G, B, model):
+    """engine wiring of rgp_convgru_seq_small_fwd (counters zeroed per launch, BN offsets, training saves) == per-step path"""
+    outs = []
+    for seq in ("small", False):
+        p = O.init_params(model, hidden=16, T=3, grid=G, dim_proj=32, dim_feature=64, seed=0, regime="S")
+        emb = SY.make_embedded(np.random.RandomState(5), B, 3, G, 32)
+        eng = GazeEngine(model, B=B, T=3, G=G, Ch=16, Cin=32, Cfeat=64, dtype=0, device="cpu", lib=EmuLib(), train=True, seq=seq)
+        assert eng.use_seq_small == (seq == "small") and not eng.use_seq
+        eng.load_tf_params(p)
+        for _ in range(2):
+            logits = eng.forward(emb=torch.from_numpy(emb)).numpy().copy()
+        outs.append((logits, eng.Z.numpy().copy(), eng.Rs.numpy().copy(), eng.Cs.numpy().copy(), eng.read_state().numpy().copy()))
+    for x, y in zip(*outs):
+        assert np.allclose(x, y, rtol=1e-6, atol=1e-7)

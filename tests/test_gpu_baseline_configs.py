@@ -249,3 +249,49 @@ def test_persistent_convlstm_matches_per_step_path_and_oracle(G, B, T, head, tra
         _report("config4_gaze_lstm_G14_T128_B8_persistent", max_map_err=float(err.max()), tol=2e-2,
                 map_err_per_t=[float(x) for x in err.max(axis=0)])
         assert err.max() <= 2e-2, err.max()
+
+
+@pytest.mark.parametrize("model,G,B,T,train", [("gaze_grcn", 7, 28, 42, False), ("gaze_grcn", 7, 5, 6, True),
+                                                 ("gaze_grcn77", 14, 8, 24, False), ("gaze_grcn77", 7, 36, 4, True),
+                                                 ("gaze_grcn", 7, 1, 3, False)])
+def test_small_batch_persistent_convgru_vs_per_step_and_oracle(model, G, B, T, train):
+    """rgp_convgru_seq_small_fwd (hidden 128, weight slices resident in shared memory, two counter exchanges per step) against
+    the per-step path - states, saved gates, maps - and at the reference's own training shape (28 clips x T = 42, hidden
+    128: train_gaze.py:74-75, gaze_rnn.py:50, gaze_grcn.py:211) against the float64 oracle."""
+    Ch = 128
+    p = O.init_params(model, hidden=Ch, T=T, grid=G, seed=6, regime="S")
+    rng = np.random.RandomState(12)
+    emb = SY.make_embedded(rng, B, T, G, 512)
+    GH = 49 if model == "gaze_grcn" else G
+    gt, _ = SY.make_gazemaps(rng, B, T, GH, GH, normalize=True)
+    res = []
+    for seq in (None, False):
+        eng = GazeEngine(model, B=B, T=T, G=G, Ch=Ch, dtype=1, device="cuda", train=train, seq=seq)
+        assert eng.use_seq_small == (seq is None) and not eng.use_seq
+        eng.load_tf_params(p)
+        for _ in range(2):
+            eng.forward(emb=torch.from_numpy(emb).cuda(), gt=torch.from_numpy(gt).cuda())
+        torch.cuda.synchronize()
+        assert not eng.seq_timed_out()
+        d = dict(probs=eng.probs.cpu().numpy(), h=eng.read_state().cpu().numpy(), hmid=eng.read_state(max(1, T // 2)).cpu().numpy())
+        if train:
+            d.update(z=eng.Z.cpu().numpy(), r=eng.Rs.cpu().numpy(), c=eng.Cs.cpu().numpy())
+        res.append(d)
+    a, b = res
+    for k in a:
+        valid = slice(None)
+        scale = max(1.0, np.abs(b[k]).max()) if k != "probs" else b[k].max()
+        if k in ("z", "r", "c"):       # saved gates: only the real positions are defined (pad rows differ by construction)
+            Wp = G + 1
+            av, bv = (x.reshape(T, B, Wp, Wp, Ch)[:, :, :G, :G] for x in (a[k], b[k]))
+            assert np.abs(av - bv).max() <= 2e-2, k
+        else:
+            assert np.abs(a[k] - b[k]).max() <= 2e-2 * scale, k
+    if T == 42:
+        with torch.no_grad():
+            lg = O.recurrent_network(model, O.to_torch(p), emb=torch.tensor(emb, dtype=torch.float64))
+            ref = O.softmax_2d(lg).numpy()
+        err = _map_err(a["probs"], ref)
+        _report("reference_shape_grcn_B28_T42_Ch128_small_seq", max_map_err=float(err.max()), tol=2e-2,
+                map_err_per_t=[float(x) for x in err.max(axis=0)])
+        assert err.max() <= 2e-2, err.max()
