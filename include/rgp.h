@@ -132,6 +132,22 @@ int rgp_convgru_seq_profile(unsigned long long* host_out, int n);
  * workspace of 2 * mtiles + 1 int32, ZEROED by the caller before every launch (flags[mtiles] != 0 afterwards = time-out). */
 int rgp_convgru_seq_small_fwd(const rgp_gru_seq_args* a, int* flags, void* stream);
 int rgp_convgru_seq_small_fits(int B, int G, int Ch);
+/* ... and its reverse-time mirror: BPTT through the T ConvGRU steps (tf.gradients of gaze_grcn.py:108-127, base.py:278-281)
+ * in ONE launch - what the per-step path does with rgp_gru_bwd_last + 2 rgp_tapgemm (RGP_EPI_BWD_RH / RGP_EPI_BWD_H) per step.
+ * Fills dG [T*M, 3Ch] (operand dtype, q-layout, columns dpre_z | dpre_r | dpre_c) for the weight-gradient contractions. */
+typedef struct rgp_gru_bwd_args {
+  void* dG; long long rowsG;      /* [T*B*S, 3Ch] bf16, zero at the pad positions (never written)                          */
+  const void* UcT;                /* [9*Ch, Ch]  bf16: rgp_transpose_taps of Uc  (row tap*Ch + in channel, K = out channel) */
+  const void* UzrT;               /* [9*Ch, 2Ch] bf16: rgp_transpose_taps of Uzr (K = z | r out channels)                   */
+  const float* Zs; const float* Rs; const float* Cs;   /* saved gates [T, B*S, Ch] fp32 q-layout                          */
+  const float* Hf;                /* fp32 p-layout states, slab t = input state of step t                                  */
+  const float* dhs;               /* [T*B*S, Ch] fp32 q-layout: dL/d(head input) of every step                             */
+  const float* bn_gamma; float alpha;   /* [T, Ch] or NULL (gaze_grcn.py:325)                                             */
+  int B, T, G, Ch;
+  int dtype;                      /* must be 1                                                                             */
+} rgp_gru_bwd_args;
+/* flags: 2 * mtiles + 1 int32, zeroed by the caller before every launch (flags[mtiles] != 0 afterwards = time-out) */
+int rgp_convgru_seq_small_bwd(const rgp_gru_bwd_args* a, int* flags, void* stream);
 
 /* Persistent ConvLSTM recurrence (gaze_lstm.py:103-133 as written, unrolled by :260-286): ALL T steps in ONE launch, for
  * any grid (frames may straddle the 128-row tiles: 14x14, BASELINE config 4).  CTA (tile, split) owns 128 q-rows and

@@ -778,6 +778,246 @@ gru_small_kernel(const __grid_constant__ CUtensorMap tmH, const __grid_constant_
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Small-batch persistent ConvGRU BPTT (tf.gradients of gaze_grcn.py:108-127, base.py:278-281): the reverse-time mirror of
+// gru_small_kernel, all T steps in one launch.  CTA (tile, split) owns 128 q-rows x 16 INPUT channels of the two
+// transposed convolutions; its slices of U^T (9 taps x Ch/64 x 16 rows) and [U_z|U_r]^T (9 x 2Ch/64 x 16 rows) - 110 KB at
+// hidden 128 - stay in shared memory, dL/dh's non-conv part lives in registers.  Step t (t = T-1 .. 0):
+//   phase RH : acc = conv^T(dpre_c_t ; U)       -> dpre_r_t = acc h_{t-1} r (1-r)  (dG_t, r columns) ; dhpart += acc r
+//   phase H  : acc = conv^T([dpre_z_t, dpre_r_t] ; U_z|U_r) -> dh = acc + dhpart + head term ; gate backward of step t-1:
+//              dpre_z_{t-1}, dpre_c_{t-1} (dG_{t-1}) ; dhpart = dh z
+// Both operands are columns of the q-layout gradient buffer dG [T*M, 3Ch] (z | r | c), written 16 channels at a time by the
+// CTAs and exchanged through per-tile counters exactly like the forward kernel: flags[0..mtiles) = "dpre_z / dpre_c of the
+// step this iteration needs are complete", flags[mtiles+1..) = "dpre_r complete".  The gate backward of the last step
+// (rgp_gru_bwd_last) is the kernel's prologue.
+// ---------------------------------------------------------------------------------------------------------------------
+constexpr int kBwdTileBytes = NC * BK * 2;                               // 2048: 16 rows of one (tap, k-chunk)
+constexpr int kSmemBwdW = 9 * 3 * kMaxKch * kBwdTileBytes;               // U^T: kch chunks, [Uz|Ur]^T: 2*kch chunks -> 110592
+constexpr int kSmemBytesGruBwd = kSmemBwdW + 2 * kSmemSlab + 256 + 1024;  // slab: up to 2*kch k-chunks
+
+__global__ void __launch_bounds__(NTHREADS, 1)
+gru_small_bwd_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constant__ CUtensorMap tmUcT,
+                     const __grid_constant__ CUtensorMap tmUzrT, const rgp_gru_bwd_args a, int* const flags,
+                     const int slab_rows) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int Ch = a.Ch, G = a.G, Wp = G + 1, S = Wp * Wp;
+  const int kch = Ch / BK;
+  uint8_t* wc = smem;                                             // [tap][kc < kch]    16 rows x 128 B
+  uint8_t* wzr = smem + 9 * kch * kBwdTileBytes;                  // [tap][kc < 2*kch]
+  uint8_t* slab = smem + kSmemBwdW;                               // [kc < 2*kch] slab_rows x 128 B
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kSmemBwdW + 2 * kSmemSlab);
+  uint64_t* wfull = bars;
+  uint64_t* fullC = bars + 1;                                     // [kMaxKch]     dpre_c slab
+  uint64_t* fullZR = fullC + kMaxKch;                             // [2*kMaxKch]   dpre_z | dpre_r slab
+  uint64_t* rh_full = fullZR + 2 * kMaxKch;
+  uint64_t* h_full = rh_full + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(h_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nsplit = Ch / NC;
+  const int tile = (int)(blockIdx.x / nsplit), split = (int)(blockIdx.x % nsplit);
+  const int ch0 = split * NC;
+  const int M = a.B * S;
+  const int mtiles = (M + BM - 1) / BM;
+  const int m0 = tile * BM;
+  int* const flagsC = flags;
+  int* const err = flags + mtiles;
+  int* const flagsR = flags + mtiles + 1;
+  const int T = a.T;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmG) : "memory");
+    mbar_init(wfull, 1);
+    for (int i = 0; i < kMaxKch; ++i) mbar_init(&fullC[i], 1);
+    for (int i = 0; i < 2 * kMaxKch; ++i) mbar_init(&fullZR[i], 1);
+    mbar_init(rh_full, 1); mbar_init(h_full, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"((uint32_t)kTmemCols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== dependency waits + TMA producer =====================
+    if (lane == 0) {
+      mbar_expect_tx(wfull, (uint32_t)(9 * 3 * kch * kBwdTileBytes));
+      for (int tap = 0; tap < 9; ++tap) {
+        for (int kc = 0; kc < kch; ++kc)
+          tma_load_2d(wc + (tap * kch + kc) * kBwdTileBytes, &tmUcT, wfull, kc * BK, tap * Ch + ch0);
+        for (int kc = 0; kc < 2 * kch; ++kc)
+          tma_load_2d(wzr + (tap * 2 * kch + kc) * kBwdTileBytes, &tmUzrT, wfull, kc * BK, tap * Ch + ch0);
+      }
+    }
+    bool dead = false;
+    for (int it = 0; it < T; ++it) {
+      const int t = T - 1 - it;
+      const int row0 = t * M + m0 - (Wp + 1);          // the transposed taps reach Wp+1 rows back (negative: zero filled)
+      wait_tiles(flagsC, tile, mtiles, nsplit * (it + 1), err, lane, dead);
+      if (lane == 0) {
+        fence_proxy_async();
+        for (int kc = 0; kc < kch; ++kc) {
+          mbar_expect_tx(&fullC[kc], (uint32_t)(slab_rows * BK * 2));
+          tma_load_2d(slab + kc * kSlabBytes, &tmG, &fullC[kc], 2 * Ch + kc * BK, row0);
+        }
+      }
+      __syncwarp();
+      if (t == 0) break;                                // dL/dh_0 is not needed
+      wait_tiles(flagsR, tile, mtiles, nsplit * (it + 1), err, lane, dead);
+      if (lane == 0) {
+        fence_proxy_async();
+        for (int kc = 0; kc < 2 * kch; ++kc) {
+          mbar_expect_tx(&fullZR[kc], (uint32_t)(slab_rows * BK * 2));
+          tma_load_2d(slab + kc * kSlabBytes, &tmG, &fullZR[kc], kc * BK, row0);
+        }
+      }
+      __syncwarp();
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(NC >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+    mbar_wait(wfull, 0);
+    for (int it = 0; it < T; ++it) {
+      const int t = T - 1 - it;
+      const uint32_t par = (uint32_t)(it & 1);
+      for (int ph = 0; ph < 2; ++ph) {
+        if (ph == 1 && t == 0) break;
+        const int nk = ph == 0 ? kch : 2 * kch;
+        for (int kc = 0; kc < nk; ++kc) {
+          mbar_wait(ph == 0 ? &fullC[kc] : &fullZR[kc], par);
+          tc_fence_after();
+          if (lane == 0) {
+            for (int tap = 0; tap < 9; ++tap) {
+              const int off = 2 * (Wp + 1) - ((tap / 3) * Wp + (tap % 3));      // btap + (Wp+1), btap = Wp+1 - o
+              const uint64_t adesc = make_sdesc(smem_u32(slab + kc * kSlabBytes) + (uint32_t)off * (BK * 2));
+              const uint64_t bdesc = make_sdesc(smem_u32(ph == 0 ? wc + (tap * kch + kc) * kBwdTileBytes
+                                                                 : wzr + (tap * 2 * kch + kc) * kBwdTileBytes));
+#pragma unroll
+              for (int k = 0; k < BK / 16; ++k)
+                tc_mma_bf16(tmem_base + (uint32_t)(ph * 16), adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc,
+                            (kc | tap | k) ? 1u : 0u);
+            }
+            if (kc == nk - 1) tc_commit(ph == 0 ? rh_full : h_full);
+          }
+          __syncwarp();
+        }
+      }
+    }
+  } else {
+    // ===================== epilogue warps 2..5: one thread = one q-row, 16 channels =====================
+    using TA = __nv_bfloat16;
+    const int lg = warp & 3;
+    const int lrow = lg * 32 + lane;
+    const int m = m0 + lrow;
+    const bool inrange = m < M;
+    const int f = m / S, q = m - f * S;
+    const int y = q / Wp, x = q - y * Wp;
+    const bool valid = inrange && y < G && x < G;
+    const long long prow = (long long)m + Wp + 1;
+    const uint32_t tlane = tmem_base + ((uint32_t)(lg * 32) << 16);
+    const int threeCh = 3 * Ch;
+    (void)f;
+    auto ld16 = [&](const float* p, float* v) { ld8(p, v); ld8(p + 8, v + 8); };
+    float dhp[NC], hp[NC];          // dhpart ; h_{t-1} of the step being differentiated (Hf slab t)
+#pragma unroll
+    for (int j = 0; j < NC; ++j) { dhp[j] = 0.f; hp[j] = 0.f; }
+    // gate backward of one step given dh: writes dpre_z / dpre_c of step `ts` (its input state in hp_), dhpart = dh z
+    auto gates = [&](int ts, const float* dh, const float* hp_) {
+      const long long mt = (long long)ts * M + m;
+      float zz[NC], cc[NC], dz[NC], dc[NC];
+      ld16(a.Zs + mt * Ch + ch0, zz);
+      ld16(a.Cs + mt * Ch + ch0, cc);
+#pragma unroll
+      for (int j = 0; j < NC; ++j) {
+        dz[j] = dh[j] * (hp_[j] - cc[j]) * zz[j] * (1.0f - zz[j]);
+        dc[j] = dh[j] * (1.0f - zz[j]) * (1.0f - cc[j] * cc[j]);
+        dhp[j] = dh[j] * zz[j];
+      }
+      stbf16x16((TA*)a.dG + mt * threeCh + ch0, dz);
+      stbf16x16((TA*)a.dG + mt * threeCh + 2 * Ch + ch0, dc);
+    };
+    auto head_term = [&](int ts, float* hd) {          // dL/dh_{ts+1} through the head: dhs (x gamma alpha with the frozen BN)
+      ld16(a.dhs + ((long long)ts * M + m) * Ch + ch0, hd);
+      if (a.bn_gamma) {
+        float g16[NC];
+        ld16(a.bn_gamma + (long long)ts * Ch + ch0, g16);
+#pragma unroll
+        for (int j = 0; j < NC; ++j) hd[j] *= g16[j] * a.alpha;
+      }
+    };
+    // ---- prologue = rgp_gru_bwd_last: step T-1 has no recurrent gradient
+    if (valid) {
+      float dh[NC];
+      head_term(T - 1, dh);
+      ld16(a.Hf + ((long long)(T - 1) * M + prow) * Ch + ch0, hp);
+      gates(T - 1, dh, hp);
+    }
+    fence_proxy_async();
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    if (warp == 2 && lane == 0) { __threadfence(); red_release_add(flagsC + tile, 1); }
+    for (int it = 0; it < T; ++it) {
+      const int t = T - 1 - it;
+      const long long mt = (long long)t * M + m;
+      float rr[NC], hd[NC], hp1[NC];
+      if (valid) {
+        ld16(a.Rs + mt * Ch + ch0, rr);
+        if (t > 0) {
+          head_term(t - 1, hd);
+          ld16(a.Hf + ((long long)(t - 1) * M + prow) * Ch + ch0, hp1);
+        }
+      }
+      // ---------------- phase RH ----------------
+      mbar_wait(rh_full, (uint32_t)(it & 1));
+      tc_fence_after();
+      float acc[NC];
+      tc_ld16(tlane, acc);
+      tc_fence_before();
+      if (valid) {
+        float dr[NC];
+#pragma unroll
+        for (int j = 0; j < NC; ++j) {
+          dr[j] = acc[j] * hp[j] * rr[j] * (1.0f - rr[j]);
+          dhp[j] = fmaf(acc[j], rr[j], dhp[j]);
+        }
+        stbf16x16((TA*)a.dG + mt * threeCh + Ch + ch0, dr);
+      }
+      fence_proxy_async();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (warp == 2 && lane == 0) { __threadfence(); red_release_add(flagsR + tile, 1); }
+      if (t == 0) break;
+      // ---------------- phase H: full dL/dh_t, then the gates of step t-1 ----------------
+      mbar_wait(h_full, (uint32_t)(it & 1));
+      tc_fence_after();
+      tc_ld16(tlane + 16u, acc);
+      tc_fence_before();
+      if (valid) {
+        float dh[NC];
+#pragma unroll
+        for (int j = 0; j < NC; ++j) { dh[j] = acc[j] + dhp[j] + hd[j]; hp[j] = hp1[j]; }
+        gates(t - 1, dh, hp);
+      }
+      fence_proxy_async();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (warp == 2 && lane == 0) { __threadfence(); red_release_add(flagsC + tile, 1); }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)kTmemCols)
+                 : "memory");
+  }
+}
+
 int slab_rows_of(int G) { return (BM + 2 * (G + 1) + 2 + 7) & ~7; }
 
 bool shape_ok(int B, int G, int Ch) {
@@ -898,7 +1138,54 @@ int convlstm_seq_fwd(const rgp_lstm_seq_args& a, cudaStream_t s) {
 
 }  // namespace rgp
 
+namespace rgp {
+int convgru_seq_small_bwd(const rgp_gru_bwd_args& a, int* flags, cudaStream_t s) {
+  RGP_CHECK_ARG(a.dtype == 1, "rgp_convgru_seq_small_bwd: bf16 operands only (dtype=%d)", a.dtype);
+  RGP_CHECK_ARG(a.T > 0 && gru_small_ok(a.B, a.G, a.Ch), "rgp_convgru_seq_small_bwd: B=%d G=%d Ch=%d T=%d does not fit", a.B, a.G,
+                a.Ch, a.T);
+  RGP_CHECK_ARG(a.dG && a.UcT && a.UzrT && a.Zs && a.Rs && a.Cs && a.Hf && a.dhs && flags, "rgp_convgru_seq_small_bwd: null pointer%s", "");
+  RGP_CHECK_ARG(((uintptr_t)a.dG & 31) == 0 && ((uintptr_t)a.Zs & 31) == 0 && ((uintptr_t)a.Rs & 31) == 0 &&
+                ((uintptr_t)a.Cs & 31) == 0 && ((uintptr_t)a.Hf & 31) == 0 && ((uintptr_t)a.dhs & 31) == 0 &&
+                ((uintptr_t)a.bn_gamma & 31) == 0 && ((uintptr_t)a.UcT & 15) == 0 && ((uintptr_t)a.UzrT & 15) == 0,
+                "rgp_convgru_seq_small_bwd: buffers must be 32-byte aligned%s", "");
+  const int Ch = a.Ch, S = (a.G + 1) * (a.G + 1);
+  const int srows = slab_rows_of(a.G);
+  CUtensorMap tmG, tmUcT, tmUzrT;
+  int rc = tc::encode_map_bf16(a.dG, 3 * Ch, a.rowsG, (long long)3 * Ch * 2, BK, srows, &tmG);
+  if (rc) return rc;
+  rc = tc::encode_map_bf16(a.UcT, Ch, 9LL * Ch, (long long)Ch * 2, BK, NC, &tmUcT);
+  if (rc) return rc;
+  rc = tc::encode_map_bf16(a.UzrT, 2 * Ch, 9LL * Ch, (long long)2 * Ch * 2, BK, NC, &tmUzrT);
+  if (rc) return rc;
+  static PerDeviceFlag attr_set = {};
+  if (attr_set.need()) {
+    cudaError_t e = cudaFuncSetAttribute(gru_small_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytesGruBwd);
+    if (e != cudaSuccess) { set_error("gru_small_bwd: cudaFuncSetAttribute(smem=%d): %s", kSmemBytesGruBwd, cudaGetErrorString(e)); return -5; }
+    attr_set.set();
+  }
+  const int mtiles = (a.B * S + BM - 1) / BM;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)(mtiles * (Ch / NC)), 1, 1);
+  cfg.blockDim = dim3(NTHREADS, 1, 1);
+  cfg.dynamicSmemBytes = kSmemBytesGruBwd;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeCooperative;
+  attr[0].val.cooperative = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, gru_small_bwd_kernel, tmG, tmUcT, tmUzrT, a, flags, srows);
+  if (e != cudaSuccess) { set_error("gru_small_bwd launch: %s", cudaGetErrorString(e)); return -5; }
+  return check_launch("gru_small_bwd");
+}
+}  // namespace rgp
+
 extern "C" {
+
+int rgp_convgru_seq_small_bwd(const rgp_gru_bwd_args* a, int* flags, void* stream) {
+  RGP_CHECK_ARG(a != nullptr, "rgp_convgru_seq_small_bwd: null args%s", "");
+  return rgp::convgru_seq_small_bwd(*a, flags, (cudaStream_t)stream);
+}
 
 int rgp_convlstm_seq_fwd(const rgp_lstm_seq_args* a, void* stream) {
   RGP_CHECK_ARG(a != nullptr, "rgp_convlstm_seq_fwd: null args%s", "");

@@ -827,6 +827,22 @@ class GazeEngine(TrainStateMixin):
         lib.rgp_transpose_taps(self._ptr("Uc_op"), self.UcT.data_ptr(), 9, Ch, Ch, self.dtype, s)
         lib.rgp_transpose_taps(self._ptr("Uzr_op"), self.UzrT.data_ptr(), 9, 2 * Ch, Ch, self.dtype, s)
         self._mark("weight_transposes")
+        if self.use_seq_small:
+            # the whole reverse-time recurrence in ONE launch (rgp_convgru_seq_small_bwd: transposed weight slices resident in
+            # shared memory, dL/dh's direct part in registers, two counter exchanges per step)
+            lib.rgp_zero(self.seq_flags.data_ptr(), self.seq_flags.numel() * 4, s)
+            a = L.GruBwdArgs()
+            a.dG, a.rowsG = self.dG.data_ptr(), self.dG.shape[0]
+            a.UcT, a.UzrT = self.UcT.data_ptr(), self.UzrT.data_ptr()
+            a.Zs, a.Rs, a.Cs = self.Z.data_ptr(), self.Rs.data_ptr(), self.Cs.data_ptr()
+            a.Hf, a.dhs = self.Hf.data_ptr(), self.dhs.data_ptr()
+            a.bn_gamma = self._ptr("bn_gamma") if self.use_bn else 0
+            a.alpha = alpha
+            a.B, a.T, a.G, a.Ch, a.dtype = B, T, G, Ch, self.dtype
+            lib.rgp_convgru_seq_small_bwd(C.byref(a), self.seq_flags.data_ptr(), s)
+            self._mark("recurrence_bwd")
+            self._wgrad_gru_cell(g)
+            return
         # ---- recurrence, backwards in time: two tap GEMMs per step (mirror of the forward)
         gam = (lambda t: self._ptr("bn_gamma") + t * Ch * 4) if self.use_bn else (lambda t: 0)
         lib.rgp_gru_bwd_last(self._slab(self.dhs, T - 1), gam(T - 1), alpha, self.Z[T - 1].data_ptr(),
@@ -845,7 +861,12 @@ class GazeEngine(TrainStateMixin):
                            save_c=self.Cs[t - 1].data_ptr(), hprev_f32=self._slab(self.Hf, t - 1),
                            dg=self._slab(self.dG, t - 1), ldg=3 * Ch, **common, **extra)
         self._mark("recurrence_bwd")
-        # ---- weight gradients: contractions over all T*B*S rows at once
+        self._wgrad_gru_cell(g)
+
+    def _wgrad_gru_cell(self, g):
+        """weight gradients of the ConvGRU cell: contractions over all T*B*S rows at once"""
+        Ch, Cin = self.Ch, self.Cin
+        rowsT = self.T * self.B * self.S
         self._wgrad(self.dG.data_ptr(), 3 * Ch, 0, 2 * Ch, self.Hop.data_ptr(), self.Hop.shape[0], Ch, Ch, rowsT,
                     self.taps3, g("Uzr_op"))
         self._wgrad(self.dG.data_ptr(), 3 * Ch, 2 * Ch, Ch, self.RH.data_ptr(), self.RH.shape[0], Ch, Ch, rowsT,

@@ -65,6 +65,16 @@ class GruSeqArgs(C.Structure):
     ]
 
 
+class GruBwdArgs(C.Structure):
+    """Mirror of ``rgp_gru_bwd_args`` (include/rgp.h)."""
+    _fields_ = [
+        ("dG", _vp), ("rowsG", _ll), ("UcT", _vp), ("UzrT", _vp),
+        ("Zs", _vp), ("Rs", _vp), ("Cs", _vp), ("Hf", _vp), ("dhs", _vp),
+        ("bn_gamma", _vp), ("alpha", _f),
+        ("B", _i), ("T", _i), ("G", _i), ("Ch", _i), ("dtype", _i),
+    ]
+
+
 class LstmSeqArgs(C.Structure):
     """Mirror of ``rgp_lstm_seq_args`` (include/rgp.h)."""
     _fields_ = [
@@ -80,6 +90,7 @@ _SIGS = {
     "rgp_convgru_seq_fwd": [C.POINTER(GruSeqArgs), _vp],
     "rgp_convgru_seq_profile": [_vp, _i],
     "rgp_convgru_seq_small_fwd": [C.POINTER(GruSeqArgs), _vp, _vp],
+    "rgp_convgru_seq_small_bwd": [C.POINTER(GruBwdArgs), _vp, _vp],
     "rgp_convlstm_seq_fwd": [C.POINTER(LstmSeqArgs), _vp],
     "rgp_convlstm_seq_profile": [_vp, _i],
     "rgp_pack_c3d": [_vp, _vp, _i, _i, _i, _i, _i, _vp],

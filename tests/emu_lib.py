@@ -873,6 +873,44 @@ class EmuLib(object):
         fl[mt + 1:] += a.T * (a.Ch // 16)
         return rc
 
+    def rgp_convgru_seq_small_bwd(self, aref, flags, stream):
+        """reverse-time recurrence = rgp_gru_bwd_last + per step (BWD_RH tap-GEMM, BWD_H tap-GEMM), as engine.py issues them"""
+        a = aref._obj
+        B, T, G, Ch = a.B, a.T, a.G, a.Ch
+        Wp = G + 1
+        S = Wp * Wp
+        M = B * S
+        mt = (M + 127) // 128
+        fl = arr(flags, (2 * mt + 1,), np.int32)
+        assert not fl.any(), "the caller zeroes the counters before every launch"
+        dhpart = np.zeros((M, Ch), dtype=np.float32)
+        btaps = [Wp + 1 - (ky * Wp + kx) for ky in range(3) for kx in range(3)]
+        es = 4
+        gam = (lambda t: a.bn_gamma + t * Ch * 4) if a.bn_gamma else (lambda t: None)
+        slab = lambda base, t, width: base + t * M * width * 4
+        self.rgp_gru_bwd_last(slab(a.dhs, T - 1, Ch), gam(T - 1), a.alpha, slab(a.Zs, T - 1, Ch), slab(a.Cs, T - 1, Ch),
+                              slab(a.Hf, T - 1, Ch), slab(a.dG, T - 1, 3 * Ch), 3 * Ch, dhpart.ctypes.data, B, G, Ch, 0, stream)
+        for t in range(T - 1, -1, -1):
+            g = L.TapGemmArgs()
+            g.dtype, g.ntaps = 0, 9
+            for i, o in enumerate(btaps):
+                g.tap_off[i] = o
+            g.M, g.rowsA, g.lda, g.N, g.S, g.Wp, g.G, g.Ch = M, M, 3 * Ch, Ch, S, Wp, G, Ch
+            g.dhpart = dhpart.ctypes.data
+            g.A, g.K, g.Bw, g.epi = slab(a.dG, t, 3 * Ch) + 2 * Ch * es, Ch, a.UcT, L.EPI_BWD_RH
+            g.save_r, g.hprev_f32, g.dg, g.ldg = slab(a.Rs, t, Ch), slab(a.Hf, t, Ch), slab(a.dG, t, 3 * Ch), 3 * Ch
+            self.rgp_tapgemm(C.byref(g), stream)
+            if t > 0:
+                g.A, g.K, g.Bw, g.epi = slab(a.dG, t, 3 * Ch), 2 * Ch, a.UzrT, L.EPI_BWD_H
+                g.dhs, g.save_z, g.save_c = slab(a.dhs, t - 1, Ch), slab(a.Zs, t - 1, Ch), slab(a.Cs, t - 1, Ch)
+                g.hprev_f32, g.dg = slab(a.Hf, t - 1, Ch), slab(a.dG, t - 1, 3 * Ch)
+                if a.bn_gamma:
+                    g.bias, g.alpha = gam(t - 1), a.alpha
+                self.rgp_tapgemm(C.byref(g), stream)
+        fl[:mt] += T * (Ch // 16)
+        fl[mt + 1:] += T * (Ch // 16)
+        return 0
+
     def rgp_convlstm_seq_fits(self, B, G, Ch):
         tiles = (B * (G + 1) ** 2 + 127) // 128
         return 1 if (Ch % 16 == 0 and G <= 14 and tiles <= 16 * max(1, 148 // (Ch // 16))) else 0

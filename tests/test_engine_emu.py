@@ -150,3 +150,11 @@ def test_small_batch_persistent_convgru_orchestration_matches_per_step(G, B, mod
         outs.append((logits, eng.Z.numpy().copy(), eng.Rs.numpy().copy(), eng.Cs.numpy().copy(), eng.read_state().numpy().copy()))
     for x, y in zip(*outs):
         assert np.allclose(x, y, rtol=1e-6, atol=1e-7)
+
+
+@pytest.mark.parametrize("model", ["gaze_grcn", "gaze_grcn77"])
+def test_small_batch_persistent_bptt_wiring(model):
+    """engine -> rgp_convgru_seq_small_fwd + rgp_convgru_seq_small_bwd (one launch each for all T steps): gradients equal
+    torch autograd on the oracle."""
+    eng, _ = _grad_check(model, "c3d", seq="small", T=4)
+    assert eng.use_seq_small

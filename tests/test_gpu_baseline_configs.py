@@ -295,3 +295,43 @@ def test_small_batch_persistent_convgru_vs_per_step_and_oracle(model, G, B, T, t
         _report("reference_shape_grcn_B28_T42_Ch128_small_seq", max_map_err=float(err.max()), tol=2e-2,
                 map_err_per_t=[float(x) for x in err.max(axis=0)])
         assert err.max() <= 2e-2, err.max()
+
+
+@pytest.mark.parametrize("model,G,B,T", [("gaze_grcn", 7, 28, 42), ("gaze_grcn", 7, 3, 5), ("gaze_grcn77", 14, 4, 6),
+                                          ("gaze_grcn77", 7, 1, 1), ("gaze_grcn", 7, 36, 3)])
+def test_small_batch_persistent_bptt_vs_per_step_and_oracle(model, G, B, T):
+    """rgp_convgru_seq_small_bwd (reverse-time recurrence in one launch) against the per-step BPTT path on the same saved
+    forward - every gradient tensor - and at the reference's own training shape (28 x T = 42, hidden 128) against torch
+    autograd on the float64 oracle (bf16 bar of the BPTT tests: 5e-2 of each tensor's largest gradient)."""
+    Ch = 128
+    p = O.init_params(model, hidden=Ch, T=T, grid=G, seed=7, regime="S")
+    rng = np.random.RandomState(13)
+    emb = SY.make_embedded(rng, B, T, G, 512)
+    GH = 49 if model == "gaze_grcn" else G
+    gt, _ = SY.make_gazemaps(rng, B, T, GH, GH, normalize=True)
+    grads = []
+    for seq in (None, False):
+        eng = GazeEngine(model, B=B, T=T, G=G, Ch=Ch, dtype=1, device="cuda", train=True, seq=seq)
+        assert eng.use_seq_small == (seq is None)
+        eng.load_tf_params(p)
+        for _ in range(2):
+            eng.forward(emb=torch.from_numpy(emb).cuda(), gt=torch.from_numpy(gt).cuda())
+            eng.backward()
+        torch.cuda.synchronize()
+        assert not eng.seq_timed_out()
+        grads.append(eng.op_to_tf(eng.grads.cpu().numpy()))
+    a, b = grads
+    for k in b:
+        if k.startswith("proj_c3d") or k == "out_b":
+            continue
+        scale = np.abs(b[k]).max()
+        assert np.abs(a[k] - b[k]).max() <= 2e-2 * scale + 1e-12, (k, np.abs(a[k] - b[k]).max(), scale)
+    if T == 42:
+        _, _, _, ref = O.forward_loss_grads(model, p, gt.astype(np.float64), emb=emb.astype(np.float64))
+        worst = {}
+        for k, r in ref.items():
+            if k == "out_b":
+                continue
+            worst[k] = float(np.abs(a[k].reshape(r.shape) - r).max() / max(np.abs(r).max(), 1e-30))
+            assert worst[k] <= 5e-2, (k, worst[k])
+        _report("reference_shape_grcn_B28_T42_Ch128_small_bptt", **worst)
