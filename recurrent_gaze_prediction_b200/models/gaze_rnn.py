@@ -372,6 +372,11 @@ class GazePredictionGRU(ModelBase):
         if self._loss_pending:
             self._loss_event.synchronize()
             self._last_loss, self._loss_pending = float(self._loss_host[0]), False
+            # the persistent small-batch kernels never hang: a dependency wait that gives up is reported through a counter
+            # and the pass is invalid - fail loudly where the loss is read (one 4-byte read, already synchronised)
+            timed_out = getattr(self.engine, "seq_timed_out", None)
+            if timed_out is not None and timed_out():
+                raise RuntimeError("a persistent recurrence kernel timed out waiting for a neighbouring tile; results invalid")
         return self._last_loss
 
     @last_loss.setter

@@ -46,9 +46,28 @@ elif case == "cfg4b8":
     emb = torch.from_numpy(SY.make_embedded(rng, B, T, G, 512)).cuda()
     for _ in range(iters):
         eng.forward(emb=emb)
-elif case == "cascade":
+elif case == "refshape":      # the reference's own training shape: small-batch persistent ConvGRU forward + BPTT kernels
+    B, T = 28, 42
+    eng = GazeEngine("gaze_grcn", B=B, T=T, Ch=128, dtype=1, device="cuda", train=True)
+    assert eng.use_seq_small
+    eng.load_tf_params(init_parameters("gaze_grcn", hidden=128, T=T, seed=0))
+    c3d = torch.from_numpy(tiled(SY.make_c3d(rng, 4, T), B)).to(torch.bfloat16).cuda()
+    gt = torch.from_numpy(tiled(SY.make_gazemaps(rng, 4, T, 49, 49, normalize=True)[0], B)).cuda()
+    for _ in range(iters):
+        eng.forward(c3d=c3d, gt=gt)
+        eng.backward()
+elif case == "cfg4b64":
+    B, T, G = 64, 32, 14
+    p = dict(init_parameters("gaze_lstm", hidden=128, T=T, grid=G, seed=0))
+    p["out_W"] = np.random.RandomState(7).uniform(-0.1, 0.1, (128, 1)).astype(np.float32)
+    eng = GazeEngine("gaze_lstm", B=B, T=T, G=G, Ch=128, dtype=1, device="cuda", head="fc")
+    eng.load_tf_params(p)
+    emb = torch.from_numpy(SY.make_embedded(rng, B, T, G, 512)).cuda()
+    for _ in range(iters):
+        eng.forward(emb=emb)
+elif case in ("cascade", "cascade2"):
     from recurrent_gaze_prediction_b200.cascade_engine import CascadeEngine
-    B, T = 32, 35
+    B, T = (32, 35) if case == "cascade" else (16, 8)
     eng = CascadeEngine(B=B, T=T, dtype=1, device="cuda")
     eng.load_tf_params(init_parameters_cascade(seed=0))
     c3d = torch.from_numpy(tiled(SY.make_c3d(rng, 8, T), B)).to(torch.bfloat16).cuda()
