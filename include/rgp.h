@@ -132,6 +132,11 @@ int rgp_convgru_seq_profile(unsigned long long* host_out, int n);
  * workspace of 2 * mtiles + 1 int32, ZEROED by the caller before every launch (flags[mtiles] != 0 afterwards = time-out). */
 int rgp_convgru_seq_small_fwd(const rgp_gru_seq_args* a, int* flags, void* stream);
 int rgp_convgru_seq_small_fits(int B, int G, int Ch);
+/* Workspace queries (no hidden allocation - the library never calls cudaMalloc).  Bytes of the int32 counter
+ * workspace `flags` the persistent small-batch kernels need (zeroed by the caller before every launch); every other
+ * entry point works in place on caller-owned buffers and needs no workspace (0). */
+long long rgp_convgru_seq_small_workspace_bytes(int B, int G);   /* forward and BPTT: 2 * mtiles + 1 counters */
+long long rgp_convlstm_seq_workspace_bytes(int B, int G);        /* mtiles + 1 counters */
 /* ... and its reverse-time mirror: BPTT through the T ConvGRU steps (tf.gradients of gaze_grcn.py:108-127, base.py:278-281)
  * in ONE launch - what the per-step path does with rgp_gru_bwd_last + 2 rgp_tapgemm (RGP_EPI_BWD_RH / RGP_EPI_BWD_H) per step.
  * Fills dG [T*M, 3Ch] (operand dtype, q-layout, columns dpre_z | dpre_r | dpre_c) for the weight-gradient contractions. */

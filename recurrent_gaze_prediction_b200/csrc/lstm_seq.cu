@@ -1197,6 +1197,16 @@ int rgp_convgru_seq_small_fwd(const rgp_gru_seq_args* a, int* flags, void* strea
   return rgp::convgru_seq_small_fwd(*a, flags, (cudaStream_t)stream);
 }
 
+long long rgp_convgru_seq_small_workspace_bytes(int B, int G) {
+  const long long mtiles = ((long long)B * (G + 1) * (G + 1) + 127) / 128;
+  return (2 * mtiles + 1) * (long long)sizeof(int);
+}
+
+long long rgp_convlstm_seq_workspace_bytes(int B, int G) {
+  const long long mtiles = ((long long)B * (G + 1) * (G + 1) + 127) / 128;
+  return (mtiles + 1) * (long long)sizeof(int);
+}
+
 int rgp_convgru_seq_small_fits(int B, int G, int Ch) { return rgp::lstmseq::gru_small_ok(B, G, Ch) ? 1 : 0; }
 
 int rgp_convlstm_seq_fits(int B, int G, int Ch) { return rgp::lstmseq::shape_ok(B, G, Ch) ? 1 : 0; }

@@ -418,11 +418,15 @@ class GazeEngine(TrainStateMixin):
         if self.lstm:
             self.Cf = z(self.rows_step, Ch)
             self.Hconv = z(B * S, 3 * Ch)
-            self.seq_flags = torch.zeros((B * S + 127) // 128 + 1, dtype=torch.int32, device=dev)
+            wsb = getattr(self.lib, "rgp_convlstm_seq_workspace_bytes", None)
+            nflag = (wsb(B, self.G) // 4) if wsb is not None else (B * S + 127) // 128 + 1
+            self.seq_flags = torch.zeros(nflag, dtype=torch.int32, device=dev)
             self.Lsave = z(T, B * S, 5 * Ch) if self.train else None
         else:
             self.RH = z(nsl * B * S + self.tail, Ch, dt=tdt)
-            self.seq_flags = torch.zeros(2 * ((B * S + 127) // 128) + 1, dtype=torch.int32, device=dev)
+            wsb = getattr(self.lib, "rgp_convgru_seq_small_workspace_bytes", None)
+            nflag = (wsb(B, self.G) // 4) if wsb is not None else 2 * ((B * S + 127) // 128) + 1
+            self.seq_flags = torch.zeros(nflag, dtype=torch.int32, device=dev)
             self.Z = z(nsl, B * S, Ch)
             self.Rs = z(T, B * S, Ch) if self.train else None
             self.Cs = z(T, B * S, Ch) if self.train else None

@@ -170,6 +170,9 @@ class RgpLib(object):
         self._dll.rgp_convlstm_seq_fits.argtypes = [_i, _i, _i]
         self._dll.rgp_convgru_seq_small_fits.restype = _i
         self._dll.rgp_convgru_seq_small_fits.argtypes = [_i, _i, _i]
+        for nm in ("rgp_convgru_seq_small_workspace_bytes", "rgp_convlstm_seq_workspace_bytes"):
+            getattr(self._dll, nm).restype = _ll
+            getattr(self._dll, nm).argtypes = [_i, _i]
         for name, sig in _SIGS.items():
             fn = getattr(self._dll, name)
             fn.argtypes = sig
@@ -205,9 +208,16 @@ class RgpLib(object):
         """a predicate: 1 if the small-batch persistent ConvGRU kernel can hold this shape"""
         return int(self._dll.rgp_convgru_seq_small_fits(B, G, Ch))
 
+    def rgp_convgru_seq_small_workspace_bytes(self, B, G):
+        return int(self._dll.rgp_convgru_seq_small_workspace_bytes(B, G))
+
+    def rgp_convlstm_seq_workspace_bytes(self, B, G):
+        return int(self._dll.rgp_convlstm_seq_workspace_bytes(B, G))
+
     def symbols(self):
         return sorted(list(_SIGS) + ["rgp_last_error", "rgp_version", "rgp_has_tcgen05", "rgp_metrics_fused_fits",
-                                     "rgp_convlstm_seq_fits", "rgp_convgru_seq_small_fits"])
+                                     "rgp_convlstm_seq_fits", "rgp_convgru_seq_small_fits", "rgp_convgru_seq_small_workspace_bytes",
+                                     "rgp_convlstm_seq_workspace_bytes"])
 
 
 _LIB = None
