@@ -186,6 +186,25 @@ int rgp_convlstm_seq_fits(int B, int G, int Ch);
  * HOST array of n <= 32*8 values laid out [step][event] (events listed in csrc/lstm_seq.cu).  Synchronises the device. */
 int rgp_convlstm_seq_profile(unsigned long long* host_out, int n);
 
+/* BPTT mirror of rgp_convlstm_seq_fwd for the co-resident regime (tiles * Ch/16 <= SMs; rgp_convgru_seq_small_fits): the gate
+ * backward of every step (rgp_lstm_gates_bwd's arithmetic, gaze_lstm.py:112-133 as written) and the transposed hidden
+ * convolution dh_{t-1} = conv^T(dHc_t; W_hi | W_hf | W_ho) for all T steps in ONE launch; fills dG4 and dHc for the weight-
+ * gradient contractions and ACCUMULATES the peephole gradients (once per row, at the end). */
+typedef struct rgp_lstm_bwd_args {
+  void* dHc; long long rowsHc;    /* [T*B*S, 3Ch] bf16 q-layout: d(hidden conv outputs) (i+c) | f | o                     */
+  void* dG4;                      /* [T*B*S, 4Ch] bf16 q-layout: d(pre-activations) i | f | c | o                         */
+  const void* WhT;                /* [9*Ch, 3Ch] bf16: rgp_transpose_taps of Wh (row tap*Ch + in channel, K = 3Ch)        */
+  const float* save;              /* [T, B*S, 5Ch] fp32: (i, f, g, o, c_{t-1}) stored by the forward pass                 */
+  const float* Cf;                /* fp32 p-layout cell after the last step (c_T)                                         */
+  const float* dhs;               /* [T*B*S, Ch] fp32 q-layout: dL/d(head input)                                          */
+  const float* wci; const float* wcf; const float* wco;   /* peepholes [G, G, Ch]                                         */
+  float* gwci; float* gwcf; float* gwco;                  /* their gradients, accumulated                                 */
+  int B, T, G, Ch;
+  int dtype;                      /* must be 1                                                                            */
+} rgp_lstm_bwd_args;
+/* flags: rgp_convlstm_seq_workspace_bytes(B, G) of int32, zeroed by the caller before every launch */
+int rgp_convlstm_seq_small_bwd(const rgp_lstm_bwd_args* a, int* flags, void* stream);
+
 /* ---- model path ------------------------------------------------------------------------- */
 /* gaze_grcn.py:225-227 (tf.transpose NCHW->NHWC of the C3D blob) fused with the fp32->operand
  * cast and the [B,T]->time-major reorder: c3d [B,T,C,P] fp32 -> out [(t*B+b)*P + p, C]. */

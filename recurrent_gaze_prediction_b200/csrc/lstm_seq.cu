@@ -1018,6 +1018,214 @@ gru_small_bwd_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_const
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Small-batch persistent ConvLSTM BPTT (tf.gradients of gaze_lstm.py:112-133 as written), the reverse-time mirror of
+// lstm_seq_kernel: all T steps in one launch.  CTA (tile, split) owns 128 q-rows x 16 channels: the gate backward of its
+// channels (rgp_lstm_gates_bwd's arithmetic) with dL/dc in registers and the peephole gradients accumulated per row in
+// shared memory for the whole sequence (3 x 16 atomics per row at the END instead of per step), and 16 INPUT channels of
+// the transposed hidden convolution dh_{t-1} = conv^T(dHc_t ; [W_hi|W_hf|W_ho]), K = 3Ch, whose weight slice (9 taps x
+// 3Ch/64 x 16 rows = 110 KB at hidden 128) is resident.  dHc_t [M, 3Ch] is exchanged through the per-tile counters; its
+// slab is loaded in halves of three k-chunks (shared memory: 110 KB weights + 60 KB slab + 48 KB peepholes / gradients).
+// ---------------------------------------------------------------------------------------------------------------------
+constexpr int kLbHalfKc = 3;
+constexpr int kSmemLbW = 9 * 3 * kMaxKch * kBwdTileBytes;                 // 110592
+constexpr int kSmemLbSlab = kLbHalfKc * kSlabBytes;                       // 61440
+constexpr int kSmemBytesLstmBwd = kSmemLbW + kSmemLbSlab + 2 * kSmemPeep + 256 + 1024;
+
+__global__ void __launch_bounds__(NTHREADS, 1)
+lstm_small_bwd_kernel(const __grid_constant__ CUtensorMap tmHc, const __grid_constant__ CUtensorMap tmWhT,
+                      const rgp_lstm_bwd_args a, int* const flags, const int slab_rows) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int Ch = a.Ch, G = a.G, Wp = G + 1, S = Wp * Wp, T = a.T;
+  const int kch3 = 3 * Ch / BK;                                  // k-chunks of K = 3Ch
+  const int nh = (kch3 + kLbHalfKc - 1) / kLbHalfKc;             // slab halves per step
+  uint8_t* wsm = smem;                                           // [tap][kc < kch3] 16 rows x 128 B
+  uint8_t* slab = smem + kSmemLbW;                               // [kc < 3]
+  float* peep = reinterpret_cast<float*>(smem + kSmemLbW + kSmemLbSlab);   // [gate][channel][row]
+  float* gacc = peep + 3 * NC * BM;                              // peephole gradients of this row, same layout
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kSmemLbW + kSmemLbSlab + 2 * kSmemPeep);
+  uint64_t* wfull = bars;
+  uint64_t* fullA = bars + 1;                                    // [3]
+  uint64_t* half_free = fullA + kLbHalfKc;
+  uint64_t* acc_full = half_free + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nsplit = Ch / NC;
+  const int tile = (int)(blockIdx.x / nsplit), split = (int)(blockIdx.x % nsplit);
+  const int ch0 = split * NC;
+  const int M = a.B * S;
+  const int mtiles = (M + BM - 1) / BM;
+  const int m0 = tile * BM;
+  int* const err = flags + mtiles;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmHc) : "memory");
+    mbar_init(wfull, 1);
+    for (int i = 0; i < kLbHalfKc; ++i) mbar_init(&fullA[i], 1);
+    mbar_init(half_free, 1); mbar_init(acc_full, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"((uint32_t)kTmemCols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== dependency wait + TMA producer (steps T-1 .. 1 need the transposed conv) =====================
+    if (lane == 0) {
+      mbar_expect_tx(wfull, (uint32_t)(9 * kch3 * kBwdTileBytes));
+      for (int tap = 0; tap < 9; ++tap)
+        for (int kc = 0; kc < kch3; ++kc)
+          tma_load_2d(wsm + (tap * kch3 + kc) * kBwdTileBytes, &tmWhT, wfull, kc * BK, tap * Ch + ch0);
+    }
+    bool dead = false;
+    long long u = 0;                                   // slab fills so far
+    for (int it = 0; it + 1 < T; ++it) {
+      const int t = T - 1 - it;
+      const int row0 = t * M + m0 - (Wp + 1);
+      wait_tiles(flags, tile, mtiles, nsplit * (it + 1), err, lane, dead);
+      for (int hh = 0; hh < nh; ++hh, ++u) {
+        if (lane == 0) {
+          if (u > 0) mbar_wait(half_free, (uint32_t)((u - 1) & 1));       // the MMAs that read the previous fill are done
+          fence_proxy_async();
+          const int nk = min(kLbHalfKc, kch3 - hh * kLbHalfKc);
+          for (int kc = 0; kc < nk; ++kc) {
+            mbar_expect_tx(&fullA[kc], (uint32_t)(slab_rows * BK * 2));
+            tma_load_2d(slab + kc * kSlabBytes, &tmHc, &fullA[kc], (hh * kLbHalfKc + kc) * BK, row0);
+          }
+        }
+        __syncwarp();
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(NC >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+    mbar_wait(wfull, 0);
+    long long u = 0;
+    for (int it = 0; it + 1 < T; ++it) {
+      for (int hh = 0; hh < nh; ++hh, ++u) {
+        const int nk = min(kLbHalfKc, kch3 - hh * kLbHalfKc);
+        for (int kc = 0; kc < nk; ++kc) {
+          mbar_wait(&fullA[kc], (uint32_t)(u & 1));
+          tc_fence_after();
+          if (lane == 0) {
+            for (int tap = 0; tap < 9; ++tap) {
+              const int off = 2 * (Wp + 1) - ((tap / 3) * Wp + (tap % 3));
+              const uint64_t adesc = make_sdesc(smem_u32(slab + kc * kSlabBytes) + (uint32_t)off * (BK * 2));
+              const uint64_t bdesc = make_sdesc(smem_u32(wsm + (tap * kch3 + hh * kLbHalfKc + kc) * kBwdTileBytes));
+#pragma unroll
+              for (int k = 0; k < BK / 16; ++k)
+                tc_mma_bf16(tmem_base, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (hh | kc | tap | k) ? 1u : 0u);
+            }
+            if (kc == nk - 1) {
+              tc_commit(half_free);
+              if (hh == nh - 1) tc_commit(acc_full);
+            }
+          }
+          __syncwarp();
+        }
+      }
+    }
+  } else {
+    // ===================== epilogue warps 2..5: gate backward, one thread = one q-row x 16 channels =====================
+    using TA = __nv_bfloat16;
+    const int lg = warp & 3;
+    const int lrow = lg * 32 + lane;
+    const int m = m0 + lrow;
+    const bool inrange = m < M;
+    const int f = m / S, q = m - f * S;
+    const int y = q / Wp, x = q - y * Wp;
+    const bool valid = inrange && y < G && x < G;
+    const long long prow = (long long)m + Wp + 1;
+    const uint32_t tlane = tmem_base + ((uint32_t)(lg * 32) << 16);
+    (void)f;
+    auto ld16 = [&](const float* p, float* v) { ld8(p, v); ld8(p + 8, v + 8); };
+    const int pidx = y * G + x;
+    {
+      const float* pw[3] = {a.wci, a.wcf, a.wco};
+#pragma unroll
+      for (int g = 0; g < 3; ++g)
+#pragma unroll
+        for (int j = 0; j < NC; ++j) {
+          peep[(g * NC + j) * BM + lrow] = valid ? pw[g][(long long)pidx * Ch + ch0 + j] : 0.f;
+          gacc[(g * NC + j) * BM + lrow] = 0.f;
+        }
+    }
+    float dc[NC], cn[NC];
+#pragma unroll
+    for (int j = 0; j < NC; ++j) { dc[j] = 0.f; cn[j] = 0.f; }
+    if (valid) ld16(a.Cf + prow * Ch + ch0, cn);                    // c_T: the cell the forward pass left behind
+    for (int it = 0; it < T; ++it) {
+      const int t = T - 1 - it;
+      const long long mt = (long long)t * M + m;
+      float gi[NC], gf[NC], gg[NC], go[NC], cp[NC], dh[NC];
+      if (valid) {
+        const float* sv = a.save + mt * 5 * Ch + ch0;
+        ld16(sv, gi); ld16(sv + Ch, gf); ld16(sv + 2 * Ch, gg); ld16(sv + 3 * Ch, go); ld16(sv + 4 * Ch, cp);
+        ld16(a.dhs + mt * Ch + ch0, dh);
+      }
+      if (it > 0) {                                                 // dL/dh_t through the hidden convolutions of step t+1
+        mbar_wait(acc_full, (uint32_t)((it - 1) & 1));
+        tc_fence_after();
+        float acc[NC];
+        tc_ld16(tlane, acc);
+        tc_fence_before();
+#pragma unroll
+        for (int j = 0; j < NC; ++j) dh[j] += acc[j];
+      }
+      if (valid) {
+        float dpi[NC], dpf[NC], dpg[NC], dpo[NC], dic[NC];
+#pragma unroll
+        for (int j = 0; j < NC; ++j) {
+          const float tc = tanhf(cn[j]);
+          const float dcn = dc[j] + dh[j] * go[j] * (1.0f - tc * tc);
+          dpo[j] = dh[j] * tc * go[j] * (1.0f - go[j]);
+          dpi[j] = dcn * gg[j] * gi[j] * (1.0f - gi[j]);
+          dpg[j] = dcn * gi[j] * (1.0f - gg[j] * gg[j]);
+          dpf[j] = dcn * cp[j] * gf[j] * (1.0f - gf[j]);
+          dc[j] = dcn * gf[j] + dpi[j] * peep[(0 * NC + j) * BM + lrow] + dpf[j] * peep[(1 * NC + j) * BM + lrow] +
+                  dpo[j] * peep[(2 * NC + j) * BM + lrow];
+          gacc[(0 * NC + j) * BM + lrow] += dpi[j] * cp[j];
+          gacc[(1 * NC + j) * BM + lrow] += dpf[j] * cp[j];
+          gacc[(2 * NC + j) * BM + lrow] += dpo[j] * cp[j];
+          dic[j] = dpi[j] + dpg[j];
+          cn[j] = cp[j];                                            // c_{t-1} is the next iteration's c_t
+        }
+        TA* hc = (TA*)a.dHc + mt * 3 * Ch + ch0;
+        stbf16x16(hc, dic); stbf16x16(hc + Ch, dpf); stbf16x16(hc + 2 * Ch, dpo);
+        TA* g4 = (TA*)a.dG4 + mt * 4 * Ch + ch0;
+        stbf16x16(g4, dpi); stbf16x16(g4 + Ch, dpf); stbf16x16(g4 + 2 * Ch, dpg); stbf16x16(g4 + 3 * Ch, dpo);
+      }
+      fence_proxy_async();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (warp == 2 && lane == 0) { __threadfence(); red_release_add(flags + tile, 1); }
+    }
+    if (valid) {
+      float* gw[3] = {a.gwci, a.gwcf, a.gwco};
+#pragma unroll
+      for (int g = 0; g < 3; ++g)
+#pragma unroll
+        for (int j = 0; j < NC; ++j) atomicAdd(gw[g] + (long long)pidx * Ch + ch0 + j, gacc[(g * NC + j) * BM + lrow]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)kTmemCols)
+                 : "memory");
+  }
+}
+
 int slab_rows_of(int G) { return (BM + 2 * (G + 1) + 2 + 7) & ~7; }
 
 bool shape_ok(int B, int G, int Ch) {
@@ -1180,7 +1388,52 @@ int convgru_seq_small_bwd(const rgp_gru_bwd_args& a, int* flags, cudaStream_t s)
 }
 }  // namespace rgp
 
+namespace rgp {
+int convlstm_seq_small_bwd(const rgp_lstm_bwd_args& a, int* flags, cudaStream_t s) {
+  RGP_CHECK_ARG(a.dtype == 1, "rgp_convlstm_seq_small_bwd: bf16 operands only (dtype=%d)", a.dtype);
+  RGP_CHECK_ARG(a.T > 0 && gru_small_ok(a.B, a.G, a.Ch), "rgp_convlstm_seq_small_bwd: B=%d G=%d Ch=%d T=%d does not fit", a.B, a.G,
+                a.Ch, a.T);
+  RGP_CHECK_ARG(a.dHc && a.dG4 && a.WhT && a.save && a.Cf && a.dhs && a.wci && a.wcf && a.wco && a.gwci && a.gwcf && a.gwco && flags,
+                "rgp_convlstm_seq_small_bwd: null pointer%s", "");
+  RGP_CHECK_ARG(((uintptr_t)a.dHc & 31) == 0 && ((uintptr_t)a.dG4 & 31) == 0 && ((uintptr_t)a.save & 31) == 0 &&
+                ((uintptr_t)a.Cf & 31) == 0 && ((uintptr_t)a.dhs & 31) == 0 && ((uintptr_t)a.WhT & 15) == 0,
+                "rgp_convlstm_seq_small_bwd: buffers must be 32-byte aligned%s", "");
+  const int Ch = a.Ch, S = (a.G + 1) * (a.G + 1);
+  const int srows = slab_rows_of(a.G);
+  CUtensorMap tmHc, tmWhT;
+  int rc = tc::encode_map_bf16(a.dHc, 3 * Ch, a.rowsHc, (long long)3 * Ch * 2, BK, srows, &tmHc);
+  if (rc) return rc;
+  rc = tc::encode_map_bf16(a.WhT, 3 * Ch, 9LL * Ch, (long long)3 * Ch * 2, BK, NC, &tmWhT);
+  if (rc) return rc;
+  static PerDeviceFlag attr_set = {};
+  if (attr_set.need()) {
+    cudaError_t e = cudaFuncSetAttribute(lstm_small_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytesLstmBwd);
+    if (e != cudaSuccess) { set_error("lstm_small_bwd: cudaFuncSetAttribute(smem=%d): %s", kSmemBytesLstmBwd, cudaGetErrorString(e)); return -5; }
+    attr_set.set();
+  }
+  const int mtiles = (a.B * S + BM - 1) / BM;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)(mtiles * (Ch / NC)), 1, 1);
+  cfg.blockDim = dim3(NTHREADS, 1, 1);
+  cfg.dynamicSmemBytes = kSmemBytesLstmBwd;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeCooperative;
+  attr[0].val.cooperative = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, lstm_small_bwd_kernel, tmHc, tmWhT, a, flags, srows);
+  if (e != cudaSuccess) { set_error("lstm_small_bwd launch: %s", cudaGetErrorString(e)); return -5; }
+  return check_launch("lstm_small_bwd");
+}
+}  // namespace rgp
+
 extern "C" {
+
+int rgp_convlstm_seq_small_bwd(const rgp_lstm_bwd_args* a, int* flags, void* stream) {
+  RGP_CHECK_ARG(a != nullptr, "rgp_convlstm_seq_small_bwd: null args%s", "");
+  return rgp::convlstm_seq_small_bwd(*a, flags, (cudaStream_t)stream);
+}
 
 int rgp_convgru_seq_small_bwd(const rgp_gru_bwd_args* a, int* flags, void* stream) {
   RGP_CHECK_ARG(a != nullptr, "rgp_convgru_seq_small_bwd: null args%s", "");

@@ -888,6 +888,20 @@ class GazeEngine(TrainStateMixin):
         rowsT = T * M
         lib.rgp_transpose_taps(self._ptr("Wh_op"), self.WhT.data_ptr(), 9, 3 * Ch, Ch, self.dtype, s)
         self._mark("weight_transposes")
+        gfits = getattr(lib, "rgp_convgru_seq_small_fits", None)
+        if self.use_seq_lstm and gfits is not None and gfits(B, G, Ch) and hasattr(lib, "rgp_convlstm_seq_small_bwd"):
+            # the whole reverse-time recurrence in ONE launch (co-resident regime)
+            lib.rgp_zero(self.seq_flags.data_ptr(), self.seq_flags.numel() * 4, s)
+            a = L.LstmBwdArgs()
+            a.dHc, a.rowsHc, a.dG4, a.WhT = self.dHc.data_ptr(), self.dHc.shape[0], self.dG.data_ptr(), self.WhT.data_ptr()
+            a.save, a.Cf, a.dhs = self.Lsave.data_ptr(), self.Cf.data_ptr(), self.dhs.data_ptr()
+            a.wci, a.wcf, a.wco = self._ptr("wci"), self._ptr("wcf"), self._ptr("wco")
+            a.gwci, a.gwcf, a.gwco = g("wci"), g("wcf"), g("wco")
+            a.B, a.T, a.G, a.Ch, a.dtype = B, T, G, Ch, self.dtype
+            lib.rgp_convlstm_seq_small_bwd(C.byref(a), self.seq_flags.data_ptr(), s)
+            self._mark("recurrence_bwd")
+            self._wgrad_lstm_cell(g)
+            return
         for t in range(T - 1, -1, -1):
             last = 1 if t == T - 1 else 0
             lib.rgp_lstm_gates_bwd(self.Lsave[t].data_ptr(), 0 if last else self.Lsave[t + 1].data_ptr(),
@@ -899,6 +913,11 @@ class GazeEngine(TrainStateMixin):
                 self._gemm(A=self._slab(self.dHc, t), rowsA=M, lda=3 * Ch, K=3 * Ch, Bw=self.WhT.data_ptr(), M=M, N=Ch,
                            taps=btaps, epi=L.EPI_STORE_F32, out_f32=self.dhrec.data_ptr(), ldo=Ch, S=S, Wp=Wp, G=G)
         self._mark("recurrence_bwd")
+        self._wgrad_lstm_cell(g)
+
+    def _wgrad_lstm_cell(self, g):
+        Ch, Cin = self.Ch, self.Cin
+        rowsT = self.T * self.B * self.S
         self._wgrad(self.dHc.data_ptr(), 3 * Ch, 0, 3 * Ch, self.Hop.data_ptr(), self.Hop.shape[0], Ch, Ch, rowsT,
                     self.taps3, g("Wh_op"))
         self._wgrad(self.dG.data_ptr(), 4 * Ch, 0, 4 * Ch, self.Xp.data_ptr(), self.Xp.shape[0], Cin, Cin, rowsT,

@@ -75,6 +75,15 @@ class GruBwdArgs(C.Structure):
     ]
 
 
+class LstmBwdArgs(C.Structure):
+    """Mirror of ``rgp_lstm_bwd_args`` (include/rgp.h)."""
+    _fields_ = [
+        ("dHc", _vp), ("rowsHc", _ll), ("dG4", _vp), ("WhT", _vp), ("save", _vp), ("Cf", _vp), ("dhs", _vp),
+        ("wci", _vp), ("wcf", _vp), ("wco", _vp), ("gwci", _vp), ("gwcf", _vp), ("gwco", _vp),
+        ("B", _i), ("T", _i), ("G", _i), ("Ch", _i), ("dtype", _i),
+    ]
+
+
 class LstmSeqArgs(C.Structure):
     """Mirror of ``rgp_lstm_seq_args`` (include/rgp.h)."""
     _fields_ = [
@@ -93,6 +102,7 @@ _SIGS = {
     "rgp_convgru_seq_small_bwd": [C.POINTER(GruBwdArgs), _vp, _vp],
     "rgp_convlstm_seq_fwd": [C.POINTER(LstmSeqArgs), _vp],
     "rgp_convlstm_seq_profile": [_vp, _i],
+    "rgp_convlstm_seq_small_bwd": [C.POINTER(LstmBwdArgs), _vp, _vp],
     "rgp_pack_c3d": [_vp, _vp, _i, _i, _i, _i, _i, _vp],
     "rgp_pack_c3d_src": [_vp, _i, _vp, _i, _i, _i, _i, _i, _vp],
     "rgp_pack_emb": [_vp, _vp, _i, _i, _i, _i, _i, _vp],

@@ -911,6 +911,36 @@ class EmuLib(object):
         fl[mt + 1:] += T * (Ch // 16)
         return 0
 
+    def rgp_convlstm_seq_small_bwd(self, aref, flags, stream):
+        """reverse-time ConvLSTM recurrence = per step rgp_lstm_gates_bwd + the conv^T tap-GEMM, as engine.py issues them"""
+        a = aref._obj
+        B, T, G, Ch = a.B, a.T, a.G, a.Ch
+        Wp = G + 1
+        S = Wp * Wp
+        M = B * S
+        mt = (M + 127) // 128
+        fl = arr(flags, (mt + 1,), np.int32)
+        assert not fl.any(), "the caller zeroes the counters before every launch"
+        dhrec = np.zeros((M, Ch), dtype=np.float32)
+        dc = np.zeros((M, Ch), dtype=np.float32)
+        btaps = [Wp + 1 - (ky * Wp + kx) for ky in range(3) for kx in range(3)]
+        for t in range(T - 1, -1, -1):
+            last = 1 if t == T - 1 else 0
+            self.rgp_lstm_gates_bwd(a.save + t * M * 5 * Ch * 4, 0 if last else a.save + (t + 1) * M * 5 * Ch * 4, a.Cf,
+                                    a.dhs + t * M * Ch * 4, dhrec.ctypes.data, dc.ctypes.data, a.wci, a.wcf, a.wco,
+                                    a.dG4 + t * M * 4 * Ch * 4, a.dHc + t * M * 3 * Ch * 4, a.gwci, a.gwcf, a.gwco, B, G, Ch,
+                                    last, 0, stream)
+            if t > 0:
+                g = L.TapGemmArgs()
+                g.dtype, g.ntaps = 0, 9
+                for i, o in enumerate(btaps):
+                    g.tap_off[i] = o
+                g.A, g.rowsA, g.lda, g.K, g.Bw, g.M, g.N = a.dHc + t * M * 3 * Ch * 4, M, 3 * Ch, 3 * Ch, a.WhT, M, Ch
+                g.epi, g.out_f32, g.ldo, g.S, g.Wp, g.G = L.EPI_STORE_F32, dhrec.ctypes.data, Ch, S, Wp, G
+                self.rgp_tapgemm(C.byref(g), stream)
+        fl[:mt] += T * (Ch // 16)
+        return 0
+
     def rgp_convlstm_seq_fits(self, B, G, Ch):
         tiles = (B * (G + 1) ** 2 + 127) // 128
         return 1 if (Ch % 16 == 0 and G <= 14 and tiles <= 16 * max(1, 148 // (Ch // 16))) else 0

@@ -32,15 +32,15 @@ def test_struct_layouts_match_the_header():
     """sizeof of the ctypes mirrors == what the C compiler lays out (checked with gcc on the header)."""
     import subprocess
     import tempfile
-    prog = '#include <stdio.h>\n#include "rgp.h"\nint main(){printf("%zu %zu %zu\\n", sizeof(rgp_tapgemm_args), sizeof(rgp_wgrad_args), sizeof(rgp_gru_seq_args));printf("%zu %zu\\n", sizeof(rgp_lstm_seq_args), sizeof(rgp_gru_bwd_args));return 0;}\n'
+    prog = '#include <stdio.h>\n#include "rgp.h"\nint main(){printf("%zu %zu %zu\\n", sizeof(rgp_tapgemm_args), sizeof(rgp_wgrad_args), sizeof(rgp_gru_seq_args));printf("%zu %zu %zu\\n", sizeof(rgp_lstm_seq_args), sizeof(rgp_gru_bwd_args), sizeof(rgp_lstm_bwd_args));return 0;}\n'
     with tempfile.TemporaryDirectory() as d:
         c = os.path.join(d, "s.c")
         open(c, "w").write(prog)
         exe = os.path.join(d, "s")
         subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), c, "-o", exe])
-        a, b, c, d2, e2 = map(int, subprocess.check_output([exe]).split())
+        a, b, c, d2, e2, f2 = map(int, subprocess.check_output([exe]).split())
     assert a == ctypes.sizeof(L.TapGemmArgs) and b == ctypes.sizeof(L.WgradArgs) and c == ctypes.sizeof(L.GruSeqArgs)
-    assert d2 == ctypes.sizeof(L.LstmSeqArgs) and e2 == ctypes.sizeof(L.GruBwdArgs)
+    assert d2 == ctypes.sizeof(L.LstmSeqArgs) and e2 == ctypes.sizeof(L.GruBwdArgs) and f2 == ctypes.sizeof(L.LstmBwdArgs)
 
 
 def test_workspace_queries():

@@ -158,3 +158,11 @@ def test_small_batch_persistent_bptt_wiring(model):
     torch autograd on the oracle."""
     eng, _ = _grad_check(model, "c3d", seq="small", T=4)
     assert eng.use_seq_small
+
+
+def test_small_batch_persistent_lstm_bptt_wiring():
+    """engine -> rgp_convlstm_seq_fwd + rgp_convlstm_seq_small_bwd (one launch each): gradients equal torch autograd on the
+    oracle, peephole gradients included."""
+    eng, _ = _grad_check("gaze_lstm", "c3d", seq=True, T=4)
+    assert eng.use_seq_lstm
+    assert any(getattr(c, "__len__", None) and c[0] == "tapgemm" for c in eng.lib.calls)

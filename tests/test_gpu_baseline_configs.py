@@ -335,3 +335,42 @@ def test_small_batch_persistent_bptt_vs_per_step_and_oracle(model, G, B, T):
             worst[k] = float(np.abs(a[k].reshape(r.shape) - r).max() / max(np.abs(r).max(), 1e-30))
             assert worst[k] <= 5e-2, (k, worst[k])
         _report("reference_shape_grcn_B28_T42_Ch128_small_bptt", **worst)
+
+
+@pytest.mark.parametrize("G,B,T,head", [(7, 28, 42, None), (7, 3, 5, None), (14, 4, 6, "fc"), (7, 1, 1, None), (14, 10, 3, "fc")])
+def test_small_batch_persistent_lstm_bptt_vs_per_step_and_oracle(G, B, T, head, monkeypatch):
+    """rgp_convlstm_seq_small_bwd (reverse-time ConvLSTM recurrence in one launch) against the per-step BPTT path - every
+    gradient tensor, the peephole gradients included - and at the reference's training shape (28 x T = 42, hidden 128)
+    against torch autograd on the float64 oracle (5e-2 of each tensor's largest gradient)."""
+    Ch = 128
+    p = O.init_params("gaze_lstm", hidden=Ch, T=T, grid=G, seed=8, regime="S", head=head)
+    rng = np.random.RandomState(14)
+    emb = SY.make_embedded(rng, B, T, G, 512)
+    GH = G if head == "fc" else 49
+    gt, _ = SY.make_gazemaps(rng, B, T, GH, GH, normalize=True)
+    grads = []
+    for seq in (None, False):
+        eng = GazeEngine("gaze_lstm", B=B, T=T, G=G, Ch=Ch, dtype=1, device="cuda", train=True, seq=seq, head=head)
+        assert eng.use_seq_lstm == (seq is None)
+        eng.load_tf_params(p)
+        for _ in range(2):
+            eng.forward(emb=torch.from_numpy(emb).cuda(), gt=torch.from_numpy(gt).cuda())
+            eng.backward()
+        torch.cuda.synchronize()
+        assert not eng.seq_timed_out()
+        grads.append(eng.op_to_tf(eng.grads.cpu().numpy()))
+    a, b = grads
+    for k in b:
+        if k.startswith("proj_c3d") or k == "out_b" or k == "ConvLSTM_Whc":
+            continue
+        scale = np.abs(b[k]).max()
+        assert np.abs(a[k] - b[k]).max() <= 2e-2 * scale + 1e-12, (k, np.abs(a[k] - b[k]).max(), scale)
+    if T == 42:
+        _, _, _, ref = O.forward_loss_grads("gaze_lstm", p, gt.astype(np.float64), emb=emb.astype(np.float64))
+        worst = {}
+        for k, r in ref.items():
+            if k in ("out_b", "ConvLSTM_Whc"):
+                continue
+            worst[k] = float(np.abs(a[k].reshape(r.shape) - r).max() / max(np.abs(r).max(), 1e-30))
+            assert worst[k] <= 5e-2, (k, worst[k])
+        _report("reference_shape_lstm_B28_T42_Ch128_small_bptt", **worst)
