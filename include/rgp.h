@@ -86,7 +86,11 @@ typedef struct rgp_tapgemm_args {
    * is the same p-layout operand (S, Wp, G describe it); each tap's A tile is fetched by a TMA im2col load with hardware
    * zero fill at the frame borders, and row m = f*G*G + y*G + x is stored at the q-row f*S + y*Wp + x of out_f32.
    * im2col = 2: the TRANSPOSE of that convolution (BPTT: dX of the input half) with RGP_EPI_DX_DENSE - A is the q-layout
-   * gradient (zero at the pad positions), tap (ky,kx) reads position (y+1-ky, x+1-kx), row m is stored at dense row m. */
+   * gradient (zero at the pad positions), tap (ky,kx) reads position (y+1-ky, x+1-kx), row m is stored at dense row m.
+   * im2col = 3 / 4: the same two convolutions with POSITION-MAJOR tiles (one tile = one position (y,x) of 128 consecutive
+   * frames, so out-of-frame taps are skipped for the whole tile: (3G-2)^2 of 9 G^2 tap-tiles); same arguments, same
+   * results bit for bit.  The library takes this order by itself for im2col = 1 / 2 when it is cheaper (many frames);
+   * RGP_PMAJOR=0 in the environment keeps the dense-M order. */
   int im2col;
 } rgp_tapgemm_args;
 

@@ -331,7 +331,37 @@ struct SlabCfg {
   int nw;        // weight-ring stages
   int slots;     // slab slots (k-chunks of A in flight)
   int tg;        // taps per weight stage (narrow tiles: one TMA box of tg*BN rows and ONE barrier round trip per tg taps)
+  int pm_rot;    // position-major conv mode: rotation of the position order per frame group (load balance)
 };
+
+// Position-major 3x3 SAME conv (im2col == 3 forward, 4 its transpose): an M tile is ONE position (y, x) of 128
+// consecutive frames, so the taps that fall outside the frame are outside it for every row of the tile and are
+// skipped - (3G-2)^2 of 9 G^2 tap-tiles are issued (0.82 at 7x7, 0.91 at 14x14). Tile order: frame group, position
+// (rotated by pm_rot per group so that the cheap corner / edge tiles spread over the CTAs), column tile.
+struct PmTile {
+  int fg, p, y, x, n0;
+  uint32_t mask;   // valid taps
+};
+__device__ __forceinline__ PmTile pm_decode(const rgp_tapgemm_args& a, int tile, int ntiles, int BNv, int rot) {
+  PmTile t;
+  const int P = a.G * a.G, per = P * ntiles;
+  t.fg = tile / per;
+  const int rem = tile - t.fg * per;
+  const int j = rem / ntiles;
+  t.n0 = (rem - j * ntiles) * BNv;
+  t.p = (int)(((long long)j + (long long)t.fg * rot) % P);
+  t.y = t.p / a.G;
+  t.x = t.p - t.y * a.G;
+  t.mask = 0;
+#pragma unroll
+  for (int tap = 0; tap < 9; ++tap) {
+    const int dy = tap / 3 - 1, dx = tap % 3 - 1;
+    const int yy = a.im2col == 4 ? t.y - dy : t.y + dy, xx = a.im2col == 4 ? t.x - dx : t.x + dx;
+    if (yy >= 0 && yy < a.G && xx >= 0 && xx < a.G) t.mask |= 1u << tap;
+  }
+  return t;
+}
+
 constexpr int kSlabMaxSlots = 4;
 constexpr int kSlabBarBytes = 512;     // (2 * nw + 8) mbarriers + the TMEM slot, nw <= kSlabMaxW
 constexpr int kSlabMaxW = 24;
@@ -362,7 +392,8 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int mtiles = (a.M + BM - 1) / BM, ntiles = a.N / BN;
-  const int total_tiles = mtiles * ntiles;
+  const bool pm = !SLAB && a.im2col >= 3;
+  const int total_tiles = pm ? ((a.M / (a.G * a.G) + BM - 1) / BM) * (a.G * a.G) * ntiles : mtiles * ntiles;
   const int kchunks = a.K / BK;
   const int ksteps = a.ntaps * kchunks;
 
@@ -407,6 +438,25 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             if (++ws == sc.nw) { ws = 0; wph ^= 1; }
           }
           if (++as == sc.slots) { as = 0; aph ^= 1; }
+        }
+      }
+    } else if (lane == 0 && pm) {
+      int stage = 0; uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const PmTile t = pm_decode(a, tile, ntiles, BN, sc.pm_rot);
+        for (int tap = 0; tap < 9; ++tap) {
+          if (!((t.mask >> tap) & 1u)) continue;
+          const int dy = tap / 3 - 1, dx = tap % 3 - 1;
+          // forward: A is a p-layout operand (pixel (0,0) at row Wp+1); transpose: a q-layout gradient, flipped taps
+          const int srow = a.im2col == 4 ? (t.y - dy) * a.Wp + (t.x - dx) : (t.y + dy + 1) * a.Wp + (t.x + dx + 1);
+          for (int kc = 0; kc < kchunks; ++kc) {
+            mbar_wait(&empty[stage], phase ^ 1);
+            uint8_t* sa = smem + stage * C::kStageBytes;
+            mbar_expect_tx(&full[stage], C::kStageBytes);
+            tma_load_3d(sa, &tmA, &full[stage], kc * BK, srow, t.fg * BM);
+            tma_load_2d(sa + BM * BK * 2, &tmB, &full[stage], kc * BK, tap * a.N + t.n0);
+            if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+          }
         }
       }
     } else if (lane == 0) {
@@ -477,7 +527,8 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         if (++acc == 2) { acc = 0; accphase ^= 1; }
         continue;
       }
-      for (int ks = 0; ks < ksteps; ++ks) {
+      const int ksteps_t = pm ? __popc(pm_decode(a, tile, ntiles, BN, sc.pm_rot).mask) * kchunks : ksteps;
+      for (int ks = 0; ks < ksteps_t; ++ks) {
         mbar_wait(&full[stage], phase);
         tc_fence_after();
         if (lane == 0) {
@@ -488,7 +539,7 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           for (int k = 0; k < BK / 16; ++k)   // +32 bytes (>>4 = 2) per K=16 slice inside the 128-byte swizzle row
             tc_mma_bf16(tacc, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (ks | k) ? 1u : 0u);
           tc_commit(&empty[stage]);
-          if (ks == ksteps - 1) tc_commit(&tfull[acc]);
+          if (ks == ksteps_t - 1) tc_commit(&tfull[acc]);
         }
         __syncwarp();
         if (++stage == C::kStages) { stage = 0; phase ^= 1; }
@@ -501,9 +552,17 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     int acc = 0; uint32_t accphase = 0;
     const bool vec = (a.N % 32 == 0) && (a.ldo % 16 == 0) && (a.ldx % 8 == 0) && (a.Ch % 32 == 0) && (a.ldg % 16 == 0);
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-      const int mt = tile / ntiles, nt = tile - mt * ntiles;
-      const int m0 = mt * BM, n0 = nt * BN;
-      const RowInfo r = make_row(a, m0 + lg * 32 + lane);
+      int n0, mrow;
+      if (pm) {           // row i of the tile = frame fg*128 + i at position p: the dense row make_row() expects
+        const PmTile t = pm_decode(a, tile, ntiles, BN, sc.pm_rot);
+        n0 = t.n0;
+        mrow = (t.fg * BM + lg * 32 + lane) * (a.G * a.G) + t.p;
+      } else {
+        const int mt = tile / ntiles, nt = tile - mt * ntiles;
+        n0 = nt * BN;
+        mrow = mt * BM + lg * 32 + lane;
+      }
+      const RowInfo r = make_row(a, mrow);
       // While the MMAs of this tile are still running: pull the epilogue's inputs (pre-activations from the
       // input-half GEMM, z, h_{t-1}) from HBM into L2, one 128-byte line per prefetch, this thread's row.
       if (r.inrange && (a.epi == RGP_EPI_GRU_ZR || a.epi == RGP_EPI_GRU_C)) {
@@ -721,7 +780,15 @@ int launch(const rgp_tapgemm_args& a, cudaStream_t s) {
   }
   CUtensorMap tmA, tmB;
   int rc;
-  if (a.im2col) {
+  if (a.im2col >= 3) {
+    const int P = a.G * a.G;
+    const long long frames = a.M / P;
+    rc = tc::encode_map_frames_bf16(a.A, a.K, a.S, frames, a.lda, BM, &tmA);
+    int rot = (int)(0.382 * P + 0.5);                 // golden-ratio stride over the positions, coprime with P
+    auto gcd = [](int x, int y) { while (y) { int t = x % y; x = y; y = t; } return x; };
+    while (rot > 1 && gcd(rot, P) != 1) ++rot;
+    sc.pm_rot = rot % P;
+  } else if (a.im2col) {
     const long long frames = a.M / (a.G * a.G);
     // im2col == 1: A is a p-layout operand (pixel (0,0) at row Wp+1); == 2: a q-layout gradient (pixel (0,0) at row 0)
     const long long row0 = a.im2col == 2 ? 0 : (a.Wp + 1);
@@ -741,8 +808,9 @@ int launch(const rgp_tapgemm_args& a, cudaStream_t s) {
     attr_set.set();
   }
   const int mtiles = (a.M + BM - 1) / BM, ntiles = a.N / BN;
-  int grid = mtiles * ntiles;
-  if (grid > num_sms()) grid = num_sms();
+  long long tiles = (long long)mtiles * ntiles;
+  if (a.im2col >= 3) tiles = ((a.M / (a.G * a.G) + BM - 1) / BM) * (long long)(a.G * a.G) * ntiles;
+  int grid = tiles > num_sms() ? num_sms() : (int)tiles;
   if (slab) {
     const int smem_bytes = sc.nw * sc.tg * BN * BK * 2 + sc.slots * sc.bytes + 1024 + kSlabBarBytes + kEpiScratchBytes;
     tapgemm_tc_kernel<BN, true><<<grid, NTHREADS, smem_bytes, s>>>(tmA, tmB, a, sc);
@@ -806,6 +874,25 @@ int encode_map_bf16(const void* base, long long dim0, long long dim1, long long 
   return 0;
 }
 
+int encode_map_frames_bf16(const void* base, int C, int rows_per_frame, long long frames, int ld, int box_frames,
+                           CUtensorMap* out) {
+  auto enc = get_encode();
+  if (!enc) { set_error("cuTensorMapEncodeTiled not available from the driver"); return -38; }
+  cuuint64_t dims[3] = {(cuuint64_t)C, (cuuint64_t)rows_per_frame, (cuuint64_t)frames};
+  cuuint64_t strides[2] = {(cuuint64_t)ld * 2, (cuuint64_t)rows_per_frame * ld * 2};
+  cuuint32_t box[3] = {64, 1, (cuuint32_t)box_frames};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled(3d) failed (%d) base=%p C=%d rows=%d frames=%lld ld=%d", (int)r, base, C, rows_per_frame,
+              frames, ld);
+    return -5;
+  }
+  return 0;
+}
+
 int encode_map_im2col_bf16(const void* base, int C, int G, long long frames, int ld, int Wp, int S, int pad, int pixels,
                            CUtensorMap* out) {
   static PFN_cuTensorMapEncodeIm2col_v12000 fn = nullptr;
@@ -851,12 +938,25 @@ int tapgemm_tc(const rgp_tapgemm_args& a, cudaStream_t s) {
   RGP_CHECK_ARG(a.K % BK == 0, "tapgemm_tc: K=%d must be a multiple of %d", a.K, BK);
   if (a.im2col)
     RGP_CHECK_ARG(a.ntaps == 9 && !a.accumulate && a.G > 0 && a.M % (a.G * a.G) == 0 && a.N % 32 == 0 &&
-                  a.S >= (a.G + 1) * a.Wp - 1 && a.Wp > a.G &&
-                  ((a.im2col == 1 && a.epi == RGP_EPI_STORE_F32) || (a.im2col == 2 && a.epi == RGP_EPI_DX_DENSE)),
+                  a.S >= (a.G + 1) * a.Wp - 1 && a.Wp > a.G && a.im2col <= 4 &&
+                  ((a.im2col % 2 == 1 && a.epi == RGP_EPI_STORE_F32) || (a.im2col % 2 == 0 && a.epi == RGP_EPI_DX_DENSE)),
                   "tapgemm_tc: im2col mode is a 3x3 SAME conv: 1 + RGP_EPI_STORE_F32 (forward) or 2 + RGP_EPI_DX_DENSE (its "
                   "transpose) (im2col=%d ntaps=%d epi=%d M=%d G=%d)", a.im2col, a.ntaps, a.epi, a.M, a.G);
   RGP_CHECK_ARG(a.lda % 8 == 0, "tapgemm_tc: lda=%d must be a multiple of 8 (16-byte TMA stride)", a.lda);
   RGP_CHECK_ARG(((uintptr_t)a.A & 15) == 0 && ((uintptr_t)a.Bw & 15) == 0, "tapgemm_tc: operands must be 16-byte aligned");
+  if (a.im2col == 1 || a.im2col == 2) {
+    // position-major tiles (im2col + 2) when skipping the out-of-frame taps outweighs the ragged last frame group:
+    // ceil(F / 128) * (3G-2)^2 tap-tiles against ceil(F * G^2 / 128) * 9.  RGP_PMAJOR=0 keeps the dense-M order.
+    const char* pe = getenv("RGP_PMAJOR");
+    const bool pm_on = !(pe && pe[0] == '0');
+    const long long F = a.M / (a.G * a.G), e3 = 3 * a.G - 2;
+    const long long cost_pm = ((F + BM - 1) / BM) * e3 * e3, cost_dense = ((long long)(a.M + BM - 1) / BM) * 9;
+    if (pm_on && a.N % 256 == 0 && cost_pm * 100 < cost_dense * 95) {
+      rgp_tapgemm_args b = a;
+      b.im2col = a.im2col + 2;
+      return launch<256>(b, s);
+    }
+  }
   const int mtiles = (a.M + BM - 1) / BM;
   // less than half a wave of 128x256 tiles (small-batch recurrence steps): 128x128 tiles fill twice the SMs
   if (a.N % 256 == 0 && (long long)mtiles * (a.N / 256) * 2 > num_sms()) return launch<256>(a, s);

@@ -40,6 +40,13 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* t
 // im2col-mode TMA load of a 4-D (C, W, H, N) activation tensor: `pixelsPerColumn` consecutive base pixels starting at
 // (w, h, n) (W fastest, then H, then N, inside the bounding box of the tensor map) x `channelsPerPixel` channels from c;
 // the pixel actually read is the base pixel + (off_w, off_h); positions outside the tensor are zero filled.
+// tiled 3-d box (channels, row of the frame, frames): one row per frame, used by the position-major conv mode
+__device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* tmap, uint64_t* bar, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+      ::"r"(smem_u32(smem_dst)), "l"(tmap), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
 __device__ __forceinline__ void tma_load_im2col_4d(void* smem_dst, const CUtensorMap* tmap, uint64_t* bar, int c, int w,
                                                    int h, int n, uint16_t off_w, uint16_t off_h) {
   asm volatile(
@@ -120,6 +127,9 @@ __device__ __forceinline__ uint64_t make_sdesc_mn(uint32_t saddr, uint32_t lbo_b
 // 2-D bf16 tensor map (dim0 = contiguous) with SWIZZLE_128B; cached per (base, shape, box).
 int encode_map_bf16(const void* base, long long dim0, long long dim1, long long stride1_bytes, int box0, int box1,
                     CUtensorMap* out);
+// [frames][rows_per_frame][C] bf16 tensor (row pitch ld elements), box = 64 channels x 1 row x box_frames frames
+int encode_map_frames_bf16(const void* base, int C, int rows_per_frame, long long frames, int ld, int box_frames,
+                           CUtensorMap* out);
 // 4-D (C, W, H, N) bf16 im2col tensor map for a k x k SAME convolution (pad = (k-1)/2) over G x G frames stored with row
 // pitch `ld` elements: W stride = ld, H stride = Wp*ld, N stride = S*ld; box = `pixels` base pixels x 64 channels, SWIZZLE_128B
 int encode_map_im2col_bf16(const void* base, int C, int G, long long frames, int ld, int Wp, int S, int pad, int pixels,

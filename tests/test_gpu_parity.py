@@ -379,3 +379,38 @@ def test_i2h_im2col_dense_rows_equal_slab_path(G, B, T, Ch, lstm, monkeypatch):
     scale = np.abs(b[:, :G, :G]).max()
     assert np.abs(a[:, :G, :G] - b[:, :G, :G]).max() <= 1e-5 * scale
     assert not a[:, G].any() and not a[:, :, G].any()          # dense mode never writes the pad row / column
+
+
+@pytest.mark.parametrize("G,B,T,Ch,model", [(7, 40, 25, 128, "gaze_grcn"), (7, 48, 8, 256, "gaze_grcn"), (14, 16, 16, 128, "gaze_lstm")])
+def test_position_major_conv_tiles_equal_dense_rows_bitwise(G, B, T, Ch, model, monkeypatch):
+    """Position-major tiles of the 3x3 SAME conv (im2col 3 / 4: one position of 128 frames per tile, out-of-frame taps
+    skipped) against the dense-M order (im2col 1 / 2): the skipped taps only ever added zeros and the order of the
+    remaining ones is the same, so the i2h pre-activations and the BPTT's dX of the input half are equal BIT FOR BIT -
+    ragged last frame group (1000 = 7 * 128 + 104 frames) and the 14x14 grid included."""
+    head = None if G == 7 else "fc"
+    p = O.init_params(model, hidden=Ch, T=T, grid=G, seed=4, regime="S", head=head)
+    rng = np.random.RandomState(3)
+    emb = torch.from_numpy(SY.make_embedded(rng, B, T, G, 512)).cuda()
+    GH = G if head == "fc" else 49
+    gt = torch.from_numpy(SY.make_gazemaps(rng, B, T, GH, GH, normalize=True)[0]).cuda()
+    out = []
+    for flag in ("1", "0"):
+        monkeypatch.setenv("RGP_PMAJOR", flag)
+        eng = GazeEngine(model, B=B, T=T, G=G, Ch=Ch, dtype=1, device="cuda", head=head, train=True)
+        eng.load_tf_params(p)
+        eng.forward(emb=emb, gt=gt)
+        xg = eng.Xg.clone()
+        # the transposed conv (dX of the input half) on the step's dG, called as the c3d entry's backward does
+        btaps = [eng.Wp + 1 - o for o in eng.taps3]
+        eng.backward()
+        NG = eng.ngx * Ch
+        eng.lib.rgp_transpose_taps(eng._ptr("Wx_op"), eng.WxT.data_ptr(), 9, NG, eng.Cin, eng.dtype, eng._s())
+        dx = torch.zeros(T * B * G * G, eng.Cin, dtype=torch.bfloat16, device="cuda")
+        eng._gemm(A=eng.dG.data_ptr(), rowsA=T * B * eng.S, lda=NG, K=NG, Bw=eng.WxT.data_ptr(), M=T * B * G * G, N=eng.Cin,
+                  taps=btaps, epi=L.EPI_DX_DENSE, S=eng.S, Wp=eng.Wp, G=G, P=G * G, out_op=dx.data_ptr(), ldo=eng.Cin, im2col=2)
+        torch.cuda.synchronize()
+        out.append((xg.cpu().numpy(), dx.float().cpu().numpy()))
+    (xa, da), (xb, db) = out
+    assert np.abs(xb).max() > 0 and np.abs(db).max() > 0
+    assert np.array_equal(xa, xb)
+    assert np.array_equal(da, db)
