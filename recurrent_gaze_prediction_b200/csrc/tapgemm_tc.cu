@@ -10,6 +10,9 @@
 //                 so the epilogue of tile i overlaps the main loop of tile i+1.
 //   warps 2..5  : epilogue.  tcgen05.ld 32 lanes x 32 columns -> registers -> fused epilogue (common.cuh).
 #include <map>
+#include <vector>
+#include <tuple>
+#include <algorithm>
 #include <mutex>
 #include <tuple>
 #include "tc_common.cuh"
@@ -334,14 +337,29 @@ struct SlabCfg {
   int pm_rot;    // position-major conv mode: rotation of the position order per frame group (load balance)
 };
 
-// Position-major 3x3 SAME conv (im2col == 3 forward, 4 its transpose): an M tile is ONE position (y, x) of 128
-// consecutive frames, so the taps that fall outside the frame are outside it for every row of the tile and are
-// skipped - (3G-2)^2 of 9 G^2 tap-tiles are issued (0.82 at 7x7, 0.91 at 14x14). Tile order: frame group, position
-// (rotated by pm_rot per group so that the cheap corner / edge tiles spread over the CTAs), column tile.
+// Position-major tiles (im2col == 3: 3x3 SAME conv forward, 4: its transpose, 5: the composed 4x4-tap head GEMM): an M
+// tile is ONE position (y, x) of 128 consecutive frames, so the taps that fall outside the frame are outside it for every
+// row of the tile and are skipped - (3G-2)^2 of 9 G^2 tap-tiles for the convs (0.82 at 7x7, 0.91 at 14x14), 27^2 = 729 of
+// 1600 row-taps per frame for the head.  Tile order: frame group, position (rotated by pm_rot per group so that the
+// cheap corner / edge tiles spread over the CTAs), column tile.  The source row of tap (ky, kx) is (y + oy) * Wp + x + ox
+// inside the frame's S rows; it is real data iff lo <= y + oy, x + ox < lo + n:
+//   3: p-layout operand,  (oy, ox) = (ky, kx),         lo = 1, n = G     4: q-layout gradient, (1 - ky, 1 - kx), lo = 0, n = G
+//   5: head-input layout (data at +3, +3 of a 10 x 10 frame), (3 - ky, 3 - kx) for the 4 x 4 taps, lo = 3, n = G - 2
 struct PmTile {
   int fg, p, y, x, n0;
   uint32_t mask;   // valid taps
 };
+__device__ __forceinline__ int pm_ntaps(const rgp_tapgemm_args& a) { return a.im2col == 5 ? 16 : 9; }
+__device__ __forceinline__ bool pm_tap(const rgp_tapgemm_args& a, int y, int x, int tap, int& srow) {
+  int oy, ox, lo, n;
+  if (a.im2col == 5) { oy = 3 - (tap >> 2); ox = 3 - (tap & 3); lo = 3; n = a.G - 2; }
+  else if (a.im2col == 4) { oy = 1 - tap / 3; ox = 1 - tap % 3; lo = 0; n = a.G; }
+  else { oy = tap / 3; ox = tap % 3; lo = 1; n = a.G; }
+  const int sy = y + oy, sx = x + ox;
+  srow = sy * a.Wp + sx;
+  return sy >= lo && sy < lo + n && sx >= lo && sx < lo + n;
+}
+__device__ __forceinline__ int pm_frames(const rgp_tapgemm_args& a) { return a.im2col == 5 ? a.M / a.S : a.M / (a.G * a.G); }
 __device__ __forceinline__ PmTile pm_decode(const rgp_tapgemm_args& a, int tile, int ntiles, int BNv, int rot) {
   PmTile t;
   const int P = a.G * a.G, per = P * ntiles;
@@ -353,11 +371,10 @@ __device__ __forceinline__ PmTile pm_decode(const rgp_tapgemm_args& a, int tile,
   t.y = t.p / a.G;
   t.x = t.p - t.y * a.G;
   t.mask = 0;
-#pragma unroll
-  for (int tap = 0; tap < 9; ++tap) {
-    const int dy = tap / 3 - 1, dx = tap % 3 - 1;
-    const int yy = a.im2col == 4 ? t.y - dy : t.y + dy, xx = a.im2col == 4 ? t.x - dx : t.x + dx;
-    if (yy >= 0 && yy < a.G && xx >= 0 && xx < a.G) t.mask |= 1u << tap;
+  const int nt = pm_ntaps(a);
+  for (int tap = 0; tap < nt; ++tap) {
+    int srow;
+    if (pm_tap(a, t.y, t.x, tap, srow)) t.mask |= 1u << tap;
   }
   return t;
 }
@@ -393,7 +410,7 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int mtiles = (a.M + BM - 1) / BM, ntiles = a.N / BN;
   const bool pm = !SLAB && a.im2col >= 3;
-  const int total_tiles = pm ? ((a.M / (a.G * a.G) + BM - 1) / BM) * (a.G * a.G) * ntiles : mtiles * ntiles;
+  const int total_tiles = pm ? ((pm_frames(a) + BM - 1) / BM) * (a.G * a.G) * ntiles : mtiles * ntiles;
   const int kchunks = a.K / BK;
   const int ksteps = a.ntaps * kchunks;
 
@@ -444,12 +461,15 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       int stage = 0; uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         const PmTile t = pm_decode(a, tile, ntiles, BN, sc.pm_rot);
-        for (int tap = 0; tap < 9; ++tap) {
-          if (!((t.mask >> tap) & 1u)) continue;
-          const int dy = tap / 3 - 1, dx = tap % 3 - 1;
-          // forward: A is a p-layout operand (pixel (0,0) at row Wp+1); transpose: a q-layout gradient, flipped taps
-          const int srow = a.im2col == 4 ? (t.y - dy) * a.Wp + (t.x - dx) : (t.y + dy + 1) * a.Wp + (t.x + dx + 1);
-          for (int kc = 0; kc < kchunks; ++kc) {
+        const int nt = pm_ntaps(a);
+        // accumulation order = the dense paths' (results equal bit for bit): convs tap-major, head k-chunk-major (slab mode)
+        const bool kmajor = a.im2col == 5;
+        const int n_out = kmajor ? kchunks : nt, n_in = kmajor ? nt : kchunks;
+        for (int io = 0; io < n_out; ++io) {
+          for (int ii = 0; ii < n_in; ++ii) {
+            const int tap = kmajor ? ii : io, kc = kmajor ? io : ii;
+            int srow;
+            if (!pm_tap(a, t.y, t.x, tap, srow)) continue;
             mbar_wait(&empty[stage], phase ^ 1);
             uint8_t* sa = smem + stage * C::kStageBytes;
             mbar_expect_tx(&full[stage], C::kStageBytes);
@@ -556,7 +576,8 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       if (pm) {           // row i of the tile = frame fg*128 + i at position p: the dense row make_row() expects
         const PmTile t = pm_decode(a, tile, ntiles, BN, sc.pm_rot);
         n0 = t.n0;
-        mrow = (t.fg * BM + lg * 32 + lane) * (a.G * a.G) + t.p;
+        const int f = t.fg * BM + lg * 32 + lane;
+        mrow = a.im2col == 5 ? f * a.S + t.y * a.Wp + t.x : f * (a.G * a.G) + t.p;
       } else {
         const int mt = tile / ntiles, nt = tile - mt * ntiles;
         n0 = nt * BN;
@@ -747,6 +768,58 @@ bool slab_enabled() {
   return v == 1;
 }
 
+long long pm_frames_host(const rgp_tapgemm_args& a) { return a.im2col == 5 ? a.M / a.S : a.M / (a.G * a.G); }
+
+// taps per position of the position-major modes (host mirror of pm_tap)
+void pm_costs(const rgp_tapgemm_args& a, std::vector<int>& cost) {
+  const int G = a.G;
+  cost.assign(G * G, 0);
+  const int nt = a.im2col == 5 ? 16 : 9;
+  for (int y = 0; y < G; ++y)
+    for (int x = 0; x < G; ++x)
+      for (int tap = 0; tap < nt; ++tap) {
+        int oy, ox, lo, n;
+        if (a.im2col == 5) { oy = 3 - (tap >> 2); ox = 3 - (tap & 3); lo = 3; n = G - 2; }
+        else if (a.im2col == 4) { oy = 1 - tap / 3; ox = 1 - tap % 3; lo = 0; n = G; }
+        else { oy = tap / 3; ox = tap % 3; lo = 1; n = G; }
+        const int sy = y + oy, sx = x + ox;
+        if (sy >= lo && sy < lo + n && sx >= lo && sx < lo + n) ++cost[y * G + x];
+      }
+}
+
+// Rotation of the position order per frame group that minimises the heaviest CTA of the static tile schedule
+// (tile i runs on CTA i % grid): exhaustive over the G*G candidates, cached per shape.
+int pm_rotation(const rgp_tapgemm_args& a, int fgroups, int ntiles, int grid) {
+  static std::map<std::tuple<int, int, int, int, int>, int> cache;
+  static std::mutex mu;
+  const auto key = std::make_tuple(a.im2col, a.G, fgroups, ntiles, grid);
+  {
+    std::lock_guard<std::mutex> g(mu);
+    auto it = cache.find(key);
+    if (it != cache.end()) return it->second;
+  }
+  std::vector<int> cost;
+  pm_costs(a, cost);
+  const int P = a.G * a.G;
+  const long long tiles = (long long)fgroups * P * ntiles;
+  int best = 0;
+  long long best_max = -1;
+  std::vector<long long> load(grid);
+  for (int rot = 0; rot < P; ++rot) {
+    std::fill(load.begin(), load.end(), 0);
+    for (long long i = 0; i < tiles; ++i) {
+      const long long fg = i / ((long long)P * ntiles), j = (i % ((long long)P * ntiles)) / ntiles;
+      load[i % grid] += cost[(j + fg * rot) % P];
+    }
+    const long long mx = *std::max_element(load.begin(), load.end());
+    if (best_max < 0 || mx < best_max) { best_max = mx; best = rot; }
+    if (tiles * P > 40000000LL) break;     // very long inputs: keep rot = 0 rather than search for seconds
+  }
+  std::lock_guard<std::mutex> g(mu);
+  cache[key] = best;
+  return best;
+}
+
 template <int BN>
 int launch(const rgp_tapgemm_args& a, cudaStream_t s) {
   using C = Cfg<BN>;
@@ -781,13 +854,9 @@ int launch(const rgp_tapgemm_args& a, cudaStream_t s) {
   CUtensorMap tmA, tmB;
   int rc;
   if (a.im2col >= 3) {
-    const int P = a.G * a.G;
-    const long long frames = a.M / P;
+    const long long frames = pm_frames_host(a);
     rc = tc::encode_map_frames_bf16(a.A, a.K, a.S, frames, a.lda, BM, &tmA);
-    int rot = (int)(0.382 * P + 0.5);                 // golden-ratio stride over the positions, coprime with P
-    auto gcd = [](int x, int y) { while (y) { int t = x % y; x = y; y = t; } return x; };
-    while (rot > 1 && gcd(rot, P) != 1) ++rot;
-    sc.pm_rot = rot % P;
+    sc.pm_rot = pm_rotation(a, (int)((frames + BM - 1) / BM), a.N / BN, num_sms());
   } else if (a.im2col) {
     const long long frames = a.M / (a.G * a.G);
     // im2col == 1: A is a p-layout operand (pixel (0,0) at row Wp+1); == 2: a q-layout gradient (pixel (0,0) at row 0)
@@ -809,7 +878,7 @@ int launch(const rgp_tapgemm_args& a, cudaStream_t s) {
   }
   const int mtiles = (a.M + BM - 1) / BM, ntiles = a.N / BN;
   long long tiles = (long long)mtiles * ntiles;
-  if (a.im2col >= 3) tiles = ((a.M / (a.G * a.G) + BM - 1) / BM) * (long long)(a.G * a.G) * ntiles;
+  if (a.im2col >= 3) tiles = ((pm_frames_host(a) + BM - 1) / BM) * (long long)(a.G * a.G) * ntiles;
   int grid = tiles > num_sms() ? num_sms() : (int)tiles;
   if (slab) {
     const int smem_bytes = sc.nw * sc.tg * BN * BK * 2 + sc.slots * sc.bytes + 1024 + kSlabBarBytes + kEpiScratchBytes;
@@ -955,6 +1024,19 @@ int tapgemm_tc(const rgp_tapgemm_args& a, cudaStream_t s) {
       rgp_tapgemm_args b = a;
       b.im2col = a.im2col + 2;
       return launch<256>(b, s);
+    }
+  }
+  if (!a.im2col && a.epi == RGP_EPI_HEAD && a.ntaps == 16 && a.N == 48 && a.G == 9 && a.Wp == 10 && a.S == 100 && !a.accumulate) {
+    // the composed head (taps (3-dy)*Wp + (3-dx)) in position-major tiles: 729 instead of 1600 row-taps per frame
+    bool pattern = true;
+    for (int t = 0; t < 16; ++t) pattern = pattern && a.tap_off[t] == (3 - (t >> 2)) * a.Wp + (3 - (t & 3));
+    const char* pe = getenv("RGP_PMAJOR");
+    const long long F = a.M / a.S;
+    const long long cost_pm = ((F + BM - 1) / BM) * 729 * 5 / 4, cost_dense = ((long long)(a.M + BM - 1) / BM) * 16;
+    if (pattern && !(pe && pe[0] == '0') && cost_pm * 100 < cost_dense * 90) {
+      rgp_tapgemm_args b = a;
+      b.im2col = 5;
+      return launch<48>(b, s);
     }
   }
   const int mtiles = (a.M + BM - 1) / BM;

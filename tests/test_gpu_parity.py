@@ -400,6 +400,7 @@ def test_position_major_conv_tiles_equal_dense_rows_bitwise(G, B, T, Ch, model, 
         eng.load_tf_params(p)
         eng.forward(emb=emb, gt=gt)
         xg = eng.Xg.clone()
+        lg = eng.logits.clone()      # 7x7 models: the composed head GEMM takes position-major tiles too (im2col 5)
         # the transposed conv (dX of the input half) on the step's dG, called as the c3d entry's backward does
         btaps = [eng.Wp + 1 - o for o in eng.taps3]
         eng.backward()
@@ -409,8 +410,9 @@ def test_position_major_conv_tiles_equal_dense_rows_bitwise(G, B, T, Ch, model, 
         eng._gemm(A=eng.dG.data_ptr(), rowsA=T * B * eng.S, lda=NG, K=NG, Bw=eng.WxT.data_ptr(), M=T * B * G * G, N=eng.Cin,
                   taps=btaps, epi=L.EPI_DX_DENSE, S=eng.S, Wp=eng.Wp, G=G, P=G * G, out_op=dx.data_ptr(), ldo=eng.Cin, im2col=2)
         torch.cuda.synchronize()
-        out.append((xg.cpu().numpy(), dx.float().cpu().numpy()))
-    (xa, da), (xb, db) = out
+        out.append((xg.cpu().numpy(), dx.float().cpu().numpy(), lg.cpu().numpy()))
+    (xa, da, la), (xb, db, lb) = out
     assert np.abs(xb).max() > 0 and np.abs(db).max() > 0
     assert np.array_equal(xa, xb)
     assert np.array_equal(da, db)
+    assert np.abs(lb).max() > 0 and np.array_equal(la, lb)

@@ -1,0 +1,10 @@
+#!/bin/bash
+mkdir -p gpurun_out
+cd "$GRAFT_REPO_ROOT" 2>/dev/null || true
+timeout 600 python -m pytest tests/test_gpu_parity.py -m gpu -q -x -k "position_major or bptt" > gpurun_out/r02p21_pytest.log 2>&1; echo "pytest rc=$?"; tail -12 gpurun_out/r02p21_pytest.log | cut -c1-300
+for pm in 0 1; do
+  echo "RGP_PMAJOR=$pm"
+  RGP_PMAJOR=$pm timeout 300 python tools/stage_times.py gaze_grcn 128 35 256 2>&1 | tail -1 | tee -a gpurun_out/r02_stage_times.log | cut -c1-900
+done
+RGP_PMAJOR=1 timeout 300 python tools/stage_times.py gaze_grcn 28 42 128 2>&1 | tail -1 | tee -a gpurun_out/r02_stage_times.log | cut -c1-900
+timeout 900 python -m pytest tests -m gpu -q -x > gpurun_out/r02p21_pytest_all.log 2>&1; echo "all rc=$?"; tail -8 gpurun_out/r02p21_pytest_all.log | cut -c1-300
