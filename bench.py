@@ -467,9 +467,10 @@ def bench_model_record(args, H, session, mode, B, feature_dtype="bf16", with_roo
 
 # DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum) from the committed `ncu --set full` captures of
 # exactly the default configuration (profiles/); None for any other configuration
-TRAFFIC = {"i2h": 1.7544e9,
-           "i2h_source": "profiles/r02_ncu_full_fwd256.txt (dense-M im2col mode: 0.458 GB read + 1.296 GB written per launch)",
-           "gru_seq": 3.6268e9}
+TRAFFIC = {"i2h": 1.7787e9,
+           "i2h_source": "profiles/r02_ncu_full4_fwd256_position_major.txt (position-major tiles: 0.479 GB read + 1.300 GB "
+                         "written per launch)",
+           "gru_seq": 3.6568e9}
 
 
 def bench_config4(args, H):
