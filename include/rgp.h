@@ -42,7 +42,14 @@ enum {
    * 8x8 p-layout rows of h_t.  Row (a,b) of frame f and column n = (ry*7+rx)*P + co is output pixel
    * (oy,ox) = (7a+ry-2, 7b+rx-2), channel co; it is stored (operand dtype) at row f*So + (oy+2)*Wo + (ox+2) of out_op
    * (leading dimension ldo) - the zero-bordered operand layout of the 5x5 top cell; columns n >= 49*P are padding. */
-  RGP_EPI_UP7 = 11
+  RGP_EPI_UP7 = 11,
+  /* the cascade's up-sampling AND the input half of its 5x5 top cell as ONE 3x3-tap GEMM over the 7x7 grid (there is no
+   * nonlinearity between gaze_grcn_cascade.py:326-331 and the cell's input convs, rnn_cell GRU_RCN_Cell fed at :379):
+   * position-major tiles only (im2col = 3: M = frames*49, A = the bottom states, p-layout S/Wp/G = 7); Bw = the composed
+   * weights of rgp_cascade_compose, [class(y)*3 + class(x)][tap][N = 1024][K], class = 0 / 1 / 2 for the first / inner /
+   * last block row or column; column n = (py*7 + px)*16 + gate of block (y, x) is stored at row
+   * f*So + (7y+py)*Wo + 7x+px, column gate of out_f32 (leading dimension ldo >= 16) - the xg of rgp_topgru_seq_fwd. */
+  RGP_EPI_UP7X = 12
 };
 
 /* One "tap GEMM":  acc[m,n] = sum_tap sum_k A[m + tap_off[tap], k] * Bw[tap*N + n, k]
@@ -378,6 +385,16 @@ int rgp_dense_logits(const float* acc, int ldacc, const float* bias, float* logi
 int rgp_topgru_seq_fwd(const float* xg, int ldx, int So, int Wo, const float* uzr, const float* uc, const float* sal,
                        const float* wsal, float* state, int carry, void* og_op, int ldo, float* h_f32, int B, int T,
                        int dtype, void* stream);
+/* Weight-space composition for RGP_EPI_UP7X: the 11x11 / stride-7 SAME transposed conv (gaze_grcn_cascade.py:317-331)
+ * followed by the 5x5 SAME input convs of the top cell (:346-351, z | r | c of 3 units) is linear in the bottom state, so
+ *   xg[7A+py, 7B+px, g] = sum_{ky,kx<3} sum_k h[A+ky-1, B+kx-1, k] * Wc[class(A), class(B)][ky, kx][(py*7+px)*16 + g][k],
+ *   Wc = sum_{dy,dx in -2..2} sum_c [0 <= 7A+py+dy <= 48][0 <= 7B+px+dx <= 48] wu[7(1-ky)+py+dy+2][7(1-kx)+px+dx+2][c][k]
+ *                                                                               * wt[dy+2][dx+2][c][g]
+ * (the bracket is the zero border the 5x5 conv sees around the 49x49 map: it only bites in the first / last block row
+ * and column, hence the 3 x 3 classes).  up [4][upn][Ch] fp32 = the op layout of the up-sampling filter used with
+ * RGP_EPI_UP7 (tap di*2+dj, row (ry*7+rx)*64 + c), wtx [25][16][64] fp32 = the top cell's input kernels (tap, gate, c);
+ * wc [9][9][1024][Ch] operand dtype (rows for phases >= 49 / gates >= 9 are written as zeros). */
+int rgp_cascade_compose(const float* up, int upn, const float* wtx, void* wc, int Ch, int dtype, void* stream);
 /* gaze_grcn_cascade.py:388-420: bias + relu + maxout of one FC layer whose GEMM output y [rows, ldy] fp32 keeps the two
  * halves tf.split(1, 2, .) separates at columns [0, n) and [half, half + n):
  *   v[r, j] = max(relu(y[r, j] + bias[j]), relu(y[r, half + j] + bias[half + j])),  j < n.

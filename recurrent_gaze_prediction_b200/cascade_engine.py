@@ -30,6 +30,7 @@ Dropout on fc1 (:401-402) is live only while the reference trains; training of t
 from __future__ import annotations
 
 import ctypes as C
+import os
 from collections import OrderedDict
 
 import numpy as np
@@ -63,7 +64,7 @@ class CascadeEngine(object):
     GH = GT
 
     def __init__(self, B=2, T=35, Ch=256, Cin=512, Cfeat=1024, dtype=0, device="cuda", lib=None, train=False,
-                 engine=None, top_in=64, seq=None, keep_top_states=False):
+                 engine=None, top_in=64, seq=None, keep_top_states=False, fuse_top=None):
         if train:
             raise NotImplementedError("the cascade (gaze_grcn_cascade.py) is built for forward / loss / inference; its "
                                       "BPTT is not built")
@@ -80,6 +81,14 @@ class CascadeEngine(object):
         self.engine = self.bottom.engine
         self.use_seq = self.bottom.use_seq
         self.keep_top_states = keep_top_states
+        # up-sampling and the top cell's input convs as ONE composed GEMM (RGP_EPI_UP7X; tcgen05 engine only).  The
+        # two-GEMM path stays for the fp32 engine and for reading the up-sampled maps (read_upsampled, net[...]).
+        can_fuse = dtype == 1 and self.engine != 1 and hasattr(self.lib, "rgp_cascade_compose")
+        if fuse_top is None:
+            fuse_top = can_fuse and os.environ.get("RGP_CASCADE_FUSE", "1") != "0"
+        if fuse_top and not can_fuse:
+            raise ValueError("fuse_top needs the bf16 tcgen05 engine")
+        self.fuse_top = bool(fuse_top)
         self._build_params()
         self._alloc()
 
@@ -205,6 +214,11 @@ class CascadeEngine(object):
     def refresh_operands(self):
         if self.dtype != 0:
             self.lib.rgp_cast(self.tparams.data_ptr(), self.tparams_op.data_ptr(), self.ntop, self.dtype, self._s())
+        if self.fuse_top:
+            if getattr(self, "Wc", None) is None:
+                self.Wc = torch.zeros(81 * 1024, self.Ch, dtype=self.tdt, device=self.device)
+            self.lib.rgp_cascade_compose(self._ptr("up_op"), UPN, self._ptr("Wtx_op"), self.Wc.data_ptr(), self.Ch,
+                                         self.dtype, self._s())
 
     # ------------------------------------------------------------------ buffers
     def _alloc(self):
@@ -251,8 +265,11 @@ class CascadeEngine(object):
         assert emb is None and not carry_state and t0 == 0, "the cascade takes C3D features from h_0 = 0"
         assert (frm_sal is not None) == (self.top_in == UPC + 1), "frm_sal goes with top_in = 65"
         self.stage_bottom(c3d)
-        self.stage_upsample()
-        self.stage_top_i2h()
+        if self.fuse_top:
+            self.stage_top_fused()
+        else:
+            self.stage_upsample()
+            self.stage_top_i2h()
         self.stage_top_recurrence(frm_sal)
         self.stage_fc()
         self.entry = "c3d"
@@ -280,6 +297,15 @@ class CascadeEngine(object):
         taps = [ky * TW + kx for ky in range(5) for kx in range(5)]
         self._gemm(A=self.U.data_ptr(), rowsA=self.U.shape[0], lda=UPC, Bw=self._pop("Wtx_op"), M=self.T * self.B * TS,
                    N=16, K=UPC, taps=taps, epi=L.EPI_STORE_F32, out_f32=self.Xg2.data_ptr(), ldo=16, S=TS, Wp=TW, G=GT)
+
+    def stage_top_fused(self):
+        """gaze_grcn_cascade.py:326-331 followed by the input convs of the top cell (:346-351, fed at :379) as one
+        3x3-tap GEMM over the 7x7 grid with composed weights (include/rgp.h: RGP_EPI_UP7X, rgp_cascade_compose):
+        4x fewer FLOPs than the two GEMMs and no 49x49x64 intermediate."""
+        b, B, T = self.bottom, self.B, self.T
+        self._gemm(A=b._slab(b.Hop, 1), rowsA=b.Hop.shape[0] - B * b.S, lda=self.Ch, Bw=self.Wc.data_ptr(),
+                   M=T * B * 49, N=1024, K=self.Ch, taps=b.taps3, epi=L.EPI_UP7X, S=b.S, Wp=b.Wp, G=7, So=TS, Wo=TW,
+                   out_f32=self.Xg2.data_ptr(), ldo=16, im2col=3)
 
     def stage_top_recurrence(self, frm_sal=None):
         sal = wsal = 0
@@ -319,6 +345,8 @@ class CascadeEngine(object):
 
     def read_upsampled(self, t):
         """up-sampled map of step t [B,49,49,64] (operand dtype -> fp32)"""
+        if self.fuse_top:
+            self.stage_upsample()        # the fused path never forms them
         n = self.B * TS
         u = self.U[t * n:(t + 1) * n].view(self.B, TW, TW, UPC)
         return u[:, 2:, 2:, :].float().contiguous()
@@ -335,6 +363,9 @@ class CascadeEngine(object):
         names = ["bottom", "upsample", "top_i2h", "top_recurrence", "fc", "loss"]
         fns = [lambda: self.stage_bottom(c3d), self.stage_upsample, self.stage_top_i2h, self.stage_top_recurrence,
                self.stage_fc, lambda: self.loss_fwd(gt)]
+        if self.fuse_top:
+            names[1:3] = ["upsample+top_i2h (one composed GEMM)"]
+            fns[1:3] = [self.stage_top_fused]
         acc = dict((n, 0.0) for n in names)
         for _ in range(iters):
             evs = [torch.cuda.Event(enable_timing=True) for _ in range(len(fns) + 1)]

@@ -41,8 +41,9 @@ int rgp_tapgemm(const rgp_tapgemm_args* a, void* stream) {
   RGP_CHECK_ARG(a->ntaps >= 1 && a->ntaps <= RGP_MAX_TAPS, "rgp_tapgemm: ntaps=%d out of range", a->ntaps);
   RGP_CHECK_ARG(a->M > 0 && a->N > 0 && a->K > 0, "rgp_tapgemm: bad shape M=%d N=%d K=%d", a->M, a->N, a->K);
   RGP_CHECK_ARG(a->dtype == 0 || a->dtype == 1, "rgp_tapgemm: dtype %d", a->dtype);
-  RGP_CHECK_ARG(a->epi >= 0 && a->epi <= RGP_EPI_UP7, "rgp_tapgemm: unknown epilogue %d", a->epi);
+  RGP_CHECK_ARG(a->epi >= 0 && a->epi <= RGP_EPI_UP7X, "rgp_tapgemm: unknown epilogue %d", a->epi);
   RGP_CHECK_ARG(!a->im2col || (a->dtype == 1 && a->engine != 1), "rgp_tapgemm: im2col mode needs the tcgen05 engine (dtype %d)", a->dtype);
+  RGP_CHECK_ARG(a->epi != RGP_EPI_UP7X || a->im2col == 3, "rgp_tapgemm: RGP_EPI_UP7X needs im2col = 3 (tcgen05 engine), got %d", a->im2col);
   if (a->dtype == 1 && a->engine != 1) return rgp::tapgemm_tc(*a, (cudaStream_t)stream);
   return rgp::tapgemm_simt(*a, (cudaStream_t)stream);
 }

@@ -221,7 +221,56 @@ int launch_topgru(const float* xg, int ldx, int So, int Wo, const float* uzr, co
 
 using namespace rgp;
 
+// Composed weights of the fused up-sampling + top input conv (rgp.h, rgp_cascade_compose).  One block per
+// (class, tap, phase) and 64-wide chunk of k; a thread owns one k and the 9 gates.
+template <typename TA>
+__global__ void __launch_bounds__(64) cascade_compose_kernel(const float* __restrict__ up, int upn, const float* __restrict__ wtx,
+                                                             TA* __restrict__ wc, int Ch) {
+  const int k = blockIdx.y * 64 + threadIdx.x;
+  int b = blockIdx.x;
+  const int ph = b % 64; b /= 64;
+  const int tap = b % 9, cls = b / 9;
+  TA* dst = wc + ((long long)(cls * 9 + tap) * 1024 + ph * 16) * Ch + k;
+  if (k >= Ch) return;
+  float acc[9];
+#pragma unroll
+  for (int g = 0; g < 9; ++g) acc[g] = 0.f;
+  if (ph < 49) {
+    const int cy = cls / 3, cx = cls % 3, ky = tap / 3, kx = tap % 3, py = ph / 7, px = ph % 7;
+    for (int dy = -2; dy <= 2; ++dy) {
+      const int iy = 7 * (1 - ky) + py + dy + 2;
+      if (iy < 0 || iy > 10 || (cy == 0 && py + dy < 0) || (cy == 2 && py + dy > 6)) continue;
+      for (int dx = -2; dx <= 2; ++dx) {
+        const int ix = 7 * (1 - kx) + px + dx + 2;
+        if (ix < 0 || ix > 10 || (cx == 0 && px + dx < 0) || (cx == 2 && px + dx > 6)) continue;
+        const int di = iy / 7, ry = iy - 7 * di, dj = ix / 7, rx = ix - 7 * dj;
+        const float* u = up + ((long long)(di * 2 + dj) * upn + (ry * 7 + rx) * 64) * Ch + k;
+        const float* w = wtx + ((dy + 2) * 5 + dx + 2) * 16 * 64;
+        for (int c = 0; c < 64; ++c) {
+          const float uv = u[(long long)c * Ch];
+#pragma unroll
+          for (int g = 0; g < 9; ++g) acc[g] = fmaf(uv, __ldg(w + g * 64 + c), acc[g]);
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int g = 0; g < 16; ++g) OpT<TA>::st(dst + (long long)g * Ch, g < 9 ? acc[g] : 0.f);
+}
+
 extern "C" {
+
+int rgp_cascade_compose(const float* up, int upn, const float* wtx, void* wc, int Ch, int dtype, void* stream) {
+  RGP_CHECK_ARG(up && wtx && wc, "rgp_cascade_compose: null pointer%s", "");
+  RGP_CHECK_ARG(Ch > 0 && upn >= 49 * 64, "rgp_cascade_compose: Ch=%d upn=%d", Ch, upn);
+  RGP_CHECK_ARG(dtype == 0 || dtype == 1, "rgp_cascade_compose: dtype %d", dtype);
+  dim3 grid(9 * 9 * 64, (Ch + 63) / 64);
+  if (dtype == 0)
+    cascade_compose_kernel<float><<<grid, 64, 0, (cudaStream_t)stream>>>(up, upn, wtx, (float*)wc, Ch);
+  else
+    cascade_compose_kernel<__nv_bfloat16><<<grid, 64, 0, (cudaStream_t)stream>>>(up, upn, wtx, (__nv_bfloat16*)wc, Ch);
+  return check_launch("cascade_compose");
+}
 
 int rgp_topgru_seq_fwd(const float* xg, int ldx, int So, int Wo, const float* uzr, const float* uc, const float* sal,
                        const float* wsal, float* state, int carry, void* og_op, int ldo, float* h_f32, int B, int T,

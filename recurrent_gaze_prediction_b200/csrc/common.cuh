@@ -95,6 +95,15 @@ __device__ __forceinline__ RowInfo make_row(const rgp_tapgemm_args& a, int m) {
         r.m = f * a.S + y * a.Wp + x;
       }
       break;
+    case RGP_EPI_UP7X: {  // position-major only: dense row m = f*49 + y*7 + x -> block origin (7y, 7x) of frame f's So rows
+      const int P = a.G * a.G;
+      const int f = m / P, p = m - f * P;
+      const int y = p / a.G, x = p - y * a.G;
+      r.valid = true;
+      r.obase = (long long)f * a.So;
+      r.hy = 7 * y; r.hx = 7 * x;
+      break;
+    }
     case RGP_EPI_UP7: {   // rows = the 8x8 p-layout blocks (a,b) of the bottom state; hy, hx = 7a, 7b (operand coordinates)
       int f = m / a.S, q = m - f * a.S;
       int ya = q / a.Wp, xb = q - ya * a.Wp;

@@ -462,6 +462,9 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         const PmTile t = pm_decode(a, tile, ntiles, BN, sc.pm_rot);
         const int nt = pm_ntaps(a);
+        // RGP_EPI_UP7X: one weight set per class of the block position (first / inner / last row and column)
+        const int wcls = a.epi == RGP_EPI_UP7X
+                             ? 9 * (3 * (t.y == 0 ? 0 : (t.y == a.G - 1 ? 2 : 1)) + (t.x == 0 ? 0 : (t.x == a.G - 1 ? 2 : 1))) : 0;
         // accumulation order = the dense paths' (results equal bit for bit): convs tap-major, head k-chunk-major (slab mode)
         const bool kmajor = a.im2col == 5;
         const int n_out = kmajor ? kchunks : nt, n_in = kmajor ? nt : kchunks;
@@ -474,7 +477,7 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             uint8_t* sa = smem + stage * C::kStageBytes;
             mbar_expect_tx(&full[stage], C::kStageBytes);
             tma_load_3d(sa, &tmA, &full[stage], kc * BK, srow, t.fg * BM);
-            tma_load_2d(sa + BM * BK * 2, &tmB, &full[stage], kc * BK, tap * a.N + t.n0);
+            tma_load_2d(sa + BM * BK * 2, &tmB, &full[stage], kc * BK, (wcls + tap) * a.N + t.n0);
             if (++stage == C::kStages) { stage = 0; phase ^= 1; }
           }
         }
@@ -613,7 +616,27 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           q.m = r.m; q.flags = (r.inrange ? 1 : 0) | (r.valid ? 2 : 0); q.prow = r.prow; q.orow = r.orow;
           rl[lane] = q;
         }
-        if (quad && (a.epi == RGP_EPI_STORE_F32 || a.epi == RGP_EPI_PROJ)) {
+        if (a.epi == RGP_EPI_UP7X) {
+          // fused up-sampling + top input conv: 32 columns = 2 pixels of this row's 7x7 block x 16 gate columns
+#pragma unroll 1
+          for (int c = 0; c < BN; c += 32) {
+            float v[32];
+            tc_ld32(tbase + (uint32_t)c, v);
+            if (r.inrange) {
+#pragma unroll
+              for (int h = 0; h < 2; ++h) {
+                const int ph = (n0 + c) / 16 + h;
+                if (ph < 49) {
+                  const int py = ph / 7, px = ph - py * 7;
+                  float* o = a.out_f32 + (r.obase + (long long)(r.hy + py) * a.Wo + r.hx + px) * a.ldo;
+#pragma unroll
+                  for (int q = 0; q < 4; ++q)
+                    st4(o + 4 * q, make_float4(v[16 * h + 4 * q], v[16 * h + 4 * q + 1], v[16 * h + 4 * q + 2], v[16 * h + 4 * q + 3]));
+                }
+              }
+            }
+          }
+        } else if (quad && (a.epi == RGP_EPI_STORE_F32 || a.epi == RGP_EPI_PROJ)) {
           // Pure-store epilogues (i2h pre-activations, projection): the 8 rows a lane serves are the same for every
           // 32-column chunk of the tile, so their destination pointers are formed once per tile and a chunk is
           // TMEM -> scratch transpose -> 8 x (16-byte scratch read, [bias,] one 16-/8-byte store): ~110 instructions
@@ -866,7 +889,7 @@ int launch(const rgp_tapgemm_args& a, cudaStream_t s) {
     rc = make_map(a.A, a.rowsA, a.lda, a.K, slab ? sc.boxrows : BM, &tmA);
   }
   if (rc) return rc;
-  rc = make_map(a.Bw, (long long)a.ntaps * a.N, a.K, a.K, (slab ? sc.tg : 1) * BN, &tmB);
+  rc = make_map(a.Bw, (long long)(a.epi == RGP_EPI_UP7X ? 81 : a.ntaps) * a.N, a.K, a.K, (slab ? sc.tg : 1) * BN, &tmB);
   if (rc) return rc;
   static PerDeviceFlag attr_set = {};
   if (attr_set.need()) {
@@ -1008,9 +1031,13 @@ int tapgemm_tc(const rgp_tapgemm_args& a, cudaStream_t s) {
   if (a.im2col)
     RGP_CHECK_ARG(a.ntaps == 9 && !a.accumulate && a.G > 0 && a.M % (a.G * a.G) == 0 && a.N % 32 == 0 &&
                   a.S >= (a.G + 1) * a.Wp - 1 && a.Wp > a.G && a.im2col <= 4 &&
-                  ((a.im2col % 2 == 1 && a.epi == RGP_EPI_STORE_F32) || (a.im2col % 2 == 0 && a.epi == RGP_EPI_DX_DENSE)),
+                  ((a.im2col % 2 == 1 && a.epi == RGP_EPI_STORE_F32) || (a.im2col % 2 == 0 && a.epi == RGP_EPI_DX_DENSE) ||
+                   (a.im2col == 3 && a.epi == RGP_EPI_UP7X)),
                   "tapgemm_tc: im2col mode is a 3x3 SAME conv: 1 + RGP_EPI_STORE_F32 (forward) or 2 + RGP_EPI_DX_DENSE (its "
                   "transpose) (im2col=%d ntaps=%d epi=%d M=%d G=%d)", a.im2col, a.ntaps, a.epi, a.M, a.G);
+  RGP_CHECK_ARG(a.epi != RGP_EPI_UP7X || (a.im2col == 3 && a.G == 7 && a.N == 1024 && a.ldo >= 16 && a.ldo % 4 == 0 && a.out_f32),
+                "tapgemm_tc: RGP_EPI_UP7X is the position-major (im2col = 3) GEMM over the 7x7 grid with N = 1024 (im2col=%d G=%d N=%d)",
+                a.im2col, a.G, a.N);
   RGP_CHECK_ARG(a.lda % 8 == 0, "tapgemm_tc: lda=%d must be a multiple of 8 (16-byte TMA stride)", a.lda);
   RGP_CHECK_ARG(((uintptr_t)a.A & 15) == 0 && ((uintptr_t)a.Bw & 15) == 0, "tapgemm_tc: operands must be 16-byte aligned");
   if (a.im2col == 1 || a.im2col == 2) {

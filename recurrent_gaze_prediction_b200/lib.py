@@ -12,7 +12,7 @@ import os
 
 RGP_MAX_TAPS = 32
 (EPI_STORE_F32, EPI_PROJ, EPI_GRU_ZR, EPI_GRU_C, EPI_HEAD, EPI_STORE_OP_P, EPI_STORE_OP,
- EPI_BWD_RH, EPI_BWD_H, EPI_DHS, EPI_DX_DENSE, EPI_UP7) = range(12)
+ EPI_BWD_RH, EPI_BWD_H, EPI_DHS, EPI_DX_DENSE, EPI_UP7, EPI_UP7X) = range(13)
 
 _vp, _i, _ll, _f, _d = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_double
 
@@ -143,6 +143,7 @@ _SIGS = {
     "rgp_dense_logits": [_vp, _i, _vp, _vp, _i, _i, _i, _vp],
     # cascade top level (gaze_grcn_cascade.py:343-424)
     "rgp_topgru_seq_fwd": [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _vp, _i, _i, _i, _vp],
+    "rgp_cascade_compose": [_vp, _i, _vp, _vp, _i, _i, _vp],
     "rgp_maxout": [_vp, _i, _vp, _i, _i, _vp, _i, _vp, _i, _i, _i, _vp],
     "rgp_fill_uniform_f64": [_vp, _ll, C.c_ulonglong, _vp],
     "rgp_fill_randint_rows": [_vp, _vp, _i, _i, _i, _i, C.c_ulonglong, _vp],

@@ -59,3 +59,31 @@ def test_cascade_persistent_bottom_matches_per_step():
     assert np.abs(a[1] - b[1]).max() <= 2e-2 * np.abs(b[1]).max()
     err = np.abs(a[1] - a[2]).max(axis=(2, 3)) / a[2].max(axis=(2, 3))
     assert err.max() <= 2e-2
+
+
+@pytest.mark.parametrize("B,T,top_in", [(3, 4, 64), (5, 35, 64), (2, 3, 65)])
+def test_cascade_fused_upsampling_and_top_input_conv(B, T, top_in):
+    """RGP_EPI_UP7X: up-sampling (11x11 / stride 7) and the top cell's 5x5 input convs as ONE composed 3x3-tap GEMM over the
+    7x7 grid (rgp_cascade_compose builds the nine border classes of weights) against the two-GEMM path: the top cell's
+    input pre-activations at every real pixel (bf16 operands either way; the two-GEMM path rounds the 49x49x64 maps to
+    bf16 in between, the fused one does not: 1e-2 of the tensor's scale), then the predicted maps against the oracle."""
+    from recurrent_gaze_prediction_b200.cascade_engine import TS, TW
+    p = O.init_params_cascade(top_in=top_in, seed=4, regime="S", fc_bias_scale=0.05)
+    rng = np.random.RandomState(6)
+    c3d = torch.from_numpy(SY.make_c3d(rng, B, T)).cuda()
+    sal = torch.from_numpy(rng.uniform(size=(B, T, 49, 49)).astype(np.float32)).cuda() if top_in == 65 else None
+    xs, preds = [], []
+    for fuse in (True, False):
+        eng = CascadeEngine(B=B, T=T, dtype=1, device="cuda", top_in=top_in, fuse_top=fuse)
+        assert eng.fuse_top == fuse
+        eng.load_tf_params(p)
+        preds.append(eng.forward(c3d=c3d, frm_sal=sal).cpu().numpy().copy())
+        torch.cuda.synchronize()
+        xs.append(eng.Xg2.view(T * B, TW, TW, 16)[:, :49, :49, :9].cpu().numpy())
+    scale = np.abs(xs[1]).max()
+    assert scale > 0 and np.abs(xs[0] - xs[1]).max() <= 1e-2 * scale, (np.abs(xs[0] - xs[1]).max(), scale)
+    with torch.no_grad():
+        ref = O.cascade_network(O.to_torch(p), c3d.cpu().double(), frm_sal=None if sal is None else sal.cpu().double()).numpy()
+    for pr in preds:
+        err = np.abs(pr - ref).max(axis=(2, 3)) / ref.max(axis=(2, 3))
+        assert err.max() <= 2e-2, err.max(axis=0)
