@@ -243,6 +243,16 @@ int rgp_lstm_gates(const float* xg, int ldx, const float* hconv, const float* wc
  * bhead [16*48, Ch]. */
 int rgp_head_compose(const float* w1, const float* w2, const float* w3, const float* out_w,
                      float* w3f, float* w23, float* w123, void* bhead, int Ch, int dtype, void* stream);
+/* rgp_head_compose for callers that cannot allocate device memory (CUDA-graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same
+ * composition, same bhead [16*48, Ch] (operand dtype) bit for bit; the intermediates w3f, w23 and w123 live in a
+ * file-scope device array of the library (776 960 bytes, held by every GPU that loads the library until exit) instead of
+ * caller workspaces, so the call allocates nothing (no cudaMalloc / cudaFree / allocating library routine).
+ * Limit: Ch <= 512 - larger Ch returns -22 with a message in rgp_last_error().  The array is shared by every call on a
+ * device and keeps the last call's contents (each call overwrites all it reads, nothing needs clearing); calls that
+ * overlap on the GPU (different streams, no ordering) race on it - order them on one stream or with events. */
+int rgp_head_compose_static(const float* w1, const float* w2, const float* w3, const float* out_w, void* bhead, int Ch,
+                            int dtype, void* stream);
 /* model_util.py:61-72 + gaze_rnn.py:149-159,381-408: per-frame spatial softmax, soft-label
  * cross-entropy (or l2), and d(loss)/d(logits).  loss_type 0 xentropy, 1 l2, 2 KLD.
  * frame_loss [n_frames] fp32 per-frame partial losses (already divided by B*T);

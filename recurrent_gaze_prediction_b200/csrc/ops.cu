@@ -651,6 +651,46 @@ int rgp_head_compose(const float* w1, const float* w2, const float* w3, const fl
   return check_launch("rgp_head_compose");
 }
 
+// rgp_head_compose_static: the same four kernels with the three intermediates (w3f, w23, w123) in a file-scope device
+// array instead of caller buffers - for callers that cannot allocate (rgp.h).  In host code `g_head_scratch` is only the
+// host-side stand-in of the symbol: its device address is looked up once per device (that device current) and cached.
+constexpr int kHeadStaticMaxCh = 512;
+constexpr int kHeadW3fOff = 0;                       // [7,7,32]   1568 floats
+constexpr int kHeadW23Off = 1600;                    // [11,11,64] 7744 floats, 256-byte aligned offset
+constexpr int kHeadW123Off = 1600 + 7808;            // [19,19,Ch] 361 * Ch floats, 256-byte aligned offset
+constexpr int kHeadScratchFloats = kHeadW123Off + 361 * kHeadStaticMaxCh;      // 194 240 floats = 776 960 bytes
+static __device__ __align__(256) float g_head_scratch[kHeadScratchFloats];
+
+static float* head_scratch_ptr() {
+  static float* ptr[rgp::kMaxDevices] = {nullptr};
+  static std::mutex mu;
+  const int dev = rgp::current_device();
+  std::lock_guard<std::mutex> g(mu);
+  if (!ptr[dev]) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_head_scratch);
+    if (e != cudaSuccess || !p) {
+      rgp::set_error("rgp_head_compose_static: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+      return nullptr;
+    }
+    ptr[dev] = static_cast<float*>(p);
+  }
+  return ptr[dev];
+}
+
+int rgp_head_compose_static(const float* w1, const float* w2, const float* w3, const float* out_w, void* bhead, int Ch,
+                            int dtype, void* stream) {
+  RGP_CHECK_ARG(w1 && w2 && w3 && out_w && bhead, "rgp_head_compose_static: null pointer%s", "");
+  RGP_CHECK_ARG(dtype == 0 || dtype == 1, "rgp_head_compose_static: dtype %d", dtype);
+  RGP_CHECK_ARG(Ch > 0 && Ch <= kHeadStaticMaxCh,
+                "rgp_head_compose_static: Ch=%d is beyond the built-in scratch (at most %d channels = %d bytes); use "
+                "rgp_head_compose with caller-owned workspaces", Ch, kHeadStaticMaxCh, kHeadScratchFloats * 4);
+  float* sc = head_scratch_ptr();
+  if (!sc) return -5;
+  // every scratch element that is read below is written first by the kernel before it in stream order: nothing to clear
+  return rgp_head_compose(w1, w2, w3, out_w, sc + kHeadW3fOff, sc + kHeadW23Off, sc + kHeadW123Off, bhead, Ch, dtype, stream);
+}
+
 int rgp_softmax_xent_fwd_bwd(const float* logits, const float* gt, float* probs, float* dlogits, float* frame_loss,
                              int n_frames, int hw, float inv_bt, int loss_type, void* stream) {
   RGP_CHECK_ARG(hw > 0 && hw <= 12000, "rgp_softmax_xent_fwd_bwd: hw=%d unsupported", hw);

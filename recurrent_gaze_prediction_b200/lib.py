@@ -111,6 +111,7 @@ _SIGS = {
     "rgp_fc_head_all": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
     "rgp_lstm_gates": [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp, _vp],
     "rgp_head_compose": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp],
+    "rgp_head_compose_static": [_vp, _vp, _vp, _vp, _vp, _i, _i, _vp],
     "rgp_softmax_xent_fwd_bwd": [_vp, _vp, _vp, _vp, _vp, _i, _i, _f, _i, _vp],
     "rgp_reduce_sum": [_vp, _ll, _vp, _vp],
     "rgp_sumsq": [_vp, _ll, _vp, _vp],
