@@ -13,6 +13,9 @@
 //   * the sampled AUCs (Borji / shuffled) are gathers: one CTA per frame, one thread per repetition.
 #include <cooperative_groups.h>
 #include <math_constants.h>
+#include <stdlib.h>
+#include <type_traits>
+#include <string.h>
 #include "common.cuh"
 
 namespace cg = cooperative_groups;
@@ -945,6 +948,496 @@ sim_cc_nss_fused_kernel(const double* __restrict__ pred, const double* __restric
   }
 }
 
+// =============================================================================================
+// Lean fused sim / cc / NSS (round 2; the kernel rgp_sim_cc_nss_resized launches).  Same contract and the same per-pixel
+// value sequence as sim_cc_nss_fused_kernel above, with far fewer instructions per pixel (that kernel was issue-bound:
+// ~225 instructions per pixel, 63 of them fp64):
+//   * the column walk goes window by window: a WINDOW is the run of output rows that read the same four source rows
+//     (oh/h ~ 7 rows); window ends and the element offsets of the four tap rows come from tables (out-of-frame rows of
+//     `constant` mode point at a zero row appended to the table), both maps' row sums are interleaved (one 16-byte load
+//     per tap row), so the row loop carries no "source row changed?" test and the window prologue is ~15 instructions;
+//   * ZERO-MINIMUM passes (both clip ranges start at exactly 0: a min-max normalised prediction, a ground truth with a
+//     zero background): a value needs the clip only if it is negative or reaches the top of the range, which its HIGH 32
+//     bits decide - one unsigned integer compare per value and a warp-uniform branch around the exact float64 clip;
+//     the running extrema of the prediction are filtered the same way on high words, and the high words of attained
+//     extrema are shared through shared memory (warp redux + atomics) so a thread walking up a smooth slope does not
+//     take the exact update at every pixel.  The exact update still sees every pixel that can be the extremum;
+//   * other ranges (negative values, non-zero minimum, NaN): per window and map, a bound on the interpolant from its four
+//     taps (Catmull-Rom weights: w1, w2 >= 0, w0, w3 <= 0, |w0| + |w3| <= 1/8) decides whether ANY pixel of the window can
+//     leave the source range; windows that cannot skip the clip (a relative margin covers the rounding of the 7
+//     operations, so the decision never changes a value);
+//   * fixations are not tested per pixel: the strip's fixation bytes are staged into shared memory with cp.async during
+//     pass 1 and the resized prediction is evaluated only at the (few) fixated pixels;
+//   * the ground-truth map in pass 1 and both maps in pass 2 feed sums only, so they use fused multiply-adds (1 + 3 instead
+//     of 4 + 3 operations; values move by <= 1 ulp, sums by ~1e-16); the prediction in pass 1 keeps rgp_resize_bicubic's
+//     operation order because its extrema and its values at fixations are contractually bit-identical;
+//   * one block-wide reduction per pass (all values at once), source maps of the next frame requested with cp.async
+//     while the current frame is walked, persistent grid (as many clusters as are co-resident).
+// =============================================================================================
+constexpr int kLeanThreads = 384;
+constexpr int kLeanWarps = kLeanThreads / 32;
+
+struct LeanGeom {
+  int h, w, oh, ow, cts;
+  size_t smem_bytes() const {
+    return ((size_t)2 * h * w + (size_t)2 * (h + 1) * cts + 2 + (size_t)oh * 4 + (size_t)cts * 4) * sizeof(double) +
+           ((size_t)4 * (h + 1) + oh + cts + h + 3) * sizeof(int);
+  }
+};
+
+__device__ __forceinline__ void cp_async8(void* smem, const void* gptr) {
+  const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s), "l"(gptr) : "memory");
+}
+__device__ __forceinline__ void cp_async4(void* smem, const void* gptr) {
+  const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(s), "l"(gptr) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+// shared-memory loads on 32-bit shared addresses (the table bases live in five registers; no generic-pointer arithmetic)
+__device__ __forceinline__ unsigned sptr(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ double2 lds_d2(unsigned a) {
+  double2 v;
+  asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(a) : "memory");
+  return v;
+}
+__device__ __forceinline__ int4 lds_i4(unsigned a) {
+  int4 v;
+  asm volatile("ld.shared.v4.s32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a) : "memory");
+  return v;
+}
+__device__ __forceinline__ int lds_i(unsigned a) {
+  int v;
+  asm volatile("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
+  return v;
+}
+
+// float64 <-> unsigned keys with the same order (NaNs excluded by the caller)
+__device__ __forceinline__ unsigned long long dkey(double v) {
+  const unsigned long long u = (unsigned long long)__double_as_longlong(v);
+  return (u >> 63) ? ~u : (u | 0x8000000000000000ull);
+}
+__device__ __forceinline__ double dunkey(unsigned long long k) {
+  return __longlong_as_double((long long)((k >> 63) ? (k & 0x7fffffffffffffffull) : ~k));
+}
+__device__ __forceinline__ void lean_reset_keys(unsigned long long* skey, int* snan, int* sext) {
+  skey[0] = dkey(CUDART_INF); skey[1] = dkey(-CUDART_INF); skey[2] = dkey(CUDART_INF); skey[3] = dkey(-CUDART_INF);
+  snan[0] = 0; snan[1] = 0;
+  sext[0] = 0x7ff00000; sext[1] = (int)0xfff00000;       // high words of +inf / -inf
+}
+
+// whether no pixel of a window can leave [mnv, mxv], from the window's four taps
+__device__ __forceinline__ bool lean_window_safe(const double t[4], double mnv, double mxv) {
+  const double M12 = t[1] > t[2] ? t[1] : t[2], m12 = t[1] > t[2] ? t[2] : t[1];
+  const double M03 = t[0] > t[3] ? t[0] : t[3], m03 = t[0] > t[3] ? t[3] : t[0];
+  const double up = M12 - m03, dn = M03 - m12;
+  const double hi = M12 + 0.125 * (up > 0.0 ? up : 0.0), lo = m12 - 0.125 * (dn > 0.0 ? dn : 0.0);
+  const double margin = 4e-15 * (fabs(t[0]) + fabs(t[1]) + fabs(t[2]) + fabs(t[3]));
+  return (hi + margin <= mxv) && (lo - margin >= mnv);   // any NaN -> false
+}
+
+// rgp_resize_bicubic's value at one pixel (same operations, same order), from a window's taps
+__device__ __forceinline__ double lean_exact(const double2 w01, const double2 w23, const double t[4]) {
+  return dA(dA(dA(dM(w01.x, t[0]), dM(w01.y, t[1])), dM(w23.x, t[2])), dM(w23.y, t[3]));
+}
+__device__ __forceinline__ double lean_fma(const double2 w01, const double2 w23, const double t[4]) {
+  return fma(w23.y, t[3], fma(w23.x, t[2], fma(w01.y, t[1], w01.x * t[0])));
+}
+__device__ __forceinline__ double lean_clip(double v, double mn, double mx) {   // NaN stays NaN, as in walk_strip
+  v = (v < mn) ? mn : v;
+  v = (v > mx) ? mx : v;
+  return v;
+}
+
+// max(v, 0) for a finite v with integer operations on the two words (a negative value has the sign bit set): keeps the
+// float64 pipe for the arithmetic.  -0.0 becomes +0.0 (equal as a value).
+__device__ __forceinline__ double lean_clip0(double v) {
+  const int hi = __double2hiint(v), lo = __double2loint(v);
+  const int keep = ~(hi >> 31);
+  return __hiloint2double(hi & keep, lo & keep);
+}
+// keeps a table address in its register (without this the compiler re-derives the shared-window address per window)
+__device__ __forceinline__ unsigned lean_pin(unsigned x) {
+  asm volatile("mov.u32 %0, %0;" : "+r"(x));
+  return x;
+}
+
+struct LeanWalk {
+  int cp, nseg, seg, cl, ra, rb;
+  __device__ __forceinline__ LeanWalk(int ct, int oh) {
+    cp = (ct + 31) & ~31;                               // column slots: whole warps share a row segment
+    if (cp > (int)blockDim.x) cp = (int)blockDim.x & ~31;
+    if (cp < 32) cp = 32;
+    nseg = max(1, (int)blockDim.x / cp);
+    seg = (int)threadIdx.x / cp;
+    cl = (int)threadIdx.x - seg * cp;
+    ra = (int)(((long long)oh * seg) / nseg);
+    rb = (int)(((long long)oh * (seg + 1)) / nseg);
+    if (seg >= nseg) { ra = 0; rb = 0; }
+  }
+};
+
+struct LeanTab {                                        // shared addresses of the tables
+  unsigned rint2, wr, woff, r0s, wend;
+};
+
+// The walk of this thread's columns and row segment.  win(ta, tb) runs once per window with the taps of both maps,
+// pix(w01, w23, ta, tb) once per pixel with the row weights.  Warps take part whole: a lane whose column lies beyond the
+// strip walks the strip's last column again between dead(true) and dead(false), which save and restore the caller's sums,
+// so every *_sync vote inside win / pix may use the full mask (the lanes of a warp share the row segment and therefore
+// execute the same windows and rows).
+template <class Win, class Pix, class Dead>
+__device__ __forceinline__ void lean_walk(const LeanWalk& k, const LeanTab& T, int ct, Win&& win, Pix&& pix, Dead&& dead) {
+  if (k.ra >= k.rb) return;
+  for (int c0 = k.cl; (c0 & ~31) < ct; c0 += k.cp) {
+    const bool live = c0 < ct;
+    const int c = live ? c0 : ct - 1;
+    if (!live) dead(true);
+    const unsigned c16 = (unsigned)c * 16u;
+    int r = k.ra;
+    int j = lds_i(T.r0s + 4u * (unsigned)r) + 2;
+    while (r < k.rb) {
+      const int re = min(lds_i(T.wend + 4u * (unsigned)j), k.rb);
+      if (re > r) {                                     // (windows without rows exist only when the map is shrunk)
+        const int4 off = lds_i4(T.woff + 16u * (unsigned)j);
+        const double2 t0 = lds_d2(T.rint2 + (unsigned)off.x + c16), t1 = lds_d2(T.rint2 + (unsigned)off.y + c16);
+        const double2 t2 = lds_d2(T.rint2 + (unsigned)off.z + c16), t3 = lds_d2(T.rint2 + (unsigned)off.w + c16);
+        const double ta[4] = {t0.x, t1.x, t2.x, t3.x}, tb[4] = {t0.y, t1.y, t2.y, t3.y};
+        win(ta, tb);
+        unsigned wa = T.wr + 32u * (unsigned)r;
+#pragma unroll 2
+        for (; r < re; ++r, wa += 32u) pix(lds_d2(wa), lds_d2(wa + 16u), ta, tb);
+      }
+      ++j;
+    }
+    if (!live) dead(false);
+  }
+}
+
+__global__ void __cluster_dims__(kCluster, 1, 1) __launch_bounds__(kLeanThreads, 2)
+sim_cc_nss_lean_kernel(const double* __restrict__ pred, const double* __restrict__ gt, const uint8_t* __restrict__ fix,
+                       double* __restrict__ out, int n, int h, int w, int oh, int ow, int cts, int nearest) {
+  extern __shared__ __align__(16) double lsm[];
+  cg::cluster_group cl = cg::this_cluster();
+  __shared__ double wpart[kLeanWarps][8];
+  __shared__ double part1[8], part2[4], tot[8];
+  __shared__ unsigned long long skey[4];                 // order-preserving keys of the source extrema (min, max) x 2 maps
+  __shared__ int snan[2];
+  __shared__ int sext[2];                                // high words of the smallest / largest resized value seen so far
+  const int tid = (int)threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const int rank = (int)cl.block_rank();
+  const int ncl = gridDim.x / kCluster;
+  const int cbase = min(ow, rank * cts), ct = min(cts, ow - cbase);
+  const long long hw = (long long)oh * ow;
+  const int shw = h * w;
+  // carve: both source maps, the interleaved row-sum table (+ a zero row), row / column weights, tap-row offsets of every
+  // window, first source row / column, window ends.  Every piece is a multiple of 16 bytes up to the int tables.
+  double* simgA = lsm;
+  double* simgB = simgA + shw;
+  double* rbase = simgB + shw;
+  double2* rint2 = reinterpret_cast<double2*>(rbase + ((reinterpret_cast<uintptr_t>(rbase) >> 3) & 1));   // 16-byte aligned
+  double* wr = reinterpret_cast<double*>(rint2 + (size_t)(h + 1) * cts);
+  double* wc = wr + oh * 4;
+  int4* woff = reinterpret_cast<int4*>(wc + cts * 4);    // woff[r0 + 2] = byte offsets of the window's four tap rows
+  int* r0s = reinterpret_cast<int*>(woff + (h + 1));
+  int* c0s = r0s + oh;
+  int* wend = c0s + cts;                                 // wend[r0 + 2] = one past the last output row of window r0
+  int f = blockIdx.x / kCluster;
+  if (f < n) {
+    const double* ps = pred + (long long)f * shw;
+    const double* gs = gt + (long long)f * shw;
+    for (int i = tid; i < shw; i += kLeanThreads) { cp_async8(simgA + i, ps + i); cp_async8(simgB + i, gs + i); }
+  }
+  fused_tables(h, w, oh, ow, cbase, ct, wr, wc, r0s, c0s);
+  for (int i = tid; i < h + 3; i += kLeanThreads) wend[i] = 0;
+  for (int i = tid; i < cts; i += kLeanThreads) rint2[h * cts + i] = make_double2(0.0, 0.0);
+  for (int j = tid; j < h + 1; j += kLeanThreads) {
+    int o[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int ri = j - 2 + i;
+      o[i] = ((ri >= 0 && ri < h) ? ri : (nearest ? min(max(ri, 0), h - 1) : h)) * cts * 16;
+    }
+    woff[j] = make_int4(o[0], o[1], o[2], o[3]);
+  }
+  if (tid == 0) lean_reset_keys(skey, snan, sext);
+  __syncthreads();
+  for (int r = tid; r < oh; r += kLeanThreads)
+    if (r == oh - 1 || r0s[r + 1] != r0s[r]) wend[r0s[r] + 2] = r + 1;
+  const LeanWalk k(ct, oh);
+  LeanTab T;
+  T.rint2 = lean_pin(sptr(rint2)); T.wr = lean_pin(sptr(wr)); T.woff = lean_pin(sptr(woff));
+  T.r0s = lean_pin(sptr(r0s)); T.wend = lean_pin(sptr(wend));
+  // fixation bytes are staged through the source-map buffers as 32-bit words when the strip rows are 4-byte aligned
+  const bool fixsm = fix && (ow % 4 == 0) && (cbase % 4 == 0) && (ct % 4 == 0) && (hw % 4 == 0) &&
+                     ((reinterpret_cast<uintptr_t>(fix) & 3) == 0) && ((size_t)oh * ct <= (size_t)2 * shw * sizeof(double));
+  const int nw4 = ct >> 2;
+  int lgq = 0;                                           // word slots per strip row: a power of two >= nw4
+  while ((1 << lgq) < nw4 && (1 << lgq) < kLeanThreads) ++lgq;
+  for (; f < n; f += ncl) {
+    cp_async_wait_all();
+    __syncthreads();                                     // source maps (and, first time, the tables) are in place
+    // ---- source statistics (clip range; np.min / np.max propagate NaN): plain extrema + a NaN flag per thread, warp
+    // shuffles, then one shared-memory atomic per warp and value on order-preserving 64-bit keys
+    {
+      double amn = CUDART_INF, amx = -CUDART_INF, bmn = CUDART_INF, bmx = -CUDART_INF;
+      bool an = false, bn = false;
+      for (int i = tid; i < shw; i += kLeanThreads) {
+        const double a = simgA[i], b = simgB[i];
+        an |= (a != a); bn |= (b != b);
+        amn = (a < amn) ? a : amn; amx = (a > amx) ? a : amx;
+        bmn = (b < bmn) ? b : bmn; bmx = (b > bmx) ? b : bmx;
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        double x;
+        x = __shfl_xor_sync(0xffffffffu, amn, o); amn = (x < amn) ? x : amn;
+        x = __shfl_xor_sync(0xffffffffu, amx, o); amx = (x > amx) ? x : amx;
+        x = __shfl_xor_sync(0xffffffffu, bmn, o); bmn = (x < bmn) ? x : bmn;
+        x = __shfl_xor_sync(0xffffffffu, bmx, o); bmx = (x > bmx) ? x : bmx;
+      }
+      an = __any_sync(0xffffffffu, an); bn = __any_sync(0xffffffffu, bn);
+      if (lane == 0) {
+        atomicMin(&skey[0], dkey(amn)); atomicMax(&skey[1], dkey(amx));
+        atomicMin(&skey[2], dkey(bmn)); atomicMax(&skey[3], dkey(bmx));
+        if (an) snan[0] = 1;
+        if (bn) snan[1] = 1;
+      }
+    }
+    // ---- row sums of both maps for this strip (operation order of resize_bicubic_sep_kernel): a thread keeps its
+    // column's four source columns and weights in registers and goes down the source rows of its row group
+    if (k.seg < k.nseg)
+      for (int c = k.cl; c < ct; c += k.cp) {
+        const int c0 = c0s[c];
+        int ci[4];
+        bool zj[4];
+        double wj[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int x = c0 + j;
+          zj[j] = !nearest && !(x >= 0 && x < w);
+          ci[j] = min(max(x, 0), w - 1);
+          wj[j] = wc[4 * c + j];
+        }
+        for (int ri = k.seg; ri < h; ri += k.nseg) {
+          const double* sa_ = simgA + ri * w;
+          const double* sb_ = simgB + ri * w;
+          double ra_ = 0.0, rb_ = 0.0;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            double va = sa_[ci[j]], vb = sb_[ci[j]];
+            if (zj[j]) { va = 0.0; vb = 0.0; }
+            ra_ = dA(ra_, dM(wj[j], va));
+            rb_ = dA(rb_, dM(wj[j], vb));
+          }
+          rint2[ri * cts + c] = make_double2(ra_, rb_);
+        }
+      }
+    __syncthreads();                                     // tables + source extrema published; simgA / simgB are free
+    // fixation bytes of the strip: requested into the (now free) source-map buffers, consumed after pass 1
+    const uint8_t* fx = fix ? fix + (long long)f * hw + cbase : nullptr;
+    uint8_t* fsm8 = reinterpret_cast<uint8_t*>(simgA);
+    if (fixsm)
+      for (int r = tid >> lgq; r < oh; r += kLeanThreads >> lgq)
+        for (int q = tid & ((1 << lgq) - 1); q < nw4; q += 1 << lgq)
+          cp_async4(fsm8 + 4 * (r * nw4 + q), fx + (long long)r * ow + 4 * q);
+    double pmn = dunkey(skey[0]), pmx = dunkey(skey[1]), gmn = dunkey(skey[2]), gmx = dunkey(skey[3]);
+    if (snan[0]) { pmn = CUDART_NAN; pmx = CUDART_NAN; }
+    if (snan[1]) { gmn = CUDART_NAN; gmx = CUDART_NAN; }
+    // both ranges start at exactly 0 and end at a positive finite value: the integer-filtered passes
+    const bool zmin = pmn == 0.0 && gmn == 0.0 && pmx > 0.0 && gmx > 0.0 && pmx < CUDART_INF && gmx < CUDART_INF;
+    const unsigned pmxh = (unsigned)__double2hiint(pmx), gmxh = (unsigned)__double2hiint(gmx);
+    // ---- pass 1: sums of both maps, extrema of the prediction
+    double sp = 0.0, sg = 0.0, mn = CUDART_INF, mx = -CUDART_INF, spf = 0.0, nf = 0.0;
+    bool bad = false;
+    double keep1[2];
+    auto dead1 = [&](bool begin) {
+      if (begin) { keep1[0] = sp; keep1[1] = sg; } else { sp = keep1[0]; sg = keep1[1]; }
+    };
+    if (zmin) {
+      // filter thresholds: high words of extrema attained by any thread of the CTA (-1 for the minimum once 0 is attained:
+      // nothing is smaller after the clip)
+      int mnh = 0x7ff00000, mxh = (int)0xfff00000;
+      const unsigned sx = lean_pin(sptr(sext));
+      lean_walk(k, T, ct,
+          [&](const double*, const double*) {
+            mnh = min(mnh, lds_i(sx)); mxh = max(mxh, lds_i(sx + 4u));
+          },
+          [&](const double2 w01, const double2 w23, const double* ta, const double* tb) {
+            double a = lean_clip0(lean_exact(w01, w23, ta));
+            double b = lean_clip0(lean_fma(w01, w23, tb));
+            const int ah = __double2hiint(a);
+            const bool ca = (ah >= mxh) | (ah <= mnh);   // candidate extremum (a > pmx implies ah >= mxh: the clip is in here)
+            const bool cb = (unsigned)__double2hiint(b) >= gmxh;
+            if (__any_sync(0xffffffffu, ca | cb)) {
+              if (cb) b = (b > gmx) ? gmx : b;
+              if (ca) {
+                a = (a > pmx) ? pmx : a;
+                if (a != a) bad = true;
+                else {
+                  if (a < mn) { mn = a; mnh = (a == 0.0) ? -1 : __double2hiint(a); atomicMin(&sext[0], mnh); }
+                  if (a > mx) { mx = a; mxh = max(mxh, __double2hiint(a)); atomicMax(&sext[1], mxh); }
+                }
+              }
+            }
+            sp += a; sg += b;
+          }, dead1);
+    } else {
+      bool safe = false;
+      lean_walk(k, T, ct,
+          [&](const double* ta, const double* tb) {
+            safe = __all_sync(0xffffffffu, lean_window_safe(ta, pmn, pmx) && lean_window_safe(tb, gmn, gmx));
+          },
+          [&](const double2 w01, const double2 w23, const double* ta, const double* tb) {
+            double a = lean_exact(w01, w23, ta);
+            double b = lean_fma(w01, w23, tb);
+            if (!safe) { a = lean_clip(a, pmn, pmx); b = lean_clip(b, gmn, gmx); }
+            sp += a; sg += b;
+            if (!(a >= mn && a <= mx)) {
+              if (a != a) bad = true; else { mn = (a < mn) ? a : mn; mx = (a > mx) ? a : mx; }
+            }
+          }, dead1);
+    }
+    if (bad) { mn = CUDART_NAN; mx = CUDART_NAN; }
+    // ---- fixations of the strip: the resized prediction is evaluated only where a byte is set
+    if (fix) {
+      auto at = [&](int r, int c) {
+        const int4 off = woff[r0s[r] + 2];
+        const char* base = reinterpret_cast<const char*>(rint2 + c);
+        const double t[4] = {reinterpret_cast<const double2*>(base + off.x)->x, reinterpret_cast<const double2*>(base + off.y)->x,
+                             reinterpret_cast<const double2*>(base + off.z)->x, reinterpret_cast<const double2*>(base + off.w)->x};
+        const double2 w01 = *reinterpret_cast<const double2*>(wr + 4 * r);
+        const double2 w23 = *reinterpret_cast<const double2*>(wr + 4 * r + 2);
+        spf += lean_clip(lean_exact(w01, w23, t), pmn, pmx);
+        nf += 1.0;
+      };
+      if (fixsm) {
+        cp_async_wait_all();
+        __syncthreads();
+        const uint32_t* fw = reinterpret_cast<const uint32_t*>(fsm8);
+        for (int r = tid >> lgq; r < oh; r += kLeanThreads >> lgq)
+          for (int q = tid & ((1 << lgq) - 1); q < nw4; q += 1 << lgq) {
+            const uint32_t word = fw[r * nw4 + q];
+            if (word) {
+#pragma unroll
+              for (int b = 0; b < 4; ++b)
+                if ((word >> (8 * b)) & 0xffu) at(r, 4 * q + b);
+            }
+          }
+      } else {
+        for (int i = tid; i < oh * ct; i += kLeanThreads) {
+          const int r = i / ct, c = i - r * ct;
+          if (fx[(long long)r * ow + c]) at(r, c);
+        }
+      }
+    }
+    sp = warp_red<SumOp>(sp); sg = warp_red<SumOp>(sg);
+    mn = warp_red<MinOp>(mn); mx = warp_red<MaxOp>(mx);
+    spf = warp_red<SumOp>(spf); nf = warp_red<SumOp>(nf);
+    __syncthreads();                                     // fixation bytes consumed: the source-map buffers are free again
+    if (f + ncl < n) {                                   // next frame's sources land while pass 2 runs
+      const double* ps = pred + (long long)(f + ncl) * shw;
+      const double* gs = gt + (long long)(f + ncl) * shw;
+      for (int i = tid; i < shw; i += kLeanThreads) { cp_async8(simgA + i, ps + i); cp_async8(simgB + i, gs + i); }
+    }
+    if (lane == 0) {
+      wpart[wid][0] = sp; wpart[wid][1] = sg; wpart[wid][2] = mn; wpart[wid][3] = mx; wpart[wid][4] = spf; wpart[wid][5] = nf;
+    }
+    __syncthreads();
+    if (tid == 32) lean_reset_keys(skey, snan, sext);    // every thread used them before the barriers above
+    if (tid < 6) {
+      double r = (tid == 2) ? CUDART_INF : (tid == 3) ? -CUDART_INF : 0.0;
+      for (int q = 0; q < kLeanWarps; ++q) {
+        const double x = wpart[q][tid];
+        r = (tid == 2) ? nmin(r, x) : (tid == 3) ? nmax(r, x) : r + x;
+      }
+      part1[tid] = r;
+    }
+    cl.sync();
+    if (tid < 6) {
+      double r = (tid == 2) ? CUDART_INF : (tid == 3) ? -CUDART_INF : 0.0;
+      for (int q = 0; q < kCluster; ++q) {
+        const double x = cl.map_shared_rank(part1, q)[tid];
+        r = (tid == 2) ? nmin(r, x) : (tid == 3) ? nmax(r, x) : r + x;
+      }
+      tot[tid] = r;
+    }
+    __syncthreads();
+    const double tsp = tot[0], tsg = tot[1];
+    const double mp = tsp / (double)hw, mg = tsg / (double)hw;
+    const double rsp = dD(1.0, tsp), rsg = dD(1.0, tsg);
+    // ---- pass 2: the same pixels again from the shared-memory tables: centred second moments, histogram intersection
+    double vpp = 0.0, vgg = 0.0, vpg = 0.0, ssim = 0.0;
+    // np.minimum propagates NaN: frames whose sums are 0 / inf / NaN (cluster-uniform) take the NaN-propagating form
+    const bool plain = (tsp - tsp == 0.0) && (tsg - tsg == 0.0) && tsp != 0.0 && tsg != 0.0;
+    auto pass2 = [&](auto plain_c) {
+      constexpr bool kPlain = decltype(plain_c)::value;
+      auto moments = [&](double a, double b) {
+        const double ax = a - mp, bx = b - mg;
+        vpp = fma(ax, ax, vpp); vgg = fma(bx, bx, vgg); vpg = fma(ax, bx, vpg);
+        const double x = b * rsg, y = a * rsp;
+        if (kPlain) ssim += (y < x) ? y : x;
+        else ssim += nmin(x, y);
+      };
+      double keep2[4];
+      auto dead2 = [&](bool begin) {
+        if (begin) { keep2[0] = vpp; keep2[1] = vgg; keep2[2] = vpg; keep2[3] = ssim; }
+        else { vpp = keep2[0]; vgg = keep2[1]; vpg = keep2[2]; ssim = keep2[3]; }
+      };
+      if (zmin) {
+        lean_walk(k, T, ct, [&](const double*, const double*) {},
+            [&](const double2 w01, const double2 w23, const double* ta, const double* tb) {
+              double a = lean_clip0(lean_fma(w01, w23, ta));
+              double b = lean_clip0(lean_fma(w01, w23, tb));
+              if (__any_sync(0xffffffffu, ((unsigned)__double2hiint(a) >= pmxh) | ((unsigned)__double2hiint(b) >= gmxh))) {
+                a = (a > pmx) ? pmx : a;
+                b = (b > gmx) ? gmx : b;
+              }
+              moments(a, b);
+            }, dead2);
+      } else {
+        bool safe = false;
+        lean_walk(k, T, ct,
+            [&](const double* ta, const double* tb) {
+              safe = __all_sync(0xffffffffu, lean_window_safe(ta, pmn, pmx) && lean_window_safe(tb, gmn, gmx));
+            },
+            [&](const double2 w01, const double2 w23, const double* ta, const double* tb) {
+              double a = lean_fma(w01, w23, ta);
+              double b = lean_fma(w01, w23, tb);
+              if (!safe) { a = lean_clip(a, pmn, pmx); b = lean_clip(b, gmn, gmx); }
+              moments(a, b);
+            }, dead2);
+      }
+    };
+    if (plain) pass2(std::true_type{});
+    else pass2(std::false_type{});
+    vpp = warp_red<SumOp>(vpp); vgg = warp_red<SumOp>(vgg); vpg = warp_red<SumOp>(vpg); ssim = warp_red<SumOp>(ssim);
+    if (lane == 0) { wpart[wid][0] = vpp; wpart[wid][1] = vgg; wpart[wid][2] = vpg; wpart[wid][3] = ssim; }
+    __syncthreads();
+    if (tid < 4) {
+      double r = 0.0;
+      for (int q = 0; q < kLeanWarps; ++q) r += wpart[q][tid];
+      part2[tid] = r;
+    }
+    cl.sync();
+    if (rank == 0 && tid == 0) {
+      const double tpp = cluster_gather<SumOp>(cl, part2, 0), tgg = cluster_gather<SumOp>(cl, part2, 1);
+      const double tpg = cluster_gather<SumOp>(cl, part2, 2), tsim = cluster_gather<SumOp>(cl, part2, 3);
+      double* o = out + (long long)f * 8;
+      o[0] = tsim;
+      o[1] = tpg / (sqrt(tpp) * sqrt(tgg));
+      const double sd = sqrt(tpp / (double)hw);
+      o[2] = (tot[5] > 0.0) ? ((tot[4] / tot[5]) - mp) / sd : CUDART_NAN;
+      o[3] = tot[2]; o[4] = tot[3]; o[5] = tot[5]; o[6] = tsp; o[7] = tsg;
+    }
+    // part1 / part2 / tot of this frame are next written after the next frame's block / cluster barriers, which every
+    // reader reaches only after its reads; rank 0's remote reads of part2 are covered by the barrier after the loop
+  }
+  cp_async_wait_all();
+  cl.sync();                                             // no CTA exits while rank 0 may still read its shared memory
+}
+
 __global__ void __cluster_dims__(kCluster, 1, 1) __launch_bounds__(kStreamThreads, 2)
 auc_judd_fused_kernel(const double* __restrict__ sal, const double* __restrict__ jitter, const uint8_t* __restrict__ fix,
                       double* __restrict__ thr_out, long long* __restrict__ counts, double* __restrict__ auc,
@@ -1225,10 +1718,40 @@ int rgp_sim_cc_nss_resized(const double* pred_src, const double* gt_src, const u
                 "use rgp_resize_bicubic + rgp_sim_cc_nss", h, w, oh, ow);
   if (n == 0) return 0;
   const rgp::FusedGeom g = fused_geom(h, w, oh, ow);
-  static bool attr = false;
-  if (!attr) {
+  // The lean kernel (two source maps + a window table more in shared memory) serves every shape it fits with two CTAs per SM
+  // would-be resident; RGP_SIM_FUSED_KERNEL=old selects the first fused kernel (kept for A/B timing and as the fallback).
+  rgp::LeanGeom lg;
+  lg.h = h; lg.w = w; lg.oh = oh; lg.ow = ow; lg.cts = g.cts;
+  static const bool force_old = [] { const char* e = getenv("RGP_SIM_FUSED_KERNEL"); return e && !strcmp(e, "old"); }();
+  if (!force_old && lg.smem_bytes() <= kFusedSmemMax) {
+    static rgp::PerDeviceFlag lean_attr = {};
+    if (lean_attr.need()) {
+      cudaFuncSetAttribute(rgp::sim_cc_nss_lean_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFusedSmemMax);
+      lean_attr.set();
+    }
+    // persistent grid: as many clusters as can be co-resident for this table size (a cluster of 8 lives inside one GPC)
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(rgp::kCluster * sm_count()));
+    cfg.blockDim = dim3(rgp::kLeanThreads);
+    cfg.dynamicSmemBytes = lg.smem_bytes();
+    cudaLaunchAttribute at;
+    at.id = cudaLaunchAttributeClusterDimension;
+    at.val.clusterDim.x = rgp::kCluster; at.val.clusterDim.y = 1; at.val.clusterDim.z = 1;
+    cfg.attrs = &at; cfg.numAttrs = 1;
+    int nc = 0;
+    if (cudaOccupancyMaxActiveClusters(&nc, rgp::sim_cc_nss_lean_kernel, &cfg) != cudaSuccess || nc <= 0) {
+      cudaGetLastError();
+      nc = sm_count() / 4;
+    }
+    const int ncl = n < nc ? n : nc;
+    rgp::sim_cc_nss_lean_kernel<<<ncl * rgp::kCluster, rgp::kLeanThreads, lg.smem_bytes(), (cudaStream_t)stream>>>(
+        pred_src, gt_src, fix, out, n, h, w, oh, ow, lg.cts, mode_nearest);
+    return rgp::check_launch("rgp_sim_cc_nss_resized");
+  }
+  static rgp::PerDeviceFlag attr = {};
+  if (attr.need()) {
     cudaFuncSetAttribute(rgp::sim_cc_nss_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFusedSmemMax);
-    attr = true;
+    attr.set();
   }
   const int ncl = n < sm_count() ? n : sm_count();
   rgp::sim_cc_nss_fused_kernel<<<ncl * rgp::kCluster, rgp::kFusedThreads, g.smem_bytes(2), (cudaStream_t)stream>>>(

@@ -270,14 +270,18 @@ class MetricsEngine(object):
             p64 = self.to_f64(p32, normalize=not pred_is_normalized)
             g64 = self.to_f64(g32, normalize=False)
             # maps below fixation resolution: enlargement fused into the metric kernels (never materialised)
-            fused = bool(self.fused) and tuple(p64.shape[1:]) != (H, W) and self.fused_fits(p64.shape[1:], (H, W)) \
-                and (self.fused == "always" or 'AUC_Judd' not in metrics)
-            if fused:
+            # sim / cc / NSS always take the fused kernel when the shape fits (the enlarged ground truth is then never
+            # needed); the AUCs take the fused kernels unless AUC-Judd is requested: it reads the enlarged prediction
+            # twice and is faster on a materialised one, which the sampled AUCs then share.
+            fits = bool(self.fused) and tuple(p64.shape[1:]) != (H, W) and self.fused_fits(p64.shape[1:], (H, W))
+            fused = fits and (self.fused == "always" or 'AUC_Judd' not in metrics)
+            if fits:
                 stats = self.sim_cc_nss_resized(p64, g64, fx, (H, W))
-            else:
+            if not fused:
                 pr = self.resize(p64, (H, W), "constant")
-                gr = self.resize(g64, (H, W), "constant")
-                stats = self.sim_cc_nss(pr, gr, fx)
+                if not fits:
+                    gr = self.resize(g64, (H, W), "constant")
+                    stats = self.sim_cc_nss(pr, gr, fx)
             res = {}
             if 'AUC_Judd' in metrics:
                 if dev_j:
