@@ -1574,6 +1574,371 @@ auc_judd_fused_kernel(const double* __restrict__ sal, const double* __restrict__
   }
 }
 
+// =============================================================================================
+// Lean fused AUC-Judd (round 2; what rgp_auc_judd_resized launches; RGP_JUDD_FUSED_KERNEL=old selects auc_judd_fused_kernel).
+// The walk of sim_cc_nss_lean_kernel applied to the one map AUC-Judd reads: windows of output rows with the four tap rows
+// in registers, tap offsets / window ends from tables, the jitter values of a window's rows requested before its
+// arithmetic (<= 8 independent 8-byte loads per thread in flight), zero-minimum passes with the integer high-word filters,
+// fixation bytes staged with cp.async and visited only where set.  Every resized value keeps rgp_resize_bicubic's
+// operation sequence (no FMA: thresholds and counts are contractually bit-identical), so thr / counts / auc equal the
+// first fused kernel's and the two-step path's bit for bit.
+// =============================================================================================
+struct JuddGeom {
+  int h, w, oh, ow, cts;
+  size_t smem_bytes() const {
+    return ((size_t)h * w + (size_t)(h + 1) * cts + 2 + (size_t)oh * 4 + (size_t)cts * 4) * sizeof(double) +
+           ((size_t)4 * (h + 1) + oh + cts + h + 3) * sizeof(int) + (((size_t)oh * cts + 15) & ~(size_t)15) + 16;
+  }
+};
+
+__device__ __forceinline__ double lds_d(unsigned a) {
+  double v;
+  asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a) : "memory");
+  return v;
+}
+
+struct JuddTab {                                        // shared addresses of the tables
+  unsigned rint, wr, woff, r0s, wend;
+};
+
+// win(ta) once per window; pix(live, w01, w23, ta, j) once per pixel with its jitter value (0 when there is none).
+// Whole warps take part (lanes beyond the strip walk its last column with live = false), so votes may use the full mask.
+template <class Win, class Pix>
+__device__ __forceinline__ void judd_walk(const LeanWalk& k, const JuddTab& T, int ct, const double* __restrict__ jt, int ow,
+                                          Win&& win, Pix&& pix) {
+  if (k.ra >= k.rb) return;
+  for (int c0 = k.cl; (c0 & ~31) < ct; c0 += k.cp) {
+    const bool live = c0 < ct;
+    const int c = live ? c0 : ct - 1;
+    const unsigned c8 = (unsigned)c * 8u;
+    int r = k.ra;
+    int j = lds_i(T.r0s + 4u * (unsigned)r) + 2;
+    while (r < k.rb) {
+      const int re = min(lds_i(T.wend + 4u * (unsigned)j), k.rb);
+      if (re > r) {
+        const int4 off = lds_i4(T.woff + 16u * (unsigned)j);
+        const double ta[4] = {lds_d(T.rint + (unsigned)off.x + c8), lds_d(T.rint + (unsigned)off.y + c8),
+                              lds_d(T.rint + (unsigned)off.z + c8), lds_d(T.rint + (unsigned)off.w + c8)};
+        win(ta);
+        for (; r < re; r += 8) {                        // (a window is ~oh/h rows; 8 per block keeps the loads in registers)
+          double jv[8];
+          const double* jp = jt ? jt + (long long)r * ow + c : nullptr;
+#pragma unroll
+          for (int u = 0; u < 8; ++u) jv[u] = (jp && r + u < re) ? jp[(long long)u * ow] : 0.0;
+          const unsigned wa = T.wr + 32u * (unsigned)r;
+#pragma unroll
+          for (int u = 0; u < 8; ++u)
+            if (r + u < re) pix(live, lds_d2(wa + 32u * u), lds_d2(wa + 32u * u + 16u), ta, jv[u]);
+        }
+        r = re;
+      }
+      ++j;
+    }
+  }
+}
+
+__global__ void __cluster_dims__(kCluster, 1, 1) __launch_bounds__(kLeanThreads, 2)
+auc_judd_lean_kernel(const double* __restrict__ sal, const double* __restrict__ jitter, const uint8_t* __restrict__ fix,
+                     double* __restrict__ thr_out, long long* __restrict__ counts, double* __restrict__ auc,
+                     int n, int h, int w, int oh, int ow, int cts, int nearest, int maxfix) {
+  extern __shared__ __align__(16) double lsm[];
+  cg::cluster_group cl = cg::this_cluster();
+  __shared__ double scr[32];
+  __shared__ double part[4];
+  __shared__ double myfix[kMaxFix];
+  __shared__ double thr[kMaxFix];
+  __shared__ int hist[kMaxFix];
+  __shared__ int mycount, total_s;
+  __shared__ double mnmx[2];
+  __shared__ unsigned long long skey[4];
+  __shared__ int snan[2];
+  __shared__ int sext[2];
+  const int tid = (int)threadIdx.x, lane = tid & 31;
+  const int nt = kLeanThreads;
+  const int rank = (int)cl.block_rank();
+  const int ncl = gridDim.x / kCluster;
+  const int cbase = min(ow, rank * cts), ct = min(cts, ow - cbase);
+  const long long hw = (long long)oh * ow;
+  const int shw = h * w;
+  const bool hj = jitter != nullptr;
+  double* simg = lsm;
+  double* rbase = simg + shw;
+  double* rint = rbase + ((reinterpret_cast<uintptr_t>(rbase) >> 3) & 1);          // 16-byte aligned
+  double* wr = rint + (size_t)(h + 1) * cts;
+  wr += (reinterpret_cast<uintptr_t>(wr) >> 3) & 1;
+  double* wc = wr + oh * 4;
+  int4* woff = reinterpret_cast<int4*>(wc + cts * 4);
+  int* r0s = reinterpret_cast<int*>(woff + (h + 1));
+  int* c0s = r0s + oh;
+  int* wend = c0s + cts;
+  uint8_t* fbuf = reinterpret_cast<uint8_t*>(wend + h + 3);
+  fbuf += (16 - (reinterpret_cast<uintptr_t>(fbuf) & 15)) & 15;
+  int f = blockIdx.x / kCluster;
+  if (f < n) {
+    const double* ps = sal + (long long)f * shw;
+    for (int i = tid; i < shw; i += nt) cp_async8(simg + i, ps + i);
+  }
+  fused_tables(h, w, oh, ow, cbase, ct, wr, wc, r0s, c0s);
+  for (int i = tid; i < h + 3; i += nt) wend[i] = 0;
+  for (int i = tid; i < cts; i += nt) rint[h * cts + i] = 0.0;
+  for (int j = tid; j < h + 1; j += nt) {
+    int o[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int ri = j - 2 + i;
+      o[i] = ((ri >= 0 && ri < h) ? ri : (nearest ? min(max(ri, 0), h - 1) : h)) * cts * 8;
+    }
+    woff[j] = make_int4(o[0], o[1], o[2], o[3]);
+  }
+  if (tid == 0) lean_reset_keys(skey, snan, sext);
+  __syncthreads();
+  for (int r = tid; r < oh; r += nt)
+    if (r == oh - 1 || r0s[r + 1] != r0s[r]) wend[r0s[r] + 2] = r + 1;
+  const LeanWalk k(ct, oh);
+  JuddTab T;
+  T.rint = lean_pin(sptr(rint)); T.wr = lean_pin(sptr(wr)); T.woff = lean_pin(sptr(woff));
+  T.r0s = lean_pin(sptr(r0s)); T.wend = lean_pin(sptr(wend));
+  const bool fixsm = (ow % 4 == 0) && (cbase % 4 == 0) && (ct % 4 == 0) && (hw % 4 == 0) &&
+                     ((reinterpret_cast<uintptr_t>(fix) & 3) == 0);
+  const int nw4 = ct >> 2;
+  int lgq = 0;
+  while ((1 << lgq) < nw4 && (1 << lgq) < nt) ++lgq;
+  for (; f < n; f += ncl) {
+    const double* jt = hj ? jitter + (long long)f * hw + cbase : nullptr;
+    const uint8_t* fx = fix + (long long)f * hw + cbase;
+    cp_async_wait_all();
+    __syncthreads();                                     // source map (and, first time, the tables) in place
+    // ---- source range (np.min / np.max propagate NaN) and the strip's row sums
+    {
+      double amn = CUDART_INF, amx = -CUDART_INF;
+      bool an = false;
+      for (int i = tid; i < shw; i += nt) {
+        const double a = simg[i];
+        an |= (a != a);
+        amn = (a < amn) ? a : amn; amx = (a > amx) ? a : amx;
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        double x;
+        x = __shfl_xor_sync(0xffffffffu, amn, o); amn = (x < amn) ? x : amn;
+        x = __shfl_xor_sync(0xffffffffu, amx, o); amx = (x > amx) ? x : amx;
+      }
+      an = __any_sync(0xffffffffu, an);
+      if (lane == 0) {
+        atomicMin(&skey[0], dkey(amn)); atomicMax(&skey[1], dkey(amx));
+        if (an) snan[0] = 1;
+      }
+    }
+    if (k.seg < k.nseg)
+      for (int c = k.cl; c < ct; c += k.cp) {
+        const int c0 = c0s[c];
+        int ci[4];
+        bool zj[4];
+        double wj[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int x = c0 + j;
+          zj[j] = !nearest && !(x >= 0 && x < w);
+          ci[j] = min(max(x, 0), w - 1);
+          wj[j] = wc[4 * c + j];
+        }
+        for (int ri = k.seg; ri < h; ri += k.nseg) {
+          const double* sa_ = simg + ri * w;
+          double ra_ = 0.0;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            double va = sa_[ci[j]];
+            if (zj[j]) va = 0.0;
+            ra_ = dA(ra_, dM(wj[j], va));
+          }
+          rint[ri * cts + c] = ra_;
+        }
+      }
+    if (tid == 0) mycount = 0;
+    for (int i = tid; i < kMaxFix; i += nt) hist[i] = 0;
+    __syncthreads();                                     // tables + source range published; simg is free
+    if (fixsm)
+      for (int r = tid >> lgq; r < oh; r += nt >> lgq)
+        for (int q = tid & ((1 << lgq) - 1); q < nw4; q += 1 << lgq)
+          cp_async4(fbuf + 4 * (r * nw4 + q), fx + (long long)r * ow + 4 * q);
+    if (f + ncl < n) {                                   // next frame's source lands while this one is walked
+      const double* ps = sal + (long long)(f + ncl) * shw;
+      for (int i = tid; i < shw; i += nt) cp_async8(simg + i, ps + i);
+    }
+    double smn = dunkey(skey[0]), smx = dunkey(skey[1]);
+    if (snan[0]) { smn = CUDART_NAN; smx = CUDART_NAN; }
+    const bool zmin = smn == 0.0 && smx > 0.0 && smx < CUDART_INF;
+    const unsigned smxh = (unsigned)__double2hiint(smx);
+    const unsigned sx = lean_pin(sptr(sext));
+    bool safe = false;
+    // resized value of a pixel (rgp_resize_bicubic's operations and order, clipped to the source range) + jitter
+    auto value = [&](const double2 w01, const double2 w23, const double* ta, double j) {
+      double a = lean_exact(w01, w23, ta);
+      if (zmin) {
+        a = lean_clip0(a);
+        if (__any_sync(0xffffffffu, (unsigned)__double2hiint(a) >= smxh)) a = (a > smx) ? smx : a;
+      } else if (!safe) {
+        a = lean_clip(a, smn, smx);
+      }
+      return judd_x(a, j, hj);
+    };
+    auto window = [&](const double* ta) {
+      if (!zmin) safe = __all_sync(0xffffffffu, lean_window_safe(ta, smn, smx));
+    };
+    // ---- pass 1: extrema of the jittered resized map
+    double mn = CUDART_INF, mx = -CUDART_INF;
+    bool bad = false;
+    {
+      int mnh = 0x7ff00000, mxh = (int)0xfff00000;       // high words of extrema attained by any thread (filters)
+      judd_walk(k, T, ct, jt, ow,
+          [&](const double* ta) {
+            window(ta);
+            mnh = min(mnh, lds_i(sx)); mxh = max(mxh, lds_i(sx + 4u));
+          },
+          [&](bool, const double2 w01, const double2 w23, const double* ta, double j) {
+            const double x = value(w01, w23, ta, j);
+            const int xh = __double2hiint(x);
+            // non-negative x orders like its high word; negative values and NaNs (sign bit / 0x7ff8..) pass the filter too
+            const bool ce = (xh >= mxh) | (xh <= mnh);
+            if (__any_sync(0xffffffffu, ce)) {
+              if (ce) {
+                if (x != x) bad = true;
+                else {
+                  if (x < mn) { mn = x; if (x >= 0.0) { mnh = min(mnh, __double2hiint(x)); atomicMin(&sext[0], mnh); } }
+                  if (x > mx) { mx = x; if (x >= 0.0) { mxh = max(mxh, __double2hiint(x)); atomicMax(&sext[1], mxh); } }
+                }
+              }
+            }
+          });
+    }
+    if (bad) { mn = CUDART_NAN; mx = CUDART_NAN; }
+    // ---- values at the fixations of the strip
+    {
+      auto at = [&](int r, int c) {
+        const int4 off = woff[r0s[r] + 2];
+        const char* base = reinterpret_cast<const char*>(rint + c);
+        const double t[4] = {*reinterpret_cast<const double*>(base + off.x), *reinterpret_cast<const double*>(base + off.y),
+                             *reinterpret_cast<const double*>(base + off.z), *reinterpret_cast<const double*>(base + off.w)};
+        const double2 w01 = *reinterpret_cast<const double2*>(wr + 4 * r);
+        const double2 w23 = *reinterpret_cast<const double2*>(wr + 4 * r + 2);
+        const double a = lean_clip(lean_exact(w01, w23, t), smn, smx);
+        const double x = judd_x(a, hj ? jt[(long long)r * ow + c] : 0.0, hj);
+        const int q = atomicAdd(&mycount, 1);
+        if (q < kMaxFix) myfix[q] = x;
+      };
+      if (fixsm) {
+        cp_async_wait_all();                             // (also completes the next frame's source; it is small)
+        __syncthreads();
+        const uint32_t* fw = reinterpret_cast<const uint32_t*>(fbuf);
+        for (int r = tid >> lgq; r < oh; r += nt >> lgq)
+          for (int q = tid & ((1 << lgq) - 1); q < nw4; q += 1 << lgq) {
+            const uint32_t word = fw[r * nw4 + q];
+            if (word) {
+#pragma unroll
+              for (int b = 0; b < 4; ++b)
+                if ((word >> (8 * b)) & 0xffu) at(r, 4 * q + b);
+            }
+          }
+      } else {
+        for (int i = tid; i < oh * ct; i += nt) {
+          const int r = i / ct, c = i - r * ct;
+          if (fx[(long long)r * ow + c]) at(r, c);
+        }
+      }
+    }
+    mn = block_red<MinOp>(mn, scr); mx = block_red<MaxOp>(mx, scr);
+    if (tid == 0) { part[0] = mn; part[1] = mx; part[2] = (double)mycount; }
+    if (tid == 32) lean_reset_keys(skey, snan, sext);    // every thread used them before the barriers of block_red
+    cl.sync();
+    if (tid == 0) {
+      mnmx[0] = cluster_gather<MinOp>(cl, part, 0);
+      mnmx[1] = cluster_gather<MaxOp>(cl, part, 1);
+      total_s = (int)cluster_gather<SumOp>(cl, part, 2);
+    }
+    __syncthreads();
+    const double gmn = mnmx[0], range = dS(mnmx[1], mnmx[0]);
+    const int total = total_s;
+    const bool ok = total > 0 && total <= maxfix && total <= kMaxFix;
+    int np2 = 1;
+    while (np2 < total) np2 <<= 1;
+    if (ok) {
+      int base = 0;
+      for (int q = 0; q < kCluster; ++q) {
+        const int cq = (int)cl.map_shared_rank(part, q)[2];
+        const double* lq = cl.map_shared_rank(myfix, q);
+        for (int i = tid; i < cq; i += nt) thr[base + i] = dD(dS(lq[i], gmn), range);
+        base += cq;
+      }
+      for (int i = total + tid; i < np2; i += nt) thr[i] = -CUDART_INF;
+      __syncthreads();
+      for (int kk = 2; kk <= np2; kk <<= 1)
+        for (int j = kk >> 1; j > 0; j >>= 1) {
+          for (int i = tid; i < np2; i += nt) {
+            const int l = i ^ j;
+            if (l > i) {
+              const double a = thr[i], b = thr[l];
+              const bool desc = (i & kk) == 0;
+              if (desc ? (a < b) : (a > b)) { thr[i] = b; thr[l] = a; }
+            }
+          }
+          __syncthreads();
+        }
+      // ---- pass 2: rank every pixel against the thresholds (jitter re-read from L2, map recomputed)
+      const double lowest = thr[total - 1];
+      const double cut = lowest * range * (1.0 - 1e-12);      // see auc_judd_kernel
+      judd_walk(k, T, ct, jt, ow, window,
+          [&](bool live, const double2 w01, const double2 w23, const double* ta, double j) {
+            const double x = value(w01, w23, ta, j);
+            const double d = dS(x, gmn);
+            if (d < cut || !live) return;
+            const double vv = dD(d, range);
+            if (vv >= lowest) {
+              int lo = 0, hi = total - 1;
+              while (lo < hi) { const int mid = (lo + hi) >> 1; if (thr[mid] <= vv) hi = mid; else lo = mid + 1; }
+              atomicAdd(&hist[lo], 1);
+            }
+          });
+    }
+    cl.sync();
+    if (rank == 0) {
+      if (ok) {
+        for (int kk = tid; kk < total; kk += nt) {
+          int c = 0;
+          for (int q = 0; q < kCluster; ++q) c += cl.map_shared_rank(hist, q)[kk];
+          hist[kk] = c;
+        }
+      }
+      __syncthreads();
+      for (int kk = tid; kk < maxfix; kk += nt) {
+        thr_out[(long long)f * maxfix + kk] = (ok && kk < total) ? thr[kk] : CUDART_NAN;
+        if (!ok || kk >= total) counts[(long long)f * maxfix + kk] = -1;
+      }
+      if (tid == 0) {
+        double a = CUDART_NAN;
+        if (ok) {
+          long long above = 0;
+          double tp0 = 0.0, fp0 = 0.0, acc = 0.0;
+          const double nfix = (double)total, nneg = (double)(hw - total);
+          for (int kk = 0; kk < total; ++kk) {
+            above += hist[kk];
+            counts[(long long)f * maxfix + kk] = above;
+            const double tp1 = (double)(kk + 1) / nfix, fp1 = (double)(above - kk - 1) / nneg;
+            acc += (fp1 - fp0) * (tp1 + tp0) / 2.0;
+            tp0 = tp1; fp0 = fp1;
+          }
+          acc += (1.0 - fp0) * (1.0 + tp0) / 2.0;
+          a = acc;
+        } else if (total > 0) {
+          a = -1.0;
+        }
+        auc[f] = a;
+      }
+    }
+    cl.sync();
+  }
+  cp_async_wait_all();
+}
+
 }  // namespace
 }  // namespace rgp
 
@@ -1690,6 +2055,24 @@ rgp::FusedGeom fused_geom(int h, int w, int oh, int ow) {
   g.cts = (ow + rgp::kCluster - 1) / rgp::kCluster;
   return g;
 }
+// persistent grid of the lean kernels: as many clusters of 8 x 384 threads as can be co-resident for this table size (a
+// cluster lives inside one GPC)
+int lean_cluster_count(const void* kernel, size_t smem) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)(rgp::kCluster * sm_count()));
+  cfg.blockDim = dim3(rgp::kLeanThreads);
+  cfg.dynamicSmemBytes = smem;
+  cudaLaunchAttribute at;
+  at.id = cudaLaunchAttributeClusterDimension;
+  at.val.clusterDim.x = rgp::kCluster; at.val.clusterDim.y = 1; at.val.clusterDim.z = 1;
+  cfg.attrs = &at; cfg.numAttrs = 1;
+  int nc = 0;
+  if (cudaOccupancyMaxActiveClusters(&nc, kernel, &cfg) != cudaSuccess || nc <= 0) {
+    cudaGetLastError();
+    nc = sm_count() / 4;
+  }
+  return nc;
+}
 constexpr size_t kFusedSmemMax = 160 * 1024;   // + <= 21 KB static in the AUC-Judd kernel
 }  // namespace
 
@@ -1729,20 +2112,7 @@ int rgp_sim_cc_nss_resized(const double* pred_src, const double* gt_src, const u
       cudaFuncSetAttribute(rgp::sim_cc_nss_lean_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFusedSmemMax);
       lean_attr.set();
     }
-    // persistent grid: as many clusters as can be co-resident for this table size (a cluster of 8 lives inside one GPC)
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)(rgp::kCluster * sm_count()));
-    cfg.blockDim = dim3(rgp::kLeanThreads);
-    cfg.dynamicSmemBytes = lg.smem_bytes();
-    cudaLaunchAttribute at;
-    at.id = cudaLaunchAttributeClusterDimension;
-    at.val.clusterDim.x = rgp::kCluster; at.val.clusterDim.y = 1; at.val.clusterDim.z = 1;
-    cfg.attrs = &at; cfg.numAttrs = 1;
-    int nc = 0;
-    if (cudaOccupancyMaxActiveClusters(&nc, rgp::sim_cc_nss_lean_kernel, &cfg) != cudaSuccess || nc <= 0) {
-      cudaGetLastError();
-      nc = sm_count() / 4;
-    }
+    const int nc = lean_cluster_count((const void*)rgp::sim_cc_nss_lean_kernel, lg.smem_bytes());
     const int ncl = n < nc ? n : nc;
     rgp::sim_cc_nss_lean_kernel<<<ncl * rgp::kCluster, rgp::kLeanThreads, lg.smem_bytes(), (cudaStream_t)stream>>>(
         pred_src, gt_src, fix, out, n, h, w, oh, ow, lg.cts, mode_nearest);
@@ -1767,10 +2137,25 @@ int rgp_auc_judd_resized(const double* sal_src, const double* jitter, const uint
                 "use rgp_resize_bicubic + rgp_auc_judd", h, w, oh, ow);
   if (n == 0) return 0;
   const rgp::FusedGeom g = fused_geom(h, w, oh, ow);
-  static bool attr = false;
-  if (!attr) {
+  rgp::JuddGeom jg;
+  jg.h = h; jg.w = w; jg.oh = oh; jg.ow = ow; jg.cts = g.cts;
+  static const bool force_old = [] { const char* e = getenv("RGP_JUDD_FUSED_KERNEL"); return e && !strcmp(e, "old"); }();
+  if (!force_old && jg.smem_bytes() <= kFusedSmemMax) {
+    static rgp::PerDeviceFlag lean_attr = {};
+    if (lean_attr.need()) {
+      cudaFuncSetAttribute(rgp::auc_judd_lean_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFusedSmemMax);
+      lean_attr.set();
+    }
+    const int nc = lean_cluster_count((const void*)rgp::auc_judd_lean_kernel, jg.smem_bytes());
+    const int ncl = n < nc ? n : nc;
+    rgp::auc_judd_lean_kernel<<<ncl * rgp::kCluster, rgp::kLeanThreads, jg.smem_bytes(), (cudaStream_t)stream>>>(
+        sal_src, jitter, fix, thr, counts, auc, n, h, w, oh, ow, jg.cts, mode_nearest, maxfix);
+    return rgp::check_launch("rgp_auc_judd_resized");
+  }
+  static rgp::PerDeviceFlag attr = {};
+  if (attr.need()) {
     cudaFuncSetAttribute(rgp::auc_judd_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFusedSmemMax);
-    attr = true;
+    attr.set();
   }
   const int ncl = n < sm_count() ? n : sm_count();
   rgp::auc_judd_fused_kernel<<<ncl * rgp::kCluster, rgp::kStreamThreads, g.smem_bytes(1), (cudaStream_t)stream>>>(
