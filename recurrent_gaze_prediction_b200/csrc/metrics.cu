@@ -723,8 +723,9 @@ struct FusedGeom {
 
 // frame-independent tables of this CTA's strip: row weights / first source row of every output row, column weights /
 // first source column of every strip column
-__device__ __forceinline__ void fused_tables(int h, int w, int oh, int ow, int cbase, int ct, double* wr, double* wc,
-                                             int* r0s, int* c0s) {
+template <class Cols>
+__device__ __forceinline__ void fused_tables_cols(int h, int w, int oh, int ow, const Cols& cols, int ct, double* wr,
+                                                  double* wc, int* r0s, int* c0s) {
   const double sr = dD((double)h, (double)oh), sc = dD((double)w, (double)ow);
   for (int r = threadIdx.x; r < oh; r += blockDim.x) {
     const double rs = dS(dM(dA((double)r, 0.5), sr), 0.5), rf = floor(rs);
@@ -732,10 +733,20 @@ __device__ __forceinline__ void fused_tables(int h, int w, int oh, int ow, int c
     r0s[r] = (int)rf - 1;
   }
   for (int c = threadIdx.x; c < ct; c += blockDim.x) {
-    const double cs = dS(dM(dA((double)(cbase + c), 0.5), sc), 0.5), cf = floor(cs);
+    const double cs = dS(dM(dA((double)cols(c), 0.5), sc), 0.5), cf = floor(cs);
     cubic_w(dS(cs, cf), wc + 4 * c);
     c0s[c] = (int)cf - 1;
   }
+}
+struct ContigCols {
+  int cbase;
+  __device__ __forceinline__ int operator()(int c) const { return cbase + c; }
+};
+__device__ __forceinline__ void fused_tables(int h, int w, int oh, int ow, int cbase, int ct, double* wr, double* wc,
+                                             int* r0s, int* c0s) {
+  ContigCols cc;
+  cc.cbase = cbase;
+  fused_tables_cols(h, w, oh, ow, cc, ct, wr, wc, r0s, c0s);
 }
 
 // source frame -> shared image, its (NaN-propagating) range, and the strip's row sums.  Ends with a barrier.
@@ -1063,6 +1074,19 @@ __device__ __forceinline__ unsigned lean_pin(unsigned x) {
   return x;
 }
 
+// Strip column -> frame column.  Contiguous strips by default.  The interleaved mapping (CTA q owns columns
+// 4*(q + 8*g) .. +3 of a width that is a multiple of 32, meant to spread the salient region's data-dependent work - clips,
+// extremum candidates, pixels above the lowest AUC threshold - over the 8 CTAs of a cluster) is kept behind a constant:
+// measured SLOWER (sim/cc/NSS 1.31 -> 1.38 ms, AUC-Judd 2.28 -> 2.41 ms per 1024 frames): the rare paths are taken per
+// WARP (votes), and interleaving puts a few salient columns into every warp instead of all of them into a few warps.
+constexpr bool kLeanInterleave = false;
+struct LeanCols {
+  int il, rank, cbase;
+  __device__ __forceinline__ int operator()(int c) const {
+    return il ? 4 * (rank + kCluster * (c >> 2)) + (c & 3) : cbase + c;
+  }
+};
+
 struct LeanWalk {
   int cp, nseg, seg, cl, ra, rb;
   __device__ __forceinline__ LeanWalk(int ct, int oh) {
@@ -1149,7 +1173,9 @@ sim_cc_nss_lean_kernel(const double* __restrict__ pred, const double* __restrict
     const double* gs = gt + (long long)f * shw;
     for (int i = tid; i < shw; i += kLeanThreads) { cp_async8(simgA + i, ps + i); cp_async8(simgB + i, gs + i); }
   }
-  fused_tables(h, w, oh, ow, cbase, ct, wr, wc, r0s, c0s);
+  LeanCols cols;
+  cols.il = kLeanInterleave && (ow % (4 * kCluster)) == 0; cols.rank = rank; cols.cbase = cbase;
+  fused_tables_cols(h, w, oh, ow, cols, ct, wr, wc, r0s, c0s);
   for (int i = tid; i < h + 3; i += kLeanThreads) wend[i] = 0;
   for (int i = tid; i < cts; i += kLeanThreads) rint2[h * cts + i] = make_double2(0.0, 0.0);
   for (int j = tid; j < h + 1; j += kLeanThreads) {
@@ -1170,7 +1196,7 @@ sim_cc_nss_lean_kernel(const double* __restrict__ pred, const double* __restrict
   T.rint2 = lean_pin(sptr(rint2)); T.wr = lean_pin(sptr(wr)); T.woff = lean_pin(sptr(woff));
   T.r0s = lean_pin(sptr(r0s)); T.wend = lean_pin(sptr(wend));
   // fixation bytes are staged through the source-map buffers as 32-bit words when the strip rows are 4-byte aligned
-  const bool fixsm = fix && (ow % 4 == 0) && (cbase % 4 == 0) && (ct % 4 == 0) && (hw % 4 == 0) &&
+  const bool fixsm = fix && (ow % 4 == 0) && (cols(0) % 4 == 0) && (ct % 4 == 0) && (hw % 4 == 0) &&
                      ((reinterpret_cast<uintptr_t>(fix) & 3) == 0) && ((size_t)oh * ct <= (size_t)2 * shw * sizeof(double));
   const int nw4 = ct >> 2;
   int lgq = 0;                                           // word slots per strip row: a power of two >= nw4
@@ -1236,12 +1262,12 @@ sim_cc_nss_lean_kernel(const double* __restrict__ pred, const double* __restrict
       }
     __syncthreads();                                     // tables + source extrema published; simgA / simgB are free
     // fixation bytes of the strip: requested into the (now free) source-map buffers, consumed after pass 1
-    const uint8_t* fx = fix ? fix + (long long)f * hw + cbase : nullptr;
+    const uint8_t* fx = fix ? fix + (long long)f * hw : nullptr;
     uint8_t* fsm8 = reinterpret_cast<uint8_t*>(simgA);
     if (fixsm)
       for (int r = tid >> lgq; r < oh; r += kLeanThreads >> lgq)
         for (int q = tid & ((1 << lgq) - 1); q < nw4; q += 1 << lgq)
-          cp_async4(fsm8 + 4 * (r * nw4 + q), fx + (long long)r * ow + 4 * q);
+          cp_async4(fsm8 + 4 * (r * nw4 + q), fx + (long long)r * ow + cols(4 * q));
     double pmn = dunkey(skey[0]), pmx = dunkey(skey[1]), gmn = dunkey(skey[2]), gmx = dunkey(skey[3]);
     if (snan[0]) { pmn = CUDART_NAN; pmx = CUDART_NAN; }
     if (snan[1]) { gmn = CUDART_NAN; gmx = CUDART_NAN; }
@@ -1328,7 +1354,7 @@ sim_cc_nss_lean_kernel(const double* __restrict__ pred, const double* __restrict
       } else {
         for (int i = tid; i < oh * ct; i += kLeanThreads) {
           const int r = i / ct, c = i - r * ct;
-          if (fx[(long long)r * ow + c]) at(r, c);
+          if (fx[(long long)r * ow + cols(c)]) at(r, c);
         }
       }
     }
@@ -1604,8 +1630,8 @@ struct JuddTab {                                        // shared addresses of t
 // win(ta) once per window; pix(live, w01, w23, ta, j) once per pixel with its jitter value (0 when there is none).
 // Whole warps take part (lanes beyond the strip walk its last column with live = false), so votes may use the full mask.
 template <class Win, class Pix>
-__device__ __forceinline__ void judd_walk(const LeanWalk& k, const JuddTab& T, int ct, const double* __restrict__ jt, int ow,
-                                          Win&& win, Pix&& pix) {
+__device__ __forceinline__ void judd_walk(const LeanWalk& k, const JuddTab& T, int ct, const LeanCols& cols,
+                                          const double* __restrict__ jt, int ow, Win&& win, Pix&& pix) {
   if (k.ra >= k.rb) return;
   for (int c0 = k.cl; (c0 & ~31) < ct; c0 += k.cp) {
     const bool live = c0 < ct;
@@ -1622,7 +1648,7 @@ __device__ __forceinline__ void judd_walk(const LeanWalk& k, const JuddTab& T, i
         win(ta);
         for (; r < re; r += 8) {                        // (a window is ~oh/h rows; 8 per block keeps the loads in registers)
           double jv[8];
-          const double* jp = jt ? jt + (long long)r * ow + c : nullptr;
+          const double* jp = jt ? jt + (long long)r * ow + cols(c) : nullptr;
 #pragma unroll
           for (int u = 0; u < 8; ++u) jv[u] = (jp && r + u < re) ? jp[(long long)u * ow] : 0.0;
           const unsigned wa = T.wr + 32u * (unsigned)r;
@@ -1637,6 +1663,7 @@ __device__ __forceinline__ void judd_walk(const LeanWalk& k, const JuddTab& T, i
   }
 }
 
+template <bool hj>                                       // hj: a jitter tensor is given
 __global__ void __cluster_dims__(kCluster, 1, 1) __launch_bounds__(kLeanThreads, 2)
 auc_judd_lean_kernel(const double* __restrict__ sal, const double* __restrict__ jitter, const uint8_t* __restrict__ fix,
                      double* __restrict__ thr_out, long long* __restrict__ counts, double* __restrict__ auc,
@@ -1660,7 +1687,6 @@ auc_judd_lean_kernel(const double* __restrict__ sal, const double* __restrict__ 
   const int cbase = min(ow, rank * cts), ct = min(cts, ow - cbase);
   const long long hw = (long long)oh * ow;
   const int shw = h * w;
-  const bool hj = jitter != nullptr;
   double* simg = lsm;
   double* rbase = simg + shw;
   double* rint = rbase + ((reinterpret_cast<uintptr_t>(rbase) >> 3) & 1);          // 16-byte aligned
@@ -1678,7 +1704,9 @@ auc_judd_lean_kernel(const double* __restrict__ sal, const double* __restrict__ 
     const double* ps = sal + (long long)f * shw;
     for (int i = tid; i < shw; i += nt) cp_async8(simg + i, ps + i);
   }
-  fused_tables(h, w, oh, ow, cbase, ct, wr, wc, r0s, c0s);
+  LeanCols cols;
+  cols.il = kLeanInterleave && (ow % (4 * kCluster)) == 0; cols.rank = rank; cols.cbase = cbase;
+  fused_tables_cols(h, w, oh, ow, cols, ct, wr, wc, r0s, c0s);
   for (int i = tid; i < h + 3; i += nt) wend[i] = 0;
   for (int i = tid; i < cts; i += nt) rint[h * cts + i] = 0.0;
   for (int j = tid; j < h + 1; j += nt) {
@@ -1698,14 +1726,20 @@ auc_judd_lean_kernel(const double* __restrict__ sal, const double* __restrict__ 
   JuddTab T;
   T.rint = lean_pin(sptr(rint)); T.wr = lean_pin(sptr(wr)); T.woff = lean_pin(sptr(woff));
   T.r0s = lean_pin(sptr(r0s)); T.wend = lean_pin(sptr(wend));
-  const bool fixsm = (ow % 4 == 0) && (cbase % 4 == 0) && (ct % 4 == 0) && (hw % 4 == 0) &&
+  const bool fixsm = (ow % 4 == 0) && (cols(0) % 4 == 0) && (ct % 4 == 0) && (hw % 4 == 0) &&
                      ((reinterpret_cast<uintptr_t>(fix) & 3) == 0);
   const int nw4 = ct >> 2;
   int lgq = 0;
   while ((1 << lgq) < nw4 && (1 << lgq) < nt) ++lgq;
   for (; f < n; f += ncl) {
-    const double* jt = hj ? jitter + (long long)f * hw + cbase : nullptr;
-    const uint8_t* fx = fix + (long long)f * hw + cbase;
+    const double* jt = hj ? jitter + (long long)f * hw : nullptr;
+    const uint8_t* fx = fix + (long long)f * hw;
+    if (hj) {                                            // the frame's jitter starts towards L2 now: every CTA asks for 1/8 of its lines
+      const char* jb = reinterpret_cast<const char*>(jt);
+      const long long nlines = (hw * 8 + 127) >> 7;
+      for (long long i = rank + (long long)kCluster * tid; i < nlines; i += (long long)kCluster * nt)
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(jb + (i << 7)));
+    }
     cp_async_wait_all();
     __syncthreads();                                     // source map (and, first time, the tables) in place
     // ---- source range (np.min / np.max propagate NaN) and the strip's row sums
@@ -1760,7 +1794,7 @@ auc_judd_lean_kernel(const double* __restrict__ sal, const double* __restrict__ 
     if (fixsm)
       for (int r = tid >> lgq; r < oh; r += nt >> lgq)
         for (int q = tid & ((1 << lgq) - 1); q < nw4; q += 1 << lgq)
-          cp_async4(fbuf + 4 * (r * nw4 + q), fx + (long long)r * ow + 4 * q);
+          cp_async4(fbuf + 4 * (r * nw4 + q), fx + (long long)r * ow + cols(4 * q));
     if (f + ncl < n) {                                   // next frame's source lands while this one is walked
       const double* ps = sal + (long long)(f + ncl) * shw;
       for (int i = tid; i < shw; i += nt) cp_async8(simg + i, ps + i);
@@ -1790,7 +1824,7 @@ auc_judd_lean_kernel(const double* __restrict__ sal, const double* __restrict__ 
     bool bad = false;
     {
       int mnh = 0x7ff00000, mxh = (int)0xfff00000;       // high words of extrema attained by any thread (filters)
-      judd_walk(k, T, ct, jt, ow,
+      judd_walk(k, T, ct, cols, jt, ow,
           [&](const double* ta) {
             window(ta);
             mnh = min(mnh, lds_i(sx)); mxh = max(mxh, lds_i(sx + 4u));
@@ -1822,7 +1856,7 @@ auc_judd_lean_kernel(const double* __restrict__ sal, const double* __restrict__ 
         const double2 w01 = *reinterpret_cast<const double2*>(wr + 4 * r);
         const double2 w23 = *reinterpret_cast<const double2*>(wr + 4 * r + 2);
         const double a = lean_clip(lean_exact(w01, w23, t), smn, smx);
-        const double x = judd_x(a, hj ? jt[(long long)r * ow + c] : 0.0, hj);
+        const double x = judd_x(a, hj ? jt[(long long)r * ow + cols(c)] : 0.0, hj);
         const int q = atomicAdd(&mycount, 1);
         if (q < kMaxFix) myfix[q] = x;
       };
@@ -1842,7 +1876,7 @@ auc_judd_lean_kernel(const double* __restrict__ sal, const double* __restrict__ 
       } else {
         for (int i = tid; i < oh * ct; i += nt) {
           const int r = i / ct, c = i - r * ct;
-          if (fx[(long long)r * ow + c]) at(r, c);
+          if (fx[(long long)r * ow + cols(c)]) at(r, c);
         }
       }
     }
@@ -1886,7 +1920,7 @@ auc_judd_lean_kernel(const double* __restrict__ sal, const double* __restrict__ 
       // ---- pass 2: rank every pixel against the thresholds (jitter re-read from L2, map recomputed)
       const double lowest = thr[total - 1];
       const double cut = lowest * range * (1.0 - 1e-12);      // see auc_judd_kernel
-      judd_walk(k, T, ct, jt, ow, window,
+      judd_walk(k, T, ct, cols, jt, ow, window,
           [&](bool live, const double2 w01, const double2 w23, const double* ta, double j) {
             const double x = value(w01, w23, ta, j);
             const double d = dS(x, gmn);
@@ -2143,13 +2177,18 @@ int rgp_auc_judd_resized(const double* sal_src, const double* jitter, const uint
   if (!force_old && jg.smem_bytes() <= kFusedSmemMax) {
     static rgp::PerDeviceFlag lean_attr = {};
     if (lean_attr.need()) {
-      cudaFuncSetAttribute(rgp::auc_judd_lean_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFusedSmemMax);
+      cudaFuncSetAttribute(rgp::auc_judd_lean_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFusedSmemMax);
+      cudaFuncSetAttribute(rgp::auc_judd_lean_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFusedSmemMax);
       lean_attr.set();
     }
-    const int nc = lean_cluster_count((const void*)rgp::auc_judd_lean_kernel, jg.smem_bytes());
+    const int nc = lean_cluster_count((const void*)rgp::auc_judd_lean_kernel<true>, jg.smem_bytes());
     const int ncl = n < nc ? n : nc;
-    rgp::auc_judd_lean_kernel<<<ncl * rgp::kCluster, rgp::kLeanThreads, jg.smem_bytes(), (cudaStream_t)stream>>>(
-        sal_src, jitter, fix, thr, counts, auc, n, h, w, oh, ow, jg.cts, mode_nearest, maxfix);
+    if (jitter)
+      rgp::auc_judd_lean_kernel<true><<<ncl * rgp::kCluster, rgp::kLeanThreads, jg.smem_bytes(), (cudaStream_t)stream>>>(
+          sal_src, jitter, fix, thr, counts, auc, n, h, w, oh, ow, jg.cts, mode_nearest, maxfix);
+    else
+      rgp::auc_judd_lean_kernel<false><<<ncl * rgp::kCluster, rgp::kLeanThreads, jg.smem_bytes(), (cudaStream_t)stream>>>(
+          sal_src, jitter, fix, thr, counts, auc, n, h, w, oh, ow, jg.cts, mode_nearest, maxfix);
     return rgp::check_launch("rgp_auc_judd_resized");
   }
   static rgp::PerDeviceFlag attr = {};

@@ -66,9 +66,9 @@ class MetricsEngine(object):
         self.lib = lib if lib is not None else L.get_lib()
         self.chunk = chunk
         # fused: the bicubic enlargement of the model maps is evaluated inside the metric kernels (rgp_*_resized) and
-        # never written to HBM.  True = where it is the faster path (measured, profiles/r01_notes.md pass 6): metric
-        # sets without AUC_Judd — the reference's AVAILABLE_METRICS; with AUC_Judd the enlarged prediction is needed
-        # twice more and the two-step path (rgp_resize_bicubic + plain kernels) wins.  "always" / False force a path.
+        # never written to HBM.  True / "always" = whenever the shape fits the kernels' tables: with the lean kernels of
+        # round 2 that is the faster path for every metric set (profiles/r02_notes.md, passes 25-33; in round 1 the
+        # two-step path won when AUC_Judd was requested).  False forces rgp_resize_bicubic + the plain kernels.
         self.fused = fused
 
     def _s(self):
@@ -270,18 +270,16 @@ class MetricsEngine(object):
             p64 = self.to_f64(p32, normalize=not pred_is_normalized)
             g64 = self.to_f64(g32, normalize=False)
             # maps below fixation resolution: enlargement fused into the metric kernels (never materialised)
-            # sim / cc / NSS always take the fused kernel when the shape fits (the enlarged ground truth is then never
-            # needed); the AUCs take the fused kernels unless AUC-Judd is requested: it reads the enlarged prediction
-            # twice and is faster on a materialised one, which the sampled AUCs then share.
-            fits = bool(self.fused) and tuple(p64.shape[1:]) != (H, W) and self.fused_fits(p64.shape[1:], (H, W))
-            fused = fits and (self.fused == "always" or 'AUC_Judd' not in metrics)
-            if fits:
+            # maps below fixation resolution: the enlargement is evaluated inside the metric kernels (never materialised).
+            # With the lean kernels of round 2 this is the faster path for every metric set, AUC-Judd included
+            # (DESIGN.md section 5); fused=False forces the two-step path.
+            fused = bool(self.fused) and tuple(p64.shape[1:]) != (H, W) and self.fused_fits(p64.shape[1:], (H, W))
+            if fused:
                 stats = self.sim_cc_nss_resized(p64, g64, fx, (H, W))
-            if not fused:
+            else:
                 pr = self.resize(p64, (H, W), "constant")
-                if not fits:
-                    gr = self.resize(g64, (H, W), "constant")
-                    stats = self.sim_cc_nss(pr, gr, fx)
+                gr = self.resize(g64, (H, W), "constant")
+                stats = self.sim_cc_nss(pr, gr, fx)
             res = {}
             if 'AUC_Judd' in metrics:
                 if dev_j:
