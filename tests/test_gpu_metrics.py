@@ -263,3 +263,53 @@ def test_device_rng_kernels_and_fast_evaluation_mode():
     for m in ("AUC_Judd", "AUC_Borji", "AUC_shuffled"):
         ok = np.isfinite(a[m])
         assert np.abs(a[m][ok] - b[m][ok]).max() < 0.08, m
+
+
+def _edge_maps(kind, rng, n, h=49, w=49):
+    """source maps that drive the lean fused kernels through their other paths (csrc/metrics.cu: zero-minimum passes with
+    saturated extrema, the bound-based passes for negative values / a non-zero minimum)."""
+    base = rng.uniform(size=(n, h, w))
+    if kind == "plateaus":             # exact zeros and an exact plateau at the maximum: clipped-to-range runs, min = 0 attained
+        m = np.clip((base - 0.3) / 0.4, 0.0, 1.0)
+        m[:, :6] = 0.0
+        m[:, -5:, 10:30] = 1.0
+        return m, np.clip((rng.uniform(size=(n, h, w)) - 0.5) * 4.0, 0.0, 1.0)
+    if kind == "negative":             # values of both signs, non-zero minimum: per-window overshoot bounds
+        return base * 3.0 - 0.5, base[::-1] * 2.0 - 0.25
+    if kind == "offset":               # strictly positive, minimum > 0
+        return base + 0.5, 2.0 + np.sin(base * 7.0)
+    raise ValueError(kind)
+
+
+@pytest.mark.parametrize("kind", ["plateaus", "negative", "offset"])
+@pytest.mark.parametrize("shape", [(360, 480), (93, 130), (20, 24)])
+def test_lean_fused_kernels_other_ranges_equal_two_step_path(eng, kind, shape):
+    """rgp_sim_cc_nss_resized / rgp_auc_judd_resized (lean kernels) against rgp_resize_bicubic + the plain kernels on maps that
+    are NOT min-max normalised: negative values, non-zero minima, exact plateaus at both ends of the range; enlarging,
+    non-multiple-of-4 widths (byte path of the fixation scan) and shrinking (windows without rows).  Extrema, n_fix,
+    thresholds, counts and AUCs bit-identical; sim / cc / NSS within 1e-12 relative (summation order, FMA in sum-only terms)."""
+    H, W = shape
+    rng = np.random.RandomState(sum(map(ord, kind)) * 1000 + H)
+    n = 5
+    p, g = _edge_maps(kind, rng, n)
+    fix = (rng.uniform(size=(n, H, W)) < 12.0 / (H * W)).astype(np.uint8)
+    fix[:, H // 2, W // 3] = 1
+    fix[3] = 0                                              # a frame without fixations
+    p64 = torch.from_numpy(p).cuda()
+    g64 = torch.from_numpy(np.ascontiguousarray(g)).cuda()
+    fx = torch.from_numpy(fix).cuda()
+    jit = torch.from_numpy(rng.rand(n, H, W)).cuda()
+    for mode in ("constant", "nearest"):
+        sa = eng.sim_cc_nss_resized(p64, g64, fx, shape, mode).cpu().numpy()
+        pr, gr = eng.resize(p64, shape, mode), eng.resize(g64, shape, mode)
+        sb = eng.sim_cc_nss(pr, gr, fx).cpu().numpy()
+        assert np.array_equal(sa[:, 3:6], sb[:, 3:6]), (mode, sa[:, 3:6], sb[:, 3:6])
+        assert np.array_equal(np.isnan(sa), np.isnan(sb))
+        ok = ~np.isnan(sb)
+        scale = np.maximum(np.abs(sb[ok]), 1.0)
+        assert (np.abs(sa[ok] - sb[ok]) / scale).max() <= 1e-12, (mode, np.abs(sa[ok] - sb[ok]).max())
+        for jd in (jit, None):
+            a1, t1, c1 = eng.auc_judd_resized(p64, fx, shape, jd, 64, mode)
+            a2, t2, c2 = eng.auc_judd(pr, fx, jd, 64)
+            assert torch.equal(c1, c2) and torch.equal(t1.nan_to_num(-7.0), t2.nan_to_num(-7.0))
+            assert np.array_equal(a1.cpu().numpy(), a2.cpu().numpy(), equal_nan=True)
