@@ -282,6 +282,14 @@ int rgp_adam_schedule(long long* step, const double* lr0, double decay, int deca
 int rgp_gradnorm_clip_adam_dev(float* p, const float* g, float* m, float* v, long long n, const double* sumsq,
                                float clip, const float* lr_t_dev, float beta1, float beta2, float eps, void* p_op,
                                int dtype, void* stream);
+/* models/base.py:270-273: the reference's other optimisers in TF1's update rules, on the globally clipped gradient
+ * (base.py:287-291).  kind 0 = tf.train.MomentumOptimizer(lr, momentum): acc = momentum*acc + g; p -= lr*acc.
+ * kind 1 = tf.train.RMSPropOptimizer(lr, decay, momentum, epsilon): ms = decay*ms + (1-decay)*g^2 (ms starts at 1);
+ * acc = momentum*acc + lr*g/sqrt(ms+eps); p -= acc.  lr = sched[1] as left by rgp_adam_schedule (which also advances the
+ * device-side global_step).  ms may be NULL for kind 0.  p_op: optional bf16 / fp32 operand copy of p (dtype 1 / 0). */
+int rgp_gradnorm_clip_momentum_dev(float* p, const float* g, float* acc, float* ms, long long n, const double* sumsq,
+                                   float clip, const float* sched, int kind, float momentum, float rms_decay, float eps,
+                                   void* p_op, int dtype, void* stream);
 int rgp_zero(void* p, long long bytes, void* stream);
 /* gaze_rnn.py:504-510 (random h-flip of half the batch) on the fed device buffers: x is [n_clips, rows_per_clip, W]
  * fp32; for each of the nsel clip indices in `clips` (device int32) every W-row is reversed in place. */

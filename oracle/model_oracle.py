@@ -473,6 +473,26 @@ def adam_step(params, grads, m, v, step_t, lr, beta1=0.9, beta2=0.999, eps=1e-8)
     return params, m, v
 
 
+def momentum_step(params, grads, accum, lr, momentum=0.9):
+    """tf.train.MomentumOptimizer(lr, momentum=0.9) (models/base.py:272-273) [TF-lib ApplyMomentum, use_nesterov=False]:
+    accum = momentum * accum + g; theta -= lr * accum."""
+    for i in range(len(params)):
+        accum[i] = momentum * accum[i] + grads[i]
+        params[i] = params[i] - lr * accum[i]
+    return params, accum
+
+
+def rmsprop_step(params, grads, ms, mom, lr, decay=0.9, momentum=0.9, eps=1e-10):
+    """tf.train.RMSPropOptimizer(lr, momentum=0.9) (models/base.py:270-271; decay 0.9 and epsilon 1e-10 are TF1's defaults)
+    [TF-lib ApplyRMSProp, centered=False]: ms = decay * ms + (1 - decay) * g^2 (the `rms` slot is created with ones);
+    mom = momentum * mom + lr * g / sqrt(ms + eps); theta -= mom."""
+    for i in range(len(params)):
+        ms[i] = decay * ms[i] + (1 - decay) * grads[i] ** 2
+        mom[i] = momentum * mom[i] + lr * grads[i] / np.sqrt(ms[i] + eps)
+        params[i] = params[i] - mom[i]
+    return params, ms, mom
+
+
 # ----------------------------------------------------------------------------
 # Host pre-processing — models/model_util.py:40-58, models/gaze_rnn.py:499-510
 # ----------------------------------------------------------------------------

@@ -491,6 +491,41 @@ __global__ void __launch_bounds__(256) clip_adam_kernel(float* __restrict__ p, c
   }
 }
 
+// base.py:270-273 — the reference's other two optimisers, in TF1's update rules [TF-lib]:
+//   kind 0  tf.train.MomentumOptimizer(lr, momentum=0.9) (ApplyMomentum, no Nesterov):
+//             accum = momentum * accum + g;  theta -= lr * accum
+//   kind 1  tf.train.RMSPropOptimizer(lr, decay=0.9, momentum=0.9, epsilon=1e-10) (ApplyRMSProp; the `rms` slot starts at ONE):
+//             ms = decay * ms + (1 - decay) * g^2;  mom = momentum * mom + lr * g / sqrt(ms + eps);  theta -= mom
+// g is the globally clipped gradient (base.py:287-291); lr = sched[1], the staircase learning rate rgp_adam_schedule leaves
+// on the device (the same schedule kernel advances global_step for every optimiser).
+template <typename TA>
+__global__ void __launch_bounds__(256) clip_momentum_kernel(float* __restrict__ p, const float* __restrict__ g,
+                                                             float* __restrict__ acc, float* __restrict__ ms, long long n,
+                                                             const double* __restrict__ sumsq, float clip,
+                                                             const float* __restrict__ sched, int kind, float momentum,
+                                                             float rms_decay, float eps, TA* __restrict__ p_op) {
+  const float lr = sched[1];
+  const float norm = (float)sqrt(sumsq[0]);
+  const float scale = clip > 0.f ? clip / fmaxf(norm, clip) : 1.0f;
+  long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  const long long stride = (long long)gridDim.x * 256;
+  for (; i < n; i += stride) {
+    const float gi = g[i] * scale;
+    float pi, ai;
+    if (kind == 0) {
+      ai = momentum * acc[i] + gi;
+      pi = p[i] - lr * ai;
+    } else {
+      const float mi = rms_decay * ms[i] + (1.0f - rms_decay) * gi * gi;
+      ms[i] = mi;
+      ai = momentum * acc[i] + lr * gi * rsqrtf(mi + eps);
+      pi = p[i] - ai;
+    }
+    acc[i] = ai; p[i] = pi;
+    if (p_op) OpT<TA>::st(p_op + i, pi);
+  }
+}
+
 }  // namespace rgp
 
 using namespace rgp;
@@ -725,6 +760,25 @@ int rgp_gradnorm_clip_adam_dev(float* p, const float* g, float* m, float* v, lon
                                void* stream) {
   RGP_CHECK_ARG(lr_t_dev != nullptr, "rgp_gradnorm_clip_adam_dev: lr_t_dev is NULL%s", "");
   return launch_clip_adam(p, g, m, v, n, sumsq, clip, 0.f, lr_t_dev, beta1, beta2, eps, p_op, dtype, stream);
+}
+
+int rgp_gradnorm_clip_momentum_dev(float* p, const float* g, float* acc, float* ms, long long n, const double* sumsq,
+                                   float clip, const float* sched, int kind, float momentum, float rms_decay, float eps,
+                                   void* p_op, int dtype, void* stream) {
+  RGP_CHECK_ARG(p && g && acc && sumsq && sched, "rgp_gradnorm_clip_momentum_dev: null pointer%s", "");
+  RGP_CHECK_ARG(kind == 0 || kind == 1, "rgp_gradnorm_clip_momentum_dev: kind=%d (0 momentum, 1 rmsprop)", kind);
+  RGP_CHECK_ARG(kind == 0 || ms != nullptr, "rgp_gradnorm_clip_momentum_dev: rmsprop needs the mean-square slot%s", "");
+  RGP_CHECK_ARG(n >= 0, "rgp_gradnorm_clip_momentum_dev: n=%lld", n);
+  if (n == 0) return 0;
+  int grid = (int)((n + 1023) / 1024);
+  if (grid > 148 * 8) grid = 148 * 8;
+  if (dtype == 0 || p_op == nullptr)
+    clip_momentum_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>(p, g, acc, ms, n, sumsq, clip, sched, kind, momentum,
+                                                                         rms_decay, eps, (float*)p_op);
+  else
+    clip_momentum_kernel<__nv_bfloat16><<<grid, 256, 0, (cudaStream_t)stream>>>(p, g, acc, ms, n, sumsq, clip, sched, kind,
+                                                                                 momentum, rms_decay, eps, (__nv_bfloat16*)p_op);
+  return check_launch("rgp_gradnorm_clip_momentum_dev");
 }
 
 int rgp_adam_schedule(long long* step, const double* lr0, double decay, int decay_steps, double beta1, double beta2,

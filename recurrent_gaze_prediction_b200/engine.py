@@ -96,6 +96,17 @@ class TrainStateMixin(object):
         self.sched = torch.zeros(2, dtype=torch.float32, device=dev)
         self._lr0_host = None
         self._step = 0
+        self.optimizer = "adam"
+
+    def set_optimizer(self, method):
+        """models/base.py:268-275: 'adam' | 'rmsprop' (RMSProp, momentum 0.9) | 'sgd' (Momentum 0.9); anything else raises
+        the reference's ValueError.  The two slot buffers are reused: adam_m = accumulator / momentum slot, adam_v = the
+        RMSProp mean-square slot, which TF creates filled with ONES.  Call before the first step (it resets the slots)."""
+        if method not in ("adam", "rmsprop", "sgd"):
+            raise ValueError('Invalid optimization method!')
+        self.optimizer = method
+        self.adam_m.zero_()
+        self.adam_v.fill_(1.0 if method == "rmsprop" else 0.0)
 
     def make_graph(self, fn):
         """Capture the launches fn() issues into a CUDA graph (one submission per step instead of ~80
@@ -176,10 +187,16 @@ class TrainStateMixin(object):
         lib.rgp_sumsq(self.grads.data_ptr(), self.nparams, self.sumsq.data_ptr(), s)
         lib.rgp_adam_schedule(self.step_dev.data_ptr(), self.lr0_dev.data_ptr(), float(decay), int(decay_steps),
                               float(beta1), float(beta2), self.sched.data_ptr(), s)
-        lib.rgp_gradnorm_clip_adam_dev(self.params.data_ptr(), self.grads.data_ptr(), self.adam_m.data_ptr(),
-                                       self.adam_v.data_ptr(), self.nparams, self.sumsq.data_ptr(), clip,
-                                       self.sched.data_ptr(), beta1, beta2, eps,
-                                       self.params_op.data_ptr() if self.dtype != 0 else 0, self.dtype, s)
+        p_op = self.params_op.data_ptr() if self.dtype != 0 else 0
+        if self.optimizer == "adam":
+            lib.rgp_gradnorm_clip_adam_dev(self.params.data_ptr(), self.grads.data_ptr(), self.adam_m.data_ptr(),
+                                           self.adam_v.data_ptr(), self.nparams, self.sumsq.data_ptr(), clip,
+                                           self.sched.data_ptr(), beta1, beta2, eps, p_op, self.dtype, s)
+        else:       # base.py:270-273: RMSProp(momentum 0.9; decay 0.9, epsilon 1e-10 = TF1 defaults) / Momentum(0.9)
+            lib.rgp_gradnorm_clip_momentum_dev(self.params.data_ptr(), self.grads.data_ptr(), self.adam_m.data_ptr(),
+                                               self.adam_v.data_ptr(), self.nparams, self.sumsq.data_ptr(), clip,
+                                               self.sched.data_ptr(), 1 if self.optimizer == "rmsprop" else 0, 0.9, 0.9,
+                                               1e-10, p_op, self.dtype, s)
         if not (self.device.type == "cuda" and torch.cuda.is_current_stream_capturing()):
             self._step += 1
             self.param_version += 1

@@ -118,6 +118,7 @@ _SIGS = {
     "rgp_gradnorm_clip_adam": [_vp, _vp, _vp, _vp, _ll, _vp, _f, _f, _f, _f, _f, _vp, _i, _vp],
     "rgp_adam_schedule": [_vp, _vp, _d, _i, _d, _d, _vp, _vp],
     "rgp_gradnorm_clip_adam_dev": [_vp, _vp, _vp, _vp, _ll, _vp, _f, _vp, _f, _f, _f, _vp, _i, _vp],
+    "rgp_gradnorm_clip_momentum_dev": [_vp, _vp, _vp, _vp, _ll, _vp, _f, _vp, _i, _f, _f, _f, _vp, _i, _vp],
     "rgp_zero": [_vp, _ll, _vp],
     "rgp_flip_w": [_vp, _vp, _i, _ll, _i, _vp],
     "rgp_wgrad": [C.POINTER(WgradArgs), _vp],

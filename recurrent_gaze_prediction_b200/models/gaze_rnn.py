@@ -230,11 +230,9 @@ class GazePredictionGRU(ModelBase):
         method = getattr(self.config, "optimization_method", 'adam')
         if method not in ('adam', 'rmsprop', 'sgd'):
             raise ValueError('Invalid optimization method!')                  # base.py:268-275
-        if method != 'adam' and getattr(self.engine, "train", False):
-            # base.py:270-273 offers RMSProp(momentum 0.9) and Momentum(0.9); every entry point of the reference sets
-            # 'adam' (gaze_rnn.py:57) and only the Adam update is built here — refuse rather than silently run Adam
-            raise NotImplementedError("optimization_method=%r: only 'adam' (the reference's setting, gaze_rnn.py:57) is "
-                                      "built on the B200 path" % method)
+        if getattr(self.engine, "train", False):
+            # base.py:268-273: Adam / RMSProp(momentum 0.9) / Momentum(0.9), all on the globally clipped gradient
+            self.engine.set_optimizer(method)
         self.global_step = 0
         self.learning_rate = self.current_learning_rate
         self.train_op = self._train_step if getattr(self.engine, "train", False) else None

@@ -388,6 +388,23 @@ class EmuLib(object):
         st[0] = t
         return 0
 
+    def rgp_gradnorm_clip_momentum_dev(self, p, g, acc, ms, n, sumsq, clip, sched, kind, momentum, rms_decay, eps, p_op,
+                                       dtype, stream):
+        P, G, A = (arr(x, (n,)) for x in (p, g, acc))
+        lr = np.float32(arr(sched, (2,))[1])
+        norm = math.sqrt(arr(sumsq, (1,), np.float64)[0])
+        scale = clip / max(norm, clip) if clip > 0 else 1.0
+        gg = G * np.float32(scale)
+        if kind == 0:
+            A[:] = np.float32(momentum) * A + gg
+            P[:] = P - lr * A
+        else:
+            Ms = arr(ms, (n,))
+            Ms[:] = np.float32(rms_decay) * Ms + np.float32(1.0 - rms_decay) * gg * gg
+            A[:] = np.float32(momentum) * A + lr * gg / np.sqrt(Ms + np.float32(eps))
+            P[:] = P - A
+        return 0
+
     def rgp_gradnorm_clip_adam_dev(self, p, g, m, v, n, sumsq, clip, lr_t_dev, b1, b2, eps, p_op, dtype, stream):
         return self.rgp_gradnorm_clip_adam(p, g, m, v, n, sumsq, clip, float(arr(lr_t_dev, (1,))[0]), b1, b2, eps, p_op,
                                            dtype, stream)

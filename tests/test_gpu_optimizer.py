@@ -152,3 +152,47 @@ def test_bf16_fed_features_are_bit_identical_to_fp32_fed():
     a = eng.Apack.clone()
     eng.stage_embed(c3d.to(torch.bfloat16).float())
     assert torch.equal(a, eng.Apack)
+
+
+@pytest.mark.parametrize("kind", ["sgd", "rmsprop"])
+@pytest.mark.parametrize("clip,gscale", [(10.0, 100.0), (10.0, 1e-3), (0.0, 100.0)])
+def test_clip_momentum_rmsprop_kernel_matches_oracle(kind, clip, gscale):
+    """rgp_gradnorm_clip_momentum_dev (models/base.py:270-273: RMSProp(momentum 0.9) / Momentum(0.9) in TF1's update rules)
+    on known (g, p, slots) against the oracle's clip_by_global_norm + momentum_step / rmsprop_step, three consecutive steps,
+    to float32 rounding; the bf16 operand copy equals the rounded parameters."""
+    lib = L.get_lib()
+    rng = np.random.RandomState(7)
+    n = 70001
+    p = rng.standard_normal(n).astype(np.float32)
+    acc = np.zeros(n, np.float32)
+    ms = np.ones(n, np.float32)
+    d = [torch.from_numpy(x.copy()).cuda() for x in (p, acc, ms)]
+    pr, ar, mr = p.astype(np.float64), acc.astype(np.float64), ms.astype(np.float64)
+    sched = torch.tensor([0.0, 1e-3], dtype=torch.float32, device="cuda")
+    lr = float(np.float32(1e-3))
+    p_op = torch.zeros(n, dtype=torch.bfloat16, device="cuda")
+    s = torch.cuda.current_stream().cuda_stream
+    mom, dec = float(np.float32(0.9)), float(np.float32(0.9))
+    for step in range(3):
+        g = (rng.standard_normal(n) * gscale / math.sqrt(n)).astype(np.float32)
+        gd = torch.from_numpy(g).cuda()
+        sumsq = torch.zeros(1, dtype=torch.float64, device="cuda")
+        lib.rgp_sumsq(gd.data_ptr(), n, sumsq.data_ptr(), s)
+        lib.rgp_gradnorm_clip_momentum_dev(d[0].data_ptr(), gd.data_ptr(), d[1].data_ptr(), d[2].data_ptr(), n,
+                                           sumsq.data_ptr(), clip, sched.data_ptr(), 1 if kind == "rmsprop" else 0, 0.9, 0.9,
+                                           1e-10, p_op.data_ptr(), 1, s)
+        gc = O.clip_by_global_norm([g.astype(np.float64)], clip)[0][0] if clip > 0 else g.astype(np.float64)
+        p_before = pr.copy()
+        if kind == "rmsprop":
+            (pr,), (mr,), (ar,) = O.rmsprop_step([pr], [gc], [mr], [ar], lr, decay=dec, momentum=mom)
+        else:
+            (pr,), (ar,) = O.momentum_step([pr], [gc], [ar], lr, momentum=mom)
+        torch.cuda.synchronize()
+        pg, ag = d[0].cpu().numpy().astype(np.float64), d[1].cpu().numpy().astype(np.float64)
+        assert np.abs(ag - ar).max() <= 1e-6 * max(np.abs(ar).max(), 1e-30), (step, np.abs(ag - ar).max())
+        assert np.abs(pg - pr).max() <= 2e-7 * np.abs(pr).max() + 1e-6 * np.abs(pr - p_before).max()
+        if kind == "rmsprop":
+            mg = d[2].cpu().numpy().astype(np.float64)
+            assert np.abs(mg - mr).max() <= 4e-7 * np.abs(mr).max()
+        assert torch.equal(p_op, d[0].to(torch.bfloat16))
+        pr, ar, mr = pg, ag, (d[2].cpu().numpy().astype(np.float64) if kind == "rmsprop" else mr)   # no drift between steps

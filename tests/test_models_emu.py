@@ -341,15 +341,37 @@ def test_dense_gru_model_class_contract():
 
 
 def test_optimisation_method_and_device_side_schedule(tmp_path):
-    """base.py:268-275: an unknown optimisation method is a ValueError; rmsprop / sgd exist in the reference but no entry
-    point selects them — refused, not silently replaced by Adam.  The staircase learning rate and Adam's bias correction
-    are evaluated by rgp_adam_schedule from the engine's own step counter, with the config's decay interval."""
+    """base.py:268-275: an unknown optimisation method is a ValueError; 'rmsprop' (RMSProp, momentum 0.9) and 'sgd'
+    (Momentum 0.9) take TF1's update rules on the globally clipped gradient (oracle: rmsprop_step / momentum_step, the rms
+    slot starting at one).  The staircase learning rate and Adam's bias correction are evaluated by rgp_adam_schedule from
+    the engine's own step counter, with the config's decay interval."""
     lib = EmuLib()
-    for method, exc in (("adagrad", ValueError), ("rmsprop", NotImplementedError), ("sgd", NotImplementedError)):
+    c = small_config()
+    c.optimization_method = "adagrad"
+    with pytest.raises(ValueError):
+        gaze_grcn.GazePredictionGRCN({'lib': lib}, data(), c)
+    for method in ("rmsprop", "sgd"):
         c = small_config()
         c.optimization_method = method
-        with pytest.raises(exc):
-            gaze_grcn.GazePredictionGRCN({'lib': lib}, data(), c)
+        m = gaze_grcn.GazePredictionGRCN({'lib': lib}, data(), c)
+        np.random.seed(1)
+        n = m.engine.nparams
+        ms = np.ones(n) if method == "rmsprop" else None
+        acc = np.zeros(n)
+        for k in range(3):
+            p0 = m.engine.params.numpy().astype(np.float64).copy()
+            m.single_step()
+            g = m.engine.grads.numpy().astype(np.float64)
+            (gc,), _ = O.clip_by_global_norm([g], m.max_grad_norm)
+            lr = float(m.engine.sched[1])
+            if method == "rmsprop":
+                (want,), (ms,), (acc,) = O.rmsprop_step([p0], [gc], [ms], [acc], lr)
+            else:
+                (want,), (acc,) = O.momentum_step([p0], [gc], [acc], lr)
+            got = m.engine.params.numpy().astype(np.float64)
+            assert np.abs(got - p0).max() > 0
+            assert np.abs(got - want).max() <= 2e-6 * max(np.abs(want - p0).max(), 1e-30) + 1e-7 * np.abs(want).max(), (method, k)
+        assert int(m.engine.step_dev[0]) == 3 == m.current_step
     c = small_config()
     c.learning_rate_decay_steps, c.learning_rate_decay, c.train_dir = 2, 0.5, str(tmp_path)
     m = gaze_grcn.GazePredictionGRCN({'lib': lib}, data(), c)
