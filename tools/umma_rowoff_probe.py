@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Probe: UMMA K-major SWIZZLE_128B operand starting at a row that is not a multiple of the 8-row swizzle atom
-(csrc/debug_umma.cu).  Prints, per (row offset, base-offset mode), the max abs error against a CPU product."""
+(csrc/debug_umma.cu; build the library with RGP_BUILD_PROBES=1: the probe is not linked into the product .so).  Prints, per (row offset, base-offset mode), the max abs error against a CPU product."""
 import ctypes as C
 import os
 import sys
