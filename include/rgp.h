@@ -425,6 +425,10 @@ int rgp_maxout(const float* y, int ldy, const float* bias, int half, int n, void
 /* All metric arithmetic is IEEE float64 with explicit round-to-nearest operations (no FMA contraction):
  * thresholds and integer counts are a bit-exact contract with NumPy's float64 evaluation.
  * Maps are [n, hw] row-major, one frame per row; fix is uint8 (non-zero = fixated). */
+/* evaluation_metrics.py:71 (`np.sum(fixation_map > 0.5)` per frame): out[i] = number of non-zero bytes of row i of the
+ * uint8 array x[n, row] (fixations per frame, needed on the host before the random index tensors are drawn). */
+int rgp_count_nonzero_rows(const uint8_t* x, int n, long long row, int* out, void* stream);
+
 /* evaluation_metrics.py:15-17,246: fp32 model output [n,hw] -> float64, optionally (x-min)/(max-min) per frame */
 int rgp_metrics_prep(const float* src, double* dst, int n, int hw, int normalize, void* stream);
 /* stand-in for skimage.transform.resize(order=3) (evaluation_metrics.py:76,137,248,255; see

@@ -1973,6 +1973,40 @@ auc_judd_lean_kernel(const double* __restrict__ sal, const double* __restrict__ 
   cp_async_wait_all();
 }
 
+// number of non-zero bytes of every row of a [n, row] uint8 array (fixations per frame: evaluation_metrics.py:71,
+// `np.sum(fixation_map > 0.5)` of each frame, needed on the host before the random index tensors are drawn)
+__global__ void __launch_bounds__(kThreads) count_nonzero_rows_kernel(const uint8_t* __restrict__ x, long long row,
+                                                                     int* __restrict__ out) {
+  __shared__ int wsum[kThreads / 32];
+  const uint8_t* p = x + (long long)blockIdx.x * row;
+  int c = 0;
+  if (((reinterpret_cast<uintptr_t>(p) | (uintptr_t)row) & 15) == 0) {
+    const uint4* q = reinterpret_cast<const uint4*>(p);
+    for (long long i = threadIdx.x; i < row / 16; i += kThreads) {
+      const uint4 v = q[i];
+      const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        // a byte is non-zero iff any of its bits is set: fold the 8 bits of every byte onto its lowest bit
+        uint32_t t = w[k];
+        t |= t >> 4; t |= t >> 2; t |= t >> 1;
+        c += __popc(t & 0x01010101u);
+      }
+    }
+  } else {
+    for (long long i = threadIdx.x; i < row; i += kThreads) c += p[i] != 0;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+  if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = c;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int t = 0;
+    for (int i = 0; i < kThreads / 32; ++i) t += wsum[i];
+    out[blockIdx.x] = t;
+  }
+}
+
 }  // namespace
 }  // namespace rgp
 
@@ -1993,6 +2027,13 @@ int sm_count() {
 }  // namespace
 
 extern "C" {
+
+int rgp_count_nonzero_rows(const uint8_t* x, int n, long long row, int* out, void* stream) {
+  RGP_CHECK_ARG(n >= 0 && row > 0 && (n == 0 || (x && out)), "rgp_count_nonzero_rows: n=%d row=%lld", n, row);
+  if (n == 0) return 0;
+  rgp::count_nonzero_rows_kernel<<<n, rgp::kThreads, 0, (cudaStream_t)stream>>>(x, row, out);
+  return rgp::check_launch("rgp_count_nonzero_rows");
+}
 
 int rgp_metrics_prep(const float* src, double* dst, int n, int hw, int normalize, void* stream) {
   RGP_CHECK_ARG(n >= 0 && hw > 0, "rgp_metrics_prep: n=%d hw=%d", n, hw);

@@ -150,6 +150,7 @@ _SIGS = {
     "rgp_fill_uniform_f64": [_vp, _ll, C.c_ulonglong, _vp],
     "rgp_fill_randint_rows": [_vp, _vp, _i, _i, _i, _i, C.c_ulonglong, _vp],
     # saliency metrics (evaluation_metrics.py)
+    "rgp_count_nonzero_rows": [_vp, _i, _ll, _vp, _vp],
     "rgp_metrics_prep": [_vp, _vp, _i, _i, _i, _vp],
     "rgp_resize_bicubic": [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp],
     "rgp_sim_cc_nss": [_vp, _vp, _vp, _vp, _i, _i, _vp],

@@ -661,6 +661,10 @@ class EmuLib(object):
     # -------------------------------------------------------------- saliency metrics (csrc/metrics.cu)
     # NumPy float64 restatements of the KERNELS' algorithms (rank-by-search for Judd, per-repetition
     # count loops for the sampled AUCs), so the host wrapper in evaluation_metrics.py is checked on CPU.
+    def rgp_count_nonzero_rows(self, x, n, row, out, stream):
+        arr(out, (n,), np.int32)[:] = np.count_nonzero(arr(x, (n, row), np.uint8), axis=1)
+        return 0
+
     def rgp_metrics_prep(self, src, dst, n, hw, normalize, stream):
         s = arr(src, (n, hw)).astype(np.float64)
         d = arr(dst, (n, hw), np.float64)

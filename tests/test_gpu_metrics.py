@@ -172,7 +172,7 @@ def test_fused_resize_metrics_equal_two_step_path(shape):
     kw = dict(union=union, jitter_values=jit, rand_index=ridx, shuf_index=sidx, return_counts=True)
     before = a.lib.launches
     ra = a.evaluate_batch(pred, gt, fix, **kw)
-    assert a.lib.launches - before == 2 + 4            # prep x2, fused sim/cc/nss, Judd, Borji, shuffled: no resize launch
+    assert a.lib.launches - before == 1 + 2 + 4        # fixation count, prep x2, fused sim/cc/nss, Judd, Borji, shuffled: no resize launch
     rb = b.evaluate_batch(pred, gt, fix, **kw)
     for k in rb:
         if k in ("sim", "cc", "NSS"):
@@ -313,3 +313,18 @@ def test_lean_fused_kernels_other_ranges_equal_two_step_path(eng, kind, shape):
             a2, t2, c2 = eng.auc_judd(pr, fx, jd, 64)
             assert torch.equal(c1, c2) and torch.equal(t1.nan_to_num(-7.0), t2.nan_to_num(-7.0))
             assert np.array_equal(a1.cpu().numpy(), a2.cpu().numpy(), equal_nan=True)
+
+
+@pytest.mark.parametrize("row", [360 * 480, 49 * 49, 1000003])
+def test_count_nonzero_rows_kernel(eng, row):
+    """rgp_count_nonzero_rows (fixations per frame) against NumPy: 16-byte path (aligned rows), byte path (odd rows), byte
+    values other than 0 / 1."""
+    rng = np.random.RandomState(row % 97)
+    n = 7
+    x = (rng.uniform(size=(n, row)) < 0.01).astype(np.uint8) * rng.randint(1, 256, size=(n, row)).astype(np.uint8)
+    x[2] = 0
+    x[3, -1] = 255
+    d = torch.from_numpy(x).cuda()
+    out = torch.full((n,), -5, dtype=torch.int32, device="cuda")
+    eng.lib.rgp_count_nonzero_rows(d.data_ptr(), n, row, out.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    assert np.array_equal(out.cpu().numpy(), np.count_nonzero(x, axis=1))
