@@ -240,17 +240,29 @@ class MetricsEngine(object):
         dev_b = dev_rng and 'AUC_Borji' in metrics and rand_index is None
         dev_j = dev_rng and 'AUC_Judd' in metrics and jitter and jitter_values is None
         if dev_rng and need_shuf and shuf_index is None:
-            # n_fix distinct picks of the union's fixated pixels per repetition: the first n_fix of a random order
+            # n_fix distinct picks of the union's fixated pixels per repetition = the n_fix smallest of one random key per
+            # union pixel (a uniformly random subset).  Vectorised over frames: one partition per (frame, repetition) row
+            # at the largest n_fix, then a sort of that short prefix so that the first k of it are the k smallest keys.
             gen = np.random.Generator(np.random.PCG64(int(seed) + 0x5EED))
             fixated = np.nonzero(union_h.ravel())[0]
-            shuf_index = []
-            for i in range(N):
-                k = int(min(nfix[i], len(fixated)))
-                if nfix[i] > 0 and k > 0:
-                    order = np.argsort(gen.random((n_rep, len(fixated)), dtype=np.float32), axis=1)[:, :k]
-                    shuf_index.append(fixated[order.T])
-                else:
-                    shuf_index.append(np.zeros((0, n_rep), dtype=np.int64))
+            L_ = len(fixated)
+            kk = np.minimum(nfix, L_).astype(np.int64)
+            kmax = int(kk.max(initial=0))
+            shuf_index = [np.zeros((0, n_rep), dtype=np.int64)] * N
+            if kmax > 0:
+                per = max(1, int(64e6 // max(1, n_rep * L_ * 4)))            # frames per block: <= 64 MB of keys
+                for b0 in range(0, N, per):
+                    b1 = min(N, b0 + per)
+                    keys = gen.random((b1 - b0, n_rep, L_), dtype=np.float32)
+                    if kmax < L_:
+                        part = np.argpartition(keys, kmax - 1, axis=2)[:, :, :kmax]
+                    else:
+                        part = np.broadcast_to(np.arange(L_), keys.shape).copy()
+                    pk = np.take_along_axis(keys, part, axis=2)
+                    part = np.take_along_axis(part, np.argsort(pk, axis=2), axis=2)      # [frames, n_rep, kmax]
+                    for i in range(b0, b1):
+                        if kk[i] > 0:
+                            shuf_index[i] = fixated[part[i - b0, :, :kk[i]].T]
         nfix_dev = nfix_i32 if dev_b else None
         if draw_b:
             rand_index = []
