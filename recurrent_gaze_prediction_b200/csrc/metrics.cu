@@ -1675,7 +1675,8 @@ auc_judd_lean_kernel(const double* __restrict__ sal, const double* __restrict__ 
   __shared__ double myfix[kMaxFix];
   __shared__ double thr[kMaxFix];
   __shared__ int hist[kMaxFix];
-  __shared__ int mycount, total_s;
+  __shared__ double dthr[kMaxFix];                       // thresholds as bounds on x - min (pass 2)
+  __shared__ int mycount, total_s, nofast;
   __shared__ double mnmx[2];
   __shared__ unsigned long long skey[4];
   __shared__ int snan[2];
@@ -1917,21 +1918,65 @@ auc_judd_lean_kernel(const double* __restrict__ sal, const double* __restrict__ 
           }
           __syncthreads();
         }
-      // ---- pass 2: rank every pixel against the thresholds (jitter re-read from L2, map recomputed)
-      const double lowest = thr[total - 1];
-      const double cut = lowest * range * (1.0 - 1e-12);      // see auc_judd_kernel
-      judd_walk(k, T, ct, cols, jt, ow, window,
-          [&](bool live, const double2 w01, const double2 w23, const double* ta, double j) {
-            const double x = value(w01, w23, ta, j);
-            const double d = dS(x, gmn);
-            if (d < cut || !live) return;
-            const double vv = dD(d, range);
-            if (vv >= lowest) {
-              int lo = 0, hi = total - 1;
-              while (lo < hi) { const int mid = (lo + hi) >> 1; if (thr[mid] <= vv) hi = mid; else lo = mid + 1; }
-              atomicAdd(&hist[lo], 1);
+      // ---- pass 2: rank every pixel against the thresholds (jitter re-read from L2, map recomputed).
+      // The reference ranks v = (x - min) / range against thr[k]; RN(d / range) is monotone in d, so "thr[k] <= v" is
+      // "dthr[k] <= d" with dthr[k] = the smallest double whose quotient reaches thr[k] - found once per threshold by
+      // stepping the candidate thr[k] * range by single ulps under the exact division.  The per-pixel division (and the
+      // conservative `cut` of auc_judd_kernel) disappear and the counts stay bit-exact by construction; a threshold
+      // whose bound cannot be established (NaN, zero / infinite range) sends the frame to the division form.
+      if (tid == 0) nofast = !(range > 0.0 && range < CUDART_INF) || !(gmn == gmn);
+      __syncthreads();
+      if (!nofast)
+        for (int kk = tid; kk < total; kk += nt) {
+          const double t = thr[kk];
+          double c = 0.0;
+          bool good = true;
+          if (t > 0.0) {
+            c = dM(t, range);
+            good = c > 0.0 && c < CUDART_INF;
+            int it = 0;
+            while (good && it < 24) {
+              const double below = __longlong_as_double(__double_as_longlong(c) - 1);    // c > 0: the previous double
+              if (!(dD(below, range) >= t)) break;
+              c = below; ++it;
+              if (!(c > 0.0)) break;
             }
-          });
+            while (good && it < 48 && dD(c, range) < t) { c = __longlong_as_double(__double_as_longlong(c) + 1); ++it; }
+            good = good && it < 48 && dD(c, range) >= t;
+          } else if (!(t == 0.0)) {
+            good = false;                                  // NaN threshold
+          }
+          dthr[kk] = c;
+          if (!good) nofast = 1;
+        }
+      __syncthreads();
+      if (!nofast) {
+        const double dlow = dthr[total - 1];
+        judd_walk(k, T, ct, cols, jt, ow, window,
+            [&](bool live, const double2 w01, const double2 w23, const double* ta, double j) {
+              const double x = value(w01, w23, ta, j);
+              const double d = dS(x, gmn);
+              if (!(d >= dlow) || !live) return;
+              int lo = 0, hi = total - 1;                  // first k with dthr[k] <= d
+              while (lo < hi) { const int mid = (lo + hi) >> 1; if (dthr[mid] <= d) hi = mid; else lo = mid + 1; }
+              atomicAdd(&hist[lo], 1);
+            });
+      } else {
+        const double lowest = thr[total - 1];
+        const double cut = lowest * range * (1.0 - 1e-12);      // see auc_judd_kernel
+        judd_walk(k, T, ct, cols, jt, ow, window,
+            [&](bool live, const double2 w01, const double2 w23, const double* ta, double j) {
+              const double x = value(w01, w23, ta, j);
+              const double d = dS(x, gmn);
+              if (d < cut || !live) return;
+              const double vv = dD(d, range);
+              if (vv >= lowest) {
+                int lo = 0, hi = total - 1;
+                while (lo < hi) { const int mid = (lo + hi) >> 1; if (thr[mid] <= vv) hi = mid; else lo = mid + 1; }
+                atomicAdd(&hist[lo], 1);
+              }
+            });
+      }
     }
     cl.sync();
     if (rank == 0) {
