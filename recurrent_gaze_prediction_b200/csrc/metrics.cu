@@ -1145,7 +1145,7 @@ sim_cc_nss_lean_kernel(const double* __restrict__ pred, const double* __restrict
   extern __shared__ __align__(16) double lsm[];
   cg::cluster_group cl = cg::this_cluster();
   __shared__ double wpart[kLeanWarps][8];
-  __shared__ double part1[8], part2[4], tot[8];
+  __shared__ double part1[2][8], part2[2][4], tot[2][8];   // by frame parity: see the note at the end of the frame loop
   __shared__ unsigned long long skey[4];                 // order-preserving keys of the source extrema (min, max) x 2 maps
   __shared__ int snan[2];
   __shared__ int sext[2];                                // high words of the smallest / largest resized value seen so far
@@ -1201,7 +1201,26 @@ sim_cc_nss_lean_kernel(const double* __restrict__ pred, const double* __restrict
   const int nw4 = ct >> 2;
   int lgq = 0;                                           // word slots per strip row: a power of two >= nw4
   while ((1 << lgq) < nw4 && (1 << lgq) < kLeanThreads) ++lgq;
-  for (; f < n; f += ncl) {
+  // scores of frame fo from the parity-q buffers (rank 0, one thread)
+  auto emit = [&](int fo, int q) {
+    if (rank != 0 || tid != 0) return;
+    const double* p2 = &part2[q][0];
+    double t4[4] = {0.0, 0.0, 0.0, 0.0};
+    for (int c = 0; c < kCluster; ++c) {
+      const double* rp = cl.map_shared_rank(p2, c);
+      t4[0] += rp[0]; t4[1] += rp[1]; t4[2] += rp[2]; t4[3] += rp[3];
+    }
+    const double tsp_ = tot[q][0], tsg_ = tot[q][1];
+    const double mp_ = tsp_ / (double)hw;
+    double* o = out + (long long)fo * 8;
+    o[0] = t4[3];
+    o[1] = t4[2] / (sqrt(t4[0]) * sqrt(t4[1]));
+    const double sd = sqrt(t4[0] / (double)hw);
+    o[2] = (tot[q][5] > 0.0) ? ((tot[q][4] / tot[q][5]) - mp_) / sd : CUDART_NAN;
+    o[3] = tot[q][2]; o[4] = tot[q][3]; o[5] = tot[q][5]; o[6] = tsp_; o[7] = tsg_;
+  };
+  int par = 0, fprev = -1;
+  for (; f < n; f += ncl, par ^= 1) {
     cp_async_wait_all();
     __syncthreads();                                     // source maps (and, first time, the tables) are in place
     // ---- source statistics (clip range; np.min / np.max propagate NaN): plain extrema + a NaN flag per thread, warp
@@ -1378,19 +1397,20 @@ sim_cc_nss_lean_kernel(const double* __restrict__ pred, const double* __restrict
         const double x = wpart[q][tid];
         r = (tid == 2) ? nmin(r, x) : (tid == 3) ? nmax(r, x) : r + x;
       }
-      part1[tid] = r;
+      part1[par][tid] = r;
     }
     cl.sync();
     if (tid < 6) {
       double r = (tid == 2) ? CUDART_INF : (tid == 3) ? -CUDART_INF : 0.0;
       for (int q = 0; q < kCluster; ++q) {
-        const double x = cl.map_shared_rank(part1, q)[tid];
+        const double x = cl.map_shared_rank(&part1[par][0], q)[tid];
         r = (tid == 2) ? nmin(r, x) : (tid == 3) ? nmax(r, x) : r + x;
       }
-      tot[tid] = r;
+      tot[par][tid] = r;
     }
+    if (fprev >= 0) emit(fprev, par ^ 1);                 // the previous frame's scores: its pass-2 partials are complete in every CTA
     __syncthreads();
-    const double tsp = tot[0], tsg = tot[1];
+    const double tsp = tot[par][0], tsg = tot[par][1];
     const double mp = tsp / (double)hw, mg = tsg / (double)hw;
     const double rsp = dD(1.0, tsp), rsg = dD(1.0, tsg);
     // ---- pass 2: the same pixels again from the shared-memory tables: centred second moments, histogram intersection
@@ -1444,23 +1464,17 @@ sim_cc_nss_lean_kernel(const double* __restrict__ pred, const double* __restrict
     if (tid < 4) {
       double r = 0.0;
       for (int q = 0; q < kLeanWarps; ++q) r += wpart[q][tid];
-      part2[tid] = r;
+      part2[par][tid] = r;
     }
-    cl.sync();
-    if (rank == 0 && tid == 0) {
-      const double tpp = cluster_gather<SumOp>(cl, part2, 0), tgg = cluster_gather<SumOp>(cl, part2, 1);
-      const double tpg = cluster_gather<SumOp>(cl, part2, 2), tsim = cluster_gather<SumOp>(cl, part2, 3);
-      double* o = out + (long long)f * 8;
-      o[0] = tsim;
-      o[1] = tpg / (sqrt(tpp) * sqrt(tgg));
-      const double sd = sqrt(tpp / (double)hw);
-      o[2] = (tot[5] > 0.0) ? ((tot[4] / tot[5]) - mp) / sd : CUDART_NAN;
-      o[3] = tot[2]; o[4] = tot[3]; o[5] = tot[5]; o[6] = tsp; o[7] = tsg;
-    }
-    // part1 / part2 / tot of this frame are next written after the next frame's block / cluster barriers, which every
-    // reader reaches only after its reads; rank 0's remote reads of part2 are covered by the barrier after the loop
+    fprev = f;
+    // No cluster barrier here: the scores of this frame are written by rank 0 after the NEXT frame's first cluster barrier
+    // (or the one after the loop), which every CTA reaches after publishing part2.  part1 / part2 / tot alternate by frame
+    // parity, so a CTA that runs ahead into the next frame never overwrites what a slower CTA (or rank 0) still reads:
+    // the buffer of parity p is rewritten two frames later, i.e. after a cluster barrier that all readers of it have passed.
   }
   cp_async_wait_all();
+  cl.sync();
+  if (fprev >= 0) emit(fprev, par ^ 1);
   cl.sync();                                             // no CTA exits while rank 0 may still read its shared memory
 }
 
