@@ -1,12 +1,19 @@
 // cascade.cu — top level of the cascade model: models/gaze_grcn_cascade.py:343-424.
 //
 //   topgru_seq_kernel : the 5x5 ConvGRU with 3 units on the 49x49 grid (:346-351,379; cell :95-129), all T steps in
-//                       one launch, one CTA per clip, state and r.h resident in shared memory for the whole sequence.
+//                       one launch, state and r.h resident in shared memory for the whole sequence.  One CTA per clip, or
+//                       (NC = 2, taken while two CTAs per clip still fit the SMs) a cluster of two CTAs per clip: each
+//                       computes half of the rows, keeps whole planes, and writes the two rows next to the split into the
+//                       partner's planes through distributed shared memory; two cluster barriers per step.
 //   maxout_kernel     : bias + relu + max of the two halves of a maxout FC (:388-420) after its GEMM.
 //
 // The two GEMM-shaped pieces around them run on the tap-GEMM engines: the 11x11 / stride-7 transposed conv as a 4-tap
 // GEMM (RGP_EPI_UP7), the input half of the top cell as a 25-tap GEMM, the two FCs as plain GEMMs.
+#include <cooperative_groups.h>
+#include <stdlib.h>
 #include "common.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace rgp {
 namespace {
@@ -22,8 +29,8 @@ constexpr int PPT = (NPIX + TOP_THREADS - 1) / TOP_THREADS;   // 5 pixels per th
 
 __device__ __forceinline__ float sigm(float x) { return 1.0f / (1.0f + expf(-x)); }
 
-template <typename TA>
-__global__ void __launch_bounds__(TOP_THREADS, 1)
+template <typename TA, int NC>
+__global__ void __cluster_dims__(NC, 1, 1) __launch_bounds__(TOP_THREADS, 1)
 topgru_seq_kernel(const float* __restrict__ xg, int ldx, int So, int Wo, const float* __restrict__ uzr,
                   const float* __restrict__ uc, const float* __restrict__ sal, const float* __restrict__ wsal,
                   float* __restrict__ state, int carry, TA* __restrict__ og_op, int ldo, float* __restrict__ h_f32,
@@ -35,7 +42,19 @@ topgru_seq_kernel(const float* __restrict__ xg, int ldx, int So, int Wo, const f
   float* wzr = ss + PLANE + 1;             // [25][NU][6]  (+1: 7 * 2809 floats is odd, the float2 reads below need 8-byte alignment)
   float* wc = wzr + 25 * NU * 6;           // [25][NU][NU]
   float* ws = wc + 25 * NU * NU;           // [25][9]
-  const int b = blockIdx.x, tid = threadIdx.x;
+  cg::cluster_group cl = cg::this_cluster();
+  const int rank = NC > 1 ? (int)cl.block_rank() : 0;
+  const int b = blockIdx.x / NC, tid = threadIdx.x;
+  // rows [y0, y1) of the grid are this CTA's; it holds whole planes and receives the partner's two rows next to the split
+  constexpr int RH = (GT + NC - 1) / NC;                 // 49 or 25
+  constexpr int PPTN = (RH * GT + TOP_THREADS - 1) / TOP_THREADS;   // 5 or 3 pixels per thread
+  const int y0 = rank * RH, y1 = min(GT, y0 + RH);
+  const int npx = (y1 - y0) * GT;
+  float* phs = NC > 1 ? cl.map_shared_rank(hs, rank ^ 1) : nullptr;       // the partner's planes
+  float* prhs = NC > 1 ? cl.map_shared_rank(rhs, rank ^ 1) : nullptr;
+  auto sync_all = [&]() { if (NC > 1) cl.sync(); else __syncthreads(); };
+  // a row of mine the partner's 5x5 window reaches: the two rows at the split
+  auto halo_row = [&](int y) { return NC > 1 && (rank == 0 ? y >= y1 - 2 : y < y0 + 2); };
 
   for (int i = tid; i < (2 * NU + 1) * PLANE; i += TOP_THREADS) sm[i] = 0.f;
   for (int i = tid; i < 25 * NU * 6; i += TOP_THREADS) wzr[i] = uzr[i];
@@ -48,7 +67,7 @@ topgru_seq_kernel(const float* __restrict__ xg, int ldx, int So, int Wo, const f
       const int p = i / NU, u = i - p * NU, y = p / GT, x = p - y * GT;
       hs[u * PLANE + (y + 2) * PW + x + 2] = state[(long long)b * NPIX * NU + i];
     }
-  __syncthreads();
+  sync_all();                 // (cluster: nobody writes into a partner's planes before they are initialised)
 
   for (int t = 0; t < T; ++t) {
     const long long f = (long long)t * B + b;
@@ -61,19 +80,19 @@ topgru_seq_kernel(const float* __restrict__ xg, int ldx, int So, int Wo, const f
       }
       __syncthreads();
     }
-    float z[PPT][NU], xc[PPT][NU];
+    float z[PPTN][NU], xc[PPTN][NU];
     // Tap-outer loops: the 18 (9) weights of a tap are read from shared memory ONCE per thread and applied to its ~5
     // pixels from registers.  (Pixel-outer, 21 LDS per pixel and tap, the kernel was bound by the LDS pipe: 33 us per step.)
-    int base[PPT];
-    bool live[PPT];
+    int base[PPTN];
+    bool live[PPTN];
     // ---- phase A: z, r and r.h  (gaze_grcn_cascade.py:108-119)
-    float acc[PPT][6];
+    float acc[PPTN][6];
 #pragma unroll
-    for (int k = 0; k < PPT; ++k) {
-      const int p = tid + k * TOP_THREADS;
-      live[k] = p < NPIX;
-      const int pc = live[k] ? p : 0;
-      const int y = pc / GT, x = pc - y * GT;
+    for (int k = 0; k < PPTN; ++k) {
+      const int pl = tid + k * TOP_THREADS;
+      live[k] = pl < npx;
+      const int pc = live[k] ? pl : 0;
+      const int y = y0 + pc / GT, x = pc - (pc / GT) * GT;
       base[k] = y * PW + x;
       const float* xp = xf + (long long)(y * Wo + x) * ldx;
       const float4 x0 = *reinterpret_cast<const float4*>(xp);
@@ -91,7 +110,7 @@ topgru_seq_kernel(const float* __restrict__ xg, int ldx, int So, int Wo, const f
         w[i] = v.x; w[i + 1] = v.y;
       }
 #pragma unroll
-      for (int k = 0; k < PPT; ++k) {
+      for (int k = 0; k < PPTN; ++k) {
         const int o = base[k] + to;
 #pragma unroll
         for (int u = 0; u < NU; ++u) {
@@ -105,7 +124,7 @@ topgru_seq_kernel(const float* __restrict__ xg, int ldx, int So, int Wo, const f
 #pragma unroll
         for (int i = 0; i < 9; ++i) q[i] = ws[tap * 9 + i];
 #pragma unroll
-        for (int k = 0; k < PPT; ++k) {
+        for (int k = 0; k < PPTN; ++k) {
           const float sv = ss[base[k] + to];
 #pragma unroll
           for (int j = 0; j < 6; ++j) acc[k][j] = fmaf(sv, q[j], acc[k][j]);
@@ -115,19 +134,21 @@ topgru_seq_kernel(const float* __restrict__ xg, int ldx, int So, int Wo, const f
       }
     }
 #pragma unroll
-    for (int k = 0; k < PPT; ++k) {
+    for (int k = 0; k < PPTN; ++k) {
       if (live[k]) {
         const int c = base[k] + 2 * PW + 2;
 #pragma unroll
         for (int u = 0; u < NU; ++u) {
           z[k][u] = sigm(acc[k][u]);
-          rhs[u * PLANE + c] = sigm(acc[k][NU + u]) * hs[u * PLANE + c];
+          const float rh = sigm(acc[k][NU + u]) * hs[u * PLANE + c];
+          rhs[u * PLANE + c] = rh;
+          if (halo_row(c / PW - 2)) prhs[u * PLANE + c] = rh;
         }
       }
     }
-    __syncthreads();
+    sync_all();
     // ---- phase B: candidate and state update  (:122-127)
-    float hn[PPT][NU];
+    float hn[PPTN][NU];
 #pragma unroll 1
     for (int tap = 0; tap < 25; ++tap) {
       const int to = (tap / KT) * PW + (tap % KT);
@@ -135,7 +156,7 @@ topgru_seq_kernel(const float* __restrict__ xg, int ldx, int So, int Wo, const f
 #pragma unroll
       for (int i = 0; i < NU * NU; ++i) w[i] = wc[tap * NU * NU + i];
 #pragma unroll
-      for (int k = 0; k < PPT; ++k) {
+      for (int k = 0; k < PPTN; ++k) {
         const int o = base[k] + to;
 #pragma unroll
         for (int u = 0; u < NU; ++u) {
@@ -146,7 +167,7 @@ topgru_seq_kernel(const float* __restrict__ xg, int ldx, int So, int Wo, const f
       }
     }
 #pragma unroll
-    for (int k = 0; k < PPT; ++k) {
+    for (int k = 0; k < PPTN; ++k) {
       if (live[k]) {
         const int c = base[k] + 2 * PW + 2;
 #pragma unroll
@@ -156,25 +177,28 @@ topgru_seq_kernel(const float* __restrict__ xg, int ldx, int So, int Wo, const f
         }
       }
     }
-    __syncthreads();      // every read of h_{t-1} is done
+    // h_{t-1} is read by other threads (and by the partner, from its own planes) only in phase A, which every thread of
+    // both CTAs has left at the barrier above: a thread may overwrite its own pixels now
 #pragma unroll
-    for (int k = 0; k < PPT; ++k) {
-      const int p = tid + k * TOP_THREADS;
-      if (p < NPIX) {
-        const int y = p / GT, x = p - y * GT;
-        const int c = (y + 2) * PW + x + 2;
+    for (int k = 0; k < PPTN; ++k) {
+      if (live[k]) {
+        const int c = base[k] + 2 * PW + 2;
+        const int y = c / PW - 2, x = c - (y + 2) * PW - 2;
+        const int p = y * GT + x;
+        const bool halo = halo_row(y);
 #pragma unroll
         for (int u = 0; u < NU; ++u) {
           hs[u * PLANE + c] = hn[k][u];
+          if (halo) phs[u * PLANE + c] = hn[k][u];
           OpT<TA>::st(og_op + f * ldo + p * NU + u, hn[k][u]);       // tf.reshape(output_g, [B,-1]): (y, x, unit)
           if (h_f32) h_f32[f * (NPIX * NU) + p * NU + u] = hn[k][u];
         }
       }
     }
-    __syncthreads();
+    sync_all();
   }
   if (state)
-    for (int i = tid; i < NPIX * NU; i += TOP_THREADS) {
+    for (int i = y0 * GT * NU + tid; i < y1 * GT * NU; i += TOP_THREADS) {
       const int p = i / NU, u = i - p * NU, y = p / GT, x = p - y * GT;
       state[(long long)b * NPIX * NU + i] = hs[u * PLANE + (y + 2) * PW + x + 2];
     }
@@ -207,12 +231,23 @@ int launch_topgru(const float* xg, int ldx, int So, int Wo, const float* uzr, co
                   cudaStream_t s) {
   static PerDeviceFlag attr_set = {};
   if (attr_set.need()) {
-    cudaError_t e = cudaFuncSetAttribute(topgru_seq_kernel<TA>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTopSmem);
+    cudaError_t e = cudaFuncSetAttribute(topgru_seq_kernel<TA, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTopSmem);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(topgru_seq_kernel<TA, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTopSmem);
     if (e != cudaSuccess) { set_error("rgp_topgru_seq_fwd: cudaFuncSetAttribute(%d): %s", kTopSmem, cudaGetErrorString(e)); return -5; }
     attr_set.set();
   }
-  topgru_seq_kernel<TA><<<B, TOP_THREADS, kTopSmem, s>>>(xg, ldx, So, Wo, uzr, uc, sal, wsal, state, carry, (TA*)og_op,
-                                                        ldo, h_f32, B, T);
+  // two CTAs per clip while they fit the SMs at once (the kernel is latency-bound: one CTA per clip leaves 84 of 148 SMs
+  // idle at 64 clips); RGP_TOPGRU_SPLIT=1 forces one CTA per clip
+  int nsm = 0;
+  cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, current_device());
+  static const bool one = [] { const char* e = getenv("RGP_TOPGRU_SPLIT"); return e && e[0] == '1'; }();
+  if (!one && 2 * B <= nsm)
+    topgru_seq_kernel<TA, 2><<<2 * B, TOP_THREADS, kTopSmem, s>>>(xg, ldx, So, Wo, uzr, uc, sal, wsal, state, carry, (TA*)og_op,
+                                                                  ldo, h_f32, B, T);
+  else
+    topgru_seq_kernel<TA, 1><<<B, TOP_THREADS, kTopSmem, s>>>(xg, ldx, So, Wo, uzr, uc, sal, wsal, state, carry, (TA*)og_op,
+                                                              ldo, h_f32, B, T);
   return check_launch("rgp_topgru_seq_fwd");
 }
 
