@@ -586,7 +586,7 @@ int convgru_seq_fwd(const rgp_gru_seq_args& a, cudaStream_t s) {
   RGP_CHECK_ARG(a.dtype == 1, "rgp_convgru_seq_fwd: bf16 operands only (dtype=%d); fp32 uses the per-step rgp_tapgemm path", a.dtype);
   RGP_CHECK_ARG(a.B > 0 && a.T > 0, "rgp_convgru_seq_fwd: bad shape B=%d T=%d", a.B, a.T);
   RGP_CHECK_ARG(BM % S == 0, "rgp_convgru_seq_fwd: a 128-row tile must hold whole frames (S=%d; G must be 7, 3 or 1)", S);
-  RGP_CHECK_ARG(a.nsplit == 1 || a.nsplit == 2, "rgp_convgru_seq_fwd: nsplit=%d", a.nsplit);
+  RGP_CHECK_ARG(a.nsplit == 1 || a.nsplit == 2 || a.nsplit == 4, "rgp_convgru_seq_fwd: nsplit=%d", a.nsplit);
   RGP_CHECK_ARG(a.mcast == 1 || a.mcast == 2 || a.mcast == 4 || a.mcast == 8, "rgp_convgru_seq_fwd: mcast=%d", a.mcast);
   RGP_CHECK_ARG(a.nsplit * a.mcast <= 8, "rgp_convgru_seq_fwd: cluster of %d CTAs (max 8)", a.nsplit * a.mcast);
   RGP_CHECK_ARG(a.Ch % 64 == 0 && a.Ch / 64 <= kMaxKChunks, "rgp_convgru_seq_fwd: Ch=%d must be a multiple of 64, at most %d",
@@ -602,7 +602,8 @@ int convgru_seq_fwd(const rgp_gru_seq_args& a, cudaStream_t s) {
                 "rgp_convgru_seq_fwd: ntile=%d needs Ch/nsplit = 128 and mcast = 1", a.ntile);
   if (NH == 256) return launch_seq<256, 1>(a, s);
   if (NH == 128) return a.ntile == 2 ? launch_seq<128, 2>(a, s) : launch_seq<128, 1>(a, s);
-  set_error("rgp_convgru_seq_fwd: Ch/nsplit = %d must be 128 or 256", NH);
+  if (NH == 64) return launch_seq<64, 1>(a, s);          // four CTAs per tile at Ch = 256 (two at Ch = 128): small batches
+  set_error("rgp_convgru_seq_fwd: Ch/nsplit = %d must be 64, 128 or 256", NH);
   return -22;
 }
 

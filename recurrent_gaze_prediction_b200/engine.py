@@ -239,15 +239,18 @@ class GazeEngine(TrainStateMixin):
         self.tdt = _tdtype(dtype)
         self.taps3 = [ky * self.Wp + kx for ky in range(3) for kx in range(3)]
         # Persistent ConvGRU recurrence (rgp_convgru_seq_fwd: all T steps in one launch, one CTA per 128-row tile).
-        # Measured on B200 (profiles/r01_notes.md): with the resident state slab it beats two tap-GEMM launches per step
-        # from 64 tiles up (128 clips, 2-CTA channel split: 2.18 vs 2.81 ms; 256 clips: 2.63 vs 3.9 ms); below that the
-        # per-step GEMMs, which spread one step over all SMs, are kept.  RGP_SEQ=0/1 forces the choice (A/B checks);
-        # nsplit / mcast are the kernel's cluster options.
+        # Measured on B200: with the resident state slab it beats two tap-GEMM launches per step from 64 tiles up (128 clips,
+        # 2-CTA channel split: 2.18 vs 2.81 ms; 256 clips: 2.63 vs 3.9 ms; profiles/r01_notes.md) and, at hidden 256 with
+        # the channel split widened to 4 CTAs per tile, at every smaller batch too (profiles/r02_notes.md pass 49: 16 / 32 /
+        # 64 / 96 clips: recurrence 2.02 / 2.03 / 2.08 / 2.38 ms per-step against 1.78 / 1.79 / 1.80 / 1.88 ms).  Hidden 128
+        # below 64 tiles keeps the co-resident small-batch kernel or the per-step GEMMs.  RGP_SEQ=0/1 forces the choice
+        # (A/B checks); nsplit / mcast are the kernel's cluster options.
         mtiles = (B * self.S + 127) // 128
         seq_arg = seq
         if seq is None:
             env = os.environ.get("RGP_SEQ", "")
-            seq = (dtype == 1 and engine != 1 and Ch in (128, 256) and (env == "1" or (env != "0" and mtiles >= 64)))
+            seq = (dtype == 1 and engine != 1 and Ch in (128, 256) and
+                   (env == "1" or (env != "0" and (mtiles >= 64 or Ch == 256))))
         self.use_seq = bool(seq) and seq != "small" and (not self.lstm) and 128 % self.S == 0
         # Small-batch persistent ConvGRU (rgp_convgru_seq_small_fwd: weight slices resident in shared memory, two counter
         # exchanges per step) - the regime below gru_seq's 64 tiles where all tiles x Ch/16 CTAs are co-resident (hidden 128:
@@ -263,7 +266,9 @@ class GazeEngine(TrainStateMixin):
         self.use_seq_lstm = bool(self.lstm and seq_arg is not False and engine != 1 and fits is not None and
                                  (dtype == 1 or seq_arg is True) and fits(B, G, Ch) and
                                  os.environ.get("RGP_SEQ", "") != "0")
-        self.nsplit = nsplit or int(os.environ.get("RGP_SEQ_NSPLIT", "0")) or (2 if (Ch == 256 and mtiles <= 74) else 1)
+        # channel split at hidden 256: as many CTAs per tile (4, 2, 1) as keeps tiles x nsplit within one wave of 148 SMs
+        self.nsplit = nsplit or int(os.environ.get("RGP_SEQ_NSPLIT", "0")) or \
+            ((4 if mtiles <= 37 else 2 if mtiles <= 74 else 1) if Ch == 256 else 1)
         # Two tiles per CTA (ntile = 2, with the 2-CTA channel split): every streamed weight box feeds the MMAs of two tiles,
         # halving the bytes an SM pulls through its L2->SMEM port per MMA.  Parity-tested; MEASURED SLOWER at the bench batch
         # (recurrence 2.98 vs 2.29 ms at 256 clips, gpurun_out/r02p11_*): the phases are not bound by the weight stream

@@ -849,7 +849,7 @@ class EmuLib(object):
         Wp = G + 1
         S = Wp * Wp
         M = B * S
-        assert (any_grid or 128 % S == 0) and a.nsplit in (1, 2)
+        assert (any_grid or 128 % S == 0) and a.nsplit in (1, 2, 4)
         train = bool(a.Rs)
         taps = [ky * Wp + kx for ky in range(3) for kx in range(3)]
         rows_step = M + ((2 * Wp + 2 + 31) // 32) * 32

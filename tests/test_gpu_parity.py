@@ -257,6 +257,10 @@ def test_wgrad_matches_numpy(engine, M, Ny, Nx, ldy, ycol0, taps):
     ("gaze_grcn", 256, 5, 2, 1, True, 2),      # odd number of tiles: the second tile of the last pair is half / out of range
     ("gaze_grcn", 256, 2, 2, 1, True, 2),      # a single tile: the pair's second tile is a ghost
     ("gaze_grcn", 256, 600, 2, 1, False, 2),   # 150 pairs on 74 clusters: CTAs walk several pairs
+    ("gaze_grcn", 256, 6, 4, 1, False, 1),     # four CTAs per tile (64 channels each)
+    ("gaze_grcn", 256, 4, 4, 2, True, 1),      # 8-CTA clusters: 2 tiles x 4 channel quarters, training saves
+    ("gaze_grcn", 128, 5, 2, 1, True, 1),      # 64-channel slices at hidden 128
+    ("gaze_grcn", 256, 90, 4, 1, False, 1),    # 45 tiles x 4 = 180 CTAs on 148 SMs: clusters walk several tiles
 ])
 def test_persistent_recurrence_matches_per_step_path(model, Ch, B, nsplit, mcast, train, ntile):
     """rgp_convgru_seq_fwd (all T steps in one launch) against the per-step tap-GEMM path on the same bf16 operands and
