@@ -243,19 +243,22 @@ class GazeEngine(TrainStateMixin):
         # 2-CTA channel split: 2.18 vs 2.81 ms; 256 clips: 2.63 vs 3.9 ms; profiles/r01_notes.md) and, at hidden 256 with
         # the channel split widened to 4 CTAs per tile, at every smaller batch too (profiles/r02_notes.md pass 49: 16 / 32 /
         # 64 / 96 clips: recurrence 2.02 / 2.03 / 2.08 / 2.38 ms per-step against 1.78 / 1.79 / 1.80 / 1.88 ms).  Hidden 128
-        # below 64 tiles keeps the co-resident small-batch kernel or the per-step GEMMs.  RGP_SEQ=0/1 forces the choice
+        # likewise beyond the co-resident small-batch kernel's range (48 / 96 clips: 1.55 / 1.57 ms per-step against 0.98 / 0.99 ms
+        # with 64-channel slices).  RGP_SEQ=0/1 forces the choice
         # (A/B checks); nsplit / mcast are the kernel's cluster options.
         mtiles = (B * self.S + 127) // 128
         seq_arg = seq
+        gfits = getattr(self.lib, "rgp_convgru_seq_small_fits", None)
         if seq is None:
             env = os.environ.get("RGP_SEQ", "")
-            seq = (dtype == 1 and engine != 1 and Ch in (128, 256) and
-                   (env == "1" or (env != "0" and (mtiles >= 64 or Ch == 256))))
+            # the co-resident small-batch kernel (below) is the faster one where it fits (hidden <= 128, <= 36 clips)
+            small_ok = bool((not self.lstm) and engine != 1 and dtype == 1 and gfits is not None and gfits(B, G, Ch) and
+                            env != "0")
+            seq = (dtype == 1 and engine != 1 and Ch in (128, 256) and (env == "1" or (env != "0" and not small_ok)))
         self.use_seq = bool(seq) and seq != "small" and (not self.lstm) and 128 % self.S == 0
         # Small-batch persistent ConvGRU (rgp_convgru_seq_small_fwd: weight slices resident in shared memory, two counter
         # exchanges per step) - the regime below gru_seq's 64 tiles where all tiles x Ch/16 CTAs are co-resident (hidden 128:
         # up to 36 clips at 7x7, the reference's batch 28).
-        gfits = getattr(self.lib, "rgp_convgru_seq_small_fits", None)
         self.use_seq_small = bool((not self.lstm) and (not self.use_seq) and seq_arg is not False and engine != 1 and
                                   gfits is not None and (dtype == 1 or seq_arg == "small") and gfits(B, G, Ch) and
                                   os.environ.get("RGP_SEQ", "") != "0")
@@ -267,8 +270,9 @@ class GazeEngine(TrainStateMixin):
                                  (dtype == 1 or seq_arg is True) and fits(B, G, Ch) and
                                  os.environ.get("RGP_SEQ", "") != "0")
         # channel split at hidden 256: as many CTAs per tile (4, 2, 1) as keeps tiles x nsplit within one wave of 148 SMs
+        # (64-channel slices at the finest: 4-way at hidden 256, 2-way at hidden 128)
         self.nsplit = nsplit or int(os.environ.get("RGP_SEQ_NSPLIT", "0")) or \
-            ((4 if mtiles <= 37 else 2 if mtiles <= 74 else 1) if Ch == 256 else 1)
+            ((4 if mtiles <= 37 else 2 if mtiles <= 74 else 1) if Ch == 256 else (2 if (Ch == 128 and mtiles <= 74) else 1))
         # Two tiles per CTA (ntile = 2, with the 2-CTA channel split): every streamed weight box feeds the MMAs of two tiles,
         # halving the bytes an SM pulls through its L2->SMEM port per MMA.  Parity-tested; MEASURED SLOWER at the bench batch
         # (recurrence 2.98 vs 2.29 ms at 256 clips, gpurun_out/r02p11_*): the phases are not bound by the weight stream
